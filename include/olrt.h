@@ -1,0 +1,185 @@
+/* olrt.h -- C ABI of libolrt.so: fused sequential real-ray trace for NVIDIA B200 (sm_100a).
+ *
+ * The reference (Optiland fork, pure Python) has no FFI; the seam this library
+ * replaces is the method
+ *     SurfaceGroup.trace(self, rays, skip=0)      optiland/surfaces/surface_group.py:232-244
+ * i.e. `for surface in surfaces: surface.trace(rays)` with
+ *     Surface.trace                               optiland/surfaces/standard_surface.py:186-233
+ * and, for the optimiser, torch autograd through those same lines, plus the
+ * RMS-spot / centroid consumers
+ *     RayOperand.rms_spot_size                    optiland/optimization/operand/ray.py:299-340
+ *     SpotDiagram.centroid / rms_spot_radius      optiland/analysis/spot_diagram.py:317-357
+ * INTEGRATION.md shows the ctypes binding a maintainer adds on the reference side.
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes, no torch types.
+ *  - All array pointers are DEVICE pointers unless marked [host].
+ *  - The caller owns every buffer; the library never allocates, frees or keeps
+ *    a pointer past the call. Host structs are copied at enqueue time.
+ *  - Every call only ENQUEUES work on `stream` (a cudaStream_t passed as void*).
+ *  - Return 0 = enqueued; <0 = OLRT_E_* argument / launch error. Nothing throws.
+ *  - Data-dependent conditions are bits in a device `status` word.
+ */
+#ifndef OLRT_H
+#define OLRT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OLRT_ABI_VERSION 1
+
+#define OLRT_MAX_SURFACES 64    /* intersected surfaces per system (object surface excluded) */
+#define OLRT_MAX_WAVELENGTHS 8  /* distinct wavelengths per launch */
+#define OLRT_MAX_NR_ITERS 128   /* per-surface Newton trip count upper bound (reference default max_iter=100) */
+#define OLRT_OPS_STRIDE 16      /* int32 words per surface in the ops table */
+#define OLRT_RESID_STRIDE (OLRT_MAX_NR_ITERS + 1)
+#define OLRT_SPOT_SUMS 10       /* doubles per spot group, see olrt_spot_sums_* */
+
+/* error codes */
+#define OLRT_OK 0
+#define OLRT_E_ARG (-1)      /* null pointer / bad size / bad table */
+#define OLRT_E_LIMIT (-2)    /* exceeds an OLRT_MAX_* limit or shared memory */
+#define OLRT_E_LAUNCH (-3)   /* cudaGetLastError() != cudaSuccess after the launch */
+
+/* ops table, one row of OLRT_OPS_STRIDE int32 per intersected surface */
+enum {
+  OLRT_OP_GEOM = 0,      /* OLRT_GEOM_* */
+  OLRT_OP_INTERACT = 1,  /* 0 refract, 1 reflect */
+  OLRT_OP_FLAGS = 2,     /* OLRT_F_* */
+  OLRT_OP_DOFF = 3,      /* offset (in reals) of this surface's block inside one prescription */
+  OLRT_OP_NCOEF = 4,     /* even asphere: m; polynomial: I*J; zernike: number of terms */
+  OLRT_OP_AUX = 5,       /* polynomial: J (columns); zernike: offset (ints) of its (n,m) table in ops */
+  OLRT_OP_NR_ITERS = 6,  /* K_s: Newton updates to take at this surface (batch-uniform) */
+  OLRT_OP_APER_OFF = 7,  /* offset (ints) of the aperture program in ops, or -1 */
+  OLRT_OP_APER_LEN = 8,  /* tokens in the aperture program */
+  OLRT_OP_RECORD = 9,    /* record slot (>=0) or -1: post-interaction global state is stored */
+  OLRT_OP_NFRAMES = 10,  /* coordinate frames in the reference_cs chain, root first (>=1) */
+  OLRT_OP_FRAMEFLAGS = 11, /* 3 bits per frame: bit0 rz, bit1 ry, bit2 rx is "truthy" (rotation applied) */
+  OLRT_OP_APER_DOFF = 12 /* offset (in reals, inside the surface block) of aperture parameters */
+};
+
+enum {
+  OLRT_GEOM_PLANE = 0,        /* optiland/geometries/plane.py:61-98 */
+  OLRT_GEOM_STANDARD = 1,     /* optiland/geometries/standard.py:89-167 */
+  OLRT_GEOM_EVEN_ASPHERE = 2, /* optiland/geometries/even_asphere.py:82-129 + newton_raphson.py:119-168 */
+  OLRT_GEOM_POLYNOMIAL = 3,   /* optiland/geometries/polynomial.py:93-142 */
+  OLRT_GEOM_ZERNIKE = 4,      /* optiland/geometries/zernike.py:133-232 */
+  OLRT_GEOM_ODD_ASPHERE = 5   /* optiland/geometries/odd_asphere.py:73-129 */
+};
+
+enum {
+  OLRT_F_RADIUS_INF = 1,  /* StandardGeometry with infinite radius: clamped plane branch, standard.py:100-103 */
+  OLRT_F_ABSORB = 2       /* material_pre has k>0 for some wavelength: homogeneous.py:45-53 */
+};
+
+/* aperture program tokens (reverse Polish), optiland/physical_apertures/ */
+enum {
+  OLRT_AP_RADIAL = 1,        /* 2 reals: r_max^2, r_min^2            radial.py:56-70 */
+  OLRT_AP_OFFSET_RADIAL = 2, /* 4 reals: r_max^2, r_min^2, ox, oy    offset_radial.py:48 */
+  OLRT_AP_ELLIPTICAL = 3,    /* 4 reals: a^2, b^2, ox, oy            elliptical.py:42 */
+  OLRT_AP_RECTANGULAR = 4,   /* 4 reals: x_min, x_max, y_min, y_max  rectangular.py:42 */
+  OLRT_AP_OR = 10,           /* base.py:255-275 */
+  OLRT_AP_AND = 11,          /* base.py:278-300 */
+  OLRT_AP_DIFF = 12          /* base.py:303-336 */
+};
+
+/* Layout of one surface block of reals (double for *_f64, float for *_f32):
+ *   frames   : NFRAMES x 9  = x, y, z, cos rz, sin rz, cos ry, sin ry, cos rx, sin rx
+ *   geometry : radius, conic, tol, norm_radius
+ *   media    : n_pre[W], n_post[W], k_pre[W]            (W = n_wavelengths)
+ *   coefs    : NCOEF reals (even asphere C_i; polynomial C_ij row-major; zernike:
+ *              per term c_j*N_j followed by its radial-polynomial coefficients)
+ *   aperture : parameters of the aperture program leaves, in token order
+ */
+#define OLRT_FRAME_REALS 9
+#define OLRT_GEOM_REALS 4
+
+/* status bits (device word, OR-accumulated) */
+#define OLRT_ST_ZERNIKE_RANGE 1u /* |x/R_n|>1 or |y/R_n|>1 at a Zernike surface: zernike.py:234-246 */
+#define OLRT_ST_WAVELENGTH 2u    /* a ray wavelength is not in olrt_sys.wavelengths */
+
+typedef struct olrt_sys {
+  int32_t n_surfaces;     /* intersected surfaces */
+  int32_t n_wavelengths;  /* W, 1..OLRT_MAX_WAVELENGTHS */
+  int32_t n_presc;        /* prescriptions in the batch (Monte Carlo trials); >=1 */
+  int32_t presc_stride;   /* reals per prescription */
+  int32_t ops_len;        /* int32 words in ops */
+  int32_t n_record;       /* record slots */
+  int32_t nr_resid_words; /* sum over Newton surfaces of (K_s + 1): shared-memory words for nr_resid */
+  int32_t reserved0;
+  int64_t rays_per_presc; /* ray r uses prescription r / rays_per_presc (ignored if n_presc==1) */
+  double wavelengths[OLRT_MAX_WAVELENGTHS]; /* distinct wavelengths, micrometres */
+} olrt_sys;
+
+/* ray state, structure of arrays; 8 device pointers each of n_rays elements.
+ * in : x y z L M N intensity wavelength   (wavelength may be NULL when W==1)
+ * out: x y z L M N intensity opd          (may alias `in` element-wise)        */
+
+int olrt_version(void);
+const char* olrt_build_info(void);
+
+/* Forward trace: SurfaceGroup.trace for RealRays (surface_group.py:232-244).
+ *  presc      [n_presc][presc_stride] reals
+ *  ops        [ops_len] int32 (shared by all prescriptions)
+ *  opd_in     initial OPD (RealRays.opd), NULL = zeros
+ *  record     NULL or [n_record][8][n_rays]: x y z L M N intensity opd after each recorded surface
+ *  dir0       NULL or [3][n_rays]: L0 M0 N0, local pre-interaction direction at the last surface
+ *  nr_resid   NULL or [n_surfaces][OLRT_RESID_STRIDE] u64-ordered doubles, zero-initialised by the
+ *             caller: max over rays of |f| seen at Newton iteration j (NaN recorded as +inf)
+ *  status     NULL or one uint32, OR-accumulated
+ *  flags      OLRT_FWD_*                                                                  */
+#define OLRT_FWD_FAST 1 /* allow FMA contraction / reciprocal sharing (not bit-faithful to the reference) */
+
+int olrt_trace_fwd_f64(const olrt_sys* sys /*host*/, const double* presc, const int32_t* ops,
+                       int64_t n_rays, const double* const in[8] /*host array of device ptrs*/,
+                       const double* opd_in, double* const out[8] /*host array of device ptrs*/,
+                       double* record, double* dir0, unsigned long long* nr_resid,
+                       uint32_t* status, int flags, void* stream);
+int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
+                       int64_t n_rays, const float* const in[8], const float* opd_in,
+                       float* const out[8], float* record, float* dir0,
+                       unsigned long long* nr_resid, uint32_t* status, int flags, void* stream);
+
+/* Backward (adjoint) of the forward trace: what torch autograd computes through
+ * Surface.trace on the reference torch backend. Recomputes the forward from `in`.
+ *  gout   [8] device ptrs: grads w.r.t. out x y z L M N intensity opd (NULL entry = zero)
+ *  gin    [8] device ptrs: grads w.r.t. in  x y z L M N intensity opd_in (NULL entry = not wanted)
+ *  gpresc [n_presc][presc_stride] accumulated with atomicAdd (caller zero-initialises)   */
+int olrt_trace_bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops,
+                       int64_t n_rays, const double* const in[8], const double* opd_in,
+                       const double* const gout[8], double* const gin[8], double* gpresc,
+                       int flags, void* stream);
+int olrt_trace_bwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
+                       int64_t n_rays, const float* const in[8], const float* opd_in,
+                       const float* const gout[8], float* const gin[8], float* gpresc,
+                       int flags, void* stream);
+
+/* Spot epilogue: per-group sums over rays (ray r belongs to group r / rays_per_group).
+ *  sums [n_groups][OLRT_SPOT_SUMS] doubles, accumulated (caller zero-initialises):
+ *    0 count  1 sum dx  2 sum dy  3 sum dx^2  4 sum dy^2  5 max (dx^2+dy^2) (u64-ordered)
+ *    6 sum intensity  7 reserved  8 shift x  9 shift y       with dx = x - shift x, dy = y - shift y
+ *  shift  NULL or [n_groups][2]: subtracted before summing (pass the centroid to get the centred
+ *         second moments and the geometric radius of spot_diagram.py:329-357 in a second call);
+ *         NULL = the group's first ray if finite, else 0 (keeps the second moments well conditioned).
+ *  flags: OLRT_SPOT_VALID_ONLY = only rays with intensity>0 (SpotDiagram, spot_diagram.py:418-425);
+ *         otherwise all rays (RayOperand.rms_spot_size, ray.py:336-340).                   */
+#define OLRT_SPOT_VALID_ONLY 1
+int olrt_spot_sums_f64(const double* x, const double* y, const double* intensity, int64_t n_rays,
+                       int64_t rays_per_group, int32_t n_groups, const double* shift, int flags,
+                       double* sums, void* stream);
+int olrt_spot_sums_f32(const float* x, const float* y, const float* intensity, int64_t n_rays,
+                       int64_t rays_per_group, int32_t n_groups, const double* shift, int flags,
+                       double* sums, void* stream);
+
+/* Benchmark helper: dependent-free FMA chains on every SM; writes the measured
+ * flop count basis to `sink`. Used by bench.py to measure the FP64 / FP32 FMA peak. */
+int olrt_fma_peak_f64(double* sink, int64_t iters, int blocks, int threads, void* stream);
+int olrt_fma_peak_f32(float* sink, int64_t iters, int blocks, int threads, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OLRT_H */

@@ -1,0 +1,112 @@
+"""ctypes binding of libolrt.so (include/olrt.h).
+
+The library is built in-tree (`optiland_pr_b200/libolrt.so`, see csrc/Makefile and
+`__graft_entry__.build`). There is NO fallback: if the shared object is missing or a
+symbol is absent, loading raises -- the product path never silently runs on the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libolrt.so")
+
+OLRT_ABI_VERSION = 1
+MAX_SURFACES = 64
+MAX_WAVELENGTHS = 8
+MAX_NR_ITERS = 128
+OPS_STRIDE = 16
+RESID_STRIDE = MAX_NR_ITERS + 1
+SPOT_SUMS = 10
+FRAME_REALS = 9
+GEOM_REALS = 4
+
+# ops row fields
+(OP_GEOM, OP_INTERACT, OP_FLAGS, OP_DOFF, OP_NCOEF, OP_AUX, OP_NR_ITERS, OP_APER_OFF,
+ OP_APER_LEN, OP_RECORD, OP_NFRAMES, OP_FRAMEFLAGS, OP_APER_DOFF) = range(13)
+
+GEOM_PLANE, GEOM_STANDARD, GEOM_EVEN_ASPHERE, GEOM_POLYNOMIAL, GEOM_ZERNIKE, GEOM_ODD_ASPHERE = range(6)
+F_RADIUS_INF, F_ABSORB = 1, 2
+AP_RADIAL, AP_OFFSET_RADIAL, AP_ELLIPTICAL, AP_RECTANGULAR = 1, 2, 3, 4
+AP_OR, AP_AND, AP_DIFF = 10, 11, 12
+ST_ZERNIKE_RANGE, ST_WAVELENGTH = 1, 2
+FWD_FAST = 1
+SPOT_VALID_ONLY = 1
+
+ERRORS = {0: "ok", -1: "OLRT_E_ARG", -2: "OLRT_E_LIMIT", -3: "OLRT_E_LAUNCH"}
+
+
+class OlrtSys(C.Structure):
+    """struct olrt_sys (include/olrt.h)."""
+
+    _fields_ = [
+        ("n_surfaces", C.c_int32),
+        ("n_wavelengths", C.c_int32),
+        ("n_presc", C.c_int32),
+        ("presc_stride", C.c_int32),
+        ("ops_len", C.c_int32),
+        ("n_record", C.c_int32),
+        ("nr_resid_words", C.c_int32),
+        ("reserved0", C.c_int32),
+        ("rays_per_presc", C.c_int64),
+        ("wavelengths", C.c_double * MAX_WAVELENGTHS),
+    ]
+
+
+PtrArray8 = C.c_void_p * 8
+
+# every symbol include/olrt.h declares (tests/test_abi.py checks the header against this list)
+EXPORTS = [
+    "olrt_version", "olrt_build_info",
+    "olrt_trace_fwd_f64", "olrt_trace_fwd_f32",
+    "olrt_trace_bwd_f64", "olrt_trace_bwd_f32",
+    "olrt_spot_sums_f64", "olrt_spot_sums_f32",
+    "olrt_fma_peak_f64", "olrt_fma_peak_f32",
+]
+
+_lib = None
+
+
+class OlrtLibraryError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen libolrt.so and declare the prototypes. Raises if it is not there."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise OlrtLibraryError(
+            f"{LIB_PATH} not found: build it with `make -C optiland_pr_b200/csrc` "
+            "(or `python -c 'import __graft_entry__ as g; g.build()'`). There is no CPU fallback."
+        )
+    lib = C.CDLL(LIB_PATH)
+    for name in EXPORTS:
+        if not hasattr(lib, name):
+            raise OlrtLibraryError(f"libolrt.so does not export {name}")
+    lib.olrt_version.restype = C.c_int
+    lib.olrt_build_info.restype = C.c_char_p
+    v = C.c_void_p
+    fwd_args = [C.POINTER(OlrtSys), v, v, C.c_int64, PtrArray8, v, PtrArray8, v, v, v, v, C.c_int, v]
+    bwd_args = [C.POINTER(OlrtSys), v, v, C.c_int64, PtrArray8, v, PtrArray8, PtrArray8, v, C.c_int, v]
+    for suf in ("f64", "f32"):
+        f = getattr(lib, f"olrt_trace_fwd_{suf}")
+        f.restype, f.argtypes = C.c_int, fwd_args
+        f = getattr(lib, f"olrt_trace_bwd_{suf}")
+        f.restype, f.argtypes = C.c_int, bwd_args
+        f = getattr(lib, f"olrt_spot_sums_{suf}")
+        f.restype = C.c_int
+        f.argtypes = [v, v, v, C.c_int64, C.c_int64, C.c_int32, v, C.c_int, v, v]
+        f = getattr(lib, f"olrt_fma_peak_{suf}")
+        f.restype, f.argtypes = C.c_int, [v, C.c_int64, C.c_int, C.c_int, v]
+    if lib.olrt_version() != OLRT_ABI_VERSION:
+        raise OlrtLibraryError("libolrt.so ABI version mismatch; rebuild it")
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise OlrtLibraryError(f"{what} failed: {ERRORS.get(rc, rc)}")

@@ -1,0 +1,233 @@
+// olrt_api.cu -- the extern "C" boundary (include/olrt.h), the spot epilogue and the FMA-peak probe.
+#include <cuda_runtime.h>
+#include <math.h>
+#include "olrt_internal.h"
+
+// ---------------------------------------------------------------------------------------------
+// argument checks shared by fwd / bwd
+// ---------------------------------------------------------------------------------------------
+static int check_sys(const olrt_sys* sys, const void* presc, const void* ops, long long n_rays) {
+  if (!sys || !presc || !ops || n_rays < 0) return OLRT_E_ARG;
+  if (sys->n_surfaces < 1 || sys->n_surfaces > OLRT_MAX_SURFACES) return OLRT_E_LIMIT;
+  if (sys->n_wavelengths < 1 || sys->n_wavelengths > OLRT_MAX_WAVELENGTHS) return OLRT_E_LIMIT;
+  if (sys->n_presc < 1 || sys->presc_stride < 1) return OLRT_E_ARG;
+  if (sys->ops_len < sys->n_surfaces * OLRT_OPS_STRIDE) return OLRT_E_ARG;
+  if (sys->n_presc > 1) {
+    if (sys->rays_per_presc < 1) return OLRT_E_ARG;
+    if ((long long)sys->n_presc * sys->rays_per_presc < n_rays) return OLRT_E_ARG;
+  }
+  return OLRT_OK;
+}
+
+template <typename R>
+static int check_rays(const olrt_sys* sys, const R* const in[8], R* const out[8]) {
+  if (!in || !out) return OLRT_E_ARG;
+  for (int q = 0; q < 7; ++q)
+    if (!in[q]) return OLRT_E_ARG;
+  if (sys->n_wavelengths > 1 && !in[7]) return OLRT_E_ARG;
+  for (int q = 0; q < 8; ++q)
+    if (!out[q]) return OLRT_E_ARG;
+  return OLRT_OK;
+}
+
+extern "C" int olrt_version(void) { return OLRT_ABI_VERSION; }
+
+extern "C" const char* olrt_build_info(void) {
+  return "libolrt sm_100a; fp64 strict(-fmad=false)+fast, fp32 fast; built " __DATE__ " " __TIME__;
+}
+
+extern "C" int olrt_trace_fwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops,
+                                  int64_t n_rays, const double* const in[8], const double* opd_in,
+                                  double* const out[8], double* record, double* dir0,
+                                  unsigned long long* nr_resid, uint32_t* status, int flags,
+                                  void* stream) {
+  int rc = check_sys(sys, presc, ops, n_rays);
+  if (rc) return rc;
+  rc = check_rays<double>(sys, in, out);
+  if (rc) return rc;
+  if (sys->n_record > 0 && !record) return OLRT_E_ARG;
+  if (n_rays == 0) return OLRT_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (flags & OLRT_FWD_FAST)
+    return olrt_fast::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, st);
+  return olrt_strict::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, st);
+}
+
+extern "C" int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
+                                  int64_t n_rays, const float* const in[8], const float* opd_in,
+                                  float* const out[8], float* record, float* dir0,
+                                  unsigned long long* nr_resid, uint32_t* status, int flags,
+                                  void* stream) {
+  (void)flags;
+  int rc = check_sys(sys, presc, ops, n_rays);
+  if (rc) return rc;
+  rc = check_rays<float>(sys, in, out);
+  if (rc) return rc;
+  if (sys->n_record > 0 && !record) return OLRT_E_ARG;
+  if (n_rays == 0) return OLRT_OK;
+  return olrt_fast::fwd_f32(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status,
+                            (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Spot epilogue. One CTA owns a contiguous slice of rays and walks the groups it overlaps;
+// per group: register accumulation -> warp shuffles -> shared -> one set of atomics per CTA.
+//   RayOperand.rms_spot_size        optiland/optimization/operand/ray.py:336-340
+//   SpotDiagram.centroid/rms/geo    optiland/analysis/spot_diagram.py:317-357
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_maxd(double v) {
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_down_sync(0xffffffffu, v, o));
+  return v;
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256) spot_sums_kernel(const R* __restrict__ x, const R* __restrict__ y,
+                                                        const R* __restrict__ inten, long long n,
+                                                        long long rpg, int n_groups,
+                                                        const double* __restrict__ shift, int flags,
+                                                        double* sums) {
+  __shared__ double s_part[8][6];
+  const long long per = (n + gridDim.x - 1) / gridDim.x;
+  const long long lo = (long long)blockIdx.x * per;
+  long long hi = lo + per;
+  if (hi > n) hi = n;
+  if (lo >= hi) return;
+  const int g_lo = (int)(lo / rpg), g_hi = (int)((hi - 1) / rpg);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int g = g_lo; g <= g_hi && g < n_groups; ++g) {
+    long long a = (long long)g * rpg, b = a + rpg;
+    double sx0, sy0;
+    if (shift) { sx0 = shift[2 * g]; sy0 = shift[2 * g + 1]; }
+    else {
+      sx0 = (double)x[a]; sy0 = (double)y[a];
+      if (!isfinite(sx0)) sx0 = 0.0;
+      if (!isfinite(sy0)) sy0 = 0.0;
+    }
+    if (a < lo) a = lo;
+    if (b > hi) b = hi;
+    double cnt = 0, sx = 0, sy = 0, sxx = 0, syy = 0, mx = 0, si = 0;
+    bool mnan = false;
+    for (long long q = a + threadIdx.x; q < b; q += blockDim.x) {
+      const double iv = (double)inten[q];
+      if ((flags & OLRT_SPOT_VALID_ONLY) && !(iv > 0.0)) continue;
+      const double dx = (double)x[q] - sx0, dy = (double)y[q] - sy0;
+      cnt += 1.0; sx += dx; sy += dy; sxx += dx * dx; syy += dy * dy; si += iv;
+      const double r2 = dx * dx + dy * dy;
+      if (r2 != r2) mnan = true;
+      mx = fmax(mx, r2);
+    }
+    if (mnan) mx = __longlong_as_double(0x7ff8000000000000LL);
+    double v[6] = {cnt, sx, sy, sxx, syy, si};
+#pragma unroll
+    for (int k = 0; k < 6; ++k) v[k] = warp_sum(v[k]);
+    // NaN-propagating max: fmax drops NaN, so carry the flag through the count of NaN lanes
+    const unsigned nanmask = __ballot_sync(0xffffffffu, mnan);
+    double wm = warp_maxd(mnan ? 0.0 : mx);
+    __syncthreads();
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) s_part[warp][k] = v[k];
+    }
+    __shared__ double s_max[8];
+    __shared__ unsigned s_nan[8];
+    if (lane == 0) { s_max[warp] = wm; s_nan[warp] = nanmask; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const int nw = blockDim.x >> 5;
+      double t[6] = {0, 0, 0, 0, 0, 0}, m = 0;
+      unsigned anynan = 0;
+      for (int w = 0; w < nw; ++w) {
+        for (int k = 0; k < 6; ++k) t[k] += s_part[w][k];
+        m = fmax(m, s_max[w]);
+        anynan |= s_nan[w];
+      }
+      double* o = sums + (long long)g * OLRT_SPOT_SUMS;
+      atomicAdd(o + 0, t[0]); atomicAdd(o + 1, t[1]); atomicAdd(o + 2, t[2]);
+      atomicAdd(o + 3, t[3]); atomicAdd(o + 4, t[4]); atomicAdd(o + 6, t[5]);
+      unsigned long long key = anynan ? 0x7ff8000000000000ULL : (unsigned long long)__double_as_longlong(m);
+      atomicMax(reinterpret_cast<unsigned long long*>(o + 5), key);
+      o[8] = sx0; o[9] = sy0;  // identical from every CTA
+    }
+  }
+}
+
+template <typename R>
+static int launch_spot(const R* x, const R* y, const R* inten, long long n, long long rpg, int n_groups,
+                       const double* shift, int flags, double* sums, cudaStream_t st) {
+  if (!x || !y || !inten || !sums || n < 0 || n_groups < 1) return OLRT_E_ARG;
+  if (rpg < 1) rpg = n > 0 ? n : 1;
+  if (n == 0) return OLRT_OK;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  long long grid = (long long)sms * 8;
+  const long long max_grid = (n + 255) / 256;
+  if (grid > max_grid) grid = max_grid;
+  spot_sums_kernel<R><<<(unsigned)grid, 256, 0, st>>>(x, y, inten, n, rpg, n_groups, shift, flags, sums);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+
+extern "C" int olrt_spot_sums_f64(const double* x, const double* y, const double* intensity,
+                                  int64_t n_rays, int64_t rays_per_group, int32_t n_groups,
+                                  const double* shift, int flags, double* sums, void* stream) {
+  return launch_spot<double>(x, y, intensity, n_rays, rays_per_group, n_groups, shift, flags, sums,
+                             (cudaStream_t)stream);
+}
+extern "C" int olrt_spot_sums_f32(const float* x, const float* y, const float* intensity,
+                                  int64_t n_rays, int64_t rays_per_group, int32_t n_groups,
+                                  const double* shift, int flags, double* sums, void* stream) {
+  return launch_spot<float>(x, y, intensity, n_rays, rays_per_group, n_groups, shift, flags, sums,
+                            (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// FMA peak probe: 8 independent chains per thread, 2 flops per FMA.
+// flops = blocks * threads * iters * 8 * 2
+// ---------------------------------------------------------------------------------------------
+template <typename R>
+__global__ void fma_peak_kernel(R* sink, long long iters) {
+  R a0 = R(threadIdx.x) * R(1e-3), a1 = a0 + R(1), a2 = a0 + R(2), a3 = a0 + R(3);
+  R a4 = a0 + R(4), a5 = a0 + R(5), a6 = a0 + R(6), a7 = a0 + R(7);
+  const R m = R(0.999999), c = R(1e-7);
+  for (long long q = 0; q < iters; ++q) {
+    a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+    a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+  }
+  const R s = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+  if (s == R(-1)) sink[0] = s;  // never true; keeps the chains alive
+}
+
+extern "C" int olrt_fma_peak_f64(double* sink, int64_t iters, int blocks, int threads, void* stream) {
+  if (!sink || iters < 1 || blocks < 1 || threads < 1 || threads > 1024) return OLRT_E_ARG;
+  fma_peak_kernel<double><<<blocks, threads, 0, (cudaStream_t)stream>>>(sink, iters);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+extern "C" int olrt_fma_peak_f32(float* sink, int64_t iters, int blocks, int threads, void* stream) {
+  if (!sink || iters < 1 || blocks < 1 || threads < 1 || threads > 1024) return OLRT_E_ARG;
+  fma_peak_kernel<float><<<blocks, threads, 0, (cudaStream_t)stream>>>(sink, iters);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+
+// ---------------------------------------------------------------------------------------------
+// backward (adjoint) entry points
+// ---------------------------------------------------------------------------------------------
+extern "C" int olrt_trace_bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops,
+                                  int64_t n_rays, const double* const in[8], const double* opd_in,
+                                  const double* const gout[8], double* const gin[8], double* gpresc,
+                                  int flags, void* stream) {
+  (void)sys; (void)presc; (void)ops; (void)n_rays; (void)in; (void)opd_in; (void)gout; (void)gin;
+  (void)gpresc; (void)flags; (void)stream;
+  return OLRT_E_ARG;  // filled in by the backward milestone
+}
+extern "C" int olrt_trace_bwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
+                                  int64_t n_rays, const float* const in[8], const float* opd_in,
+                                  const float* const gout[8], float* const gin[8], float* gpresc,
+                                  int flags, void* stream) {
+  (void)sys; (void)presc; (void)ops; (void)n_rays; (void)in; (void)opd_in; (void)gout; (void)gin;
+  (void)gpresc; (void)flags; (void)stream;
+  return OLRT_E_ARG;
+}

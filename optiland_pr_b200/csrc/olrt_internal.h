@@ -1,0 +1,14 @@
+// olrt_internal.h -- launch entry points exported by the two kernel translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include "../../include/olrt.h"
+
+#define OLRT_DECL_FWD(NS, SUF, R)                                                                  \
+  namespace NS {                                                                                   \
+  int fwd_##SUF(const olrt_sys* sys, const R* presc, const int32_t* ops, long long n_rays,         \
+                const R* const in[8], const R* opd_in, R* const out[8], R* record, R* dir0,        \
+                unsigned long long* nr_resid, uint32_t* status, cudaStream_t stream);              \
+  }
+OLRT_DECL_FWD(olrt_strict, f64, double)
+OLRT_DECL_FWD(olrt_fast, f64, double)
+OLRT_DECL_FWD(olrt_fast, f32, float)

@@ -1,0 +1,260 @@
+// trace_common.cuh -- device-side building blocks of the fused sequential ray trace.
+//
+// Every function restates one piece of the reference's per-surface arithmetic
+// (file:line cited at each function) for ONE ray held in registers. Operation
+// order follows the reference line by line so that the strict build
+// (-fmad=false) reproduces NumPy float64 bit-for-bit for + - * / sqrt.
+//
+// This header is compiled into two translation units:
+//   trace_strict.cu  (-fmad=false)  namespace olrt_strict   fp64
+//   trace_fast.cu    (-fmad=true)   namespace olrt_fast     fp64 + fp32
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/olrt.h"
+
+namespace OLRT_NS {
+
+template <typename R>
+struct RayState {
+  R x, y, z, L, M, N, i, opd;
+};
+
+template <typename R> __device__ __forceinline__ R r_sqrt(R v);
+template <> __device__ __forceinline__ double r_sqrt<double>(double v) { return sqrt(v); }
+template <> __device__ __forceinline__ float r_sqrt<float>(float v) { return sqrtf(v); }
+template <typename R> __device__ __forceinline__ R r_abs(R v);
+template <> __device__ __forceinline__ double r_abs<double>(double v) { return fabs(v); }
+template <> __device__ __forceinline__ float r_abs<float>(float v) { return fabsf(v); }
+template <typename R> __device__ __forceinline__ R r_exp(R v);
+template <> __device__ __forceinline__ double r_exp<double>(double v) { return exp(v); }
+template <> __device__ __forceinline__ float r_exp<float>(float v) { return expf(v); }
+
+// np.sign semantics: -1, 0, +1, NaN -> NaN   (real_rays.py:541)
+template <typename R>
+__device__ __forceinline__ R r_sign(R v) {
+  return (v > R(0)) ? R(1) : ((v < R(0)) ? R(-1) : ((v == R(0)) ? R(0) : v));
+}
+
+// ---------------------------------------------------------------------------
+// CoordinateSystem.localize / globalize     coordinate_system.py:73-107
+// RealRays.rotate_x/y/z                     rays/real_rays.py:90-130
+// BaseRays.translate                        rays/base.py:28-42
+// One frame = x y z cz sz cy sy cx sx ; fl bit0 rz, bit1 ry, bit2 rx truthy.
+// ---------------------------------------------------------------------------
+template <typename R>
+__device__ __forceinline__ void frame_localize(RayState<R>& r, const R* f, int fl) {
+  r.x = r.x + (-f[0]);
+  r.y = r.y + (-f[1]);
+  r.z = r.z + (-f[2]);
+  if (fl & 1) {  // rotate_z(-rz): cos(-a)=cos a, sin(-a)=-sin a
+    const R c = f[3], s = -f[4];
+    const R x = r.x * c - r.y * s, y = r.x * s + r.y * c;
+    const R L = r.L * c - r.M * s, M = r.L * s + r.M * c;
+    r.x = x; r.y = y; r.L = L; r.M = M;
+  }
+  if (fl & 2) {  // rotate_y(-ry)
+    const R c = f[5], s = -f[6];
+    const R x = r.x * c + r.z * s, z = (-r.x) * s + r.z * c;
+    const R L = r.L * c + r.N * s, N = (-r.L) * s + r.N * c;
+    r.x = x; r.z = z; r.L = L; r.N = N;
+  }
+  if (fl & 4) {  // rotate_x(-rx)
+    const R c = f[7], s = -f[8];
+    const R y = r.y * c - r.z * s, z = r.y * s + r.z * c;
+    const R M = r.M * c - r.N * s, N = r.M * s + r.N * c;
+    r.y = y; r.z = z; r.M = M; r.N = N;
+  }
+}
+
+template <typename R>
+__device__ __forceinline__ void frame_globalize(RayState<R>& r, const R* f, int fl) {
+  if (fl & 4) {  // rotate_x(rx)
+    const R c = f[7], s = f[8];
+    const R y = r.y * c - r.z * s, z = r.y * s + r.z * c;
+    const R M = r.M * c - r.N * s, N = r.M * s + r.N * c;
+    r.y = y; r.z = z; r.M = M; r.N = N;
+  }
+  if (fl & 2) {  // rotate_y(ry)
+    const R c = f[5], s = f[6];
+    const R x = r.x * c + r.z * s, z = (-r.x) * s + r.z * c;
+    const R L = r.L * c + r.N * s, N = (-r.L) * s + r.N * c;
+    r.x = x; r.z = z; r.L = L; r.N = N;
+  }
+  if (fl & 1) {  // rotate_z(rz)
+    const R c = f[3], s = f[4];
+    const R x = r.x * c - r.y * s, y = r.x * s + r.y * c;
+    const R L = r.L * c - r.M * s, M = r.L * s + r.M * c;
+    r.x = x; r.y = y; r.L = L; r.M = M;
+  }
+  r.x = r.x + f[0];
+  r.y = r.y + f[1];
+  r.z = r.z + f[2];
+}
+
+// chain: reference_cs first on the way in, last on the way out
+template <typename R>
+__device__ __forceinline__ void cs_localize(RayState<R>& r, const R* frames, int nframes, int flags) {
+  for (int q = 0; q < nframes; ++q)
+    frame_localize(r, frames + q * OLRT_FRAME_REALS, (flags >> (3 * q)) & 7);
+}
+template <typename R>
+__device__ __forceinline__ void cs_globalize(RayState<R>& r, const R* frames, int nframes, int flags) {
+  for (int q = nframes - 1; q >= 0; --q)
+    frame_globalize(r, frames + q * OLRT_FRAME_REALS, (flags >> (3 * q)) & 7);
+}
+
+// ---------------------------------------------------------------------------
+// StandardGeometry.distance                 geometries/standard.py:89-140
+// ---------------------------------------------------------------------------
+template <typename R>
+__device__ __forceinline__ R conic_distance(const RayState<R>& r, R radius, R k, bool radius_inf) {
+  if (radius_inf) {  // standard.py:100-103
+    const R Ns = (r_abs(r.N) > R(1e-14)) ? r.N : R(1e-14);
+    return (-r.z) / Ns;
+  }
+  const R N2 = r.N * r.N;
+  const R a = k * N2 + r.L * r.L + r.M * r.M + N2;
+  const R b = (R(2) * k) * r.N * r.z + (R(2) * r.L) * r.x + (R(2) * r.M) * r.y -
+              (R(2) * r.N) * radius + (R(2) * r.N) * r.z;
+  const R z2 = r.z * r.z;
+  const R c = k * z2 - (R(2) * radius) * r.z + r.x * r.x + r.y * r.y + z2;
+  const R d = b * b - (R(4) * a) * c;
+  const R sd = r_sqrt(d);
+  const R a2 = R(2) * a;
+  const R t1 = ((-b) + sd) / a2;
+  const R t2 = ((-b) - sd) / a2;
+  const R z1 = r.z + t1 * r.N;
+  const R zz2 = r.z + t2 * r.N;
+  R t = (r_abs(z1) <= r_abs(zz2)) ? t1 : t2;
+  if (a == R(0)) t = (-c) / b;
+  return t;
+}
+
+// conic part of the sag and of the slope denominator, shared by every NR geometry
+// sag:   r2 / (R * (1 + sqrt(1 - (1+k) r2 / R^2)))     standard.py:73-87
+// denom: R * sqrt(1 - (1+k) r2 / R^2)                  standard.py:154-156
+template <typename R>
+__device__ __forceinline__ void conic_sag_denom(R r2, R radius, R k, R& sag, R& denom) {
+  const R s = r_sqrt(R(1) - (R(1) + k) * r2 / (radius * radius));
+  sag = r2 / (radius * (R(1) + s));
+  denom = radius * s;
+}
+
+// StandardGeometry.surface_normal           geometries/standard.py:142-167
+template <typename R>
+__device__ __forceinline__ void conic_normal(R x, R y, R radius, R k, R& nx, R& ny, R& nz) {
+  const R r2 = x * x + y * y;
+  const R denom = radius * r_sqrt(R(1) - (R(1) + k) * r2 / (radius * radius));
+  const R dfdx = x / denom, dfdy = y / denom;
+  const R mag = r_sqrt(dfdx * dfdx + dfdy * dfdy + R(1));
+  nx = dfdx / mag;
+  ny = dfdy / mag;
+  nz = R(-1) / mag;
+}
+
+// slopes -> unit normal, common tail of every NR geometry's _surface_normal
+template <typename R>
+__device__ __forceinline__ void slopes_to_normal(R zx, R zy, R& nx, R& ny, R& nz) {
+  const R mag = r_sqrt(zx * zx + zy * zy + R(1));
+  nx = zx / mag;
+  ny = zy / mag;
+  nz = R(-1) / mag;
+}
+
+// ---------------------------------------------------------------------------
+// RealRays.refract / reflect / _align_surface_normal   rays/real_rays.py:141-181, 511-547
+// ---------------------------------------------------------------------------
+template <typename R>
+__device__ __forceinline__ void refract(RayState<R>& r, R nx, R ny, R nz, R n1, R n2) {
+  const R L0 = r.L, M0 = r.M, N0 = r.N;
+  const R u = n1 / n2;
+  R dot = L0 * nx + M0 * ny + N0 * nz;
+  const R sg = r_sign(dot);
+  nx = nx * sg; ny = ny * sg; nz = nz * sg;
+  dot = r_abs(dot);
+  const R root = r_sqrt(R(1) - (u * u) * (R(1) - dot * dot));  // NaN => TIR
+  r.L = u * L0 + nx * root - (u * nx) * dot;
+  r.M = u * M0 + ny * root - (u * ny) * dot;
+  r.N = u * N0 + nz * root - (u * nz) * dot;
+}
+
+template <typename R>
+__device__ __forceinline__ void reflect(RayState<R>& r, R nx, R ny, R nz) {
+  R dot = r.L * nx + r.M * ny + r.N * nz;
+  const R sg = r_sign(dot);
+  nx = nx * sg; ny = ny * sg; nz = nz * sg;
+  dot = r_abs(dot);
+  const R d2 = R(2) * dot;
+  r.L = r.L - d2 * nx;
+  r.M = r.M - d2 * ny;
+  r.N = r.N - d2 * nz;
+}
+
+// ---------------------------------------------------------------------------
+// Aperture program (reverse Polish) on local x, y     physical_apertures/*.py
+// ---------------------------------------------------------------------------
+template <typename R>
+__device__ __forceinline__ bool aperture_contains(const int32_t* prog, int len, const R* p, R x, R y) {
+  uint32_t stack = 0;  // bit stack, top = bit 0
+  for (int q = 0; q < len; ++q) {
+    const int tok = prog[q];
+    bool v;
+    switch (tok) {
+      case OLRT_AP_RADIAL: {  // radial.py:56-70
+        const R r2 = x * x + y * y;
+        v = (r2 <= p[0]) & (r2 >= p[1]);
+        p += 2;
+        stack = (stack << 1) | (v ? 1u : 0u);
+        break;
+      }
+      case OLRT_AP_OFFSET_RADIAL: {  // offset_radial.py:48
+        const R dx = x - p[2], dy = y - p[3];
+        const R r2 = dx * dx + dy * dy;
+        v = (r2 <= p[0]) & (r2 >= p[1]);
+        p += 4;
+        stack = (stack << 1) | (v ? 1u : 0u);
+        break;
+      }
+      case OLRT_AP_ELLIPTICAL: {  // elliptical.py:42
+        const R dx = x - p[2], dy = y - p[3];
+        v = ((dx * dx) / p[0] + (dy * dy) / p[1]) <= R(1);
+        p += 4;
+        stack = (stack << 1) | (v ? 1u : 0u);
+        break;
+      }
+      case OLRT_AP_RECTANGULAR: {  // rectangular.py:42
+        v = (p[0] <= x) & (x <= p[1]) & (p[2] <= y) & (y <= p[3]);
+        p += 4;
+        stack = (stack << 1) | (v ? 1u : 0u);
+        break;
+      }
+      default: {  // boolean nodes, base.py:255-336: operands a (below) and b (top)
+        const uint32_t b = stack & 1u, a = (stack >> 1) & 1u;
+        uint32_t o;
+        if (tok == OLRT_AP_OR) o = a | b;
+        else if (tok == OLRT_AP_AND) o = a & b;
+        else o = a & (b ^ 1u);
+        stack = ((stack >> 2) << 1) | o;
+        break;
+      }
+    }
+  }
+  return (stack & 1u) != 0;
+}
+
+// ordered-uint64 view of a non-negative double; NaN -> +inf pattern
+__device__ __forceinline__ unsigned long long resid_bits(double a) {
+  if (!(a == a)) a = __longlong_as_double(0x7ff0000000000000LL);
+  return (unsigned long long)__double_as_longlong(a);
+}
+
+// warp max of u64 keys with two 32-bit redux ops, result valid on all lanes
+__device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v) {
+  const uint32_t hi = (uint32_t)(v >> 32), lo = (uint32_t)v;
+  const uint32_t mhi = __reduce_max_sync(0xffffffffu, hi);
+  const uint32_t mlo = __reduce_max_sync(0xffffffffu, (hi == mhi) ? lo : 0u);
+  return ((unsigned long long)mhi << 32) | mlo;
+}
+
+}  // namespace OLRT_NS

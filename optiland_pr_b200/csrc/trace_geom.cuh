@@ -1,0 +1,196 @@
+// trace_geom.cuh -- sag f(x,y) and slopes (df/dx, df/dy) of the Newton-Raphson geometries.
+// Each evaluator returns the sag and, when WANT_SLOPES, the un-normalised slopes that the
+// reference's `_surface_normal` turns into (zx, zy, -1)/|.|.
+#pragma once
+#include "trace_common.cuh"
+
+namespace OLRT_NS {
+
+template <typename R>
+struct SurfParams {      // one surface's view of the prescription staged in shared memory
+  const int32_t* op;     // ops row
+  const int32_t* ops;    // ops base (aperture programs, zernike index tables)
+  const R* frames;       // NFRAMES x 9
+  R radius, conic, tol, norm_radius;
+  const R* media;        // n_pre[W], n_post[W], k_pre[W]
+  const R* coef;         // NCOEF reals
+  const R* aper;         // aperture leaf parameters
+  int geom, ncoef, aux;
+};
+
+template <typename R>
+__device__ __forceinline__ R ipow(R b, int e) {  // b**e by repeated multiplication, e >= 0
+  R p = R(1);
+  for (int q = 0; q < e; ++q) p = p * b;
+  return p;
+}
+
+// EvenAsphere.sag / _surface_normal         geometries/even_asphere.py:82-129
+template <typename R, bool WANT_SLOPES>
+__device__ __forceinline__ void even_asphere_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy) {
+  const R r2 = x * x + y * y;
+  R denom;
+  conic_sag_denom(r2, sp.radius, sp.conic, sag, denom);
+  if (WANT_SLOPES) { zx = x / denom; zy = y / denom; }
+  R pw = R(1);  // r2**i
+  for (int i = 0; i < sp.ncoef; ++i) {
+    const R Ci = sp.coef[i];
+    if (WANT_SLOPES) {
+      const R two_i1 = R(2 * (i + 1));
+      zx = zx + ((two_i1 * x) * Ci) * pw;  // 2*(i+1)*x*Ci*r2**i
+      zy = zy + ((two_i1 * y) * Ci) * pw;
+    }
+    pw = pw * r2;           // r2**(i+1)
+    sag = sag + Ci * pw;    // z + Ci*r2**(i+1)
+  }
+}
+
+// OddAsphere.sag / _surface_normal          geometries/odd_asphere.py:73-129
+template <typename R, bool WANT_SLOPES>
+__device__ __forceinline__ void odd_asphere_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy) {
+  const R r2 = x * x + y * y;
+  const R r = r_sqrt(r2);
+  R denom;
+  conic_sag_denom(r2, sp.radius, sp.conic, sag, denom);
+  if (WANT_SLOPES) { zx = x / denom; zy = y / denom; }
+  R pw = R(1);  // r**i
+  for (int i = 0; i < sp.ncoef; ++i) {
+    const R Ci = sp.coef[i];
+    if (WANT_SLOPES) {
+      // (i+1)*x*Ci*r**(i-1); non-finite terms are zeroed (odd_asphere.py:117-118)
+      const R rp = (i == 0) ? (R(1) / r) : ipow(r, i - 1);
+      R xt = ((R(i + 1) * x) * Ci) * rp;
+      R yt = ((R(i + 1) * y) * Ci) * rp;
+      if (!isfinite(xt)) xt = R(0);
+      if (!isfinite(yt)) yt = R(0);
+      zx = zx + xt;
+      zy = zy + yt;
+    }
+    pw = pw * r;            // r**(i+1)
+    sag = sag + Ci * pw;
+  }
+}
+
+// PolynomialGeometry.sag / _surface_normal  geometries/polynomial.py:93-142
+// coef = C[i][j] row-major, I = ncoef/J rows, J = aux columns
+template <typename R, bool WANT_SLOPES>
+__device__ __forceinline__ void polynomial_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy) {
+  const R r2 = x * x + y * y;
+  R denom;
+  conic_sag_denom(r2, sp.radius, sp.conic, sag, denom);
+  if (WANT_SLOPES) { zx = x / denom; zy = y / denom; }
+  const int J = sp.aux, I = (J > 0) ? sp.ncoef / J : 0;
+  R xi = R(1), xim1 = R(0);  // x**i, x**(i-1)
+  for (int i = 0; i < I; ++i) {
+    R yj = R(1);
+    for (int j = 0; j < J; ++j) {
+      const R C = sp.coef[i * J + j];
+      sag = sag + (C * xi) * yj;
+      if (WANT_SLOPES) {
+        if (i >= 1) zx = zx + ((R(i) * C) * xim1) * yj;
+      }
+      yj = yj * y;
+    }
+    xim1 = xi;
+    xi = xi * x;
+  }
+  if (WANT_SLOPES) {  // second pass, same order as the reference's dzdy loop
+    R xi2 = R(1);
+    for (int i = 0; i < I; ++i) {
+      R yjm1 = R(1);  // y**(j-1) starting at j=1
+      for (int j = 1; j < J; ++j) {
+        const R C = sp.coef[i * J + j];
+        zy = zy + ((R(j) * C) * xi2) * yjm1;
+        yjm1 = yjm1 * y;
+      }
+      xi2 = xi2 * x;
+    }
+  }
+}
+
+// ZernikePolynomialGeometry.sag / _surface_normal   geometries/zernike.py:133-232
+// BaseZernike.get_term/_radial_term/_azimuthal_term/get_derivative/_radial_derivative
+//                                                   zernike/base.py:42-299
+// Per term in coef: c, c*N, rc_0 .. rc_{smax-1}  (radial coefficients, highest power first),
+// (n, m) pairs in ops at sp.aux. cos/sin(m phi) by angle-addition from cos phi = x/rho.
+template <typename R, bool WANT_SLOPES>
+__device__ __forceinline__ void zernike_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy,
+                                             uint32_t& status) {
+  const R Rn = sp.norm_radius;
+  const R xn = x / Rn, yn = y / Rn;
+  if (r_abs(xn) > R(1) || r_abs(yn) > R(1)) status |= OLRT_ST_ZERNIKE_RANGE;  // zernike.py:234-246
+  const R rho2 = xn * xn + yn * yn;
+  const R rho = r_sqrt(rho2);
+  // phi = arctan2(yn, xn); arctan2(0,0)=0
+  R cph = R(1), sph = R(0);
+  if (rho > R(0)) { cph = xn / rho; sph = yn / rho; }
+  const R r2 = x * x + y * y;
+  R denom;
+  conic_sag_denom(r2, sp.radius, sp.conic, sag, denom);
+  R drho_dx = R(0), drho_dy = R(0), dphi_dx = R(0), dphi_dy = R(0);
+  if (WANT_SLOPES) {
+    zx = x / denom; zy = y / denom;
+    const R eps = R(1e-14);
+    const R Rn2 = Rn * Rn;
+    drho_dx = (x / Rn2) / (rho + eps);
+    drho_dy = (y / Rn2) / (rho + eps);
+    dphi_dx = (-yn) / (rho2 + eps) * (R(1) / Rn);
+    dphi_dy = (xn) / (rho2 + eps) * (R(1) / Rn);
+  }
+  R zsum = R(0);
+  const int32_t* nm = sp.ops + sp.aux;
+  const R* tc = sp.coef;
+  const int nterms = sp.ncoef;
+  for (int j = 0; j < nterms; ++j) {
+    const int n = nm[2 * j], m = nm[2 * j + 1];
+    const int ma = (m < 0) ? -m : m;
+    const int smax = (n - ma) / 2 + 1;
+    const R c = tc[0], cN = tc[1];
+    const R* rc = tc + 2;
+    tc += 2 + smax;
+    // cos(ma*phi), sin(ma*phi)
+    R cm = R(1), sm = R(0);
+    for (int q = 0; q < ma; ++q) {
+      const R cn = cm * cph - sm * sph;
+      sm = sm * cph + cm * sph;
+      cm = cn;
+    }
+    // radial polynomial and derivative (Horner in rho^2)
+    R H = R(0), Hd = R(0);
+    for (int k = 0; k < smax; ++k) {
+      H = H * rho2 + rc[k];
+      if (WANT_SLOPES) {
+        const int e = n - 2 * k;  // power of this term
+        if (ma > 0 || k < smax - 1) Hd = Hd * rho2 + rc[k] * R(e);
+      }
+    }
+    const R rm = ipow(rho, ma);
+    const R Rad = H * rm;
+    const R az = (m >= 0) ? cm : sm;
+    zsum = zsum + (cN * Rad) * az;
+    if (WANT_SLOPES && c != R(0)) {
+      const R dRad = (ma > 0) ? Hd * ipow(rho, ma - 1) : Hd * rho;
+      R dZdr, dZdp;
+      if (m == 0) { dZdr = dRad; dZdp = R(0); }
+      else if (m > 0) { dZdr = dRad * cm; dZdp = R(-m) * Rad * sm; }
+      else { dZdr = dRad * sm; dZdp = R(ma) * Rad * cm; }
+      zx = zx + c * (dZdr * drho_dx + dZdp * dphi_dx);
+      zy = zy + c * (dZdr * drho_dy + dZdp * dphi_dy);
+    }
+  }
+  sag = sag + zsum;
+}
+
+// dispatch: sag (and slopes) of an NR geometry at (x, y)
+template <typename R, bool WANT_SLOPES>
+__device__ __forceinline__ void nr_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy,
+                                        uint32_t& status) {
+  switch (sp.geom) {
+    case OLRT_GEOM_EVEN_ASPHERE: even_asphere_eval<R, WANT_SLOPES>(sp, x, y, sag, zx, zy); break;
+    case OLRT_GEOM_ODD_ASPHERE: odd_asphere_eval<R, WANT_SLOPES>(sp, x, y, sag, zx, zy); break;
+    case OLRT_GEOM_POLYNOMIAL: polynomial_eval<R, WANT_SLOPES>(sp, x, y, sag, zx, zy); break;
+    default: zernike_eval<R, WANT_SLOPES>(sp, x, y, sag, zx, zy, status); break;
+  }
+}
+
+}  // namespace OLRT_NS

@@ -1,0 +1,56 @@
+// trace_launch.cuh -- host-side launchers, instantiated once per translation unit
+// (strict / fast). Grid = one wave of persistent CTAs: SM count x resident CTAs per SM.
+#pragma once
+#include "trace_fwd.cuh"
+#include "trace_bwd.cuh"
+
+namespace OLRT_NS {
+
+inline int sm_count() {
+  int dev = 0, n = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess)
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  return n > 0 ? n : 148;
+}
+
+// block size: 256 unless the prescription batch needs tiles that do not straddle prescriptions
+inline int pick_block(const olrt_sys* sys) {
+  if (sys->n_presc <= 1) return 256;
+  for (int b = 256; b >= 32; b >>= 1)
+    if (sys->rays_per_presc % b == 0) return b;
+  return 0;
+}
+
+template <typename R>
+int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
+               long long n_rays, const R* const in[8], const R* opd_in, R* const out[8], R* record,
+               R* dir0, unsigned long long* nr_resid, uint32_t* status, cudaStream_t stream) {
+  FwdParams<R> P;
+  for (int q = 0; q < 8; ++q) { P.in[q] = in[q]; P.out[q] = out[q]; }
+  P.opd_in = opd_in; P.record = record; P.dir0 = dir0; P.presc = presc; P.ops = ops;
+  P.nr_resid = nr_resid; P.status = status; P.n_rays = n_rays;
+  P.rays_per_presc = sys->rays_per_presc > 0 ? sys->rays_per_presc : n_rays;
+  P.n_surfaces = sys->n_surfaces; P.n_wavelengths = sys->n_wavelengths; P.n_presc = sys->n_presc;
+  P.presc_stride = sys->presc_stride; P.ops_len = sys->ops_len; P.n_record = sys->n_record;
+  for (int q = 0; q < OLRT_MAX_WAVELENGTHS; ++q) P.wavelengths[q] = (R)sys->wavelengths[q];
+  P.four_pi = (R)(4.0 * 3.141592653589793);
+
+  const int block = pick_block(sys);
+  if (block == 0) return OLRT_E_ARG;
+  const size_t smem = (size_t)((sys->presc_stride + 1) & ~1) * sizeof(R) +
+                      (size_t)((sys->ops_len + 1) & ~1) * sizeof(int32_t) +
+                      (size_t)(nr_resid ? sys->nr_resid_words : 0) * sizeof(unsigned long long);
+  if (smem > 200 * 1024) return OLRT_E_LIMIT;
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(trace_fwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int per_sm = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fwd_kernel<R>, block, smem);
+  if (per_sm < 1) per_sm = 1;
+  const long long n_tiles = (n_rays + block - 1) / block;
+  long long grid = (long long)sm_count() * per_sm;
+  if (grid > n_tiles) grid = n_tiles;
+  trace_fwd_kernel<R><<<(unsigned)grid, block, smem, stream>>>(P);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+
+}  // namespace OLRT_NS

@@ -1,0 +1,13 @@
+// Strict build: compiled with -fmad=false so that every + - * / sqrt rounds exactly where the
+// reference's NumPy float64 expression rounds (bit-identical vignetting masks).
+#define OLRT_NS olrt_strict
+#include "trace_launch.cuh"
+#include "olrt_internal.h"
+
+namespace olrt_strict {
+int fwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, long long n_rays,
+            const double* const in[8], const double* opd_in, double* const out[8], double* record,
+            double* dir0, unsigned long long* nr_resid, uint32_t* status, cudaStream_t stream) {
+  return launch_fwd<double>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, stream);
+}
+}  // namespace olrt_strict

@@ -1,0 +1,150 @@
+"""Optic facade for the hot path: the calls analyses and operands make before reading
+`surface_group.x[-1, :]`.
+
+    Optic.add_surface / add_field / add_wavelength / set_aperture   optiland/optic/optic.py
+    Optic.trace(Hx, Hy, wavelength, num_rays, distribution)         optic.py:584-609
+    Optic.trace_generic(Hx, Hy, Px, Py, wavelength)                 optic.py:611-632
+    RealRayTracer.trace / trace_generic                             raytrace/real_ray_tracer.py:37-133
+    RayGenerator.generate_rays (infinite-object AngleField branch)  rays/ray_generator.py:28-106,
+                                                                    fields/field_types.py:139-169
+
+Scope notes: ray generation here is the infinite-conjugate angle-field case
+without vignetting factors; the first-order quantities EPL / EPD it needs are INPUTS
+(`set_paraxial`) because the paraxial tracer (optiland/paraxial.py) is outside the hot path.
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+
+from . import backend as be
+from .rays import RealRays
+from .surfaces import SurfaceGroup
+
+
+def pupil_points(distribution: str, num_rays: int, seed=None):
+    """Pupil sampling, host side (optiland/distribution.py): 'random' (:132-158, r=sqrt(U),
+    theta=2*pi*U from numpy default_rng(seed)), 'hexapolar' (:189-220), 'uniform'."""
+    if distribution == "random":
+        rng = np.random.default_rng(seed)
+        r = rng.uniform(size=num_rays)
+        theta = rng.uniform(0, 2 * np.pi, size=num_rays)
+        return np.sqrt(r) * np.cos(theta), np.sqrt(r) * np.sin(theta)
+    if distribution == "hexapolar":
+        x, y = [0.0], [0.0]
+        for i in range(num_rays):
+            num_theta = 6 * (i + 1)
+            theta = np.linspace(0, 2 * np.pi, num_theta + 1)[:-1]
+            r = (i + 1) / num_rays
+            x.extend(r * np.cos(theta))
+            y.extend(r * np.sin(theta))
+        return np.asarray(x), np.asarray(y)
+    if distribution == "uniform":
+        g = np.linspace(-1, 1, num_rays)
+        xx, yy = np.meshgrid(g, g)
+        keep = xx**2 + yy**2 <= 1
+        return xx[keep], yy[keep]
+    raise ValueError(f"distribution {distribution!r} is not implemented")
+
+
+class Optic:
+    def __init__(self, name=None):
+        self.name = name
+        self.surface_group = SurfaceGroup()
+        self.fields = []          # (x, y) in degrees
+        self.wavelengths = []     # micrometres
+        self.primary_index = 0
+        self.aperture = None
+        self._EPL = None
+        self._EPD = None
+
+    # ---- construction ------------------------------------------------------------------------
+    def add_surface(self, **kwargs):
+        return self.surface_group.add_surface(**kwargs)
+
+    def set_aperture(self, aperture_type, value):
+        self.aperture = (aperture_type, value)
+        if aperture_type == "EPD":
+            self._EPD = float(value)
+
+    def set_field_type(self, field_type):
+        if field_type != "angle":
+            raise ValueError("only angle fields are implemented")
+
+    def add_field(self, y=0.0, x=0.0):
+        self.fields.append((float(x), float(y)))
+
+    def add_wavelength(self, value, is_primary=False):
+        self.wavelengths.append(float(value))
+        if is_primary:
+            self.primary_index = len(self.wavelengths) - 1
+
+    def set_paraxial(self, EPL, EPD=None):
+        """Entrance-pupil location / diameter (optiland/paraxial.py:207-280), supplied by the caller."""
+        self._EPL = float(EPL)
+        if EPD is not None:
+            self._EPD = float(EPD)
+
+    @property
+    def primary_wavelength(self):
+        return self.wavelengths[self.primary_index]
+
+    @property
+    def max_field(self):
+        return max(math.hypot(fx, fy) for fx, fy in self.fields) if self.fields else 0.0
+
+    def get_field_coords(self):
+        mf = self.max_field
+        return [(fx / mf if mf else 0.0, fy / mf if mf else 0.0) for fx, fy in self.fields]
+
+    # ---- ray generation: ray_generator.py:28-106 + AngleField.get_ray_origins (infinite object) ---
+    def generate_rays(self, Hx, Hy, Px, Py, wavelength) -> RealRays:
+        if self._EPL is None or self._EPD is None:
+            raise ValueError("call set_paraxial(EPL, EPD) first")
+        dt, dev = be.get_precision(), be.get_device()
+        f64 = lambda a: torch.as_tensor(np.asarray(a, dtype=np.float64), device=dev).reshape(-1)
+        Hx, Hy, Px, Py = f64(Hx), f64(Hy), f64(Px), f64(Py)
+        EPL, EPD, mf = self._EPL, self._EPD, self.max_field
+        z_pos = [float(s.geometry.cs.z) for s in self.surface_group.surfaces[1:-1]]
+        offset = EPD - min(z_pos)                              # field_types.py:223-239
+        x = -torch.tan(torch.deg2rad(mf * Hx)) * (offset + EPL)
+        y = -torch.tan(torch.deg2rad(mf * Hy)) * (offset + EPL)
+        z = float(self.surface_group.surfaces[1].geometry.cs.z) - offset
+        x0 = Px * EPD / 2 * 1.0 + x
+        y0 = Py * EPD / 2 * 1.0 + y
+        z0 = torch.full_like(Px, z)
+        x1 = Px * EPD * 1.0 / 2
+        y1 = Py * EPD * 1.0 / 2
+        z1 = torch.full_like(Px, EPL)
+        mag = torch.sqrt((x1 - x0) ** 2 + (y1 - y0) ** 2 + (z1 - z0) ** 2)
+        is_zero = mag < 1e-9
+        mag = torch.where(is_zero, torch.ones_like(mag), mag)
+        L = torch.where(is_zero, torch.zeros_like(mag), (x1 - x0) / mag)
+        M = torch.where(is_zero, torch.zeros_like(mag), (y1 - y0) / mag)
+        N = torch.where(is_zero, torch.ones_like(mag), (z1 - z0) / mag)
+        w = torch.ones_like(x1) * wavelength
+        c = lambda t: t.to(dt)
+        return RealRays(c(x0), c(y0), c(z0), c(L), c(M), c(N), c(torch.ones_like(Px)), c(w))
+
+    # ---- RealRayTracer.trace / trace_generic, real_ray_tracer.py:37-133 -------------------------
+    def trace(self, Hx, Hy, wavelength, num_rays=100, distribution="hexapolar", seed=None):
+        if isinstance(distribution, str):
+            Px, Py = pupil_points(distribution, num_rays, seed)
+        else:
+            Px, Py = distribution
+        Hx, Hy = np.atleast_1d(Hx).astype(np.float64), np.atleast_1d(Hy).astype(np.float64)
+        nf, npup = len(Hx), len(Px)
+        rays = self.generate_rays(np.repeat(Hx, npup), np.repeat(Hy, npup), np.tile(Px, nf),
+                                  np.tile(Py, nf), wavelength)
+        self.surface_group.trace(rays, wavelengths=[float(wavelength)])
+        return rays
+
+    def trace_generic(self, Hx, Hy, Px, Py, wavelength):
+        arrs = [np.atleast_1d(np.asarray(a, dtype=np.float64)) for a in (Hx, Hy, Px, Py)]
+        n = max(a.size for a in arrs)
+        arrs = [np.full(n, a[0]) if a.size == 1 else a for a in arrs]
+        rays = self.generate_rays(*arrs, wavelength)
+        self.surface_group.trace(rays, wavelengths=[float(wavelength)])
+        return rays

@@ -1,0 +1,327 @@
+"""Prescription packer: SurfaceGroup -> flat tables for libolrt (layout in include/olrt.h).
+
+Walks `surface_group.surfaces` exactly as `SurfaceGroup.trace` does
+(optiland/surfaces/surface_group.py:232-244) and turns every `Surface` into one row of the
+int32 `ops` table plus one block of reals. It is duck-typed on the reference's attribute
+names (geometry.radius / .k / .coefficients / .cs.{x,y,z,rx,ry,rz,reference_cs},
+material_post.n(w) / .k(w), aperture.r_max ..., interaction_model.is_reflective), so the
+same code packs the reference's own objects (drop-in adapter) and this package's mirror
+classes.
+
+Refractive index n and extinction k are evaluated here, once per (surface, distinct
+wavelength), with the surface's own material objects (optiland/materials/base.py:73-119),
+and staged to the kernel -- the reference re-evaluates them per ray array on every call.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _lib as L
+
+_GEOM_BY_NAME = {
+    "Plane": L.GEOM_PLANE,
+    "StandardGeometry": L.GEOM_STANDARD,
+    "EvenAsphere": L.GEOM_EVEN_ASPHERE,
+    "OddAsphere": L.GEOM_ODD_ASPHERE,
+    "PolynomialGeometry": L.GEOM_POLYNOMIAL,
+    "ZernikePolynomialGeometry": L.GEOM_ZERNIKE,
+}
+_NR_GEOMS = (L.GEOM_EVEN_ASPHERE, L.GEOM_ODD_ASPHERE, L.GEOM_POLYNOMIAL, L.GEOM_ZERNIKE)
+
+
+class NotEligible(Exception):
+    """The surface group contains something the fused kernel does not implement."""
+
+
+def _f(v) -> float:
+    """Scalar value of a python number / numpy 0-d or 1-element array / torch tensor."""
+    if hasattr(v, "detach"):
+        return float(v.detach().cpu().reshape(-1)[0].item())
+    a = np.asarray(v, dtype=np.float64).reshape(-1)
+    return float(a[0])
+
+
+def _sq(v):
+    """`v**2` evaluated on the object itself, the way the reference's `contains` does."""
+    return _f(v**2)
+
+
+def zernike_radial_coefficients(n: int, m: int) -> list[float]:
+    """Coefficients of R_n^|m|(rho), highest power first (zernike/base.py:215-239)."""
+    ma = abs(m)
+    out = []
+    for k in range((n - ma) // 2 + 1):
+        num = math.factorial(n - k)
+        den = math.factorial(k) * math.factorial((n + ma) // 2 - k) * math.factorial((n - ma) // 2 - k)
+        out.append(float((-1) ** k * num // den) if num % den == 0 else (-1) ** k * num / den)
+    return out
+
+
+@dataclass
+class SurfaceLayout:
+    """Where one surface's parameters sit inside a prescription (offsets in reals)."""
+
+    index: int            # index into surface_group.surfaces
+    geom: int
+    doff: int             # start of the block
+    frames: int           # offset of frame 0
+    nframes: int
+    radius: int
+    conic: int
+    tol: int
+    norm_radius: int
+    media: int            # n_pre[W], n_post[W], k_pre[W]
+    coef: int
+    ncoef_reals: int
+    aper: int
+    max_iter: int = 0
+    tol_value: float = 0.0
+    zernike_terms: list = field(default_factory=list)  # (n, m, offset of c, N_j)
+
+
+@dataclass
+class PackedSystem:
+    ops: np.ndarray                 # int32 [ops_len]
+    presc: np.ndarray               # float64 [n_presc, stride]
+    wavelengths: list
+    layouts: list                   # SurfaceLayout per intersected surface
+    record_surfaces: list           # surface_group index per record slot
+    object_records: list            # surface_group indices of ObjectSurface (record = the input rays)
+    n_surfaces: int = 0
+
+    @property
+    def stride(self) -> int:
+        return int(self.presc.shape[1])
+
+    def nr_rows(self):
+        return [k for k, lay in enumerate(self.layouts) if lay.geom in _NR_GEOMS]
+
+    def set_nr_iters(self, iters) -> None:
+        for k, lay in enumerate(self.layouts):
+            if lay.geom in _NR_GEOMS:
+                self.ops[k * L.OPS_STRIDE + L.OP_NR_ITERS] = int(iters[k])
+
+    def nr_iters(self):
+        return [int(self.ops[k * L.OPS_STRIDE + L.OP_NR_ITERS]) for k in range(self.n_surfaces)]
+
+    def nr_resid_words(self) -> int:
+        return sum(self.nr_iters()[k] + 1 for k in self.nr_rows())
+
+    def make_sys(self, n_presc: int = 1, rays_per_presc: int = 0) -> "L.OlrtSys":
+        s = L.OlrtSys()
+        s.n_surfaces = self.n_surfaces
+        s.n_wavelengths = len(self.wavelengths)
+        s.n_presc = n_presc
+        s.presc_stride = self.stride
+        s.ops_len = int(self.ops.shape[0])
+        s.n_record = len(self.record_surfaces)
+        s.nr_resid_words = self.nr_resid_words()
+        s.rays_per_presc = rays_per_presc
+        for q, w in enumerate(self.wavelengths):
+            s.wavelengths[q] = float(w)
+        return s
+
+
+# --------------------------------------------------------------------------------------------
+# materials: n(lambda), k(lambda) per distinct wavelength     optiland/materials/base.py:73-119
+# --------------------------------------------------------------------------------------------
+def _material_value(mat, which: str, wl: float) -> float:
+    fn = getattr(mat, which)
+    try:
+        return _f(fn(wl))
+    except Exception:
+        return _f(fn(np.array([wl], dtype=np.float64)))
+
+
+# --------------------------------------------------------------------------------------------
+# apertures -> reverse-Polish program                         optiland/physical_apertures/*.py
+# --------------------------------------------------------------------------------------------
+def _compile_aperture(ap, tokens: list, params: list) -> None:
+    name = type(ap).__name__
+    if name == "RadialAperture":
+        tokens.append(L.AP_RADIAL)
+        params += [_sq(ap.r_max), _sq(ap.r_min)]
+    elif name == "OffsetRadialAperture":
+        tokens.append(L.AP_OFFSET_RADIAL)
+        params += [_sq(ap.r_max), _sq(ap.r_min), _f(ap.offset_x), _f(ap.offset_y)]
+    elif name == "EllipticalAperture":
+        tokens.append(L.AP_ELLIPTICAL)
+        params += [_sq(ap.a), _sq(ap.b), _f(ap.offset_x), _f(ap.offset_y)]
+    elif name == "RectangularAperture":
+        tokens.append(L.AP_RECTANGULAR)
+        params += [_f(ap.x_min), _f(ap.x_max), _f(ap.y_min), _f(ap.y_max)]
+    elif name in ("UnionAperture", "IntersectionAperture", "DifferenceAperture"):
+        _compile_aperture(ap.a, tokens, params)
+        _compile_aperture(ap.b, tokens, params)
+        tokens.append({"UnionAperture": L.AP_OR, "IntersectionAperture": L.AP_AND,
+                       "DifferenceAperture": L.AP_DIFF}[name])
+    else:
+        raise NotEligible(f"aperture type {name} is not implemented in the fused kernel")
+    if len(tokens) > 30:
+        raise NotEligible("aperture tree too deep for the fused kernel")
+
+
+def _frames_of(cs) -> list:
+    """reference_cs chain, root first (coordinate_system.py:73-89)."""
+    chain = []
+    while cs is not None:
+        chain.append(cs)
+        cs = getattr(cs, "reference_cs", None)
+    chain.reverse()
+    return chain
+
+
+def _is_inf(v) -> bool:
+    return math.isinf(_f(v))
+
+
+def check_surface(surf) -> None:
+    """Raise NotEligible unless `Surface.trace` on this surface is covered by the kernel."""
+    g = surf.geometry
+    gname = type(g).__name__
+    if gname not in _GEOM_BY_NAME:
+        raise NotEligible(f"geometry {gname} is not implemented in the fused kernel")
+    im = surf.interaction_model
+    if type(im).__name__ != "RefractiveReflectiveModel":
+        raise NotEligible(f"interaction model {type(im).__name__} is not implemented")
+    if getattr(im, "coating", None) is not None or getattr(im, "bsdf", None) is not None:
+        raise NotEligible("coatings / BSDFs are not implemented in the fused kernel")
+    for mat in (surf.material_pre, surf.material_post):
+        pm = getattr(mat, "propagation_model", None)
+        if pm is not None and type(pm).__name__ != "HomogeneousPropagation":
+            raise NotEligible(f"propagation model {type(pm).__name__} is not implemented")
+
+
+def pack_surface_group(surfaces, wavelengths, record="all", skip: int = 0) -> PackedSystem:
+    """Pack `surfaces[skip:]` for the distinct `wavelengths` (micrometres)."""
+    wavelengths = [float(w) for w in wavelengths]
+    W = len(wavelengths)
+    if not 1 <= W <= L.MAX_WAVELENGTHS:
+        raise NotEligible(f"{W} distinct wavelengths (limit {L.MAX_WAVELENGTHS})")
+    traced = list(enumerate(surfaces))[skip:]
+    real = [(gi, s) for gi, s in traced if type(s).__name__ != "ObjectSurface"]
+    object_records = [gi for gi, s in traced if type(s).__name__ == "ObjectSurface"]
+    S = len(real)
+    if not 1 <= S <= L.MAX_SURFACES:
+        raise NotEligible(f"{S} surfaces (limit {L.MAX_SURFACES})")
+    if record == "all":
+        rec_set = [gi for gi, _ in real]
+    elif record == "last":
+        rec_set = [real[-1][0]]
+    elif record in (None, "none"):
+        rec_set = []
+    else:
+        rec_set = [int(r) for r in record]
+
+    ops = [0] * (S * L.OPS_STRIDE)
+    extra_ops: list = []
+    reals: list = []
+    layouts = []
+    record_surfaces = []
+    for k, (gi, surf) in enumerate(real):
+        check_surface(surf)
+        g = surf.geometry
+        geom = _GEOM_BY_NAME[type(g).__name__]
+        row = k * L.OPS_STRIDE
+        doff = len(reals)
+        frames = _frames_of(g.cs)
+        if len(frames) > 10:
+            raise NotEligible("reference_cs chain longer than 10 frames")
+        fflags = 0
+        for q, cs in enumerate(frames):
+            rx, ry, rz = _f(cs.rx), _f(cs.ry), _f(cs.rz)
+            reals += [_f(cs.x), _f(cs.y), _f(cs.z),
+                      float(np.cos(np.float64(rz))), float(np.sin(np.float64(rz))),
+                      float(np.cos(np.float64(ry))), float(np.sin(np.float64(ry))),
+                      float(np.cos(np.float64(rx))), float(np.sin(np.float64(rx)))]
+            fl = (1 if bool(rz) else 0) | (2 if bool(ry) else 0) | (4 if bool(rx) else 0)
+            fflags |= fl << (3 * q)
+        goff = len(reals)
+        flags = 0
+        if geom == L.GEOM_PLANE:
+            radius, conic = math.inf, 0.0
+        else:
+            radius, conic = _f(g.radius), _f(g.k)
+            if _is_inf(g.radius):
+                flags |= L.F_RADIUS_INF
+        tol = float(getattr(g, "tol", 0.0)) if geom in _NR_GEOMS else 0.0
+        max_iter = int(getattr(g, "max_iter", 0)) if geom in _NR_GEOMS else 0
+        if max_iter > L.MAX_NR_ITERS:
+            raise NotEligible(f"max_iter {max_iter} > {L.MAX_NR_ITERS}")
+        norm_radius = _f(getattr(g, "norm_radius", 1.0)) if geom == L.GEOM_ZERNIKE else 1.0
+        reals += [radius, conic, tol, norm_radius]
+        moff = len(reals)
+        pre, post = surf.material_pre, surf.material_post
+        n_pre = [_material_value(pre, "n", w) for w in wavelengths]
+        n_post = [_material_value(post, "n", w) for w in wavelengths]
+        k_pre = [_material_value(pre, "k", w) for w in wavelengths]
+        if any(v > 0 for v in k_pre):  # be.any(k > 0), propagation/homogeneous.py:45-47
+            flags |= L.F_ABSORB
+        reals += n_pre + n_post + k_pre
+        coff = len(reals)
+        ncoef, aux = 0, 0
+        zterms = []
+        if geom in (L.GEOM_EVEN_ASPHERE, L.GEOM_ODD_ASPHERE):
+            cs_ = [_f(c) for c in g.coefficients]
+            ncoef = len(cs_)
+            reals += cs_
+        elif geom == L.GEOM_POLYNOMIAL:
+            rows = [[_f(c) for c in r] for r in g.coefficients]
+            J = len(rows[0]) if rows else 0
+            if any(len(r) != J for r in rows):
+                raise NotEligible("ragged polynomial coefficient table")
+            ncoef, aux = len(rows) * J, J
+            for r in rows:
+                reals += r
+        elif geom == L.GEOM_ZERNIKE:
+            z = g.zernike
+            aux = S * L.OPS_STRIDE + len(extra_ops)
+            coeffs = [_f(c) for c in z.coeffs]
+            ncoef = len(coeffs)
+            for (n, m), c in zip(z.indices, coeffs):
+                n, m = int(n), int(m)
+                norm = _f(z._norm_constant(n, m))
+                extra_ops += [n, m]
+                zterms.append((n, m, len(reals), norm))
+                reals += [c, c * norm] + zernike_radial_coefficients(n, m)
+        aoff_reals = len(reals) - doff
+        ap_off, ap_len = -1, 0
+        if surf.aperture:
+            toks: list = []
+            prm: list = []
+            _compile_aperture(surf.aperture, toks, prm)
+            ap_off = S * L.OPS_STRIDE + len(extra_ops)
+            ap_len = len(toks)
+            extra_ops += toks
+            reals += prm
+        slot = -1
+        if gi in rec_set:
+            slot = len(record_surfaces)
+            record_surfaces.append(gi)
+        ops[row + L.OP_GEOM] = geom
+        ops[row + L.OP_INTERACT] = 1 if surf.interaction_model.is_reflective else 0
+        ops[row + L.OP_FLAGS] = flags
+        ops[row + L.OP_DOFF] = doff
+        ops[row + L.OP_NCOEF] = ncoef
+        ops[row + L.OP_AUX] = aux
+        ops[row + L.OP_NR_ITERS] = 0
+        ops[row + L.OP_APER_OFF] = ap_off
+        ops[row + L.OP_APER_LEN] = ap_len
+        ops[row + L.OP_RECORD] = slot
+        ops[row + L.OP_NFRAMES] = len(frames)
+        ops[row + L.OP_FRAMEFLAGS] = fflags
+        ops[row + L.OP_APER_DOFF] = aoff_reals
+        layouts.append(SurfaceLayout(
+            index=gi, geom=geom, doff=doff, frames=doff, nframes=len(frames), radius=goff,
+            conic=goff + 1, tol=goff + 2, norm_radius=goff + 3, media=moff, coef=coff,
+            ncoef_reals=len(reals) - coff - (len(reals) - doff - aoff_reals), aper=doff + aoff_reals,
+            max_iter=max_iter, tol_value=tol, zernike_terms=zterms))
+    packed = PackedSystem(
+        ops=np.asarray(ops + extra_ops, dtype=np.int32),
+        presc=np.asarray(reals, dtype=np.float64).reshape(1, -1),
+        wavelengths=wavelengths, layouts=layouts, record_surfaces=record_surfaces,
+        object_records=object_records, n_surfaces=S)
+    return packed

@@ -1,0 +1,242 @@
+"""Surface / ObjectSurface / SurfaceGroup mirroring the reference's interface for the hot path.
+
+    SurfaceGroup.trace(rays, skip=0)   optiland/surfaces/surface_group.py:232-244
+    SurfaceGroup.x/y/z/L/M/N/intensity/opd  (stack of non-empty records)  :95-140
+    SurfaceGroup.add_surface           :246-353 (+ factories/*.py for cs / material / geometry)
+    Surface._record / reset            optiland/surfaces/standard_surface.py:244-286
+
+`trace` performs ONE launch of the fused CUDA kernel for the whole surface loop; the
+per-surface recorded arrays the analyses read afterwards are views into the kernel's record
+buffer. There is no per-surface Python path and no CPU fallback in this package: a surface the
+kernel does not implement raises `NotEligible`.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import backend as be
+from .apertures import configure_aperture
+from .coordinate_system import CoordinateSystem
+from .geometries import (EvenAsphere, OddAsphere, Plane, PolynomialGeometry, StandardGeometry,
+                         ZernikePolynomialGeometry)
+from .materials import BaseMaterial, IdealMaterial, Material
+from .prescription import PackedSystem, pack_surface_group
+from .rays import RealRays
+from .trace import fused_trace
+
+_RECORD_FIELDS = ("x", "y", "z", "L", "M", "N", "intensity", "opd")
+
+
+class RefractiveReflectiveModel:
+    """interactions/refractive_reflective_model.py:21-55 (coatings / BSDF out of scope)."""
+
+    interaction_type = "refractive_reflective"
+
+    def __init__(self, parent_surface=None, is_reflective=False, coating=None, bsdf=None):
+        self.parent_surface = parent_surface
+        self.is_reflective = is_reflective
+        self.coating = coating
+        self.bsdf = bsdf
+
+
+class Surface:
+    def __init__(self, previous_surface, material_post, geometry, is_stop=False, aperture=None,
+                 surface_type=None, comment="", interaction_model=None):
+        self.geometry = geometry
+        self.previous_surface = previous_surface
+        self.material_post = material_post
+        self.is_stop = is_stop
+        self.aperture = configure_aperture(aperture)
+        self.surface_type = surface_type
+        self.comment = comment
+        self.interaction_model = interaction_model or RefractiveReflectiveModel(self)
+        self.interaction_model.parent_surface = self
+        self.thickness = 0.0
+        self.reset()
+
+    @property
+    def material_pre(self):
+        return (self.previous_surface.material_post if self.previous_surface is not None
+                else self.material_post)
+
+    def reset(self):
+        """standard_surface.py:244-258"""
+        e = torch.empty(0)
+        self.x = self.y = self.z = self.L = self.M = self.N = e
+        self.intensity = self.aoi = self.opd = e
+        self.u = e
+
+    def _set_record(self, rec):
+        """rec: [8, N] tensor view of the kernel's record buffer."""
+        for q, name in enumerate(_RECORD_FIELDS):
+            setattr(self, name, rec[q])
+
+
+class ObjectSurface(Surface):
+    """surfaces/object_surface.py:22-72: only records the incoming rays."""
+
+    def __init__(self, geometry, material_post, comment=""):
+        super().__init__(None, material_post, geometry, comment=comment)
+
+    @property
+    def is_infinite(self):
+        return math.isinf(float(self.geometry.cs.z))
+
+
+class SurfaceGroup:
+    def __init__(self, surfaces=None):
+        self._surfaces = list(surfaces) if surfaces else []
+        self._link()
+        self.record = "all"      # "all" | "last" | list of surface indices
+        self.fast_math = False   # True: FMA-contracted fp64 kernel (not bit-faithful)
+        self._packed_cache = None
+        self.last_trace = None
+
+    # ---- structure -----------------------------------------------------------------------
+    def _link(self):
+        for k, s in enumerate(self._surfaces):
+            s.previous_surface = self._surfaces[k - 1] if k > 0 else None
+
+    @property
+    def surfaces(self):
+        return tuple(self._surfaces)
+
+    @property
+    def num_surfaces(self):
+        return len(self._surfaces)
+
+    def invalidate(self):
+        """Call after mutating any prescription value in place."""
+        self._packed_cache = None
+
+    def add_surface(self, new_surface=None, surface_type="standard", comment="", index=None,
+                    is_stop=False, material="air", **kwargs):
+        """Subset of surface_group.py:246-353 + factories: sequential `thickness` positioning or
+        absolute x/y/z, decenter dx/dy, tilts rx/ry/rz, radius, conic, coefficients, aperture."""
+        if new_surface is not None:
+            self._surfaces.insert(len(self._surfaces) if index is None else index, new_surface)
+            self._link()
+            self.invalidate()
+            return new_surface
+        if index is None:
+            index = len(self._surfaces)
+        if index != len(self._surfaces):
+            raise IndexError("this mirror only appends surfaces in order")
+        # coordinate system, factories/coordinate_system_factory.py:25-88
+        if "z" in kwargs:
+            if "thickness" in kwargs:
+                raise ValueError('Cannot define both "thickness" and "z".')
+            x, y, z = kwargs.get("x", 0), kwargs.get("y", 0), kwargs["z"]
+        else:
+            thickness = kwargs.get("thickness", 0)
+            x, y = kwargs.get("dx", 0), kwargs.get("dy", 0)
+            if index == 0:
+                z = -thickness
+            elif index == 1:
+                z = 0
+            else:
+                prev = self._surfaces[index - 1]
+                z = prev.geometry.cs.z + prev.thickness
+        cs = CoordinateSystem(x=x, y=y, z=z, rx=kwargs.get("rx", 0), ry=kwargs.get("ry", 0),
+                              rz=kwargs.get("rz", 0))
+        # materials, factories/material_factory.py:22-93
+        if isinstance(material, BaseMaterial):
+            post = material
+        elif isinstance(material, tuple):
+            post = Material(material[0], material[1])
+        elif material.lower() == "air":
+            post = IdealMaterial(n=1.0, k=0.0)
+        elif material.lower() == "mirror":
+            post = self._surfaces[index - 1].material_post
+        else:
+            post = Material(material)
+        # geometry, factories/geometry_factory.py:60-230, geometry_configs.py:30-183
+        radius = kwargs.get("radius", math.inf)
+        conic = kwargs.get("conic", 0.0)
+        tol, max_iter = kwargs.get("tol", 1e-6), kwargs.get("max_iter", 100)
+        coefficients = kwargs.get("coefficients")
+        if surface_type == "standard":
+            rinf = math.isinf(float(radius)) if not hasattr(radius, "requires_grad") else bool(torch.isinf(radius))
+            geometry = Plane(cs) if rinf else StandardGeometry(cs, radius, conic)
+        elif surface_type == "even_asphere":
+            geometry = EvenAsphere(cs, radius, conic, tol, max_iter, coefficients)
+        elif surface_type == "odd_asphere":
+            geometry = OddAsphere(cs, radius, conic, tol, max_iter, coefficients)
+        elif surface_type == "polynomial":
+            geometry = PolynomialGeometry(cs, radius, conic, tol, max_iter, coefficients)
+        elif surface_type == "zernike":
+            geometry = ZernikePolynomialGeometry(cs, radius, conic, tol, max_iter, coefficients,
+                                                 kwargs.get("zernike_type", "fringe"),
+                                                 kwargs.get("norm_radius", 1.0))
+        else:
+            raise ValueError(f"surface_type {surface_type!r} is not implemented in optiland_pr_b200")
+        if index == 0:
+            surf = ObjectSurface(geometry, post, comment)
+        else:
+            surf = Surface(None, post, geometry, is_stop=is_stop, aperture=kwargs.get("aperture"),
+                           surface_type=surface_type, comment=comment,
+                           interaction_model=RefractiveReflectiveModel(
+                               None, is_reflective=(isinstance(material, str) and material == "mirror")))
+        surf.thickness = kwargs.get("thickness", 0.0)
+        self._surfaces.append(surf)
+        self._link()
+        self.invalidate()
+        return surf
+
+    # ---- recorded arrays, surface_group.py:95-140 -------------------------------------------
+    def _stacked(self, name):
+        return torch.stack([getattr(s, name) for s in self._surfaces if getattr(s, name).numel() > 0])
+
+    x = property(lambda self: self._stacked("x"))
+    y = property(lambda self: self._stacked("y"))
+    z = property(lambda self: self._stacked("z"))
+    L = property(lambda self: self._stacked("L"))
+    M = property(lambda self: self._stacked("M"))
+    N = property(lambda self: self._stacked("N"))
+    intensity = property(lambda self: self._stacked("intensity"))
+    opd = property(lambda self: self._stacked("opd"))
+
+    def reset(self):
+        for s in self._surfaces:
+            s.reset()
+
+    # ---- the hot path ----------------------------------------------------------------------
+    def pack(self, wavelengths, skip=0) -> PackedSystem:
+        """Pack on every call (microseconds; prescriptions are mutable) but remember the Newton
+        trip counts K_s that the last trace of this group settled on as the next guess."""
+        packed = pack_surface_group(self._surfaces, wavelengths, record=self.record, skip=skip)
+        guess = self._packed_cache or {}
+        for k in packed.nr_rows():
+            lay = packed.layouts[k]
+            packed.ops[k * 16 + 6] = min(lay.max_iter, guess.get(lay.index, 2))
+        return packed
+
+    def trace(self, rays, skip=0, wavelengths=None):
+        """surface_group.py:232-244. `wavelengths` (distinct values of rays.w) may be passed to
+        avoid the device->host sync of torch.unique."""
+        if not isinstance(rays, RealRays):
+            raise TypeError("optiland_pr_b200.SurfaceGroup.trace only traces RealRays")
+        self.reset()
+        if wavelengths is None:
+            wavelengths = torch.unique(rays.w).cpu().tolist()
+        packed = self.pack(wavelengths, skip)
+        ins = rays.components()
+        res = fused_trace(packed, ins, opd_in=rays.opd, want_dir0=True, fast=self.fast_math)
+        if res.status & 1:
+            raise ValueError("Zernike coordinates must be normalized to [-1, 1]. Consider updating "
+                             "the normalization radius to 1.1x the surface aperture.")
+        if res.status & 2:
+            raise ValueError("a ray wavelength is missing from `wavelengths`")
+        for gi in packed.object_records:  # ObjectSurface.trace: record only, object_surface.py:56-72
+            self._surfaces[gi]._set_record(torch.stack(
+                [rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd]).clone())
+        for slot, gi in enumerate(packed.record_surfaces):
+            self._surfaces[gi]._set_record(res.record[slot])
+        o = res.out
+        rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd = (o[q] for q in range(8))
+        rays.L0, rays.M0, rays.N0 = res.dir0[0], res.dir0[1], res.dir0[2]
+        self._packed_cache = {packed.layouts[k].index: res.nr_iters[k] for k in packed.nr_rows()}
+        self.last_trace = res
+        return rays

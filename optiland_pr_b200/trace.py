@@ -1,0 +1,149 @@
+"""Launch driver: torch tensors -> libolrt C ABI (include/olrt.h).
+
+`fused_trace` is the one place that calls `olrt_trace_fwd_*`. It owns no numerics: every
+arithmetic step of `Surface.trace` (optiland/surfaces/standard_surface.py:186-233) happens in
+the CUDA kernel. PyTorch is used for device memory and streams only.
+
+Newton-Raphson surfaces: the reference stops iterating when the maximum |f| over the WHOLE ray
+batch drops below `tol` (optiland/geometries/newton_raphson.py:137-149), so every ray takes the
+same number K_s of updates. The kernel takes K_s as an input and reports max|f| per iteration;
+this driver checks the reported maxima against the reference's rule and relaunches with the
+corrected K_s when the guess was wrong ("Newton contract").
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from .prescription import PackedSystem
+
+
+@dataclass
+class TraceResult:
+    out: torch.Tensor            # [8, N]: x y z L M N intensity opd (global frame, after last surface)
+    record: torch.Tensor | None  # [n_record, 8, N]
+    dir0: torch.Tensor | None    # [3, N]: L0 M0 N0 at the last surface (local frame)
+    nr_iters: list               # K_s actually used per intersected surface
+    status: int
+    launches: int
+
+
+def _ptr(t) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+def _device_tables(packed: PackedSystem, dtype, device):
+    """ops / presc on the device, cached on the PackedSystem until it is mutated."""
+    key = (str(dtype), str(device), packed.ops.tobytes(), packed.presc.ctypes.data, packed.presc.shape)
+    cache = getattr(packed, "_dev_cache", None)
+    if cache is not None and cache[0] == key and cache[3] == packed.presc.tobytes():
+        return cache[1], cache[2]
+    ops = torch.from_numpy(packed.ops.copy()).to(device)
+    presc = torch.from_numpy(np.ascontiguousarray(packed.presc)).to(device=device, dtype=dtype)
+    packed._dev_cache = (key, ops, presc, packed.presc.tobytes())
+    return ops, presc
+
+
+def _true_iters(resid_row: np.ndarray, k_used: int, tol: float, max_iter: int):
+    """Reference exit rule on the reported maxima. Returns (K_true or None if more are needed)."""
+    for j in range(k_used + 1):
+        v = resid_row[j]
+        if math.isinf(v) or math.isnan(v):
+            return max_iter  # a NaN ray never passes `max|f| < tol`: newton_raphson.py:148
+        if j < max_iter and v < tol:
+            return j
+        if j == max_iter:
+            return max_iter
+    return None
+
+
+def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tensor | None = None,
+                n_presc: int = 1, rays_per_presc: int = 0, want_dir0: bool = False,
+                fast: bool = False, verify_nr: bool = True, out: torch.Tensor | None = None,
+                max_relaunch: int = 24) -> TraceResult:
+    """Trace rays through a packed system on the current CUDA device and stream.
+
+    rays_in: sequence of 8 tensors x y z L M N intensity wavelength (1-D, same length, CUDA,
+             float64 or float32; wavelength may be None when the system has one wavelength).
+    presc:   optional device tensor [n_presc, stride] overriding packed.presc (Monte Carlo batch).
+    """
+    lib = L.load()
+    x = rays_in[0]
+    if not x.is_cuda:
+        raise L.OlrtLibraryError("fused_trace needs CUDA tensors; there is no CPU path")
+    dtype, device = x.dtype, x.device
+    if dtype not in (torch.float64, torch.float32):
+        raise TypeError(f"unsupported dtype {dtype}")
+    n = int(x.numel())
+    ins = []
+    for q in range(8):
+        t = rays_in[q] if q < len(rays_in) else None
+        if t is None:
+            if q < 7 or len(packed.wavelengths) > 1:
+                raise ValueError(f"ray component {q} is required")
+            ins.append(None)
+            continue
+        if t.dtype != dtype or t.device != device or t.numel() != n:
+            raise ValueError("ray components must share dtype, device and length")
+        ins.append(t.contiguous())
+    if opd_in is not None:
+        opd_in = opd_in.to(dtype).contiguous()
+    ops_d, presc_d = _device_tables(packed, dtype, device)
+    if presc is not None:
+        presc_d = presc.to(device=device, dtype=dtype).contiguous()
+        n_presc = int(presc_d.shape[0])
+    n_rec = len(packed.record_surfaces)
+    if out is None:
+        out = torch.empty((8, n), dtype=dtype, device=device)
+    record = torch.empty((n_rec, 8, n), dtype=dtype, device=device) if n_rec else None
+    dir0 = torch.empty((3, n), dtype=dtype, device=device) if want_dir0 else None
+    nr_rows = packed.nr_rows()
+    status_t = torch.zeros(1, dtype=torch.int32, device=device)
+    fn = lib.olrt_trace_fwd_f64 if dtype == torch.float64 else lib.olrt_trace_fwd_f32
+    in_arr = L.PtrArray8(*[_ptr(t) for t in ins])
+    out_arr = L.PtrArray8(*[out[q].data_ptr() for q in range(8)])
+    stream = torch.cuda.current_stream(device).cuda_stream
+    launches = 0
+    with torch.cuda.device(device):
+        while True:
+            resid = None
+            if nr_rows and verify_nr:
+                resid = torch.zeros((packed.n_surfaces, L.RESID_STRIDE), dtype=torch.int64, device=device)
+                ops_d, _ = _device_tables(packed, dtype, device)
+            sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=rays_per_presc)
+            sys_.presc_stride = int(presc_d.shape[1])
+            rc = fn(C.byref(sys_), presc_d.data_ptr(), ops_d.data_ptr(), n, in_arr, _ptr(opd_in),
+                    out_arr, _ptr(record), _ptr(dir0), _ptr(resid), status_t.data_ptr(),
+                    L.FWD_FAST if fast else 0, stream)
+            L.check(rc, "olrt_trace_fwd")
+            launches += 1
+            if resid is None or n == 0:
+                break
+            res = resid.cpu().numpy().view(np.float64)
+            iters = packed.nr_iters()
+            changed = False
+            for k in nr_rows:
+                lay = packed.layouts[k]
+                kt = _true_iters(res[k], iters[k], lay.tol_value, lay.max_iter)
+                if kt is None:
+                    iters[k] = min(lay.max_iter, max(iters[k] * 2, iters[k] + 2))
+                    changed = True
+                    break
+                if kt != iters[k]:
+                    iters[k] = kt
+                    changed = True
+                    break
+            if not changed:
+                break
+            if launches > max_relaunch:
+                raise L.OlrtLibraryError("Newton iteration counts did not settle")
+            packed.set_nr_iters(iters)
+            status_t.zero_()
+    status = int(status_t.item()) if (nr_rows or len(packed.wavelengths) > 1) else 0
+    return TraceResult(out=out, record=record, dir0=dir0, nr_iters=packed.nr_iters(), status=status,
+                       launches=launches)
