@@ -1,0 +1,41 @@
+"""CPU: the NumPy oracle reproduces the reference outputs stored in tests/golden (made by running the
+unmodified reference, oracle/make_golden.py), and the mirror classes pack the same tables as the
+reference's own objects."""
+import numpy as np
+import pytest
+
+from helpers import FIELDS8, MIRRORS, load_golden, mirror_packed, rel_err
+from oracle import trace_np
+
+
+@pytest.mark.parametrize("name", sorted(MIRRORS))
+def test_mirror_packs_like_reference_objects(name):
+    g = load_golden(name)
+    _, packed = mirror_packed(name, g["wavelengths"])
+    assert np.array_equal(packed.ops, g["ops"])
+    assert np.array_equal(packed.presc, g["presc"])
+
+
+@pytest.mark.parametrize("name", sorted(MIRRORS))
+def test_oracle_bit_exact_against_stored_reference(name):
+    g = load_golden(name)
+    _, packed = mirror_packed(name, g["wavelengths"])
+    out = trace_np.trace_packed(packed, trace_np.Rays(*g["rays_in"]))
+    rec = np.array(out["records"])
+    assert rec.shape == g["records"].shape
+    for q, f in enumerate(FIELDS8):
+        assert np.array_equal(rec[:, q], g["records"][:, q], equal_nan=True), f
+    if "nr_iters" in g:
+        assert list(out["nr_iters"]) == list(g["nr_iters"])
+
+
+@pytest.mark.parametrize("name", sorted(MIRRORS))
+def test_fixed_iteration_replay_equals_exit_rule(name):
+    """A launch with K_s fixed to the counts the exit rule produced gives the same bits
+    (this is the contract between the kernel and the host driver)."""
+    g = load_golden(name)
+    _, packed = mirror_packed(name, g["wavelengths"])
+    a = trace_np.trace_packed(packed, trace_np.Rays(*g["rays_in"]))
+    b = trace_np.trace_packed(packed, trace_np.Rays(*g["rays_in"]), fixed_iters=a["nr_iters"])
+    assert np.array_equal(np.array(a["records"]), np.array(b["records"]), equal_nan=True)
+    assert rel_err(np.array(a["records"]), g["records"]) == 0.0
