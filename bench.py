@@ -1,0 +1,368 @@
+#!/usr/bin/env python
+"""bench.py -- ray-surface intersections per second of the fused real-ray trace on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
+    python bench.py --impl reference [--steps K] [--warmup W]      # CPU baseline arm (NumPy port)
+    torchrun --nproc-per-node N bench.py --gpus N ...              # one rank per GPU
+
+Workload (BASELINE.json configs[1]): the even-asphere double Gauss (S_eff = 12 intersected
+surfaces, 4 of them Newton-Raphson even aspheres), 3 fields x 16 777 216 random pupil rays at the
+primary wavelength, fp64, forward trace + RMS-spot epilogue. One step = one pass over that batch.
+`value` = rays x S_eff / time with the rays resident in HBM; `e2e` = the same through the public
+call `Optic.trace(Hx, Hy, wl, distribution=(Px, Py))` with the pupil grid in pinned HOST memory
+(host->device copy, ray generation, trace, epilogue and the device->host read of the RMS values
+all inside the timed region). Multi-GPU: rays are independent, every rank traces its own batch
+(weak scaling); the only collective is an NCCL all-reduce of the [3][10] spot sums.
+
+Only the `cpu_baseline` leg and `--impl reference` execute oracle/ (the NumPy restatement of the
+reference; the Python reference itself cannot travel to the GPU box).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+RAYS_PER_FIELD = 16_777_216
+FIELDS = [(0.0, 0.0), (0.0, 10.0 / 14.0), (0.0, 1.0)]
+WAVELENGTH = 0.5876
+METRIC = "ray-surfaces/sec fwd (fp64, even-asphere double Gauss, 3 fields x 16M rays) on B200"
+UNIT = "ray-surfaces/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rays-per-field", type=int, default=RAYS_PER_FIELD)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--extras", type=int, default=1, help="also time fp32 / fast / fwd+bwd legs")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled DURING the timed region
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            parts = [p.strip() for p in s.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the NumPy oracle on a bounded sample of the same workload, all host cores
+# ---------------------------------------------------------------------------------------------
+def cpu_arm(steps: int, warmup: int, budget_s: float = 20.0):
+    from oracle import cpu_bench
+
+    return cpu_bench.run_subprocess("even_asphere_double_gauss", [list(f) for f in FIELDS], WAVELENGTH,
+                                    steps=steps, warmup=warmup, budget_s=budget_s)
+
+
+def reference_main(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 5))
+    r = cpu_arm(steps, min(args.warmup, 1), budget_s=30.0)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "even-asphere double Gauss, 3 fields x 16M random pupil rays, fwd trace + RMS spot",
+                   "sample": r["sample"]},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                         "sample": r["sample"]},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    if args.impl == "reference":
+        reference_main(args)
+        return
+    import torch
+    import torch.distributed as dist
+
+    import optiland_pr_b200 as ol
+    from optiland_pr_b200 import _lib, flops, samples, spot
+    from optiland_pr_b200.trace import fused_trace
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+    ol.backend.set_device(f"cuda:{local}")
+    ol.backend.set_precision("float64")
+
+    npf = args.rays_per_field
+    nf = len(FIELDS)
+    lens = samples.EvenAsphereDoubleGauss()
+    lens.surface_group.record = "none"
+    S_eff = lens.surface_group.num_surfaces - 1
+    # pupil grid on the host (pinned): the reference's RandomDistribution(seed) arithmetic
+    rng = np.random.default_rng(1 + rank)
+    r_ = rng.uniform(size=npf)
+    th = rng.uniform(0, 2 * np.pi, size=npf)
+    Px_h = torch.from_numpy(np.sqrt(r_) * np.cos(th)).pin_memory()
+    Py_h = torch.from_numpy(np.sqrt(r_) * np.sin(th)).pin_memory()
+    del r_, th
+    Hx = [f[0] for f in FIELDS]
+    Hy = [f[1] for f in FIELDS]
+
+    # ---- device-resident inputs for `value`
+    rays = lens.generate_rays(torch.tensor(Hx, device=dev).repeat_interleave(npf),
+                              torch.tensor(Hy, device=dev).repeat_interleave(npf),
+                              Px_h.to(dev).repeat(nf), Py_h.to(dev).repeat(nf), WAVELENGTH)
+    ins = rays.components()
+    ins[7] = None  # one wavelength: the kernel does not read the wavelength array
+    n = int(ins[0].numel())
+    packed = lens.surface_group.pack([WAVELENGTH])
+    out = torch.empty((8, n), dtype=torch.float64, device=dev)
+    sums = torch.zeros((nf, _lib.SPOT_SUMS), dtype=torch.float64, device=dev)
+
+    def step_resident(fast=False):
+        res = fused_trace(packed, ins, out=out, fast=fast)
+        spot.spot_sums(out[0], out[1], out[6], nf, npf, out=sums)
+        if world > 1:
+            dist.all_reduce(sums)
+        return res
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms / steps
+
+    # settle the Newton trip counts K_s (first call may relaunch), then time
+    res0 = step_resident()
+    nr_iters = res0.nr_iters
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_step = timed(step_resident, args.steps, max(args.warmup, 3))
+    clocks = sampler.stop() if rank == 0 else None
+    launches_per_step = 2
+    value = n * S_eff * world / (ms_step * 1e-3)
+    rms_resident = spot.spot_stats(sums)["rms"].cpu().tolist()
+
+    # ---- dominant kernel alone (roofline): trace_fwd_kernel<double>, strict build
+    def only_trace():
+        fused_trace(packed, ins, out=out, verify_nr=False)
+    ms_kernel = timed(only_trace, args.steps, 3)
+    fl_ray = flops.flops_per_ray(packed, nr_iters)
+    by_ray = flops.bytes_per_ray(8, 1)
+    # measured FP64 FMA peak on this GPU (dependent-free DFMA chains, all SMs)
+    sink = torch.zeros(1, dtype=torch.float64, device=dev)
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    st = torch.cuda.current_stream().cuda_stream
+
+    def peak(fn, iters, blocks, threads):
+        def go():
+            _lib.check(fn(sink.data_ptr() if fn is lib.olrt_fma_peak_f64 else sink32.data_ptr(), iters, blocks,
+                          threads, st), "fma_peak")
+        ms = timed(go, 3, 2)
+        return blocks * threads * iters * 8 * 2 / (ms * 1e-3) / 1e12
+
+    sink32 = torch.zeros(1, dtype=torch.float32, device=dev)
+    fp64_peak = peak(lib.olrt_fma_peak_f64, 1 << 16, sms * 8, 256)
+    fp32_peak = peak(lib.olrt_fma_peak_f32, 1 << 17, sms * 8, 256)
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    hbm_peak, hbm_src = 6650.0, "fallback"
+    if os.path.exists(peaks_path):
+        with open(peaks_path) as f:
+            hbm_peak, hbm_src = float(json.load(f)["hbm_gbs"]), "measured"
+    ach_tf = fl_ray * n / (ms_kernel * 1e-3) / 1e12
+    ach_gbs = by_ray * n / (ms_kernel * 1e-3) / 1e9
+    roofline = {
+        "kernel": "trace_fwd_kernel<double> (strict, -fmad=false)",
+        "bound": "fp64_fma", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+        "frac": ach_tf / fp64_peak, "peak_source": "olrt_fma_peak_f64 measured in this run",
+        "flops_per_ray": fl_ray, "bytes_per_ray": by_ray, "nr_iters": nr_iters, "ms_per_launch": ms_kernel,
+        "hbm": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
+                "peak_source": hbm_src + " (MEASURED_PEAKS.json hbm_gbs)"},
+        "traffic": None,
+    }
+    tr_path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr_path):
+        with open(tr_path) as f:
+            roofline["traffic"] = json.load(f).get("trace_fwd_f64_bytes_per_launch")
+
+    # ---- e2e: public API with host inputs
+    h2d = Px_h.numel() * 8 * 2 + nf * 8 * 2
+    d2h = nf * 8
+    rms_host = torch.empty(nf, dtype=torch.float64).pin_memory()
+
+    def step_e2e():
+        rr = lens.trace(Hx, Hy, WAVELENGTH, distribution=(Px_h, Py_h))
+        s = spot.spot_sums(rr.x, rr.y, rr.i, nf, npf, out=sums)
+        if world > 1:
+            dist.all_reduce(s)
+        rms_host.copy_(spot.spot_stats(s)["rms"], non_blocking=False)
+
+    del out, ins, rays
+    torch.cuda.empty_cache()
+    ms_e2e = timed(step_e2e, max(2, args.steps // 2), 3)
+    e2e_value = n * S_eff * world / (ms_e2e * 1e-3)
+
+    extras = {}
+    if args.extras and world == 1:
+        extras = run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64_peak)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "even-asphere double Gauss (12 intersected surfaces, 4 Newton-Raphson even aspheres), "
+                               f"{nf} fields x {npf} random pupil rays per GPU, primary wavelength, fwd trace + RMS spot",
+                   "rays_per_gpu": n, "surfaces": S_eff, "precision": "float64 strict (bit-faithful op order)",
+                   "l2": "inputs (2.7 GB) and outputs (3.2 GB) per step far exceed the 126 MB L2; no flush needed",
+                   "parallelism": f"rays sharded over {world} GPU(s), spot sums all-reduced"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h,
+                "api": "Optic.trace(Hx, Hy, wl, distribution=(Px, Py) pinned host) + spot.rms -> host"},
+        "gpu_launches": launches_per_step * args.steps,
+        "roofline": roofline, "clocks": clocks,
+        "rms_spot_mm": rms_resident, "rms_spot_mm_e2e": rms_host.tolist(),
+        "extras": extras,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        r = cpu_arm(1, 0, budget_s=15.0)
+        line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                                "sample": r["sample"], "rms_spot_mm": r.get("rms")}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64_peak):
+    """Other precisions / modes on the same workload, one field at a time to bound memory."""
+    from optiland_pr_b200 import flops
+    from optiland_pr_b200.trace import fused_trace
+
+    dev = torch.device("cuda", torch.cuda.current_device())
+    out = {}
+    rng = np.random.default_rng(7)
+    n = npf * nf
+    r_ = torch.from_numpy(rng.uniform(size=npf)).to(dev)
+    th = torch.from_numpy(rng.uniform(0, 2 * np.pi, size=npf)).to(dev)
+    Px, Py = torch.sqrt(r_) * torch.cos(th), torch.sqrt(r_) * torch.sin(th)
+    Hx = torch.tensor([f[0] for f in FIELDS], device=dev).repeat_interleave(npf)
+    Hy = torch.tensor([f[1] for f in FIELDS], device=dev).repeat_interleave(npf)
+    rays = lens.generate_rays(Hx, Hy, Px.repeat(nf), Py.repeat(nf), WAVELENGTH)
+    ins64 = rays.components()
+    ins64[7] = None
+    o64 = torch.empty((8, n), dtype=torch.float64, device=dev)
+    fl_ray = flops.flops_per_ray(packed)
+    for name, fast in (("fp64_fast_fwd", True),):
+        ms = timed(lambda: fused_trace(packed, ins64, out=o64, fast=fast, verify_nr=False), args.steps, 3)
+        out[name] = {"ray_surfaces_per_s": n * S_eff / (ms * 1e-3), "ms": ms,
+                     "frac_fp64_fma_peak": fl_ray * n / (ms * 1e-3) / 1e12 / fp64_peak}
+    ins32 = [t.float() if t is not None else None for t in ins64]
+    o32 = torch.empty((8, n), dtype=torch.float32, device=dev)
+    ms = timed(lambda: fused_trace(packed, ins32, out=o32, verify_nr=False), args.steps, 3)
+    out["fp32_fwd"] = {"ray_surfaces_per_s": n * S_eff / (ms * 1e-3), "ms": ms,
+                       "frac_fp32_fma_peak": fl_ray * n / (ms * 1e-3) / 1e12 / fp32_peak,
+                       "hbm_gbs": 60 * n / (ms * 1e-3) / 1e9}
+    out["fp64_fma_peak_tflops"] = fp64_peak
+    out["fp32_fma_peak_tflops"] = fp32_peak
+    try:
+        from optiland_pr_b200.autograd import bench_backward
+    except ImportError:
+        bench_backward = None
+    if bench_backward is not None:
+        out.update(bench_backward(lens, packed, ins64, timed, args, fp64_peak))
+    return out
+
+
+if __name__ == "__main__":
+    main()

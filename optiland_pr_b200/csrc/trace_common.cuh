@@ -113,6 +113,24 @@ __device__ __forceinline__ R conic_distance(const RayState<R>& r, R radius, R k,
     const R Ns = (r_abs(r.N) > R(1e-14)) ? r.N : R(1e-14);
     return (-r.z) / Ns;
   }
+  if (sizeof(R) == 4) {
+    // fp32 only (parity bar is a tolerance): b^2-4ac cancels catastrophically for a
+    // ray launched far from the vertex, so move the origin to the ray's closest approach to the
+    // vertex first and take the roots as q/a and c/q. Root choice is the reference's (standard.py:134).
+    const R dd = r.L * r.L + r.M * r.M + r.N * r.N;
+    const R t0 = -(r.x * r.L + r.y * r.M + r.z * r.N) / dd;
+    const R x = r.x + t0 * r.L, y = r.y + t0 * r.M, z = r.z + t0 * r.N;
+    const R a = k * r.N * r.N + dd;
+    const R hb = k * r.N * z + (r.L * x + r.M * y + r.N * z) - r.N * radius;
+    const R c = k * z * z - (R(2) * radius) * z + (x * x + y * y + z * z);
+    const R sd = r_sqrt(hb * hb - a * c);
+    const R q = -(hb + ((hb < R(0)) ? -sd : sd));
+    const R t1 = q / a;
+    const R t2 = (q != R(0)) ? c / q : R(0);
+    R t = (r_abs(z + t1 * r.N) <= r_abs(z + t2 * r.N)) ? t1 : t2;
+    if (a == R(0)) t = (-c) / (R(2) * hb);
+    return t0 + t;
+  }
   const R N2 = r.N * r.N;
   const R a = k * N2 + r.L * r.L + r.M * r.M + N2;
   const R b = (R(2) * k) * r.N * r.z + (R(2) * r.L) * r.x + (R(2) * r.M) * r.y -

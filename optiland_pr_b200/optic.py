@@ -101,10 +101,17 @@ class Optic:
 
     # ---- ray generation: ray_generator.py:28-106 + AngleField.get_ray_origins (infinite object) ---
     def generate_rays(self, Hx, Hy, Px, Py, wavelength) -> RealRays:
+        """Hx, Hy, Px, Py: scalars, NumPy arrays or torch tensors (host tensors are copied to the
+        device asynchronously -- pass pinned memory to overlap), broadcast against each other."""
         if self._EPL is None or self._EPD is None:
             raise ValueError("call set_paraxial(EPL, EPD) first")
         dt, dev = be.get_precision(), be.get_device()
-        f64 = lambda a: torch.as_tensor(np.asarray(a, dtype=np.float64), device=dev).reshape(-1)
+
+        def f64(a):
+            if isinstance(a, torch.Tensor):
+                return a.to(device=dev, dtype=torch.float64, non_blocking=True).reshape(-1)
+            return torch.as_tensor(np.asarray(a, dtype=np.float64), device=dev).reshape(-1)
+
         Hx, Hy, Px, Py = f64(Hx), f64(Hy), f64(Px), f64(Py)
         EPL, EPD, mf = self._EPL, self._EPD, self.max_field
         z_pos = [float(s.geometry.cs.z) for s in self.surface_group.surfaces[1:-1]]
@@ -114,30 +121,40 @@ class Optic:
         z = float(self.surface_group.surfaces[1].geometry.cs.z) - offset
         x0 = Px * EPD / 2 * 1.0 + x
         y0 = Py * EPD / 2 * 1.0 + y
-        z0 = torch.full_like(Px, z)
+        z0 = torch.full_like(x0, z)
         x1 = Px * EPD * 1.0 / 2
         y1 = Py * EPD * 1.0 / 2
-        z1 = torch.full_like(Px, EPL)
+        z1 = torch.full_like(x0, EPL)
         mag = torch.sqrt((x1 - x0) ** 2 + (y1 - y0) ** 2 + (z1 - z0) ** 2)
         is_zero = mag < 1e-9
         mag = torch.where(is_zero, torch.ones_like(mag), mag)
         L = torch.where(is_zero, torch.zeros_like(mag), (x1 - x0) / mag)
         M = torch.where(is_zero, torch.zeros_like(mag), (y1 - y0) / mag)
         N = torch.where(is_zero, torch.ones_like(mag), (z1 - z0) / mag)
-        w = torch.ones_like(x1) * wavelength
+        w = torch.ones_like(x0) * wavelength
         c = lambda t: t.to(dt)
-        return RealRays(c(x0), c(y0), c(z0), c(L), c(M), c(N), c(torch.ones_like(Px)), c(w))
+        return RealRays(c(x0), c(y0), c(z0), c(L), c(M), c(N), c(torch.ones_like(x0)), c(w))
 
     # ---- RealRayTracer.trace / trace_generic, real_ray_tracer.py:37-133 -------------------------
     def trace(self, Hx, Hy, wavelength, num_rays=100, distribution="hexapolar", seed=None):
+        """N rays = fields x pupil points, field-major (real_ray_tracer.py:61-77). `distribution`
+        may be a name or a (Px, Py) pair of NumPy arrays / torch tensors (pinned host or device)."""
         if isinstance(distribution, str):
             Px, Py = pupil_points(distribution, num_rays, seed)
         else:
             Px, Py = distribution
-        Hx, Hy = np.atleast_1d(Hx).astype(np.float64), np.atleast_1d(Hy).astype(np.float64)
-        nf, npup = len(Hx), len(Px)
-        rays = self.generate_rays(np.repeat(Hx, npup), np.repeat(Hy, npup), np.tile(Px, nf),
-                                  np.tile(Py, nf), wavelength)
+        dev = be.get_device()
+        Hx = torch.as_tensor(np.atleast_1d(Hx).astype(np.float64), device=dev)
+        Hy = torch.as_tensor(np.atleast_1d(Hy).astype(np.float64), device=dev)
+        nf, npup = int(Hx.numel()), len(Px)
+        if isinstance(Px, torch.Tensor):
+            Px = Px.to(device=dev, dtype=torch.float64, non_blocking=True)
+            Py = Py.to(device=dev, dtype=torch.float64, non_blocking=True)
+        else:
+            Px = torch.as_tensor(np.asarray(Px, dtype=np.float64), device=dev)
+            Py = torch.as_tensor(np.asarray(Py, dtype=np.float64), device=dev)
+        rays = self.generate_rays(Hx.repeat_interleave(npup), Hy.repeat_interleave(npup),
+                                  Px.repeat(nf), Py.repeat(nf), wavelength)
         self.surface_group.trace(rays, wavelengths=[float(wavelength)])
         return rays
 
