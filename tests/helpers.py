@@ -37,3 +37,16 @@ def rel_err(a, b):
     if not m.any():
         return 0.0
     return float(np.max(np.abs(a[m] - b[m]) / np.maximum(np.abs(b[m]), 1.0)))
+
+
+def scale_rel_err(a, b):
+    """fp32 tolerance (DESIGN.md "fp32 parity"): per surface and component, max |a-b| over the rays
+    divided by the scale of that component on that surface, max(max |b|, 1). a, b: [S, N]."""
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    assert np.array_equal(np.isnan(a), np.isnan(b)), "NaN pattern differs"
+    worst = 0.0
+    for s in range(b.shape[0]):
+        m = ~np.isnan(b[s])
+        if m.any():
+            worst = max(worst, float(np.max(np.abs(a[s][m] - b[s][m])) / max(float(np.max(np.abs(b[s][m]))), 1.0)))
+    return worst
