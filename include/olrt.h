@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define OLRT_ABI_VERSION 1
+#define OLRT_ABI_VERSION 2
 
 #define OLRT_MAX_SURFACES 64    /* intersected surfaces per system (object surface excluded) */
 #define OLRT_MAX_WAVELENGTHS 8  /* distinct wavelengths per launch */
@@ -100,6 +100,11 @@ enum {
 /* status bits (device word, OR-accumulated) */
 #define OLRT_ST_ZERNIKE_RANGE 1u /* |x/R_n|>1 or |y/R_n|>1 at a Zernike surface: zernike.py:234-246 */
 #define OLRT_ST_WAVELENGTH 2u    /* a ray wavelength is not in olrt_sys.wavelengths */
+#define OLRT_ST_BAD_HINT 4u      /* olrt_sys.kernel_hint claims something the ops table does not satisfy: nothing traced */
+
+/* kernel_hint bits */
+#define OLRT_HINT_FASTKINDS 1 /* every surface is a plane / conic / even asphere on one untilted frame,
+                                aperture none or a single RadialAperture: the straight-line kernel (trace_fk.cuh) runs */
 
 typedef struct olrt_sys {
   int32_t n_surfaces;     /* intersected surfaces */
@@ -109,7 +114,7 @@ typedef struct olrt_sys {
   int32_t ops_len;        /* int32 words in ops */
   int32_t n_record;       /* record slots */
   int32_t nr_resid_words; /* sum over Newton surfaces of (K_s + 1): shared-memory words for nr_resid */
-  int32_t reserved0;
+  int32_t kernel_hint;    /* OLRT_HINT_* (the ops table lives on the device; the host states what it holds) */
   int64_t rays_per_presc; /* ray r uses prescription r / rays_per_presc (ignored if n_presc==1) */
   double wavelengths[OLRT_MAX_WAVELENGTHS]; /* distinct wavelengths, micrometres */
 } olrt_sys;
@@ -130,6 +135,10 @@ const char* olrt_build_info(void);
  *  nr_resid   NULL or [n_surfaces][OLRT_RESID_STRIDE] u64-ordered doubles, zero-initialised by the
  *             caller: max over rays of |f| seen at Newton iteration j (NaN recorded as +inf)
  *  status     NULL or one uint32, OR-accumulated
+ *  fixup      [1 + n_rays] uint32 workspace, required by _f64 (ignored by _f32): the main kernel uses
+ *             unguarded division / square-root sequences and lists the rays whose result came out
+ *             non-finite; a second kernel re-traces exactly those with IEEE div.rn / sqrt.rn, so the
+ *             stored result is the IEEE one for every ray. fixup[0] = how many rays were re-traced.
  *  flags      OLRT_FWD_*                                                                  */
 #define OLRT_FWD_FAST 1 /* allow FMA contraction / reciprocal sharing (not bit-faithful to the reference) */
 
@@ -137,11 +146,12 @@ int olrt_trace_fwd_f64(const olrt_sys* sys /*host*/, const double* presc, const 
                        int64_t n_rays, const double* const in[8] /*host array of device ptrs*/,
                        const double* opd_in, double* const out[8] /*host array of device ptrs*/,
                        double* record, double* dir0, unsigned long long* nr_resid,
-                       uint32_t* status, int flags, void* stream);
+                       uint32_t* status, uint32_t* fixup, int flags, void* stream);
 int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
                        int64_t n_rays, const float* const in[8], const float* opd_in,
                        float* const out[8], float* record, float* dir0,
-                       unsigned long long* nr_resid, uint32_t* status, int flags, void* stream);
+                       unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags,
+                       void* stream);
 
 /* Backward (adjoint) of the forward trace: what torch autograd computes through
  * Surface.trace on the reference torch backend. Recomputes the forward from `in`.
@@ -178,6 +188,12 @@ int olrt_spot_sums_f32(const float* x, const float* y, const float* intensity, i
  * flop count basis to `sink`. Used by bench.py to measure the FP64 / FP32 FMA peak. */
 int olrt_fma_peak_f64(double* sink, int64_t iters, int blocks, int threads, void* stream);
 int olrt_fma_peak_f32(float* sink, int64_t iters, int blocks, int threads, void* stream);
+
+/* Self-test of the kernels' own IEEE division / square-root sequences (csrc/math64.cuh):
+ * quot[i] = a[i] / b[i], root[i] = sqrt(a[i]) as the trace kernels compute them; the caller compares
+ * them bit for bit with an IEEE implementation (tests/test_gpu_math.py). */
+int olrt_selftest_math_f64(const double* a, const double* b, double* quot, double* root, int64_t n,
+                           void* stream);
 
 #ifdef __cplusplus
 }

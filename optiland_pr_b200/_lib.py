@@ -10,9 +10,9 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libolrt.so")
+LIB_PATH = os.environ.get("OLRT_LIB") or os.path.join(_HERE, "libolrt.so")  # OLRT_LIB: A/B builds only
 
-OLRT_ABI_VERSION = 1
+OLRT_ABI_VERSION = 2
 MAX_SURFACES = 64
 MAX_WAVELENGTHS = 8
 MAX_NR_ITERS = 128
@@ -30,7 +30,8 @@ GEOM_PLANE, GEOM_STANDARD, GEOM_EVEN_ASPHERE, GEOM_POLYNOMIAL, GEOM_ZERNIKE, GEO
 F_RADIUS_INF, F_ABSORB = 1, 2
 AP_RADIAL, AP_OFFSET_RADIAL, AP_ELLIPTICAL, AP_RECTANGULAR = 1, 2, 3, 4
 AP_OR, AP_AND, AP_DIFF = 10, 11, 12
-ST_ZERNIKE_RANGE, ST_WAVELENGTH = 1, 2
+ST_ZERNIKE_RANGE, ST_WAVELENGTH, ST_BAD_HINT = 1, 2, 4
+HINT_FASTKINDS = 1
 FWD_FAST = 1
 SPOT_VALID_ONLY = 1
 
@@ -48,7 +49,7 @@ class OlrtSys(C.Structure):
         ("ops_len", C.c_int32),
         ("n_record", C.c_int32),
         ("nr_resid_words", C.c_int32),
-        ("reserved0", C.c_int32),
+        ("kernel_hint", C.c_int32),
         ("rays_per_presc", C.c_int64),
         ("wavelengths", C.c_double * MAX_WAVELENGTHS),
     ]
@@ -63,6 +64,7 @@ EXPORTS = [
     "olrt_trace_bwd_f64", "olrt_trace_bwd_f32",
     "olrt_spot_sums_f64", "olrt_spot_sums_f32",
     "olrt_fma_peak_f64", "olrt_fma_peak_f32",
+    "olrt_selftest_math_f64",
 ]
 
 _lib = None
@@ -89,7 +91,7 @@ def load():
     lib.olrt_version.restype = C.c_int
     lib.olrt_build_info.restype = C.c_char_p
     v = C.c_void_p
-    fwd_args = [C.POINTER(OlrtSys), v, v, C.c_int64, PtrArray8, v, PtrArray8, v, v, v, v, C.c_int, v]
+    fwd_args = [C.POINTER(OlrtSys), v, v, C.c_int64, PtrArray8, v, PtrArray8, v, v, v, v, v, C.c_int, v]
     bwd_args = [C.POINTER(OlrtSys), v, v, C.c_int64, PtrArray8, v, PtrArray8, PtrArray8, v, C.c_int, v]
     for suf in ("f64", "f32"):
         f = getattr(lib, f"olrt_trace_fwd_{suf}")
@@ -101,6 +103,8 @@ def load():
         f.argtypes = [v, v, v, C.c_int64, C.c_int64, C.c_int32, v, C.c_int, v, v]
         f = getattr(lib, f"olrt_fma_peak_{suf}")
         f.restype, f.argtypes = C.c_int, [v, C.c_int64, C.c_int, C.c_int, v]
+    lib.olrt_selftest_math_f64.restype = C.c_int
+    lib.olrt_selftest_math_f64.argtypes = [v, v, v, v, C.c_int64, v]
     if lib.olrt_version() != OLRT_ABI_VERSION:
         raise OlrtLibraryError("libolrt.so ABI version mismatch; rebuild it")
     _lib = lib

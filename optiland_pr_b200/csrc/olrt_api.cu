@@ -39,25 +39,26 @@ extern "C" const char* olrt_build_info(void) {
 extern "C" int olrt_trace_fwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops,
                                   int64_t n_rays, const double* const in[8], const double* opd_in,
                                   double* const out[8], double* record, double* dir0,
-                                  unsigned long long* nr_resid, uint32_t* status, int flags,
-                                  void* stream) {
+                                  unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup,
+                                  int flags, void* stream) {
   int rc = check_sys(sys, presc, ops, n_rays);
   if (rc) return rc;
   rc = check_rays<double>(sys, in, out);
   if (rc) return rc;
   if (sys->n_record > 0 && !record) return OLRT_E_ARG;
+  if (!fixup || n_rays > 0xffffffffLL) return OLRT_E_ARG;
   if (n_rays == 0) return OLRT_OK;
   cudaStream_t st = (cudaStream_t)stream;
   if (flags & OLRT_FWD_FAST)
-    return olrt_fast::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, st);
-  return olrt_strict::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, st);
+    return olrt_fast::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, st);
+  return olrt_strict::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, st);
 }
 
 extern "C" int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
                                   int64_t n_rays, const float* const in[8], const float* opd_in,
                                   float* const out[8], float* record, float* dir0,
-                                  unsigned long long* nr_resid, uint32_t* status, int flags,
-                                  void* stream) {
+                                  unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup,
+                                  int flags, void* stream) {
   (void)flags;
   int rc = check_sys(sys, presc, ops, n_rays);
   if (rc) return rc;
@@ -65,7 +66,7 @@ extern "C" int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const
   if (rc) return rc;
   if (sys->n_record > 0 && !record) return OLRT_E_ARG;
   if (n_rays == 0) return OLRT_OK;
-  return olrt_fast::fwd_f32(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status,
+  return olrt_fast::fwd_f32(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup,
                             (cudaStream_t)stream);
 }
 
@@ -210,6 +211,13 @@ extern "C" int olrt_fma_peak_f32(float* sink, int64_t iters, int blocks, int thr
   if (!sink || iters < 1 || blocks < 1 || threads < 1 || threads > 1024) return OLRT_E_ARG;
   fma_peak_kernel<float><<<blocks, threads, 0, (cudaStream_t)stream>>>(sink, iters);
   return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+
+extern "C" int olrt_selftest_math_f64(const double* a, const double* b, double* quot, double* root,
+                                      int64_t n, void* stream) {
+  if (!a || !b || !quot || !root || n < 0) return OLRT_E_ARG;
+  if (n == 0) return OLRT_OK;
+  return olrt_strict::selftest_math(a, b, quot, root, n, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------------

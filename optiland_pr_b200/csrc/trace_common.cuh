@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/olrt.h"
+#include "math64.cuh"
 
 namespace OLRT_NS {
 
@@ -105,14 +106,52 @@ __device__ __forceinline__ void cs_globalize(RayState<R>& r, const R* frames, in
 }
 
 // ---------------------------------------------------------------------------
-// StandardGeometry.distance                 geometries/standard.py:89-140
+// Integer powers: NumPy evaluates `a ** e` as a (e = 1), np.square (e = 2) and libm pow() for e >= 3.
+// glibc's pow is within 0.53 ulp but not always correctly rounded (measured here: equal to the
+// correctly rounded a^3 for 96 % of random doubles), so no device sequence can match it bit for bit;
+// the kernels use the chain of rounded products (<= 1 ulp from it). This is why surfaces with
+// polynomial terms of degree >= 3 are compared at 1e-10 instead of bit for bit.
+// ---------------------------------------------------------------------------
+template <typename R> struct PowChain {
+  R a, hi;
+  __device__ __forceinline__ explicit PowChain(R a_) : a(a_), hi(a_) {}
+  __device__ __forceinline__ R value() const { return hi; }
+  __device__ __forceinline__ void next() { hi = hi * a; }
+};
+
+// ---------------------------------------------------------------------------
+// Per-surface constants derived once per CTA (plain IEEE ops on the prescription, so the same
+// bits the reference gets when it evaluates them per call): staged in shared memory.
 // ---------------------------------------------------------------------------
 template <typename R>
-__device__ __forceinline__ R conic_distance(const RayState<R>& r, R radius, R k, bool radius_inf) {
+struct ConicConst {
+  R radius, k;
+  R c1;    // 1 + k                 standard.py:84, :155
+  R R2;    // radius**2
+  R twoR;  // 2 * radius            standard.py:114
+  R rR2;   // refined reciprocal of R2 (fp64: shared by every  .../radius**2)
+};
+
+template <int MM> __device__ __forceinline__ double div_R2(double a, const ConicConst<double>& cc) {
+  return div_with<MM>(a, cc.R2, cc.rR2);
+}
+template <int MM> __device__ __forceinline__ float div_R2(float a, const ConicConst<float>& cc) {
+  return a / cc.R2;
+}
+
+// ---------------------------------------------------------------------------
+// StandardGeometry.distance                 geometries/standard.py:89-140
+// The reference's b = 2(...), d = b^2 - 4ac, t = (-b +- sqrt d)/(2a) is evaluated in the half-b
+// form: scaling by 2 and 4 is exact in binary floating point, so b' = b/2, d' = d/4,
+// sqrt(d') = sqrt(d)/2 and (-b' +- sqrt d')/a are the SAME bits with fewer multiplications.
+// ---------------------------------------------------------------------------
+template <typename R, int MM>
+__device__ __forceinline__ R conic_distance(const RayState<R>& r, const ConicConst<R>& cc, bool radius_inf) {
   if (radius_inf) {  // standard.py:100-103
     const R Ns = (r_abs(r.N) > R(1e-14)) ? r.N : R(1e-14);
-    return (-r.z) / Ns;
+    return m_div<MM>(-r.z, Ns);
   }
+  const R radius = cc.radius, k = cc.k;
   if (sizeof(R) == 4) {
     // fp32 only (parity bar is a tolerance): b^2-4ac cancels catastrophically for a
     // ray launched far from the vertex, so move the origin to the ray's closest approach to the
@@ -122,7 +161,7 @@ __device__ __forceinline__ R conic_distance(const RayState<R>& r, R radius, R k,
     const R x = r.x + t0 * r.L, y = r.y + t0 * r.M, z = r.z + t0 * r.N;
     const R a = k * r.N * r.N + dd;
     const R hb = k * r.N * z + (r.L * x + r.M * y + r.N * z) - r.N * radius;
-    const R c = k * z * z - (R(2) * radius) * z + (x * x + y * y + z * z);
+    const R c = k * z * z - cc.twoR * z + (x * x + y * y + z * z);
     const R sd = r_sqrt(hb * hb - a * c);
     const R q = -(hb + ((hb < R(0)) ? -sd : sd));
     const R t1 = q / a;
@@ -132,66 +171,77 @@ __device__ __forceinline__ R conic_distance(const RayState<R>& r, R radius, R k,
     return t0 + t;
   }
   const R N2 = r.N * r.N;
-  const R a = k * N2 + r.L * r.L + r.M * r.M + N2;
-  const R b = (R(2) * k) * r.N * r.z + (R(2) * r.L) * r.x + (R(2) * r.M) * r.y -
-              (R(2) * r.N) * radius + (R(2) * r.N) * r.z;
   const R z2 = r.z * r.z;
-  const R c = k * z2 - (R(2) * radius) * r.z + r.x * r.x + r.y * r.y + z2;
-  const R d = b * b - (R(4) * a) * c;
-  const R sd = r_sqrt(d);
-  const R a2 = R(2) * a;
-  const R t1 = ((-b) + sd) / a2;
-  const R t2 = ((-b) - sd) / a2;
+  R a, hb, c;
+  if (k == R(0)) {  // 0*v + w == w bit for bit (finite v): the sphere skips the conic terms
+    a = r.L * r.L + r.M * r.M + N2;
+    hb = r.L * r.x + r.M * r.y - r.N * radius + r.N * r.z;
+    c = R(0) - cc.twoR * r.z + r.x * r.x + r.y * r.y + z2;
+  } else {
+    a = k * N2 + r.L * r.L + r.M * r.M + N2;
+    hb = (k * r.N) * r.z + r.L * r.x + r.M * r.y - r.N * radius + r.N * r.z;
+    c = k * z2 - cc.twoR * r.z + r.x * r.x + r.y * r.y + z2;
+  }
+  const R d = hb * hb - a * c;
+  const R sd = m_sqrt<MM>(d);
+  const Recip<R, MM> ra(a);
+  const R t1 = ra.div((-hb) + sd);
+  const R t2 = ra.div((-hb) - sd);
   const R z1 = r.z + t1 * r.N;
   const R zz2 = r.z + t2 * r.N;
   R t = (r_abs(z1) <= r_abs(zz2)) ? t1 : t2;
-  if (a == R(0)) t = (-c) / b;
+  if (a == R(0)) t = m_div<MM>(-c, R(2) * hb);
   return t;
 }
 
 // conic part of the sag and of the slope denominator, shared by every NR geometry
 // sag:   r2 / (R * (1 + sqrt(1 - (1+k) r2 / R^2)))     standard.py:73-87
 // denom: R * sqrt(1 - (1+k) r2 / R^2)                  standard.py:154-156
-template <typename R>
-__device__ __forceinline__ void conic_sag_denom(R r2, R radius, R k, R& sag, R& denom) {
-  const R s = r_sqrt(R(1) - (R(1) + k) * r2 / (radius * radius));
-  sag = r2 / (radius * (R(1) + s));
-  denom = radius * s;
+template <typename R, int MM>
+__device__ __forceinline__ void conic_sag_denom(R r2, const ConicConst<R>& cc, R& sag, R& denom) {
+  const R s = m_sqrt<MM>(R(1) - div_R2<MM>(cc.c1 * r2, cc));
+  sag = m_div<MM>(r2, cc.radius * (R(1) + s));
+  denom = cc.radius * s;
+}
+template <typename R, int MM>
+__device__ __forceinline__ R conic_denom(R r2, const ConicConst<R>& cc) {
+  return cc.radius * m_sqrt<MM>(R(1) - div_R2<MM>(cc.c1 * r2, cc));
+}
+
+// slopes -> unit normal: (zx, zy, -1)/|.|   standard.py:158-165 and every NR _surface_normal
+template <typename R, int MM>
+__device__ __forceinline__ void slopes_to_normal(R zx, R zy, R& nx, R& ny, R& nz) {
+  const Recip<R, MM> rm(m_sqrt<MM>(zx * zx + zy * zy + R(1)));
+  nx = rm.div(zx);
+  ny = rm.div(zy);
+  nz = rm.div(R(-1));
 }
 
 // StandardGeometry.surface_normal           geometries/standard.py:142-167
-template <typename R>
-__device__ __forceinline__ void conic_normal(R x, R y, R radius, R k, R& nx, R& ny, R& nz) {
+template <typename R, int MM>
+__device__ __forceinline__ void conic_normal(R x, R y, const ConicConst<R>& cc, R& nx, R& ny, R& nz) {
   const R r2 = x * x + y * y;
-  const R denom = radius * r_sqrt(R(1) - (R(1) + k) * r2 / (radius * radius));
-  const R dfdx = x / denom, dfdy = y / denom;
-  const R mag = r_sqrt(dfdx * dfdx + dfdy * dfdy + R(1));
-  nx = dfdx / mag;
-  ny = dfdy / mag;
-  nz = R(-1) / mag;
-}
-
-// slopes -> unit normal, common tail of every NR geometry's _surface_normal
-template <typename R>
-__device__ __forceinline__ void slopes_to_normal(R zx, R zy, R& nx, R& ny, R& nz) {
-  const R mag = r_sqrt(zx * zx + zy * zy + R(1));
-  nx = zx / mag;
-  ny = zy / mag;
-  nz = R(-1) / mag;
+  const Recip<R, MM> rd(conic_denom<R, MM>(r2, cc));
+  slopes_to_normal<R, MM>(rd.div(x), rd.div(y), nx, ny, nz);
 }
 
 // ---------------------------------------------------------------------------
 // RealRays.refract / reflect / _align_surface_normal   rays/real_rays.py:141-181, 511-547
+// u = n1/n2 and u2 = u*u are per-(surface, wavelength) constants.
 // ---------------------------------------------------------------------------
 template <typename R>
-__device__ __forceinline__ void refract(RayState<R>& r, R nx, R ny, R nz, R n1, R n2) {
-  const R L0 = r.L, M0 = r.M, N0 = r.N;
-  const R u = n1 / n2;
-  R dot = L0 * nx + M0 * ny + N0 * nz;
-  const R sg = r_sign(dot);
-  nx = nx * sg; ny = ny * sg; nz = nz * sg;
+__device__ __forceinline__ void align_normal(R& nx, R& ny, R& nz, R& dot) {
+  if (dot < R(0)) { nx = -nx; ny = -ny; nz = -nz; }        // n * sign(dot), sign = -1
+  else if (!(dot > R(0))) { const R sg = r_sign(dot); nx = nx * sg; ny = ny * sg; nz = nz * sg; }
   dot = r_abs(dot);
-  const R root = r_sqrt(R(1) - (u * u) * (R(1) - dot * dot));  // NaN => TIR
+}
+
+template <typename R, int MM>
+__device__ __forceinline__ void refract(RayState<R>& r, R nx, R ny, R nz, R u, R u2) {
+  const R L0 = r.L, M0 = r.M, N0 = r.N;
+  R dot = L0 * nx + M0 * ny + N0 * nz;
+  align_normal(nx, ny, nz, dot);
+  const R root = m_sqrt<MM>(R(1) - u2 * (R(1) - dot * dot));  // NaN => TIR
   r.L = u * L0 + nx * root - (u * nx) * dot;
   r.M = u * M0 + ny * root - (u * ny) * dot;
   r.N = u * N0 + nz * root - (u * nz) * dot;
@@ -200,9 +250,7 @@ __device__ __forceinline__ void refract(RayState<R>& r, R nx, R ny, R nz, R n1, 
 template <typename R>
 __device__ __forceinline__ void reflect(RayState<R>& r, R nx, R ny, R nz) {
   R dot = r.L * nx + r.M * ny + r.N * nz;
-  const R sg = r_sign(dot);
-  nx = nx * sg; ny = ny * sg; nz = nz * sg;
-  dot = r_abs(dot);
+  align_normal(nx, ny, nz, dot);
   const R d2 = R(2) * dot;
   r.L = r.L - d2 * nx;
   r.M = r.M - d2 * ny;

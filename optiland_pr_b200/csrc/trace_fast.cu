@@ -7,12 +7,12 @@
 namespace olrt_fast {
 int fwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, long long n_rays,
             const double* const in[8], const double* opd_in, double* const out[8], double* record,
-            double* dir0, unsigned long long* nr_resid, uint32_t* status, cudaStream_t stream) {
-  return launch_fwd<double>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, stream);
+            double* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, cudaStream_t stream) {
+  return launch_fwd<double>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, stream);
 }
 int fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, long long n_rays,
             const float* const in[8], const float* opd_in, float* const out[8], float* record,
-            float* dir0, unsigned long long* nr_resid, uint32_t* status, cudaStream_t stream) {
-  return launch_fwd<float>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, stream);
+            float* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, cudaStream_t stream) {
+  return launch_fwd<float>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, stream);
 }
 }  // namespace olrt_fast

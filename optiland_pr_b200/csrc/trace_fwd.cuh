@@ -20,6 +20,7 @@ struct FwdParams {
   const int32_t* ops;
   unsigned long long* nr_resid;
   uint32_t* status;
+  uint32_t* fixup;  // [1 + n_rays]: count, then indices of rays to re-trace in IEEE mode (fp64)
   long long n_rays;
   long long rays_per_presc;
   int n_surfaces, n_wavelengths, n_presc, presc_stride, ops_len, n_record;
@@ -27,20 +28,70 @@ struct FwdParams {
   R four_pi;  // 4*pi rounded once on the host like the reference's Python float product
 };
 
+// derived per-surface constants in shared memory: c1, R2, twoR, rR2, then u[W], u2[W], alpha[W]
+#define OLRT_DER_BASE 4
+__host__ __device__ __forceinline__ int der_stride(int W) { return OLRT_DER_BASE + 3 * W; }
+
+template <typename R> __device__ __forceinline__ R rcp_for_table(R v);
+template <> __device__ __forceinline__ double rcp_for_table<double>(double v) { return rcp_refined(v); }
+template <> __device__ __forceinline__ float rcp_for_table<float>(float v) { return 1.0f / v; }
+
+// one thread per surface: plain IEEE ops on the prescription (what the reference evaluates per call)
 template <typename R>
+__device__ __forceinline__ void derive_surface(const int32_t* s_ops, const R* s_presc, R* s_der, int s, int W,
+                                               const R* wavelengths, R four_pi) {
+  const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
+  const R* g = s_presc + op[OLRT_OP_DOFF] + op[OLRT_OP_NFRAMES] * OLRT_FRAME_REALS;
+  R* d = s_der + s * der_stride(W);
+  const R radius = g[0], k = g[1];
+  d[0] = R(1) + k;
+  d[1] = radius * radius;
+  d[2] = R(2) * radius;
+  d[3] = rcp_for_table<R>(d[1]);
+  const R* media = g + OLRT_GEOM_REALS;
+  for (int w = 0; w < W; ++w) {
+    const R u = media[w] / media[W + w];  // real_rays.py:153
+    d[OLRT_DER_BASE + w] = u;
+    d[OLRT_DER_BASE + W + w] = u * u;
+    d[OLRT_DER_BASE + 2 * W + w] = four_pi * media[2 * W + w] / wavelengths[w];  // homogeneous.py:49
+  }
+}
+
+// DIRECT: read the prescription where it lies (global memory) and derive the constants on the spot
+// (fix-up kernel: every thread may belong to a different prescription of the batch).
+template <typename R, bool DIRECT>
 __device__ __forceinline__ void load_surface(SurfParams<R>& sp, const int32_t* s_ops, const R* s_presc,
-                                             int s, int W) {
+                                             const R* s_der, int s, int W, int widx) {
   const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
   sp.op = op;
   sp.ops = s_ops;
   const R* blk = s_presc + op[OLRT_OP_DOFF];
   sp.frames = blk;
   const R* g = blk + op[OLRT_OP_NFRAMES] * OLRT_FRAME_REALS;
-  sp.radius = g[0];
-  sp.conic = g[1];
+  sp.cc.radius = g[0];
+  sp.cc.k = g[1];
   sp.tol = g[2];
   sp.norm_radius = g[3];
   sp.media = g + OLRT_GEOM_REALS;
+  sp.n1 = sp.media[widx];
+  if (DIRECT) {
+    sp.cc.c1 = R(1) + g[1];
+    sp.cc.R2 = g[0] * g[0];
+    sp.cc.twoR = R(2) * g[0];
+    sp.cc.rR2 = R(0);
+    sp.u = sp.n1 / sp.media[W + widx];
+    sp.u2 = sp.u * sp.u;
+    sp.alpha = R(0);
+  } else {
+    const R* d = s_der + s * der_stride(W);
+    sp.cc.c1 = d[0];
+    sp.cc.R2 = d[1];
+    sp.cc.twoR = d[2];
+    sp.cc.rR2 = d[3];
+    sp.u = d[OLRT_DER_BASE + widx];
+    sp.u2 = d[OLRT_DER_BASE + W + widx];
+    sp.alpha = d[OLRT_DER_BASE + 2 * W + widx];
+  }
   sp.coef = sp.media + 3 * W;
   sp.aper = blk + op[OLRT_OP_APER_DOFF];
   sp.geom = op[OLRT_OP_GEOM];
@@ -48,46 +99,73 @@ __device__ __forceinline__ void load_surface(SurfParams<R>& sp, const int32_t* s
   sp.aux = op[OLRT_OP_AUX];
 }
 
-// Surface.trace for one ray. `resid` (shared, may be null) collects max|f| per Newton iteration.
-template <typename R>
+// surface kinds: straight-line instantiations for the common cases, the interpreter for the rest
+enum { KIND_GENERIC = 0, KIND_PLANE = 1, KIND_CONIC = 2, KIND_EVEN = 3 };
+
+__device__ __forceinline__ int surface_kind(const int32_t* op) {
+  const int geom = op[OLRT_OP_GEOM], flags = op[OLRT_OP_FLAGS];
+  const bool simple = op[OLRT_OP_NFRAMES] == 1 && op[OLRT_OP_FRAMEFLAGS] == 0;
+  if (!simple) return KIND_GENERIC;
+  if (geom == OLRT_GEOM_PLANE) return KIND_PLANE;
+  if (geom == OLRT_GEOM_STANDARD && !(flags & OLRT_F_RADIUS_INF)) return KIND_CONIC;
+  if (geom == OLRT_GEOM_EVEN_ASPHERE && !(flags & OLRT_F_RADIUS_INF)) return KIND_EVEN;
+  return KIND_GENERIC;
+}
+
+// Surface.trace for one ray. KIND fixes the geometry and the single untilted frame at compile time.
+// `resid` (shared, may be null) collects max|f| per Newton iteration.
+template <typename R, int KIND, int MM>
 __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>& sp, int widx, int W,
                                              R wavelength, R four_pi, bool valid,
                                              unsigned long long* resid, uint32_t& status,
                                              R& L0, R& M0, R& N0) {
   const int32_t* op = sp.op;
-  const int flags = op[OLRT_OP_FLAGS];
-  const int nframes = op[OLRT_OP_NFRAMES], fflags = op[OLRT_OP_FRAMEFLAGS];
+  const int geom = (KIND == KIND_PLANE) ? OLRT_GEOM_PLANE
+                   : (KIND == KIND_CONIC) ? OLRT_GEOM_STANDARD
+                   : (KIND == KIND_EVEN) ? OLRT_GEOM_EVEN_ASPHERE : sp.geom;
+  const int flags = (KIND == KIND_GENERIC) ? op[OLRT_OP_FLAGS] : (op[OLRT_OP_FLAGS] & OLRT_F_ABSORB);
+  const int nframes = (KIND == KIND_GENERIC) ? op[OLRT_OP_NFRAMES] : 1;
+  const int fflags = (KIND == KIND_GENERIC) ? op[OLRT_OP_FRAMEFLAGS] : 0;
 
-  cs_localize(r, sp.frames, nframes, fflags);  // geometry.localize, standard_surface.py:199
+  // geometry.localize, standard_surface.py:199
+  if (KIND == KIND_GENERIC) cs_localize(r, sp.frames, nframes, fflags);
+  else frame_localize(r, sp.frames, 0);
 
   // t = geometry.distance(rays), standard_surface.py:211
   R t;
-  if (sp.geom == OLRT_GEOM_PLANE) {
-    t = (-r.z) / r.N;  // plane.py:61-77
+  if (geom == OLRT_GEOM_PLANE) {
+    t = m_div<MM>(-r.z, r.N);  // plane.py:61-77
   } else {
-    t = conic_distance(r, sp.radius, sp.conic, (flags & OLRT_F_RADIUS_INF) != 0);
-    if (sp.geom >= OLRT_GEOM_EVEN_ASPHERE) {  // newton_raphson.py:119-168
+    t = conic_distance<R, MM>(r, sp.cc, (flags & OLRT_F_RADIUS_INF) != 0);
+    if (geom >= OLRT_GEOM_EVEN_ASPHERE) {  // newton_raphson.py:119-168
       const int K = op[OLRT_OP_NR_ITERS];
       for (int j = 0; j <= K; ++j) {
         if (j == K && resid == nullptr) break;
         const R xi = r.x + t * r.L, yi = r.y + t * r.M, zi = r.z + t * r.N;
         R sag, zx = R(0), zy = R(0);
-        if (j < K) nr_eval<R, true>(sp, xi, yi, sag, zx, zy, status);
-        else nr_eval<R, false>(sp, xi, yi, sag, zx, zy, status);
+        if (j < K) {
+          if (KIND == KIND_EVEN) even_asphere_eval<R, true, MM>(sp, xi, yi, sag, zx, zy);
+          else nr_eval<R, true, MM>(sp, xi, yi, sag, zx, zy, status);
+        } else {
+          if (KIND == KIND_EVEN) even_asphere_eval<R, false, MM>(sp, xi, yi, sag, zx, zy);
+          else nr_eval<R, false, MM>(sp, xi, yi, sag, zx, zy, status);
+        }
         const R f = sag - zi;
         if (resid != nullptr) {
-          const unsigned long long key = valid ? resid_bits((double)r_abs(f)) : 0ull;
+          // MM_FAST: a NaN here puts the ray on the fix-up list, whose IEEE re-trace reports it instead
+          const unsigned long long key = (valid && !(MM == MM_FAST && f != f)) ? resid_bits((double)r_abs(f)) : 0ull;
           const unsigned long long wmax = warp_max_u64(key);
           if ((threadIdx.x & 31) == 0 && wmax != 0ull) atomicMax(resid + j, wmax);
         }
         if (j == K) break;
         R nx, ny, nz;
-        slopes_to_normal(zx, zy, nx, ny, nz);
+        slopes_to_normal<R, MM>(zx, zy, nx, ny, nz);
         const R nzs = (r_abs(nz) > R(1e-14)) ? nz : R(1e-14);
-        const R fx = (-nx) / nzs, fy = (-ny) / nzs;
+        const Recip<R, MM> rn(nzs);
+        const R fx = rn.div(-nx), fy = rn.div(-ny);
         const R df = fx * r.L + fy * r.M - r.N;
         const R dfs = (r_abs(df) > R(1e-14)) ? df : R(1e-14);
-        t = t - f / dfs;
+        t = t - m_div<MM>(f, dfs);
       }
     }
   }
@@ -102,8 +180,7 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
     r.i = r.i * r_exp((-alpha) * t * R(1e3));
   }
   // rays.opd = rays.opd + |t * n_pre|, standard_surface.py:218
-  const R n1 = sp.media[widx];
-  r.opd = r.opd + r_abs(t * n1);
+  r.opd = r.opd + r_abs(t * sp.n1);
 
   // aperture.clip, physical_apertures/base.py:71-82 -> real_rays.py:132-139
   const int aoff = op[OLRT_OP_APER_OFF];
@@ -114,41 +191,92 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
 
   // interaction_model.interact_real_rays, refractive_reflective_model.py:32-55
   R nx, ny, nz;
-  if (sp.geom == OLRT_GEOM_PLANE) {
+  if (geom == OLRT_GEOM_PLANE) {
     nx = R(0); ny = R(0); nz = R(1);  // plane.py:79-98
-  } else if (sp.geom == OLRT_GEOM_STANDARD) {
-    conic_normal(r.x, r.y, sp.radius, sp.conic, nx, ny, nz);
+  } else if (geom == OLRT_GEOM_STANDARD) {
+    conic_normal<R, MM>(r.x, r.y, sp.cc, nx, ny, nz);
   } else {
     R sag, zx, zy;
     uint32_t st2 = 0;
-    nr_eval<R, true>(sp, r.x, r.y, sag, zx, zy, st2);
-    slopes_to_normal(zx, zy, nx, ny, nz);
+    if (KIND == KIND_EVEN) even_asphere_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy);
+    else nr_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy, st2);
+    slopes_to_normal<R, MM>(zx, zy, nx, ny, nz);
   }
   L0 = r.L; M0 = r.M; N0 = r.N;
-  if (op[OLRT_OP_INTERACT] == 1) {
-    reflect(r, nx, ny, nz);
-  } else {
-    const R n2 = sp.media[W + widx];
-    refract(r, nx, ny, nz, n1, n2);
-  }
+  if (op[OLRT_OP_INTERACT] == 1) reflect(r, nx, ny, nz);
+  else refract<R, MM>(r, nx, ny, nz, sp.u, sp.u2);
 
-  cs_globalize(r, sp.frames, nframes, fflags);  // geometry.globalize, standard_surface.py:228
+  // geometry.globalize, standard_surface.py:228
+  if (KIND == KIND_GENERIC) cs_globalize(r, sp.frames, nframes, fflags);
+  else frame_globalize(r, sp.frames, 0);
 }
 
-template <typename R>
-__global__ void __launch_bounds__(256) trace_fwd_kernel(const FwdParams<R> P) {
+#ifndef OLRT_FWD_MIN_BLOCKS
+#define OLRT_FWD_MIN_BLOCKS 2
+#endif
+
+template <typename R> __device__ __forceinline__ bool nonfinite(R v);
+template <> __device__ __forceinline__ bool nonfinite<double>(double v) {
+  return ((unsigned)__double2hiint(v) << 1) >= 0xffe00000u;  // exponent all ones: inf or NaN
+}
+template <> __device__ __forceinline__ bool nonfinite<float>(float v) {
+  return ((unsigned)__float_as_int(v) << 1) >= 0xff000000u;
+}
+
+// all surfaces for one ray; stores the recorded surfaces on the way
+template <typename R, bool FIX>
+__device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r, const int32_t* s_ops,
+                                          const R* presc, const R* s_der, const int* s_kind,
+                                          const int* s_roff, unsigned long long* s_resid, int widx, R wl,
+                                          bool valid, long long idx, uint32_t& status, R& L0, R& M0, R& N0) {
+  const int S = P.n_surfaces, W = P.n_wavelengths;
+  const bool want_resid = (P.nr_resid != nullptr);
+  for (int s = 0; s < S; ++s) {
+    SurfParams<R> sp;
+    load_surface<R, FIX>(sp, s_ops, presc, s_der, s, W, widx);
+    unsigned long long* resid =
+        (want_resid && sp.geom >= OLRT_GEOM_EVEN_ASPHERE) ? (s_resid + s_roff[s]) : nullptr;
+    if (FIX) {
+      surface_step<R, KIND_GENERIC, MM_IEEE>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0);
+    } else {
+      switch (s_kind[s]) {  // warp-uniform
+        case KIND_PLANE: surface_step<R, KIND_PLANE, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
+        case KIND_CONIC: surface_step<R, KIND_CONIC, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
+        case KIND_EVEN: surface_step<R, KIND_EVEN, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
+        default: surface_step<R, KIND_GENERIC, MM_GUARD>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
+      }
+    }
+    const int slot = sp.op[OLRT_OP_RECORD];
+    if (slot >= 0 && valid && P.record != nullptr) {  // Surface._record, standard_surface.py:266-286
+      R* rec = P.record + (long long)slot * 8 * P.n_rays + idx;
+      rec[0] = r.x; rec[P.n_rays] = r.y; rec[2 * P.n_rays] = r.z;
+      rec[3 * P.n_rays] = r.L; rec[4 * P.n_rays] = r.M; rec[5 * P.n_rays] = r.N;
+      rec[6 * P.n_rays] = r.i; rec[7 * P.n_rays] = r.opd;
+    }
+  }
+}
+
+// FIX = false: the main pass over every ray (tiles of blockDim rays, grid-stride).
+// FIX = true : the fix-up pass over the rays the main pass listed in P.fixup (fp64 only): IEEE
+//              division / square root everywhere, prescription read in place.
+template <typename R, bool FIX>
+__global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(const FwdParams<R> P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int S = P.n_surfaces, W = P.n_wavelengths;
   R* s_presc = reinterpret_cast<R*>(smem_raw);
   const int presc_pad = (P.presc_stride + 1) & ~1;
-  int32_t* s_ops = reinterpret_cast<int32_t*>(s_presc + presc_pad);
+  R* s_der = s_presc + presc_pad;
+  const int der_pad = (S * der_stride(W) + 1) & ~1;
+  int32_t* s_ops = reinterpret_cast<int32_t*>(s_der + der_pad);
   const int ops_pad = (P.ops_len + 1) & ~1;
   unsigned long long* s_resid = reinterpret_cast<unsigned long long*>(s_ops + ops_pad);
   __shared__ int s_roff[OLRT_MAX_SURFACES + 1];
+  __shared__ int s_kind[OLRT_MAX_SURFACES];
 
-  const int S = P.n_surfaces, W = P.n_wavelengths;
   for (int q = threadIdx.x; q < P.ops_len; q += blockDim.x) s_ops[q] = P.ops[q];
   __syncthreads();
   const bool want_resid = (P.nr_resid != nullptr);
+  if (threadIdx.x < S) s_kind[threadIdx.x] = surface_kind(s_ops + threadIdx.x * OLRT_OPS_STRIDE);
   if (threadIdx.x == 0) {
     int off = 0;
     for (int s = 0; s < S; ++s) {
@@ -161,59 +289,71 @@ __global__ void __launch_bounds__(256) trace_fwd_kernel(const FwdParams<R> P) {
   __syncthreads();
   const int n_resid = s_roff[S];
   for (int q = threadIdx.x; q < n_resid; q += blockDim.x) s_resid[q] = 0ull;
+  __syncthreads();
 
   uint32_t status = 0;
   int cur_p = -1;
-  const long long n_tiles = (P.n_rays + blockDim.x - 1) / blockDim.x;
+  long long n_items = P.n_rays;
+  if (FIX) n_items = (long long)P.fixup[0];
+  const long long n_tiles = (n_items + blockDim.x - 1) / blockDim.x;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long base = tile * blockDim.x;
-    const int p = (P.n_presc > 1) ? (int)(base / P.rays_per_presc) : 0;
-    if (p != cur_p) {
-      __syncthreads();
-      const R* src = P.presc + (long long)p * P.presc_stride;
-      for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) s_presc[q] = src[q];
-      cur_p = p;
-      __syncthreads();
+    if (!FIX) {
+      const int p = (P.n_presc > 1) ? (int)(base / P.rays_per_presc) : 0;
+      if (p != cur_p) {
+        __syncthreads();
+        const R* src = P.presc + (long long)p * P.presc_stride;
+        for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) s_presc[q] = src[q];
+        cur_p = p;
+        __syncthreads();
+        if (threadIdx.x < S) derive_surface<R>(s_ops, s_presc, s_der, threadIdx.x, W, P.wavelengths, P.four_pi);
+        __syncthreads();
+      }
     }
-    const long long idx = base + threadIdx.x;
-    const bool valid = idx < P.n_rays;
-    const long long li = valid ? idx : (P.n_rays - 1);
+    const long long item = base + threadIdx.x;
+    const bool valid = item < n_items;
+    long long idx = valid ? item : (n_items - 1);
+    if (FIX) idx = (long long)P.fixup[1 + idx];
+    const R* presc = s_presc;
+    if (FIX) presc = P.presc + ((P.n_presc > 1) ? (idx / P.rays_per_presc) : 0) * P.presc_stride;
 
     RayState<R> r;
-    r.x = P.in[0][li]; r.y = P.in[1][li]; r.z = P.in[2][li];
-    r.L = P.in[3][li]; r.M = P.in[4][li]; r.N = P.in[5][li];
-    r.i = P.in[6][li];
-    r.opd = (P.opd_in != nullptr) ? P.opd_in[li] : R(0);
+    r.x = P.in[0][idx]; r.y = P.in[1][idx]; r.z = P.in[2][idx];
+    r.L = P.in[3][idx]; r.M = P.in[4][idx]; r.N = P.in[5][idx];
+    r.i = P.in[6][idx];
+    r.opd = (P.opd_in != nullptr) ? P.opd_in[idx] : R(0);
     int widx = 0;
     R wl = P.wavelengths[0];
     if (W > 1) {
-      wl = P.in[7][li];
+      wl = P.in[7][idx];
       widx = -1;
       for (int q = 0; q < W; ++q) if (wl == P.wavelengths[q]) widx = q;
       if (widx < 0) { status |= OLRT_ST_WAVELENGTH; widx = 0; r.i = R(0) / R(0); }
     }
 
     R L0 = r.L, M0 = r.M, N0 = r.N;
-    for (int s = 0; s < S; ++s) {
-      SurfParams<R> sp;
-      load_surface(sp, s_ops, s_presc, s, W);
-      unsigned long long* resid =
-          (want_resid && sp.geom >= OLRT_GEOM_EVEN_ASPHERE) ? (s_resid + s_roff[s]) : nullptr;
-      surface_step(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0);
-      const int slot = sp.op[OLRT_OP_RECORD];
-      if (slot >= 0 && valid && P.record != nullptr) {  // Surface._record, standard_surface.py:266-286
-        R* rec = P.record + (long long)slot * 8 * P.n_rays + idx;
-        rec[0] = r.x; rec[P.n_rays] = r.y; rec[2 * P.n_rays] = r.z;
-        rec[3 * P.n_rays] = r.L; rec[4 * P.n_rays] = r.M; rec[5 * P.n_rays] = r.N;
-        rec[6 * P.n_rays] = r.i; rec[7 * P.n_rays] = r.opd;
-      }
-    }
+    trace_ray<R, FIX>(P, r, s_ops, presc, s_der, s_kind, s_roff, s_resid, widx, wl, valid, idx, status,
+                      L0, M0, N0);
     if (valid) {
       P.out[0][idx] = r.x; P.out[1][idx] = r.y; P.out[2][idx] = r.z;
       P.out[3][idx] = r.L; P.out[4][idx] = r.M; P.out[5][idx] = r.N;
       P.out[6][idx] = r.i; P.out[7][idx] = r.opd;
       if (P.dir0 != nullptr) {
         P.dir0[idx] = L0; P.dir0[P.n_rays + idx] = M0; P.dir0[2 * P.n_rays + idx] = N0;
+      }
+    }
+    if (!FIX && sizeof(R) == 8 && P.fixup != nullptr) {
+      // anything non-finite (a real miss / TIR, or a value outside the fast path's domain): list the
+      // ray for the IEEE re-trace. Warp-aggregated append.
+      const bool bad = valid && (nonfinite(r.x) | nonfinite(r.y) | nonfinite(r.z) | nonfinite(r.L) |
+                                 nonfinite(r.M) | nonfinite(r.N) | nonfinite(r.opd) | nonfinite(r.i));
+      const unsigned m = __ballot_sync(0xffffffffu, bad);
+      if (m != 0u) {
+        const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+        unsigned pos = 0;
+        if (lane == leader) pos = atomicAdd(P.fixup, (unsigned)__popc(m));
+        pos = __shfl_sync(0xffffffffu, pos, leader);
+        if (bad) P.fixup[1 + pos + __popc(m & ((1u << lane) - 1u))] = (uint32_t)idx;
       }
     }
   }

@@ -11,8 +11,10 @@ struct SurfParams {      // one surface's view of the prescription staged in sha
   const int32_t* op;     // ops row
   const int32_t* ops;    // ops base (aperture programs, zernike index tables)
   const R* frames;       // NFRAMES x 9
-  R radius, conic, tol, norm_radius;
+  ConicConst<R> cc;      // radius, conic and the constants derived from them
+  R tol, norm_radius;
   const R* media;        // n_pre[W], n_post[W], k_pre[W]
+  R n1, u, u2, alpha;    // this ray's wavelength: n_pre, u = n_pre/n_post, u*u, 4 pi k_pre / lambda
   const R* coef;         // NCOEF reals
   const R* aper;         // aperture leaf parameters
   int geom, ncoef, aux;
@@ -26,39 +28,41 @@ __device__ __forceinline__ R ipow(R b, int e) {  // b**e by repeated multiplicat
 }
 
 // EvenAsphere.sag / _surface_normal         geometries/even_asphere.py:82-129
-template <typename R, bool WANT_SLOPES>
+template <typename R, bool WANT_SLOPES, int MM>
 __device__ __forceinline__ void even_asphere_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy) {
   const R r2 = x * x + y * y;
   R denom;
-  conic_sag_denom(r2, sp.radius, sp.conic, sag, denom);
-  if (WANT_SLOPES) { zx = x / denom; zy = y / denom; }
-  R pw = R(1);  // r2**i
+  conic_sag_denom<R, MM>(r2, sp.cc, sag, denom);
+  if (WANT_SLOPES) { const Recip<R, MM> rd(denom); zx = rd.div(x); zy = rd.div(y); }
+  R prev = R(1);        // r2**i
+  PowChain<R> pw(r2);   // r2**(i+1), correctly rounded like np.power
   for (int i = 0; i < sp.ncoef; ++i) {
     const R Ci = sp.coef[i];
     if (WANT_SLOPES) {
       const R two_i1 = R(2 * (i + 1));
-      zx = zx + ((two_i1 * x) * Ci) * pw;  // 2*(i+1)*x*Ci*r2**i
-      zy = zy + ((two_i1 * y) * Ci) * pw;
+      zx = zx + ((two_i1 * x) * Ci) * prev;  // 2*(i+1)*x*Ci*r2**i
+      zy = zy + ((two_i1 * y) * Ci) * prev;
     }
-    pw = pw * r2;           // r2**(i+1)
-    sag = sag + Ci * pw;    // z + Ci*r2**(i+1)
+    sag = sag + Ci * pw.value();  // z + Ci*r2**(i+1)
+    prev = pw.value();
+    if (i + 1 < sp.ncoef) pw.next();
   }
 }
 
 // OddAsphere.sag / _surface_normal          geometries/odd_asphere.py:73-129
-template <typename R, bool WANT_SLOPES>
+template <typename R, bool WANT_SLOPES, int MM>
 __device__ __forceinline__ void odd_asphere_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy) {
   const R r2 = x * x + y * y;
-  const R r = r_sqrt(r2);
+  const R r = m_sqrt<MM>(r2);
   R denom;
-  conic_sag_denom(r2, sp.radius, sp.conic, sag, denom);
-  if (WANT_SLOPES) { zx = x / denom; zy = y / denom; }
+  conic_sag_denom<R, MM>(r2, sp.cc, sag, denom);
+  if (WANT_SLOPES) { const Recip<R, MM> rd(denom); zx = rd.div(x); zy = rd.div(y); }
   R pw = R(1);  // r**i
   for (int i = 0; i < sp.ncoef; ++i) {
     const R Ci = sp.coef[i];
     if (WANT_SLOPES) {
       // (i+1)*x*Ci*r**(i-1); non-finite terms are zeroed (odd_asphere.py:117-118)
-      const R rp = (i == 0) ? (R(1) / r) : ipow(r, i - 1);
+      const R rp = (i == 0) ? m_div<MM>(R(1), r) : ipow(r, i - 1);
       R xt = ((R(i + 1) * x) * Ci) * rp;
       R yt = ((R(i + 1) * y) * Ci) * rp;
       if (!isfinite(xt)) xt = R(0);
@@ -73,12 +77,12 @@ __device__ __forceinline__ void odd_asphere_eval(const SurfParams<R>& sp, R x, R
 
 // PolynomialGeometry.sag / _surface_normal  geometries/polynomial.py:93-142
 // coef = C[i][j] row-major, I = ncoef/J rows, J = aux columns
-template <typename R, bool WANT_SLOPES>
+template <typename R, bool WANT_SLOPES, int MM>
 __device__ __forceinline__ void polynomial_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy) {
   const R r2 = x * x + y * y;
   R denom;
-  conic_sag_denom(r2, sp.radius, sp.conic, sag, denom);
-  if (WANT_SLOPES) { zx = x / denom; zy = y / denom; }
+  conic_sag_denom<R, MM>(r2, sp.cc, sag, denom);
+  if (WANT_SLOPES) { const Recip<R, MM> rd(denom); zx = rd.div(x); zy = rd.div(y); }
   const int J = sp.aux, I = (J > 0) ? sp.ncoef / J : 0;
   R xi = R(1), xim1 = R(0);  // x**i, x**(i-1)
   for (int i = 0; i < I; ++i) {
@@ -113,7 +117,7 @@ __device__ __forceinline__ void polynomial_eval(const SurfParams<R>& sp, R x, R 
 //                                                   zernike/base.py:42-299
 // Per term in coef: c, c*N, rc_0 .. rc_{smax-1}  (radial coefficients, highest power first),
 // (n, m) pairs in ops at sp.aux. cos/sin(m phi) by angle-addition from cos phi = x/rho.
-template <typename R, bool WANT_SLOPES>
+template <typename R, bool WANT_SLOPES, int MM>
 __device__ __forceinline__ void zernike_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy,
                                              uint32_t& status) {
   const R Rn = sp.norm_radius;
@@ -126,7 +130,7 @@ __device__ __forceinline__ void zernike_eval(const SurfParams<R>& sp, R x, R y, 
   if (rho > R(0)) { cph = xn / rho; sph = yn / rho; }
   const R r2 = x * x + y * y;
   R denom;
-  conic_sag_denom(r2, sp.radius, sp.conic, sag, denom);
+  conic_sag_denom<R, MM>(r2, sp.cc, sag, denom);
   R drho_dx = R(0), drho_dy = R(0), dphi_dx = R(0), dphi_dy = R(0);
   if (WANT_SLOPES) {
     zx = x / denom; zy = y / denom;
@@ -182,14 +186,14 @@ __device__ __forceinline__ void zernike_eval(const SurfParams<R>& sp, R x, R y, 
 }
 
 // dispatch: sag (and slopes) of an NR geometry at (x, y)
-template <typename R, bool WANT_SLOPES>
+template <typename R, bool WANT_SLOPES, int MM>
 __device__ __forceinline__ void nr_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy,
                                         uint32_t& status) {
   switch (sp.geom) {
-    case OLRT_GEOM_EVEN_ASPHERE: even_asphere_eval<R, WANT_SLOPES>(sp, x, y, sag, zx, zy); break;
-    case OLRT_GEOM_ODD_ASPHERE: odd_asphere_eval<R, WANT_SLOPES>(sp, x, y, sag, zx, zy); break;
-    case OLRT_GEOM_POLYNOMIAL: polynomial_eval<R, WANT_SLOPES>(sp, x, y, sag, zx, zy); break;
-    default: zernike_eval<R, WANT_SLOPES>(sp, x, y, sag, zx, zy, status); break;
+    case OLRT_GEOM_EVEN_ASPHERE: even_asphere_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy); break;
+    case OLRT_GEOM_ODD_ASPHERE: odd_asphere_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy); break;
+    case OLRT_GEOM_POLYNOMIAL: polynomial_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy); break;
+    default: zernike_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy, status); break;
   }
 }
 

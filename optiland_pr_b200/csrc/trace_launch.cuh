@@ -2,6 +2,7 @@
 // (strict / fast). Grid = one wave of persistent CTAs: SM count x resident CTAs per SM.
 #pragma once
 #include "trace_fwd.cuh"
+#include "trace_fk.cuh"
 #include "trace_bwd.cuh"
 
 namespace OLRT_NS {
@@ -21,14 +22,20 @@ inline int pick_block(const olrt_sys* sys) {
   return 0;
 }
 
+inline void launch_fixup(const FwdParams<double>& P, unsigned grid, int block, size_t smem, cudaStream_t stream) {
+  trace_fwd_kernel<double, true><<<grid, block, smem, stream>>>(P);
+}
+inline void launch_fixup(const FwdParams<float>&, unsigned, int, size_t, cudaStream_t) {}
+
 template <typename R>
 int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
                long long n_rays, const R* const in[8], const R* opd_in, R* const out[8], R* record,
-               R* dir0, unsigned long long* nr_resid, uint32_t* status, cudaStream_t stream) {
+               R* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, cudaStream_t stream) {
   FwdParams<R> P;
   for (int q = 0; q < 8; ++q) { P.in[q] = in[q]; P.out[q] = out[q]; }
   P.opd_in = opd_in; P.record = record; P.dir0 = dir0; P.presc = presc; P.ops = ops;
   P.nr_resid = nr_resid; P.status = status; P.n_rays = n_rays;
+  P.fixup = (sizeof(R) == 8) ? fixup : nullptr;
   P.rays_per_presc = sys->rays_per_presc > 0 ? sys->rays_per_presc : n_rays;
   P.n_surfaces = sys->n_surfaces; P.n_wavelengths = sys->n_wavelengths; P.n_presc = sys->n_presc;
   P.presc_stride = sys->presc_stride; P.ops_len = sys->ops_len; P.n_record = sys->n_record;
@@ -38,19 +45,38 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
   const int block = pick_block(sys);
   if (block == 0) return OLRT_E_ARG;
   const size_t smem = (size_t)((sys->presc_stride + 1) & ~1) * sizeof(R) +
+                      (size_t)((sys->n_surfaces * der_stride(sys->n_wavelengths) + 1) & ~1) * sizeof(R) +
                       (size_t)((sys->ops_len + 1) & ~1) * sizeof(int32_t) +
                       (size_t)(nr_resid ? sys->nr_resid_words : 0) * sizeof(unsigned long long);
   if (smem > 200 * 1024) return OLRT_E_LIMIT;
-  if (smem > 48 * 1024)
-    cudaFuncSetAttribute(trace_fwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (smem > 48 * 1024) {
+    cudaFuncSetAttribute(trace_fwd_kernel<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (sizeof(R) == 8)
+      cudaFuncSetAttribute(trace_fwd_kernel<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  }
+  const bool fk = (sys->kernel_hint & OLRT_HINT_FASTKINDS) != 0;
+  if (fk && smem > 48 * 1024)
+    cudaFuncSetAttribute(trace_fk_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   int per_sm = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fwd_kernel<R>, block, smem);
+  if (fk) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fk_kernel<R>, block, smem);
+  else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fwd_kernel<R, false>, block, smem);
   if (per_sm < 1) per_sm = 1;
   const long long n_tiles = (n_rays + block - 1) / block;
   long long grid = (long long)sm_count() * per_sm;
   if (grid > n_tiles) grid = n_tiles;
-  trace_fwd_kernel<R><<<(unsigned)grid, block, smem, stream>>>(P);
-  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+  if (P.fixup != nullptr) cudaMemsetAsync(P.fixup, 0, sizeof(uint32_t), stream);
+  if (fk) trace_fk_kernel<R><<<(unsigned)grid, block, smem, stream>>>(P);
+  else trace_fwd_kernel<R, false><<<(unsigned)grid, block, smem, stream>>>(P);
+  if (cudaGetLastError() != cudaSuccess) return OLRT_E_LAUNCH;
+  if (sizeof(R) == 8 && P.fixup != nullptr) {
+    // re-trace the listed rays (non-finite results) with IEEE division / sqrt; the count is read on
+    // the device, so the grid is fixed: one CTA per SM walks the list
+    long long fgrid = sm_count();
+    if (fgrid > n_tiles) fgrid = n_tiles;
+    launch_fixup(P, (unsigned)fgrid, block, smem, stream);
+    if (cudaGetLastError() != cudaSuccess) return OLRT_E_LAUNCH;
+  }
+  return OLRT_OK;
 }
 
 }  // namespace OLRT_NS

@@ -110,8 +110,30 @@ class PackedSystem:
     def nr_resid_words(self) -> int:
         return sum(self.nr_iters()[k] + 1 for k in self.nr_rows())
 
+    def fastkinds(self) -> bool:
+        """True when every surface is a plane / finite conic / even asphere on one untilted frame
+        with no aperture or a single RadialAperture (include/olrt.h,
+        OLRT_HINT_FASTKINDS; the kernel re-checks it)."""
+        for k in range(self.n_surfaces):
+            row = k * L.OPS_STRIDE
+            op = self.ops[row:row + L.OPS_STRIDE]
+            geom, flags = int(op[L.OP_GEOM]), int(op[L.OP_FLAGS])
+            if op[L.OP_NFRAMES] != 1 or op[L.OP_FRAMEFLAGS] != 0:
+                return False
+            if geom == L.GEOM_PLANE:
+                pass
+            elif geom in (L.GEOM_STANDARD, L.GEOM_EVEN_ASPHERE) and not flags & L.F_RADIUS_INF:
+                pass
+            else:
+                return False
+            aoff = int(op[L.OP_APER_OFF])
+            if aoff >= 0 and not (op[L.OP_APER_LEN] == 1 and self.ops[aoff] == L.AP_RADIAL):
+                return False
+        return True
+
     def make_sys(self, n_presc: int = 1, rays_per_presc: int = 0) -> "L.OlrtSys":
         s = L.OlrtSys()
+        s.kernel_hint = L.HINT_FASTKINDS if self.fastkinds() else 0
         s.n_surfaces = self.n_surfaces
         s.n_wavelengths = len(self.wavelengths)
         s.n_presc = n_presc

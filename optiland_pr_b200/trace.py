@@ -31,10 +31,24 @@ class TraceResult:
     nr_iters: list               # K_s actually used per intersected surface
     status: int
     launches: int
+    fixups: int = -1             # rays re-traced by the IEEE fix-up kernel (fp64; -1 = not read back)
 
 
 def _ptr(t) -> int:
     return 0 if t is None else t.data_ptr()
+
+
+_FIXUP = {}
+
+
+def _fixup_workspace(n: int, device):
+    """uint32 [1 + n] scratch for the IEEE re-trace list, cached per device (grown on demand)."""
+    key = str(device)
+    t = _FIXUP.get(key)
+    if t is None or t.numel() < n + 1:
+        t = torch.empty(max(n + 1, 1 << 16), dtype=torch.int32, device=device)
+        _FIXUP[key] = t
+    return t
 
 
 def _device_tables(packed: PackedSystem, dtype, device):
@@ -65,7 +79,7 @@ def _true_iters(resid_row: np.ndarray, k_used: int, tol: float, max_iter: int):
 def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tensor | None = None,
                 n_presc: int = 1, rays_per_presc: int = 0, want_dir0: bool = False,
                 fast: bool = False, verify_nr: bool = True, out: torch.Tensor | None = None,
-                max_relaunch: int = 24) -> TraceResult:
+                max_relaunch: int = 24, read_fixups: bool = True, check_status: bool = True) -> TraceResult:
     """Trace rays through a packed system on the current CUDA device and stream.
 
     rays_in: sequence of 8 tensors x y z L M N intensity wavelength (1-D, same length, CUDA,
@@ -104,6 +118,7 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
     dir0 = torch.empty((3, n), dtype=dtype, device=device) if want_dir0 else None
     nr_rows = packed.nr_rows()
     status_t = torch.zeros(1, dtype=torch.int32, device=device)
+    fixup = _fixup_workspace(n, device) if dtype == torch.float64 else None
     fn = lib.olrt_trace_fwd_f64 if dtype == torch.float64 else lib.olrt_trace_fwd_f32
     in_arr = L.PtrArray8(*[_ptr(t) for t in ins])
     out_arr = L.PtrArray8(*[out[q].data_ptr() for q in range(8)])
@@ -118,7 +133,7 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
             sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=rays_per_presc)
             sys_.presc_stride = int(presc_d.shape[1])
             rc = fn(C.byref(sys_), presc_d.data_ptr(), ops_d.data_ptr(), n, in_arr, _ptr(opd_in),
-                    out_arr, _ptr(record), _ptr(dir0), _ptr(resid), status_t.data_ptr(),
+                    out_arr, _ptr(record), _ptr(dir0), _ptr(resid), status_t.data_ptr(), _ptr(fixup),
                     L.FWD_FAST if fast else 0, stream)
             L.check(rc, "olrt_trace_fwd")
             launches += 1
@@ -144,6 +159,9 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
                 raise L.OlrtLibraryError("Newton iteration counts did not settle")
             packed.set_nr_iters(iters)
             status_t.zero_()
-    status = int(status_t.item()) if (nr_rows or len(packed.wavelengths) > 1) else 0
+    status = int(status_t.item()) if check_status else 0  # device->host sync
+    if status & L.ST_BAD_HINT:
+        raise L.OlrtLibraryError("kernel_hint does not match the ops table (packer bug)")
+    fixups = int(fixup[0].item()) if (fixup is not None and read_fixups and check_status) else -1
     return TraceResult(out=out, record=record, dir0=dir0, nr_iters=packed.nr_iters(), status=status,
-                       launches=launches)
+                       launches=launches, fixups=fixups)

@@ -39,14 +39,21 @@ def rel_err(a, b):
     return float(np.max(np.abs(a[m] - b[m]) / np.maximum(np.abs(b[m]), 1.0)))
 
 
-def scale_rel_err(a, b):
-    """fp32 tolerance (DESIGN.md "fp32 parity"): per surface and component, max |a-b| over the rays
-    divided by the scale of that component on that surface, max(max |b|, 1). a, b: [S, N]."""
-    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
-    assert np.array_equal(np.isnan(a), np.isnan(b)), "NaN pattern differs"
-    worst = 0.0
-    for s in range(b.shape[0]):
-        m = ~np.isnan(b[s])
-        if m.any():
-            worst = max(worst, float(np.max(np.abs(a[s][m] - b[s][m])) / max(float(np.max(np.abs(b[s][m]))), 1.0)))
-    return worst
+def fp32_errors(rec, ref):
+    """fp32 parity numbers (DESIGN.md "fp32 parity"); rec, ref: [S, 8, N].
+    positions : max |dp| over the rays of a surface / the largest |coordinate| of the bundle there
+                (relative error of the position vectors), worst surface;
+    directions: max |dL|, |dM|, |dN| (unit vectors: absolute = relative);
+    opd       : relative to the OPD itself."""
+    rec, ref = np.asarray(rec, dtype=np.float64), np.asarray(ref, dtype=np.float64)
+    assert np.array_equal(np.isnan(rec), np.isnan(ref)), "NaN pattern differs"
+    pos = dirs = opd = 0.0
+    for s in range(ref.shape[0]):
+        m = ~np.isnan(ref[s]).any(axis=0)
+        if not m.any():
+            continue
+        scale = max(float(np.max(np.abs(ref[s, 0:3][:, m]))), 1.0)
+        pos = max(pos, float(np.max(np.abs(rec[s, 0:3][:, m] - ref[s, 0:3][:, m]))) / scale)
+        dirs = max(dirs, float(np.max(np.abs(rec[s, 3:6][:, m] - ref[s, 3:6][:, m]))))
+        opd = max(opd, float(np.max(np.abs(rec[s, 7][m] - ref[s, 7][m]) / np.maximum(np.abs(ref[s, 7][m]), 1.0))))
+    return pos, dirs, opd

@@ -65,7 +65,7 @@ def test_argument_errors_do_not_need_a_gpu():
     lib = _lib.load()
     sys_ = _lib.OlrtSys()
     arr = _lib.PtrArray8()
-    rc = lib.olrt_trace_fwd_f64(ctypes.byref(sys_), None, None, 0, arr, None, arr, None, None, None, None, 0, None)
+    rc = lib.olrt_trace_fwd_f64(ctypes.byref(sys_), None, None, 0, arr, None, arr, None, None, None, None, None, 0, None)
     assert rc == -1
     rc = lib.olrt_spot_sums_f64(None, None, None, 0, 0, 1, None, 0, None, None)
     assert rc == -1
