@@ -43,6 +43,7 @@ extern "C" {
 #define OLRT_E_ARG (-1)      /* null pointer / bad size / bad table */
 #define OLRT_E_LIMIT (-2)    /* exceeds an OLRT_MAX_* limit or shared memory */
 #define OLRT_E_LAUNCH (-3)   /* cudaGetLastError() != cudaSuccess after the launch */
+#define OLRT_E_UNSUPPORTED (-4) /* the request is outside what the kernel implements (never approximated) */
 
 /* ops table, one row of OLRT_OPS_STRIDE int32 per intersected surface */
 enum {
@@ -153,18 +154,25 @@ int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* o
                        unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags,
                        void* stream);
 
-/* Backward (adjoint) of the forward trace: what torch autograd computes through
- * Surface.trace on the reference torch backend. Recomputes the forward from `in`.
- *  gout   [8] device ptrs: grads w.r.t. out x y z L M N intensity opd (NULL entry = zero)
- *  gin    [8] device ptrs: grads w.r.t. in  x y z L M N intensity opd_in (NULL entry = not wanted)
- *  gpresc [n_presc][presc_stride] accumulated with atomicAdd (caller zero-initialises)   */
-int olrt_trace_bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops,
-                       int64_t n_rays, const double* const in[8], const double* opd_in,
-                       const double* const gout[8], double* const gin[8], double* gpresc,
+/* Backward (adjoint) of the forward trace: what torch autograd computes through Surface.trace on the
+ * reference torch backend (optimization/optimizer/torch/base.py:95-154 -> loss.backward()).
+ * Checkpoints = the forward's records: the forward must have recorded EVERY surface (n_record ==
+ * n_surfaces, record slot s == surface s); record[s-1] is the state entering surface s.
+ *  record  [n_surfaces][8][n_rays] as written by olrt_trace_fwd_*
+ *  gout    [8] device ptrs or NULL: d loss / d out x y z L M N intensity opd (NULL entry = zero)
+ *  grecord NULL or [n_surfaces][8][n_rays]: d loss / d recorded state (added to gout at the last surface)
+ *  gin     [8] device ptrs: d loss / d in x y z L M N intensity opd_in (NULL entry = not wanted)
+ *  gpresc  [n_presc][presc_stride] accumulated with atomicAdd (caller zero-initialises): filled for
+ *          frame x y z, radius, conic and even-asphere coefficients; other entries stay zero
+ *  status  NULL or one uint32: OLRT_ST_BAD_HINT when a surface is outside the differentiable set (plane /
+ *          conic / even asphere with <= 8 coefficients on one untilted frame): nothing is written then   */
+int olrt_trace_bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, int64_t n_rays,
+                       const double* const in[8], const double* record, const double* const gout[8],
+                       const double* grecord, double* const gin[8], double* gpresc, uint32_t* status,
                        int flags, void* stream);
-int olrt_trace_bwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
-                       int64_t n_rays, const float* const in[8], const float* opd_in,
-                       const float* const gout[8], float* const gin[8], float* gpresc,
+int olrt_trace_bwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, int64_t n_rays,
+                       const float* const in[8], const float* record, const float* const gout[8],
+                       const float* grecord, float* const gin[8], float* gpresc, uint32_t* status,
                        int flags, void* stream);
 
 /* Spot epilogue: per-group sums over rays (ray r belongs to group r / rays_per_group).

@@ -35,7 +35,7 @@ HINT_FASTKINDS = 1
 FWD_FAST = 1
 SPOT_VALID_ONLY = 1
 
-ERRORS = {0: "ok", -1: "OLRT_E_ARG", -2: "OLRT_E_LIMIT", -3: "OLRT_E_LAUNCH"}
+ERRORS = {0: "ok", -1: "OLRT_E_ARG", -2: "OLRT_E_LIMIT", -3: "OLRT_E_LAUNCH", -4: "OLRT_E_UNSUPPORTED"}
 
 
 class OlrtSys(C.Structure):
@@ -92,7 +92,7 @@ def load():
     lib.olrt_build_info.restype = C.c_char_p
     v = C.c_void_p
     fwd_args = [C.POINTER(OlrtSys), v, v, C.c_int64, PtrArray8, v, PtrArray8, v, v, v, v, v, C.c_int, v]
-    bwd_args = [C.POINTER(OlrtSys), v, v, C.c_int64, PtrArray8, v, PtrArray8, PtrArray8, v, C.c_int, v]
+    bwd_args = [C.POINTER(OlrtSys), v, v, C.c_int64, PtrArray8, v, PtrArray8, v, PtrArray8, v, v, C.c_int, v]
     for suf in ("f64", "f32"):
         f = getattr(lib, f"olrt_trace_fwd_{suf}")
         f.restype, f.argtypes = C.c_int, fwd_args

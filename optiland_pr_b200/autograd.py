@@ -1,0 +1,123 @@
+"""torch.autograd.Function over the fused forward / backward kernels.
+
+What it replaces: torch autograd recording every elementwise op of `Surface.trace`
+(optiland/surfaces/standard_surface.py:186-233) when the reference runs on its torch backend with
+`be.grad_mode.enable()` (optimization/optimizer/torch/base.py:95-154 calls loss.backward() through
+that graph). Here the graph has ONE node: forward = `olrt_trace_fwd_*` recording every surface (the
+records are the checkpoints), backward = `olrt_trace_bwd_*`.
+
+The prescription enters the node as one flat tensor assembled by `prescription_tensor` from the live
+parameter tensors (geometry.radius / .k / .coefficients[i], cs.x / .y / .z), so gradients flow on to
+whatever those depend on (e.g. cs.z of later surfaces on an earlier thickness, optic_updater.py:67-85).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from .prescription import PackedSystem
+from .trace import _device_tables, _fixup_workspace, _ptr, fused_trace
+
+
+def _live_entries(packed: PackedSystem, surfaces):
+    """[(offset in the prescription, tensor)] for every parameter that is a torch tensor."""
+    out = []
+    for lay in packed.layouts:
+        surf = surfaces[lay.index]
+        g = surf.geometry
+        cs = g.cs
+        for q, nm in enumerate(("x", "y", "z")):
+            v = getattr(cs, nm)
+            if isinstance(v, torch.Tensor):
+                out.append((lay.frames + q, v))
+        if lay.geom != L.GEOM_PLANE:
+            if isinstance(g.radius, torch.Tensor):
+                out.append((lay.radius, g.radius))
+            if isinstance(getattr(g, "k", None), torch.Tensor):
+                out.append((lay.conic, g.k))
+        if lay.geom in (L.GEOM_EVEN_ASPHERE, L.GEOM_ODD_ASPHERE):
+            for i, c in enumerate(g.coefficients):
+                if isinstance(c, torch.Tensor):
+                    out.append((lay.coef + i, c))
+    return out
+
+
+def prescription_tensor(packed: PackedSystem, surfaces, dtype, device) -> torch.Tensor:
+    """Flat prescription [stride] on `device`, differentiable w.r.t. the live parameter tensors."""
+    base = torch.from_numpy(np.ascontiguousarray(packed.presc[0])).to(device=device, dtype=dtype)
+    live = _live_entries(packed, surfaces)
+    if not live:
+        return base
+    idx = torch.tensor([o for o, _ in live], dtype=torch.int64, device=device)
+    vals = torch.stack([t.to(device=device, dtype=dtype).reshape(()) for _, t in live])
+    return base.scatter(0, idx, vals)
+
+
+class FusedTraceFn(torch.autograd.Function):
+    """(presc, x, y, z, L, M, N, i, opd_in, w) -> (out [8, N], record [S, 8, N])."""
+
+    @staticmethod
+    def forward(ctx, presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast):
+        if packed.record_surfaces != [lay.index for lay in packed.layouts]:
+            raise L.OlrtLibraryError("the differentiable trace needs every surface recorded (record='all')")
+        ins = [x, y, z, Lc, M, N, inten, w]
+        res = fused_trace(packed, [t.detach() if t is not None else None for t in ins],
+                          opd_in=None if opd_in is None else opd_in.detach(),
+                          presc=presc.detach().reshape(1, -1), want_dir0=True, fast=fast)
+        ctx.packed = packed
+        ctx.nr_iters = list(res.nr_iters)
+        ctx.save_for_backward(presc.detach(), *[t.detach() for t in ins if t is not None], res.record)
+        ctx.has_w = w is not None
+        ctx.has_opd = opd_in is not None
+        ctx.status = res.status
+        ctx.dir0 = res.dir0
+        ctx.mark_non_differentiable(res.dir0)
+        return res.out, res.record, res.dir0
+
+    @staticmethod
+    def backward(ctx, gout, grecord, _gdir0):
+        packed = ctx.packed
+        saved = ctx.saved_tensors
+        presc, record = saved[0], saved[-1]
+        ins = list(saved[1:-1])
+        if not ctx.has_w:
+            ins.append(None)
+        dtype, device = record.dtype, record.device
+        n = int(record.shape[2])
+        lib = L.load()
+        packed.set_nr_iters(ctx.nr_iters)
+        ops_d, _ = _device_tables(packed, dtype, device)
+        gin = torch.zeros((8, n), dtype=dtype, device=device)
+        gpresc = torch.zeros_like(presc)
+        status = torch.zeros(1, dtype=torch.int32, device=device)
+        gout = None if gout is None else gout.contiguous()
+        grecord = None if grecord is None else grecord.contiguous()
+        sys_ = packed.make_sys()
+        sys_.presc_stride = int(presc.numel())
+        fn = lib.olrt_trace_bwd_f64 if dtype == torch.float64 else lib.olrt_trace_bwd_f32
+        in_arr = L.PtrArray8(*[_ptr(t) for t in ins])
+        gout_arr = L.PtrArray8(*[0 if gout is None else gout[q].data_ptr() for q in range(8)])
+        gin_arr = L.PtrArray8(*[gin[q].data_ptr() for q in range(8)])
+        with torch.cuda.device(device):
+            rc = fn(C.byref(sys_), presc.data_ptr(), ops_d.data_ptr(), n, in_arr, record.data_ptr(), gout_arr,
+                    _ptr(grecord), gin_arr, gpresc.data_ptr(), status.data_ptr(), 0,
+                    torch.cuda.current_stream(device).cuda_stream)
+        if rc == -4:
+            raise NotImplementedError("olrt_trace_bwd: this lens is outside the differentiable set")
+        L.check(rc, "olrt_trace_bwd")
+        if int(status.item()) & L.ST_BAD_HINT:
+            raise NotImplementedError(
+                "olrt_trace_bwd: gradients are implemented for plane / conic / even-asphere surfaces on an "
+                "untilted frame; this lens has a surface outside that set")
+        g = [gin[q] for q in range(7)]
+        return (gpresc, g[0], g[1], g[2], g[3], g[4], g[5], g[6], gin[7] if ctx.has_opd else None, None, None,
+                None)
+
+
+def trace_differentiable(packed: PackedSystem, presc: torch.Tensor, rays_in, opd_in=None, fast: bool = False):
+    """rays_in: 8 tensors (w may be None for a single wavelength). Returns (out, record, dir0)."""
+    x, y, z, Lc, M, N, inten, w = (list(rays_in) + [None])[:8]
+    return FusedTraceFn.apply(presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast)

@@ -223,19 +223,39 @@ extern "C" int olrt_selftest_math_f64(const double* a, const double* b, double* 
 // ---------------------------------------------------------------------------------------------
 // backward (adjoint) entry points
 // ---------------------------------------------------------------------------------------------
+template <typename R>
+static int check_bwd(const olrt_sys* sys, const R* presc, const int32_t* ops, long long n_rays,
+                     const R* const in[8], const R* record, R* gpresc) {
+  int rc = check_sys(sys, presc, ops, n_rays);
+  if (rc) return rc;
+  if (!in || !record || !gpresc) return OLRT_E_ARG;
+  for (int q = 0; q < 7; ++q)
+    if (!in[q]) return OLRT_E_ARG;
+  if (sys->n_wavelengths > 1 && !in[7]) return OLRT_E_ARG;
+  if (sys->n_record != sys->n_surfaces) return OLRT_E_UNSUPPORTED;  // every surface must be recorded
+  return OLRT_OK;
+}
+
 extern "C" int olrt_trace_bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops,
-                                  int64_t n_rays, const double* const in[8], const double* opd_in,
-                                  const double* const gout[8], double* const gin[8], double* gpresc,
-                                  int flags, void* stream) {
-  (void)sys; (void)presc; (void)ops; (void)n_rays; (void)in; (void)opd_in; (void)gout; (void)gin;
-  (void)gpresc; (void)flags; (void)stream;
-  return OLRT_E_ARG;  // filled in by the backward milestone
+                                  int64_t n_rays, const double* const in[8], const double* record,
+                                  const double* const gout[8], const double* grecord,
+                                  double* const gin[8], double* gpresc, uint32_t* status, int flags,
+                                  void* stream) {
+  (void)flags;
+  int rc = check_bwd<double>(sys, presc, ops, n_rays, in, record, gpresc);
+  if (rc) return rc;
+  if (n_rays == 0) return OLRT_OK;
+  return olrt_fast::bwd_f64(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status,
+                            (cudaStream_t)stream);
 }
 extern "C" int olrt_trace_bwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
-                                  int64_t n_rays, const float* const in[8], const float* opd_in,
-                                  const float* const gout[8], float* const gin[8], float* gpresc,
-                                  int flags, void* stream) {
-  (void)sys; (void)presc; (void)ops; (void)n_rays; (void)in; (void)opd_in; (void)gout; (void)gin;
-  (void)gpresc; (void)flags; (void)stream;
-  return OLRT_E_ARG;
+                                  int64_t n_rays, const float* const in[8], const float* record,
+                                  const float* const gout[8], const float* grecord, float* const gin[8],
+                                  float* gpresc, uint32_t* status, int flags, void* stream) {
+  (void)flags;
+  int rc = check_bwd<float>(sys, presc, ops, n_rays, in, record, gpresc);
+  if (rc) return rc;
+  if (n_rays == 0) return OLRT_OK;
+  return olrt_fast::bwd_f32(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status,
+                            (cudaStream_t)stream);
 }

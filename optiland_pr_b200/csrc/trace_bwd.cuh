@@ -1,3 +1,427 @@
-// trace_bwd.cuh -- adjoint kernel (filled in by the backward milestone)
+// trace_bwd.cuh -- the adjoint (backward) kernel of the fused trace: what torch autograd computes through
+//   Surface.trace                      optiland/surfaces/standard_surface.py:186-233
+// on the reference's torch backend, for one ray per thread, surface by surface in REVERSE order.
+//
+// Checkpoints: the forward launch records the post-interaction global state of every surface
+// (Surface._record, standard_surface.py:266-286); record[s-1] is exactly the state that enters
+// surface s, so this kernel never re-traces the system: per surface it loads the 7 entry values,
+// recomputes that one surface keeping the intermediates in registers, and pulls the incoming
+// gradients (d loss / d state after surface s) back to the entry state and to the surface's
+// prescription entries. Parameter gradients: per-thread partials -> warp shuffles -> one
+// shared-memory atomic per warp -> one global atomicAdd per CTA and entry at the end.
+//
+// Newton-Raphson surfaces are differentiated the way autograd sees them: the K batch-uniform updates
+// t <- t - f/f' actually taken in the forward are unrolled and each is differentiated exactly (with the
+// second derivatives of the sag), NOT replaced by the implicit-function gradient of the converged
+// root -- the two differ by O(residual), more than the 1e-8 gradient bar when tol = 1e-6.
+//
+// Differentiable here: plane, sphere / conic, even asphere on a single untilted frame (the fast kinds
+// of trace_fk.cuh) with any aperture program, absorption, refraction and reflection; gradients w.r.t.
+// frame x y z, radius, conic, even-asphere coefficients and the input rays x y z L M N intensity opd.
+// Anything else returns OLRT_E_UNSUPPORTED on the host side (no silent approximation).
 #pragma once
-#include "trace_geom.cuh"
+#include "trace_fwd.cuh"
+
+namespace OLRT_NS {
+
+#define OLRT_BWD_MAXC 8  // even-asphere coefficients with a gradient slot in registers
+
+template <typename R>
+struct BwdParams {
+  const R* in[8];
+  const R* record;    // [S][8][N] forward records, slot s == surface s
+  const R* gout[8];   // d loss / d final state (entries may be null)
+  const R* grecord;   // null or [S][8][N]: d loss / d recorded state of every surface
+  R* gin[8];          // d loss / d x y z L M N intensity opd_in (entries may be null)
+  R* gpresc;          // [n_presc][presc_stride], atomically accumulated
+  const R* presc;
+  const int32_t* ops;
+  long long n_rays;
+  long long rays_per_presc;
+  int n_surfaces, n_wavelengths, n_presc, presc_stride, ops_len;
+  R wavelengths[OLRT_MAX_WAVELENGTHS];
+  R four_pi;
+};
+
+template <typename R>
+__device__ __forceinline__ R b_div(R a, R b) { return a / b; }
+
+// sag S, slope factor G (zx = x G, zy = y G) and dG/dr2 of conic + even-asphere terms at (x, y)
+template <typename R>
+struct SagEval {
+  R r2, s, S, G, Gp;
+};
+
+template <typename R>
+__device__ __forceinline__ void sag_eval(const SurfParams<R>& sp, bool plane, R x, R y, SagEval<R>& e) {
+  e.r2 = x * x + y * y;
+  if (plane) { e.s = R(1); e.S = R(0); e.G = R(0); e.Gp = R(0); return; }
+  const R Rr = sp.cc.radius, c1 = sp.cc.c1;
+  const R B = R(1) - c1 * e.r2 / (Rr * Rr);
+  e.s = sqrt(B);
+  e.S = e.r2 / (Rr * (R(1) + e.s));
+  e.G = R(1) / (Rr * e.s);
+  e.Gp = c1 / (R(2) * Rr * Rr * Rr * e.s * e.s * e.s);
+  if (sp.geom == OLRT_GEOM_EVEN_ASPHERE) {
+    R pw = R(1), pwm1 = R(0);  // r2^i, r2^(i-1)
+    for (int i = 0; i < sp.ncoef; ++i) {
+      const R Ci = sp.coef[i];
+      const R k2 = R(2 * (i + 1));
+      e.G += k2 * Ci * pw;
+      e.Gp += k2 * R(i) * Ci * pwm1;
+      pwm1 = pw;
+      pw = pw * e.r2;
+      e.S += Ci * pw;
+    }
+  }
+}
+
+// adjoint of (S, zx, zy)(x, y; R, k, C) given (gS, gzx, gzy); accumulates gx, gy and the parameter partials
+template <typename R>
+__device__ __forceinline__ void sag_adjoint(const SurfParams<R>& sp, bool plane, R x, R y, const SagEval<R>& e,
+                                            R gS, R gzx, R gzy, R& gx, R& gy, R& gR, R& gk, R* gC) {
+  if (plane) return;
+  const R q = gzx * x + gzy * y;  // gradient w.r.t. G
+  const R zx = x * e.G, zy = y * e.G;
+  gx += gS * zx + gzx * e.G + q * e.Gp * (R(2) * x);
+  gy += gS * zy + gzy * e.G + q * e.Gp * (R(2) * y);
+  const R Rr = sp.cc.radius, c1 = sp.cc.c1, s = e.s, r2 = e.r2;
+  const R ds_dR = c1 * r2 / (Rr * Rr * Rr * s);
+  const R ds_dk = -r2 / (R(2) * Rr * Rr * s);
+  const R one_s = R(1) + s;
+  const R dSc_ds = -r2 / (Rr * one_s * one_s);
+  const R dSc_dR = -r2 / (Rr * Rr * one_s) + dSc_ds * ds_dR;
+  const R dg0_ds = -R(1) / (Rr * s * s);
+  const R dg0_dR = -R(1) / (Rr * Rr * s) + dg0_ds * ds_dR;
+  gR += gS * dSc_dR + q * dg0_dR;
+  gk += gS * dSc_ds * ds_dk + q * dg0_ds * ds_dk;
+  if (sp.geom == OLRT_GEOM_EVEN_ASPHERE) {
+    R pw = R(1);
+#pragma unroll
+    for (int i = 0; i < OLRT_BWD_MAXC; ++i) {
+      if (i < sp.ncoef) {
+        const R k2 = R(2 * (i + 1));
+        const R pw1 = pw * r2;
+        gC[i] += gS * pw1 + q * k2 * pw;
+        pw = pw1;
+      }
+    }
+  }
+}
+
+// closed-form conic intersection in the half-b form (trace_common.cuh); also returns a, hb for the adjoint
+template <typename R>
+__device__ __forceinline__ R conic_t(const SurfParams<R>& sp, R x, R y, R z, R L, R M, R N, R& a, R& hb) {
+  const R Rr = sp.cc.radius, k = sp.cc.k;
+  a = k * N * N + L * L + M * M + N * N;
+  hb = k * N * z + L * x + M * y - N * Rr + N * z;
+  const R c = k * z * z - R(2) * Rr * z + x * x + y * y + z * z;
+  const R sd = sqrt(hb * hb - a * c);
+  const R t1 = (-hb + sd) / a, t2 = (-hb - sd) / a;
+  R t = (r_abs(z + t1 * N) <= r_abs(z + t2 * N)) ? t1 : t2;
+  if (a == R(0)) t = -c / (R(2) * hb);
+  return t;
+}
+
+template <typename R>
+__device__ __forceinline__ R warp_sum(R v) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// one surface, reverse mode. Entry state e* (global), incoming grads g* (w.r.t. the state after the surface,
+// global) are replaced by the grads w.r.t. the entry state. gi: intensity, gopd: opd (passes through).
+template <typename R>
+__device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int widx, R ex, R ey, R ez, R eL, R eM,
+                                            R eN, R ei, R& gx, R& gy, R& gz, R& gL, R& gM, R& gN, R& gi, R gopd,
+                                            R& gTx, R& gTy, R& gTz, R& gR, R& gk, R* gC) {
+  const int32_t* op = sp.op;
+  const bool plane = (sp.geom == OLRT_GEOM_PLANE);
+  const int flags = op[OLRT_OP_FLAGS];
+  const R* f = sp.frames;
+  // ---- forward recompute (local frame)
+  const R x = ex - f[0], y = ey - f[1], z = ez - f[2];
+  const R L = eL, M = eM, N = eN;
+  R a = R(0), hb = R(0), t0;
+  if (plane) t0 = -z / N;
+  else t0 = conic_t(sp, x, y, z, L, M, N, a, hb);
+  const int K = (sp.geom == OLRT_GEOM_EVEN_ASPHERE) ? op[OLRT_OP_NR_ITERS] : 0;
+  R t = t0;
+  for (int j = 0; j < K; ++j) {
+    SagEval<R> e;
+    const R qx = x + t * L, qy = y + t * M, qz = z + t * N;
+    sag_eval(sp, false, qx, qy, e);
+    const R h = qx * e.G * L + qy * e.G * M - N;
+    t = t - (e.S - qz) / h;
+  }
+  const R Qx = x + t * L, Qy = y + t * M;
+  SagEval<R> eq;
+  sag_eval(sp, plane, Qx, Qy, eq);
+  R nx, ny, nz, mag = R(1);
+  const R zx = Qx * eq.G, zy = Qy * eq.G;
+  if (plane) { nx = R(0); ny = R(0); nz = R(1); }
+  else { mag = sqrt(zx * zx + zy * zy + R(1)); nx = zx / mag; ny = zy / mag; nz = R(-1) / mag; }
+  const R dot = L * nx + M * ny + N * nz;
+  const R sg = r_sign(dot), c = r_abs(dot);
+  const R ax = nx * sg, ay = ny * sg, az = nz * sg;  // aligned normal
+  // ---- adjoint of globalize: out = local + T
+  gTx += gx; gTy += gy; gTz += gz;
+  // ---- interaction
+  R gDx, gDy, gDz, gax, gay, gaz, gc;
+  if (op[OLRT_OP_INTERACT] == 1) {  // D' = D - 2 c a
+    gDx = gL; gDy = gM; gDz = gN;
+    gc = R(-2) * (ax * gL + ay * gM + az * gN);
+    gax = R(-2) * c * gL; gay = R(-2) * c * gM; gaz = R(-2) * c * gN;
+  } else {  // D' = u D + a (root - u c)
+    const R u = sp.u, u2 = sp.u2;
+    const R root = sqrt(R(1) - u2 * (R(1) - c * c));
+    const R w = root - u * c;
+    gDx = u * gL; gDy = u * gM; gDz = u * gN;
+    gax = w * gL; gay = w * gM; gaz = w * gN;
+    const R gw = ax * gL + ay * gM + az * gN;
+    gc = -u * gw + (gw / (R(2) * root)) * (R(2) * u2 * c);
+  }
+  const R gdot = sg * gc;
+  R gnx = sg * gax + gdot * L, gny = sg * gay + gdot * M, gnz = sg * gaz + gdot * N;
+  gDx += gdot * nx; gDy += gdot * ny; gDz += gdot * nz;
+  // ---- normal = (zx, zy, -1) / mag
+  R gzx = R(0), gzy = R(0);
+  if (!plane) {
+    const R ng = nx * gnx + ny * gny + nz * gnz;
+    gzx = (gnx - nx * ng) / mag;
+    gzy = (gny - ny * ng) / mag;
+  }
+  R gQx = gx, gQy = gy, gQz = gz;  // position after propagation (clip and interaction do not move it)
+  sag_adjoint(sp, plane, Qx, Qy, eq, R(0), gzx, gzy, gQx, gQy, gR, gk, gC);
+  // ---- clip (where(~inside, 0, i)), absorption, opd
+  R gt = gopd * ((t * sp.n1 < R(0)) ? -sp.n1 : sp.n1);
+  const int aoff = op[OLRT_OP_APER_OFF];
+  if (aoff >= 0) {
+    if (!aperture_contains(sp.ops + aoff, op[OLRT_OP_APER_LEN], sp.aper, Qx, Qy)) gi = R(0);
+  }
+  if (flags & OLRT_F_ABSORB) {
+    const R alpha = sp.alpha;  // 4 pi k / lambda, homogeneous.py:49
+    const R E = r_exp((-alpha) * t * R(1e3));
+    gt += gi * ei * E * (-alpha * R(1e3));  // i' = i E
+    gi = gi * E;
+  }
+  // ---- Q = P + t D
+  R gPx = gQx, gPy = gQy, gPz = gQz;
+  gDx += t * gQx; gDy += t * gQy; gDz += t * gQz;
+  R gtj = gt + L * gQx + M * gQy + N * gQz;
+  // ---- Newton updates in reverse: t_{j+1} = t_j - f_j / h_j
+  for (int j = K - 1; j >= 0; --j) {
+    R tj = t0;
+    for (int q = 0; q < j; ++q) {  // recompute t_j (K is 1-3 in practice)
+      SagEval<R> e;
+      const R qx = x + tj * L, qy = y + tj * M, qz = z + tj * N;
+      sag_eval(sp, false, qx, qy, e);
+      tj = tj - (e.S - qz) / (qx * e.G * L + qy * e.G * M - N);
+    }
+    SagEval<R> e;
+    const R qx = x + tj * L, qy = y + tj * M, qz = z + tj * N;
+    sag_eval(sp, false, qx, qy, e);
+    const R sx = qx * e.G, sy = qy * e.G;
+    const R fj = e.S - qz, h = sx * L + sy * M - N;
+    const R gf = -gtj / h, gh = gtj * fj / (h * h);
+    gDx += gh * sx; gDy += gh * sy; gDz -= gh;
+    R gqx = R(0), gqy = R(0);
+    const R gqz = -gf;
+    sag_adjoint(sp, false, qx, qy, e, gf, gh * L, gh * M, gqx, gqy, gR, gk, gC);
+    gPx += gqx; gPy += gqy; gPz += gqz;
+    gDx += tj * gqx; gDy += tj * gqy; gDz += tj * gqz;
+    gtj = gtj + L * gqx + M * gqy + N * gqz;
+  }
+  // ---- t0: plane or conic (implicit differentiation of the quadratic the root satisfies)
+  if (plane) {
+    gPz += -gtj / N;
+    gDz += -gtj * t0 / N;
+  } else {
+    const R Rr = sp.cc.radius, k = sp.cc.k;
+    const R den = R(2) * (a * t0 + hb);
+    const R ga = -gtj * t0 * t0 / den, ghb = -gtj * R(2) * t0 / den, gcc = -gtj / den;
+    gk += ga * N * N + ghb * N * z + gcc * z * z;
+    gR += -ghb * N - R(2) * gcc * z;
+    gDx += ga * R(2) * L + ghb * x;
+    gDy += ga * R(2) * M + ghb * y;
+    gDz += ga * R(2) * N * (k + R(1)) + ghb * (k * z - Rr + z);
+    gPx += ghb * L + R(2) * gcc * x;
+    gPy += ghb * M + R(2) * gcc * y;
+    gPz += ghb * (k * N + N) + gcc * (R(2) * k * z - R(2) * Rr + R(2) * z);
+  }
+  // ---- localize: P = entry - T
+  gTx -= gPx; gTy -= gPy; gTz -= gPz;
+  gx = gPx; gy = gPy; gz = gPz;
+  gL = gDx; gM = gDy; gN = gDz;
+}
+
+
+template <typename R>
+__device__ __forceinline__ bool bwd_supported(const int32_t* s_ops, int s) {
+  const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
+  const int k = surface_kind(op);
+  if (k == KIND_GENERIC) return false;
+  if (op[OLRT_OP_GEOM] == OLRT_GEOM_EVEN_ASPHERE && op[OLRT_OP_NCOEF] > OLRT_BWD_MAXC) return false;
+  return op[OLRT_OP_RECORD] == s;
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256) trace_bwd_kernel(const BwdParams<R> P, uint32_t* status) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int S = P.n_surfaces, W = P.n_wavelengths;
+  R* s_presc = reinterpret_cast<R*>(smem_raw);
+  const int presc_pad = (P.presc_stride + 1) & ~1;
+  R* s_der = s_presc + presc_pad;
+  const int der_pad = (S * der_stride(W) + 1) & ~1;
+  R* s_gp = s_der + der_pad;  // block accumulator of d loss / d presc
+  int32_t* s_ops = reinterpret_cast<int32_t*>(s_gp + presc_pad);
+  __shared__ int s_bad;
+
+  for (int q = threadIdx.x; q < P.ops_len; q += blockDim.x) s_ops[q] = P.ops[q];
+  for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) s_gp[q] = R(0);
+  if (threadIdx.x == 0) s_bad = 0;
+  __syncthreads();
+  if (threadIdx.x < S && !bwd_supported<R>(s_ops, threadIdx.x)) s_bad = 1;
+  __syncthreads();
+  if (s_bad) {
+    if (threadIdx.x == 0 && status != nullptr) atomicOr(status, OLRT_ST_BAD_HINT);
+    return;
+  }
+  const long long N = P.n_rays;
+  const int lane = threadIdx.x & 31;
+  int cur_p = -1;
+  const long long n_tiles = (N + blockDim.x - 1) / blockDim.x;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long base = tile * blockDim.x;
+    const int p = (P.n_presc > 1) ? (int)(base / P.rays_per_presc) : 0;
+    if (p != cur_p) {
+      __syncthreads();
+      if (cur_p >= 0) {  // flush the previous prescription's gradients
+        for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) {
+          const R v = s_gp[q];
+          if (v != R(0)) atomicAdd(P.gpresc + (long long)cur_p * P.presc_stride + q, v);
+          s_gp[q] = R(0);
+        }
+      }
+      const R* src = P.presc + (long long)p * P.presc_stride;
+      for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) s_presc[q] = src[q];
+      cur_p = p;
+      __syncthreads();
+      if (threadIdx.x < S) derive_surface<R>(s_ops, s_presc, s_der, threadIdx.x, W, P.wavelengths, P.four_pi);
+      __syncthreads();
+    }
+    const long long item = base + threadIdx.x;
+    const bool valid = item < N;
+    const long long idx = valid ? item : (N - 1);
+    int widx = 0;
+    if (W > 1) {
+      const R wl = P.in[7][idx];
+      for (int q = 0; q < W; ++q) if (wl == P.wavelengths[q]) widx = q;
+    }
+    auto ld = [&](const R* ptr) { return (ptr != nullptr && valid) ? ptr[idx] : R(0); };
+    R gx = ld(P.gout[0]), gy = ld(P.gout[1]), gz = ld(P.gout[2]);
+    R gL = ld(P.gout[3]), gM = ld(P.gout[4]), gN = ld(P.gout[5]);
+    R gi = ld(P.gout[6]), gopd = ld(P.gout[7]);
+    for (int s = S - 1; s >= 0; --s) {
+      if (P.grecord != nullptr && valid) {
+        const R* g = P.grecord + (long long)s * 8 * N + idx;
+        gx += g[0]; gy += g[N]; gz += g[2 * N]; gL += g[3 * N]; gM += g[4 * N]; gN += g[5 * N];
+        gi += g[6 * N]; gopd += g[7 * N];
+      }
+      R ex, ey, ez, eL, eM, eN, ei;
+      if (s == 0) {
+        ex = P.in[0][idx]; ey = P.in[1][idx]; ez = P.in[2][idx];
+        eL = P.in[3][idx]; eM = P.in[4][idx]; eN = P.in[5][idx]; ei = P.in[6][idx];
+      } else {
+        const R* rc = P.record + (long long)(s - 1) * 8 * N + idx;
+        ex = rc[0]; ey = rc[N]; ez = rc[2 * N]; eL = rc[3 * N]; eM = rc[4 * N]; eN = rc[5 * N]; ei = rc[6 * N];
+      }
+      SurfParams<R> sp;
+      load_surface<R, false>(sp, s_ops, s_presc, s_der, s, W, widx);
+      R gTx = R(0), gTy = R(0), gTz = R(0), gR = R(0), gk = R(0);
+      R gC[OLRT_BWD_MAXC];
+#pragma unroll
+      for (int i = 0; i < OLRT_BWD_MAXC; ++i) gC[i] = R(0);
+      bwd_surface<R>(sp, W, widx, ex, ey, ez, eL, eM, eN, ei, gx, gy, gz, gL, gM, gN, gi, gopd, gTx, gTy, gTz,
+                     gR, gk, gC);
+      if (!valid) { gTx = gTy = gTz = gR = gk = R(0); }
+      // parameter partials: warp shuffle -> one shared atomic per warp
+      const int doff = sp.op[OLRT_OP_DOFF];
+      const int goff = doff + sp.op[OLRT_OP_NFRAMES] * OLRT_FRAME_REALS;
+      R v;
+      v = warp_sum(gTx); if (lane == 0) atomicAdd(s_gp + doff + 0, v);
+      v = warp_sum(gTy); if (lane == 0) atomicAdd(s_gp + doff + 1, v);
+      v = warp_sum(gTz); if (lane == 0) atomicAdd(s_gp + doff + 2, v);
+      if (sp.geom != OLRT_GEOM_PLANE) {
+        v = warp_sum(gR); if (lane == 0) atomicAdd(s_gp + goff + 0, v);
+        v = warp_sum(gk); if (lane == 0) atomicAdd(s_gp + goff + 1, v);
+        if (sp.geom == OLRT_GEOM_EVEN_ASPHERE) {
+          const int coff = goff + OLRT_GEOM_REALS + 3 * W;
+#pragma unroll
+          for (int i = 0; i < OLRT_BWD_MAXC; ++i) {
+            if (i < sp.ncoef) {
+              v = warp_sum(valid ? gC[i] : R(0));
+              if (lane == 0) atomicAdd(s_gp + coff + i, v);
+            }
+          }
+        }
+      }
+    }
+    if (valid) {
+      if (P.gin[0]) P.gin[0][idx] = gx;
+      if (P.gin[1]) P.gin[1][idx] = gy;
+      if (P.gin[2]) P.gin[2][idx] = gz;
+      if (P.gin[3]) P.gin[3][idx] = gL;
+      if (P.gin[4]) P.gin[4][idx] = gM;
+      if (P.gin[5]) P.gin[5][idx] = gN;
+      if (P.gin[6]) P.gin[6][idx] = gi;
+      if (P.gin[7]) P.gin[7][idx] = gopd;
+    }
+  }
+  __syncthreads();
+  if (cur_p >= 0) {
+    for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) {
+      const R v = s_gp[q];
+      if (v != R(0)) atomicAdd(P.gpresc + (long long)cur_p * P.presc_stride + q, v);
+    }
+  }
+}
+
+template <typename R>
+int launch_bwd(const olrt_sys* sys, const R* presc, const int32_t* ops, long long n_rays, const R* const in[8],
+               const R* record, const R* const gout[8], const R* grecord, R* const gin[8], R* gpresc,
+               uint32_t* status, cudaStream_t stream) {
+  BwdParams<R> P;
+  for (int q = 0; q < 8; ++q) { P.in[q] = in[q]; P.gout[q] = gout ? gout[q] : nullptr; P.gin[q] = gin ? gin[q] : nullptr; }
+  P.record = record; P.grecord = grecord; P.gpresc = gpresc; P.presc = presc; P.ops = ops; P.n_rays = n_rays;
+  P.rays_per_presc = sys->rays_per_presc > 0 ? sys->rays_per_presc : n_rays;
+  P.n_surfaces = sys->n_surfaces; P.n_wavelengths = sys->n_wavelengths; P.n_presc = sys->n_presc;
+  P.presc_stride = sys->presc_stride; P.ops_len = sys->ops_len;
+  for (int q = 0; q < OLRT_MAX_WAVELENGTHS; ++q) P.wavelengths[q] = (R)sys->wavelengths[q];
+  P.four_pi = (R)(4.0 * 3.141592653589793);
+  int block = 256;
+  if (sys->n_presc > 1) {
+    block = 0;
+    for (int b = 256; b >= 32; b >>= 1) if (sys->rays_per_presc % b == 0) { block = b; break; }
+    if (block == 0) return OLRT_E_ARG;
+  }
+  const size_t pp = (size_t)((sys->presc_stride + 1) & ~1);
+  const size_t smem = 2 * pp * sizeof(R) +
+                      (size_t)((sys->n_surfaces * der_stride(sys->n_wavelengths) + 1) & ~1) * sizeof(R) +
+                      (size_t)((sys->ops_len + 1) & ~1) * sizeof(int32_t);
+  if (smem > 200 * 1024) return OLRT_E_LIMIT;
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(trace_bwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int per_sm = 0, dev = 0, sms = 148;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_bwd_kernel<R>, block, smem);
+  if (per_sm < 1) per_sm = 1;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const long long n_tiles = (n_rays + block - 1) / block;
+  long long grid = (long long)sms * per_sm;
+  if (grid > n_tiles) grid = n_tiles;
+  trace_bwd_kernel<R><<<(unsigned)grid, block, smem, stream>>>(P, status);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+
+}  // namespace OLRT_NS

@@ -15,4 +15,14 @@ int fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, long lo
             float* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, cudaStream_t stream) {
   return launch_fwd<float>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, stream);
 }
+int bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, long long n_rays,
+            const double* const in[8], const double* record, const double* const gout[8], const double* grecord,
+            double* const gin[8], double* gpresc, uint32_t* status, cudaStream_t stream) {
+  return launch_bwd<double>(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, stream);
+}
+int bwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, long long n_rays,
+            const float* const in[8], const float* record, const float* const gout[8], const float* grecord,
+            float* const gin[8], float* gpresc, uint32_t* status, cudaStream_t stream) {
+  return launch_bwd<float>(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, stream);
+}
 }  // namespace olrt_fast
