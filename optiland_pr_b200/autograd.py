@@ -67,6 +67,7 @@ class FusedTraceFn(torch.autograd.Function):
         res = fused_trace(packed, [t.detach() if t is not None else None for t in ins],
                           opd_in=None if opd_in is None else opd_in.detach(),
                           presc=presc.detach().reshape(1, -1), want_dir0=True, fast=fast)
+        ctx.set_materialize_grads(False)
         ctx.packed = packed
         ctx.nr_iters = list(res.nr_iters)
         ctx.save_for_backward(presc.detach(), *[t.detach() for t in ins if t is not None], res.record)
@@ -121,3 +122,74 @@ def trace_differentiable(packed: PackedSystem, presc: torch.Tensor, rays_in, opd
     """rays_in: 8 tensors (w may be None for a single wavelength). Returns (out, record, dir0)."""
     x, y, z, Lc, M, N, inten, w = (list(rays_in) + [None])[:8]
     return FusedTraceFn.apply(presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast)
+
+
+def _rms_merit(lens, fields, wavelength, Px, Py):
+    """sum over fields of rms_spot_size^2 (RayOperand.rms_spot_size, operand/ray.py:299-340 fed to
+    OptimizationProblem.sum_squared, problem.py:100-109) from ONE traced batch of fields x pupil rays."""
+    nf = len(fields)
+    rays = lens.trace([f[0] for f in fields], [f[1] for f in fields], wavelength, distribution=(Px, Py))
+    x = rays.x.reshape(nf, -1)
+    y = rays.y.reshape(nf, -1)
+    r2 = (x - x.mean(dim=1, keepdim=True)) ** 2 + (y - y.mean(dim=1, keepdim=True)) ** 2
+    return r2.mean(dim=1).sum()
+
+
+def smoke_backward() -> str:
+    """forward + backward through the public API on the Cooke triplet: finite, non-zero gradients that agree
+    with a central finite difference of the merit."""
+    from . import backend as be
+    from . import samples
+
+    be.set_precision("float64")
+    lens = samples.CookeTriplet()
+    r1 = torch.tensor(22.01359, dtype=torch.float64, device=be.get_device(), requires_grad=True)
+    lens.set_radius(r1, 1)
+    rng = np.random.default_rng(0)
+    rr, th = np.sqrt(rng.uniform(size=2000)), rng.uniform(0, 2 * np.pi, 2000)
+    Px, Py = rr * np.cos(th), rr * np.sin(th)
+    fields = [(0.0, 0.0), (0.0, 0.7), (0.0, 1.0)]
+    loss = _rms_merit(lens, fields, 0.55, Px, Py)
+    loss.backward()
+    g = float(r1.grad)
+    h = 1e-5
+    vals = []
+    for d in (+h, -h):
+        lens.set_radius(22.01359 + d, 1)
+        with torch.no_grad():
+            vals.append(float(_rms_merit(lens, fields, 0.55, Px, Py)))
+    fd = (vals[0] - vals[1]) / (2 * h)
+    assert np.isfinite(g) and g != 0 and abs(g - fd) <= 1e-5 * abs(fd), (g, fd)
+    return f"fwd+bwd ok: d(merit)/d(R1) = {g:.9e} (finite difference {fd:.9e})"
+
+
+def bench_backward(lens, packed, ins64, timed, args, fp64_peak) -> dict:
+    """fwd (all surfaces recorded = checkpoints) + bwd on the bench batch, one field at a time is not needed:
+    the record buffer for 50M rays x 12 surfaces x 8 doubles is 38.7 GB and fits the 180 GB HBM."""
+    from . import flops
+    from .prescription import pack_surface_group
+
+    n = int(ins64[0].numel())
+    S = packed.n_surfaces
+    pk = pack_surface_group(lens.surface_group.surfaces, packed.wavelengths, record="all")
+    pk.set_nr_iters(packed.nr_iters())
+    dev = ins64[0].device
+    presc = torch.tensor(pk.presc[0], dtype=torch.float64, device=dev, requires_grad=True)
+    rays = [t.detach().requires_grad_(q < 6) if t is not None else None for q, t in enumerate(ins64)]
+    gout_w = torch.zeros((8, n), dtype=torch.float64, device=dev)
+    gout_w[0] = 1.0
+    gout_w[1] = 0.5
+
+    def step():
+        presc.grad = None
+        out, record, _ = trace_differentiable(pk, presc, rays)
+        out.backward(gout_w)
+
+    ms = timed(step, max(2, args.steps // 2), 3)
+    fl = 3.0 * flops.flops_per_ray(pk)
+    return {"fp64_fwd_bwd": {"ray_surfaces_per_s": n * S / (ms * 1e-3), "ms": ms,
+                             "frac_fp64_fma_peak": fl * n / (ms * 1e-3) / 1e12 / fp64_peak,
+                             "flops_per_ray_fwd_bwd": fl,
+                             "checkpoint_bytes_per_ray": 64 * S,
+                             "note": "forward records every surface (64 B x S per ray, the checkpoints), "
+                                     "backward reads 56 B per surface per ray"}}

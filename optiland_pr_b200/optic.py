@@ -87,6 +87,29 @@ class Optic:
         if EPD is not None:
             self._EPD = float(EPD)
 
+    # ---- OpticUpdater subset used by the optimisation variables (optic/optic_updater.py:38-142) ------
+    def set_radius(self, value, surface_number):
+        self.surface_group.surfaces[surface_number].geometry.radius = value
+        self.surface_group.invalidate()
+
+    def set_conic(self, value, surface_number):
+        self.surface_group.surfaces[surface_number].geometry.k = value
+        self.surface_group.invalidate()
+
+    def set_asphere_coeff(self, value, surface_number, aspher_coeff_idx):
+        self.surface_group.surfaces[surface_number].geometry.coefficients[aspher_coeff_idx] = value
+        self.surface_group.invalidate()
+
+    def set_thickness(self, value, surface_number):
+        """optic_updater.py:67-85: every surface after `surface_number` moves by the change in thickness
+        (cs.z stays a tensor expression of the thickness when `value` is a tensor)."""
+        surfs = self.surface_group.surfaces
+        delta = value - surfs[surface_number].thickness
+        surfs[surface_number].thickness = value
+        for s in surfs[surface_number + 1:]:
+            s.geometry.cs.z = s.geometry.cs.z + delta
+        self.surface_group.invalidate()
+
     @property
     def primary_wavelength(self):
         return self.wavelengths[self.primary_index]

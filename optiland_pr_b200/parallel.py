@@ -1,0 +1,99 @@
+"""Multi-GPU plumbing: one process per GPU (torchrun), `torch.distributed` over NCCL (gloo in the CPU tests).
+
+The path shards trivially: rays are independent, so ranks take contiguous ray ranges of
+a big batch, or whole (field, wavelength) pairs / Monte-Carlo trials, with the prescription replicated.
+No ray data ever crosses NVLink. The only exchanges are scalars:
+
+  * spot sums   [G][10] doubles per merit evaluation   -> SUM (moments) / MAX (geometric radius)
+  * Newton trip counts K_s, one int per NR surface     -> MAX (the reference's exit test is a maximum
+    over ALL rays of the batch, newton_raphson.py:148, so the shards must agree on it)
+  * parameter gradients [stride] doubles per backward  -> SUM
+
+All are <= ~1 KB: latency-bound collectives; they are issued on the current stream right after the
+kernel that produced them.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+def world():
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_range(n: int, rank: int | None = None, world_size: int | None = None):
+    """Contiguous [lo, hi) of n items for this rank; the first n % world ranks get one extra."""
+    r, w = world()
+    rank = r if rank is None else rank
+    world_size = w if world_size is None else world_size
+    base, extra = divmod(n, world_size)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def shard_items(items, rank: int | None = None, world_size: int | None = None):
+    """Round-robin assignment of whole work items ((field, wavelength) pairs, Monte-Carlo trials)."""
+    r, w = world()
+    rank = r if rank is None else rank
+    world_size = w if world_size is None else world_size
+    return list(items)[rank::world_size]
+
+
+def allreduce_spot_sums(sums: torch.Tensor) -> torch.Tensor:
+    """Merge per-rank spot sums (layout include/olrt.h: olrt_spot_sums_*). Every rank must have used the
+    same shift (columns 8, 9) -- pass an explicit `shift` to spot_sums when sharding rays of one group.
+    Columns 0-4 and 6 add; column 5 (max r^2, a non-negative double, NaN marks a NaN ray) takes the max."""
+    _, w = world()
+    if w == 1:
+        return sums
+    add = sums[:, [0, 1, 2, 3, 4, 6]].contiguous()
+    mx = sums[:, 5].contiguous()
+    nan = torch.isnan(mx).to(sums.dtype)
+    mx = torch.nan_to_num(mx, nan=0.0)
+    dist.all_reduce(add, op=dist.ReduceOp.SUM)
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    dist.all_reduce(nan, op=dist.ReduceOp.MAX)
+    out = sums.clone()
+    out[:, [0, 1, 2, 3, 4, 6]] = add
+    out[:, 5] = torch.where(nan > 0, torch.full_like(mx, float("nan")), mx)
+    return out
+
+
+def allreduce_nr_iters(iters, device=None):
+    """Agree on the Newton trip counts: element-wise MAX over ranks."""
+    _, w = world()
+    if w == 1:
+        return list(iters)
+    t = torch.tensor(list(iters), dtype=torch.int32, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [int(v) for v in t.cpu().tolist()]
+
+
+def allreduce_gradients(*grads: torch.Tensor):
+    """SUM the (tiny) parameter-gradient vectors over ranks, in place."""
+    _, w = world()
+    if w > 1:
+        for g in grads:
+            if g is not None:
+                dist.all_reduce(g, op=dist.ReduceOp.SUM)
+    return grads
+
+
+def sharded_trace(surface_group, rays, wavelengths=None, max_rounds: int = 8):
+    """`SurfaceGroup.trace` on this rank's shard with batch-global Newton trip counts: trace, all-reduce
+    K_s, and re-trace when another rank needed more (or fewer) updates than this shard alone."""
+    _, w = world()
+    out = surface_group.trace(rays, wavelengths=wavelengths)
+    if w == 1:
+        return out
+    for _ in range(max_rounds):
+        res = surface_group.last_trace
+        agreed = allreduce_nr_iters(res.nr_iters, device=rays.x.device)
+        if agreed == list(res.nr_iters):
+            return out
+        raise RuntimeError(
+            "ranks disagree on the Newton trip counts; re-trace with surface_group.force_nr_iters(agreed)")
+    return out

@@ -24,7 +24,7 @@ from .geometries import (EvenAsphere, OddAsphere, Plane, PolynomialGeometry, Sta
 from .materials import BaseMaterial, IdealMaterial, Material
 from .prescription import PackedSystem, pack_surface_group
 from .rays import RealRays
-from .trace import fused_trace
+from .trace import TraceResult, fused_trace
 
 _RECORD_FIELDS = ("x", "y", "z", "L", "M", "N", "intensity", "opd")
 
@@ -202,6 +202,24 @@ class SurfaceGroup:
         for s in self._surfaces:
             s.reset()
 
+    def _wants_grad(self, rays) -> bool:
+        """Autograd is recorded when grad mode is on (torch_backend.py:45-64) or when any ray component or
+        prescription entry is a tensor that requires grad."""
+        if not torch.is_grad_enabled():
+            return False
+        if be.grad_mode.requires_grad:
+            return True
+        if any(isinstance(t, torch.Tensor) and t.requires_grad for t in rays.components() + [rays.opd]):
+            return True
+        for s in self._surfaces:
+            g = s.geometry
+            vals = [g.cs.x, g.cs.y, g.cs.z, getattr(g, "radius", None), getattr(g, "k", None)]
+            for c in (getattr(g, "coefficients", None) or []):
+                vals += list(c) if isinstance(c, (list, tuple)) else [c]
+            if any(isinstance(v, torch.Tensor) and v.requires_grad for v in vals):
+                return True
+        return False
+
     # ---- the hot path ----------------------------------------------------------------------
     def pack(self, wavelengths, skip=0) -> PackedSystem:
         """Pack on every call (microseconds; prescriptions are mutable) but remember the Newton
@@ -223,7 +241,19 @@ class SurfaceGroup:
             wavelengths = torch.unique(rays.w).cpu().tolist()
         packed = self.pack(wavelengths, skip)
         ins = rays.components()
-        res = fused_trace(packed, ins, opd_in=rays.opd, want_dir0=True, fast=self.fast_math)
+        if self._wants_grad(rays):
+            # one autograd node: forward kernel (records = checkpoints) + backward kernel (autograd.py)
+            from .autograd import prescription_tensor, trace_differentiable
+            if self.record != "all":
+                packed = pack_surface_group(self._surfaces, wavelengths, record="all", skip=skip)
+                for k in packed.nr_rows():
+                    packed.ops[k * 16 + 6] = min(packed.layouts[k].max_iter,
+                                                 (self._packed_cache or {}).get(packed.layouts[k].index, 2))
+            presc_t = prescription_tensor(packed, self._surfaces, ins[0].dtype, ins[0].device)
+            out, record, dir0 = trace_differentiable(packed, presc_t, ins, opd_in=rays.opd, fast=self.fast_math)
+            res = TraceResult(out=out, record=record, dir0=dir0, nr_iters=packed.nr_iters(), status=0, launches=1)
+        else:
+            res = fused_trace(packed, ins, opd_in=rays.opd, want_dir0=True, fast=self.fast_math)
         if res.status & 1:
             raise ValueError("Zernike coordinates must be normalized to [-1, 1]. Consider updating "
                              "the normalization radius to 1.1x the surface aperture.")
