@@ -105,3 +105,86 @@ class AsphericSinglet(Optic):
         self.add_field(y=0)
         self.add_wavelength(0.587, is_primary=True)
         self.set_paraxial(EPL=0.0, EPD=20.0)
+
+
+# ---- builders shared with oracle/make_golden.py: the SAME calls build the lens on the reference's Optic and
+# ---- on this package's Optic (`lens` is either; `ap` is the module holding the aperture classes)
+TMA_COEFFS = (
+    [[2.05790534e-05, -2.04095791e-05, 4.55045366e-05, 1.47183545e-05],
+     [3.64010850e-08, -9.18266382e-06, 3.12457789e-07, -3.43010757e-08],
+     [-1.18212287e-04, 2.97963986e-06, -1.31354947e-06, 7.34797747e-07],
+     [-1.09979245e-06, 8.55358588e-07, -3.94583506e-07, -5.01115270e-08]],
+    [[-2.05802662e-05, 2.05376130e-05, -2.91883756e-05, 4.01274602e-05],
+     [-2.94473576e-08, -1.63268440e-06, -5.35655902e-06, -1.50920309e-05],
+     [4.87006021e-05, -1.70308923e-05, 2.12362562e-05, 1.51092539e-05],
+     [-1.04657810e-05, -2.25376153e-05, -8.02314506e-06, 3.02373985e-06]],
+    [[2.05787912e-05, -2.05604065e-05, 2.54616632e-05, -3.62841214e-05],
+     [6.24577550e-10, 1.09936457e-07, -2.69199040e-06, -1.05068667e-05],
+     [-3.28005504e-05, 1.88336844e-05, -3.34058539e-05, 4.93261709e-06],
+     [6.09659324e-07, -1.58589636e-06, -1.16163570e-05, -2.26243673e-05]],
+)
+
+
+def build_three_mirror(lens, to_array=lambda a: a):
+    """Off-axis three-mirror anastigmat of docs/gallery/reflective/three_mirror_anastigmat.ipynb: polynomial
+    4x4 freeform mirrors, rx tilts, dy decenters (BASELINE config C3)."""
+    lens.set_aperture(aperture_type="EPD", value=10)
+    lens.set_field_type(field_type="angle")
+    for fy in (0, 1.5, -1.5):
+        lens.add_field(y=fy)
+    lens.add_wavelength(value=0.486)
+    lens.add_wavelength(value=0.587, is_primary=True)
+    lens.add_wavelength(value=0.656)
+    lens.add_surface(index=0, radius=INF, thickness=INF)
+    lens.add_surface(index=1, radius=-99.9773, thickness=-20.0003, conic=2.35645e-06, material="mirror",
+                     rx=-0.261801, is_stop=True, surface_type="polynomial", coefficients=to_array(TMA_COEFFS[0]))
+    lens.add_surface(index=2, radius=-100.019, thickness=20.0003, conic=-2.21455e-07, material="mirror",
+                     rx=-0.174532, dy=-11.5, surface_type="polynomial", coefficients=to_array(TMA_COEFFS[1]))
+    lens.add_surface(index=3, radius=-99.9774, thickness=-20.0003, conic=5.32063e-08, material="mirror",
+                     rx=-0.0174547, dy=-15, surface_type="polynomial", coefficients=to_array(TMA_COEFFS[2]))
+    lens.add_surface(index=4, dy=-19.3)
+    return lens
+
+
+ZERNIKE_PLATE_COEFFS = [0.0, 0.0, 0.0, 2.0e-2, -1.5e-2, 1.0e-2, 4.0e-3, -3.0e-3, 2.5e-3, 0.0, 1.0e-3, -8.0e-4]
+
+
+def build_freeform_plate(lens, ap, zernike_type="fringe"):
+    """Refractive test system exercising what the sample lenses do not: a Zernike freeform (fringe / noll /
+    standard), an odd asphere, tilts about all three axes with decenters, elliptical / rectangular / boolean
+    apertures, an absorbing glass, and a steep glass-to-air exit that totally reflects part of the pupil."""
+    lens.set_aperture(aperture_type="EPD", value=12)
+    lens.set_field_type(field_type="angle")
+    for fy in (0, 6):
+        lens.add_field(y=fy)
+    lens.add_wavelength(value=0.55, is_primary=True)
+    lens.add_surface(index=0, radius=INF, thickness=INF)
+    lens.add_surface(index=1, radius=60.0, thickness=6.0, material="N-SK16", is_stop=True, surface_type="zernike",
+                     conic=-0.3, coefficients=list(ZERNIKE_PLATE_COEFFS), zernike_type=zernike_type, norm_radius=9.5,
+                     aperture=ap.RadialAperture(r_max=7.0, r_min=0.5))
+    lens.add_surface(index=2, radius=-45.0, thickness=4.0, surface_type="odd_asphere", conic=0.1,
+                     coefficients=[0.0, 1.0e-4, -2.0e-5, 3.0e-6], rx=0.03, ry=-0.02, dx=0.4,
+                     aperture=ap.DifferenceAperture(ap.EllipticalAperture(6.5, 5.5, 0.2, -0.1),
+                                                    ap.RectangularAperture(-1.0, 1.0, -0.6, 0.6)))
+    lens.add_surface(index=3, radius=35.0, thickness=5.0, material=("F5", "schott"), conic=0.0, rz=0.5, ry=0.04,
+                     dy=-0.3, aperture=ap.UnionAperture(ap.OffsetRadialAperture(5.0, 0.0, 0.5, 0.5),
+                                                        ap.IntersectionAperture(ap.RadialAperture(6.0),
+                                                                                ap.RectangularAperture(-6, 6, -2, 2))))
+    lens.add_surface(index=4, radius=7.5, thickness=12.0, conic=-0.2)        # steep exit: TIR at the rim
+    lens.add_surface(index=5)
+    return lens
+
+
+class ThreeMirrorAnastigmat(Optic):
+    def __init__(self):
+        super().__init__("TMA")
+        build_three_mirror(self)
+        self.set_paraxial(EPL=0.0, EPD=10.0)
+
+
+class FreeformPlate(Optic):
+    def __init__(self, zernike_type="fringe"):
+        super().__init__("FreeformPlate")
+        from . import apertures
+        build_freeform_plate(self, apertures, zernike_type)
+        self.set_paraxial(EPL=0.0, EPD=12.0)

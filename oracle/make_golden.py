@@ -93,6 +93,7 @@ def run_case(name, lens, rays, wavelengths, extra=None):
     rec = np.stack([np.stack([np.asarray(getattr(s, k), dtype=np.float64) for k in FIELDS8])
                     for s in sg.surfaces[1:]])
     packed = pack_surface_group(sg.surfaces, wavelengths)
+    nr_iters = []  # Newton updates the reference took: sag evaluations - 1 is not observable; use the oracle
     paraxial = np.array([float(lens.paraxial.EPL()), float(lens.paraxial.EPD())])
     out = dict(rays_in=rays_in, records=rec, wavelengths=np.asarray(wavelengths, dtype=np.float64),
                ops=packed.ops, presc=packed.presc, paraxial=paraxial)
@@ -126,6 +127,17 @@ def main():
     lens = AsphericSinglet()
     rays = gen_rays(lens, [(0.0, 0.0)], [0.587], "hexapolar", 12)
     run_case("aspheric_singlet", lens, rays, [0.587])
+    # C3: off-axis three-mirror anastigmat (polynomial freeforms, rx tilts, dy decenters, mirrors)
+    lens = my_samples.build_three_mirror(ref_optic.Optic(name="TMA"), to_array=np.array)
+    wl = [0.486, 0.587, 0.656]
+    rays = gen_rays(lens, lens.fields.get_field_coords(), wl, "random", 120, seed=2)
+    run_case("three_mirror", lens, rays, wl)
+    # Zernike / odd-asphere / tilted / apertured / absorbing plate with TIR, one fixture per index scheme
+    import optiland.physical_apertures as ref_ap
+    for zt in ("fringe", "noll", "standard"):
+        lens = my_samples.build_freeform_plate(ref_optic.Optic(name="plate"), ref_ap, zt)
+        rays = gen_rays(lens, lens.fields.get_field_coords(), [0.55], "random", 700, seed=3)
+        run_case("freeform_plate_" + zt, lens, rays, [0.55])
 
 
 if __name__ == "__main__":

@@ -14,7 +14,13 @@ MIRRORS = {
     "double_gauss": samples.DoubleGauss,
     "even_asphere_double_gauss": samples.EvenAsphereDoubleGauss,
     "aspheric_singlet": samples.AsphericSinglet,
+    "three_mirror": samples.ThreeMirrorAnastigmat,
+    "freeform_plate_fringe": lambda: samples.FreeformPlate("fringe"),
+    "freeform_plate_noll": lambda: samples.FreeformPlate("noll"),
+    "freeform_plate_standard": lambda: samples.FreeformPlate("standard"),
 }
+# lenses inside the backward kernel's differentiable set (gradient fixtures exist for these)
+GRAD_MIRRORS = ("cooke_triplet", "double_gauss", "even_asphere_double_gauss", "aspheric_singlet")
 # fixtures whose surfaces are all closed-form (+,-,*,/,sqrt only): oracle must match the reference bit for bit
 CLOSED_FORM = ("cooke_triplet", "double_gauss")
 

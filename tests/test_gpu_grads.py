@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import MIRRORS, load_golden, mirror_packed
+from helpers import GRAD_MIRRORS, load_golden, mirror_packed
 from optiland_pr_b200.autograd import trace_differentiable
 
 pytestmark = pytest.mark.gpu
@@ -28,7 +28,7 @@ def _rel(a, b, floor):
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor)))
 
 
-@pytest.mark.parametrize("name", sorted(MIRRORS))
+@pytest.mark.parametrize("name", sorted(GRAD_MIRRORS))
 def test_fp64_gradients_match_reference_autograd(name):
     g, loss, gin, gpresc = _run(name)
     assert abs(loss - g["loss"]) <= 1e-10 * abs(g["loss"])
