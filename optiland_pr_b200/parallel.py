@@ -82,18 +82,21 @@ def allreduce_gradients(*grads: torch.Tensor):
     return grads
 
 
-def sharded_trace(surface_group, rays, wavelengths=None, max_rounds: int = 8):
-    """`SurfaceGroup.trace` on this rank's shard with batch-global Newton trip counts: trace, all-reduce
-    K_s, and re-trace when another rank needed more (or fewer) updates than this shard alone."""
+def sharded_trace(surface_group, rays, wavelengths=None):
+    """`SurfaceGroup.trace` on this rank's shard with BATCH-global Newton trip counts: trace the shard
+    (its own exit rule), all-reduce K_s with MAX -- the reference's test is a maximum over all rays of the
+    batch (newton_raphson.py:148) -- and re-trace with the agreed counts where this shard alone needed fewer."""
     _, w = world()
     out = surface_group.trace(rays, wavelengths=wavelengths)
     if w == 1:
         return out
-    for _ in range(max_rounds):
-        res = surface_group.last_trace
-        agreed = allreduce_nr_iters(res.nr_iters, device=rays.x.device)
-        if agreed == list(res.nr_iters):
-            return out
-        raise RuntimeError(
-            "ranks disagree on the Newton trip counts; re-trace with surface_group.force_nr_iters(agreed)")
+    local = list(surface_group.last_trace.nr_iters)
+    agreed = allreduce_nr_iters(local, device=rays.x.device)
+    if agreed != local:
+        surfaces = [s for s in surface_group.surfaces if type(s).__name__ != "ObjectSurface"]
+        surface_group.forced_nr_iters = {surface_group.surfaces.index(s): k for s, k in zip(surfaces, agreed)}
+        try:
+            out = surface_group.trace(rays, wavelengths=wavelengths)
+        finally:
+            surface_group.forced_nr_iters = None
     return out

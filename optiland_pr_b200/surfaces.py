@@ -92,6 +92,7 @@ class SurfaceGroup:
         self.record = "all"      # "all" | "last" | list of surface indices
         self.fast_math = False   # True: FMA-contracted fp64 kernel (not bit-faithful)
         self._packed_cache = None
+        self.forced_nr_iters = None  # {surface index: K}: skip the exit-rule check (sharded batches, parallel.py)
         self.last_trace = None
 
     # ---- structure -----------------------------------------------------------------------
@@ -225,7 +226,7 @@ class SurfaceGroup:
         """Pack on every call (microseconds; prescriptions are mutable) but remember the Newton
         trip counts K_s that the last trace of this group settled on as the next guess."""
         packed = pack_surface_group(self._surfaces, wavelengths, record=self.record, skip=skip)
-        guess = self._packed_cache or {}
+        guess = self.forced_nr_iters or self._packed_cache or {}
         for k in packed.nr_rows():
             lay = packed.layouts[k]
             packed.ops[k * 16 + 6] = min(lay.max_iter, guess.get(lay.index, 2))
@@ -253,7 +254,8 @@ class SurfaceGroup:
             out, record, dir0 = trace_differentiable(packed, presc_t, ins, opd_in=rays.opd, fast=self.fast_math)
             res = TraceResult(out=out, record=record, dir0=dir0, nr_iters=packed.nr_iters(), status=0, launches=1)
         else:
-            res = fused_trace(packed, ins, opd_in=rays.opd, want_dir0=True, fast=self.fast_math)
+            res = fused_trace(packed, ins, opd_in=rays.opd, want_dir0=True, fast=self.fast_math,
+                              verify_nr=self.forced_nr_iters is None)
         if res.status & 1:
             raise ValueError("Zernike coordinates must be normalized to [-1, 1]. Consider updating "
                              "the normalization radius to 1.1x the surface aperture.")
