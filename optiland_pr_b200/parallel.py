@@ -87,6 +87,8 @@ def sharded_trace(surface_group, rays, wavelengths=None):
     (its own exit rule), all-reduce K_s with MAX -- the reference's test is a maximum over all rays of the
     batch (newton_raphson.py:148) -- and re-trace with the agreed counts where this shard alone needed fewer."""
     _, w = world()
+    names = ("x", "y", "z", "L", "M", "N", "i", "opd")
+    start = [getattr(rays, q) for q in names]  # trace() replaces these attributes, it does not write in place
     out = surface_group.trace(rays, wavelengths=wavelengths)
     if w == 1:
         return out
@@ -95,6 +97,8 @@ def sharded_trace(surface_group, rays, wavelengths=None):
     if agreed != local:
         surfaces = [s for s in surface_group.surfaces if type(s).__name__ != "ObjectSurface"]
         surface_group.forced_nr_iters = {surface_group.surfaces.index(s): k for s, k in zip(surfaces, agreed)}
+        for q, v in zip(names, start):
+            setattr(rays, q, v)
         try:
             out = surface_group.trace(rays, wavelengths=wavelengths)
         finally:
