@@ -197,6 +197,22 @@ int olrt_spot_sums_f32(const float* x, const float* y, const float* intensity, i
 int olrt_fma_peak_f64(double* sink, int64_t iters, int blocks, int threads, void* stream);
 int olrt_fma_peak_f32(float* sink, int64_t iters, int blocks, int threads, void* stream);
 
+/* Ray launch: RayGenerator.generate_rays (optiland/rays/ray_generator.py:28-106) with
+ * AngleField.get_ray_origins (optiland/fields/field_types.py:139-169) for an object at infinity, angle
+ * fields, no vignetting factors. Rays are field-major (ray f * n_pupil + p), as RealRayTracer.trace builds
+ * them (raytrace/real_ray_tracer.py:67-77).
+ *  Px, Py    [n_pupil] doubles (device): normalised pupil coordinates
+ *  field_xy  [n_fields][2] doubles (device): -tan(radians(max_field * H)) * (offset + EPL) per field, x then y
+ *  EPD, EPL  entrance pupil diameter / location (paraxial.py:207-280); z_start = positions[1] - offset
+ *  out       [8] device ptrs x y z L M N intensity wavelength (entry 7 may be NULL); fp64 arithmetic, stored
+ *            in the output precision                                                                    */
+int olrt_generate_rays_f64(const double* Px, const double* Py, int64_t n_pupil, const double* field_xy,
+                           int32_t n_fields, double EPD, double EPL, double z_start, double wavelength,
+                           double* const out[8], void* stream);
+int olrt_generate_rays_f32(const double* Px, const double* Py, int64_t n_pupil, const double* field_xy,
+                           int32_t n_fields, double EPD, double EPL, double z_start, double wavelength,
+                           float* const out[8], void* stream);
+
 /* Self-test of the kernels' own IEEE division / square-root sequences (csrc/math64.cuh):
  * quot[i] = a[i] / b[i], root[i] = sqrt(a[i]) as the trace kernels compute them; the caller compares
  * them bit for bit with an IEEE implementation (tests/test_gpu_math.py). */

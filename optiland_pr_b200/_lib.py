@@ -65,6 +65,7 @@ EXPORTS = [
     "olrt_spot_sums_f64", "olrt_spot_sums_f32",
     "olrt_fma_peak_f64", "olrt_fma_peak_f32",
     "olrt_selftest_math_f64",
+    "olrt_generate_rays_f64", "olrt_generate_rays_f32",
 ]
 
 _lib = None
@@ -103,6 +104,10 @@ def load():
         f.argtypes = [v, v, v, C.c_int64, C.c_int64, C.c_int32, v, C.c_int, v, v]
         f = getattr(lib, f"olrt_fma_peak_{suf}")
         f.restype, f.argtypes = C.c_int, [v, C.c_int64, C.c_int, C.c_int, v]
+    for suf in ("f64", "f32"):
+        f = getattr(lib, f"olrt_generate_rays_{suf}")
+        f.restype = C.c_int
+        f.argtypes = [v, v, C.c_int64, v, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double, PtrArray8, v]
     lib.olrt_selftest_math_f64.restype = C.c_int
     lib.olrt_selftest_math_f64.argtypes = [v, v, v, v, C.c_int64, v]
     if lib.olrt_version() != OLRT_ABI_VERSION:

@@ -21,4 +21,58 @@ int selftest_math(const double* a, const double* b, double* q, double* r, long l
   selftest_math_kernel<<<sm_count() * 8, 256, 0, stream>>>(a, b, q, r, n);
   return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
 }
+
+// Ray launch for an object at infinity, angle fields, no vignetting factors:
+//   RayGenerator.generate_rays        optiland/rays/ray_generator.py:28-106
+//   AngleField.get_ray_origins        optiland/fields/field_types.py:139-169
+// field_xy[f] = (-tan(radians(max_field Hx))(offset+EPL), same for y) is evaluated on the host (one value per
+// field); everything per ray is here, in the reference's operation order (this TU is built -fmad=false).
+// Rays are field-major: ray f * n_pupil + p. Arithmetic in fp64, stored as R.
+template <typename R>
+__global__ void __launch_bounds__(256) generate_rays_kernel(const double* __restrict__ Px, const double* __restrict__ Py,
+                                                            long long n_pupil, const double* __restrict__ field_xy,
+                                                            int n_fields, double EPD, double EPL, double z_start,
+                                                            double wavelength, R* ox, R* oy, R* oz, R* oL, R* oM,
+                                                            R* oN, R* oi, R* ow) {
+  const long long total = n_pupil * n_fields;
+  for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < total;
+       r += (long long)gridDim.x * blockDim.x) {
+    const long long f = r / n_pupil, p = r - f * n_pupil;
+    const double px = Px[p], py = Py[p];
+    const double xf = field_xy[2 * f], yf = field_xy[2 * f + 1];
+    const double x1 = px * EPD / 2.0, y1 = py * EPD / 2.0;   // Px * EPD * vx / 2, vx = 1
+    const double x0 = x1 + xf, y0 = y1 + yf;                 // Px * EPD / 2 * vx + x
+    const double dx = x1 - x0, dy = y1 - y0, dz = EPL - z_start;
+    double mag = sqrt(dx * dx + dy * dy + dz * dz);
+    const bool is_zero = mag < 1e-9;
+    if (is_zero) mag = 1.0;
+    ox[r] = (R)x0; oy[r] = (R)y0; oz[r] = (R)z_start;
+    oL[r] = (R)(is_zero ? 0.0 : dx / mag);
+    oM[r] = (R)(is_zero ? 0.0 : dy / mag);
+    oN[r] = (R)(is_zero ? 1.0 : dz / mag);
+    oi[r] = (R)1.0;
+    if (ow != nullptr) ow[r] = (R)wavelength;
+  }
+}
+template <typename R>
+static int launch_generate(const double* Px, const double* Py, long long n_pupil, const double* field_xy, int n_fields,
+                           double EPD, double EPL, double z_start, double wavelength, R* const out[8],
+                           cudaStream_t stream) {
+  const long long total = n_pupil * n_fields;
+  long long grid = (long long)sm_count() * 8;
+  const long long need = (total + 255) / 256;
+  if (grid > need) grid = need;
+  generate_rays_kernel<R><<<(unsigned)grid, 256, 0, stream>>>(Px, Py, n_pupil, field_xy, n_fields, EPD, EPL, z_start,
+                                                              wavelength, out[0], out[1], out[2], out[3], out[4],
+                                                              out[5], out[6], out[7]);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+int generate_f64(const double* Px, const double* Py, long long n_pupil, const double* field_xy, int n_fields,
+                 double EPD, double EPL, double z_start, double wavelength, double* const out[8], cudaStream_t st) {
+  return launch_generate<double>(Px, Py, n_pupil, field_xy, n_fields, EPD, EPL, z_start, wavelength, out, st);
+}
+int generate_f32(const double* Px, const double* Py, long long n_pupil, const double* field_xy, int n_fields,
+                 double EPD, double EPL, double z_start, double wavelength, float* const out[8], cudaStream_t st) {
+  return launch_generate<float>(Px, Py, n_pupil, field_xy, n_fields, EPD, EPL, z_start, wavelength, out, st);
+}
 }  // namespace olrt_strict

@@ -167,19 +167,47 @@ class Optic:
         else:
             Px, Py = distribution
         dev = be.get_device()
-        Hx = torch.as_tensor(np.atleast_1d(Hx).astype(np.float64), device=dev)
-        Hy = torch.as_tensor(np.atleast_1d(Hy).astype(np.float64), device=dev)
-        nf, npup = int(Hx.numel()), len(Px)
+        Hx = np.atleast_1d(np.asarray(Hx, dtype=np.float64))
+        Hy = np.atleast_1d(np.asarray(Hy, dtype=np.float64))
         if isinstance(Px, torch.Tensor):
             Px = Px.to(device=dev, dtype=torch.float64, non_blocking=True)
             Py = Py.to(device=dev, dtype=torch.float64, non_blocking=True)
         else:
             Px = torch.as_tensor(np.asarray(Px, dtype=np.float64), device=dev)
             Py = torch.as_tensor(np.asarray(Py, dtype=np.float64), device=dev)
-        rays = self.generate_rays(Hx.repeat_interleave(npup), Hy.repeat_interleave(npup),
-                                  Px.repeat(nf), Py.repeat(nf), wavelength)
+        rays = self.launch_rays(Hx, Hy, Px, Py, wavelength)
         self.surface_group.trace(rays, wavelengths=[float(wavelength)])
         return rays
+
+    def launch_rays(self, Hx, Hy, Px, Py, wavelength) -> RealRays:
+        """fields x pupil rays (field-major) from the ray-launch kernel `olrt_generate_rays_*`
+        (ray_generator.py:28-106 + field_types.py:139-169, object at infinity). Hx, Hy: [F] NumPy arrays
+        (one entry per field); Px, Py: [P] float64 device tensors."""
+        import ctypes as C
+
+        from . import _lib as L
+        if self._EPL is None or self._EPD is None:
+            raise ValueError("call set_paraxial(EPL, EPD) first")
+        lib = L.load()
+        dt, dev = be.get_precision(), Px.device
+        EPL, EPD, mf = self._EPL, self._EPD, self.max_field
+        z_pos = [float(s.geometry.cs.z) for s in self.surface_group.surfaces[1:-1]]
+        offset = EPD - min(z_pos)                              # field_types.py:223-239
+        hx, hy = np.asarray(Hx, dtype=np.float64).reshape(-1), np.asarray(Hy, dtype=np.float64).reshape(-1)
+        fxy = np.stack([-np.tan(np.radians(mf * hx)) * (offset + EPL),
+                        -np.tan(np.radians(mf * hy)) * (offset + EPL)], axis=1)
+        fxy_d = torch.from_numpy(np.ascontiguousarray(fxy)).to(dev, non_blocking=True)
+        z_start = float(self.surface_group.surfaces[1].geometry.cs.z) - offset
+        nf, npup = int(hx.size), int(Px.numel())
+        out = torch.empty((8, nf * npup), dtype=dt, device=dev)
+        fn = lib.olrt_generate_rays_f64 if dt == torch.float64 else lib.olrt_generate_rays_f32
+        Px, Py = Px.contiguous(), Py.contiguous()
+        with torch.cuda.device(dev):
+            rc = fn(Px.data_ptr(), Py.data_ptr(), npup, fxy_d.data_ptr(), nf, float(EPD), float(EPL), z_start,
+                    float(wavelength), L.PtrArray8(*[out[q].data_ptr() for q in range(8)]),
+                    torch.cuda.current_stream(dev).cuda_stream)
+        L.check(rc, "olrt_generate_rays")
+        return RealRays(*[out[q] for q in range(8)])
 
     def trace_generic(self, Hx, Hy, Px, Py, wavelength):
         arrs = [np.atleast_1d(np.asarray(a, dtype=np.float64)) for a in (Hx, Hy, Px, Py)]
