@@ -169,6 +169,11 @@ class Optic:
         dev = be.get_device()
         Hx = np.atleast_1d(np.asarray(Hx, dtype=np.float64))
         Hy = np.atleast_1d(np.asarray(Hy, dtype=np.float64))
+        sg = self.surface_group
+        if (isinstance(Px, torch.Tensor) and not Px.is_cuda and Px.dtype == torch.float64
+                and Px.numel() >= self.pipeline_min_rays and sg.record in ("none", "last", None)
+                and not sg._wants_grad_params()):
+            return self._trace_pipelined(Hx, Hy, Px, Py, wavelength)
         if isinstance(Px, torch.Tensor):
             Px = Px.to(device=dev, dtype=torch.float64, non_blocking=True)
             Py = Py.to(device=dev, dtype=torch.float64, non_blocking=True)
@@ -179,7 +184,86 @@ class Optic:
         self.surface_group.trace(rays, wavelengths=[float(wavelength)])
         return rays
 
-    def launch_rays(self, Hx, Hy, Px, Py, wavelength) -> RealRays:
+    pipeline_min_rays = 1 << 21   # host pupil grids at least this long are streamed in chunks
+    pipeline_chunks = 4
+
+    def _trace_pipelined(self, Hx, Hy, Px_h, Py_h, wavelength):
+        """Same result as launch_rays + SurfaceGroup.trace for a pupil grid that lives in (pinned) HOST
+        memory: the grid is copied in chunks on a side stream while the chunks already on the device
+        are launched and traced, so the host->device copy overlaps the kernels instead of preceding them.
+        Each (chunk, field) slice is a contiguous range of the field-major ray arrays. The Newton trip
+        counts stay batch-global: every slice is checked against the reference's exit rule and, if slices
+        disagree, the whole batch is traced again with the largest counts (newton_raphson.py:148)."""
+        from .trace import fused_trace
+        sg = self.surface_group
+        dev = torch.device(be.get_device())
+        dt = be.get_precision()
+        nf, npup = int(Hx.size), int(Px_h.numel())
+        n = nf * npup
+        main = torch.cuda.current_stream(dev)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        cs = self._copy_stream
+        Px_d = torch.empty(npup, dtype=torch.float64, device=dev)
+        Py_d = torch.empty(npup, dtype=torch.float64, device=dev)
+        rays_in = torch.empty((8, n), dtype=dt, device=dev)
+        out = torch.empty((8, n), dtype=dt, device=dev)
+        dir0 = torch.empty((3, n), dtype=dt, device=dev)
+        C_ = max(1, min(self.pipeline_chunks, npup // 65536))
+        edges = [(c * npup // C_, (c + 1) * npup // C_) for c in range(C_)]
+        cs.wait_stream(main)
+        events = []
+        with torch.cuda.stream(cs):
+            for lo, hi in edges:
+                Px_d[lo:hi].copy_(Px_h[lo:hi], non_blocking=True)
+                Py_d[lo:hi].copy_(Py_h[lo:hi], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+                events.append(ev)
+        packed = sg.pack([float(wavelength)])
+        status_t = torch.zeros(1, dtype=torch.int32, device=dev)
+        from . import _lib as L
+        from .trace import slice_true_iters
+        n_slices = len(edges) * nf
+        has_nr = bool(packed.nr_rows())
+        for attempt in range(8):
+            k_used = packed.nr_iters()
+            resid = (torch.zeros((n_slices, packed.n_surfaces, L.RESID_STRIDE), dtype=torch.int64, device=dev)
+                     if has_nr else None)
+            q_ = 0
+            for (lo, hi), ev in zip(edges, events):
+                main.wait_event(ev)
+                for f in range(nf):
+                    a, b = f * npup + lo, f * npup + hi
+                    self.launch_rays(Hx[f:f + 1], Hy[f:f + 1], Px_d[lo:hi], Py_d[lo:hi], wavelength,
+                                     out=rays_in[:, a:b])
+                    fused_trace(packed, [rays_in[q, a:b] for q in range(7)] + [None], out=out[:, a:b],
+                                dir0_out=dir0[:, a:b], fast=sg.fast_math, verify_nr=False, check_status=False,
+                                status_t=status_t, resid_out=None if resid is None else resid[q_])
+                    q_ += 1
+            if not has_nr:
+                break
+            # ONE read-back for the whole batch: the batch-global exit rule is the max over the slices
+            rows = resid.cpu().numpy().view(np.float64)
+            per_slice = [slice_true_iters(packed, rows[q], k_used) for q in range(n_slices)]
+            if any(v is None for ps in per_slice for v in ps):      # some slice needs more updates
+                packed.set_nr_iters([min(lay.max_iter, max(k * 2, k + 2)) if lay.geom >= 2 else 0
+                                     for k, lay in zip(k_used, packed.layouts)])
+                continue
+            batch = [max(col) for col in zip(*per_slice)]
+            if batch == k_used:
+                break
+            packed.set_nr_iters(batch)
+        st = int(status_t.item())
+        if st & 1:
+            raise ValueError("Zernike coordinates must be normalized to [-1, 1]. Consider updating "
+                             "the normalization radius to 1.1x the surface aperture.")
+        rays = RealRays(*[rays_in[q] for q in range(8)])
+        sg.reset()
+        sg._finish(rays, packed, out, None, dir0, packed.nr_iters())
+        return rays
+
+    def launch_rays(self, Hx, Hy, Px, Py, wavelength, out=None) -> RealRays:
         """fields x pupil rays (field-major) from the ray-launch kernel `olrt_generate_rays_*`
         (ray_generator.py:28-106 + field_types.py:139-169, object at infinity). Hx, Hy: [F] NumPy arrays
         (one entry per field); Px, Py: [P] float64 device tensors."""
@@ -199,7 +283,8 @@ class Optic:
         fxy_d = torch.from_numpy(np.ascontiguousarray(fxy)).to(dev, non_blocking=True)
         z_start = float(self.surface_group.surfaces[1].geometry.cs.z) - offset
         nf, npup = int(hx.size), int(Px.numel())
-        out = torch.empty((8, nf * npup), dtype=dt, device=dev)
+        if out is None:
+            out = torch.empty((8, nf * npup), dtype=dt, device=dev)
         fn = lib.olrt_generate_rays_f64 if dt == torch.float64 else lib.olrt_generate_rays_f32
         Px, Py = Px.contiguous(), Py.contiguous()
         with torch.cuda.device(dev):
@@ -207,6 +292,8 @@ class Optic:
                     float(wavelength), L.PtrArray8(*[out[q].data_ptr() for q in range(8)]),
                     torch.cuda.current_stream(dev).cuda_stream)
         L.check(rc, "olrt_generate_rays")
+        if not out.is_contiguous():
+            return None  # a slice of a larger batch: the caller owns the RealRays object
         return RealRays(*[out[q] for q in range(8)])
 
     def trace_generic(self, Hx, Hy, Px, Py, wavelength):

@@ -203,14 +203,22 @@ class SurfaceGroup:
         for s in self._surfaces:
             s.reset()
 
-    def _wants_grad(self, rays) -> bool:
-        """Autograd is recorded when grad mode is on (torch_backend.py:45-64) or when any ray component or
-        prescription entry is a tensor that requires grad."""
+    def _finish(self, rays, packed, out, record, dir0, nr_iters):
+        """Hand the kernel's buffers to the objects the analyses read (surface_group.py:95-140,
+        standard_surface.py:266-286, real_rays.py:82-86)."""
+        for gi in packed.object_records:  # ObjectSurface.trace: record only, object_surface.py:56-72
+            self._surfaces[gi]._set_record(torch.stack(
+                [rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd]).clone())
+        for slot, gi in enumerate(packed.record_surfaces):
+            self._surfaces[gi]._set_record(record[slot] if record is not None else out)
+        rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd = (out[q] for q in range(8))
+        rays.L0, rays.M0, rays.N0 = dir0[0], dir0[1], dir0[2]
+        self._packed_cache = {packed.layouts[k].index: nr_iters[k] for k in packed.nr_rows()}
+
+    def _wants_grad_params(self) -> bool:
         if not torch.is_grad_enabled():
             return False
         if be.grad_mode.requires_grad:
-            return True
-        if any(isinstance(t, torch.Tensor) and t.requires_grad for t in rays.components() + [rays.opd]):
             return True
         for s in self._surfaces:
             g = s.geometry
@@ -220,6 +228,17 @@ class SurfaceGroup:
             if any(isinstance(v, torch.Tensor) and v.requires_grad for v in vals):
                 return True
         return False
+
+    def _wants_grad(self, rays) -> bool:
+        """Autograd is recorded when grad mode is on (torch_backend.py:45-64) or when any ray component or
+        prescription entry is a tensor that requires grad."""
+        if not torch.is_grad_enabled():
+            return False
+        if be.grad_mode.requires_grad:
+            return True
+        if any(isinstance(t, torch.Tensor) and t.requires_grad for t in rays.components() + [rays.opd]):
+            return True
+        return self._wants_grad_params()
 
     # ---- the hot path ----------------------------------------------------------------------
     def pack(self, wavelengths, skip=0) -> PackedSystem:
@@ -261,14 +280,6 @@ class SurfaceGroup:
                              "the normalization radius to 1.1x the surface aperture.")
         if res.status & 2:
             raise ValueError("a ray wavelength is missing from `wavelengths`")
-        for gi in packed.object_records:  # ObjectSurface.trace: record only, object_surface.py:56-72
-            self._surfaces[gi]._set_record(torch.stack(
-                [rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd]).clone())
-        for slot, gi in enumerate(packed.record_surfaces):
-            self._surfaces[gi]._set_record(res.record[slot])
-        o = res.out
-        rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd = (o[q] for q in range(8))
-        rays.L0, rays.M0, rays.N0 = res.dir0[0], res.dir0[1], res.dir0[2]
-        self._packed_cache = {packed.layouts[k].index: res.nr_iters[k] for k in packed.nr_rows()}
+        self._finish(rays, packed, res.out, res.record, res.dir0, res.nr_iters)
         self.last_trace = res
         return rays

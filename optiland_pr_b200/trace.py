@@ -32,6 +32,7 @@ class TraceResult:
     status: int
     launches: int
     fixups: int = -1             # rays re-traced by the IEEE fix-up kernel (fp64; -1 = not read back)
+    nr_true: list | None = None  # with nr_floor: the counts this slice alone satisfies the exit rule with
 
 
 def _ptr(t) -> int:
@@ -76,15 +77,33 @@ def _true_iters(resid_row: np.ndarray, k_used: int, tol: float, max_iter: int):
     return None
 
 
+def slice_true_iters(packed: PackedSystem, resid_rows: np.ndarray, k_used):
+    """Reference exit rule on one slice's reported maxima (float64 view of a `resid_out` buffer).
+    Returns the trip counts this slice satisfies the rule with, or None where it needs more than k_used."""
+    out = list(k_used)
+    for k in packed.nr_rows():
+        lay = packed.layouts[k]
+        out[k] = _true_iters(resid_rows[k], k_used[k], lay.tol_value, lay.max_iter)
+    return out
+
+
 def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tensor | None = None,
                 n_presc: int = 1, rays_per_presc: int = 0, want_dir0: bool = False,
                 fast: bool = False, verify_nr: bool = True, out: torch.Tensor | None = None,
-                max_relaunch: int = 24, read_fixups: bool = True, check_status: bool = True) -> TraceResult:
+                max_relaunch: int = 24, read_fixups: bool = True, check_status: bool = True,
+                dir0_out: torch.Tensor | None = None, status_t: torch.Tensor | None = None,
+                nr_floor: bool = False, resid_out: torch.Tensor | None = None) -> TraceResult:
     """Trace rays through a packed system on the current CUDA device and stream.
 
     rays_in: sequence of 8 tensors x y z L M N intensity wavelength (1-D, same length, CUDA,
              float64 or float32; wavelength may be None when the system has one wavelength).
     presc:   optional device tensor [n_presc, stride] overriding packed.presc (Monte Carlo batch).
+    resid_out: zero-initialised int64 [n_surfaces, RESID_STRIDE] device tensor: the kernel reports its
+             per-iteration residual maxima there and this call does NOT read them back (no host sync);
+             the caller checks them later with `slice_true_iters` (slices of one batch, optic.py).
+    nr_floor: this call traces one SLICE of a larger batch: never lower the Newton trip counts below the
+             ones in `packed` (another slice may need them), only raise them; the counts this slice alone
+             would have needed come back in `TraceResult.nr_true`.
     """
     lib = L.load()
     x = rays_in[0]
@@ -115,29 +134,41 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
     if out is None:
         out = torch.empty((8, n), dtype=dtype, device=device)
     record = torch.empty((n_rec, 8, n), dtype=dtype, device=device) if n_rec else None
-    dir0 = torch.empty((3, n), dtype=dtype, device=device) if want_dir0 else None
+    dir0 = dir0_out if dir0_out is not None else (
+        torch.empty((3, n), dtype=dtype, device=device) if want_dir0 else None)
     nr_rows = packed.nr_rows()
-    status_t = torch.zeros(1, dtype=torch.int32, device=device)
+    own_status = status_t is None
+    if own_status:  # a caller tracing one batch in slices shares one OR-accumulated word
+        status_t = torch.zeros(1, dtype=torch.int32, device=device)
+    nr_true = None
     fixup = _fixup_workspace(n, device) if dtype == torch.float64 else None
     fn = lib.olrt_trace_fwd_f64 if dtype == torch.float64 else lib.olrt_trace_fwd_f32
     in_arr = L.PtrArray8(*[_ptr(t) for t in ins])
     out_arr = L.PtrArray8(*[out[q].data_ptr() for q in range(8)])
+    # dir0 rows may be slices of a larger buffer: the kernel writes [3][n] with stride n, so a sliced
+    # destination needs its own contiguous scratch (copied back below)
+    dir0_tmp = None
+    if dir0 is not None and not dir0.is_contiguous():
+        dir0_tmp = torch.empty((3, n), dtype=dtype, device=device)
+    dir0_ptr = _ptr(dir0_tmp if dir0_tmp is not None else dir0)
     stream = torch.cuda.current_stream(device).cuda_stream
     launches = 0
     with torch.cuda.device(device):
         while True:
             resid = None
-            if nr_rows and verify_nr:
+            if nr_rows and resid_out is not None:
+                resid = resid_out
+            elif nr_rows and verify_nr:
                 resid = torch.zeros((packed.n_surfaces, L.RESID_STRIDE), dtype=torch.int64, device=device)
                 ops_d, _ = _device_tables(packed, dtype, device)
             sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=rays_per_presc)
             sys_.presc_stride = int(presc_d.shape[1])
             rc = fn(C.byref(sys_), presc_d.data_ptr(), ops_d.data_ptr(), n, in_arr, _ptr(opd_in),
-                    out_arr, _ptr(record), _ptr(dir0), _ptr(resid), status_t.data_ptr(), _ptr(fixup),
+                    out_arr, _ptr(record), dir0_ptr, _ptr(resid), status_t.data_ptr(), _ptr(fixup),
                     L.FWD_FAST if fast else 0, stream)
             L.check(rc, "olrt_trace_fwd")
             launches += 1
-            if resid is None or n == 0:
+            if resid is None or n == 0 or resid_out is not None:
                 break
             res = resid.cpu().numpy().view(np.float64)
             iters = packed.nr_iters()
@@ -149,6 +180,10 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
                     iters[k] = min(lay.max_iter, max(iters[k] * 2, iters[k] + 2))
                     changed = True
                     break
+                if kt < iters[k] and nr_floor:
+                    nr_true = nr_true if nr_true is not None else list(iters)
+                    nr_true[k] = kt
+                    continue
                 if kt != iters[k]:
                     iters[k] = kt
                     changed = True
@@ -158,10 +193,15 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
             if launches > max_relaunch:
                 raise L.OlrtLibraryError("Newton iteration counts did not settle")
             packed.set_nr_iters(iters)
-            status_t.zero_()
+            nr_true = None
+            if own_status:
+                status_t.zero_()
+    if dir0_tmp is not None:
+        dir0.copy_(dir0_tmp)
     status = int(status_t.item()) if check_status else 0  # device->host sync
     if status & L.ST_BAD_HINT:
         raise L.OlrtLibraryError("kernel_hint does not match the ops table (packer bug)")
     fixups = int(fixup[0].item()) if (fixup is not None and read_fixups and check_status) else -1
     return TraceResult(out=out, record=record, dir0=dir0, nr_iters=packed.nr_iters(), status=status,
-                       launches=launches, fixups=fixups)
+                       launches=launches, fixups=fixups,
+                       nr_true=nr_true if nr_true is not None else packed.nr_iters())

@@ -42,3 +42,26 @@ def test_cuda_ray_launch_matches_reference_bits():
         for fi in range(len(fields)):
             k = fi * len(lens.wavelengths) + wi
             assert np.array_equal(got[:, fi * 150:(fi + 1) * 150], g["rays_in"][:, k * 150:(k + 1) * 150]), (fi, wi)
+
+
+@pytest.mark.gpu
+def test_pipelined_host_pupil_equals_resident_trace():
+    """Optic.trace with a pinned HOST pupil grid (chunked copy overlapped with launch + trace) gives the
+    same bits as the same call with the grid already on the device."""
+    import torch
+
+    from optiland_pr_b200 import backend as be
+
+    be.set_precision("float64")
+    lens = samples.EvenAsphereDoubleGauss()
+    lens.surface_group.record = "last"
+    lens.pipeline_min_rays = 1 << 16
+    px, py = raygen_np.random_pupil(300_000, seed=5)
+    Hx, Hy = [0.0, 0.0, 0.0], [0.0, 0.7, 1.0]
+    a = lens.trace(Hx, Hy, 0.5876, distribution=(torch.from_numpy(px).pin_memory(), torch.from_numpy(py).pin_memory()))
+    xa = torch.stack([a.x, a.y, a.z, a.L, a.M, a.N, a.i, a.opd, a.L0, a.M0, a.N0]).cpu().numpy()
+    last_a = lens.surface_group.x[-1].cpu().numpy()
+    b = lens.trace(Hx, Hy, 0.5876, distribution=(torch.from_numpy(px).cuda(), torch.from_numpy(py).cuda()))
+    xb = torch.stack([b.x, b.y, b.z, b.L, b.M, b.N, b.i, b.opd, b.L0, b.M0, b.N0]).cpu().numpy()
+    assert np.array_equal(xa, xb, equal_nan=True)
+    assert np.array_equal(last_a, lens.surface_group.x[-1].cpu().numpy())
