@@ -43,25 +43,44 @@ struct BwdParams {
   R four_pi;
 };
 
+// The adjoint has no bit-parity contract (bar: 1e-8): unguarded refinement sequences, no slow paths.
+template <typename R> __device__ __forceinline__ R bdiv(R a, R b) { return m_div<MM_FAST>(a, b); }
+template <typename R> __device__ __forceinline__ R bsqrt(R a) { return m_sqrt<MM_FAST>(a); }
+
+template <typename R> __device__ __forceinline__ R brcp(R a);
+template <> __device__ __forceinline__ double brcp<double>(double a) {  // one cubic Newton step: ~2^-60 relative
+  double r = rcp_seed(a);
+  double e = __fma_rn(-a, r, 1.0);
+  e = __fma_rn(e, e, e);
+  return __fma_rn(r, e, r);
+}
+template <> __device__ __forceinline__ float brcp<float>(float a) { return 1.0f / a; }
+
+// reciprocal powers of the radius, once per surface
 template <typename R>
-__device__ __forceinline__ R b_div(R a, R b) { return a / b; }
+struct BwdConst {
+  R iR, iR2, iR3;
+};
 
 // sag S, slope factor G (zx = x G, zy = y G) and dG/dr2 of conic + even-asphere terms at (x, y)
 template <typename R>
 struct SagEval {
-  R r2, s, S, G, Gp;
+  R r2, s, is, i1s, S, G, Gp;  // is = 1/s, i1s = 1/(1+s)
 };
 
 template <typename R>
-__device__ __forceinline__ void sag_eval(const SurfParams<R>& sp, bool plane, R x, R y, SagEval<R>& e) {
+__device__ __forceinline__ void sag_eval(const SurfParams<R>& sp, const BwdConst<R>& bc, bool plane, R x, R y,
+                                         SagEval<R>& e) {
   e.r2 = x * x + y * y;
-  if (plane) { e.s = R(1); e.S = R(0); e.G = R(0); e.Gp = R(0); return; }
-  const R Rr = sp.cc.radius, c1 = sp.cc.c1;
-  const R B = R(1) - c1 * e.r2 / (Rr * Rr);
-  e.s = sqrt(B);
-  e.S = e.r2 / (Rr * (R(1) + e.s));
-  e.G = R(1) / (Rr * e.s);
-  e.Gp = c1 / (R(2) * Rr * Rr * Rr * e.s * e.s * e.s);
+  if (plane) { e.s = R(1); e.is = R(1); e.i1s = R(0.5); e.S = R(0); e.G = R(0); e.Gp = R(0); return; }
+  const R c1 = sp.cc.c1;
+  const R B = R(1) - c1 * e.r2 * bc.iR2;
+  e.s = bsqrt(B);
+  e.is = brcp(e.s);
+  e.i1s = brcp(R(1) + e.s);
+  e.S = e.r2 * bc.iR * e.i1s;
+  e.G = bc.iR * e.is;
+  e.Gp = R(0.5) * c1 * bc.iR3 * e.is * e.is * e.is;
   if (sp.geom == OLRT_GEOM_EVEN_ASPHERE) {
     R pw = R(1), pwm1 = R(0);  // r2^i, r2^(i-1)
     for (int i = 0; i < sp.ncoef; ++i) {
@@ -78,23 +97,23 @@ __device__ __forceinline__ void sag_eval(const SurfParams<R>& sp, bool plane, R 
 
 // adjoint of (S, zx, zy)(x, y; R, k, C) given (gS, gzx, gzy); accumulates gx, gy and the parameter partials
 template <typename R>
-__device__ __forceinline__ void sag_adjoint(const SurfParams<R>& sp, bool plane, R x, R y, const SagEval<R>& e,
-                                            R gS, R gzx, R gzy, R& gx, R& gy, R& gR, R& gk, R* gC) {
+__device__ __forceinline__ void sag_adjoint(const SurfParams<R>& sp, const BwdConst<R>& bc, bool plane, R x, R y,
+                                            const SagEval<R>& e, R gS, R gzx, R gzy, R& gx, R& gy, R& gR, R& gk,
+                                            R* gC) {
   if (plane) return;
   const R q = gzx * x + gzy * y;  // gradient w.r.t. G
   const R zx = x * e.G, zy = y * e.G;
   gx += gS * zx + gzx * e.G + q * e.Gp * (R(2) * x);
   gy += gS * zy + gzy * e.G + q * e.Gp * (R(2) * y);
-  const R Rr = sp.cc.radius, c1 = sp.cc.c1, s = e.s, r2 = e.r2;
-  const R ds_dR = c1 * r2 / (Rr * Rr * Rr * s);
-  const R ds_dk = -r2 / (R(2) * Rr * Rr * s);
-  const R one_s = R(1) + s;
-  const R dSc_ds = -r2 / (Rr * one_s * one_s);
-  const R dSc_dR = -r2 / (Rr * Rr * one_s) + dSc_ds * ds_dR;
-  const R dg0_ds = -R(1) / (Rr * s * s);
-  const R dg0_dR = -R(1) / (Rr * Rr * s) + dg0_ds * ds_dR;
+  const R c1 = sp.cc.c1, r2 = e.r2;
+  const R ds_dR = c1 * r2 * bc.iR3 * e.is;
+  const R ds_dk = R(-0.5) * r2 * bc.iR2 * e.is;
+  const R dSc_ds = -r2 * bc.iR * e.i1s * e.i1s;
+  const R dSc_dR = -r2 * bc.iR2 * e.i1s + dSc_ds * ds_dR;
+  const R dg0_ds = -bc.iR * e.is * e.is;
+  const R dg0_dR = -bc.iR2 * e.is + dg0_ds * ds_dR;
   gR += gS * dSc_dR + q * dg0_dR;
-  gk += gS * dSc_ds * ds_dk + q * dg0_ds * ds_dk;
+  gk += (gS * dSc_ds + q * dg0_ds) * ds_dk;
   if (sp.geom == OLRT_GEOM_EVEN_ASPHERE) {
     R pw = R(1);
 #pragma unroll
@@ -116,8 +135,9 @@ __device__ __forceinline__ R conic_t(const SurfParams<R>& sp, R x, R y, R z, R L
   a = k * N * N + L * L + M * M + N * N;
   hb = k * N * z + L * x + M * y - N * Rr + N * z;
   const R c = k * z * z - R(2) * Rr * z + x * x + y * y + z * z;
-  const R sd = sqrt(hb * hb - a * c);
-  const R t1 = (-hb + sd) / a, t2 = (-hb - sd) / a;
+  const R sd = bsqrt(hb * hb - a * c);
+  const R ia = brcp(a);
+  const R t1 = (-hb + sd) * ia, t2 = (-hb - sd) * ia;
   R t = (r_abs(z + t1 * N) <= r_abs(z + t2 * N)) ? t1 : t2;
   if (a == R(0)) t = -c / (R(2) * hb);
   return t;
@@ -142,25 +162,30 @@ __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int 
   // ---- forward recompute (local frame)
   const R x = ex - f[0], y = ey - f[1], z = ez - f[2];
   const R L = eL, M = eM, N = eN;
+  BwdConst<R> bc;
+  bc.iR = plane ? R(0) : brcp(sp.cc.radius);
+  bc.iR2 = bc.iR * bc.iR;
+  bc.iR3 = bc.iR2 * bc.iR;
+  const R iN = plane ? brcp(N) : R(0);
   R a = R(0), hb = R(0), t0;
-  if (plane) t0 = -z / N;
+  if (plane) t0 = -z * iN;
   else t0 = conic_t(sp, x, y, z, L, M, N, a, hb);
   const int K = (sp.geom == OLRT_GEOM_EVEN_ASPHERE) ? op[OLRT_OP_NR_ITERS] : 0;
   R t = t0;
   for (int j = 0; j < K; ++j) {
     SagEval<R> e;
     const R qx = x + t * L, qy = y + t * M, qz = z + t * N;
-    sag_eval(sp, false, qx, qy, e);
+    sag_eval(sp, bc, false, qx, qy, e);
     const R h = qx * e.G * L + qy * e.G * M - N;
-    t = t - (e.S - qz) / h;
+    t = t - (e.S - qz) * brcp(h);
   }
   const R Qx = x + t * L, Qy = y + t * M;
   SagEval<R> eq;
-  sag_eval(sp, plane, Qx, Qy, eq);
-  R nx, ny, nz, mag = R(1);
+  sag_eval(sp, bc, plane, Qx, Qy, eq);
+  R nx, ny, nz, imag = R(1);
   const R zx = Qx * eq.G, zy = Qy * eq.G;
   if (plane) { nx = R(0); ny = R(0); nz = R(1); }
-  else { mag = sqrt(zx * zx + zy * zy + R(1)); nx = zx / mag; ny = zy / mag; nz = R(-1) / mag; }
+  else { imag = brcp(bsqrt(zx * zx + zy * zy + R(1))); nx = zx * imag; ny = zy * imag; nz = -imag; }
   const R dot = L * nx + M * ny + N * nz;
   const R sg = r_sign(dot), c = r_abs(dot);
   const R ax = nx * sg, ay = ny * sg, az = nz * sg;  // aligned normal
@@ -174,12 +199,12 @@ __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int 
     gax = R(-2) * c * gL; gay = R(-2) * c * gM; gaz = R(-2) * c * gN;
   } else {  // D' = u D + a (root - u c)
     const R u = sp.u, u2 = sp.u2;
-    const R root = sqrt(R(1) - u2 * (R(1) - c * c));
+    const R root = bsqrt(R(1) - u2 * (R(1) - c * c));
     const R w = root - u * c;
     gDx = u * gL; gDy = u * gM; gDz = u * gN;
     gax = w * gL; gay = w * gM; gaz = w * gN;
     const R gw = ax * gL + ay * gM + az * gN;
-    gc = -u * gw + (gw / (R(2) * root)) * (R(2) * u2 * c);
+    gc = -u * gw + gw * brcp(root) * (u2 * c);
   }
   const R gdot = sg * gc;
   R gnx = sg * gax + gdot * L, gny = sg * gay + gdot * M, gnz = sg * gaz + gdot * N;
@@ -188,11 +213,11 @@ __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int 
   R gzx = R(0), gzy = R(0);
   if (!plane) {
     const R ng = nx * gnx + ny * gny + nz * gnz;
-    gzx = (gnx - nx * ng) / mag;
-    gzy = (gny - ny * ng) / mag;
+    gzx = (gnx - nx * ng) * imag;
+    gzy = (gny - ny * ng) * imag;
   }
   R gQx = gx, gQy = gy, gQz = gz;  // position after propagation (clip and interaction do not move it)
-  sag_adjoint(sp, plane, Qx, Qy, eq, R(0), gzx, gzy, gQx, gQy, gR, gk, gC);
+  sag_adjoint(sp, bc, plane, Qx, Qy, eq, R(0), gzx, gzy, gQx, gQy, gR, gk, gC);
   // ---- clip (where(~inside, 0, i)), absorption, opd
   R gt = gopd * ((t * sp.n1 < R(0)) ? -sp.n1 : sp.n1);
   const int aoff = op[OLRT_OP_APER_OFF];
@@ -215,31 +240,31 @@ __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int 
     for (int q = 0; q < j; ++q) {  // recompute t_j (K is 1-3 in practice)
       SagEval<R> e;
       const R qx = x + tj * L, qy = y + tj * M, qz = z + tj * N;
-      sag_eval(sp, false, qx, qy, e);
-      tj = tj - (e.S - qz) / (qx * e.G * L + qy * e.G * M - N);
+      sag_eval(sp, bc, false, qx, qy, e);
+      tj = tj - (e.S - qz) * brcp(qx * e.G * L + qy * e.G * M - N);
     }
     SagEval<R> e;
     const R qx = x + tj * L, qy = y + tj * M, qz = z + tj * N;
-    sag_eval(sp, false, qx, qy, e);
+    sag_eval(sp, bc, false, qx, qy, e);
     const R sx = qx * e.G, sy = qy * e.G;
-    const R fj = e.S - qz, h = sx * L + sy * M - N;
-    const R gf = -gtj / h, gh = gtj * fj / (h * h);
+    const R fj = e.S - qz, ih = brcp(sx * L + sy * M - N);
+    const R gf = -gtj * ih, gh = gtj * fj * ih * ih;
     gDx += gh * sx; gDy += gh * sy; gDz -= gh;
     R gqx = R(0), gqy = R(0);
     const R gqz = -gf;
-    sag_adjoint(sp, false, qx, qy, e, gf, gh * L, gh * M, gqx, gqy, gR, gk, gC);
+    sag_adjoint(sp, bc, false, qx, qy, e, gf, gh * L, gh * M, gqx, gqy, gR, gk, gC);
     gPx += gqx; gPy += gqy; gPz += gqz;
     gDx += tj * gqx; gDy += tj * gqy; gDz += tj * gqz;
     gtj = gtj + L * gqx + M * gqy + N * gqz;
   }
   // ---- t0: plane or conic (implicit differentiation of the quadratic the root satisfies)
   if (plane) {
-    gPz += -gtj / N;
-    gDz += -gtj * t0 / N;
+    gPz += -gtj * iN;
+    gDz += -gtj * t0 * iN;
   } else {
     const R Rr = sp.cc.radius, k = sp.cc.k;
-    const R den = R(2) * (a * t0 + hb);
-    const R ga = -gtj * t0 * t0 / den, ghb = -gtj * R(2) * t0 / den, gcc = -gtj / den;
+    const R gcc = -gtj * brcp(R(2) * (a * t0 + hb));
+    const R ga = gcc * t0 * t0, ghb = gcc * R(2) * t0;
     gk += ga * N * N + ghb * N * z + gcc * z * z;
     gR += -ghb * N - R(2) * gcc * z;
     gDx += ga * R(2) * L + ghb * x;
