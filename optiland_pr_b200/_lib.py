@@ -33,6 +33,7 @@ AP_OR, AP_AND, AP_DIFF = 10, 11, 12
 ST_ZERNIKE_RANGE, ST_WAVELENGTH, ST_BAD_HINT = 1, 2, 4
 HINT_FASTKINDS = 1
 FWD_FAST = 1
+FWD_REPLAY = 2
 SPOT_VALID_ONLY = 1
 
 ERRORS = {0: "ok", -1: "OLRT_E_ARG", -2: "OLRT_E_LIMIT", -3: "OLRT_E_LAUNCH", -4: "OLRT_E_UNSUPPORTED"}

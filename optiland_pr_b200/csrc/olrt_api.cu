@@ -50,8 +50,8 @@ extern "C" int olrt_trace_fwd_f64(const olrt_sys* sys, const double* presc, cons
   if (n_rays == 0) return OLRT_OK;
   cudaStream_t st = (cudaStream_t)stream;
   if (flags & OLRT_FWD_FAST)
-    return olrt_fast::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, st);
-  return olrt_strict::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, st);
+    return olrt_fast::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags, st);
+  return olrt_strict::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, 0, st);
 }
 
 extern "C" int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
@@ -59,14 +59,13 @@ extern "C" int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const
                                   float* const out[8], float* record, float* dir0,
                                   unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup,
                                   int flags, void* stream) {
-  (void)flags;
   int rc = check_sys(sys, presc, ops, n_rays);
   if (rc) return rc;
   rc = check_rays<float>(sys, in, out);
   if (rc) return rc;
   if (sys->n_record > 0 && !record) return OLRT_E_ARG;
   if (n_rays == 0) return OLRT_OK;
-  return olrt_fast::fwd_f32(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup,
+  return olrt_fast::fwd_f32(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags,
                             (cudaStream_t)stream);
 }
 

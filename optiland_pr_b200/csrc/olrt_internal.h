@@ -7,7 +7,8 @@
   namespace NS {                                                                                   \
   int fwd_##SUF(const olrt_sys* sys, const R* presc, const int32_t* ops, long long n_rays,         \
                 const R* const in[8], const R* opd_in, R* const out[8], R* record, R* dir0,        \
-                unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, cudaStream_t stream); \
+                unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags,      \
+                cudaStream_t stream);                                                              \
   }
 OLRT_DECL_FWD(olrt_strict, f64, double)
 OLRT_DECL_FWD(olrt_fast, f64, double)

@@ -323,4 +323,16 @@ __device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v)
   return ((unsigned long long)mhi << 32) | mlo;
 }
 
+// Fold one warp's keys into a shared-memory running maximum. The slot is read first (one broadcast
+// LDS) and the redux + atomic run only when some lane would raise it: after the first few tiles of a
+// persistent CTA the slot already holds (nearly) the CTA's maximum and the common case is 5 instructions.
+// A stale read can only cause a redundant atomicMax, never a lost update. All 32 lanes must call.
+__device__ __forceinline__ void report_resid(unsigned long long* slot, unsigned long long key) {
+  const unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(slot);
+  if (__any_sync(0xffffffffu, key > cur)) {
+    const unsigned long long wmax = warp_max_u64(key);
+    if ((threadIdx.x & 31) == 0) atomicMax(slot, wmax);
+  }
+}
+
 }  // namespace OLRT_NS

@@ -1,19 +1,20 @@
 // Fast build: FMA contraction allowed (-fmad=true). fp64 here is NOT bit-faithful to the
 // reference (last-ulp differences); fp32 is only ever built fast (its parity bar is 1e-5).
 #define OLRT_NS olrt_fast
+#define OLRT_FX 1  // this TU also carries the reduced-algebra kernel (trace_fx.cuh)
 #include "trace_launch.cuh"
 #include "olrt_internal.h"
 
 namespace olrt_fast {
 int fwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, long long n_rays,
             const double* const in[8], const double* opd_in, double* const out[8], double* record,
-            double* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, cudaStream_t stream) {
-  return launch_fwd<double>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, stream);
+            double* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags, cudaStream_t stream) {
+  return launch_fwd<double>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags, stream);
 }
 int fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, long long n_rays,
             const float* const in[8], const float* opd_in, float* const out[8], float* record,
-            float* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, cudaStream_t stream) {
-  return launch_fwd<float>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, stream);
+            float* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags, cudaStream_t stream) {
+  return launch_fwd<float>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags, stream);
 }
 int bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, long long n_rays,
             const double* const in[8], const double* record, const double* const gout[8], const double* grecord,

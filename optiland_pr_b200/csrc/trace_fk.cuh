@@ -144,8 +144,7 @@ __device__ __forceinline__ void fk_even(RayState<R>& r, const SurfParams<R>& sp,
     const R f = sag - zi;
     if (resid != nullptr) {  // NaN: the ray is on its way to the fix-up list, which reports it (IEEE)
       const unsigned long long key = (valid && f == f) ? resid_bits((double)r_abs(f)) : 0ull;
-      const unsigned long long wmax = warp_max_u64(key);
-      if ((threadIdx.x & 31) == 0 && wmax != 0ull) atomicMax(resid + j, wmax);
+      report_resid(resid + j, key);
     }
     slopes_to_normal<R, MM>(zx, zy, nx, ny, nz);
     if (j >= K) break;
@@ -180,7 +179,7 @@ __device__ __forceinline__ bool is_pos_zero(R v) { return v == R(0) && !signbit(
 // Main pass for lenses whose surfaces are ALL fast kinds (olrt_sys.kernel_hint & OLRT_HINT_FASTKINDS,
 // verified here: a wrong hint sets OLRT_ST_BAD_HINT and traces nothing).
 template <typename R>
-__global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fk_kernel(const FwdParams<R> P) {
+__global__ void __launch_bounds__(OLRT_FK_BLOCK, OLRT_FK_MIN_BLOCKS) trace_fk_kernel(const FwdParams<R> P) {
   constexpr int MM = MM_FAST;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int S = P.n_surfaces, W = P.n_wavelengths;

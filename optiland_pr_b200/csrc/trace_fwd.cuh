@@ -154,8 +154,7 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
         if (resid != nullptr) {
           // MM_FAST: a NaN here puts the ray on the fix-up list, whose IEEE re-trace reports it instead
           const unsigned long long key = (valid && !(MM == MM_FAST && f != f)) ? resid_bits((double)r_abs(f)) : 0ull;
-          const unsigned long long wmax = warp_max_u64(key);
-          if ((threadIdx.x & 31) == 0 && wmax != 0ull) atomicMax(resid + j, wmax);
+          report_resid(resid + j, key);
         }
         if (j == K) break;
         R nx, ny, nz;
@@ -213,6 +212,14 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
 
 #ifndef OLRT_FWD_MIN_BLOCKS
 #define OLRT_FWD_MIN_BLOCKS 2
+#endif
+// fast-kinds kernel CTA shape (trace_fk.cuh): threads per CTA and resident CTAs per SM the register
+// budget is sized for
+#ifndef OLRT_FK_BLOCK
+#define OLRT_FK_BLOCK 256
+#endif
+#ifndef OLRT_FK_MIN_BLOCKS
+#define OLRT_FK_MIN_BLOCKS 2
 #endif
 
 template <typename R> __device__ __forceinline__ bool nonfinite(R v);

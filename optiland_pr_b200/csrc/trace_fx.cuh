@@ -1,0 +1,447 @@
+// trace_fx.cuh -- the tolerance-mode forward kernel for the fast kinds (plane, sphere / conic, even
+// asphere on one untilted frame; radial aperture or none; absorbing media allowed).
+//
+// The strict kernels (trace_fk.cuh, trace_fwd.cuh) replay the reference's operations one by one so that
+// the results are the same bits. This kernel computes the SAME quantities -- the same roots, the same
+// Newton iterates, the same clip / TIR decisions -- from algebraically equivalent expressions that need
+// far fewer fp64 instructions, and is held to the stated tolerance (1e-10 relative, identical masks)
+// instead of to the bit:
+//   * 1/b and 1/sqrt(a) come from the MUFU seed (2^-20, measured) and ONE third-order refinement
+//     (measured 2^-53 on 2^22 operands, scratch/seed_probe.cu); a/b = a * (1/b), sqrt(a) = a * rsqrt(a)
+//   * sphere normal = (P - C)/R (no square root); conic normal = sgn(R) (x, y, -(R - (1+k) z)) / |.|
+//     (standard.py:142-167 evaluates the same vector as (x/(R q), y/(R q), -1)/|.|, q = sqrt(1-(1+k)r^2/R^2),
+//     and R q = R - (1+k) z on the sheet the root selection picks)
+//   * Newton slopes are used as they are: the reference normalises (zx, zy, -1), then divides nx, ny by nz
+//     again (newton_raphson.py:151-160) -- fx = -nx/nz = zx
+//   * even-asphere sums in Horner form; Snell as T = u D + n (root - u |dot|) sgn(dot)
+// Zero radicands, zero divisors and NaN rays leave this kernel as non-finite outputs and are re-traced by
+// the IEEE fix-up pass (trace_fwd.cuh, FIX = true) exactly like in the strict build; fp32 uses the
+// hardware's IEEE-safe sqrtf / reciprocal instead (there is no fp32 fix-up pass).
+#pragma once
+#include "trace_fk.cuh"
+
+namespace OLRT_NS {
+
+#ifndef OLRT_FX_BLOCK
+#define OLRT_FX_BLOCK 256
+#endif
+#ifndef OLRT_FX_MIN_BLOCKS
+#define OLRT_FX_MIN_BLOCKS 2
+#endif
+
+template <typename R> struct FxMath;
+template <> struct FxMath<double> {
+  static __device__ __forceinline__ double rcp(double b) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(b));
+    double e = fma(-b, r, 1.0);
+    e = fma(e, e, e);
+    return fma(r, e, r);
+  }
+  static __device__ __forceinline__ double rsqrt(double a) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+    const double e = fma(a, -(y * y), 1.0);
+    const double p = fma(e, 0.375, 0.5);
+    return fma(p, y * e, y);
+  }
+  static __device__ __forceinline__ double sqrt_(double a) { return a * rsqrt(a); }
+  static __device__ __forceinline__ void sqrt_pair(double a, double& s, double& is) { is = rsqrt(a); s = a * is; }
+  static __device__ __forceinline__ double copysign_(double m, double s) { return copysign(m, s); }
+  // m * sign(s) for s != 0: flip m's sign bit when s is negative
+  static __device__ __forceinline__ double flipsign(double m, double s) {
+    return __hiloint2double(__double2hiint(m) ^ (__double2hiint(s) & (int)0x80000000), __double2loint(m));
+  }
+};
+template <> struct FxMath<float> {
+  static __device__ __forceinline__ float rcp(float b) { return __frcp_rn(b); }
+  static __device__ __forceinline__ float rsqrt(float a) { return rsqrtf(a); }
+  static __device__ __forceinline__ float sqrt_(float a) { return sqrtf(a); }
+  static __device__ __forceinline__ void sqrt_pair(float a, float& s, float& is) { s = sqrtf(a); is = rsqrtf(a); }
+  static __device__ __forceinline__ float copysign_(float m, float s) { return copysignf(m, s); }
+  static __device__ __forceinline__ float flipsign(float m, float s) {
+    return __int_as_float(__float_as_int(m) ^ (__float_as_int(s) & (int)0x80000000));
+  }
+};
+
+// per-surface table in shared memory, built once per CTA (per prescription of a Monte-Carlo batch)
+template <typename R> struct __align__(16) FxSurf {
+  R xc, yc;
+  R zc, radius;
+  R iR, c1;         // 1/R, 1+k
+  R k, c1iR2;       // k, (1+k)/R^2
+  R rmax2, rmin2;   // radial aperture (r_max^2, r_min^2)
+  R twoR, pad;
+};
+template <typename R> struct __align__(16) FxMedium {
+  R n1, u, u2, nalpha;  // n_pre, n_pre/n_post, its square, -(4 pi k / lambda) * 1e3
+};
+struct __align__(16) FxInfo {
+  int kind;      // KIND_* | FX_*
+  int K;         // Newton updates
+  int ncoef;
+  int coef_off;  // offset (reals) of this surface's coefficients in the padded table s_coef
+  // ncoef above is rounded up to a multiple of 4 there (zero padding leaves the Horner sums unchanged)
+  int record;
+  int roff;      // first residual slot of this surface
+  int pad0, pad1;
+};
+enum { FX_CENTERED = 16, FX_REFLECT = 32, FX_SPHERE = 64, FX_APER = 128 };
+
+template <typename R>
+__host__ __device__ __forceinline__ size_t fx_smem_bytes(int presc_stride, int S, int W, int ops_len, int resid_words) {
+  return (size_t)((presc_stride + 3) & ~3) * sizeof(R) + (size_t)((presc_stride + 4 * S + 3) & ~3) * sizeof(R) +
+         (size_t)S * sizeof(FxSurf<R>) +
+         (size_t)S * W * sizeof(FxMedium<R>) + (size_t)S * sizeof(FxInfo) +
+         (size_t)((ops_len + 3) & ~3) * sizeof(int32_t) + (size_t)resid_words * sizeof(unsigned long long);
+}
+
+template <typename R>
+__device__ __forceinline__ void fx_build_surface(const int32_t* s_ops, const R* s_presc, FxSurf<R>* s_surf,
+                                                 FxMedium<R>* s_med, FxInfo* s_info, R* s_coef, int s, int S, int W,
+                                                 const R* wavelengths, R four_pi) {
+  const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
+  const int doff = op[OLRT_OP_DOFF];
+  const R* f = s_presc + doff;
+  const R* g = f + OLRT_FRAME_REALS;  // one frame (fast kind)
+  const R* media = g + OLRT_GEOM_REALS;
+  FxSurf<R>& sf = s_surf[s];
+  sf.xc = f[0]; sf.yc = f[1]; sf.zc = f[2];
+  const R radius = g[0], k = g[1];
+  sf.radius = radius; sf.k = k; sf.c1 = R(1) + k;
+  sf.iR = R(1) / radius;
+  sf.c1iR2 = (R(1) + k) / (radius * radius);
+  sf.twoR = R(2) * radius;
+  sf.pad = R(0);
+  int kind = s_info[s].kind & 15;
+  if (is_pos_zero(f[0]) && is_pos_zero(f[1])) kind |= FX_CENTERED;
+  if (op[OLRT_OP_INTERACT] == 1) kind |= FX_REFLECT;
+  if (k == R(0)) kind |= FX_SPHERE;
+  if (op[OLRT_OP_APER_OFF] >= 0) {
+    const R* ap = f + op[OLRT_OP_APER_DOFF];
+    sf.rmax2 = ap[0]; sf.rmin2 = ap[1];
+    kind |= FX_APER;
+  } else {
+    sf.rmax2 = R(0); sf.rmin2 = R(0);
+  }
+  s_info[s].kind = kind;
+  s_info[s].K = op[OLRT_OP_NR_ITERS];
+  // coefficients, zero-padded to a multiple of 4: slot = (reals before this surface) + 4 s bounds the padding
+  const int m = ((kind & 15) == KIND_EVEN) ? op[OLRT_OP_NCOEF] : 0;
+  const int m4 = (m + 3) & ~3;
+  const int coff = (doff + 4 * s + 3) & ~3;
+  const R* csrc = media + 3 * W;
+  for (int i = 0; i < m4; ++i) s_coef[coff + i] = (i < m) ? csrc[i] : R(0);
+  s_info[s].ncoef = m4;
+  s_info[s].coef_off = coff;
+  s_info[s].record = op[OLRT_OP_RECORD];
+  const bool absorb = (op[OLRT_OP_FLAGS] & OLRT_F_ABSORB) != 0;
+  for (int w = 0; w < W; ++w) {
+    FxMedium<R>& md = s_med[s * W + w];
+    const R u = media[w] / media[W + w];
+    md.n1 = media[w]; md.u = u; md.u2 = u * u;
+    md.nalpha = absorb ? -(four_pi * media[2 * W + w] / wavelengths[w]) * R(1e3) : R(0);
+  }
+}
+
+// StandardGeometry.distance, standard.py:89-140, for a ray already in the surface frame
+template <typename R>
+__device__ __forceinline__ R fx_conic_t(R x, R y, R z, R L, R M, R N, const FxSurf<R>& sf, bool sphere) {
+  typedef FxMath<R> Mx;
+  if (sizeof(R) == 4) {  // fp32 keeps the shifted, cancellation-free form of the strict fp32 path
+    RayState<R> rs; rs.x = x; rs.y = y; rs.z = z; rs.L = L; rs.M = M; rs.N = N;
+    ConicConst<R> cc; cc.radius = sf.radius; cc.k = sf.k; cc.c1 = sf.c1; cc.R2 = sf.radius * sf.radius;
+    cc.twoR = sf.twoR; cc.rR2 = R(0);
+    return conic_distance<R, MM_FAST>(rs, cc, false);
+  }
+  const R NN = N * N;
+  R a = fma(L, L, fma(M, M, NN));
+  R hb = fma(L, x, fma(M, y, N * (z - sf.radius)));
+  R c = fma(x, x, fma(y, y, z * (z - sf.twoR)));
+  if (!sphere) {
+    const R k = sf.k;
+    a = fma(k, NN, a);
+    hb = fma(k * N, z, hb);
+    c = fma(k * z, z, c);
+  }
+  const R sd = Mx::sqrt_(fma(hb, hb, -(a * c)));  // miss: NaN
+  const R ra = Mx::rcp(a);
+  const R t1 = (sd - hb) * ra, t2 = (-hb - sd) * ra;
+  const R z1 = fma(t1, N, z), z2 = fma(t2, N, z);
+  return (r_abs(z1) <= r_abs(z2)) ? t1 : t2;  // a == 0 (paraboloid, ray along the axis): non-finite -> fix-up
+}
+
+// propagate + Beer-Lambert exponent + OPD + radial clip, with the ray in the surface frame
+template <typename R>
+__device__ __forceinline__ void fx_arrive(RayState<R>& r, R t, const FxSurf<R>& sf, const FxMedium<R>& md,
+                                          int kind, R r2, R& att) {
+  att = fma(md.nalpha, t, att);
+  r.opd = fma(r_abs(t), r_abs(md.n1), r.opd);  // opd + |t n|, standard_surface.py:218
+  if (kind & FX_APER) {
+    const bool inside = (r2 <= sf.rmax2) & (r2 >= sf.rmin2);
+    if (!inside) { r.i = R(0); att = R(0); }
+  }
+}
+
+// RealRays.refract / reflect, real_rays.py:141-181, with dot = D . n already known
+template <typename R>
+__device__ __forceinline__ void fx_interact(RayState<R>& r, R nx, R ny, R nz, R dot, const FxMedium<R>& md, int kind) {
+  typedef FxMath<R> Mx;
+  if (kind & FX_REFLECT) {
+    const R d2 = dot + dot;
+    r.L = fma(-d2, nx, r.L); r.M = fma(-d2, ny, r.M); r.N = fma(-d2, nz, r.N);
+    return;
+  }
+  const R v = fma(md.u2, fma(dot, dot, R(-1)), R(1));  // 1 - u^2 (1 - dot^2); < 0: TIR -> NaN
+  const R root = Mx::sqrt_(v);
+  R g = Mx::flipsign(fma(-md.u, r_abs(dot), root), dot);
+  if (dot == R(0)) g = R(0);  // n * sign(0)
+  r.L = fma(md.u, r.L, nx * g);
+  r.M = fma(md.u, r.M, ny * g);
+  r.N = fma(md.u, r.N, nz * g);
+}
+
+template <typename R>
+__device__ __forceinline__ void fx_localize(RayState<R>& r, const FxSurf<R>& sf, int kind) {
+  if (!(kind & FX_CENTERED)) { r.x = r.x - sf.xc; r.y = r.y - sf.yc; }
+  r.z = r.z - sf.zc;
+}
+template <typename R>
+__device__ __forceinline__ void fx_globalize(RayState<R>& r, const FxSurf<R>& sf, int kind) {
+  if (!(kind & FX_CENTERED)) { r.x = r.x + sf.xc; r.y = r.y + sf.yc; }
+  r.z = r.z + sf.zc;
+}
+
+template <typename R>
+__device__ __forceinline__ void fx_plane(RayState<R>& r, const FxSurf<R>& sf, const FxMedium<R>& md, int kind,
+                                         R& att) {
+  typedef FxMath<R> Mx;
+  fx_localize(r, sf, kind);
+  const R t = -r.z * Mx::rcp(r.N);  // plane.py:61-77
+  r.x = fma(t, r.L, r.x); r.y = fma(t, r.M, r.y); r.z = fma(t, r.N, r.z);
+  fx_arrive(r, t, sf, md, kind, fma(r.x, r.x, r.y * r.y), att);
+  if (kind & FX_REFLECT) {
+    r.N = -r.N;
+  } else {  // n = (0, 0, 1): T = (u L, u M, sgn(N) root)
+    const R N = r.N;
+    const R root = Mx::sqrt_(fma(md.u2, fma(N, N, R(-1)), R(1)));
+    r.L = md.u * r.L; r.M = md.u * r.M;
+    r.N = (N == R(0)) ? R(0) * root : Mx::copysign_(root, N);
+  }
+  fx_globalize(r, sf, kind);
+}
+
+template <typename R>
+__device__ __forceinline__ void fx_conic(RayState<R>& r, const FxSurf<R>& sf, const FxMedium<R>& md, int kind,
+                                         R& att) {
+  typedef FxMath<R> Mx;
+  fx_localize(r, sf, kind);
+  const bool sphere = (kind & FX_SPHERE) != 0;
+  const R t = fx_conic_t(r.x, r.y, r.z, r.L, r.M, r.N, sf, sphere);
+  r.x = fma(t, r.L, r.x); r.y = fma(t, r.M, r.y); r.z = fma(t, r.N, r.z);
+  const R r2 = fma(r.x, r.x, r.y * r.y);
+  fx_arrive(r, t, sf, md, kind, r2, att);
+  R nx, ny, nz;
+  if (sphere) {
+    nx = r.x * sf.iR; ny = r.y * sf.iR; nz = fma(r.z, sf.iR, R(-1));
+  } else {
+    const R w = fma(-sf.c1, r.z, sf.radius);
+    const R g = Mx::copysign_(Mx::rsqrt(fma(w, w, r2)), sf.radius);
+    nx = r.x * g; ny = r.y * g; nz = -w * g;
+  }
+  const R dot = fma(r.L, nx, fma(r.M, ny, r.N * nz));
+  fx_interact(r, nx, ny, nz, dot, md, kind);
+  fx_globalize(r, sf, kind);
+}
+
+// Even asphere, newton_raphson.py:119-168 + even_asphere.py:82-129.  With s = r^2:
+//   sag = s/(R (1 + q)) + s Q(s),  q = sqrt(1 - (1+k) s / R^2),  Q(s) = sum_i C_i s^i
+//   dz/dx = x (1/(R q) + 2 (Q + s Q')),  f = sag - z,  f' = zx L + zy M - N
+template <typename R>
+__device__ __forceinline__ void fx_even(RayState<R>& r, const FxSurf<R>& sf, const FxMedium<R>& md, int kind,
+                                        const FxInfo& info, const R* coef, bool valid, unsigned long long* resid,
+                                        R& att) {
+  typedef FxMath<R> Mx;
+  fx_localize(r, sf, kind);
+  R t = fx_conic_t(r.x, r.y, r.z, r.L, r.M, r.N, sf, (kind & FX_SPHERE) != 0);
+  const int K = info.K, m = info.ncoef;
+  R xi, yi, zi, zx, zy, fp, r2;
+  for (int j = 0;; ++j) {
+    xi = fma(t, r.L, r.x); yi = fma(t, r.M, r.y); zi = fma(t, r.N, r.z);
+    r2 = fma(xi, xi, yi * yi);
+    R q, iq;
+    Mx::sqrt_pair(fma(-sf.c1iR2, r2, R(1)), q, iq);
+    // Q(s) and Q'(s) by Horner, four coefficients per step (the table is zero-padded to a multiple of 4);
+    // the top block starts from Q = c3, Q' = 0
+    R Q = R(0), Qp = R(0);
+    if (m > 0) {
+      const R* cb = coef + (m - 4);
+      Q = fma(cb[3], r2, cb[2]); Qp = cb[3];
+      Qp = fma(Qp, r2, Q); Q = fma(Q, r2, cb[1]);
+      Qp = fma(Qp, r2, Q); Q = fma(Q, r2, cb[0]);
+      for (int b = m - 8; b >= 0; b -= 4) {
+        cb = coef + b;
+        Qp = fma(Qp, r2, Q); Q = fma(Q, r2, cb[3]);
+        Qp = fma(Qp, r2, Q); Q = fma(Q, r2, cb[2]);
+        Qp = fma(Qp, r2, Q); Q = fma(Q, r2, cb[1]);
+        Qp = fma(Qp, r2, Q); Q = fma(Q, r2, cb[0]);
+      }
+    }
+    const R g = fma(R(2), fma(r2, Qp, Q), sf.iR * iq);
+    zx = xi * g; zy = yi * g;
+    fp = fma(zx, r.L, fma(zy, r.M, -r.N));
+    const bool lastj = (j >= K);
+    if (lastj && resid == nullptr) break;
+    const R f = fma(r2, Q, (r2 * sf.iR) * Mx::rcp(R(1) + q)) - zi;
+    if (resid != nullptr) {  // NaN: the fix-up pass (IEEE) reports it
+      const unsigned long long key = (valid && f == f) ? resid_bits((double)r_abs(f)) : 0ull;
+      report_resid(resid + j, key);
+    }
+    if (lastj) break;
+    const R dfs = (r_abs(fp) > R(1e-14)) ? fp : R(1e-14);
+    t = fma(-f, Mx::rcp(dfs), t);
+  }
+  r.x = xi; r.y = yi; r.z = zi;
+  fx_arrive(r, t, sf, md, kind, r2, att);
+  const R w = Mx::rsqrt(fma(zx, zx, fma(zy, zy, R(1))));
+  fx_interact(r, zx * w, zy * w, -w, fp * w, md, kind);
+  fx_globalize(r, sf, kind);
+}
+
+template <typename R>
+__global__ void __launch_bounds__(OLRT_FX_BLOCK, OLRT_FX_MIN_BLOCKS) trace_fx_kernel(const FwdParams<R> P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int S = P.n_surfaces, W = P.n_wavelengths;
+  R* s_presc = reinterpret_cast<R*>(smem_raw);
+  R* s_coef = s_presc + ((P.presc_stride + 3) & ~3);
+  FxSurf<R>* s_surf = reinterpret_cast<FxSurf<R>*>(s_coef + ((P.presc_stride + 4 * S + 3) & ~3));
+  FxMedium<R>* s_med = reinterpret_cast<FxMedium<R>*>(s_surf + S);
+  FxInfo* s_info = reinterpret_cast<FxInfo*>(s_med + S * W);
+  int32_t* s_ops = reinterpret_cast<int32_t*>(s_info + S);
+  unsigned long long* s_resid = reinterpret_cast<unsigned long long*>(s_ops + ((P.ops_len + 3) & ~3));
+  __shared__ int s_bad, s_nresid;
+
+  for (int q = threadIdx.x; q < P.ops_len; q += blockDim.x) s_ops[q] = P.ops[q];
+  if (threadIdx.x == 0) s_bad = 0;
+  __syncthreads();
+  const bool want_resid = (P.nr_resid != nullptr);
+  if (threadIdx.x < S) {
+    const int k = fk_kind(s_ops, threadIdx.x);
+    s_info[threadIdx.x].kind = k;
+    if (k == KIND_GENERIC) s_bad = 1;
+  }
+  if (threadIdx.x == 0) {
+    int off = 0;
+    for (int s = 0; s < S; ++s) {
+      s_info[s].roff = off;
+      const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
+      if (want_resid && op[OLRT_OP_GEOM] >= OLRT_GEOM_EVEN_ASPHERE) off += op[OLRT_OP_NR_ITERS] + 1;
+    }
+    s_nresid = off;
+  }
+  __syncthreads();
+  if (s_bad) {
+    if (threadIdx.x == 0 && P.status != nullptr) atomicOr(P.status, OLRT_ST_BAD_HINT);
+    return;
+  }
+  const int n_resid = s_nresid;
+  for (int q = threadIdx.x; q < n_resid; q += blockDim.x) s_resid[q] = 0ull;
+  __syncthreads();
+
+  uint32_t status = 0;
+  int cur_p = -1;
+  const long long n_tiles = (P.n_rays + blockDim.x - 1) / blockDim.x;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long base = tile * blockDim.x;
+    const int p = (P.n_presc > 1) ? (int)(base / P.rays_per_presc) : 0;
+    if (p != cur_p) {
+      __syncthreads();
+      const R* src = P.presc + (long long)p * P.presc_stride;
+      for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) s_presc[q] = src[q];
+      cur_p = p;
+      __syncthreads();
+      if (threadIdx.x < S)
+        fx_build_surface<R>(s_ops, s_presc, s_surf, s_med, s_info, s_coef, threadIdx.x, S, W, P.wavelengths,
+                            P.four_pi);
+      __syncthreads();
+    }
+    const long long item = base + threadIdx.x;
+    const bool valid = item < P.n_rays;
+    const long long idx = valid ? item : (P.n_rays - 1);
+
+    RayState<R> r;
+    r.x = P.in[0][idx]; r.y = P.in[1][idx]; r.z = P.in[2][idx];
+    r.L = P.in[3][idx]; r.M = P.in[4][idx]; r.N = P.in[5][idx];
+    r.i = P.in[6][idx];
+    r.opd = (P.opd_in != nullptr) ? P.opd_in[idx] : R(0);
+    int widx = 0;
+    if (W > 1) {
+      const R wl = P.in[7][idx];
+      widx = -1;
+      for (int q = 0; q < W; ++q) if (wl == P.wavelengths[q]) widx = q;
+      if (widx < 0) { status |= OLRT_ST_WAVELENGTH; widx = 0; r.i = R(0) / R(0); }
+    }
+
+    R L0 = r.L, M0 = r.M, N0 = r.N, att = R(0);
+    for (int s = 0; s < S; ++s) {
+      // direction entering the surface: after the loop, the pre-interaction direction at the last surface
+      // (real_rays.py:82-86; the frame of a fast kind has no rotation, so local == global direction)
+      L0 = r.L; M0 = r.M; N0 = r.N;
+      const FxSurf<R>& sf = s_surf[s];
+      const FxMedium<R>& md = s_med[s * W + widx];
+      const FxInfo& info = s_info[s];
+      const int kind = info.kind;
+      switch (kind & 15) {  // warp-uniform
+        case KIND_PLANE: fx_plane<R>(r, sf, md, kind, att); break;
+        case KIND_CONIC: fx_conic<R>(r, sf, md, kind, att); break;
+        default:
+          fx_even<R>(r, sf, md, kind, info, s_coef + info.coef_off, valid,
+                     want_resid ? (s_resid + info.roff) : nullptr, att);
+          break;
+      }
+      const int slot = info.record;
+      if (slot >= 0 && valid && P.record != nullptr) {  // Surface._record, standard_surface.py:266-286
+        R* rec = P.record + (long long)slot * 8 * P.n_rays + idx;
+        rec[0] = r.x; rec[P.n_rays] = r.y; rec[2 * P.n_rays] = r.z;
+        rec[3 * P.n_rays] = r.L; rec[4 * P.n_rays] = r.M; rec[5 * P.n_rays] = r.N;
+        rec[6 * P.n_rays] = fk_intensity(r.i, att); rec[7 * P.n_rays] = r.opd;
+      }
+    }
+    r.i = fk_intensity(r.i, att);
+    if (valid) {
+      P.out[0][idx] = r.x; P.out[1][idx] = r.y; P.out[2][idx] = r.z;
+      P.out[3][idx] = r.L; P.out[4][idx] = r.M; P.out[5][idx] = r.N;
+      P.out[6][idx] = r.i; P.out[7][idx] = r.opd;
+      if (P.dir0 != nullptr) {
+        P.dir0[idx] = L0; P.dir0[P.n_rays + idx] = M0; P.dir0[2 * P.n_rays + idx] = N0;
+      }
+    }
+    if (sizeof(R) == 8 && P.fixup != nullptr) {
+      const bool bad = valid && (nonfinite(r.x) | nonfinite(r.y) | nonfinite(r.z) | nonfinite(r.L) |
+                                 nonfinite(r.M) | nonfinite(r.N) | nonfinite(r.opd) | nonfinite(r.i));
+      const unsigned m = __ballot_sync(0xffffffffu, bad);
+      if (m != 0u) {
+        const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+        unsigned pos = 0;
+        if (lane == leader) pos = atomicAdd(P.fixup, (unsigned)__popc(m));
+        pos = __shfl_sync(0xffffffffu, pos, leader);
+        if (bad) P.fixup[1 + pos + __popc(m & ((1u << lane) - 1u))] = (uint32_t)idx;
+      }
+    }
+  }
+
+  __syncthreads();
+  if (want_resid) {
+    for (int s = 0; s < S; ++s) {
+      const int lo = s_info[s].roff, hi = (s + 1 < S) ? s_info[s + 1].roff : n_resid;
+      for (int q = lo + threadIdx.x; q < hi; q += blockDim.x) {
+        const unsigned long long v = s_resid[q];
+        if (v != 0ull) atomicMax(P.nr_resid + (long long)s * OLRT_RESID_STRIDE + (q - lo), v);
+      }
+    }
+  }
+  status = __reduce_or_sync(0xffffffffu, status);
+  if (P.status != nullptr && status != 0 && (threadIdx.x & 31) == 0) atomicOr(P.status, status);
+}
+
+}  // namespace OLRT_NS

@@ -3,6 +3,9 @@
 #pragma once
 #include "trace_fwd.cuh"
 #include "trace_fk.cuh"
+#ifdef OLRT_FX
+#include "trace_fx.cuh"
+#endif
 #include "trace_bwd.cuh"
 
 namespace OLRT_NS {
@@ -15,8 +18,13 @@ inline int sm_count() {
 }
 
 // block size: 256 unless the prescription batch needs tiles that do not straddle prescriptions
-inline int pick_block(const olrt_sys* sys) {
-  if (sys->n_presc <= 1) return 256;
+inline int pick_block(const olrt_sys* sys, bool fk, bool fx) {
+#ifdef OLRT_FX
+  if (sys->n_presc <= 1 && fx) return OLRT_FX_BLOCK;
+#else
+  (void)fx;
+#endif
+  if (sys->n_presc <= 1) return fk ? OLRT_FK_BLOCK : 256;
   for (int b = 256; b >= 32; b >>= 1)
     if (sys->rays_per_presc % b == 0) return b;
   return 0;
@@ -30,7 +38,8 @@ inline void launch_fixup(const FwdParams<float>&, unsigned, int, size_t, cudaStr
 template <typename R>
 int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
                long long n_rays, const R* const in[8], const R* opd_in, R* const out[8], R* record,
-               R* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, cudaStream_t stream) {
+               R* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags,
+               cudaStream_t stream) {
   FwdParams<R> P;
   for (int q = 0; q < 8; ++q) { P.in[q] = in[q]; P.out[q] = out[q]; }
   P.opd_in = opd_in; P.record = record; P.dir0 = dir0; P.presc = presc; P.ops = ops;
@@ -42,38 +51,64 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
   for (int q = 0; q < OLRT_MAX_WAVELENGTHS; ++q) P.wavelengths[q] = (R)sys->wavelengths[q];
   P.four_pi = (R)(4.0 * 3.141592653589793);
 
-  const int block = pick_block(sys);
+  const bool fk = (sys->kernel_hint & OLRT_HINT_FASTKINDS) != 0;
+#ifdef OLRT_FX
+  const bool fx = fk && !(flags & OLRT_FWD_REPLAY);
+#else
+  const bool fx = false;
+  (void)flags;
+#endif
+  const int block = pick_block(sys, fk, fx);
   if (block == 0) return OLRT_E_ARG;
+  const int resid_words = nr_resid ? sys->nr_resid_words : 0;
   const size_t smem = (size_t)((sys->presc_stride + 1) & ~1) * sizeof(R) +
                       (size_t)((sys->n_surfaces * der_stride(sys->n_wavelengths) + 1) & ~1) * sizeof(R) +
                       (size_t)((sys->ops_len + 1) & ~1) * sizeof(int32_t) +
-                      (size_t)(nr_resid ? sys->nr_resid_words : 0) * sizeof(unsigned long long);
+                      (size_t)resid_words * sizeof(unsigned long long);
   if (smem > 200 * 1024) return OLRT_E_LIMIT;
   if (smem > 48 * 1024) {
     cudaFuncSetAttribute(trace_fwd_kernel<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (sizeof(R) == 8)
       cudaFuncSetAttribute(trace_fwd_kernel<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   }
-  const bool fk = (sys->kernel_hint & OLRT_HINT_FASTKINDS) != 0;
-  if (fk && smem > 48 * 1024)
-    cudaFuncSetAttribute(trace_fk_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  int per_sm = 0;
-  if (fk) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fk_kernel<R>, block, smem);
-  else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fwd_kernel<R, false>, block, smem);
-  if (per_sm < 1) per_sm = 1;
   const long long n_tiles = (n_rays + block - 1) / block;
-  long long grid = (long long)sm_count() * per_sm;
-  if (grid > n_tiles) grid = n_tiles;
   if (P.fixup != nullptr) cudaMemsetAsync(P.fixup, 0, sizeof(uint32_t), stream);
-  if (fk) trace_fk_kernel<R><<<(unsigned)grid, block, smem, stream>>>(P);
-  else trace_fwd_kernel<R, false><<<(unsigned)grid, block, smem, stream>>>(P);
+  int per_sm = 0;
+  if (fx) {
+#ifdef OLRT_FX
+    const size_t xsmem = fx_smem_bytes<R>(sys->presc_stride, sys->n_surfaces, sys->n_wavelengths, sys->ops_len,
+                                          resid_words);
+    if (xsmem > 200 * 1024) return OLRT_E_LIMIT;
+    if (xsmem > 48 * 1024)
+      cudaFuncSetAttribute(trace_fx_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xsmem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fx_kernel<R>, block, xsmem);
+    if (per_sm < 1) per_sm = 1;
+    long long grid = (long long)sm_count() * per_sm;
+    if (grid > n_tiles) grid = n_tiles;
+    trace_fx_kernel<R><<<(unsigned)grid, block, xsmem, stream>>>(P);
+#endif
+  } else if (fk) {
+    if (smem > 48 * 1024)
+      cudaFuncSetAttribute(trace_fk_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fk_kernel<R>, block, smem);
+    if (per_sm < 1) per_sm = 1;
+    long long grid = (long long)sm_count() * per_sm;
+    if (grid > n_tiles) grid = n_tiles;
+    trace_fk_kernel<R><<<(unsigned)grid, block, smem, stream>>>(P);
+  } else {
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fwd_kernel<R, false>, block, smem);
+    if (per_sm < 1) per_sm = 1;
+    long long grid = (long long)sm_count() * per_sm;
+    if (grid > n_tiles) grid = n_tiles;
+    trace_fwd_kernel<R, false><<<(unsigned)grid, block, smem, stream>>>(P);
+  }
   if (cudaGetLastError() != cudaSuccess) return OLRT_E_LAUNCH;
   if (sizeof(R) == 8 && P.fixup != nullptr) {
     // re-trace the listed rays (non-finite results) with IEEE division / sqrt; the count is read on
     // the device, so the grid is fixed: one CTA per SM walks the list
     long long fgrid = sm_count();
     if (fgrid > n_tiles) fgrid = n_tiles;
-    launch_fixup(P, (unsigned)fgrid, block, smem, stream);
+    launch_fixup(P, (unsigned)fgrid, block > 256 ? 256 : block, smem, stream);
     if (cudaGetLastError() != cudaSuccess) return OLRT_E_LAUNCH;
   }
   return OLRT_OK;

@@ -7,8 +7,8 @@
 namespace olrt_strict {
 int fwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, long long n_rays,
             const double* const in[8], const double* opd_in, double* const out[8], double* record,
-            double* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, cudaStream_t stream) {
-  return launch_fwd<double>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, stream);
+            double* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags, cudaStream_t stream) {
+  return launch_fwd<double>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags, stream);
 }
 
 __global__ void selftest_math_kernel(const double* a, const double* b, double* q, double* r, long long n) {

@@ -92,7 +92,8 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
                 fast: bool = False, verify_nr: bool = True, out: torch.Tensor | None = None,
                 max_relaunch: int = 24, read_fixups: bool = True, check_status: bool = True,
                 dir0_out: torch.Tensor | None = None, status_t: torch.Tensor | None = None,
-                nr_floor: bool = False, resid_out: torch.Tensor | None = None) -> TraceResult:
+                nr_floor: bool = False, resid_out: torch.Tensor | None = None,
+                replay: bool = False) -> TraceResult:
     """Trace rays through a packed system on the current CUDA device and stream.
 
     rays_in: sequence of 8 tensors x y z L M N intensity wavelength (1-D, same length, CUDA,
@@ -101,6 +102,8 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
     resid_out: zero-initialised int64 [n_surfaces, RESID_STRIDE] device tensor: the kernel reports its
              per-iteration residual maxima there and this call does NOT read them back (no host sync);
              the caller checks them later with `slice_true_iters` (slices of one batch, optic.py).
+    fast:    tolerance mode (<= 1e-10 relative to the reference, identical masks) instead of bit-faithful;
+             `replay` keeps the reference's operation order even then (A/B measurements; fp32 too).
     nr_floor: this call traces one SLICE of a larger batch: never lower the Newton trip counts below the
              ones in `packed` (another slice may need them), only raise them; the counts this slice alone
              would have needed come back in `TraceResult.nr_true`.
@@ -165,7 +168,7 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
             sys_.presc_stride = int(presc_d.shape[1])
             rc = fn(C.byref(sys_), presc_d.data_ptr(), ops_d.data_ptr(), n, in_arr, _ptr(opd_in),
                     out_arr, _ptr(record), dir0_ptr, _ptr(resid), status_t.data_ptr(), _ptr(fixup),
-                    L.FWD_FAST if fast else 0, stream)
+                    (L.FWD_FAST if fast else 0) | (L.FWD_REPLAY if replay else 0), stream)
             L.check(rc, "olrt_trace_fwd")
             launches += 1
             if resid is None or n == 0 or resid_out is not None:
