@@ -190,7 +190,7 @@ def main():
     out = torch.empty((8, n), dtype=torch.float64, device=dev)
     sums = torch.zeros((nf, _lib.SPOT_SUMS), dtype=torch.float64, device=dev)
 
-    def step_resident(fast=False):
+    def step_resident(fast=True):
         res = fused_trace(packed, ins, out=out, fast=fast)
         spot.spot_sums(out[0], out[1], out[6], nf, npf, out=sums)
         if world > 1:
@@ -231,9 +231,21 @@ def main():
     value = n * S_eff * world / (ms_step * 1e-3)
     rms_resident = spot.spot_stats(sums)["rms"].cpu().tolist()
 
-    # ---- dominant kernel alone (roofline): trace_fwd_kernel<double>, strict build
+    # ---- parity guard on the bench batch itself: the timed (tolerance-mode) result against the strict,
+    # bit-faithful kernel's result for the same rays (the strict kernel is what tests/ pin to the reference bit for bit)
+    strict_out = fused_trace(packed, ins, fast=False).out
+    den = torch.clamp(strict_out.abs(), min=1.0)
+    parity = {"max_rel_err_vs_strict_kernel": float(((out - strict_out).abs() / den).nan_to_num(0.0).max()),
+              "nan_pattern_identical": bool((out.isnan() == strict_out.isnan()).all()),
+              "vignetting_mask_identical": bool(((out[6] == 0) == (strict_out[6] == 0)).all()),
+              "bar": "1e-10 relative, masks identical (BASELINE.json north_star)"}
+    ms_strict = timed(lambda: fused_trace(packed, ins, out=strict_out, fast=False, verify_nr=False, check_status=False),
+                      max(2, args.steps // 2), 3)
+    del strict_out, den
+
+    # ---- dominant kernel alone (roofline): trace_fx_kernel<double>
     def only_trace():
-        fused_trace(packed, ins, out=out, verify_nr=False, check_status=False)
+        fused_trace(packed, ins, out=out, fast=True, verify_nr=False, check_status=False)
     ms_kernel = timed(only_trace, args.steps, 3)
     fl_ray = flops.flops_per_ray(packed, nr_iters)
     by_ray = flops.bytes_per_ray(8, 1)
@@ -260,13 +272,16 @@ def main():
     ach_tf = fl_ray * n / (ms_kernel * 1e-3) / 1e12
     ach_gbs = by_ray * n / (ms_kernel * 1e-3) / 1e9
     roofline = {
-        "kernel": "trace_fk_kernel<double> (strict build, -fmad=false) + its IEEE fix-up pass",
+        "kernel": "trace_fx_kernel<double> (tolerance mode: <= 1e-10 relative, masks identical) + its IEEE fix-up pass",
         "bound": "fp64_fma", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s",
         "frac": ach_tf / fp64_peak, "peak_source": "olrt_fma_peak_f64 measured in this run",
         "flops_per_ray": fl_ray, "bytes_per_ray": by_ray, "nr_iters": nr_iters, "ms_per_launch": ms_kernel,
         "hbm": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
                 "peak_source": hbm_src + " (MEASURED_PEAKS.json hbm_gbs)"},
         "traffic": None,
+        "strict_mode": {"kernel": "trace_fk_kernel<double> (-fmad=false, the reference's operation order, bit-identical)",
+                        "ms_per_launch": ms_strict, "ray_surfaces_per_s": n * S_eff / (ms_strict * 1e-3),
+                        "frac": fl_ray * n / (ms_strict * 1e-3) / 1e12 / fp64_peak},
     }
     tr_path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr_path):
@@ -304,7 +319,8 @@ def main():
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "even-asphere double Gauss (12 intersected surfaces, 4 Newton-Raphson even aspheres), "
                                f"{nf} fields x {npf} random pupil rays per GPU, primary wavelength, fwd trace + RMS spot",
-                   "rays_per_gpu": n, "surfaces": S_eff, "precision": "float64 strict (bit-faithful op order)",
+                   "rays_per_gpu": n, "surfaces": S_eff, "precision": "float64, tolerance mode (<= 1e-10 relative to the reference, identical masks; "
+                                                                  "the bit-identical strict mode is timed in roofline.strict_mode)",
                    "l2": "inputs (2.7 GB) and outputs (3.2 GB) per step far exceed the 126 MB L2; no flush needed",
                    "parallelism": f"rays sharded over {world} GPU(s), spot sums all-reduced"},
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
@@ -312,7 +328,7 @@ def main():
                 "api": "Optic.trace(Hx, Hy, wl, distribution=(Px, Py) pinned host) + spot.rms -> host; the pupil copy is "
                        "streamed in 4 chunks on a side stream and overlaps ray launch + trace"},
         "gpu_launches": launches_per_step * args.steps,
-        "roofline": roofline, "clocks": clocks,
+        "roofline": roofline, "parity_check": parity, "clocks": clocks,
         "rms_spot_mm": rms_resident, "rms_spot_mm_e2e": rms_host.tolist(),
         "extras": extras,
     }
@@ -344,8 +360,8 @@ def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64
     ins64[7] = None
     o64 = torch.empty((8, n), dtype=torch.float64, device=dev)
     fl_ray = flops.flops_per_ray(packed)
-    for name, fast in (("fp64_fast_fwd", True),):
-        ms = timed(lambda: fused_trace(packed, ins64, out=o64, fast=fast, verify_nr=False, check_status=False), args.steps, 3)
+    for name, kw in (("fp64_replay_order_fma_fwd", {"fast": True, "replay": True}),):
+        ms = timed(lambda: fused_trace(packed, ins64, out=o64, verify_nr=False, check_status=False, **kw), args.steps, 3)
         out[name] = {"ray_surfaces_per_s": n * S_eff / (ms * 1e-3), "ms": ms,
                      "frac_fp64_fma_peak": fl_ray * n / (ms * 1e-3) / 1e12 / fp64_peak}
     ins32 = [t.float() if t is not None else None for t in ins64]

@@ -182,7 +182,7 @@ def bench_backward(lens, packed, ins64, timed, args, fp64_peak) -> dict:
 
     def step():
         presc.grad = None
-        out, record, _ = trace_differentiable(pk, presc, rays)
+        out, record, _ = trace_differentiable(pk, presc, rays, fast=True)
         out.backward(gout_w)
 
     ms = timed(step, max(2, args.steps // 2), 3)

@@ -90,7 +90,10 @@ class SurfaceGroup:
         self._surfaces = list(surfaces) if surfaces else []
         self._link()
         self.record = "all"      # "all" | "last" | list of surface indices
-        self.fast_math = False   # True: FMA-contracted fp64 kernel (not bit-faithful)
+        # fp64 mode. True (default): tolerance mode -- the north-star bar, <= 1e-10 relative to the reference with
+        # identical vignetting / TIR masks (reduced-algebra kernel, csrc/trace_fx.cuh). False: strict mode --
+        # the reference's operation order without FMA contraction, bit-identical for + - * / sqrt, ~2x slower.
+        self.fast_math = True
         self._packed_cache = None
         self.forced_nr_iters = None  # {surface index: K}: skip the exit-rule check (sharded batches, parallel.py)
         self.last_trace = None

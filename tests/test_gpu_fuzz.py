@@ -69,3 +69,35 @@ def test_strict_bit_exact_with_dead_rays(lens_name, n):
     rec, ref = rec[:, :, keep], ref[:, :, keep]
     assert np.array_equal(rec[:, 6] == 0, ref[:, 6] == 0)
     assert res.fixups >= int(dead.sum())
+
+
+@pytest.mark.parametrize("lens_name,n", [("CookeTriplet", 200_000), ("DoubleGauss", 100_000),
+                                         ("EvenAsphereDoubleGauss", 100_000), ("AsphericSinglet", 50_000)])
+def test_tolerance_mode_with_dead_rays(lens_name, n):
+    """OLRT_FWD_FAST (reduced-algebra kernel) on the same wild batches. The bar is a tolerance, and these rays
+    are far outside any clear aperture: a ray within rounding of a miss / TIR boundary is ill-conditioned for ANY
+    evaluation order (sqrt of a difference that cancels to ~0), so the test states what it measures:
+      * NaN pattern and vignetting mask identical except for at most 5e-5 of the rays (boundary rays),
+      * every other ray within 1e-10 except at most 1e-4 of them (conditioning), none beyond 1e-6."""
+    lens = getattr(samples, lens_name)()
+    lens.surface_group.surfaces[2].aperture = RadialAperture(r_max=7.5, r_min=0.25)
+    wl = lens.wavelengths
+    packed = pack_surface_group(lens.surface_group.surfaces, wl)
+    rays_in = _wild_rays(n, 12, wl)
+    ora = trace_np.trace_packed(packed, trace_np.Rays(*rays_in))
+    ref = np.array(ora["records"])
+    res = fused_trace(packed, [torch.tensor(rays_in[q], device="cuda") for q in range(8)], fast=True)
+    torch.cuda.synchronize()
+    rec = res.record.cpu().numpy()
+    bad = (np.isnan(rec) != np.isnan(ref)).any(axis=(0, 1)) | ((rec[:, 6] == 0) != (ref[:, 6] == 0)).any(axis=0)
+    assert bad.mean() <= 5e-5, int(bad.sum())
+    rec, ref = rec[:, :, ~bad], ref[:, :, ~bad]
+    m = ~np.isnan(ref)
+    err = np.zeros_like(ref)
+    err[m] = np.abs(rec[m] - ref[m]) / np.maximum(np.abs(ref[m]), 1.0)
+    per_ray = err.max(axis=(0, 1))
+    print(lens_name, "boundary rays", int(bad.sum()), "worst", per_ray.max(), "frac > 1e-10", (per_ray > 1e-10).mean(),
+          "median", np.median(per_ray))
+    assert (per_ray > 1e-10).mean() <= 1e-4, (per_ray > 1e-10).sum()
+    assert per_ray.max() <= 1e-6, per_ray.max()
+    assert res.nr_iters == ora["nr_iters"]
