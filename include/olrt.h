@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define OLRT_ABI_VERSION 2
+#define OLRT_ABI_VERSION 3
 
 #define OLRT_MAX_SURFACES 64    /* intersected surfaces per system (object surface excluded) */
 #define OLRT_MAX_WAVELENGTHS 8  /* distinct wavelengths per launch */
@@ -215,6 +215,42 @@ int olrt_generate_rays_f64(const double* Px, const double* Py, int64_t n_pupil, 
 int olrt_generate_rays_f32(const double* Px, const double* Py, int64_t n_pupil, const double* field_xy,
                            int32_t n_fields, double EPD, double EPL, double z_start, double wavelength,
                            float* const out[8], void* stream);
+
+/* Fused ray launch + trace + spot epilogue ("pupil mode"): what RealRayTracer.trace does per call
+ * (raytrace/real_ray_tracer.py:61-82: generate the rays of every field from one pupil grid, then
+ * SurfaceGroup.trace) followed, optionally, by the sums RayOperand.rms_spot_size / SpotDiagram need
+ * (optimization/operand/ray.py:336-340, analysis/spot_diagram.py:317-357) -- in ONE kernel: the launched rays
+ * never exist in HBM, and with out == NULL nothing per ray is written at all (merit-function evaluation).
+ * One call traces pupil points [p_lo, p_lo + p_len) of EVERY field, so a host pupil grid can be streamed in
+ * chunks; ray (field f, pupil point p) lives at index f * n_pupil + p of the output arrays, the field-major
+ * order of real_ray_tracer.py:67-77, and belongs to spot group f.
+ * Implemented by the tolerance-mode kernel for lenses of planes / conics / even aspheres (flags must contain
+ * OLRT_FWD_FAST for fp64; olrt_sys.kernel_hint & OLRT_HINT_FASTKINDS; one wavelength, one prescription, no
+ * per-surface records): anything else returns OLRT_E_UNSUPPORTED and the caller uses
+ * olrt_generate_rays_* + olrt_trace_fwd_* + olrt_spot_sums_*.                                              */
+typedef struct olrt_pupil {
+  const double* Px;        /* [n_pupil] normalised pupil coordinates (device) */
+  const double* Py;
+  const double* field_xy;  /* [n_fields][2] (device), as for olrt_generate_rays_* */
+  int64_t n_pupil;         /* pupil points per field */
+  int64_t p_lo, p_len;     /* the pupil range this call traces */
+  int32_t n_fields;
+  int32_t reserved0;
+  double EPD, EPL, z_start, wavelength;
+} olrt_pupil;
+/*  out        NULL, or [8] device ptrs to arrays of n_fields * n_pupil (x y z L M N intensity opd)
+ *  dir0       NULL or [3][n_fields * n_pupil]
+ *  spot_sums  NULL or [n_fields][OLRT_SPOT_SUMS], zeroed by the caller before the first chunk; columns as for
+ *             olrt_spot_sums_* except 8, 9 (the caller knows the shift); spot_shift [n_fields][2] is required
+ *  spot_flags OLRT_SPOT_*; flags OLRT_FWD_*; the other arguments as for olrt_trace_fwd_*                    */
+int olrt_trace_pupil_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, const olrt_pupil* pupil,
+                         double* const out[8], double* dir0, unsigned long long* nr_resid, uint32_t* status,
+                         uint32_t* fixup, double* spot_sums, const double* spot_shift, int spot_flags, int flags,
+                         void* stream);
+int olrt_trace_pupil_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, const olrt_pupil* pupil,
+                         float* const out[8], float* dir0, unsigned long long* nr_resid, uint32_t* status,
+                         uint32_t* fixup, double* spot_sums, const double* spot_shift, int spot_flags, int flags,
+                         void* stream);
 
 /* Self-test of the kernels' own IEEE division / square-root sequences (csrc/math64.cuh):
  * quot[i] = a[i] / b[i], root[i] = sqrt(a[i]) as the trace kernels compute them; the caller compares

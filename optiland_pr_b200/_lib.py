@@ -12,7 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("OLRT_LIB") or os.path.join(_HERE, "libolrt.so")  # OLRT_LIB: A/B builds only
 
-OLRT_ABI_VERSION = 2
+OLRT_ABI_VERSION = 3
 MAX_SURFACES = 64
 MAX_WAVELENGTHS = 8
 MAX_NR_ITERS = 128
@@ -56,6 +56,17 @@ class OlrtSys(C.Structure):
     ]
 
 
+class OlrtPupil(C.Structure):
+    """struct olrt_pupil (include/olrt.h): in-kernel ray launch for olrt_trace_pupil_*."""
+
+    _fields_ = [
+        ("Px", C.c_void_p), ("Py", C.c_void_p), ("field_xy", C.c_void_p),
+        ("n_pupil", C.c_int64), ("p_lo", C.c_int64), ("p_len", C.c_int64),
+        ("n_fields", C.c_int32), ("reserved0", C.c_int32),
+        ("EPD", C.c_double), ("EPL", C.c_double), ("z_start", C.c_double), ("wavelength", C.c_double),
+    ]
+
+
 PtrArray8 = C.c_void_p * 8
 
 # every symbol include/olrt.h declares (tests/test_abi.py checks the header against this list)
@@ -67,6 +78,7 @@ EXPORTS = [
     "olrt_fma_peak_f64", "olrt_fma_peak_f32",
     "olrt_selftest_math_f64",
     "olrt_generate_rays_f64", "olrt_generate_rays_f32",
+    "olrt_trace_pupil_f64", "olrt_trace_pupil_f32",
 ]
 
 _lib = None
@@ -109,6 +121,11 @@ def load():
         f = getattr(lib, f"olrt_generate_rays_{suf}")
         f.restype = C.c_int
         f.argtypes = [v, v, C.c_int64, v, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double, PtrArray8, v]
+    for suf in ("f64", "f32"):
+        f = getattr(lib, f"olrt_trace_pupil_{suf}")
+        f.restype = C.c_int
+        f.argtypes = [C.POINTER(OlrtSys), v, v, C.POINTER(OlrtPupil), C.POINTER(PtrArray8), v, v, v, v, v, v,
+                      C.c_int, C.c_int, v]
     lib.olrt_selftest_math_f64.restype = C.c_int
     lib.olrt_selftest_math_f64.argtypes = [v, v, v, v, C.c_int64, v]
     if lib.olrt_version() != OLRT_ABI_VERSION:

@@ -14,6 +14,16 @@ OLRT_DECL_FWD(olrt_strict, f64, double)
 OLRT_DECL_FWD(olrt_fast, f64, double)
 OLRT_DECL_FWD(olrt_fast, f32, float)
 
+#define OLRT_DECL_PUPIL(SUF, R)                                                                          \
+  namespace olrt_fast {                                                                                  \
+  int pupil_##SUF(const olrt_sys* sys, const R* presc, const int32_t* ops, const olrt_pupil* pupil,      \
+                  R* const out[8], R* dir0, unsigned long long* nr_resid, uint32_t* status,              \
+                  uint32_t* fixup, double* spot, const double* spot_shift, int spot_flags, int flags,    \
+                  cudaStream_t stream);                                                                  \
+  }
+OLRT_DECL_PUPIL(f64, double)
+OLRT_DECL_PUPIL(f32, float)
+
 namespace olrt_strict {
 int selftest_math(const double* a, const double* b, double* q, double* r, long long n, cudaStream_t stream);
 }

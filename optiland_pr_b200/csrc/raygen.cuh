@@ -1,0 +1,41 @@
+// raygen.cuh -- one launched ray, shared by the ray-launch kernel (trace_strict.cu) and the trace kernels'
+// pupil mode (trace_fx.cuh, trace_fwd.cuh fix-up pass):
+//   RayGenerator.generate_rays        optiland/rays/ray_generator.py:28-106
+//   AngleField.get_ray_origins        optiland/fields/field_types.py:139-169   (object at infinity, vx = vy = 1)
+// Written with the explicitly rounded intrinsics (never contracted into FMAs, IEEE division and square
+// root), so every translation unit produces the same bits as the reference's NumPy expression.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace OLRT_NS {
+
+struct GenParams {
+  const double* px;   // [n_pupil] normalised pupil coordinates (device); nullptr = rays come from FwdParams::in
+  const double* py;
+  const double* fxy;  // [n_fields][2]: -tan(radians(max_field H)) (offset + EPL), x then y
+  long long n_pupil;  // pupil points per field = distance between fields in the output arrays
+  long long p_lo;     // this launch traces pupil points [p_lo, p_lo + len) of every field
+  long long len;
+  int n_fields;
+  double EPD, EPL, z_start, wavelength;
+};
+
+// ray (field f, pupil point p): origin on the launch plane, direction towards the pupil point
+__device__ __forceinline__ void gen_ray(const GenParams& G, int f, long long p, double& x0, double& y0,
+                                        double& L, double& M, double& N) {
+  const double px = G.px[p], py = G.py[p];
+  const double xf = G.fxy[2 * f], yf = G.fxy[2 * f + 1];
+  const double x1 = __dmul_rn(__dmul_rn(px, G.EPD), 0.5);   // Px * EPD * vx / 2
+  const double y1 = __dmul_rn(__dmul_rn(py, G.EPD), 0.5);
+  x0 = __dadd_rn(x1, xf);
+  y0 = __dadd_rn(y1, yf);
+  const double dx = __dadd_rn(x1, -x0), dy = __dadd_rn(y1, -y0), dz = __dadd_rn(G.EPL, -G.z_start);
+  double mag = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
+  const bool is_zero = mag < 1e-9;
+  if (is_zero) mag = 1.0;
+  L = is_zero ? 0.0 : __ddiv_rn(dx, mag);
+  M = is_zero ? 0.0 : __ddiv_rn(dy, mag);
+  N = is_zero ? 1.0 : __ddiv_rn(dz, mag);
+}
+
+}  // namespace OLRT_NS

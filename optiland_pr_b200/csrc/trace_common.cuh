@@ -13,6 +13,7 @@
 #include <stdint.h>
 #include "../../include/olrt.h"
 #include "math64.cuh"
+#include "raygen.cuh"
 
 namespace OLRT_NS {
 

@@ -16,6 +16,26 @@ int fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, long lo
             float* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags, cudaStream_t stream) {
   return launch_fwd<float>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags, stream);
 }
+static GenParams to_gen(const olrt_pupil* q) {
+  GenParams g;
+  g.px = q->Px; g.py = q->Py; g.fxy = q->field_xy; g.n_pupil = q->n_pupil; g.p_lo = q->p_lo; g.len = q->p_len;
+  g.n_fields = q->n_fields; g.EPD = q->EPD; g.EPL = q->EPL; g.z_start = q->z_start; g.wavelength = q->wavelength;
+  return g;
+}
+int pupil_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, const olrt_pupil* pupil,
+              double* const out[8], double* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup,
+              double* spot, const double* spot_shift, int spot_flags, int flags, cudaStream_t stream) {
+  const GenParams g = to_gen(pupil);
+  return launch_fwd<double>(sys, presc, ops, g.len * g.n_fields, nullptr, nullptr, out, nullptr, dir0, nr_resid, status,
+                            fixup, flags, stream, &g, spot, spot_shift, spot_flags);
+}
+int pupil_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, const olrt_pupil* pupil,
+              float* const out[8], float* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup,
+              double* spot, const double* spot_shift, int spot_flags, int flags, cudaStream_t stream) {
+  const GenParams g = to_gen(pupil);
+  return launch_fwd<float>(sys, presc, ops, g.len * g.n_fields, nullptr, nullptr, out, nullptr, dir0, nr_resid, status,
+                           fixup, flags, stream, &g, spot, spot_shift, spot_flags);
+}
 int bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, long long n_rays,
             const double* const in[8], const double* record, const double* const gout[8], const double* grecord,
             double* const gin[8], double* gpresc, uint32_t* status, cudaStream_t stream) {

@@ -26,6 +26,13 @@ struct FwdParams {
   int n_surfaces, n_wavelengths, n_presc, presc_stride, ops_len, n_record;
   R wavelengths[OLRT_MAX_WAVELENGTHS];
   R four_pi;  // 4*pi rounded once on the host like the reference's Python float product
+  // length of the out / dir0 / record arrays (ray idx lives at [q][idx], stride n_total); == n_rays unless the
+  // rays are launched in the kernel (pupil mode), where one launch covers a pupil range of every field
+  long long n_total;
+  GenParams gen;             // gen.px != nullptr: pupil mode (olrt_trace_pupil_*), `in` is not read
+  double* spot;              // fused spot epilogue: [n_groups][OLRT_SPOT_SUMS] sums, group = field (pupil mode)
+  const double* spot_shift;  // [n_groups][2] shift the sums are taken about (required with spot)
+  int spot_flags;            // OLRT_SPOT_*
 };
 
 // derived per-surface constants in shared memory: c1, R2, twoR, rR2, then u[W], u2[W], alpha[W]
@@ -255,12 +262,27 @@ __device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r,
     }
     const int slot = sp.op[OLRT_OP_RECORD];
     if (slot >= 0 && valid && P.record != nullptr) {  // Surface._record, standard_surface.py:266-286
-      R* rec = P.record + (long long)slot * 8 * P.n_rays + idx;
-      rec[0] = r.x; rec[P.n_rays] = r.y; rec[2 * P.n_rays] = r.z;
-      rec[3 * P.n_rays] = r.L; rec[4 * P.n_rays] = r.M; rec[5 * P.n_rays] = r.N;
-      rec[6 * P.n_rays] = r.i; rec[7 * P.n_rays] = r.opd;
+      const long long NT = P.n_total;
+      R* rec = P.record + (long long)slot * 8 * NT + idx;
+      rec[0] = r.x; rec[NT] = r.y; rec[2 * NT] = r.z;
+      rec[3 * NT] = r.L; rec[4 * NT] = r.M; rec[5 * NT] = r.N;
+      rec[6 * NT] = r.i; rec[7 * NT] = r.opd;
     }
   }
+}
+
+// one ray's contribution to the fused spot sums, straight to global memory (fix-up pass: a handful of rays)
+template <typename R>
+__device__ __forceinline__ void spot_add_one(const FwdParams<R>& P, int g, const RayState<R>& r) {
+  const double iv = (double)r.i;
+  if ((P.spot_flags & OLRT_SPOT_VALID_ONLY) && !(iv > 0.0)) return;
+  const double dx = (double)r.x - P.spot_shift[2 * g], dy = (double)r.y - P.spot_shift[2 * g + 1];
+  double* o = P.spot + (long long)g * OLRT_SPOT_SUMS;
+  atomicAdd(o + 0, 1.0); atomicAdd(o + 1, dx); atomicAdd(o + 2, dy);
+  atomicAdd(o + 3, dx * dx); atomicAdd(o + 4, dy * dy); atomicAdd(o + 6, iv);
+  const double r2 = dx * dx + dy * dy;
+  const unsigned long long key = (r2 != r2) ? 0x7ff8000000000000ULL : (unsigned long long)__double_as_longlong(r2);
+  atomicMax(reinterpret_cast<unsigned long long*>(o + 5), key);
 }
 
 // FIX = false: the main pass over every ray (tiles of blockDim rays, grid-stride).
@@ -325,13 +347,21 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
     if (FIX) presc = P.presc + ((P.n_presc > 1) ? (idx / P.rays_per_presc) : 0) * P.presc_stride;
 
     RayState<R> r;
-    r.x = P.in[0][idx]; r.y = P.in[1][idx]; r.z = P.in[2][idx];
-    r.L = P.in[3][idx]; r.M = P.in[4][idx]; r.N = P.in[5][idx];
-    r.i = P.in[6][idx];
-    r.opd = (P.opd_in != nullptr) ? P.opd_in[idx] : R(0);
     int widx = 0;
     R wl = P.wavelengths[0];
-    if (W > 1) {
+    if (FIX && P.gen.px != nullptr) {  // pupil mode: launch the listed ray again (idx = f * n_pupil + p)
+      const int f = (int)(idx / P.gen.n_pupil);
+      double x0, y0, dL, dM, dN;
+      gen_ray(P.gen, f, idx - (long long)f * P.gen.n_pupil, x0, y0, dL, dM, dN);
+      r.x = (R)x0; r.y = (R)y0; r.z = (R)P.gen.z_start; r.L = (R)dL; r.M = (R)dM; r.N = (R)dN;
+      r.i = R(1); r.opd = R(0);
+    } else {
+      r.x = P.in[0][idx]; r.y = P.in[1][idx]; r.z = P.in[2][idx];
+      r.L = P.in[3][idx]; r.M = P.in[4][idx]; r.N = P.in[5][idx];
+      r.i = P.in[6][idx];
+      r.opd = (P.opd_in != nullptr) ? P.opd_in[idx] : R(0);
+    }
+    if (W > 1 && !(FIX && P.gen.px != nullptr)) {
       wl = P.in[7][idx];
       widx = -1;
       for (int q = 0; q < W; ++q) if (wl == P.wavelengths[q]) widx = q;
@@ -342,12 +372,16 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
     trace_ray<R, FIX>(P, r, s_ops, presc, s_der, s_kind, s_roff, s_resid, widx, wl, valid, idx, status,
                       L0, M0, N0);
     if (valid) {
-      P.out[0][idx] = r.x; P.out[1][idx] = r.y; P.out[2][idx] = r.z;
-      P.out[3][idx] = r.L; P.out[4][idx] = r.M; P.out[5][idx] = r.N;
-      P.out[6][idx] = r.i; P.out[7][idx] = r.opd;
-      if (P.dir0 != nullptr) {
-        P.dir0[idx] = L0; P.dir0[P.n_rays + idx] = M0; P.dir0[2 * P.n_rays + idx] = N0;
+      if (P.out[0] != nullptr) {
+        P.out[0][idx] = r.x; P.out[1][idx] = r.y; P.out[2][idx] = r.z;
+        P.out[3][idx] = r.L; P.out[4][idx] = r.M; P.out[5][idx] = r.N;
+        P.out[6][idx] = r.i; P.out[7][idx] = r.opd;
       }
+      if (P.dir0 != nullptr) {
+        P.dir0[idx] = L0; P.dir0[P.n_total + idx] = M0; P.dir0[2 * P.n_total + idx] = N0;
+      }
+      if (FIX && P.spot != nullptr)  // the main pass left this ray out of the fused spot sums
+        spot_add_one(P, (P.gen.px != nullptr) ? (int)(idx / P.gen.n_pupil) : (int)(idx / P.rays_per_presc), r);
     }
     if (!FIX && sizeof(R) == 8 && P.fixup != nullptr) {
       // anything non-finite (a real miss / TIR, or a value outside the fast path's domain): list the

@@ -308,6 +308,26 @@ __device__ __forceinline__ void fx_even(RayState<R>& r, const FxSurf<R>& sf, con
   fx_globalize(r, sf, kind);
 }
 
+// warp-reduce one thread's spot sums and add them to the group's row (one set of atomics per warp; a CTA
+// flushes once per field it visits). Column layout: include/olrt.h, olrt_spot_sums_*.
+__device__ __forceinline__ void fx_spot_flush(double* spot, int g, double cnt, double sx, double sy, double sxx,
+                                              double syy, double si, double mx, bool mnan) {
+  double v[6] = {cnt, sx, sy, sxx, syy, si};
+#pragma unroll
+  for (int k = 0; k < 6; ++k)
+    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_down_sync(0xffffffffu, v[k], o);
+  const unsigned nanmask = __ballot_sync(0xffffffffu, mnan);
+  double wm = mnan ? 0.0 : mx;
+  for (int o = 16; o > 0; o >>= 1) wm = fmax(wm, __shfl_down_sync(0xffffffffu, wm, o));
+  if ((threadIdx.x & 31) == 0) {
+    double* o = spot + (long long)g * OLRT_SPOT_SUMS;
+    atomicAdd(o + 0, v[0]); atomicAdd(o + 1, v[1]); atomicAdd(o + 2, v[2]);
+    atomicAdd(o + 3, v[3]); atomicAdd(o + 4, v[4]); atomicAdd(o + 6, v[5]);
+    const unsigned long long key = nanmask ? 0x7ff8000000000000ULL : (unsigned long long)__double_as_longlong(wm);
+    atomicMax(reinterpret_cast<unsigned long long*>(o + 5), key);
+  }
+}
+
 template <typename R>
 __global__ void __launch_bounds__(OLRT_FX_BLOCK, OLRT_FX_MIN_BLOCKS) trace_fx_kernel(const FwdParams<R> P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -350,7 +370,17 @@ __global__ void __launch_bounds__(OLRT_FX_BLOCK, OLRT_FX_MIN_BLOCKS) trace_fx_ke
 
   uint32_t status = 0;
   int cur_p = -1;
-  const long long n_tiles = (P.n_rays + blockDim.x - 1) / blockDim.x;
+  // pupil mode (olrt_trace_pupil_*): the launch covers pupil points [p_lo, p_lo + len) of every field; a tile
+  // never straddles two fields, ray (f, p) lives at index f * n_pupil + p of the output arrays
+  const bool pupil = (P.gen.px != nullptr);
+  const long long tpf = pupil ? (P.gen.len + blockDim.x - 1) / blockDim.x : 0;  // tiles per field
+  const long long n_tiles = pupil ? tpf * P.gen.n_fields : (P.n_rays + blockDim.x - 1) / blockDim.x;
+  const long long NT = P.n_total;
+  // fused spot epilogue: per-thread sums for the current group, flushed when the group changes
+  const bool want_spot = (P.spot != nullptr);
+  int sp_g = -1;
+  double sp_cnt = 0, sp_x = 0, sp_y = 0, sp_xx = 0, sp_yy = 0, sp_i = 0, sp_max = 0, sp_sx = 0, sp_sy = 0;
+  bool sp_nan = false;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long base = tile * blockDim.x;
     const int p = (P.n_presc > 1) ? (int)(base / P.rays_per_presc) : 0;
@@ -365,21 +395,36 @@ __global__ void __launch_bounds__(OLRT_FX_BLOCK, OLRT_FX_MIN_BLOCKS) trace_fx_ke
                             P.four_pi);
       __syncthreads();
     }
-    const long long item = base + threadIdx.x;
-    const bool valid = item < P.n_rays;
-    const long long idx = valid ? item : (P.n_rays - 1);
-
     RayState<R> r;
-    r.x = P.in[0][idx]; r.y = P.in[1][idx]; r.z = P.in[2][idx];
-    r.L = P.in[3][idx]; r.M = P.in[4][idx]; r.N = P.in[5][idx];
-    r.i = P.in[6][idx];
-    r.opd = (P.opd_in != nullptr) ? P.opd_in[idx] : R(0);
+    bool valid;
+    long long idx;
+    int group = 0;
     int widx = 0;
-    if (W > 1) {
-      const R wl = P.in[7][idx];
-      widx = -1;
-      for (int q = 0; q < W; ++q) if (wl == P.wavelengths[q]) widx = q;
-      if (widx < 0) { status |= OLRT_ST_WAVELENGTH; widx = 0; r.i = R(0) / R(0); }
+    if (pupil) {
+      const int f = (int)(tile / tpf);
+      const long long pp = (tile - (long long)f * tpf) * blockDim.x + threadIdx.x;
+      valid = pp < P.gen.len;
+      const long long pq = P.gen.p_lo + (valid ? pp : (P.gen.len - 1));
+      idx = (long long)f * P.gen.n_pupil + pq;
+      group = f;
+      double x0, y0, dL, dM, dN;
+      gen_ray(P.gen, f, pq, x0, y0, dL, dM, dN);
+      r.x = (R)x0; r.y = (R)y0; r.z = (R)P.gen.z_start; r.L = (R)dL; r.M = (R)dM; r.N = (R)dN;
+      r.i = R(1); r.opd = R(0);
+    } else {
+      const long long item = base + threadIdx.x;
+      valid = item < P.n_rays;
+      idx = valid ? item : (P.n_rays - 1);
+      r.x = P.in[0][idx]; r.y = P.in[1][idx]; r.z = P.in[2][idx];
+      r.L = P.in[3][idx]; r.M = P.in[4][idx]; r.N = P.in[5][idx];
+      r.i = P.in[6][idx];
+      r.opd = (P.opd_in != nullptr) ? P.opd_in[idx] : R(0);
+      if (W > 1) {
+        const R wl = P.in[7][idx];
+        widx = -1;
+        for (int q = 0; q < W; ++q) if (wl == P.wavelengths[q]) widx = q;
+        if (widx < 0) { status |= OLRT_ST_WAVELENGTH; widx = 0; r.i = R(0) / R(0); }
+      }
     }
 
     R L0 = r.L, M0 = r.M, N0 = r.N, att = R(0);
@@ -401,24 +446,27 @@ __global__ void __launch_bounds__(OLRT_FX_BLOCK, OLRT_FX_MIN_BLOCKS) trace_fx_ke
       }
       const int slot = info.record;
       if (slot >= 0 && valid && P.record != nullptr) {  // Surface._record, standard_surface.py:266-286
-        R* rec = P.record + (long long)slot * 8 * P.n_rays + idx;
-        rec[0] = r.x; rec[P.n_rays] = r.y; rec[2 * P.n_rays] = r.z;
-        rec[3 * P.n_rays] = r.L; rec[4 * P.n_rays] = r.M; rec[5 * P.n_rays] = r.N;
-        rec[6 * P.n_rays] = fk_intensity(r.i, att); rec[7 * P.n_rays] = r.opd;
+        R* rec = P.record + (long long)slot * 8 * NT + idx;
+        rec[0] = r.x; rec[NT] = r.y; rec[2 * NT] = r.z;
+        rec[3 * NT] = r.L; rec[4 * NT] = r.M; rec[5 * NT] = r.N;
+        rec[6 * NT] = fk_intensity(r.i, att); rec[7 * NT] = r.opd;
       }
     }
     r.i = fk_intensity(r.i, att);
     if (valid) {
-      P.out[0][idx] = r.x; P.out[1][idx] = r.y; P.out[2][idx] = r.z;
-      P.out[3][idx] = r.L; P.out[4][idx] = r.M; P.out[5][idx] = r.N;
-      P.out[6][idx] = r.i; P.out[7][idx] = r.opd;
+      if (P.out[0] != nullptr) {
+        P.out[0][idx] = r.x; P.out[1][idx] = r.y; P.out[2][idx] = r.z;
+        P.out[3][idx] = r.L; P.out[4][idx] = r.M; P.out[5][idx] = r.N;
+        P.out[6][idx] = r.i; P.out[7][idx] = r.opd;
+      }
       if (P.dir0 != nullptr) {
-        P.dir0[idx] = L0; P.dir0[P.n_rays + idx] = M0; P.dir0[2 * P.n_rays + idx] = N0;
+        P.dir0[idx] = L0; P.dir0[NT + idx] = M0; P.dir0[2 * NT + idx] = N0;
       }
     }
+    bool bad = false;
     if (sizeof(R) == 8 && P.fixup != nullptr) {
-      const bool bad = valid && (nonfinite(r.x) | nonfinite(r.y) | nonfinite(r.z) | nonfinite(r.L) |
-                                 nonfinite(r.M) | nonfinite(r.N) | nonfinite(r.opd) | nonfinite(r.i));
+      bad = valid && (nonfinite(r.x) | nonfinite(r.y) | nonfinite(r.z) | nonfinite(r.L) |
+                      nonfinite(r.M) | nonfinite(r.N) | nonfinite(r.opd) | nonfinite(r.i));
       const unsigned m = __ballot_sync(0xffffffffu, bad);
       if (m != 0u) {
         const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
@@ -428,7 +476,26 @@ __global__ void __launch_bounds__(OLRT_FX_BLOCK, OLRT_FX_MIN_BLOCKS) trace_fx_ke
         if (bad) P.fixup[1 + pos + __popc(m & ((1u << lane) - 1u))] = (uint32_t)idx;
       }
     }
+    if (want_spot) {  // RayOperand.rms_spot_size / SpotDiagram sums, ray.py:336-340, spot_diagram.py:317-357
+      if (group != sp_g) {  // warp-uniform (a tile belongs to one field)
+        if (sp_g >= 0) fx_spot_flush(P.spot, sp_g, sp_cnt, sp_x, sp_y, sp_xx, sp_yy, sp_i, sp_max, sp_nan);
+        sp_g = group;
+        sp_cnt = sp_x = sp_y = sp_xx = sp_yy = sp_i = sp_max = 0.0;
+        sp_nan = false;
+        sp_sx = P.spot_shift[2 * group]; sp_sy = P.spot_shift[2 * group + 1];
+      }
+      const double iv = (double)r.i;
+      // a ray on the fix-up list is added by the fix-up pass with its IEEE result
+      if (valid && !bad && !((P.spot_flags & OLRT_SPOT_VALID_ONLY) && !(iv > 0.0))) {
+        const double dx = (double)r.x - sp_sx, dy = (double)r.y - sp_sy;
+        sp_cnt += 1.0; sp_x += dx; sp_y += dy; sp_xx = fma(dx, dx, sp_xx); sp_yy = fma(dy, dy, sp_yy); sp_i += iv;
+        const double r2 = fma(dx, dx, dy * dy);
+        if (r2 != r2) sp_nan = true;
+        sp_max = fmax(sp_max, r2);
+      }
+    }
   }
+  if (want_spot && sp_g >= 0) fx_spot_flush(P.spot, sp_g, sp_cnt, sp_x, sp_y, sp_xx, sp_yy, sp_i, sp_max, sp_nan);
 
   __syncthreads();
   if (want_resid) {

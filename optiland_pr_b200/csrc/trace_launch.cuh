@@ -39,9 +39,10 @@ template <typename R>
 int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
                long long n_rays, const R* const in[8], const R* opd_in, R* const out[8], R* record,
                R* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags,
-               cudaStream_t stream) {
+               cudaStream_t stream, const GenParams* gen = nullptr, double* spot = nullptr,
+               const double* spot_shift = nullptr, int spot_flags = 0) {
   FwdParams<R> P;
-  for (int q = 0; q < 8; ++q) { P.in[q] = in[q]; P.out[q] = out[q]; }
+  for (int q = 0; q < 8; ++q) { P.in[q] = in ? in[q] : nullptr; P.out[q] = out ? out[q] : nullptr; }
   P.opd_in = opd_in; P.record = record; P.dir0 = dir0; P.presc = presc; P.ops = ops;
   P.nr_resid = nr_resid; P.status = status; P.n_rays = n_rays;
   P.fixup = (sizeof(R) == 8) ? fixup : nullptr;
@@ -50,6 +51,13 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
   P.presc_stride = sys->presc_stride; P.ops_len = sys->ops_len; P.n_record = sys->n_record;
   for (int q = 0; q < OLRT_MAX_WAVELENGTHS; ++q) P.wavelengths[q] = (R)sys->wavelengths[q];
   P.four_pi = (R)(4.0 * 3.141592653589793);
+  P.n_total = n_rays;
+  P.gen.px = nullptr;
+  if (gen != nullptr) {  // pupil mode: n_rays = rays of this launch, arrays span every field's full pupil grid
+    P.gen = *gen;
+    P.n_total = gen->n_pupil * gen->n_fields;
+  }
+  P.spot = spot; P.spot_shift = spot_shift; P.spot_flags = spot_flags;
 
   const bool fk = (sys->kernel_hint & OLRT_HINT_FASTKINDS) != 0;
 #ifdef OLRT_FX
@@ -71,7 +79,12 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
     if (sizeof(R) == 8)
       cudaFuncSetAttribute(trace_fwd_kernel<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   }
-  const long long n_tiles = (n_rays + block - 1) / block;
+  long long n_tiles = (n_rays + block - 1) / block;
+  if (gen != nullptr) {
+    if (!fx) return OLRT_E_UNSUPPORTED;  // in-kernel ray launch exists in the reduced-algebra kernel only
+    n_tiles = ((gen->len + block - 1) / block) * gen->n_fields;
+  }
+  if (spot != nullptr && (!fx || gen == nullptr || spot_shift == nullptr)) return OLRT_E_UNSUPPORTED;
   if (P.fixup != nullptr) cudaMemsetAsync(P.fixup, 0, sizeof(uint32_t), stream);
   int per_sm = 0;
   if (fx) {

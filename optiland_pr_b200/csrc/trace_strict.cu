@@ -35,21 +35,16 @@ __global__ void __launch_bounds__(256) generate_rays_kernel(const double* __rest
                                                             double wavelength, R* ox, R* oy, R* oz, R* oL, R* oM,
                                                             R* oN, R* oi, R* ow) {
   const long long total = n_pupil * n_fields;
+  GenParams G;
+  G.px = Px; G.py = Py; G.fxy = field_xy; G.n_pupil = n_pupil; G.p_lo = 0; G.len = n_pupil; G.n_fields = n_fields;
+  G.EPD = EPD; G.EPL = EPL; G.z_start = z_start; G.wavelength = wavelength;
   for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < total;
        r += (long long)gridDim.x * blockDim.x) {
     const long long f = r / n_pupil, p = r - f * n_pupil;
-    const double px = Px[p], py = Py[p];
-    const double xf = field_xy[2 * f], yf = field_xy[2 * f + 1];
-    const double x1 = px * EPD / 2.0, y1 = py * EPD / 2.0;   // Px * EPD * vx / 2, vx = 1
-    const double x0 = x1 + xf, y0 = y1 + yf;                 // Px * EPD / 2 * vx + x
-    const double dx = x1 - x0, dy = y1 - y0, dz = EPL - z_start;
-    double mag = sqrt(dx * dx + dy * dy + dz * dz);
-    const bool is_zero = mag < 1e-9;
-    if (is_zero) mag = 1.0;
+    double x0, y0, dL, dM, dN;
+    gen_ray(G, (int)f, p, x0, y0, dL, dM, dN);
     ox[r] = (R)x0; oy[r] = (R)y0; oz[r] = (R)z_start;
-    oL[r] = (R)(is_zero ? 0.0 : dx / mag);
-    oM[r] = (R)(is_zero ? 0.0 : dy / mag);
-    oN[r] = (R)(is_zero ? 1.0 : dz / mag);
+    oL[r] = (R)dL; oM[r] = (R)dM; oN[r] = (R)dN;
     oi[r] = (R)1.0;
     if (ow != nullptr) ow[r] = (R)wavelength;
   }

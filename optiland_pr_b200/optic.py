@@ -159,9 +159,12 @@ class Optic:
         return RealRays(c(x0), c(y0), c(z0), c(L), c(M), c(N), c(torch.ones_like(x0)), c(w))
 
     # ---- RealRayTracer.trace / trace_generic, real_ray_tracer.py:37-133 -------------------------
-    def trace(self, Hx, Hy, wavelength, num_rays=100, distribution="hexapolar", seed=None):
+    def trace(self, Hx, Hy, wavelength, num_rays=100, distribution="hexapolar", seed=None, spot=False):
         """N rays = fields x pupil points, field-major (real_ray_tracer.py:61-77). `distribution`
-        may be a name or a (Px, Py) pair of NumPy arrays / torch tensors (pinned host or device)."""
+        may be a name or a (Px, Py) pair of NumPy arrays / torch tensors (pinned host or device).
+        spot=True also leaves the per-field spot sums (layout: include/olrt.h, olrt_spot_sums_*) in
+        `rays.spot_sums` -- taken inside the trace kernel when the lens allows it (spot.spot_stats turns them
+        into centroid / RMS radius)."""
         if isinstance(distribution, str):
             Px, Py = pupil_points(distribution, num_rays, seed)
         else:
@@ -173,7 +176,7 @@ class Optic:
         if (isinstance(Px, torch.Tensor) and not Px.is_cuda and Px.dtype == torch.float64
                 and Px.numel() >= self.pipeline_min_rays and sg.record in ("none", "last", None)
                 and not sg._wants_grad_params()):
-            return self._trace_pipelined(Hx, Hy, Px, Py, wavelength)
+            return self._trace_pipelined(Hx, Hy, Px, Py, wavelength, spot)
         if isinstance(Px, torch.Tensor):
             Px = Px.to(device=dev, dtype=torch.float64, non_blocking=True)
             Py = Py.to(device=dev, dtype=torch.float64, non_blocking=True)
@@ -182,19 +185,29 @@ class Optic:
             Py = torch.as_tensor(np.asarray(Py, dtype=np.float64), device=dev)
         rays = self.launch_rays(Hx, Hy, Px, Py, wavelength)
         self.surface_group.trace(rays, wavelengths=[float(wavelength)])
+        if spot:
+            from .spot import spot_sums
+            rays.spot_sums = spot_sums(rays.x, rays.y, rays.i, int(Hx.size), int(Px.numel()))
         return rays
 
     pipeline_min_rays = 1 << 21   # host pupil grids at least this long are streamed in chunks
     pipeline_chunks = 4
 
-    def _trace_pipelined(self, Hx, Hy, Px_h, Py_h, wavelength):
+    def _trace_pipelined(self, Hx, Hy, Px_h, Py_h, wavelength, spot=False):
         """Same result as launch_rays + SurfaceGroup.trace for a pupil grid that lives in (pinned) HOST
-        memory: the grid is copied in chunks on a side stream while the chunks already on the device
-        are launched and traced, so the host->device copy overlaps the kernels instead of preceding them.
-        Each (chunk, field) slice is a contiguous range of the field-major ray arrays. The Newton trip
-        counts stay batch-global: every slice is checked against the reference's exit rule and, if slices
-        disagree, the whole batch is traced again with the largest counts (newton_raphson.py:148)."""
-        from .trace import fused_trace
+        memory: the grid is copied in chunks on a side stream while the chunks already on the device are
+        traced, so the host->device copy overlaps the kernels instead of preceding them.
+
+        Tolerance mode, lens of planes / conics / even aspheres: ONE kernel per chunk launches the rays of every
+        field for the chunk's pupil points, traces them and (spot=True) accumulates the spot sums
+        (`olrt_trace_pupil_*`); the launched rays never exist in memory. Otherwise each (chunk, field) slice is
+        launched by `olrt_generate_rays_*` and traced by `olrt_trace_fwd_*`.
+
+        The Newton trip counts stay batch-global: every chunk reports its residual maxima, ONE read-back checks
+        them against the reference's exit rule (newton_raphson.py:148) and, if the counts were wrong for some
+        chunk, the whole batch is traced again with the corrected counts."""
+        from . import _lib as L
+        from .trace import fused_trace, fused_trace_pupil, slice_true_iters
         sg = self.surface_group
         dev = torch.device(be.get_device())
         dt = be.get_precision()
@@ -206,40 +219,80 @@ class Optic:
         cs = self._copy_stream
         Px_d = torch.empty(npup, dtype=torch.float64, device=dev)
         Py_d = torch.empty(npup, dtype=torch.float64, device=dev)
-        rays_in = torch.empty((8, n), dtype=dt, device=dev)
         out = torch.empty((8, n), dtype=dt, device=dev)
         dir0 = torch.empty((3, n), dtype=dt, device=dev)
+        # chunk edges: a short first chunk (the only copy nothing overlaps), then equal ones
         C_ = max(1, min(self.pipeline_chunks, npup // 65536))
-        edges = [(c * npup // C_, (c + 1) * npup // C_) for c in range(C_)]
+        if C_ >= 4:
+            cuts = [0, npup // (2 * C_), npup // C_] + [c * npup // C_ for c in range(2, C_ + 1)]
+        else:
+            cuts = [c * npup // C_ for c in range(C_ + 1)]
+        edges = [(a_, b_) for a_, b_ in zip(cuts[:-1], cuts[1:]) if b_ > a_]
+        fxy_np, z_start = self._field_offsets(Hx, Hy)
+        fxy_all = torch.from_numpy(fxy_np).to(dev, non_blocking=True)
+        packed = sg.pack([float(wavelength)])
+        fused = bool(sg.fast_math and packed.fastkinds() and self._EPL is not None and self._EPD is not None)
+        if fused and packed.record_surfaces:   # record == "last": the final state IS the last surface's record
+            keep, sg.record = sg.record, "none"
+            try:
+                packed = sg.pack([float(wavelength)])
+            finally:
+                sg.record = keep
+        gen_kw = dict(EPD=self._EPD, EPL=self._EPL, z_start=z_start, wavelength=float(wavelength), dtype=dt)
+        status_t = torch.zeros(1, dtype=torch.int32, device=dev)
+        sums = shift = None
+        if spot:  # sums are taken about each field's chief-ray image point (one tiny launch, no read-back)
+            sums = torch.zeros((nf, L.SPOT_SUMS), dtype=torch.float64, device=dev)
+            if fused:
+                zero = torch.zeros(1, dtype=torch.float64, device=dev)
+                chief = torch.empty((8, nf), dtype=dt, device=dev)
+                fused_trace_pupil(packed, zero, zero, fxy_all, out=chief, status_t=status_t, **gen_kw)
+                shift = chief[:2].t().to(torch.float64).nan_to_num(0.0, 0.0, 0.0).contiguous()
         cs.wait_stream(main)
         events = []
+        tl = [] if getattr(self, "debug_timeline", False) else None   # [(label, timing event)]
+
+        def mark(label, stream):
+            if tl is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record(stream)
+                tl.append((label, e))
+        mark("start", main)
         with torch.cuda.stream(cs):
-            for lo, hi in edges:
+            for c_, (lo, hi) in enumerate(edges):
                 Px_d[lo:hi].copy_(Px_h[lo:hi], non_blocking=True)
                 Py_d[lo:hi].copy_(Py_h[lo:hi], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(cs)
                 events.append(ev)
-        packed = sg.pack([float(wavelength)])
-        status_t = torch.zeros(1, dtype=torch.int32, device=dev)
-        from . import _lib as L
-        from .trace import slice_true_iters
-        n_slices = len(edges) * nf
+                mark(f"copy{c_}", cs)
+        rays_in = None if fused else torch.empty((8, n), dtype=dt, device=dev)
+        n_slices = len(edges) * (1 if fused else nf)
         has_nr = bool(packed.nr_rows())
         for attempt in range(8):
             k_used = packed.nr_iters()
             resid = (torch.zeros((n_slices, packed.n_surfaces, L.RESID_STRIDE), dtype=torch.int64, device=dev)
                      if has_nr else None)
+            if attempt and sums is not None:
+                sums.zero_()
             q_ = 0
             for (lo, hi), ev in zip(edges, events):
                 main.wait_event(ev)
+                if fused:
+                    fused_trace_pupil(packed, Px_d, Py_d, fxy_all, p_lo=lo, p_len=hi - lo, out=out, dir0=dir0,
+                                      spot=sums, spot_shift=shift, status_t=status_t,
+                                      resid_out=None if resid is None else resid[q_], **gen_kw)
+                    mark(f"chunk{q_}", main)
+                    q_ += 1
+                    continue
                 for f in range(nf):
                     a, b = f * npup + lo, f * npup + hi
                     self.launch_rays(Hx[f:f + 1], Hy[f:f + 1], Px_d[lo:hi], Py_d[lo:hi], wavelength,
-                                     out=rays_in[:, a:b])
+                                     out=rays_in[:, a:b], fxy_d=fxy_all[f:f + 1])
                     fused_trace(packed, [rays_in[q, a:b] for q in range(7)] + [None], out=out[:, a:b],
                                 dir0_out=dir0[:, a:b], fast=sg.fast_math, verify_nr=False, check_status=False,
                                 status_t=status_t, resid_out=None if resid is None else resid[q_])
+                    mark(f"slice{q_}", main)
                     q_ += 1
             if not has_nr:
                 break
@@ -255,15 +308,41 @@ class Optic:
                 break
             packed.set_nr_iters(batch)
         st = int(status_t.item())
+        if tl is not None:
+            torch.cuda.synchronize(dev)
+            self.last_timeline = [(lb, tl[0][1].elapsed_time(e)) for lb, e in tl]
         if st & 1:
             raise ValueError("Zernike coordinates must be normalized to [-1, 1]. Consider updating "
                              "the normalization radius to 1.1x the surface aperture.")
-        rays = RealRays(*[rays_in[q] for q in range(8)])
+        if fused:
+            rays = RealRays.from_traced(out, dir0, wavelength)
+        else:
+            rays = RealRays(*[rays_in[q] for q in range(8)])
         sg.reset()
         sg._finish(rays, packed, out, None, dir0, packed.nr_iters())
+        if fused and sg.record == "last":
+            sg.surfaces[-1]._set_record(out)
+        if spot:
+            if fused:
+                sums[:, 8:10] = shift
+            else:
+                from .spot import spot_sums
+                spot_sums(rays.x, rays.y, rays.i, nf, npup, out=sums)
+            rays.spot_sums = sums
         return rays
 
-    def launch_rays(self, Hx, Hy, Px, Py, wavelength, out=None) -> RealRays:
+    def _field_offsets(self, Hx, Hy):
+        """(fxy [F, 2] NumPy, z_start): -tan(radians(max_field H)) (offset + EPL) per field and the launch plane,
+        field_types.py:139-169, :223-239 (object at infinity)."""
+        EPL, EPD, mf = self._EPL, self._EPD, self.max_field
+        z_pos = [float(s.geometry.cs.z) for s in self.surface_group.surfaces[1:-1]]
+        offset = EPD - min(z_pos)
+        hx, hy = np.asarray(Hx, dtype=np.float64).reshape(-1), np.asarray(Hy, dtype=np.float64).reshape(-1)
+        fxy = np.stack([-np.tan(np.radians(mf * hx)) * (offset + EPL),
+                        -np.tan(np.radians(mf * hy)) * (offset + EPL)], axis=1)
+        return np.ascontiguousarray(fxy), float(self.surface_group.surfaces[1].geometry.cs.z) - offset
+
+    def launch_rays(self, Hx, Hy, Px, Py, wavelength, out=None, fxy_d=None) -> RealRays:
         """fields x pupil rays (field-major) from the ray-launch kernel `olrt_generate_rays_*`
         (ray_generator.py:28-106 + field_types.py:139-169, object at infinity). Hx, Hy: [F] NumPy arrays
         (one entry per field); Px, Py: [P] float64 device tensors."""
@@ -274,15 +353,11 @@ class Optic:
             raise ValueError("call set_paraxial(EPL, EPD) first")
         lib = L.load()
         dt, dev = be.get_precision(), Px.device
-        EPL, EPD, mf = self._EPL, self._EPD, self.max_field
-        z_pos = [float(s.geometry.cs.z) for s in self.surface_group.surfaces[1:-1]]
-        offset = EPD - min(z_pos)                              # field_types.py:223-239
-        hx, hy = np.asarray(Hx, dtype=np.float64).reshape(-1), np.asarray(Hy, dtype=np.float64).reshape(-1)
-        fxy = np.stack([-np.tan(np.radians(mf * hx)) * (offset + EPL),
-                        -np.tan(np.radians(mf * hy)) * (offset + EPL)], axis=1)
-        fxy_d = torch.from_numpy(np.ascontiguousarray(fxy)).to(dev, non_blocking=True)
-        z_start = float(self.surface_group.surfaces[1].geometry.cs.z) - offset
-        nf, npup = int(hx.size), int(Px.numel())
+        EPL, EPD = self._EPL, self._EPD
+        fxy, z_start = self._field_offsets(Hx, Hy)
+        if fxy_d is None:      # a caller launching many slices uploads the table once and passes row views
+            fxy_d = torch.from_numpy(fxy).to(dev, non_blocking=True)
+        nf, npup = int(fxy.shape[0]), int(Px.numel())
         if out is None:
             out = torch.empty((8, nf * npup), dtype=dt, device=dev)
         fn = lib.olrt_generate_rays_f64 if dt == torch.float64 else lib.olrt_generate_rays_f32

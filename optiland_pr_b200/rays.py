@@ -38,6 +38,18 @@ class RealRays(BaseRays):
         self.N0 = None
         self.is_normalized = True
 
+    @classmethod
+    def from_traced(cls, out, dir0, wavelength):
+        """Rays whose launch state never existed in memory (the kernel launched them, olrt_trace_pupil_*):
+        rows of `out` [8, N] are the state after the last surface, `dir0` [3, N] the pre-interaction direction
+        there; the wavelength is a stride-0 view."""
+        r = cls.__new__(cls)
+        r.x, r.y, r.z, r.L, r.M, r.N, r.i, r.opd = (out[q] for q in range(8))
+        r.w = torch.as_tensor(float(wavelength), dtype=out.dtype, device=out.device).expand(out.shape[1])
+        r.L0, r.M0, r.N0 = (dir0[0], dir0[1], dir0[2]) if dir0 is not None else (None, None, None)
+        r.is_normalized = True
+        return r
+
     def __len__(self):
         return int(self.x.numel())
 

@@ -209,9 +209,12 @@ class SurfaceGroup:
     def _finish(self, rays, packed, out, record, dir0, nr_iters):
         """Hand the kernel's buffers to the objects the analyses read (surface_group.py:95-140,
         standard_surface.py:266-286, real_rays.py:82-86)."""
-        for gi in packed.object_records:  # ObjectSurface.trace: record only, object_surface.py:56-72
-            self._surfaces[gi]._set_record(torch.stack(
-                [rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd]).clone())
+        # ObjectSurface.trace: record only, object_surface.py:56-72. The launch state is copied (the reference
+        # records copies) only when every surface is recorded; "last" / "none" / a list never read it.
+        if self.record == "all":
+            for gi in packed.object_records:
+                self._surfaces[gi]._set_record(torch.stack(
+                    [rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd]))
         for slot, gi in enumerate(packed.record_surfaces):
             self._surfaces[gi]._set_record(record[slot] if record is not None else out)
         rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd = (out[q] for q in range(8))

@@ -208,3 +208,44 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
     return TraceResult(out=out, record=record, dir0=dir0, nr_iters=packed.nr_iters(), status=status,
                        launches=launches, fixups=fixups,
                        nr_true=nr_true if nr_true is not None else packed.nr_iters())
+
+
+def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, field_xy: torch.Tensor, *,
+                      EPD: float, EPL: float, z_start: float, wavelength: float, p_lo: int = 0,
+                      p_len: int | None = None, dtype=torch.float64, out: torch.Tensor | None = None,
+                      dir0: torch.Tensor | None = None, spot: torch.Tensor | None = None,
+                      spot_shift: torch.Tensor | None = None, spot_valid_only: bool = False,
+                      resid_out: torch.Tensor | None = None, status_t: torch.Tensor | None = None) -> None:
+    """Enqueue `olrt_trace_pupil_*` (include/olrt.h): launch the rays of every field for pupil points
+    [p_lo, p_lo + p_len) in the kernel, trace them, optionally accumulate the spot sums. Nothing is read back:
+    the caller owns `status_t`, `resid_out` (see fused_trace) and checks them after the last chunk.
+    out: [8, F * P] or None (epilogue only); dir0: [3, F * P] or None; spot: [F, SPOT_SUMS] float64 (zeroed by
+    the caller); spot_shift: [F, 2] float64. Raises NotImplementedError where the C ABI answers
+    OLRT_E_UNSUPPORTED (the caller then uses launch + fused_trace + spot_sums)."""
+    lib = L.load()
+    if not Px.is_cuda:
+        raise L.OlrtLibraryError("fused_trace_pupil needs CUDA tensors; there is no CPU path")
+    device = Px.device
+    npup = int(Px.numel())
+    nf = int(field_xy.shape[0])
+    p_len = npup - p_lo if p_len is None else p_len
+    ops_d, presc_d = _device_tables(packed, dtype, device)
+    pu = L.OlrtPupil(Px.data_ptr(), Py.data_ptr(), field_xy.data_ptr(), npup, int(p_lo), int(p_len), nf, 0,
+                     float(EPD), float(EPL), float(z_start), float(wavelength))
+    sys_ = packed.make_sys()
+    sys_.presc_stride = int(presc_d.shape[1])
+    fixup = _fixup_workspace(nf * npup, device) if dtype == torch.float64 else None
+    out_arr = None
+    if out is not None:
+        if out.dtype != dtype or tuple(out.shape) != (8, nf * npup) or not out.is_contiguous():
+            raise ValueError("out must be a contiguous [8, n_fields * n_pupil] tensor of the trace dtype")
+        out_arr = C.byref(L.PtrArray8(*[out[q].data_ptr() for q in range(8)]))
+    fn = lib.olrt_trace_pupil_f64 if dtype == torch.float64 else lib.olrt_trace_pupil_f32
+    with torch.cuda.device(device):
+        rc = fn(C.byref(sys_), presc_d.data_ptr(), ops_d.data_ptr(), C.byref(pu), out_arr, _ptr(dir0),
+                _ptr(resid_out), _ptr(status_t), _ptr(fixup), _ptr(spot), _ptr(spot_shift),
+                L.SPOT_VALID_ONLY if spot_valid_only else 0, L.FWD_FAST,
+                torch.cuda.current_stream(device).cuda_stream)
+    if rc == -4:
+        raise NotImplementedError("olrt_trace_pupil: this lens / mode needs the separate launch + trace kernels")
+    L.check(rc, "olrt_trace_pupil")
