@@ -147,7 +147,7 @@ def main():
     import torch.distributed as dist
 
     import optiland_pr_b200 as ol
-    from optiland_pr_b200 import _lib, flops, samples, spot
+    from optiland_pr_b200 import _lib, flops, parallel, samples, spot
     from optiland_pr_b200.trace import fused_trace
 
     rank = int(os.environ.get("RANK", "0"))
@@ -179,23 +179,65 @@ def main():
     Hx = [f[0] for f in FIELDS]
     Hy = [f[1] for f in FIELDS]
 
-    # ---- device-resident inputs for `value`
-    rays = lens.generate_rays(torch.tensor(Hx, device=dev).repeat_interleave(npf),
-                              torch.tensor(Hy, device=dev).repeat_interleave(npf),
-                              Px_h.to(dev).repeat(nf), Py_h.to(dev).repeat(nf), WAVELENGTH)
-    ins = rays.components()
-    ins[7] = None  # one wavelength: the kernel does not read the wavelength array
-    n = int(ins[0].numel())
+    # ---- device-resident inputs for `value`: the pupil grid (what Optic.trace is given), already in HBM
+    from optiland_pr_b200.trace import fused_trace_pupil, slice_true_iters
+    Px_d, Py_d = Px_h.to(dev), Py_h.to(dev)
+    n = nf * npf
     packed = lens.surface_group.pack([WAVELENGTH])
+    fxy_np, z_start = lens._field_offsets(np.asarray(Hx), np.asarray(Hy))
+    fxy_d = torch.from_numpy(fxy_np).to(dev)
+    gen_kw = dict(EPD=lens._EPD, EPL=lens._EPL, z_start=z_start, wavelength=WAVELENGTH, dtype=torch.float64)
     out = torch.empty((8, n), dtype=torch.float64, device=dev)
     sums = torch.zeros((nf, _lib.SPOT_SUMS), dtype=torch.float64, device=dev)
+    status_t = torch.zeros(1, dtype=torch.int32, device=dev)
+    resid = torch.zeros((packed.n_surfaces, _lib.RESID_STRIDE), dtype=torch.int64, device=dev)
+    zero1 = torch.zeros(1, dtype=torch.float64, device=dev)
+    chief = torch.empty((8, nf), dtype=torch.float64, device=dev)
 
-    def step_resident(fast=True):
-        res = fused_trace(packed, ins, out=out, fast=fast)
-        spot.spot_sums(out[0], out[1], out[6], nf, npf, out=sums)
+    resid_h = [torch.zeros(resid.shape, dtype=torch.int64).pin_memory() for _ in range(2)]
+    resid_ev = [None, None]
+    tick = [0]
+
+    def check_newton(slot):
+        """The reference's exit rule (newton_raphson.py:148) on the residual maxima one step reported."""
+        resid_ev[slot].synchronize()
+        k_used = packed.nr_iters()
+        return slice_true_iters(packed, resid_h[slot].numpy().view(np.float64), k_used) == k_used
+
+    def step_resident(settle=False):
+        """One pass of the hot path: launch the rays of the 3 fields from the pupil grid, trace them, write the
+        final ray state and take the spot sums -- one kernel (olrt_trace_pupil_f64) plus its IEEE fix-up pass.
+        The Newton trip counts every step used are checked against the reference's exit rule from the residual
+        maxima the kernel reports; the (small) read-back of step k is examined while step k+1 runs."""
+        slot = tick[0] & 1
+        sums.zero_()
+        resid.zero_()
+        fused_trace_pupil(packed, zero1, zero1, fxy_d, out=chief, **gen_kw)          # chief rays -> spot shift
+        shift = chief[:2].t().nan_to_num(0.0, 0.0, 0.0).contiguous()
+        fused_trace_pupil(packed, Px_d, Py_d, fxy_d, out=out, spot=sums, spot_shift=shift, resid_out=resid,
+                          status_t=status_t, **gen_kw)
+        sums[:, 8:10] = shift
         if world > 1:
-            dist.all_reduce(sums)
-        return res
+            sums.copy_(parallel.allreduce_spot_sums(sums))
+        resid_h[slot].copy_(resid, non_blocking=True)
+        resid_ev[slot] = torch.cuda.Event()
+        resid_ev[slot].record()
+        prev = slot ^ 1
+        if resid_ev[prev] is not None and not settle:
+            if not check_newton(prev):
+                raise SystemExit("Newton trip counts changed between steps")
+            resid_ev[prev] = None
+        tick[0] += 1
+        if settle:   # first calls: find the counts the exit rule asks for
+            resid_ev[slot].synchronize()
+            k_used = packed.nr_iters()
+            k_true = slice_true_iters(packed, resid_h[slot].numpy().view(np.float64), k_used)
+            resid_ev[slot] = None
+            if k_true != k_used:
+                packed.set_nr_iters([min(lay.max_iter, max(k * 2, k + 2)) if kt is None else kt
+                                     for k, kt, lay in zip(k_used, k_true, packed.layouts)])
+                return False
+        return True
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -220,35 +262,51 @@ def main():
         return ms / steps
 
     # settle the Newton trip counts K_s (first call may relaunch), then time
-    res0 = step_resident()
-    nr_iters = res0.nr_iters
+    for _ in range(8):
+        if step_resident(settle=True):
+            break
+    nr_iters = packed.nr_iters()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     ms_step = timed(step_resident, args.steps, max(args.warmup, 3))
     clocks = sampler.stop() if rank == 0 else None
-    launches_per_step = 3  # trace main pass + IEEE fix-up pass + spot sums
+    for slot in (0, 1):   # the last step's residuals
+        if resid_ev[slot] is not None and not check_newton(slot):
+            raise SystemExit("Newton trip counts changed between steps")
+    launches_per_step = 4  # (chief rays + batch) x (fused launch/trace/spot kernel + its IEEE fix-up pass)
     value = n * S_eff * world / (ms_step * 1e-3)
     rms_resident = spot.spot_stats(sums)["rms"].cpu().tolist()
+    if int(status_t.item()) != 0:
+        raise SystemExit("trace status word is not clean")
 
-    # ---- parity guard on the bench batch itself: the timed (tolerance-mode) result against the strict,
-    # bit-faithful kernel's result for the same rays (the strict kernel is what tests/ pin to the reference bit for bit)
+    # ---- parity guard on the bench batch itself: the timed (tolerance-mode, in-kernel launched) result against
+    # the separate launch kernel + the strict, bit-faithful trace kernel (the pair tests/ pin to the reference bit
+    # for bit) on the same rays
+    rays = lens.launch_rays(np.asarray(Hx), np.asarray(Hy), Px_d, Py_d, WAVELENGTH)
+    ins = rays.components()
+    ins[7] = None
     strict_out = fused_trace(packed, ins, fast=False).out
     den = torch.clamp(strict_out.abs(), min=1.0)
     parity = {"max_rel_err_vs_strict_kernel": float(((out - strict_out).abs() / den).nan_to_num(0.0).max()),
               "nan_pattern_identical": bool((out.isnan() == strict_out.isnan()).all()),
               "vignetting_mask_identical": bool(((out[6] == 0) == (strict_out[6] == 0)).all()),
               "bar": "1e-10 relative, masks identical (BASELINE.json north_star)"}
+    del den
     ms_strict = timed(lambda: fused_trace(packed, ins, out=strict_out, fast=False, verify_nr=False, check_status=False),
                       max(2, args.steps // 2), 3)
-    del strict_out, den
+    ms_fx_arrays = timed(lambda: fused_trace(packed, ins, out=strict_out, fast=True, verify_nr=False, check_status=False),
+                         max(2, args.steps // 2), 3)
+    del strict_out, rays, ins
 
-    # ---- dominant kernel alone (roofline): trace_fx_kernel<double>
+    # ---- dominant kernel alone (roofline): trace_fx_kernel<double> in pupil mode with the fused spot sums
+    shift0 = sums[:, 8:10].contiguous()
+
     def only_trace():
-        fused_trace(packed, ins, out=out, fast=True, verify_nr=False, check_status=False)
+        fused_trace_pupil(packed, Px_d, Py_d, fxy_d, out=out, spot=sums, spot_shift=shift0, **gen_kw)
     ms_kernel = timed(only_trace, args.steps, 3)
     fl_ray = flops.flops_per_ray(packed, nr_iters)
-    by_ray = flops.bytes_per_ray(8, 1)
+    by_ray = 64.0 + 16.0 / nf   # 8 output doubles per ray + the pupil point (Px, Py) shared by the nf fields
     # measured FP64 FMA peak on this GPU (dependent-free DFMA chains, all SMs)
     sink = torch.zeros(1, dtype=torch.float64, device=dev)
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
@@ -272,13 +330,19 @@ def main():
     ach_tf = fl_ray * n / (ms_kernel * 1e-3) / 1e12
     ach_gbs = by_ray * n / (ms_kernel * 1e-3) / 1e9
     roofline = {
-        "kernel": "trace_fx_kernel<double> (tolerance mode: <= 1e-10 relative, masks identical) + its IEEE fix-up pass",
+        "kernel": "trace_fx_kernel<double>, pupil mode (in-kernel ray launch + trace + spot sums; tolerance mode: "
+                  "<= 1e-10 relative, masks identical) + its IEEE fix-up pass",
         "bound": "fp64_fma", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s",
         "frac": ach_tf / fp64_peak, "peak_source": "olrt_fma_peak_f64 measured in this run",
-        "flops_per_ray": fl_ray, "bytes_per_ray": by_ray, "nr_iters": nr_iters, "ms_per_launch": ms_kernel,
+        "flops_per_ray": fl_ray, "flops_note": "the trace's algorithmic count (SURVEY.md 8d); ray launch and spot "
+                                               "sums are executed but not counted",
+        "bytes_per_ray": by_ray, "nr_iters": nr_iters, "ms_per_launch": ms_kernel,
         "hbm": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
                 "peak_source": hbm_src + " (MEASURED_PEAKS.json hbm_gbs)"},
         "traffic": None,
+        "same_kernel_on_ray_arrays": {"ms_per_launch": ms_fx_arrays, "bytes_per_ray": 120.0,
+                                      "note": "olrt_trace_fwd_f64 | OLRT_FWD_FAST: 7 input + 8 output arrays, no "
+                                              "launch / spot fusion"},
         "strict_mode": {"kernel": "trace_fk_kernel<double> (-fmad=false, the reference's operation order, bit-identical)",
                         "ms_per_launch": ms_strict, "ray_surfaces_per_s": n * S_eff / (ms_strict * 1e-3),
                         "frac": fl_ray * n / (ms_strict * 1e-3) / 1e12 / fp64_peak},
@@ -286,7 +350,7 @@ def main():
     tr_path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr_path):
         with open(tr_path) as f:
-            roofline["traffic"] = json.load(f).get("trace_fwd_f64_bytes_per_launch")
+            roofline["traffic"] = json.load(f).get("trace_pupil_f64_bytes_per_launch")
 
     # ---- e2e: public API with host inputs
     h2d = Px_h.numel() * 8 * 2 + nf * 8 * 2
@@ -294,13 +358,13 @@ def main():
     rms_host = torch.empty(nf, dtype=torch.float64).pin_memory()
 
     def step_e2e():
-        rr = lens.trace(Hx, Hy, WAVELENGTH, distribution=(Px_h, Py_h))
-        s = spot.spot_sums(rr.x, rr.y, rr.i, nf, npf, out=sums)
+        rr = lens.trace(Hx, Hy, WAVELENGTH, distribution=(Px_h, Py_h), spot=True)
+        s = rr.spot_sums
         if world > 1:
-            dist.all_reduce(s)
+            s = parallel.allreduce_spot_sums(s)
         rms_host.copy_(spot.spot_stats(s)["rms"], non_blocking=False)
 
-    del out, ins, rays
+    del out, Px_d, Py_d
     torch.cuda.empty_cache()
     ms_e2e = timed(step_e2e, max(2, args.steps // 2), 3)
     e2e_value = n * S_eff * world / (ms_e2e * 1e-3)
@@ -318,15 +382,16 @@ def main():
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "even-asphere double Gauss (12 intersected surfaces, 4 Newton-Raphson even aspheres), "
-                               f"{nf} fields x {npf} random pupil rays per GPU, primary wavelength, fwd trace + RMS spot",
+                               f"{nf} fields x {npf} random pupil rays per GPU, primary wavelength, ray launch + fwd trace + final ray state + RMS spot",
                    "rays_per_gpu": n, "surfaces": S_eff, "precision": "float64, tolerance mode (<= 1e-10 relative to the reference, identical masks; "
                                                                   "the bit-identical strict mode is timed in roofline.strict_mode)",
-                   "l2": "inputs (2.7 GB) and outputs (3.2 GB) per step far exceed the 126 MB L2; no flush needed",
+                   "l2": "inputs (268 MB pupil grid) and outputs (3.2 GB) per step exceed the 126 MB L2; no flush needed",
                    "parallelism": f"rays sharded over {world} GPU(s), spot sums all-reduced"},
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h,
-                "api": "Optic.trace(Hx, Hy, wl, distribution=(Px, Py) pinned host) + spot.rms -> host; the pupil copy is "
-                       "streamed in 4 chunks on a side stream and overlaps ray launch + trace"},
+                "api": "Optic.trace(Hx, Hy, wl, distribution=(Px, Py) pinned host, spot=True) + spot.spot_stats -> host; "
+                       "the pupil copy is streamed in chunks on a side stream and overlaps the fused launch + trace + "
+                       "spot kernel of the chunks already on the device"},
         "gpu_launches": launches_per_step * args.steps,
         "roofline": roofline, "parity_check": parity, "clocks": clocks,
         "rms_spot_mm": rms_resident, "rms_spot_mm_e2e": rms_host.tolist(),

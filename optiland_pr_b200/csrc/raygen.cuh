@@ -2,10 +2,13 @@
 // pupil mode (trace_fx.cuh, trace_fwd.cuh fix-up pass):
 //   RayGenerator.generate_rays        optiland/rays/ray_generator.py:28-106
 //   AngleField.get_ray_origins        optiland/fields/field_types.py:139-169   (object at infinity, vx = vy = 1)
-// Written with the explicitly rounded intrinsics (never contracted into FMAs, IEEE division and square
-// root), so every translation unit produces the same bits as the reference's NumPy expression.
+// Written with the explicitly rounded intrinsics (never contracted into FMAs) and the kernels' own IEEE
+// division / square-root sequences (math64.cuh: the same bits as div.rn.f64 / sqrt.rn.f64 for operands of
+// ordinary magnitude, one shared reciprocal for the three quotients, no branches), so every translation unit
+// produces the same bits as the reference's NumPy expression (tests/test_raygen.py).
 #pragma once
 #include <cuda_runtime.h>
+#include "math64.cuh"
 
 namespace OLRT_NS {
 
@@ -30,12 +33,14 @@ __device__ __forceinline__ void gen_ray(const GenParams& G, int f, long long p, 
   x0 = __dadd_rn(x1, xf);
   y0 = __dadd_rn(y1, yf);
   const double dx = __dadd_rn(x1, -x0), dy = __dadd_rn(y1, -y0), dz = __dadd_rn(G.EPL, -G.z_start);
-  double mag = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
-  const bool is_zero = mag < 1e-9;
+  const double rad = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+  double mag = m_sqrt<MM_FAST>(rad);
+  const bool is_zero = (mag < 1e-9) | (rad == 0.0);   // the unguarded sequence returns NaN for sqrt(0)
   if (is_zero) mag = 1.0;
-  L = is_zero ? 0.0 : __ddiv_rn(dx, mag);
-  M = is_zero ? 0.0 : __ddiv_rn(dy, mag);
-  N = is_zero ? 1.0 : __ddiv_rn(dz, mag);
+  const Recip<double, MM_FAST> rm(mag);
+  L = is_zero ? 0.0 : rm.div(dx);
+  M = is_zero ? 0.0 : rm.div(dy);
+  N = is_zero ? 1.0 : rm.div(dz);
 }
 
 }  // namespace OLRT_NS

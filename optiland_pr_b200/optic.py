@@ -183,6 +183,11 @@ class Optic:
         else:
             Px = torch.as_tensor(np.asarray(Px, dtype=np.float64), device=dev)
             Py = torch.as_tensor(np.asarray(Py, dtype=np.float64), device=dev)
+        if (sg.fast_math and sg.record in ("none", "last", None) and not sg._wants_grad_params()
+                and self._EPL is not None and self._EPD is not None and Px.numel() > 0
+                and sg.pack([float(wavelength)]).fastkinds()):
+            # the grid is on the device: one fused launch + trace (+ spot) kernel over the whole pupil
+            return self._trace_pipelined(Hx, Hy, Px.contiguous(), Py.contiguous(), wavelength, spot)
         rays = self.launch_rays(Hx, Hy, Px, Py, wavelength)
         self.surface_group.trace(rays, wavelengths=[float(wavelength)])
         if spot:
@@ -217,12 +222,13 @@ class Optic:
         if getattr(self, "_copy_stream", None) is None:
             self._copy_stream = torch.cuda.Stream(device=dev)
         cs = self._copy_stream
-        Px_d = torch.empty(npup, dtype=torch.float64, device=dev)
-        Py_d = torch.empty(npup, dtype=torch.float64, device=dev)
+        resident = Px_h.is_cuda
+        Px_d = Px_h if resident else torch.empty(npup, dtype=torch.float64, device=dev)
+        Py_d = Py_h if resident else torch.empty(npup, dtype=torch.float64, device=dev)
         out = torch.empty((8, n), dtype=dt, device=dev)
         dir0 = torch.empty((3, n), dtype=dt, device=dev)
         # chunk edges: a short first chunk (the only copy nothing overlaps), then equal ones
-        C_ = max(1, min(self.pipeline_chunks, npup // 65536))
+        C_ = 1 if resident else max(1, min(self.pipeline_chunks, npup // 65536))
         if C_ >= 4:
             cuts = [0, npup // (2 * C_), npup // C_] + [c * npup // C_ for c in range(2, C_ + 1)]
         else:
@@ -260,8 +266,9 @@ class Optic:
         mark("start", main)
         with torch.cuda.stream(cs):
             for c_, (lo, hi) in enumerate(edges):
-                Px_d[lo:hi].copy_(Px_h[lo:hi], non_blocking=True)
-                Py_d[lo:hi].copy_(Py_h[lo:hi], non_blocking=True)
+                if not resident:
+                    Px_d[lo:hi].copy_(Px_h[lo:hi], non_blocking=True)
+                    Py_d[lo:hi].copy_(Py_h[lo:hi], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(cs)
                 events.append(ev)
