@@ -25,6 +25,7 @@
 namespace OLRT_NS {
 
 #define OLRT_BWD_MAXC 8  // even-asphere coefficients with a gradient slot in registers
+#define OLRT_BWD_SLOTS (5 + OLRT_BWD_MAXC)  // frame x y z, radius, conic, coefficients
 
 template <typename R>
 struct BwdParams {
@@ -141,6 +142,18 @@ __device__ __forceinline__ R conic_t(const SurfParams<R>& sp, R x, R y, R z, R L
   R t = (r_abs(z + t1 * N) <= r_abs(z + t2 * N)) ? t1 : t2;
   if (a == R(0)) t = -c / (R(2) * hb);
   return t;
+}
+
+// 4- or 8-byte asynchronous global -> shared copy (one element of a checkpoint), cp.async group helpers
+template <typename R>
+__device__ __forceinline__ void cp_async_elem(R* dst_shared, const R* src_global) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst_shared);
+  if (sizeof(R) == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(src_global) : "memory");
+  else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src_global) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N_> __device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N_) : "memory");
 }
 
 template <typename R>
@@ -281,6 +294,28 @@ __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int 
 }
 
 
+// sum the 32 lane-private partials of every (surface, slot) and add them to the prescription gradient; clears
+// the accumulators. Called by the whole CTA after a __syncthreads().
+template <typename R>
+__device__ __forceinline__ void bwd_flush(R* s_acc, const int32_t* s_ops, int S, int W, R* gpresc) {
+  for (int q = threadIdx.x; q < S * OLRT_BWD_SLOTS; q += blockDim.x) {
+    const int s = q / OLRT_BWD_SLOTS, j = q - s * OLRT_BWD_SLOTS;
+    R* a = s_acc + (size_t)q * 32;
+    R v = R(0);
+    for (int l = 0; l < 32; ++l) { v += a[(l + threadIdx.x) & 31]; }   // rotated start: no bank conflicts
+    for (int l = 0; l < 32; ++l) a[l] = R(0);
+    if (v == R(0)) continue;
+    const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
+    const int doff = op[OLRT_OP_DOFF];
+    const int goff = doff + op[OLRT_OP_NFRAMES] * OLRT_FRAME_REALS;
+    int off;
+    if (j < 3) off = doff + j;
+    else if (j < 5) off = goff + (j - 3);
+    else off = goff + OLRT_GEOM_REALS + 3 * W + (j - 5);
+    atomicAdd(gpresc + off, v);
+  }
+}
+
 template <typename R>
 __device__ __forceinline__ bool bwd_supported(const int32_t* s_ops, int s) {
   const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
@@ -291,19 +326,25 @@ __device__ __forceinline__ bool bwd_supported(const int32_t* s_ops, int s) {
 }
 
 template <typename R>
-__global__ void __launch_bounds__(256) trace_bwd_kernel(const BwdParams<R> P, uint32_t* status) {
+__global__ void __launch_bounds__(256, 2) trace_bwd_kernel(const BwdParams<R> P, uint32_t* status) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int S = P.n_surfaces, W = P.n_wavelengths;
   R* s_presc = reinterpret_cast<R*>(smem_raw);
   const int presc_pad = (P.presc_stride + 1) & ~1;
   R* s_der = s_presc + presc_pad;
   const int der_pad = (S * der_stride(W) + 1) & ~1;
-  R* s_gp = s_der + der_pad;  // block accumulator of d loss / d presc
-  int32_t* s_ops = reinterpret_cast<int32_t*>(s_gp + presc_pad);
+  // d loss / d presc, accumulated per LANE: s_acc[(s * OLRT_BWD_SLOTS + j) * 32 + lane], j = frame x y z, radius,
+  // conic, coefficients. A lane adds its own partial with one shared-memory atomic (8 warps share a slot, no
+  // two lanes do), so there is no per-ray warp reduction; the 32 lanes are summed once per prescription.
+  R* s_acc = s_der + der_pad;
+  // entry states (checkpoints) of the next surface, staged by cp.async while the current one is differentiated:
+  // s_ck[(buf * 7 + q) * blockDim + tid]
+  R* s_ck = s_acc + (size_t)S * OLRT_BWD_SLOTS * 32;
+  int32_t* s_ops = reinterpret_cast<int32_t*>(s_ck + 2 * 7 * blockDim.x);
   __shared__ int s_bad;
 
   for (int q = threadIdx.x; q < P.ops_len; q += blockDim.x) s_ops[q] = P.ops[q];
-  for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) s_gp[q] = R(0);
+  for (int q = threadIdx.x; q < S * OLRT_BWD_SLOTS * 32; q += blockDim.x) s_acc[q] = R(0);
   if (threadIdx.x == 0) s_bad = 0;
   __syncthreads();
   if (threadIdx.x < S && !bwd_supported<R>(s_ops, threadIdx.x)) s_bad = 1;
@@ -322,11 +363,8 @@ __global__ void __launch_bounds__(256) trace_bwd_kernel(const BwdParams<R> P, ui
     if (p != cur_p) {
       __syncthreads();
       if (cur_p >= 0) {  // flush the previous prescription's gradients
-        for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) {
-          const R v = s_gp[q];
-          if (v != R(0)) atomicAdd(P.gpresc + (long long)cur_p * P.presc_stride + q, v);
-          s_gp[q] = R(0);
-        }
+        bwd_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
+        __syncthreads();
       }
       const R* src = P.presc + (long long)p * P.presc_stride;
       for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) s_presc[q] = src[q];
@@ -347,20 +385,30 @@ __global__ void __launch_bounds__(256) trace_bwd_kernel(const BwdParams<R> P, ui
     R gx = ld(P.gout[0]), gy = ld(P.gout[1]), gz = ld(P.gout[2]);
     R gL = ld(P.gout[3]), gM = ld(P.gout[4]), gN = ld(P.gout[5]);
     R gi = ld(P.gout[6]), gopd = ld(P.gout[7]);
+    // entry state of surface s = record[s-1] (the launch state for s == 0): staged one surface ahead
+    auto stage = [&](int s_) {
+      R* dst = s_ck + (size_t)((s_ & 1) * 7) * blockDim.x + threadIdx.x;
+      if (s_ == 0) {
+#pragma unroll
+        for (int q = 0; q < 7; ++q) cp_async_elem(dst + (size_t)q * blockDim.x, P.in[q] + idx);
+      } else {
+        const R* rc = P.record + (long long)(s_ - 1) * 8 * N + idx;
+#pragma unroll
+        for (int q = 0; q < 7; ++q) cp_async_elem(dst + (size_t)q * blockDim.x, rc + (long long)q * N);
+      }
+      cp_async_commit();
+    };
+    stage(S - 1);
     for (int s = S - 1; s >= 0; --s) {
+      if (s > 0) { stage(s - 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
       if (P.grecord != nullptr && valid) {
         const R* g = P.grecord + (long long)s * 8 * N + idx;
         gx += g[0]; gy += g[N]; gz += g[2 * N]; gL += g[3 * N]; gM += g[4 * N]; gN += g[5 * N];
         gi += g[6 * N]; gopd += g[7 * N];
       }
-      R ex, ey, ez, eL, eM, eN, ei;
-      if (s == 0) {
-        ex = P.in[0][idx]; ey = P.in[1][idx]; ez = P.in[2][idx];
-        eL = P.in[3][idx]; eM = P.in[4][idx]; eN = P.in[5][idx]; ei = P.in[6][idx];
-      } else {
-        const R* rc = P.record + (long long)(s - 1) * 8 * N + idx;
-        ex = rc[0]; ey = rc[N]; ez = rc[2 * N]; eL = rc[3 * N]; eM = rc[4 * N]; eN = rc[5 * N]; ei = rc[6 * N];
-      }
+      const R* ck = s_ck + (size_t)((s & 1) * 7) * blockDim.x + threadIdx.x;
+      const R ex = ck[0], ey = ck[blockDim.x], ez = ck[2 * blockDim.x], eL = ck[3 * blockDim.x],
+              eM = ck[4 * blockDim.x], eN = ck[5 * blockDim.x], ei = ck[6 * blockDim.x];
       SurfParams<R> sp;
       load_surface<R, false>(sp, s_ops, s_presc, s_der, s, W, widx);
       R gTx = R(0), gTy = R(0), gTz = R(0), gR = R(0), gk = R(0);
@@ -369,25 +417,15 @@ __global__ void __launch_bounds__(256) trace_bwd_kernel(const BwdParams<R> P, ui
       for (int i = 0; i < OLRT_BWD_MAXC; ++i) gC[i] = R(0);
       bwd_surface<R>(sp, W, widx, ex, ey, ez, eL, eM, eN, ei, gx, gy, gz, gL, gM, gN, gi, gopd, gTx, gTy, gTz,
                      gR, gk, gC);
-      if (!valid) { gTx = gTy = gTz = gR = gk = R(0); }
-      // parameter partials: warp shuffle -> one shared atomic per warp
-      const int doff = sp.op[OLRT_OP_DOFF];
-      const int goff = doff + sp.op[OLRT_OP_NFRAMES] * OLRT_FRAME_REALS;
-      R v;
-      v = warp_sum(gTx); if (lane == 0) atomicAdd(s_gp + doff + 0, v);
-      v = warp_sum(gTy); if (lane == 0) atomicAdd(s_gp + doff + 1, v);
-      v = warp_sum(gTz); if (lane == 0) atomicAdd(s_gp + doff + 2, v);
-      if (sp.geom != OLRT_GEOM_PLANE) {
-        v = warp_sum(gR); if (lane == 0) atomicAdd(s_gp + goff + 0, v);
-        v = warp_sum(gk); if (lane == 0) atomicAdd(s_gp + goff + 1, v);
-        if (sp.geom == OLRT_GEOM_EVEN_ASPHERE) {
-          const int coff = goff + OLRT_GEOM_REALS + 3 * W;
+      if (valid) {  // parameter partials: one lane-private shared atomic each
+        R* acc = s_acc + (size_t)s * OLRT_BWD_SLOTS * 32 + lane;
+        atomicAdd(acc + 0 * 32, gTx); atomicAdd(acc + 1 * 32, gTy); atomicAdd(acc + 2 * 32, gTz);
+        if (sp.geom != OLRT_GEOM_PLANE) {
+          atomicAdd(acc + 3 * 32, gR); atomicAdd(acc + 4 * 32, gk);
+          if (sp.geom == OLRT_GEOM_EVEN_ASPHERE) {
 #pragma unroll
-          for (int i = 0; i < OLRT_BWD_MAXC; ++i) {
-            if (i < sp.ncoef) {
-              v = warp_sum(valid ? gC[i] : R(0));
-              if (lane == 0) atomicAdd(s_gp + coff + i, v);
-            }
+            for (int i = 0; i < OLRT_BWD_MAXC; ++i)
+              if (i < sp.ncoef) atomicAdd(acc + (5 + i) * 32, gC[i]);
           }
         }
       }
@@ -404,12 +442,7 @@ __global__ void __launch_bounds__(256) trace_bwd_kernel(const BwdParams<R> P, ui
     }
   }
   __syncthreads();
-  if (cur_p >= 0) {
-    for (int q = threadIdx.x; q < P.presc_stride; q += blockDim.x) {
-      const R v = s_gp[q];
-      if (v != R(0)) atomicAdd(P.gpresc + (long long)cur_p * P.presc_stride + q, v);
-    }
-  }
+  if (cur_p >= 0) bwd_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
 }
 
 template <typename R>
@@ -431,8 +464,9 @@ int launch_bwd(const olrt_sys* sys, const R* presc, const int32_t* ops, long lon
     if (block == 0) return OLRT_E_ARG;
   }
   const size_t pp = (size_t)((sys->presc_stride + 1) & ~1);
-  const size_t smem = 2 * pp * sizeof(R) +
+  const size_t smem = pp * sizeof(R) +
                       (size_t)((sys->n_surfaces * der_stride(sys->n_wavelengths) + 1) & ~1) * sizeof(R) +
+                      (size_t)sys->n_surfaces * OLRT_BWD_SLOTS * 32 * sizeof(R) + (size_t)2 * 7 * block * sizeof(R) +
                       (size_t)((sys->ops_len + 1) & ~1) * sizeof(int32_t);
   if (smem > 200 * 1024) return OLRT_E_LIMIT;
   if (smem > 48 * 1024)

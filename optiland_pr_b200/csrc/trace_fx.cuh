@@ -28,6 +28,9 @@ namespace OLRT_NS {
 #ifndef OLRT_FX_MIN_BLOCKS
 #define OLRT_FX_MIN_BLOCKS 2
 #endif
+#ifndef OLRT_FX_MIN_BLOCKS_F32  // fp32 rays need half the registers: twice the resident warps
+#define OLRT_FX_MIN_BLOCKS_F32 3
+#endif
 
 template <typename R> struct FxMath;
 template <> struct FxMath<double> {
@@ -53,11 +56,25 @@ template <> struct FxMath<double> {
     return __hiloint2double(__double2hiint(m) ^ (__double2hiint(s) & (int)0x80000000), __double2loint(m));
   }
 };
+// fp32: the hardware's approximate reciprocal / rsqrt / sqrt (1-2 ulp, one MUFU each; 0 -> inf / 0, negative -> NaN
+// like the IEEE functions): the fp32 bar is 1e-5 relative, 100x the fp32 rounding unit.
 template <> struct FxMath<float> {
-  static __device__ __forceinline__ float rcp(float b) { return __frcp_rn(b); }
-  static __device__ __forceinline__ float rsqrt(float a) { return rsqrtf(a); }
-  static __device__ __forceinline__ float sqrt_(float a) { return sqrtf(a); }
-  static __device__ __forceinline__ void sqrt_pair(float a, float& s, float& is) { s = sqrtf(a); is = rsqrtf(a); }
+  static __device__ __forceinline__ float rcp(float b) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+    return r;
+  }
+  static __device__ __forceinline__ float rsqrt(float a) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r;
+  }
+  static __device__ __forceinline__ float sqrt_(float a) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r;
+  }
+  static __device__ __forceinline__ void sqrt_pair(float a, float& s, float& is) { s = sqrt_(a); is = rsqrt(a); }
   static __device__ __forceinline__ float copysign_(float m, float s) { return copysignf(m, s); }
   static __device__ __forceinline__ float flipsign(float m, float s) {
     return __int_as_float(__float_as_int(m) ^ (__float_as_int(s) & (int)0x80000000));
@@ -148,11 +165,25 @@ __device__ __forceinline__ void fx_build_surface(const int32_t* s_ops, const R* 
 template <typename R>
 __device__ __forceinline__ R fx_conic_t(R x, R y, R z, R L, R M, R N, const FxSurf<R>& sf, bool sphere) {
   typedef FxMath<R> Mx;
-  if (sizeof(R) == 4) {  // fp32 keeps the shifted, cancellation-free form of the strict fp32 path
-    RayState<R> rs; rs.x = x; rs.y = y; rs.z = z; rs.L = L; rs.M = M; rs.N = N;
-    ConicConst<R> cc; cc.radius = sf.radius; cc.k = sf.k; cc.c1 = sf.c1; cc.R2 = sf.radius * sf.radius;
-    cc.twoR = sf.twoR; cc.rR2 = R(0);
-    return conic_distance<R, MM_FAST>(rs, cc, false);
+  if (sizeof(R) == 4) {
+    // fp32: b^2 - 4ac cancels catastrophically for a ray launched far from the vertex, so the
+    // origin moves to the ray's closest approach to the vertex first and the roots are taken as q/a and c/q.
+    // Root choice is the reference's (standard.py:134).
+    const R k = sf.k;
+    const R dd = fma(L, L, fma(M, M, N * N));
+    const R idd = Mx::rcp(dd);
+    const R ts = -fma(x, L, fma(y, M, z * N)) * idd;
+    const R xs = fma(ts, L, x), ys = fma(ts, M, y), zs = fma(ts, N, z);
+    const R a = fma(k * N, N, dd);
+    const R hb = fma(k * N, zs, fma(L, xs, fma(M, ys, N * zs))) - N * sf.radius;
+    const R c = fma(k * zs, zs, fma(xs, xs, fma(ys, ys, zs * (zs - sf.twoR))));
+    const R sd = Mx::sqrt_(fma(hb, hb, -(a * c)));
+    const R q = -(hb + ((hb < R(0)) ? -sd : sd));
+    const R t1 = q * Mx::rcp(a);
+    const R t2 = (q != R(0)) ? c * Mx::rcp(q) : R(0);
+    R t = (r_abs(fma(t1, N, zs)) <= r_abs(fma(t2, N, zs))) ? t1 : t2;
+    if (a == R(0)) t = -c * Mx::rcp(R(2) * hb);
+    return ts + t;
   }
   const R NN = N * N;
   R a = fma(L, L, fma(M, M, NN));
@@ -329,7 +360,8 @@ __device__ __forceinline__ void fx_spot_flush(double* spot, int g, double cnt, d
 }
 
 template <typename R>
-__global__ void __launch_bounds__(OLRT_FX_BLOCK, OLRT_FX_MIN_BLOCKS) trace_fx_kernel(const FwdParams<R> P) {
+__global__ void __launch_bounds__(OLRT_FX_BLOCK, (sizeof(R) == 4 ? OLRT_FX_MIN_BLOCKS_F32 : OLRT_FX_MIN_BLOCKS))
+trace_fx_kernel(const FwdParams<R> P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int S = P.n_surfaces, W = P.n_wavelengths;
   R* s_presc = reinterpret_cast<R*>(smem_raw);

@@ -45,20 +45,18 @@ def shard_items(items, rank: int | None = None, world_size: int | None = None):
 def allreduce_spot_sums(sums: torch.Tensor) -> torch.Tensor:
     """Merge per-rank spot sums (layout include/olrt.h: olrt_spot_sums_*). Every rank must have used the
     same shift (columns 8, 9) -- pass an explicit `shift` to spot_sums when sharding rays of one group.
-    Columns 0-4 and 6 add; column 5 (max r^2, a non-negative double, NaN marks a NaN ray) takes the max."""
+    Columns 0-4 and 6 add; column 5 (max r^2, a non-negative double, NaN marks a NaN ray) takes the max.
+    ONE collective: the [G, 10] rows of every rank are gathered (< 1 KB each) and merged locally."""
     _, w = world()
     if w == 1:
         return sums
-    add = sums[:, [0, 1, 2, 3, 4, 6]].contiguous()
-    mx = sums[:, 5].contiguous()
-    nan = torch.isnan(mx).to(sums.dtype)
-    mx = torch.nan_to_num(mx, nan=0.0)
-    dist.all_reduce(add, op=dist.ReduceOp.SUM)
-    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-    dist.all_reduce(nan, op=dist.ReduceOp.MAX)
-    out = sums.clone()
-    out[:, [0, 1, 2, 3, 4, 6]] = add
-    out[:, 5] = torch.where(nan > 0, torch.full_like(mx, float("nan")), mx)
+    sums = sums.contiguous()
+    parts = [torch.empty_like(sums) for _ in range(w)]
+    dist.all_gather(parts, sums)
+    buf = torch.stack(parts)
+    out = buf.sum(dim=0)
+    out[:, 5] = buf[:, :, 5].amax(dim=0)      # amax propagates NaN
+    out[:, 7:] = sums[:, 7:]
     return out
 
 

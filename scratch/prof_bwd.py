@@ -22,3 +22,18 @@ for it in range(4):
     out.backward(g)
 torch.cuda.synchronize()
 print("ok", float(presc.grad.abs().sum()))
+def tm(fn, k=5):
+    fn(); torch.cuda.synchronize()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(k): fn()
+    e1.record(); torch.cuda.synchronize(); return e0.elapsed_time(e1) / k
+def fwd_only():
+    with torch.no_grad():
+        trace_differentiable(pk, presc, leaf, fast=True)
+def fwd_bwd():
+    presc.grad = None
+    out, rec, _ = trace_differentiable(pk, presc, leaf, fast=True)
+    out.backward(g)
+a, b = tm(fwd_only), tm(fwd_bwd)
+print(f"n={n}: fwd(record all) {a:.3f} ms, fwd+bwd {b:.3f} ms, bwd {b-a:.3f} ms  ({n*12/b/1e6:.1f} G rs/s fwd+bwd)")
