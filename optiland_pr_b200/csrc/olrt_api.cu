@@ -43,11 +43,11 @@ extern "C" int olrt_trace_fwd_f64(const olrt_sys* sys, const double* presc, cons
                                   int flags, void* stream) {
   int rc = check_sys(sys, presc, ops, n_rays);
   if (rc) return rc;
+  if (n_rays == 0) return OLRT_OK;  // an empty batch has no arrays to check (their pointers may be null)
   rc = check_rays<double>(sys, in, out);
   if (rc) return rc;
   if (sys->n_record > 0 && !record) return OLRT_E_ARG;
   if (!fixup || n_rays > 0xffffffffLL) return OLRT_E_ARG;
-  if (n_rays == 0) return OLRT_OK;
   cudaStream_t st = (cudaStream_t)stream;
   if (flags & OLRT_FWD_FAST)
     return olrt_fast::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags, st);
@@ -61,10 +61,10 @@ extern "C" int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const
                                   int flags, void* stream) {
   int rc = check_sys(sys, presc, ops, n_rays);
   if (rc) return rc;
+  if (n_rays == 0) return OLRT_OK;
   rc = check_rays<float>(sys, in, out);
   if (rc) return rc;
   if (sys->n_record > 0 && !record) return OLRT_E_ARG;
-  if (n_rays == 0) return OLRT_OK;
   return olrt_fast::fwd_f32(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags,
                             (cudaStream_t)stream);
 }

@@ -1,0 +1,101 @@
+"""GPU edge cases (rim rays, vertex hits, a == 0, N ~ 0, empty and ragged batches) against the NumPy
+oracle, which tests/test_oracle_vs_reference_live.py pins to the unmodified reference on the same constructions.
+Strict mode: bit for bit. Tolerance mode: <= 1e-10 with identical masks and NaN patterns."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import trace_np
+from optiland_pr_b200 import backend as be
+from optiland_pr_b200.apertures import RadialAperture
+from optiland_pr_b200.optic import Optic
+from optiland_pr_b200.prescription import pack_surface_group
+from optiland_pr_b200.trace import fused_trace
+
+pytestmark = pytest.mark.gpu
+INF = float("inf")
+
+
+def _singlet(**kw):
+    be.set_precision("float64")
+    lens = Optic("edge")
+    lens.add_surface(index=0, radius=INF, thickness=INF)
+    lens.add_surface(index=1, thickness=5.0, material="N-SF11", is_stop=True, **kw)
+    lens.add_surface(index=2, radius=INF, thickness=20.0)
+    lens.add_surface(index=3)
+    lens.add_wavelength(0.55, is_primary=True)
+    return lens
+
+
+def _check(lens, rays_in, fast, keep=None):
+    packed = pack_surface_group(lens.surface_group.surfaces, [0.55])
+    with np.errstate(all="ignore"):
+        want = np.array(trace_np.trace_packed(packed, trace_np.Rays(*rays_in))["records"])
+    res = fused_trace(packed, [torch.tensor(rays_in[q], device="cuda") for q in range(8)], fast=fast)
+    got = res.record.cpu().numpy()
+    if keep is not None:
+        got, want = got[:, :, keep], want[:, :, keep]
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    assert np.array_equal(got[:, 6] == 0, want[:, 6] == 0)
+    if fast:
+        m = ~np.isnan(want)
+        assert np.max(np.abs(got[m] - want[m]) / np.maximum(np.abs(want[m]), 1.0), initial=0.0) <= 1e-10
+    else:
+        for q in (0, 1, 2, 3, 4, 5, 7):
+            assert np.array_equal(got[:, q], want[:, q], equal_nan=True), q
+        assert np.allclose(got[:, 6], want[:, 6], rtol=1e-12, atol=0, equal_nan=True)
+    return want
+
+
+@pytest.mark.parametrize("fast", [False, True], ids=["strict", "tolerance"])
+def test_paraboloid_axis_rays_a_equals_zero(fast):
+    """k = -1, rays along the axis: a = k N^2 + L^2 + M^2 + N^2 == 0 -> t = -c / b (standard.py:136-138)."""
+    lens = _singlet(radius=30.0, conic=-1.0)
+    n = 64
+    rng = np.random.default_rng(5)
+    x, y = rng.uniform(-4, 4, n), rng.uniform(-4, 4, n)
+    x[0] = y[0] = 0.0
+    rays_in = np.stack([x, y, np.full(n, -3.0), np.zeros(n), np.zeros(n), np.ones(n), np.ones(n), np.full(n, 0.55)])
+    want = _check(lens, rays_in, fast)
+    assert np.isfinite(want[0, 2]).all()
+
+
+@pytest.mark.parametrize("fast", [False, True], ids=["strict", "tolerance"])
+def test_flat_standard_surface_grazing_rays_clamp(fast):
+    """StandardGeometry with an infinite radius: t = -z / where(|N| > 1e-14, N, 1e-14) (standard.py:100-103)."""
+    lens = _singlet(radius=INF)
+    n = 32
+    N = np.concatenate([np.array([0.0, 1e-15, -1e-15, 1e-14, 2e-14, 1e-9]), np.linspace(0.01, 1.0, n - 6)])
+    L = np.sqrt(np.maximum(0.0, 1.0 - N * N))
+    rays_in = np.stack([np.zeros(n), np.linspace(-1, 1, n), np.full(n, -1.0), L, np.zeros(n), N, np.ones(n),
+                        np.full(n, 0.55)])
+    # The six grazing rays leave the second plane exactly AT the critical angle (1 - u^2 (1 - dot^2) cancels to 0 or
+    # to a few 1e-17): whether N' is 0 (t = inf at the image) or 3e-9 is decided by the last rounding, so only the
+    # bit-faithful strict mode is held to the reference there; tolerance mode is checked on the other rays.
+    _check(lens, rays_in, fast, keep=(N >= 0.01) if fast else None)
+
+
+@pytest.mark.parametrize("fast", [False, True], ids=["strict", "tolerance"])
+def test_rim_rays_on_the_aperture_edge(fast):
+    lens = _singlet(radius=40.0, aperture=RadialAperture(r_max=3.0, r_min=0.5))
+    r = np.array([0.0, 0.5, np.nextafter(0.5, 0), np.nextafter(0.5, 1), 3.0, np.nextafter(3.0, 0), np.nextafter(3.0, 4),
+                  1.0, 2.999999999, 3.000000001])
+    n = r.size
+    rays_in = np.stack([r, np.zeros(n), np.full(n, -2.0), np.zeros(n), np.zeros(n), np.ones(n), np.ones(n),
+                        np.full(n, 0.55)])
+    want = _check(lens, rays_in, fast)
+    assert (want[0, 6] == 0).any() and (want[0, 6] != 0).any()
+
+
+@pytest.mark.parametrize("fast", [False, True], ids=["strict", "tolerance"])
+@pytest.mark.parametrize("n", [0, 1, 31, 257])
+def test_empty_and_ragged_batches(n, fast):
+    lens = _singlet(radius=25.0)
+    rng = np.random.default_rng(n)
+    x, y = rng.uniform(-3, 3, n), rng.uniform(-3, 3, n)
+    rays_in = np.stack([x, y, np.full(n, -2.0), np.zeros(n), np.zeros(n), np.ones(n), np.ones(n), np.full(n, 0.55)])
+    packed = pack_surface_group(lens.surface_group.surfaces, [0.55])
+    res = fused_trace(packed, [torch.tensor(rays_in[q], device="cuda") for q in range(8)], fast=fast)
+    assert tuple(res.out.shape) == (8, n)
+    if n:
+        _check(lens, rays_in, fast)

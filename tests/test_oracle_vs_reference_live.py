@@ -1,0 +1,132 @@
+"""CPU, build container only: the NumPy oracle against the UNMODIFIED reference imported from /root/reference, on
+fresh random inputs and on the adversarial cases SURVEY.md 8c lists (rim rays, misses, TIR, vertex hits, a == 0,
+N ~ 0). Skipped where the reference is absent (the GPU box); the committed fixtures in tests/golden cover that case.
+Closed-form surfaces: bit for bit. Newton-Raphson surfaces with powers >= 3: 1e-12 (libm pow vs rounded products)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ref_shim, trace_np
+from optiland_pr_b200.prescription import pack_surface_group
+
+pytestmark = [pytest.mark.reference,
+              pytest.mark.skipif(not os.path.isdir(ref_shim.REFERENCE_PATH), reason="reference tree not present")]
+
+FIELDS8 = ("x", "y", "z", "L", "M", "N", "intensity", "opd")
+
+
+@pytest.fixture(scope="module")
+def ref():
+    ref_shim.install()
+    import optiland.backend as be
+    be.set_backend("numpy")
+    from optiland import optic
+    from optiland.rays import RealRays
+    from optiland.samples.objectives import CookeTriplet, DoubleGauss
+    from optiland.samples.simple import AsphericSinglet
+    return dict(be=be, Optic=optic.Optic, RealRays=RealRays, CookeTriplet=CookeTriplet, DoubleGauss=DoubleGauss,
+                AsphericSinglet=AsphericSinglet)
+
+
+def _both(ref, lens, rays_in, wavelengths):
+    """(reference records [S, 8, N], oracle records) for the same rays."""
+    rays = ref["RealRays"](*[rays_in[q].copy() for q in range(8)])
+    sg = lens.surface_group
+    with np.errstate(all="ignore"):
+        sg.trace(rays)
+    want = np.stack([np.stack([np.asarray(getattr(s, k), dtype=np.float64) for k in FIELDS8])
+                     for s in sg.surfaces[1:]])
+    packed = pack_surface_group(sg.surfaces, list(wavelengths))
+    with np.errstate(all="ignore"):
+        got = np.array(trace_np.trace_packed(packed, trace_np.Rays(*rays_in))["records"])
+    return want, got
+
+
+def _wild(n, seed, wavelengths, half_width, cone, z0=-8.0):
+    rng = np.random.default_rng(seed)
+    x, y = rng.uniform(-half_width, half_width, n), rng.uniform(-half_width, half_width, n)
+    L, M = rng.uniform(-cone, cone, n), rng.uniform(-cone, cone, n)
+    x[:6] = 0.0; y[:6] = 0.0; L[:6] = 0.0; M[:6] = 0.0                  # vertex hits: r2 == 0, normal incidence
+    N = np.sqrt(1.0 - L * L - M * M)
+    return np.stack([x, y, np.full(n, z0), L, M, N, np.ones(n), rng.choice(np.asarray(wavelengths), n)])
+
+
+@pytest.mark.parametrize("name,seed", [("CookeTriplet", 21), ("DoubleGauss", 22)])
+def test_closed_form_lenses_bit_exact_on_wild_rays(ref, name, seed):
+    lens = ref[name]()
+    wl = [0.4861, 0.5876, 0.6563]
+    rays_in = _wild(6000, seed, wl, half_width=14.0, cone=0.55)
+    want, got = _both(ref, lens, rays_in, wl)
+    dead = np.isnan(want[-1, 0]).mean()
+    assert 0.02 < dead < 0.98          # misses and TIR really occur
+    for q, f in enumerate(FIELDS8):
+        if f == "intensity":           # exp() of the absorption: same libm here, still compared as a tolerance
+            assert np.allclose(got[:, q], want[:, q], rtol=1e-14, atol=0, equal_nan=True)
+        else:
+            assert np.array_equal(got[:, q], want[:, q], equal_nan=True), f
+
+
+def test_even_asphere_newton_counts_and_values(ref):
+    lens = ref["AsphericSinglet"]()
+    rays_in = _wild(4000, 23, [0.587], half_width=4.0, cone=0.05, z0=-2.0)
+    want, got = _both(ref, lens, rays_in, [0.587])
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    m = ~np.isnan(want)
+    assert np.max(np.abs(got[m] - want[m]) / np.maximum(np.abs(want[m]), 1.0)) <= 1e-12
+    assert np.array_equal(got[:, 6] == 0, want[:, 6] == 0)
+
+
+def _singlet(ref, **kw):
+    be = ref["be"]
+    lens = ref["Optic"]()
+    lens.add_surface(index=0, radius=be.inf, thickness=be.inf)
+    lens.add_surface(index=1, thickness=5.0, material="N-BK7", is_stop=True, **kw)
+    lens.add_surface(index=2, radius=be.inf, thickness=20.0)
+    lens.add_surface(index=3)
+    lens.set_aperture(aperture_type="EPD", value=10)
+    lens.set_field_type(field_type="angle")
+    lens.add_field(y=0)
+    lens.add_wavelength(value=0.55, is_primary=True)
+    return lens
+
+
+def test_paraboloid_axis_ray_a_equals_zero(ref):
+    """k = -1 and a ray along the axis direction: a = k N^2 + L^2 + M^2 + N^2 == 0 -> t = -c / b (standard.py:136-138)."""
+    lens = _singlet(ref, radius=30.0, conic=-1.0)
+    n = 64
+    rng = np.random.default_rng(5)
+    x, y = rng.uniform(-4, 4, n), rng.uniform(-4, 4, n)
+    x[0] = y[0] = 0.0
+    z = np.full(n, -3.0)
+    rays_in = np.stack([x, y, z, np.zeros(n), np.zeros(n), np.ones(n), np.ones(n), np.full(n, 0.55)])
+    want, got = _both(ref, lens, rays_in, [0.55])
+    assert np.isfinite(want[0, 2]).all()
+    assert np.array_equal(got, want, equal_nan=True)
+
+
+def test_flat_standard_surface_grazing_rays_clamp(ref):
+    """StandardGeometry with an infinite radius: t = -z / where(|N| > 1e-14, N, 1e-14) (standard.py:100-103)."""
+    be = ref["be"]
+    lens = _singlet(ref, radius=be.inf)
+    n = 32
+    N = np.concatenate([np.array([0.0, 1e-15, -1e-15, 1e-14, 2e-14, 1e-9]), np.linspace(0.01, 1.0, n - 6)])
+    L = np.sqrt(np.maximum(0.0, 1.0 - N * N))
+    rays_in = np.stack([np.zeros(n), np.linspace(-1, 1, n), np.full(n, -1.0), L, np.zeros(n), N, np.ones(n),
+                        np.full(n, 0.55)])
+    want, got = _both(ref, lens, rays_in, [0.55])
+    assert np.array_equal(got, want, equal_nan=True)
+
+
+def test_rim_rays_on_the_aperture_edge(ref):
+    """Rays landing exactly on, just inside and just outside r_max of a radial aperture: identical clip decisions."""
+    import optiland.physical_apertures as ref_ap
+    lens = _singlet(ref, radius=40.0, aperture=ref_ap.RadialAperture(r_max=3.0, r_min=0.5))
+    r = np.array([0.0, 0.5, np.nextafter(0.5, 0), np.nextafter(0.5, 1), 3.0, np.nextafter(3.0, 0), np.nextafter(3.0, 4),
+                  1.0, 2.999999999, 3.000000001])
+    n = r.size
+    rays_in = np.stack([r, np.zeros(n), np.full(n, -2.0), np.zeros(n), np.zeros(n), np.ones(n), np.ones(n),
+                        np.full(n, 0.55)])
+    want, got = _both(ref, lens, rays_in, [0.55])
+    assert (want[0, 6] == 0).any() and (want[0, 6] != 0).any()
+    assert np.array_equal(got, want, equal_nan=True)
