@@ -437,6 +437,7 @@ def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64
                        "hbm_gbs": 60 * n / (ms * 1e-3) / 1e9}
     out["fp64_fma_peak_tflops"] = fp64_peak
     out["fp32_fma_peak_tflops"] = fp32_peak
+    out.update(bench_monte_carlo(torch, lens, S_eff))
     try:
         from optiland_pr_b200.autograd import bench_backward
     except ImportError:
@@ -444,6 +445,42 @@ def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64
     if bench_backward is not None:
         out.update(bench_backward(lens, packed, ins64, timed, args, fp64_peak))
     return out
+
+
+def bench_monte_carlo(torch, lens, S_eff, trials=4096, rays=262_144):
+    """BASELINE config C5: 4096 perturbed copies of the lens x 262 144 rays each, merit = RMS spot at Hy = 1.
+    One fused launch per round (olrt_trace_pupil_f64 with a prescription batch): no per-ray data in HBM."""
+    from optiland_pr_b200.tolerancing import DistributionSampler, MonteCarloSpot, Perturbation
+    s = lens.surface_group.surfaces
+    curved = [k for k in range(1, len(s) - 1) if np.isfinite(float(s[k].geometry.radius))]
+    perts = [Perturbation(lens, "radius", DistributionSampler("normal", seed=100 + k, loc=float(s[k].geometry.radius),
+                                                              scale=1e-3 * abs(float(s[k].geometry.radius))), k)
+             for k in curved]
+    perts += [Perturbation(lens, "thickness", DistributionSampler("normal", seed=200 + k, loc=float(s[k].thickness),
+                                                                  scale=0.02), k) for k in (1, 2, 3, 5, 8)]
+    perts += [Perturbation(lens, "decenter", DistributionSampler("normal", seed=300 + k, loc=0.0, scale=0.1), k, axis=ax)
+              for k, ax in ((1, "x"), (5, "y"), (7, "x"), (10, "y"))]
+    rng = np.random.default_rng(3)
+    r_, th = rng.uniform(size=rays), rng.uniform(0, 2 * np.pi, size=rays)
+    Px = torch.from_numpy(np.sqrt(r_) * np.cos(th)).cuda()
+    Py = torch.from_numpy(np.sqrt(r_) * np.sin(th)).cuda()
+    mc = MonteCarloSpot(lens, perts)
+    mc.run(64, [0.0], [1.0], WAVELENGTH, Px, Py)           # warm-up (workspace allocation)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    rms = mc.run(trials, [0.0], [1.0], WAVELENGTH, Px, Py)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t1 = time.perf_counter()
+    MonteCarloSpot(lens, perts).draw(trials)
+    t_draw = time.perf_counter() - t1
+    rms = rms.cpu().numpy()
+    return {"mc_tolerancing_c5": {
+        "trials": trials, "rays_per_trial": rays, "perturbations": len(perts), "path": mc.last_path,
+        "seconds": dt, "seconds_host_draws": t_draw, "ray_surfaces_per_s": trials * rays * S_eff / dt,
+        "rms_spot_mm_mean_std": [float(rms.mean()), float(rms.std())],
+        "note": "wall clock of MonteCarloSpot.run: reference-order scalar draws on the host, nominal-lens Newton "
+                "counts, chief rays, one fused launch per round, per-trial Newton-count check, merits read back"}}
 
 
 if __name__ == "__main__":

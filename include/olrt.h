@@ -224,8 +224,12 @@ int olrt_generate_rays_f32(const double* Px, const double* Py, int64_t n_pupil, 
  * One call traces pupil points [p_lo, p_lo + p_len) of EVERY field, so a host pupil grid can be streamed in
  * chunks; ray (field f, pupil point p) lives at index f * n_pupil + p of the output arrays, the field-major
  * order of real_ray_tracer.py:67-77, and belongs to spot group f.
+ * With olrt_sys.n_presc > 1 (Monte-Carlo tolerancing, tolerancing/monte_carlo.py:60-123: every trial re-traces
+ * the same fields and pupil grid through a perturbed prescription) the groups are g = trial * n_fields + f:
+ * arrays hold n_presc * n_fields * n_pupil rays, spot_sums / spot_shift n_presc * n_fields rows; with
+ * out == NULL the whole tolerancing run moves no per-ray data at all.
  * Implemented by the tolerance-mode kernel for lenses of planes / conics / even aspheres (flags must contain
- * OLRT_FWD_FAST for fp64; olrt_sys.kernel_hint & OLRT_HINT_FASTKINDS; one wavelength, one prescription, no
+ * OLRT_FWD_FAST for fp64; olrt_sys.kernel_hint & OLRT_HINT_FASTKINDS; one wavelength, no
  * per-surface records): anything else returns OLRT_E_UNSUPPORTED and the caller uses
  * olrt_generate_rays_* + olrt_trace_fwd_* + olrt_spot_sums_*.                                              */
 typedef struct olrt_pupil {
@@ -242,15 +246,21 @@ typedef struct olrt_pupil {
  *  dir0       NULL or [3][n_fields * n_pupil]
  *  spot_sums  NULL or [n_fields][OLRT_SPOT_SUMS], zeroed by the caller before the first chunk; columns as for
  *             olrt_spot_sums_* except 8, 9 (the caller knows the shift); spot_shift [n_fields][2] is required
- *  spot_flags OLRT_SPOT_*; flags OLRT_FWD_*; the other arguments as for olrt_trace_fwd_*                    */
+ *  spot_flags OLRT_SPOT_*; flags OLRT_FWD_*; the other arguments as for olrt_trace_fwd_*
+ *  group_k    NULL, or [groups][n_surfaces] int32 (device): Newton trip counts PER GROUP instead of ops word 6.
+ *             The reference traces every (trial, field) on its own, so its exit rule (max |f| over that trace's
+ *             rays < tol, newton_raphson.py:148) gives each group its own K_s (<= OLRT_GROUP_RESID - 1 here).
+ *  group_resid NULL, or [groups][n_surfaces][OLRT_GROUP_RESID] u64 (device, zeroed by the caller): max |f| per
+ *             group, surface and iteration (bits of a non-negative double), for the caller to check K_s with.    */
+#define OLRT_GROUP_RESID 8
 int olrt_trace_pupil_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, const olrt_pupil* pupil,
                          double* const out[8], double* dir0, unsigned long long* nr_resid, uint32_t* status,
-                         uint32_t* fixup, double* spot_sums, const double* spot_shift, int spot_flags, int flags,
-                         void* stream);
+                         uint32_t* fixup, double* spot_sums, const double* spot_shift, int spot_flags,
+                         const int32_t* group_k, unsigned long long* group_resid, int flags, void* stream);
 int olrt_trace_pupil_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, const olrt_pupil* pupil,
                          float* const out[8], float* dir0, unsigned long long* nr_resid, uint32_t* status,
-                         uint32_t* fixup, double* spot_sums, const double* spot_shift, int spot_flags, int flags,
-                         void* stream);
+                         uint32_t* fixup, double* spot_sums, const double* spot_shift, int spot_flags,
+                         const int32_t* group_k, unsigned long long* group_resid, int flags, void* stream);
 
 /* Self-test of the kernels' own IEEE division / square-root sequences (csrc/math64.cuh):
  * quot[i] = a[i] / b[i], root[i] = sqrt(a[i]) as the trace kernels compute them; the caller compares

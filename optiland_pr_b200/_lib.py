@@ -19,6 +19,7 @@ MAX_NR_ITERS = 128
 OPS_STRIDE = 16
 RESID_STRIDE = MAX_NR_ITERS + 1
 SPOT_SUMS = 10
+GROUP_RESID = 8
 FRAME_REALS = 9
 GEOM_REALS = 4
 
@@ -125,7 +126,7 @@ def load():
         f = getattr(lib, f"olrt_trace_pupil_{suf}")
         f.restype = C.c_int
         f.argtypes = [C.POINTER(OlrtSys), v, v, C.POINTER(OlrtPupil), C.POINTER(PtrArray8), v, v, v, v, v, v,
-                      C.c_int, C.c_int, v]
+                      C.c_int, v, v, C.c_int, v]
     lib.olrt_selftest_math_f64.restype = C.c_int
     lib.olrt_selftest_math_f64.argtypes = [v, v, v, v, C.c_int64, v]
     if lib.olrt_version() != OLRT_ABI_VERSION:

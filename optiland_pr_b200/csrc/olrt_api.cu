@@ -75,12 +75,15 @@ static int check_pupil(const olrt_sys* sys, const R* presc, const int32_t* ops, 
   if (!q || !q->Px || !q->Py || !q->field_xy) return OLRT_E_ARG;
   if (q->n_fields < 1 || q->n_pupil < 1 || q->p_lo < 0 || q->p_len < 0 || q->p_lo + q->p_len > q->n_pupil)
     return OLRT_E_ARG;
-  const int rc = check_sys(sys, presc, ops, q->p_len * q->n_fields);
+  if (!sys || sys->n_presc < 1) return OLRT_E_ARG;
+  olrt_sys one = *sys;   // in pupil mode every prescription traces the same pupil range: rays_per_presc is implied
+  one.rays_per_presc = q->p_len * q->n_fields;
+  const int rc = check_sys(&one, presc, ops, q->p_len * q->n_fields * sys->n_presc);
   if (rc) return rc;
   if (out) for (int k = 0; k < 8; ++k) if (!out[k]) return OLRT_E_ARG;
   if (spot && !shift) return OLRT_E_ARG;
-  if (q->n_pupil * (long long)q->n_fields > 0xffffffffLL) return OLRT_E_LIMIT;
-  if (!(sys->kernel_hint & OLRT_HINT_FASTKINDS) || sys->n_presc != 1 || sys->n_wavelengths != 1 || sys->n_record != 0)
+  if (q->n_pupil * (long long)q->n_fields * sys->n_presc > 0xffffffffLL) return OLRT_E_LIMIT;
+  if (!(sys->kernel_hint & OLRT_HINT_FASTKINDS) || sys->n_wavelengths != 1 || sys->n_record != 0)
     return OLRT_E_UNSUPPORTED;
   return OLRT_OK;
 }
@@ -88,7 +91,8 @@ static int check_pupil(const olrt_sys* sys, const R* presc, const int32_t* ops, 
 extern "C" int olrt_trace_pupil_f64(const olrt_sys* sys, const double* presc, const int32_t* ops,
                                     const olrt_pupil* pupil, double* const out[8], double* dir0,
                                     unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup,
-                                    double* spot_sums, const double* spot_shift, int spot_flags, int flags,
+                                    double* spot_sums, const double* spot_shift, int spot_flags,
+                                    const int32_t* group_k, unsigned long long* group_resid, int flags,
                                     void* stream) {
   const int rc = check_pupil<double>(sys, presc, ops, pupil, out, spot_sums, spot_shift);
   if (rc) return rc;
@@ -96,20 +100,21 @@ extern "C" int olrt_trace_pupil_f64(const olrt_sys* sys, const double* presc, co
   if (!(flags & OLRT_FWD_FAST) || (flags & OLRT_FWD_REPLAY)) return OLRT_E_UNSUPPORTED;
   if (pupil->p_len == 0) return OLRT_OK;
   return olrt_fast::pupil_f64(sys, presc, ops, pupil, out, dir0, nr_resid, status, fixup, spot_sums, spot_shift,
-                              spot_flags, flags, (cudaStream_t)stream);
+                              spot_flags, group_k, group_resid, flags, (cudaStream_t)stream);
 }
 
 extern "C" int olrt_trace_pupil_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
                                     const olrt_pupil* pupil, float* const out[8], float* dir0,
                                     unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup,
-                                    double* spot_sums, const double* spot_shift, int spot_flags, int flags,
+                                    double* spot_sums, const double* spot_shift, int spot_flags,
+                                    const int32_t* group_k, unsigned long long* group_resid, int flags,
                                     void* stream) {
   const int rc = check_pupil<float>(sys, presc, ops, pupil, out, spot_sums, spot_shift);
   if (rc) return rc;
   if (flags & OLRT_FWD_REPLAY) return OLRT_E_UNSUPPORTED;
   if (pupil->p_len == 0) return OLRT_OK;
   return olrt_fast::pupil_f32(sys, presc, ops, pupil, out, dir0, nr_resid, status, fixup, spot_sums, spot_shift,
-                              spot_flags, flags, (cudaStream_t)stream);
+                              spot_flags, group_k, group_resid, flags, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -18,7 +18,8 @@ OLRT_DECL_FWD(olrt_fast, f32, float)
   namespace olrt_fast {                                                                                  \
   int pupil_##SUF(const olrt_sys* sys, const R* presc, const int32_t* ops, const olrt_pupil* pupil,      \
                   R* const out[8], R* dir0, unsigned long long* nr_resid, uint32_t* status,              \
-                  uint32_t* fixup, double* spot, const double* spot_shift, int spot_flags, int flags,    \
+                  uint32_t* fixup, double* spot, const double* spot_shift, int spot_flags,               \
+                  const int32_t* group_k, unsigned long long* group_resid, int flags,                    \
                   cudaStream_t stream);                                                                  \
   }
 OLRT_DECL_PUPIL(f64, double)

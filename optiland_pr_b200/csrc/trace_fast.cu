@@ -24,17 +24,19 @@ static GenParams to_gen(const olrt_pupil* q) {
 }
 int pupil_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, const olrt_pupil* pupil,
               double* const out[8], double* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup,
-              double* spot, const double* spot_shift, int spot_flags, int flags, cudaStream_t stream) {
+              double* spot, const double* spot_shift, int spot_flags, const int32_t* group_k,
+              unsigned long long* group_resid, int flags, cudaStream_t stream) {
   const GenParams g = to_gen(pupil);
-  return launch_fwd<double>(sys, presc, ops, g.len * g.n_fields, nullptr, nullptr, out, nullptr, dir0, nr_resid, status,
-                            fixup, flags, stream, &g, spot, spot_shift, spot_flags);
+  return launch_fwd<double>(sys, presc, ops, g.len * g.n_fields * sys->n_presc, nullptr, nullptr, out, nullptr, dir0, nr_resid, status,
+                            fixup, flags, stream, &g, spot, spot_shift, spot_flags, group_k, group_resid);
 }
 int pupil_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, const olrt_pupil* pupil,
               float* const out[8], float* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup,
-              double* spot, const double* spot_shift, int spot_flags, int flags, cudaStream_t stream) {
+              double* spot, const double* spot_shift, int spot_flags, const int32_t* group_k,
+              unsigned long long* group_resid, int flags, cudaStream_t stream) {
   const GenParams g = to_gen(pupil);
-  return launch_fwd<float>(sys, presc, ops, g.len * g.n_fields, nullptr, nullptr, out, nullptr, dir0, nr_resid, status,
-                           fixup, flags, stream, &g, spot, spot_shift, spot_flags);
+  return launch_fwd<float>(sys, presc, ops, g.len * g.n_fields * sys->n_presc, nullptr, nullptr, out, nullptr, dir0, nr_resid, status,
+                           fixup, flags, stream, &g, spot, spot_shift, spot_flags, group_k, group_resid);
 }
 int bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, long long n_rays,
             const double* const in[8], const double* record, const double* const gout[8], const double* grecord,

@@ -30,6 +30,11 @@ struct FwdParams {
   // rays are launched in the kernel (pupil mode), where one launch covers a pupil range of every field
   long long n_total;
   GenParams gen;             // gen.px != nullptr: pupil mode (olrt_trace_pupil_*), `in` is not read
+  // per-group Newton trip counts (pupil mode): the reference traces every (trial, field) on its own, so its exit
+  // rule -- max |f| over THAT trace's rays < tol, newton_raphson.py:148 -- yields one K_s per group. group_k
+  // [G][S] replaces ops word 6, group_resid [G][S][OLRT_GROUP_RESID] receives each group's residual maxima.
+  const int32_t* group_k;
+  unsigned long long* group_resid;
   double* spot;              // fused spot epilogue: [n_groups][OLRT_SPOT_SUMS] sums, group = field (pupil mode)
   const double* spot_shift;  // [n_groups][2] shift the sums are taken about (required with spot)
   int spot_flags;            // OLRT_SPOT_*
@@ -104,6 +109,7 @@ __device__ __forceinline__ void load_surface(SurfParams<R>& sp, const int32_t* s
   sp.geom = op[OLRT_OP_GEOM];
   sp.ncoef = op[OLRT_OP_NCOEF];
   sp.aux = op[OLRT_OP_AUX];
+  sp.nr_iters = op[OLRT_OP_NR_ITERS];
 }
 
 // surface kinds: straight-line instantiations for the common cases, the interpreter for the rest
@@ -145,7 +151,7 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
   } else {
     t = conic_distance<R, MM>(r, sp.cc, (flags & OLRT_F_RADIUS_INF) != 0);
     if (geom >= OLRT_GEOM_EVEN_ASPHERE) {  // newton_raphson.py:119-168
-      const int K = op[OLRT_OP_NR_ITERS];
+      const int K = sp.nr_iters;
       for (int j = 0; j <= K; ++j) {
         if (j == K && resid == nullptr) break;
         const R xi = r.x + t * r.L, yi = r.y + t * r.M, zi = r.z + t * r.N;
@@ -250,6 +256,12 @@ __device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r,
     load_surface<R, FIX>(sp, s_ops, presc, s_der, s, W, widx);
     unsigned long long* resid =
         (want_resid && sp.geom >= OLRT_GEOM_EVEN_ASPHERE) ? (s_resid + s_roff[s]) : nullptr;
+    if (FIX && P.group_k != nullptr && P.gen.px != nullptr) {  // group mode: this ray's group decides K and the slots
+      const long long g_ = idx / P.gen.n_pupil;
+      sp.nr_iters = min(P.group_k[g_ * S + s], OLRT_GROUP_RESID - 1);
+      resid = (P.group_resid != nullptr && sp.geom >= OLRT_GEOM_EVEN_ASPHERE)
+                  ? P.group_resid + (g_ * S + s) * OLRT_GROUP_RESID : nullptr;
+    }
     if (FIX) {
       surface_step<R, KIND_GENERIC, MM_IEEE>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0);
     } else {
@@ -344,15 +356,20 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
     long long idx = valid ? item : (n_items - 1);
     if (FIX) idx = (long long)P.fixup[1 + idx];
     const R* presc = s_presc;
-    if (FIX) presc = P.presc + ((P.n_presc > 1) ? (idx / P.rays_per_presc) : 0) * P.presc_stride;
+    if (FIX) {  // pupil mode: idx = (prescription * n_fields + field) * n_pupil + pupil point
+      long long pi = 0;
+      if (P.n_presc > 1) pi = (P.gen.px != nullptr) ? (idx / P.gen.n_pupil) / P.gen.n_fields : idx / P.rays_per_presc;
+      presc = P.presc + pi * P.presc_stride;
+    }
 
     RayState<R> r;
     int widx = 0;
     R wl = P.wavelengths[0];
     if (FIX && P.gen.px != nullptr) {  // pupil mode: launch the listed ray again (idx = f * n_pupil + p)
-      const int f = (int)(idx / P.gen.n_pupil);
+      const long long g_ = idx / P.gen.n_pupil;
+      const int f = (int)(g_ % P.gen.n_fields);
       double x0, y0, dL, dM, dN;
-      gen_ray(P.gen, f, idx - (long long)f * P.gen.n_pupil, x0, y0, dL, dM, dN);
+      gen_ray(P.gen, f, idx - g_ * P.gen.n_pupil, x0, y0, dL, dM, dN);
       r.x = (R)x0; r.y = (R)y0; r.z = (R)P.gen.z_start; r.L = (R)dL; r.M = (R)dM; r.N = (R)dN;
       r.i = R(1); r.opd = R(0);
     } else {

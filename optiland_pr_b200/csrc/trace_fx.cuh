@@ -290,12 +290,12 @@ __device__ __forceinline__ void fx_conic(RayState<R>& r, const FxSurf<R>& sf, co
 //   dz/dx = x (1/(R q) + 2 (Q + s Q')),  f = sag - z,  f' = zx L + zy M - N
 template <typename R>
 __device__ __forceinline__ void fx_even(RayState<R>& r, const FxSurf<R>& sf, const FxMedium<R>& md, int kind,
-                                        const FxInfo& info, const R* coef, bool valid, unsigned long long* resid,
-                                        R& att) {
+                                        const FxInfo& info, int K, const R* coef, bool valid,
+                                        unsigned long long* resid, R& att) {
   typedef FxMath<R> Mx;
   fx_localize(r, sf, kind);
   R t = fx_conic_t(r.x, r.y, r.z, r.L, r.M, r.N, sf, (kind & FX_SPHERE) != 0);
-  const int K = info.K, m = info.ncoef;
+  const int m = info.ncoef;
   R xi, yi, zi, zx, zy, fp, r2;
   for (int j = 0;; ++j) {
     xi = fma(t, r.L, r.x); yi = fma(t, r.M, r.y); zi = fma(t, r.N, r.z);
@@ -339,6 +339,16 @@ __device__ __forceinline__ void fx_even(RayState<R>& r, const FxSurf<R>& sf, con
   fx_globalize(r, sf, kind);
 }
 
+// group mode: add one group's residual maxima (shared, [S][OLRT_GROUP_RESID]) to its global rows and clear them.
+// Called by the whole CTA between two __syncthreads().
+__device__ __forceinline__ void fx_group_flush(unsigned long long* group_resid, int g, int S, unsigned long long* s_resid) {
+  for (int q = threadIdx.x; q < S * OLRT_GROUP_RESID; q += blockDim.x) {
+    const unsigned long long v = s_resid[q];
+    if (v != 0ull) atomicMax(group_resid + (long long)g * S * OLRT_GROUP_RESID + q, v);
+    s_resid[q] = 0ull;
+  }
+}
+
 // warp-reduce one thread's spot sums and add them to the group's row (one set of atomics per warp; a CTA
 // flushes once per field it visits). Column layout: include/olrt.h, olrt_spot_sums_*.
 __device__ __forceinline__ void fx_spot_flush(double* spot, int g, double cnt, double sx, double sy, double sxx,
@@ -372,11 +382,14 @@ trace_fx_kernel(const FwdParams<R> P) {
   int32_t* s_ops = reinterpret_cast<int32_t*>(s_info + S);
   unsigned long long* s_resid = reinterpret_cast<unsigned long long*>(s_ops + ((P.ops_len + 3) & ~3));
   __shared__ int s_bad, s_nresid;
+  __shared__ int s_gk[OLRT_MAX_SURFACES];  // group mode: the current group's Newton trip counts
 
   for (int q = threadIdx.x; q < P.ops_len; q += blockDim.x) s_ops[q] = P.ops[q];
   if (threadIdx.x == 0) s_bad = 0;
   __syncthreads();
-  const bool want_resid = (P.nr_resid != nullptr);
+  // group mode: per-(trial, field) Newton trip counts and residual maxima (FwdParams::group_k)
+  const bool gmode = (P.gen.px != nullptr) && (P.group_k != nullptr);
+  const bool want_resid = gmode ? (P.group_resid != nullptr) : (P.nr_resid != nullptr);
   if (threadIdx.x < S) {
     const int k = fk_kind(s_ops, threadIdx.x);
     s_info[threadIdx.x].kind = k;
@@ -387,7 +400,8 @@ trace_fx_kernel(const FwdParams<R> P) {
     for (int s = 0; s < S; ++s) {
       s_info[s].roff = off;
       const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
-      if (want_resid && op[OLRT_OP_GEOM] >= OLRT_GEOM_EVEN_ASPHERE) off += op[OLRT_OP_NR_ITERS] + 1;
+      if (gmode) { if (want_resid) off += OLRT_GROUP_RESID; }
+      else if (want_resid && op[OLRT_OP_GEOM] >= OLRT_GEOM_EVEN_ASPHERE) off += op[OLRT_OP_NR_ITERS] + 1;
     }
     s_nresid = off;
   }
@@ -401,21 +415,30 @@ trace_fx_kernel(const FwdParams<R> P) {
   __syncthreads();
 
   uint32_t status = 0;
-  int cur_p = -1;
-  // pupil mode (olrt_trace_pupil_*): the launch covers pupil points [p_lo, p_lo + len) of every field; a tile
-  // never straddles two fields, ray (f, p) lives at index f * n_pupil + p of the output arrays
+  int cur_p = -1, cur_g = -1;
+  // pupil mode (olrt_trace_pupil_*): the launch covers pupil points [p_lo, p_lo + len) of every GROUP
+  // g = prescription * n_fields + field (Monte-Carlo trials x fields); a tile never straddles two groups, ray
+  // (g, p) lives at index g * n_pupil + p of the output arrays and belongs to spot group g. Each CTA walks a
+  // contiguous range of tiles, so it stays inside one prescription / one spot group as long as possible.
   const bool pupil = (P.gen.px != nullptr);
-  const long long tpf = pupil ? (P.gen.len + blockDim.x - 1) / blockDim.x : 0;  // tiles per field
-  const long long n_tiles = pupil ? tpf * P.gen.n_fields : (P.n_rays + blockDim.x - 1) / blockDim.x;
+  const long long tpf = pupil ? (P.gen.len + blockDim.x - 1) / blockDim.x : 0;  // tiles per group
+  const long long n_tiles = pupil ? tpf * P.gen.n_fields * P.n_presc : (P.n_rays + blockDim.x - 1) / blockDim.x;
   const long long NT = P.n_total;
+  long long tile_lo = blockIdx.x, tile_hi = n_tiles, tile_step = gridDim.x;
+  if (pupil) {
+    tile_lo = n_tiles * blockIdx.x / gridDim.x;
+    tile_hi = n_tiles * (blockIdx.x + 1) / gridDim.x;
+    tile_step = 1;
+  }
   // fused spot epilogue: per-thread sums for the current group, flushed when the group changes
   const bool want_spot = (P.spot != nullptr);
   int sp_g = -1;
   double sp_cnt = 0, sp_x = 0, sp_y = 0, sp_xx = 0, sp_yy = 0, sp_i = 0, sp_max = 0, sp_sx = 0, sp_sy = 0;
   bool sp_nan = false;
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  for (long long tile = tile_lo; tile < tile_hi; tile += tile_step) {
     const long long base = tile * blockDim.x;
-    const int p = (P.n_presc > 1) ? (int)(base / P.rays_per_presc) : 0;
+    const int grp = pupil ? (int)(tile / tpf) : 0;
+    const int p = (P.n_presc > 1) ? (pupil ? grp / P.gen.n_fields : (int)(base / P.rays_per_presc)) : 0;
     if (p != cur_p) {
       __syncthreads();
       const R* src = P.presc + (long long)p * P.presc_stride;
@@ -427,18 +450,28 @@ trace_fx_kernel(const FwdParams<R> P) {
                             P.four_pi);
       __syncthreads();
     }
+    if (gmode && grp != cur_g) {  // next (trial, field): hand its residual maxima over, fetch its trip counts
+      __syncthreads();
+      if (want_resid && cur_g >= 0) fx_group_flush(P.group_resid, cur_g, S, s_resid);
+      if (threadIdx.x < S) {
+        int k = P.group_k[(long long)grp * S + threadIdx.x];
+        s_gk[threadIdx.x] = k < OLRT_GROUP_RESID ? k : OLRT_GROUP_RESID - 1;
+      }
+      cur_g = grp;
+      __syncthreads();
+    }
     RayState<R> r;
     bool valid;
     long long idx;
     int group = 0;
     int widx = 0;
     if (pupil) {
-      const int f = (int)(tile / tpf);
-      const long long pp = (tile - (long long)f * tpf) * blockDim.x + threadIdx.x;
+      const int f = grp - p * P.gen.n_fields;
+      const long long pp = (tile - (long long)grp * tpf) * blockDim.x + threadIdx.x;
       valid = pp < P.gen.len;
       const long long pq = P.gen.p_lo + (valid ? pp : (P.gen.len - 1));
-      idx = (long long)f * P.gen.n_pupil + pq;
-      group = f;
+      idx = (long long)grp * P.gen.n_pupil + pq;
+      group = grp;
       double x0, y0, dL, dM, dN;
       gen_ray(P.gen, f, pq, x0, y0, dL, dM, dN);
       r.x = (R)x0; r.y = (R)y0; r.z = (R)P.gen.z_start; r.L = (R)dL; r.M = (R)dM; r.N = (R)dN;
@@ -472,7 +505,7 @@ trace_fx_kernel(const FwdParams<R> P) {
         case KIND_PLANE: fx_plane<R>(r, sf, md, kind, att); break;
         case KIND_CONIC: fx_conic<R>(r, sf, md, kind, att); break;
         default:
-          fx_even<R>(r, sf, md, kind, info, s_coef + info.coef_off, valid,
+          fx_even<R>(r, sf, md, kind, info, gmode ? s_gk[s] : info.K, s_coef + info.coef_off, valid,
                      want_resid ? (s_resid + info.roff) : nullptr, att);
           break;
       }
@@ -530,7 +563,9 @@ trace_fx_kernel(const FwdParams<R> P) {
   if (want_spot && sp_g >= 0) fx_spot_flush(P.spot, sp_g, sp_cnt, sp_x, sp_y, sp_xx, sp_yy, sp_i, sp_max, sp_nan);
 
   __syncthreads();
-  if (want_resid) {
+  if (gmode) {
+    if (want_resid && cur_g >= 0) fx_group_flush(P.group_resid, cur_g, S, s_resid);
+  } else if (want_resid) {
     for (int s = 0; s < S; ++s) {
       const int lo = s_info[s].roff, hi = (s + 1 < S) ? s_info[s + 1].roff : n_resid;
       for (int q = lo + threadIdx.x; q < hi; q += blockDim.x) {

@@ -18,6 +18,7 @@ struct SurfParams {      // one surface's view of the prescription staged in sha
   const R* coef;         // NCOEF reals
   const R* aper;         // aperture leaf parameters
   int geom, ncoef, aux;
+  int nr_iters;          // K_s: Newton updates at this surface (ops word 6, or the ray's group in group mode)
 };
 
 template <typename R>

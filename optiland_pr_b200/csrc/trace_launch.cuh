@@ -18,9 +18,9 @@ inline int sm_count() {
 }
 
 // block size: 256 unless the prescription batch needs tiles that do not straddle prescriptions
-inline int pick_block(const olrt_sys* sys, bool fk, bool fx) {
+inline int pick_block(const olrt_sys* sys, bool fk, bool fx, bool pupil) {
 #ifdef OLRT_FX
-  if (sys->n_presc <= 1 && fx) return OLRT_FX_BLOCK;
+  if ((sys->n_presc <= 1 || pupil) && fx) return OLRT_FX_BLOCK;  // pupil mode: tiles never straddle groups
 #else
   (void)fx;
 #endif
@@ -40,7 +40,8 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
                long long n_rays, const R* const in[8], const R* opd_in, R* const out[8], R* record,
                R* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags,
                cudaStream_t stream, const GenParams* gen = nullptr, double* spot = nullptr,
-               const double* spot_shift = nullptr, int spot_flags = 0) {
+               const double* spot_shift = nullptr, int spot_flags = 0, const int32_t* group_k = nullptr,
+               unsigned long long* group_resid = nullptr) {
   FwdParams<R> P;
   for (int q = 0; q < 8; ++q) { P.in[q] = in ? in[q] : nullptr; P.out[q] = out ? out[q] : nullptr; }
   P.opd_in = opd_in; P.record = record; P.dir0 = dir0; P.presc = presc; P.ops = ops;
@@ -55,9 +56,11 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
   P.gen.px = nullptr;
   if (gen != nullptr) {  // pupil mode: n_rays = rays of this launch, arrays span every field's full pupil grid
     P.gen = *gen;
-    P.n_total = gen->n_pupil * gen->n_fields;
+    P.n_total = gen->n_pupil * gen->n_fields * sys->n_presc;
   }
   P.spot = spot; P.spot_shift = spot_shift; P.spot_flags = spot_flags;
+  P.group_k = (gen != nullptr) ? group_k : nullptr;
+  P.group_resid = (gen != nullptr && group_k != nullptr) ? group_resid : nullptr;
 
   const bool fk = (sys->kernel_hint & OLRT_HINT_FASTKINDS) != 0;
 #ifdef OLRT_FX
@@ -66,9 +69,11 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
   const bool fx = false;
   (void)flags;
 #endif
-  const int block = pick_block(sys, fk, fx);
+  const int block = pick_block(sys, fk, fx, gen != nullptr);
   if (block == 0) return OLRT_E_ARG;
-  const int resid_words = nr_resid ? sys->nr_resid_words : 0;
+  int resid_words = nr_resid ? sys->nr_resid_words : 0;
+  if (P.group_resid != nullptr && resid_words < sys->n_surfaces * OLRT_GROUP_RESID)
+    resid_words = sys->n_surfaces * OLRT_GROUP_RESID;
   const size_t smem = (size_t)((sys->presc_stride + 1) & ~1) * sizeof(R) +
                       (size_t)((sys->n_surfaces * der_stride(sys->n_wavelengths) + 1) & ~1) * sizeof(R) +
                       (size_t)((sys->ops_len + 1) & ~1) * sizeof(int32_t) +
@@ -82,7 +87,7 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
   long long n_tiles = (n_rays + block - 1) / block;
   if (gen != nullptr) {
     if (!fx) return OLRT_E_UNSUPPORTED;  // in-kernel ray launch exists in the reduced-algebra kernel only
-    n_tiles = ((gen->len + block - 1) / block) * gen->n_fields;
+    n_tiles = ((gen->len + block - 1) / block) * gen->n_fields * sys->n_presc;
   }
   if (spot != nullptr && (!fx || gen == nullptr || spot_shift == nullptr)) return OLRT_E_UNSUPPORTED;
   if (P.fixup != nullptr) cudaMemsetAsync(P.fixup, 0, sizeof(uint32_t), stream);

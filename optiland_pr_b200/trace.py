@@ -215,12 +215,19 @@ def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, 
                       p_len: int | None = None, dtype=torch.float64, out: torch.Tensor | None = None,
                       dir0: torch.Tensor | None = None, spot: torch.Tensor | None = None,
                       spot_shift: torch.Tensor | None = None, spot_valid_only: bool = False,
-                      resid_out: torch.Tensor | None = None, status_t: torch.Tensor | None = None) -> None:
+                      resid_out: torch.Tensor | None = None, status_t: torch.Tensor | None = None,
+                      presc: torch.Tensor | None = None, group_k: torch.Tensor | None = None,
+                      group_resid: torch.Tensor | None = None) -> None:
     """Enqueue `olrt_trace_pupil_*` (include/olrt.h): launch the rays of every field for pupil points
     [p_lo, p_lo + p_len) in the kernel, trace them, optionally accumulate the spot sums. Nothing is read back:
     the caller owns `status_t`, `resid_out` (see fused_trace) and checks them after the last chunk.
     out: [8, F * P] or None (epilogue only); dir0: [3, F * P] or None; spot: [F, SPOT_SUMS] float64 (zeroed by
-    the caller); spot_shift: [F, 2] float64. Raises NotImplementedError where the C ABI answers
+    the caller); spot_shift: [F, 2] float64. presc: optional [n_presc, stride] device tensor (Monte-Carlo batch):
+    every prescription traces the same fields and pupil range, F above becomes n_presc * F (trial-major).
+    group_k: optional int32 [groups, n_surfaces] device tensor of Newton trip counts per group (trial x field)
+    instead of the batch-global counts in `packed`; group_resid: int64 [groups, n_surfaces, GROUP_RESID] (zeroed)
+    receives each group's residual maxima (`group_true_iters` applies the reference's exit rule to them).
+    Raises NotImplementedError where the C ABI answers
     OLRT_E_UNSUPPORTED (the caller then uses launch + fused_trace + spot_sums)."""
     lib = L.load()
     if not Px.is_cuda:
@@ -230,22 +237,47 @@ def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, 
     nf = int(field_xy.shape[0])
     p_len = npup - p_lo if p_len is None else p_len
     ops_d, presc_d = _device_tables(packed, dtype, device)
+    n_presc = 1
+    if presc is not None:
+        presc_d = presc.to(device=device, dtype=dtype).contiguous()
+        n_presc = int(presc_d.shape[0])
     pu = L.OlrtPupil(Px.data_ptr(), Py.data_ptr(), field_xy.data_ptr(), npup, int(p_lo), int(p_len), nf, 0,
                      float(EPD), float(EPL), float(z_start), float(wavelength))
-    sys_ = packed.make_sys()
+    sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=nf * p_len)
     sys_.presc_stride = int(presc_d.shape[1])
-    fixup = _fixup_workspace(nf * npup, device) if dtype == torch.float64 else None
+    n_total = n_presc * nf * npup
+    fixup = _fixup_workspace(n_total, device) if dtype == torch.float64 else None
     out_arr = None
     if out is not None:
-        if out.dtype != dtype or tuple(out.shape) != (8, nf * npup) or not out.is_contiguous():
-            raise ValueError("out must be a contiguous [8, n_fields * n_pupil] tensor of the trace dtype")
+        if out.dtype != dtype or tuple(out.shape) != (8, n_total) or not out.is_contiguous():
+            raise ValueError("out must be a contiguous [8, n_presc * n_fields * n_pupil] tensor of the trace dtype")
         out_arr = C.byref(L.PtrArray8(*[out[q].data_ptr() for q in range(8)]))
     fn = lib.olrt_trace_pupil_f64 if dtype == torch.float64 else lib.olrt_trace_pupil_f32
     with torch.cuda.device(device):
         rc = fn(C.byref(sys_), presc_d.data_ptr(), ops_d.data_ptr(), C.byref(pu), out_arr, _ptr(dir0),
                 _ptr(resid_out), _ptr(status_t), _ptr(fixup), _ptr(spot), _ptr(spot_shift),
-                L.SPOT_VALID_ONLY if spot_valid_only else 0, L.FWD_FAST,
+                L.SPOT_VALID_ONLY if spot_valid_only else 0, _ptr(group_k), _ptr(group_resid), L.FWD_FAST,
                 torch.cuda.current_stream(device).cuda_stream)
     if rc == -4:
         raise NotImplementedError("olrt_trace_pupil: this lens / mode needs the separate launch + trace kernels")
     L.check(rc, "olrt_trace_pupil")
+
+
+def group_true_iters(packed: PackedSystem, resid: np.ndarray, k_used: np.ndarray) -> np.ndarray:
+    """The reference's exit rule (newton_raphson.py:137-149) per group. resid: float64 view [G, S, GROUP_RESID] of
+    a `group_resid` buffer; k_used: int [G, S]. Returns int [G, S]: the trip counts each group satisfies the rule
+    with, -1 where it needs more than it was given (or more than GROUP_RESID - 1)."""
+    G = resid.shape[0]
+    out = np.zeros((G, packed.n_surfaces), dtype=np.int32)
+    for k in packed.nr_rows():
+        lay = packed.layouts[k]
+        r = resid[:, k, :]
+        bad = ~np.isfinite(r)
+        ok = (r < lay.tol_value) & ~bad
+        j = np.arange(L.GROUP_RESID)[None, :]
+        seen = j <= k_used[:, k][:, None]                 # slots the kernel actually reported
+        hit = ok & seen & (j < lay.max_iter)
+        first = np.where(hit.any(axis=1), hit.argmax(axis=1), -1)
+        first = np.where((bad & seen).any(axis=1), -1, first)   # a NaN ray: the reference runs max_iter
+        out[:, k] = first
+    return out
