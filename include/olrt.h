@@ -262,6 +262,32 @@ int olrt_trace_pupil_f32(const olrt_sys* sys, const float* presc, const int32_t*
                          uint32_t* fixup, double* spot_sums, const double* spot_shift, int spot_flags,
                          const int32_t* group_k, unsigned long long* group_resid, int flags, void* stream);
 
+/* OPD / wavefront epilogue: per ray, the optical path from the image surface back to the
+ * reference sphere, the launch-plane tilt correction and the OPD in waves relative to the chief ray --
+ * ReferenceStrategy._opd_image_to_xp (optiland/wavefront/strategy.py:68-116), _correct_tilt (:118-166) and steps
+ * 4-5 of ChiefRayStrategy.compute_wavefront_data (:203-229), in the reference's operation order (fp64: the same
+ * bits for the same traced rays). The reference sphere (centre = chief-ray image point, radius to the paraxial
+ * exit pupil, :231-240) and opd_ref are per-field scalars the caller derives from the chief ray with the same
+ * kernel (OLRT_OPD_RAW).
+ *  rays   [8] device ptrs x y z L M N intensity opd AT THE IMAGE SURFACE (intensity is not read)
+ *  Px, Py NULL, or [n] normalised pupil coordinates of the rays (tilt term; a chief ray passes NULL = 0, 0)
+ *  opd_out [n]: OPD in waves, (opd_ref - opd) / (wavelength * 1e-3); with OLRT_OPD_RAW the tilt-corrected
+ *          opd (mm) itself, which is what opd_ref is for the chief ray
+ *  pupil  NULL or [3][n]: intersection with the reference sphere (pupil_x, pupil_y, pupil_z)              */
+typedef struct olrt_refsphere {
+  double xc, yc, zc, R;    /* reference sphere */
+  double n_image;          /* index of the image space */
+  double opd_ref;          /* chief-ray OPD (mm), ignored with OLRT_OPD_RAW */
+  double wavelength;       /* micrometres */
+  double tilt_ux, tilt_uy; /* direction cosines of the field (angle fields), 0 0 otherwise */
+  double epd;              /* entrance pupil diameter */
+} olrt_refsphere;
+#define OLRT_OPD_RAW 1
+int olrt_opd_epilogue_f64(const double* const rays[8], const double* Px, const double* Py, int64_t n,
+                          const olrt_refsphere* sphere, double* opd_out, double* pupil, int flags, void* stream);
+int olrt_opd_epilogue_f32(const float* const rays[8], const double* Px, const double* Py, int64_t n,
+                          const olrt_refsphere* sphere, float* opd_out, float* pupil, int flags, void* stream);
+
 /* Self-test of the kernels' own IEEE division / square-root sequences (csrc/math64.cuh):
  * quot[i] = a[i] / b[i], root[i] = sqrt(a[i]) as the trace kernels compute them; the caller compares
  * them bit for bit with an IEEE implementation (tests/test_gpu_math.py). */

@@ -68,6 +68,14 @@ class OlrtPupil(C.Structure):
     ]
 
 
+class OlrtRefSphere(C.Structure):
+    """struct olrt_refsphere (include/olrt.h)."""
+
+    _fields_ = [(k, C.c_double) for k in ("xc", "yc", "zc", "R", "n_image", "opd_ref", "wavelength", "tilt_ux",
+                                          "tilt_uy", "epd")]
+
+
+OPD_RAW = 1
 PtrArray8 = C.c_void_p * 8
 
 # every symbol include/olrt.h declares (tests/test_abi.py checks the header against this list)
@@ -80,6 +88,7 @@ EXPORTS = [
     "olrt_selftest_math_f64",
     "olrt_generate_rays_f64", "olrt_generate_rays_f32",
     "olrt_trace_pupil_f64", "olrt_trace_pupil_f32",
+    "olrt_opd_epilogue_f64", "olrt_opd_epilogue_f32",
 ]
 
 _lib = None
@@ -127,6 +136,10 @@ def load():
         f.restype = C.c_int
         f.argtypes = [C.POINTER(OlrtSys), v, v, C.POINTER(OlrtPupil), C.POINTER(PtrArray8), v, v, v, v, v, v,
                       C.c_int, v, v, C.c_int, v]
+    for suf in ("f64", "f32"):
+        f = getattr(lib, f"olrt_opd_epilogue_{suf}")
+        f.restype = C.c_int
+        f.argtypes = [PtrArray8, v, v, C.c_int64, C.POINTER(OlrtRefSphere), v, v, C.c_int, v]
     lib.olrt_selftest_math_f64.restype = C.c_int
     lib.olrt_selftest_math_f64.argtypes = [v, v, v, v, C.c_int64, v]
     if lib.olrt_version() != OLRT_ABI_VERSION:

@@ -332,3 +332,28 @@ extern "C" int olrt_trace_bwd_f32(const olrt_sys* sys, const float* presc, const
   return olrt_fast::bwd_f32(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status,
                             (cudaStream_t)stream);
 }
+
+// ---------------------------------------------------------------------------------------------
+// OPD / wavefront epilogue (kernel in trace_strict.cu)
+// ---------------------------------------------------------------------------------------------
+template <typename R>
+static int check_opd(const R* const rays[8], long long n, const olrt_refsphere* s, const R* opd_out) {
+  if (!rays || !s || n < 0) return OLRT_E_ARG;
+  if (n == 0) return OLRT_OK;
+  for (int q = 0; q < 8; ++q) if (q != 6 && !rays[q]) return OLRT_E_ARG;
+  return opd_out ? OLRT_OK : OLRT_E_ARG;
+}
+extern "C" int olrt_opd_epilogue_f64(const double* const rays[8], const double* Px, const double* Py, int64_t n,
+                                     const olrt_refsphere* sphere, double* opd_out, double* pupil, int flags,
+                                     void* stream) {
+  const int rc = check_opd<double>(rays, n, sphere, opd_out);
+  if (rc || n == 0) return rc;
+  return olrt_strict::opd_f64(rays, Px, Py, n, sphere, opd_out, pupil, flags, (cudaStream_t)stream);
+}
+extern "C" int olrt_opd_epilogue_f32(const float* const rays[8], const double* Px, const double* Py, int64_t n,
+                                     const olrt_refsphere* sphere, float* opd_out, float* pupil, int flags,
+                                     void* stream) {
+  const int rc = check_opd<float>(rays, n, sphere, opd_out);
+  if (rc || n == 0) return rc;
+  return olrt_strict::opd_f32(rays, Px, Py, n, sphere, opd_out, pupil, flags, (cudaStream_t)stream);
+}

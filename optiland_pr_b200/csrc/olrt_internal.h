@@ -44,3 +44,10 @@ int generate_f64(const double* Px, const double* Py, long long n_pupil, const do
 int generate_f32(const double* Px, const double* Py, long long n_pupil, const double* field_xy, int n_fields,
                  double EPD, double EPL, double z_start, double wavelength, float* const out[8], cudaStream_t st);
 }
+
+namespace olrt_strict {
+int opd_f64(const double* const rays[8], const double* Px, const double* Py, long long n, const olrt_refsphere* s,
+            double* opd_out, double* pupil, int flags, cudaStream_t st);
+int opd_f32(const float* const rays[8], const double* Px, const double* Py, long long n, const olrt_refsphere* s,
+            float* opd_out, float* pupil, int flags, cudaStream_t st);
+}

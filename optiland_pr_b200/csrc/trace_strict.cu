@@ -70,4 +70,61 @@ int generate_f32(const double* Px, const double* Py, long long n_pupil, const do
                  double EPD, double EPL, double z_start, double wavelength, float* const out[8], cudaStream_t st) {
   return launch_generate<float>(Px, Py, n_pupil, field_xy, n_fields, EPD, EPL, z_start, wavelength, out, st);
 }
+
+// OPD / wavefront epilogue, wavefront/strategy.py:68-116, :118-166, :203-229. This TU is built -fmad=false and
+// uses IEEE division / sqrt: for the same traced rays the fp64 results are the reference's bits. Streaming kernel
+// (56 B in, 8-32 B out per ray): HBM bound, the arithmetic is free.
+template <typename R>
+__global__ void __launch_bounds__(256) opd_epilogue_kernel(const R* __restrict__ x, const R* __restrict__ y,
+                                                           const R* __restrict__ z, const R* __restrict__ L,
+                                                           const R* __restrict__ M, const R* __restrict__ N,
+                                                           const R* __restrict__ opd_in, const double* __restrict__ Px,
+                                                           const double* __restrict__ Py, long long n,
+                                                           const olrt_refsphere S, R* opd_out, R* pupil, int flags) {
+  for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+    const double xr = (double)x[r], yr = (double)y[r], zr = (double)z[r];
+    const double l0 = (double)L[r], m0 = (double)M[r], n0 = (double)N[r];
+    const double l = -l0, m = -m0, nn = -n0;
+    const double a = l * l + m * m + nn * nn;
+    const double b = 2.0 * (l * (xr - S.xc) + m * (yr - S.yc) + nn * (zr - S.zc));
+    const double c = xr * xr + yr * yr + zr * zr - 2.0 * (xr * S.xc + yr * S.yc + zr * S.zc) + S.xc * S.xc +
+                     S.yc * S.yc + S.zc * S.zc - S.R * S.R;
+    double d = b * b - 4.0 * a * c;
+    if (d < 0.0) d = 0.0;
+    const double sd = sqrt(d);
+    double t = (-b - sd) / (2.0 * a);
+    if (t < 0.0) t = (-b + sd) / (2.0 * a);
+    const double opd_img = S.n_image * t;
+    double opd = (double)opd_in[r] - opd_img;
+    if (S.tilt_ux != 0.0 || S.tilt_uy != 0.0 || Px != nullptr) {  // AngleField: remove the launch-plane tilt
+      const double px = Px ? Px[r] : 0.0, py = Py ? Py[r] : 0.0;
+      opd = opd + (S.tilt_ux * (px * S.epd / 2.0) + S.tilt_uy * (py * S.epd / 2.0));
+    }
+    opd_out[r] = (R)((flags & OLRT_OPD_RAW) ? opd : (S.opd_ref - opd) / (S.wavelength * 1e-3));
+    if (pupil != nullptr) {
+      const double t2 = opd_img / S.n_image;
+      pupil[r] = (R)(xr - t2 * l0);
+      pupil[n + r] = (R)(yr - t2 * m0);
+      pupil[2 * n + r] = (R)(zr - t2 * n0);
+    }
+  }
+}
+template <typename R>
+static int launch_opd(const R* const rays[8], const double* Px, const double* Py, long long n, const olrt_refsphere* s,
+                      R* opd_out, R* pupil, int flags, cudaStream_t st) {
+  long long grid = (long long)sm_count() * 8;
+  const long long need = (n + 255) / 256;
+  if (grid > need) grid = need;
+  opd_epilogue_kernel<R><<<(unsigned)grid, 256, 0, st>>>(rays[0], rays[1], rays[2], rays[3], rays[4], rays[5], rays[7],
+                                                         Px, Py, n, *s, opd_out, pupil, flags);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+int opd_f64(const double* const rays[8], const double* Px, const double* Py, long long n, const olrt_refsphere* s,
+            double* opd_out, double* pupil, int flags, cudaStream_t st) {
+  return launch_opd<double>(rays, Px, Py, n, s, opd_out, pupil, flags, st);
+}
+int opd_f32(const float* const rays[8], const double* Px, const double* Py, long long n, const olrt_refsphere* s,
+            float* opd_out, float* pupil, int flags, cudaStream_t st) {
+  return launch_opd<float>(rays, Px, Py, n, s, opd_out, pupil, flags, st);
+}
 }  // namespace olrt_strict

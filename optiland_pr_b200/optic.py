@@ -59,6 +59,7 @@ class Optic:
         self.aperture = None
         self._EPL = None
         self._EPD = None
+        self._XPL = None
 
     # ---- construction ------------------------------------------------------------------------
     def add_surface(self, **kwargs):
@@ -81,11 +82,14 @@ class Optic:
         if is_primary:
             self.primary_index = len(self.wavelengths) - 1
 
-    def set_paraxial(self, EPL, EPD=None):
-        """Entrance-pupil location / diameter (optiland/paraxial.py:207-280), supplied by the caller."""
+    def set_paraxial(self, EPL, EPD=None, XPL=None):
+        """Entrance-pupil location / diameter and exit-pupil location relative to the image surface
+        (optiland/paraxial.py:207-280, :282-310), supplied by the caller."""
         self._EPL = float(EPL)
         if EPD is not None:
             self._EPD = float(EPD)
+        if XPL is not None:
+            self._XPL = float(XPL)
 
     # ---- OpticUpdater subset used by the optimisation variables (optic/optic_updater.py:38-142) ------
     def set_radius(self, value, surface_number):

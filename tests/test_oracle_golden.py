@@ -39,3 +39,23 @@ def test_fixed_iteration_replay_equals_exit_rule(name):
     b = trace_np.trace_packed(packed, trace_np.Rays(*g["rays_in"]), fixed_iters=a["nr_iters"])
     assert np.array_equal(np.array(a["records"]), np.array(b["records"]), equal_nan=True)
     assert rel_err(np.array(a["records"]), g["records"]) == 0.0
+
+
+def test_wavefront_oracle_bit_exact():
+    """oracle/wavefront_np.py against Wavefront(..., strategy="chief_ray").get_data of the unmodified reference
+    (tests/golden/wavefront_cooke.npz, oracle/make_golden_wavefront.py): same bits for the OPD map in waves, the
+    exit-pupil intersection points and the reference-sphere radius."""
+    from oracle import wavefront_np
+    g = load_golden("wavefront_cooke")
+    names = ("x", "y", "z", "L", "M", "N", "opd")
+    for k, f in enumerate(g["fields"]):
+        rays = {n: g[f"f{k}_rays"][q] for q, n in enumerate(names)}
+        rays["i"] = g[f"f{k}_rays"][7]
+        chief = {n: g[f"f{k}_chief"][q] for q, n in enumerate(names)}
+        got = wavefront_np.chief_ray_wavefront(rays, chief, tuple(f), float(g["wavelength"]), g["px"], g["py"],
+                                               epd=float(g["EPD"]), max_field=float(g["max_field"]),
+                                               pupil_z=float(g["pupil_z"]), n_image=float(g["n_image"]))
+        assert got["radius"] == float(g[f"f{k}_radius"])
+        assert np.array_equal(got["opd"], g[f"f{k}_opd"], equal_nan=True)
+        assert np.array_equal(np.stack([got["pupil_x"], got["pupil_y"], got["pupil_z"]]), g[f"f{k}_pupil"], equal_nan=True)
+        assert np.array_equal(got["intensity"], g[f"f{k}_intensity"])
