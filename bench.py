@@ -194,6 +194,21 @@ def main():
     zero1 = torch.zeros(1, dtype=torch.float64, device=dev)
     chief = torch.empty((8, nf), dtype=torch.float64, device=dev)
 
+    # multi-GPU: the merit exchange of step k (one all-gather of the [3][10] sums, < 1 KB) runs on NCCL's stream
+    # while step k+1 traces; it is merged one step later (double-buffered)
+    sums2 = [torch.zeros_like(sums) for _ in range(2)]
+    parts2 = [[torch.empty_like(sums) for _ in range(world)] for _ in range(2)]
+    works = [None, None]
+
+    def merge(slot_):
+        works[slot_].wait()
+        works[slot_] = None
+        buf = torch.stack(parts2[slot_])
+        m = buf.sum(dim=0)
+        m[:, 5] = buf[:, :, 5].amax(dim=0)
+        m[:, 7:] = sums2[slot_][:, 7:]
+        sums.copy_(m)
+
     resid_h = [torch.zeros(resid.shape, dtype=torch.int64).pin_memory() for _ in range(2)]
     resid_ev = [None, None]
     tick = [0]
@@ -210,15 +225,18 @@ def main():
         The Newton trip counts every step used are checked against the reference's exit rule from the residual
         maxima the kernel reports; the (small) read-back of step k is examined while step k+1 runs."""
         slot = tick[0] & 1
-        sums.zero_()
+        cur = sums2[slot] if world > 1 else sums
+        cur.zero_()
         resid.zero_()
         fused_trace_pupil(packed, zero1, zero1, fxy_d, out=chief, **gen_kw)          # chief rays -> spot shift
         shift = chief[:2].t().nan_to_num(0.0, 0.0, 0.0).contiguous()
-        fused_trace_pupil(packed, Px_d, Py_d, fxy_d, out=out, spot=sums, spot_shift=shift, resid_out=resid,
+        fused_trace_pupil(packed, Px_d, Py_d, fxy_d, out=out, spot=cur, spot_shift=shift, resid_out=resid,
                           status_t=status_t, **gen_kw)
-        sums[:, 8:10] = shift
+        cur[:, 8:10] = shift
         if world > 1:
-            sums.copy_(parallel.allreduce_spot_sums(sums))
+            works[slot] = dist.all_gather(parts2[slot], cur, async_op=True)
+            if works[slot ^ 1] is not None:
+                merge(slot ^ 1)
         resid_h[slot].copy_(resid, non_blocking=True)
         resid_ev[slot] = torch.cuda.Event()
         resid_ev[slot].record()
@@ -271,9 +289,13 @@ def main():
         sampler.start()
     ms_step = timed(step_resident, args.steps, max(args.warmup, 3))
     clocks = sampler.stop() if rank == 0 else None
-    for slot in (0, 1):   # the last step's residuals
+    for slot in (0, 1):   # the last step's residuals and merit exchange
         if resid_ev[slot] is not None and not check_newton(slot):
             raise SystemExit("Newton trip counts changed between steps")
+    last = (tick[0] - 1) & 1
+    for slot in (last ^ 1, last):
+        if works[slot] is not None:
+            merge(slot)
     launches_per_step = 4  # (chief rays + batch) x (fused launch/trace/spot kernel + its IEEE fix-up pass)
     value = n * S_eff * world / (ms_step * 1e-3)
     rms_resident = spot.spot_stats(sums)["rms"].cpu().tolist()
