@@ -460,12 +460,66 @@ def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64
     out["fp64_fma_peak_tflops"] = fp64_peak
     out["fp32_fma_peak_tflops"] = fp32_peak
     out.update(bench_monte_carlo(torch, lens, S_eff))
+    out.update(bench_other_configs(torch, timed, args))
     try:
         from optiland_pr_b200.autograd import bench_backward
     except ImportError:
         bench_backward = None
     if bench_backward is not None:
         out.update(bench_backward(lens, packed, ins64, timed, args, fp64_peak))
+    return out
+
+
+def bench_other_configs(torch, timed, args):
+    """BASELINE configs C1 (Cooke triplet, 3 fields x 3 wavelengths x 1M rays, RMS spot per pair) and C3 (off-axis
+    three-mirror polynomial freeform system: Newton-Raphson on every mirror, tilts, decenters -- the interpreter
+    kernel) as throughput figures next to the headline; their VALUES are pinned by the parity tests."""
+    from optiland_pr_b200 import samples, spot
+    from optiland_pr_b200.trace import fused_trace
+    out = {}
+    dev = torch.device("cuda", torch.cuda.current_device())
+    # ---- C1
+    lens = samples.CookeTriplet()
+    lens.surface_group.record = "none"
+    n1 = 1_000_000
+    rng = np.random.default_rng(0)
+    r_, th = rng.uniform(size=n1), rng.uniform(0, 2 * np.pi, size=n1)
+    Px = torch.from_numpy(np.sqrt(r_) * np.cos(th)).to(dev)
+    Py = torch.from_numpy(np.sqrt(r_) * np.sin(th)).to(dev)
+    S1 = lens.surface_group.num_surfaces - 1
+
+    def c1():       # SpotDiagram: all 9 (field, wavelength) pairs in one fused launch per pass, two passes
+        sd = spot.SpotDiagram(lens, distribution=(Px, Py))
+        return sd._rms.cpu()
+
+    ms = timed(c1, max(2, args.steps // 2), 3)
+    out["c1_cooke_9_pairs_x_1M"] = {"ms": ms, "ray_surfaces_per_s": 2 * 9 * n1 * S1 / (ms * 1e-3),
+                                    "passes": 2,
+                                    "api": "spot.SpotDiagram(lens): centroid pass + radius pass over 3 fields x 3 "
+                                           "wavelengths, one fused launch + trace + spot kernel each, RMS -> host"}
+    # ---- C3
+    lens = samples.ThreeMirrorAnastigmat()
+    wl = lens.primary_wavelength
+    n3 = 1 << 24
+    r_, th = rng.uniform(size=n3), rng.uniform(0, 2 * np.pi, size=n3)
+    Px = torch.from_numpy(np.sqrt(r_) * np.cos(th)).to(dev)
+    Py = torch.from_numpy(np.sqrt(r_) * np.sin(th)).to(dev)
+    f0 = lens.get_field_coords()[0]
+    rays = lens.launch_rays(np.array([f0[0]]), np.array([f0[1]]), Px, Py, wl)
+    ins = rays.components()
+    ins[7] = None
+    lens.surface_group.record = "none"
+    packed = lens.surface_group.pack([float(wl)])
+    o = torch.empty((8, n3), dtype=torch.float64, device=dev)
+    res = fused_trace(packed, ins, out=o, fast=True)           # settles the Newton counts
+    S3 = lens.surface_group.num_surfaces - 1
+    for name, fast in (("tolerance", True), ("strict", False)):
+        ms = timed(lambda: fused_trace(packed, ins, out=o, fast=fast, verify_nr=False, check_status=False),
+                   max(2, args.steps // 2), 2)
+        out["c3_three_mirror_freeform_16M_" + name] = {"ms": ms, "ray_surfaces_per_s": n3 * S3 / (ms * 1e-3),
+                                                       "nr_iters": res.nr_iters,
+                                                       "kernel": "trace_fwd_kernel (interpreter: 4x4 polynomial "
+                                                                 "freeforms, Newton-Raphson, tilts, decenters)"}
     return out
 
 

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define OLRT_ABI_VERSION 3
+#define OLRT_ABI_VERSION 4
 
 #define OLRT_MAX_SURFACES 64    /* intersected surfaces per system (object surface excluded) */
 #define OLRT_MAX_WAVELENGTHS 8  /* distinct wavelengths per launch */
@@ -200,21 +200,38 @@ int olrt_spot_sums_f32(const float* x, const float* y, const float* intensity, i
 int olrt_fma_peak_f64(double* sink, int64_t iters, int blocks, int threads, void* stream);
 int olrt_fma_peak_f32(float* sink, int64_t iters, int blocks, int threads, void* stream);
 
-/* Ray launch: RayGenerator.generate_rays (optiland/rays/ray_generator.py:28-106) with
- * AngleField.get_ray_origins (optiland/fields/field_types.py:139-169) for an object at infinity, angle
- * fields, no vignetting factors. Rays are field-major (ray f * n_pupil + p), as RealRayTracer.trace builds
- * them (raytrace/real_ray_tracer.py:67-77).
- *  Px, Py    [n_pupil] doubles (device): normalised pupil coordinates
- *  field_xy  [n_fields][2] doubles (device): -tan(radians(max_field * H)) * (offset + EPL) per field, x then y
- *  EPD, EPL  entrance pupil diameter / location (paraxial.py:207-280); z_start = positions[1] - offset
- *  out       [8] device ptrs x y z L M N intensity wavelength (entry 7 may be NULL); fp64 arithmetic, stored
- *            in the output precision                                                                    */
-int olrt_generate_rays_f64(const double* Px, const double* Py, int64_t n_pupil, const double* field_xy,
-                           int32_t n_fields, double EPD, double EPL, double z_start, double wavelength,
-                           double* const out[8], void* stream);
-int olrt_generate_rays_f32(const double* Px, const double* Py, int64_t n_pupil, const double* field_xy,
-                           int32_t n_fields, double EPD, double EPL, double z_start, double wavelength,
-                           float* const out[8], void* stream);
+/* Ray launch: RayGenerator.generate_rays (optiland/rays/ray_generator.py:28-106, the
+ * non-telecentric branch) with the ray origins of AngleField.get_ray_origins (optiland/fields/field_types.py:139-169:
+ * object at infinity or finite) and ObjectHeightField.get_ray_origins (:245-272) and the per-field vignetting
+ * factors of FieldGroup.get_vig_factor (fields/field_group.py:80-109). Everything per FIELD is a host scalar
+ * (a handful of values per field), everything per RAY is in the kernel, in the reference's operation order.
+ * Rays are field-major (ray f * n_pupil + p), as RealRayTracer.trace builds them (raytrace/real_ray_tracer.py:67-77).
+ *  Px, Py     [n_pupil] doubles (device): normalised pupil coordinates
+ *  field_xy   [n_fields][2] doubles (device), x then y.
+ *             field_z == NULL (object at infinity): -tan(radians(max_field * H)) * (offset + EPL); the ray starts
+ *             at (Px EPD / 2 vx + field_x, Py EPD / 2 vy + field_y, z_start), z_start = positions[1] - offset.
+ *             field_z != NULL (finite object): the object POINT of the field, (field_x, field_y, field_z[f]) --
+ *             -tan(radians(max_field * H)) * (EPL - z_obj) on the object plane for angle fields, (max_field * H,
+ *             sag + z_obj) for object-height fields; every ray of the field starts there; z_start is not read.
+ *  field_vig  NULL (no vignetting), or [n_fields][2] doubles (device): vx = 1 - vig_x, vy = 1 - vig_y
+ *             (ray_generator.py:50-52); the ray aims at (Px EPD vx / 2, Py EPD vy / 2, EPL).
+ *  EPD, EPL   entrance pupil diameter / location (paraxial.py:207-280)
+ *  out        [8] device ptrs x y z L M N intensity wavelength (entry 7 may be NULL); fp64 arithmetic, stored
+ *             in the output precision. p_lo / p_len are ignored here (all n_pupil points are launched).        */
+typedef struct olrt_pupil {
+  const double* Px;        /* [n_pupil] normalised pupil coordinates (device) */
+  const double* Py;
+  const double* field_xy;  /* [n_fields][2] (device) */
+  const double* field_vig; /* NULL or [n_fields][2] (device) */
+  const double* field_z;   /* NULL or [n_fields] (device) */
+  int64_t n_pupil;         /* pupil points per field */
+  int64_t p_lo, p_len;     /* olrt_trace_pupil_*: the pupil range this call traces */
+  int32_t n_fields;
+  int32_t reserved0;
+  double EPD, EPL, z_start, wavelength;
+} olrt_pupil;
+int olrt_generate_rays_f64(const olrt_pupil* pupil, double* const out[8], void* stream);
+int olrt_generate_rays_f32(const olrt_pupil* pupil, float* const out[8], void* stream);
 
 /* Fused ray launch + trace + spot epilogue ("pupil mode"): what RealRayTracer.trace does per call
  * (raytrace/real_ray_tracer.py:61-82: generate the rays of every field from one pupil grid, then
@@ -232,16 +249,6 @@ int olrt_generate_rays_f32(const double* Px, const double* Py, int64_t n_pupil, 
  * OLRT_FWD_FAST for fp64; olrt_sys.kernel_hint & OLRT_HINT_FASTKINDS; one wavelength, no
  * per-surface records): anything else returns OLRT_E_UNSUPPORTED and the caller uses
  * olrt_generate_rays_* + olrt_trace_fwd_* + olrt_spot_sums_*.                                              */
-typedef struct olrt_pupil {
-  const double* Px;        /* [n_pupil] normalised pupil coordinates (device) */
-  const double* Py;
-  const double* field_xy;  /* [n_fields][2] (device), as for olrt_generate_rays_* */
-  int64_t n_pupil;         /* pupil points per field */
-  int64_t p_lo, p_len;     /* the pupil range this call traces */
-  int32_t n_fields;
-  int32_t reserved0;
-  double EPD, EPL, z_start, wavelength;
-} olrt_pupil;
 /*  out        NULL, or [8] device ptrs to arrays of n_fields * n_pupil (x y z L M N intensity opd)
  *  dir0       NULL or [3][n_fields * n_pupil]
  *  spot_sums  NULL or [n_fields][OLRT_SPOT_SUMS], zeroed by the caller before the first chunk; columns as for

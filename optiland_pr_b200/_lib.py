@@ -12,7 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("OLRT_LIB") or os.path.join(_HERE, "libolrt.so")  # OLRT_LIB: A/B builds only
 
-OLRT_ABI_VERSION = 3
+OLRT_ABI_VERSION = 4
 MAX_SURFACES = 64
 MAX_WAVELENGTHS = 8
 MAX_NR_ITERS = 128
@@ -62,6 +62,7 @@ class OlrtPupil(C.Structure):
 
     _fields_ = [
         ("Px", C.c_void_p), ("Py", C.c_void_p), ("field_xy", C.c_void_p),
+        ("field_vig", C.c_void_p), ("field_z", C.c_void_p),
         ("n_pupil", C.c_int64), ("p_lo", C.c_int64), ("p_len", C.c_int64),
         ("n_fields", C.c_int32), ("reserved0", C.c_int32),
         ("EPD", C.c_double), ("EPL", C.c_double), ("z_start", C.c_double), ("wavelength", C.c_double),
@@ -130,7 +131,7 @@ def load():
     for suf in ("f64", "f32"):
         f = getattr(lib, f"olrt_generate_rays_{suf}")
         f.restype = C.c_int
-        f.argtypes = [v, v, C.c_int64, v, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double, PtrArray8, v]
+        f.argtypes = [C.POINTER(OlrtPupil), PtrArray8, v]
     for suf in ("f64", "f32"):
         f = getattr(lib, f"olrt_trace_pupil_{suf}")
         f.restype = C.c_int

@@ -260,30 +260,23 @@ extern "C" int olrt_fma_peak_f32(float* sink, int64_t iters, int blocks, int thr
   return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
 }
 
-static int check_generate(const void* Px, const void* Py, long long n_pupil, const void* fxy, int n_fields,
-                          void* const out[8]) {
-  if (!Px || !Py || !fxy || !out || n_pupil < 0 || n_fields < 1) return OLRT_E_ARG;
-  for (int q = 0; q < 7; ++q)
-    if (!out[q]) return OLRT_E_ARG;
+static int check_generate(const olrt_pupil* q, void* const out[8]) {
+  if (!q || !q->Px || !q->Py || !q->field_xy || !out || q->n_pupil < 0 || q->n_fields < 1) return OLRT_E_ARG;
+  for (int k = 0; k < 7; ++k)
+    if (!out[k]) return OLRT_E_ARG;
   return OLRT_OK;
 }
-extern "C" int olrt_generate_rays_f64(const double* Px, const double* Py, int64_t n_pupil, const double* field_xy,
-                                      int32_t n_fields, double EPD, double EPL, double z_start, double wavelength,
-                                      double* const out[8], void* stream) {
-  int rc = check_generate(Px, Py, n_pupil, field_xy, n_fields, (void* const*)out);
+extern "C" int olrt_generate_rays_f64(const olrt_pupil* pupil, double* const out[8], void* stream) {
+  int rc = check_generate(pupil, (void* const*)out);
   if (rc) return rc;
-  if (n_pupil == 0) return OLRT_OK;
-  return olrt_strict::generate_f64(Px, Py, n_pupil, field_xy, n_fields, EPD, EPL, z_start, wavelength, out,
-                                   (cudaStream_t)stream);
+  if (pupil->n_pupil == 0) return OLRT_OK;
+  return olrt_strict::generate_f64(pupil, out, (cudaStream_t)stream);
 }
-extern "C" int olrt_generate_rays_f32(const double* Px, const double* Py, int64_t n_pupil, const double* field_xy,
-                                      int32_t n_fields, double EPD, double EPL, double z_start, double wavelength,
-                                      float* const out[8], void* stream) {
-  int rc = check_generate(Px, Py, n_pupil, field_xy, n_fields, (void* const*)out);
+extern "C" int olrt_generate_rays_f32(const olrt_pupil* pupil, float* const out[8], void* stream) {
+  int rc = check_generate(pupil, (void* const*)out);
   if (rc) return rc;
-  if (n_pupil == 0) return OLRT_OK;
-  return olrt_strict::generate_f32(Px, Py, n_pupil, field_xy, n_fields, EPD, EPL, z_start, wavelength, out,
-                                   (cudaStream_t)stream);
+  if (pupil->n_pupil == 0) return OLRT_OK;
+  return olrt_strict::generate_f32(pupil, out, (cudaStream_t)stream);
 }
 
 extern "C" int olrt_selftest_math_f64(const double* a, const double* b, double* quot, double* root,

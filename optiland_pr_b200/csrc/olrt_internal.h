@@ -39,10 +39,8 @@ OLRT_DECL_BWD(f64, double)
 OLRT_DECL_BWD(f32, float)
 
 namespace olrt_strict {
-int generate_f64(const double* Px, const double* Py, long long n_pupil, const double* field_xy, int n_fields,
-                 double EPD, double EPL, double z_start, double wavelength, double* const out[8], cudaStream_t st);
-int generate_f32(const double* Px, const double* Py, long long n_pupil, const double* field_xy, int n_fields,
-                 double EPD, double EPL, double z_start, double wavelength, float* const out[8], cudaStream_t st);
+int generate_f64(const olrt_pupil* pupil, double* const out[8], cudaStream_t st);
+int generate_f32(const olrt_pupil* pupil, float* const out[8], cudaStream_t st);
 }
 
 namespace olrt_strict {

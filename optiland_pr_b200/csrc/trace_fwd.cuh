@@ -368,9 +368,9 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
     if (FIX && P.gen.px != nullptr) {  // pupil mode: launch the listed ray again (idx = f * n_pupil + p)
       const long long g_ = idx / P.gen.n_pupil;
       const int f = (int)(g_ % P.gen.n_fields);
-      double x0, y0, dL, dM, dN;
-      gen_ray(P.gen, f, idx - g_ * P.gen.n_pupil, x0, y0, dL, dM, dN);
-      r.x = (R)x0; r.y = (R)y0; r.z = (R)P.gen.z_start; r.L = (R)dL; r.M = (R)dM; r.N = (R)dN;
+      double x0, y0, z0, dL, dM, dN;
+      gen_ray(P.gen, f, idx - g_ * P.gen.n_pupil, x0, y0, z0, dL, dM, dN);
+      r.x = (R)x0; r.y = (R)y0; r.z = (R)z0; r.L = (R)dL; r.M = (R)dM; r.N = (R)dN;
       r.i = R(1); r.opd = R(0);
     } else {
       r.x = P.in[0][idx]; r.y = P.in[1][idx]; r.z = P.in[2][idx];

@@ -472,9 +472,9 @@ trace_fx_kernel(const FwdParams<R> P) {
       const long long pq = P.gen.p_lo + (valid ? pp : (P.gen.len - 1));
       idx = (long long)grp * P.gen.n_pupil + pq;
       group = grp;
-      double x0, y0, dL, dM, dN;
-      gen_ray(P.gen, f, pq, x0, y0, dL, dM, dN);
-      r.x = (R)x0; r.y = (R)y0; r.z = (R)P.gen.z_start; r.L = (R)dL; r.M = (R)dM; r.N = (R)dN;
+      double x0, y0, z0, dL, dM, dN;
+      gen_ray(P.gen, f, pq, x0, y0, z0, dL, dM, dN);
+      r.x = (R)x0; r.y = (R)y0; r.z = (R)z0; r.L = (R)dL; r.M = (R)dM; r.N = (R)dN;
       r.i = R(1); r.opd = R(0);
     } else {
       const long long item = base + threadIdx.x;

@@ -22,53 +22,50 @@ int selftest_math(const double* a, const double* b, double* q, double* r, long l
   return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
 }
 
-// Ray launch for an object at infinity, angle fields, no vignetting factors:
-//   RayGenerator.generate_rays        optiland/rays/ray_generator.py:28-106
-//   AngleField.get_ray_origins        optiland/fields/field_types.py:139-169
-// field_xy[f] = (-tan(radians(max_field Hx))(offset+EPL), same for y) is evaluated on the host (one value per
-// field); everything per ray is here, in the reference's operation order (this TU is built -fmad=false).
+// Ray launch (object at infinity or finite, angle / object-height fields, vignetting factors):
+//   RayGenerator.generate_rays            optiland/rays/ray_generator.py:28-106
+//   AngleField / ObjectHeightField.get_ray_origins   optiland/fields/field_types.py:139-169, :245-272
+// The per-field scalars (launch-plane offset or object point, vx, vy) are evaluated on the host; everything per
+// ray is in gen_ray (raygen.cuh), in the reference's operation order (this TU is built -fmad=false).
 // Rays are field-major: ray f * n_pupil + p. Arithmetic in fp64, stored as R.
 template <typename R>
-__global__ void __launch_bounds__(256) generate_rays_kernel(const double* __restrict__ Px, const double* __restrict__ Py,
-                                                            long long n_pupil, const double* __restrict__ field_xy,
-                                                            int n_fields, double EPD, double EPL, double z_start,
-                                                            double wavelength, R* ox, R* oy, R* oz, R* oL, R* oM,
+__global__ void __launch_bounds__(256) generate_rays_kernel(const GenParams G, R* ox, R* oy, R* oz, R* oL, R* oM,
                                                             R* oN, R* oi, R* ow) {
-  const long long total = n_pupil * n_fields;
-  GenParams G;
-  G.px = Px; G.py = Py; G.fxy = field_xy; G.n_pupil = n_pupil; G.p_lo = 0; G.len = n_pupil; G.n_fields = n_fields;
-  G.EPD = EPD; G.EPL = EPL; G.z_start = z_start; G.wavelength = wavelength;
+  const long long total = G.n_pupil * G.n_fields;
   for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < total;
        r += (long long)gridDim.x * blockDim.x) {
-    const long long f = r / n_pupil, p = r - f * n_pupil;
-    double x0, y0, dL, dM, dN;
-    gen_ray(G, (int)f, p, x0, y0, dL, dM, dN);
-    ox[r] = (R)x0; oy[r] = (R)y0; oz[r] = (R)z_start;
+    const long long f = r / G.n_pupil, p = r - f * G.n_pupil;
+    double x0, y0, z0, dL, dM, dN;
+    gen_ray(G, (int)f, p, x0, y0, z0, dL, dM, dN);
+    ox[r] = (R)x0; oy[r] = (R)y0; oz[r] = (R)z0;
     oL[r] = (R)dL; oM[r] = (R)dM; oN[r] = (R)dN;
     oi[r] = (R)1.0;
-    if (ow != nullptr) ow[r] = (R)wavelength;
+    if (ow != nullptr) ow[r] = (R)G.wavelength;
   }
 }
+static GenParams to_gen(const olrt_pupil* q) {
+  GenParams g;
+  g.px = q->Px; g.py = q->Py; g.fxy = q->field_xy; g.vig = q->field_vig; g.fz = q->field_z;
+  g.n_pupil = q->n_pupil; g.p_lo = 0; g.len = q->n_pupil;
+  g.n_fields = q->n_fields; g.EPD = q->EPD; g.EPL = q->EPL; g.z_start = q->z_start; g.wavelength = q->wavelength;
+  return g;
+}
 template <typename R>
-static int launch_generate(const double* Px, const double* Py, long long n_pupil, const double* field_xy, int n_fields,
-                           double EPD, double EPL, double z_start, double wavelength, R* const out[8],
-                           cudaStream_t stream) {
-  const long long total = n_pupil * n_fields;
+static int launch_generate(const olrt_pupil* pupil, R* const out[8], cudaStream_t stream) {
+  const GenParams G = to_gen(pupil);
+  const long long total = G.n_pupil * G.n_fields;
   long long grid = (long long)sm_count() * 8;
   const long long need = (total + 255) / 256;
   if (grid > need) grid = need;
-  generate_rays_kernel<R><<<(unsigned)grid, 256, 0, stream>>>(Px, Py, n_pupil, field_xy, n_fields, EPD, EPL, z_start,
-                                                              wavelength, out[0], out[1], out[2], out[3], out[4],
-                                                              out[5], out[6], out[7]);
+  generate_rays_kernel<R><<<(unsigned)grid, 256, 0, stream>>>(G, out[0], out[1], out[2], out[3], out[4], out[5],
+                                                              out[6], out[7]);
   return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
 }
-int generate_f64(const double* Px, const double* Py, long long n_pupil, const double* field_xy, int n_fields,
-                 double EPD, double EPL, double z_start, double wavelength, double* const out[8], cudaStream_t st) {
-  return launch_generate<double>(Px, Py, n_pupil, field_xy, n_fields, EPD, EPL, z_start, wavelength, out, st);
+int generate_f64(const olrt_pupil* pupil, double* const out[8], cudaStream_t st) {
+  return launch_generate<double>(pupil, out, st);
 }
-int generate_f32(const double* Px, const double* Py, long long n_pupil, const double* field_xy, int n_fields,
-                 double EPD, double EPL, double z_start, double wavelength, float* const out[8], cudaStream_t st) {
-  return launch_generate<float>(Px, Py, n_pupil, field_xy, n_fields, EPD, EPL, z_start, wavelength, out, st);
+int generate_f32(const olrt_pupil* pupil, float* const out[8], cudaStream_t st) {
+  return launch_generate<float>(pupil, out, st);
 }
 
 // OPD / wavefront epilogue, wavefront/strategy.py:68-116, :118-166, :203-229. This TU is built -fmad=false and

@@ -5,12 +5,14 @@
     Optic.trace(Hx, Hy, wavelength, num_rays, distribution)         optic.py:584-609
     Optic.trace_generic(Hx, Hy, Px, Py, wavelength)                 optic.py:611-632
     RealRayTracer.trace / trace_generic                             raytrace/real_ray_tracer.py:37-133
-    RayGenerator.generate_rays (infinite-object AngleField branch)  rays/ray_generator.py:28-106,
-                                                                    fields/field_types.py:139-169
+    RayGenerator.generate_rays (non-telecentric branch)             rays/ray_generator.py:28-106
+    AngleField / ObjectHeightField.get_ray_origins                  fields/field_types.py:139-169, :245-272
+    FieldGroup.get_vig_factor                                       fields/field_group.py:80-109
 
-Scope notes: ray generation here is the infinite-conjugate angle-field case
-without vignetting factors; the first-order quantities EPL / EPD it needs are INPUTS
-(`set_paraxial`) because the paraxial tracer (optiland/paraxial.py) is outside the hot path.
+Scope notes: ray generation covers angle fields (object at infinity or finite), object-height
+fields and per-field vignetting factors; object-space telecentric systems and paraxial-image-height fields are
+not mirrored. The first-order quantities EPL / EPD it needs are INPUTS (`set_paraxial`) because the paraxial
+tracer (optiland/paraxial.py) is outside the hot path.
 """
 from __future__ import annotations
 
@@ -49,11 +51,53 @@ def pupil_points(distribution: str, num_rays: int, seed=None):
     raise ValueError(f"distribution {distribution!r} is not implemented")
 
 
+class FieldTable:
+    """The per-field scalars of the ray launch (include/olrt.h, olrt_pupil): `fxy` [F, 2] launch-plane offsets
+    (object at infinity) or object points (finite object), `vig` [F, 2] = (vx, vy) or None, `fz` [F] or None,
+    `z_start`. `to(device)` uploads them in ONE copy; `rows(f)` is the table of field f alone."""
+
+    def __init__(self, fxy, vig, fz, z_start):
+        self.fxy, self.vig, self.fz, self.z_start = fxy, vig, fz, float(z_start)
+        self.fxy_d = self.vig_d = self.fz_d = None
+
+    @property
+    def n_fields(self):
+        return int(self.fxy.shape[0])
+
+    def to(self, device):
+        F = self.n_fields
+        parts = [self.fxy.ravel()] + ([self.vig.ravel()] if self.vig is not None else []) \
+            + ([self.fz.ravel()] if self.fz is not None else [])
+        flat = torch.from_numpy(np.ascontiguousarray(np.concatenate(parts), dtype=np.float64)).to(device, non_blocking=True)
+        self.fxy_d = flat[:2 * F].view(F, 2)
+        o = 2 * F
+        if self.vig is not None:
+            self.vig_d = flat[o:o + 2 * F].view(F, 2)
+            o += 2 * F
+        if self.fz is not None:
+            self.fz_d = flat[o:o + F]
+        return self
+
+    def rows(self, f):
+        t = FieldTable(self.fxy[f:f + 1], None if self.vig is None else self.vig[f:f + 1],
+                       None if self.fz is None else self.fz[f:f + 1], self.z_start)
+        t.fxy_d = self.fxy_d[f:f + 1]
+        t.vig_d = None if self.vig_d is None else self.vig_d[f:f + 1]
+        t.fz_d = None if self.fz_d is None else self.fz_d[f:f + 1]
+        return t
+
+    def kwargs(self):
+        """The keyword arguments of trace.fused_trace_pupil that come from this table."""
+        return dict(z_start=self.z_start, field_vig=self.vig_d, field_z=self.fz_d)
+
+
 class Optic:
     def __init__(self, name=None):
         self.name = name
         self.surface_group = SurfaceGroup()
-        self.fields = []          # (x, y) in degrees
+        self.fields = []          # (x, y): degrees (angle fields) or lens units (object-height fields)
+        self.vignetting = []      # (vx, vy) vignetting factors per field, fields/field.py:22-32
+        self.field_type = "angle"
         self.wavelengths = []     # micrometres
         self.primary_index = 0
         self.aperture = None
@@ -71,11 +115,27 @@ class Optic:
             self._EPD = float(value)
 
     def set_field_type(self, field_type):
-        if field_type != "angle":
-            raise ValueError("only angle fields are implemented")
+        if field_type not in ("angle", "object_height"):
+            raise ValueError('field_type must be "angle" or "object_height" (paraxial image heights are not mirrored)')
+        self.field_type = field_type
 
-    def add_field(self, y=0.0, x=0.0):
+    def add_field(self, y=0.0, x=0.0, vx=0.0, vy=0.0):
         self.fields.append((float(x), float(y)))
+        self.vignetting.append((float(vx), float(vy)))
+
+    def get_vig_factor(self, Hx, Hy):
+        """FieldGroup.get_vig_factor, fields/field_group.py:80-109: the vignetting factors of the NEAREST defined
+        field (normalised coordinates). Returns (vx [n], vy [n]) NumPy arrays."""
+        Hx = np.atleast_1d(np.asarray(Hx, dtype=np.float64))
+        Hy = np.atleast_1d(np.asarray(Hy, dtype=np.float64))
+        mf = self.max_field
+        pts = np.asarray(self.fields, dtype=np.float64).reshape(-1, 2)
+        if mf != 0:
+            pts = pts / mf
+        v = np.asarray(self.vignetting, dtype=np.float64).reshape(-1, 2)
+        d2 = (Hx[:, None] - pts[None, :, 0]) ** 2 + (Hy[:, None] - pts[None, :, 1]) ** 2
+        near = np.argmin(d2, axis=1)
+        return v[near, 0], v[near, 1]
 
     def add_wavelength(self, value, is_primary=False):
         self.wavelengths.append(float(value))
@@ -120,7 +180,11 @@ class Optic:
 
     @property
     def max_field(self):
-        return max(math.hypot(fx, fy) for fx, fy in self.fields) if self.fields else 0.0
+        """be.max(be.sqrt(x_fields**2 + y_fields**2)), fields/field_group.py:61-63."""
+        if not self.fields:
+            return 0.0
+        f = np.asarray(self.fields, dtype=np.float64)
+        return float(np.max(np.sqrt(f[:, 0] ** 2 + f[:, 1] ** 2)))
 
     def get_field_coords(self):
         mf = self.max_field
@@ -139,18 +203,38 @@ class Optic:
                 return a.to(device=dev, dtype=torch.float64, non_blocking=True).reshape(-1)
             return torch.as_tensor(np.asarray(a, dtype=np.float64), device=dev).reshape(-1)
 
+        vx = vy = 1.0
+        if any(v != (0.0, 0.0) for v in self.vignetting):
+            hx_h = Hx.cpu().numpy() if isinstance(Hx, torch.Tensor) else np.asarray(Hx, dtype=np.float64)
+            hy_h = Hy.cpu().numpy() if isinstance(Hy, torch.Tensor) else np.asarray(Hy, dtype=np.float64)
+            hx_h, hy_h = np.broadcast_arrays(np.atleast_1d(hx_h), np.atleast_1d(hy_h))
+            vxf, vyf = self.get_vig_factor(hx_h.reshape(-1), hy_h.reshape(-1))
+            vx, vy = f64(1 - vxf), f64(1 - vyf)
         Hx, Hy, Px, Py = f64(Hx), f64(Hy), f64(Px), f64(Py)
         EPL, EPD, mf = self._EPL, self._EPD, self.max_field
-        z_pos = [float(s.geometry.cs.z) for s in self.surface_group.surfaces[1:-1]]
-        offset = EPD - min(z_pos)                              # field_types.py:223-239
-        x = -torch.tan(torch.deg2rad(mf * Hx)) * (offset + EPL)
-        y = -torch.tan(torch.deg2rad(mf * Hy)) * (offset + EPL)
-        z = float(self.surface_group.surfaces[1].geometry.cs.z) - offset
-        x0 = Px * EPD / 2 * 1.0 + x
-        y0 = Py * EPD / 2 * 1.0 + y
-        z0 = torch.full_like(x0, z)
-        x1 = Px * EPD * 1.0 / 2
-        y1 = Py * EPD * 1.0 / 2
+        obj = self.surface_group.surfaces[0]
+        if self.field_type == "object_height":
+            if obj.is_infinite:
+                raise ValueError('Field type cannot be "object_height" for an object at infinity.')
+            x0 = (mf * Hx) * torch.ones_like(Px)
+            y0 = (mf * Hy) * torch.ones_like(Px)
+            z0 = torch.as_tensor(self._object_sag(x0.cpu().numpy(), y0.cpu().numpy()), device=dev) + float(obj.geometry.cs.z)
+        elif obj.is_infinite:
+            z_pos = [float(s.geometry.cs.z) for s in self.surface_group.surfaces[1:-1]]
+            offset = EPD - min(z_pos)                              # field_types.py:223-239
+            x = -torch.tan(torch.deg2rad(mf * Hx)) * (offset + EPL)
+            y = -torch.tan(torch.deg2rad(mf * Hy)) * (offset + EPL)
+            z = float(self.surface_group.surfaces[1].geometry.cs.z) - offset
+            x0 = Px * EPD / 2 * vx + x
+            y0 = Py * EPD / 2 * vy + y
+            z0 = torch.full_like(x0, z)
+        else:
+            zo = float(obj.geometry.cs.z)
+            x0 = (-torch.tan(torch.deg2rad(mf * Hx)) * (EPL - zo)) * torch.ones_like(Px)
+            y0 = (-torch.tan(torch.deg2rad(mf * Hy)) * (EPL - zo)) * torch.ones_like(Px)
+            z0 = torch.full_like(x0, zo)
+        x1 = Px * EPD * vx / 2
+        y1 = Py * EPD * vy / 2
         z1 = torch.full_like(x0, EPL)
         mag = torch.sqrt((x1 - x0) ** 2 + (y1 - y0) ** 2 + (z1 - z0) ** 2)
         is_zero = mag < 1e-9
@@ -188,10 +272,11 @@ class Optic:
             Px = torch.as_tensor(np.asarray(Px, dtype=np.float64), device=dev)
             Py = torch.as_tensor(np.asarray(Py, dtype=np.float64), device=dev)
         if (sg.fast_math and sg.record in ("none", "last", None) and not sg._wants_grad_params()
-                and self._EPL is not None and self._EPD is not None and Px.numel() > 0
-                and sg.pack([float(wavelength)]).fastkinds()):
-            # the grid is on the device: one fused launch + trace (+ spot) kernel over the whole pupil
-            return self._trace_pipelined(Hx, Hy, Px.contiguous(), Py.contiguous(), wavelength, spot)
+                and self._EPL is not None and self._EPD is not None and Px.numel() > 0):
+            packed = sg.pack([float(wavelength)])
+            if packed.fastkinds():
+                # the grid is on the device: one fused launch + trace (+ spot) kernel over the whole pupil
+                return self._trace_pipelined(Hx, Hy, Px.contiguous(), Py.contiguous(), wavelength, spot, packed)
         rays = self.launch_rays(Hx, Hy, Px, Py, wavelength)
         self.surface_group.trace(rays, wavelengths=[float(wavelength)])
         if spot:
@@ -202,7 +287,7 @@ class Optic:
     pipeline_min_rays = 1 << 21   # host pupil grids at least this long are streamed in chunks
     pipeline_chunks = 4
 
-    def _trace_pipelined(self, Hx, Hy, Px_h, Py_h, wavelength, spot=False):
+    def _trace_pipelined(self, Hx, Hy, Px_h, Py_h, wavelength, spot=False, packed=None):
         """Same result as launch_rays + SurfaceGroup.trace for a pupil grid that lives in (pinned) HOST
         memory: the grid is copied in chunks on a side stream while the chunks already on the device are
         traced, so the host->device copy overlaps the kernels instead of preceding them.
@@ -238,9 +323,9 @@ class Optic:
         else:
             cuts = [c * npup // C_ for c in range(C_ + 1)]
         edges = [(a_, b_) for a_, b_ in zip(cuts[:-1], cuts[1:]) if b_ > a_]
-        fxy_np, z_start = self._field_offsets(Hx, Hy)
-        fxy_all = torch.from_numpy(fxy_np).to(dev, non_blocking=True)
-        packed = sg.pack([float(wavelength)])
+        ft = self._field_table(Hx, Hy).to(dev)
+        fxy_all = ft.fxy_d
+        packed = sg.pack([float(wavelength)]) if packed is None else packed
         fused = bool(sg.fast_math and packed.fastkinds() and self._EPL is not None and self._EPD is not None)
         if fused and packed.record_surfaces:   # record == "last": the final state IS the last surface's record
             keep, sg.record = sg.record, "none"
@@ -248,7 +333,7 @@ class Optic:
                 packed = sg.pack([float(wavelength)])
             finally:
                 sg.record = keep
-        gen_kw = dict(EPD=self._EPD, EPL=self._EPL, z_start=z_start, wavelength=float(wavelength), dtype=dt)
+        gen_kw = dict(EPD=self._EPD, EPL=self._EPL, wavelength=float(wavelength), dtype=dt, **ft.kwargs())
         status_t = torch.zeros(1, dtype=torch.int32, device=dev)
         sums = shift = None
         if spot:  # sums are taken about each field's chief-ray image point (one tiny launch, no read-back)
@@ -299,7 +384,7 @@ class Optic:
                 for f in range(nf):
                     a, b = f * npup + lo, f * npup + hi
                     self.launch_rays(Hx[f:f + 1], Hy[f:f + 1], Px_d[lo:hi], Py_d[lo:hi], wavelength,
-                                     out=rays_in[:, a:b], fxy_d=fxy_all[f:f + 1])
+                                     out=rays_in[:, a:b], table=ft.rows(f))
                     fused_trace(packed, [rays_in[q, a:b] for q in range(7)] + [None], out=out[:, a:b],
                                 dir0_out=dir0[:, a:b], fast=sg.fast_math, verify_nr=False, check_status=False,
                                 status_t=status_t, resid_out=None if resid is None else resid[q_])
@@ -353,10 +438,49 @@ class Optic:
                         -np.tan(np.radians(mf * hy)) * (offset + EPL)], axis=1)
         return np.ascontiguousarray(fxy), float(self.surface_group.surfaces[1].geometry.cs.z) - offset
 
-    def launch_rays(self, Hx, Hy, Px, Py, wavelength, out=None, fxy_d=None) -> RealRays:
+    def _object_sag(self, x, y):
+        """Sag of the object surface at (x, y) (NumPy, fp64): 0 for a plane, geometries/standard.py:73-87 for a
+        conic -- what ObjectHeightField.get_ray_origins adds to the object's z (field_types.py:271)."""
+        g = self.surface_group.surfaces[0].geometry
+        name = type(g).__name__
+        if name == "Plane":
+            return np.zeros_like(np.asarray(x, dtype=np.float64))
+        if name == "StandardGeometry":
+            R, k = float(g.radius), float(g.k)
+            r2 = x ** 2 + y ** 2
+            return r2 / (R * (1 + np.sqrt(1 - (1 + k) * r2 / R ** 2)))
+        raise NotImplementedError(f"object-height fields on a {name} object surface")
+
+    def _field_table(self, Hx, Hy) -> FieldTable:
+        """The per-field launch scalars for fields (Hx[f], Hy[f]) (host, NumPy fp64, the reference's expressions):
+        AngleField.get_ray_origins field_types.py:139-169, ObjectHeightField.get_ray_origins :245-272,
+        vx = 1 - vig_x ray_generator.py:50-52."""
+        hx, hy = np.asarray(Hx, dtype=np.float64).reshape(-1), np.asarray(Hy, dtype=np.float64).reshape(-1)
+        vig = None
+        if any(v != (0.0, 0.0) for v in self.vignetting):
+            vxf, vyf = self.get_vig_factor(hx, hy)
+            vig = np.ascontiguousarray(np.stack([1 - vxf, 1 - vyf], axis=1))
+        obj = self.surface_group.surfaces[0]
+        mf = self.max_field
+        if self.field_type == "object_height":
+            if obj.is_infinite:
+                raise ValueError('Field type cannot be "object_height" for an object at infinity.')
+            x0, y0 = mf * hx, mf * hy
+            fz = self._object_sag(x0, y0) + float(obj.geometry.cs.z)
+            return FieldTable(np.ascontiguousarray(np.stack([x0, y0], axis=1)), vig, np.ascontiguousarray(fz), 0.0)
+        if obj.is_infinite:
+            fxy, z_start = self._field_offsets(hx, hy)
+            return FieldTable(fxy, vig, None, z_start)
+        zo = float(obj.geometry.cs.z)
+        EPL = self._EPL
+        fxy = np.stack([-np.tan(np.radians(mf * hx)) * (EPL - zo), -np.tan(np.radians(mf * hy)) * (EPL - zo)], axis=1)
+        return FieldTable(np.ascontiguousarray(fxy), vig, np.full(hx.size, zo), 0.0)
+
+    def launch_rays(self, Hx, Hy, Px, Py, wavelength, out=None, table=None) -> RealRays:
         """fields x pupil rays (field-major) from the ray-launch kernel `olrt_generate_rays_*`
-        (ray_generator.py:28-106 + field_types.py:139-169, object at infinity). Hx, Hy: [F] NumPy arrays
-        (one entry per field); Px, Py: [P] float64 device tensors."""
+        (ray_generator.py:28-106 + field_types.py:139-169, :245-272). Hx, Hy: [F] NumPy arrays
+        (one entry per field); Px, Py: [P] float64 device tensors. `table`: a FieldTable already on the device
+        (a caller launching many slices uploads it once and passes `table.rows(f)`)."""
         import ctypes as C
 
         from . import _lib as L
@@ -365,17 +489,18 @@ class Optic:
         lib = L.load()
         dt, dev = be.get_precision(), Px.device
         EPL, EPD = self._EPL, self._EPD
-        fxy, z_start = self._field_offsets(Hx, Hy)
-        if fxy_d is None:      # a caller launching many slices uploads the table once and passes row views
-            fxy_d = torch.from_numpy(fxy).to(dev, non_blocking=True)
-        nf, npup = int(fxy.shape[0]), int(Px.numel())
+        if table is None:
+            table = self._field_table(Hx, Hy).to(dev)
+        nf, npup = table.n_fields, int(Px.numel())
         if out is None:
             out = torch.empty((8, nf * npup), dtype=dt, device=dev)
         fn = lib.olrt_generate_rays_f64 if dt == torch.float64 else lib.olrt_generate_rays_f32
         Px, Py = Px.contiguous(), Py.contiguous()
+        from .trace import _ptr
+        pu = L.OlrtPupil(Px.data_ptr(), Py.data_ptr(), table.fxy_d.data_ptr(), _ptr(table.vig_d), _ptr(table.fz_d),
+                         npup, 0, npup, nf, 0, float(EPD), float(EPL), table.z_start, float(wavelength))
         with torch.cuda.device(dev):
-            rc = fn(Px.data_ptr(), Py.data_ptr(), npup, fxy_d.data_ptr(), nf, float(EPD), float(EPL), z_start,
-                    float(wavelength), L.PtrArray8(*[out[q].data_ptr() for q in range(8)]),
+            rc = fn(C.byref(pu), L.PtrArray8(*[out[q].data_ptr() for q in range(8)]),
                     torch.cuda.current_stream(dev).cuda_stream)
         L.check(rc, "olrt_generate_rays")
         if not out.is_contiguous():

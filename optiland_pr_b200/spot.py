@@ -68,3 +68,96 @@ def spot_radii(x, y, intensity, n_groups=1, rays_per_group=None, reference_centr
     rms = torch.sqrt((s2[:, 3] + s2[:, 4]) / s2[:, 0])
     geo = torch.sqrt(s2[:, 5])  # stored as the bits of a double (u64-ordered atomicMax)
     return dict(cx=c[:, 0], cy=c[:, 1], rms=rms, geo=geo, count=s2[:, 0])
+
+
+class SpotDiagram:
+    """analysis/spot_diagram.py:203-357 without the plotting: centroid(), rms_spot_radius() and
+    geometric_spot_radius() for fields x wavelengths.
+
+    The reference traces one (field, wavelength) pair per Python call (spot_diagram.py:387-395) and keeps every ray;
+    here ALL pairs go through one fused launch + trace + spot kernel per pass: the wavelengths are
+    rows of a prescription batch (the media of a row are the indices at its wavelength), the fields share the pupil
+    grid, the launched and traced rays never exist in memory. Pass 1 takes the sums about the chief-ray image points
+    (-> centroids of the reference wavelength, spot_diagram.py:317-327); pass 2 takes them about those centroids
+    (-> RMS and maximum radius, :329-357). Rays with intensity <= 0 or NaN are left out, as :427-429 does.
+    Lenses outside the fused kernel's surface kinds go through Optic.trace per pair and the two-pass `spot_radii`."""
+
+    def __init__(self, optic, fields="all", wavelengths="all", num_rings=6, distribution="hexapolar"):
+        import numpy as np
+
+        from . import backend as be
+        from .optic import pupil_points
+        from .trace import fused_spot_groups
+        self.optic = optic
+        self.fields = optic.get_field_coords() if fields == "all" else list(fields)
+        self.wavelengths = list(optic.wavelengths) if wavelengths == "all" else [float(w) for w in wavelengths]
+        ref_w = optic.primary_wavelength
+        self.ref_index = self.wavelengths.index(ref_w) if ref_w in self.wavelengths else 0
+        dev = torch.device(be.get_device())
+        dt = be.get_precision()
+        if isinstance(distribution, str):
+            px, py = pupil_points(distribution, num_rings)
+        else:
+            px, py = distribution
+        Px = torch.as_tensor(px, dtype=torch.float64, device=dev).contiguous()
+        Py = torch.as_tensor(py, dtype=torch.float64, device=dev).contiguous()
+        nf, nw = len(self.fields), len(self.wavelengths)
+        Hx = np.array([f[0] for f in self.fields], dtype=np.float64)
+        Hy = np.array([f[1] for f in self.fields], dtype=np.float64)
+        sg = optic.surface_group
+        keep = sg.record
+        sg.record = "none"
+        try:
+            packs = [sg.pack([w]) for w in self.wavelengths]
+        finally:
+            sg.record = keep
+        p0 = packs[0]
+        fused = bool(sg.fast_math and p0.fastkinds() and optic._EPL is not None and optic._EPD is not None
+                     and all(np.array_equal(p.ops, p0.ops) for p in packs))
+        self.path = "fused" if fused else "per_pair"
+        if fused:
+            ft = optic._field_table(Hx, Hy).to(dev)
+            gen_kw = dict(EPD=optic._EPD, EPL=optic._EPL, wavelength=float(self.wavelengths[0]), dtype=dt, **ft.kwargs())
+            presc = torch.from_numpy(np.concatenate([p.presc for p in packs], axis=0)).to(dev)
+            k0 = np.zeros((nf, p0.n_surfaces), dtype=np.int32)
+            for k in p0.nr_rows():
+                k0[:, k] = 2
+            s1, kg = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, k0, valid_only=True)
+            st = spot_stats(s1)
+            cen = torch.stack([st["cx"], st["cy"]], dim=1).reshape(nw, nf, 2)[self.ref_index]     # [nf, 2]
+            shift2 = cen.unsqueeze(0).expand(nw, nf, 2).reshape(-1, 2).contiguous()
+            s2, _ = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, kg, shift=shift2, valid_only=True,
+                                      settle=False)
+            self.group_iters = kg
+        else:
+            npup = int(Px.numel())
+            xs, ys, is_ = [], [], []
+            for w in self.wavelengths:      # one trace per pair: the Newton exit rule is per trace
+                for f in range(nf):
+                    rays = optic.trace(Hx[f:f + 1], Hy[f:f + 1], w, distribution=(Px, Py))
+                    xs.append(rays.x), ys.append(rays.y), is_.append(rays.i)
+            x, y, i = torch.cat(xs), torch.cat(ys), torch.cat(is_)
+            s1 = spot_sums(x, y, i, nw * nf, npup, None, True)
+            st = spot_stats(s1)
+            cen = torch.stack([st["cx"], st["cy"]], dim=1).reshape(nw, nf, 2)[self.ref_index]
+            shift2 = cen.unsqueeze(0).expand(nw, nf, 2).reshape(-1, 2).contiguous()
+            s2 = spot_sums(x, y, i, nw * nf, npup, shift2, True)
+        self._centroid = cen
+        self._rms = torch.sqrt((s2[:, 3] + s2[:, 4]) / s2[:, 0]).reshape(nw, nf)
+        self._geo = torch.sqrt(s2[:, 5]).reshape(nw, nf)
+        self.count = s2[:, 0].reshape(nw, nf)
+
+    def centroid(self):
+        """[(cx, cy)] per field, reference wavelength (spot_diagram.py:317-327)."""
+        c = self._centroid.cpu()
+        return [(c[f, 0], c[f, 1]) for f in range(c.shape[0])]
+
+    def rms_spot_radius(self):
+        """[field][wavelength] (spot_diagram.py:344-357)."""
+        r = self._rms.cpu()
+        return [[r[w, f] for w in range(r.shape[0])] for f in range(r.shape[1])]
+
+    def geometric_spot_radius(self):
+        """[field][wavelength] (spot_diagram.py:329-342)."""
+        r = self._geo.cpu()
+        return [[r[w, f] for w in range(r.shape[0])] for f in range(r.shape[1])]

@@ -150,9 +150,9 @@ class MonteCarloSpot:
         Py = torch.as_tensor(np.asarray(Py, dtype=np.float64) if not isinstance(Py, torch.Tensor) else Py,
                              dtype=torch.float64, device=dev).contiguous()
         npup = int(Px.numel())
-        fxy_np, z_start = lens._field_offsets(Hx, Hy)
-        fxy = torch.from_numpy(fxy_np).to(dev)
-        gen_kw = dict(EPD=lens._EPD, EPL=lens._EPL, z_start=z_start, wavelength=float(wavelength), dtype=dt)
+        ft = lens._field_table(Hx, Hy).to(dev)
+        fxy = ft.fxy_d
+        gen_kw = dict(EPD=lens._EPD, EPL=lens._EPL, wavelength=float(wavelength), dtype=dt, **ft.kwargs())
         rms_local = torch.empty((hi - lo, nf), dtype=torch.float64, device=dev)
         fused = bool(packed.fastkinds())
         self.last_path = "fused" if fused else "chunked"
@@ -160,50 +160,15 @@ class MonteCarloSpot:
         zero1 = torch.zeros(1, dtype=torch.float64, device=dev)
         has_nr = bool(packed.nr_rows())
         from .spot import spot_stats, spot_sums
-        from .trace import group_true_iters
+        from .trace import fused_spot_groups
         S = packed.n_surfaces
         nr_rows = packed.nr_rows()
 
         def fused_groups(presc_t, k0):
-            """One fused launch per round over `presc_t` [T, stride]; the Newton trip counts are PER GROUP (trial x
-            field), as in the reference where every (trial, field) is its own trace: groups whose counts fail the
-            exit rule are traced again with corrected counts. Returns (rms [T, nf], counts [T * nf, S])."""
-            T = int(presc_t.shape[0])
-            G = T * nf
-            kg = np.repeat(k0[None, :, :], T, axis=0).reshape(G, S).astype(np.int32)
-            rms = torch.empty(G, dtype=torch.float64, device=dev)
-            todo = np.arange(T)
-            chief = torch.empty((8, G), dtype=dt, device=dev)
-            fused_trace_pupil(packed, zero1, zero1, fxy, out=chief, presc=presc_t,
-                              group_k=torch.from_numpy(kg).to(dev), **gen_kw)
-            shift_all = chief[:2].t().to(torch.float64).nan_to_num(0.0, 0.0, 0.0).contiguous()
-            for rnd in range(8):
-                sel = torch.from_numpy(todo).to(dev)
-                gsel = (todo[:, None] * nf + np.arange(nf)[None, :]).reshape(-1)
-                gsel_t = torch.from_numpy(gsel).to(dev)
-                k_t = torch.from_numpy(kg[gsel]).to(dev)
-                sums = torch.zeros((gsel.size, L.SPOT_SUMS), dtype=torch.float64, device=dev)
-                gres = torch.zeros((gsel.size, S, L.GROUP_RESID), dtype=torch.int64, device=dev) if nr_rows else None
-                shift = shift_all[gsel_t].contiguous()
-                fused_trace_pupil(packed, Px, Py, fxy, out=None, spot=sums, spot_shift=shift,
-                                  presc=presc_t[sel].contiguous(), group_k=k_t, group_resid=gres, **gen_kw)
-                sums[:, 8:10] = shift
-                rms[gsel_t] = spot_stats(sums)["rms"]
-                if not nr_rows:
-                    break
-                kt = group_true_iters(packed, gres.cpu().numpy().view(np.float64), kg[gsel])
-                wrong = (kt != kg[gsel]).any(axis=1)
-                if not wrong.any():
-                    break
-                need_more = kt < 0
-                kg_new = np.where(need_more, np.minimum(kg[gsel] * 2 + 1, L.GROUP_RESID - 1), kt)
-                if (need_more & (kg[gsel] >= L.GROUP_RESID - 1)).any():
-                    raise NotImplementedError("a trial needs more than %d Newton updates" % (L.GROUP_RESID - 1))
-                kg[gsel] = kg_new
-                todo = np.unique(gsel[wrong] // nf)
-            else:
-                raise L.OlrtLibraryError("Newton trip counts did not settle")
-            return rms.reshape(T, nf), kg
+            """(rms [T, nf], counts [T * nf, S]) from trace.fused_spot_groups: one fused launch per round over
+            `presc_t` [T, stride], Newton trip counts per (trial, field) group."""
+            sums, kg = fused_spot_groups(packed, presc_t, Px, Py, fxy, gen_kw, k0)
+            return spot_stats(sums)["rms"].reshape(int(presc_t.shape[0]), nf), kg
 
         k_nominal = np.zeros((nf, S), dtype=np.int32)
         for k in nr_rows:

@@ -217,7 +217,8 @@ def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, 
                       spot_shift: torch.Tensor | None = None, spot_valid_only: bool = False,
                       resid_out: torch.Tensor | None = None, status_t: torch.Tensor | None = None,
                       presc: torch.Tensor | None = None, group_k: torch.Tensor | None = None,
-                      group_resid: torch.Tensor | None = None) -> None:
+                      group_resid: torch.Tensor | None = None, field_vig: torch.Tensor | None = None,
+                      field_z: torch.Tensor | None = None) -> None:
     """Enqueue `olrt_trace_pupil_*` (include/olrt.h): launch the rays of every field for pupil points
     [p_lo, p_lo + p_len) in the kernel, trace them, optionally accumulate the spot sums. Nothing is read back:
     the caller owns `status_t`, `resid_out` (see fused_trace) and checks them after the last chunk.
@@ -227,6 +228,8 @@ def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, 
     group_k: optional int32 [groups, n_surfaces] device tensor of Newton trip counts per group (trial x field)
     instead of the batch-global counts in `packed`; group_resid: int64 [groups, n_surfaces, GROUP_RESID] (zeroed)
     receives each group's residual maxima (`group_true_iters` applies the reference's exit rule to them).
+    field_vig: optional [F, 2] float64 device tensor of (vx, vy) = 1 - vignetting factors; field_z: optional [F]
+    float64 device tensor -- finite object, `field_xy` / `field_z` are then each field's object point (olrt.h).
     Raises NotImplementedError where the C ABI answers
     OLRT_E_UNSUPPORTED (the caller then uses launch + fused_trace + spot_sums)."""
     lib = L.load()
@@ -241,7 +244,7 @@ def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, 
     if presc is not None:
         presc_d = presc.to(device=device, dtype=dtype).contiguous()
         n_presc = int(presc_d.shape[0])
-    pu = L.OlrtPupil(Px.data_ptr(), Py.data_ptr(), field_xy.data_ptr(), npup, int(p_lo), int(p_len), nf, 0,
+    pu = L.OlrtPupil(Px.data_ptr(), Py.data_ptr(), field_xy.data_ptr(), _ptr(field_vig), _ptr(field_z), npup, int(p_lo), int(p_len), nf, 0,
                      float(EPD), float(EPL), float(z_start), float(wavelength))
     sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=nf * p_len)
     sys_.presc_stride = int(presc_d.shape[1])
@@ -281,3 +284,59 @@ def group_true_iters(packed: PackedSystem, resid: np.ndarray, k_used: np.ndarray
         first = np.where((bad & seen).any(axis=1), -1, first)   # a NaN ray: the reference runs max_iter
         out[:, k] = first
     return out
+
+
+def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Tensor, Py: torch.Tensor,
+                      field_xy: torch.Tensor, gen_kw: dict, k0: np.ndarray, *, shift: torch.Tensor | None = None,
+                      valid_only: bool = False, settle: bool = True):
+    """Spot sums of every (prescription, field) group from fused launch + trace + spot kernels that write nothing
+    per ray. `presc_t` [T, stride] holds one prescription per row (Monte-Carlo trials, or one row per WAVELENGTH:
+    the media live in the prescription row); the groups are g = row * n_fields + field. The Newton trip counts are
+    PER GROUP, as in the reference where every (trial / wavelength, field) is its own trace (newton_raphson.py:148):
+    `k0` [n_fields, S] is the first guess, groups whose counts fail the exit rule are traced again with corrected
+    counts (settle=False: `k0` is [G, S] and trusted). shift: [G, 2] point the sums are taken about (default: each
+    group's chief-ray image point, from one more tiny launch). Returns (sums [G, SPOT_SUMS] with columns 8:10 =
+    shift, counts [G, S] int32)."""
+    dev = Px.device
+    dt = gen_kw.get("dtype", torch.float64)
+    nf, S = int(field_xy.shape[0]), packed.n_surfaces
+    T = int(presc_t.shape[0])
+    G = T * nf
+    nr_rows = packed.nr_rows()
+    kg = (np.repeat(k0[None, :, :], T, axis=0).reshape(G, S) if k0.shape[0] == nf and k0.ndim == 2 and G != nf
+          else np.asarray(k0).reshape(G, S)).astype(np.int32)
+    if shift is None:
+        zero1 = torch.zeros(1, dtype=torch.float64, device=dev)
+        chief = torch.empty((8, G), dtype=dt, device=dev)
+        fused_trace_pupil(packed, zero1, zero1, field_xy, out=chief, presc=presc_t,
+                          group_k=torch.from_numpy(kg).to(dev), **gen_kw)
+        shift = chief[:2].t().to(torch.float64).nan_to_num(0.0, 0.0, 0.0).contiguous()
+    out_sums = torch.empty((G, L.SPOT_SUMS), dtype=torch.float64, device=dev)
+    todo = np.arange(T)
+    for _ in range(8):
+        sel = torch.from_numpy(todo).to(dev)
+        gsel = (todo[:, None] * nf + np.arange(nf)[None, :]).reshape(-1)
+        gsel_t = torch.from_numpy(gsel).to(dev)
+        k_t = torch.from_numpy(kg[gsel]).to(dev)
+        sums = torch.zeros((gsel.size, L.SPOT_SUMS), dtype=torch.float64, device=dev)
+        check = bool(nr_rows) and settle
+        gres = torch.zeros((gsel.size, S, L.GROUP_RESID), dtype=torch.int64, device=dev) if check else None
+        sh = shift[gsel_t].contiguous()
+        fused_trace_pupil(packed, Px, Py, field_xy, out=None, spot=sums, spot_shift=sh, spot_valid_only=valid_only,
+                          presc=presc_t[sel].contiguous(), group_k=k_t, group_resid=gres, **gen_kw)
+        sums[:, 8:10] = sh
+        out_sums[gsel_t] = sums
+        if not check:
+            break
+        kt = group_true_iters(packed, gres.cpu().numpy().view(np.float64), kg[gsel])
+        wrong = (kt != kg[gsel]).any(axis=1)
+        if not wrong.any():
+            break
+        need_more = kt < 0
+        if (need_more & (kg[gsel] >= L.GROUP_RESID - 1)).any():
+            raise NotImplementedError("a group needs more than %d Newton updates" % (L.GROUP_RESID - 1))
+        kg[gsel] = np.where(need_more, np.minimum(kg[gsel] * 2 + 1, L.GROUP_RESID - 1), kt)
+        todo = np.unique(gsel[wrong] // nf)
+    else:
+        raise L.OlrtLibraryError("Newton trip counts did not settle")
+    return out_sums, kg
