@@ -68,7 +68,13 @@ enum {
   OLRT_GEOM_EVEN_ASPHERE = 2, /* optiland/geometries/even_asphere.py:82-129 + newton_raphson.py:119-168 */
   OLRT_GEOM_POLYNOMIAL = 3,   /* optiland/geometries/polynomial.py:93-142 */
   OLRT_GEOM_ZERNIKE = 4,      /* optiland/geometries/zernike.py:133-232 */
-  OLRT_GEOM_ODD_ASPHERE = 5   /* optiland/geometries/odd_asphere.py:73-129 */
+  OLRT_GEOM_ODD_ASPHERE = 5,  /* optiland/geometries/odd_asphere.py:73-129 */
+  OLRT_GEOM_BICONIC = 6,      /* optiland/geometries/biconic.py:69-158; coefficients: cx cy (1+kx)cx^2 (1+ky)cy^2;
+                                 radius / conic slots = Rx, kx (the base conic of the first Newton guess) */
+  OLRT_GEOM_TOROIDAL = 7,     /* optiland/geometries/toroidal.py:84-240; coefficients: R_rot c_yz (1+k)c_yz^2 then
+                                 AUX polynomial terms of y^2, y^4 ...; radius / conic slots = R_yz, 0 */
+  OLRT_GEOM_CHEBYSHEV = 8     /* optiland/geometries/chebyshev.py:103-217; coefficients: norm_x norm_y then C[i][j]
+                                 row-major with AUX columns */
 };
 
 enum {
@@ -101,6 +107,7 @@ enum {
 /* status bits (device word, OR-accumulated) */
 #define OLRT_ST_ZERNIKE_RANGE 1u /* |x/R_n|>1 or |y/R_n|>1 at a Zernike surface: zernike.py:234-246 */
 #define OLRT_ST_WAVELENGTH 2u    /* a ray wavelength is not in olrt_sys.wavelengths */
+#define OLRT_ST_CHEBYSHEV_RANGE 8u /* |x/norm_x|>1 or |y/norm_y|>1 at a Chebyshev surface: chebyshev.py:204-217 */
 #define OLRT_ST_BAD_HINT 4u      /* olrt_sys.kernel_hint claims something the ops table does not satisfy: nothing traced */
 
 /* kernel_hint bits */

@@ -186,6 +186,115 @@ __device__ __forceinline__ void zernike_eval(const SurfParams<R>& sp, R x, R y, 
   sag = sag + zsum;
 }
 
+// BiconicGeometry.sag / _surface_normal     geometries/biconic.py:69-158
+// coef = cx, cy, (1+kx) cx^2, (1+ky) cy^2 (host, NumPy fp64: the reference's own scalars)
+template <typename R, bool WANT_SLOPES, int MM>
+__device__ __forceinline__ void biconic_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy) {
+  const R eps = R(1e-14);
+  R z[2];
+  const R v[2] = {x, y};
+  R sl[2] = {R(0), R(0)};
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const R c = sp.coef[q], A = sp.coef[2 + q], w = v[q];
+    z[q] = R(0);
+    if (c == R(0)) continue;                      // be.all(self.cx == 0): no contribution from this profile
+    const R val = R(1) - A * (w * w);
+    const R den = R(1) + m_sqrt<MM>((val < eps) ? R(0) : val);
+    z[q] = m_div<MM>(c * (w * w), (r_abs(den) < eps) ? eps : den);
+    if (WANT_SLOPES) {
+      const R ds = m_sqrt<MM>((val < eps) ? eps : val);
+      sl[q] = m_div<MM>(c * w, (r_abs(ds) < eps) ? eps : ds);
+    }
+  }
+  sag = z[0] + z[1];
+  if (WANT_SLOPES) { zx = sl[0]; zy = sl[1]; }
+}
+
+// ToroidalGeometry.sag / _surface_normal    geometries/toroidal.py:84-240
+// coef = R_rot, c_yz, (1+k) c_yz^2, then aux polynomial coefficients of y^2, y^4, ...
+template <typename R, bool WANT_SLOPES, int MM>
+__device__ __forceinline__ void toroidal_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy) {
+  const R eps = R(1e-14);
+  const R Rrot = sp.coef[0], c = sp.coef[1], A = sp.coef[2];
+  const R* poly = sp.coef + 3;
+  const int np_ = sp.aux;
+  const R y2 = y * y;
+  R z_y = R(0), dz = R(0);
+  if (c != R(0)) {
+    const R val = R(1) - A * y2;
+    const R den = R(1) + m_sqrt<MM>((val < R(0)) ? R(0) : val);
+    z_y = m_div<MM>(c * y2, (r_abs(den) < eps) ? eps : den);
+    if (WANT_SLOPES) {
+      const R ds = m_sqrt<MM>((val < eps) ? eps : val);
+      dz = m_div<MM>(c * y, (r_abs(ds) < eps) ? eps : ds);
+    }
+  }
+  if (np_ > 0) {
+    R pt = R(0), pw = y2, pd = R(0), pwd = y;
+    for (int i = 0; i < np_; ++i) {
+      const R Ci = poly[i];
+      pt = pt + Ci * pw;
+      pw = pw * y2;
+      if (WANT_SLOPES) {
+        pd = pd + (Ci * R(2 * (i + 1))) * pwd;
+        pwd = pwd * y2;
+      }
+    }
+    z_y = z_y + pt;
+    if (WANT_SLOPES) dz = dz + pd;
+  }
+  if (isinf(Rrot)) {
+    sag = z_y;
+    if (WANT_SLOPES) { zx = R(0); zy = dz; }
+    return;
+  }
+  const R d = Rrot - z_y;
+  const R term = d * d - x * x;
+  sag = (term < R(0)) ? R(NAN) : z_y + (d - r_sign(d) * m_sqrt<MM>(term));
+  if (WANT_SLOPES) {
+    const bool ok = term >= R(0);
+    const R sq = m_sqrt<MM>(ok ? term : eps);
+    const R ssq = (r_abs(sq) < eps) ? eps : sq;
+    const R sR = r_sign(Rrot);
+    zx = ok ? m_div<MM>(sR * x, ssq) : R(0);
+    zy = ok ? m_div<MM>((sR * d) * dz, ssq) : R(0);
+  }
+}
+
+// ChebyshevPolynomialGeometry.sag / _surface_normal   geometries/chebyshev.py:103-217
+// coef = norm_x, norm_y, then C[i][j] row-major with aux columns; T_n(x) = cos(n arccos x), the derivative
+// n sin(n arccos x) / sqrt(1 - x^2) exactly as the reference writes it (libm vs CUDA libm: 1e-10 bar, not bits).
+template <typename R, bool WANT_SLOPES, int MM>
+__device__ __forceinline__ void chebyshev_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy,
+                                               uint32_t& status) {
+  const R xn = x / sp.coef[0], yn = y / sp.coef[1];
+  if (r_abs(xn) > R(1) || r_abs(yn) > R(1)) status |= OLRT_ST_CHEBYSHEV_RANGE;  // chebyshev.py:204-217
+  const R r2 = x * x + y * y;
+  R denom;
+  conic_sag_denom<R, MM>(r2, sp.cc, sag, denom);
+  if (WANT_SLOPES) { zx = x / denom; zy = y / denom; }
+  const int J = sp.aux, I = (J > 0) ? (sp.ncoef - 2) / J : 0;
+  const R* C = sp.coef + 2;
+  const R ax = acos(xn), ay = acos(yn);
+  const R sx = r_sqrt(R(1) - xn * xn), sy = r_sqrt(R(1) - yn * yn);
+  for (int i = 0; i < I; ++i) {
+    const R Ti = cos(R(i) * ax);
+    const R dTi = WANT_SLOPES ? (R(i) * sin(R(i) * ax)) / sx : R(0);
+    for (int j = 0; j < J; ++j) {
+      const R Cij = C[i * J + j];
+      if (Cij == R(0)) continue;                  // be.argwhere(self.coefficients != 0)
+      const R Tj = cos(R(j) * ay);
+      sag = sag + (Cij * Ti) * Tj;
+      if (WANT_SLOPES) {
+        const R dTj = (R(j) * sin(R(j) * ay)) / sy;
+        zx = zx + (dTi * Cij) * Tj;
+        zy = zy + (dTj * Cij) * Ti;
+      }
+    }
+  }
+}
+
 // dispatch: sag (and slopes) of an NR geometry at (x, y)
 template <typename R, bool WANT_SLOPES, int MM>
 __device__ __forceinline__ void nr_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy,
@@ -194,6 +303,9 @@ __device__ __forceinline__ void nr_eval(const SurfParams<R>& sp, R x, R y, R& sa
     case OLRT_GEOM_EVEN_ASPHERE: even_asphere_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy); break;
     case OLRT_GEOM_ODD_ASPHERE: odd_asphere_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy); break;
     case OLRT_GEOM_POLYNOMIAL: polynomial_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy); break;
+    case OLRT_GEOM_BICONIC: biconic_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy); break;
+    case OLRT_GEOM_TOROIDAL: toroidal_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy); break;
+    case OLRT_GEOM_CHEBYSHEV: chebyshev_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy, status); break;
     default: zernike_eval<R, WANT_SLOPES, MM>(sp, x, y, sag, zx, zy, status); break;
   }
 }

@@ -75,6 +75,49 @@ class PolynomialGeometry(NewtonRaphsonGeometry):
         self.is_symmetric = False
 
 
+class BiconicGeometry(NewtonRaphsonGeometry):
+    """geometries/biconic.py:29-67: independent conic profiles in x and y; the base conic of the first Newton
+    guess is the x profile (radius_x, conic_x)."""
+
+    def __init__(self, coordinate_system, radius_x, radius_y, conic_x=0.0, conic_y=0.0, tol=1e-10, max_iter=100):
+        super().__init__(coordinate_system, radius_x, conic_x, tol, max_iter)
+        self.Rx, self.Ry, self.kx, self.ky = radius_x, radius_y, conic_x, conic_y
+        self.is_symmetric = False
+
+    def flip(self):
+        self.Rx, self.Ry = -self.Rx, -self.Ry
+        self.radius = -self.radius
+
+
+class ToroidalGeometry(NewtonRaphsonGeometry):
+    """geometries/toroidal.py:26-82: a Y-Z conic + even polynomial profile rotated about an axis at distance
+    radius_x; the base conic of the first Newton guess is a sphere of radius_y."""
+
+    def __init__(self, coordinate_system, radius_x, radius_y, conic=0.0, coeffs_poly_y=None, tol=1e-10,
+                 max_iter=100):
+        super().__init__(coordinate_system, radius_y, 0.0, tol, max_iter)
+        self.R_rot, self.R_yz, self.k_yz = radius_x, radius_y, conic
+        self.coeffs_poly_y = list(coeffs_poly_y) if coeffs_poly_y is not None else []
+        self.is_symmetric = False
+
+    def flip(self):
+        self.R_rot, self.R_yz = -self.R_rot, -self.R_yz
+        self.radius = -self.radius
+
+
+class ChebyshevPolynomialGeometry(NewtonRaphsonGeometry):
+    """geometries/chebyshev.py:33-98: conic + sum C[i][j] T_i(x / norm_x) T_j(y / norm_y)."""
+
+    def __init__(self, coordinate_system, radius, conic=0.0, tol=1e-10, max_iter=100, coefficients=None,
+                 norm_x=1, norm_y=1):
+        super().__init__(coordinate_system, radius, conic, tol, max_iter)
+        rows = coefficients if coefficients is not None else []
+        rows = [list(r) for r in rows] if len(rows) and hasattr(rows[0], "__len__") else ([list(rows)] if len(rows) else [])
+        self.coefficients = rows if rows else [[0.0]]
+        self.norm_x, self.norm_y = norm_x, norm_y
+        self.is_symmetric = False
+
+
 # ---- Zernike index schemes (OSA/ANSI "standard", Noll, Fringe) --------------------------------
 def _number_standard(n, m):
     return (n * (n + 2) + m) // 2

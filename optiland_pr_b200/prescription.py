@@ -28,8 +28,18 @@ _GEOM_BY_NAME = {
     "OddAsphere": L.GEOM_ODD_ASPHERE,
     "PolynomialGeometry": L.GEOM_POLYNOMIAL,
     "ZernikePolynomialGeometry": L.GEOM_ZERNIKE,
+    "BiconicGeometry": L.GEOM_BICONIC,
+    "ToroidalGeometry": L.GEOM_TOROIDAL,
+    "ChebyshevPolynomialGeometry": L.GEOM_CHEBYSHEV,
 }
-_NR_GEOMS = (L.GEOM_EVEN_ASPHERE, L.GEOM_ODD_ASPHERE, L.GEOM_POLYNOMIAL, L.GEOM_ZERNIKE)
+_NR_GEOMS = (L.GEOM_EVEN_ASPHERE, L.GEOM_ODD_ASPHERE, L.GEOM_POLYNOMIAL, L.GEOM_ZERNIKE, L.GEOM_BICONIC,
+             L.GEOM_TOROIDAL, L.GEOM_CHEBYSHEV)
+
+
+def _curvature(radius):
+    """be.where(be.isinf(R) | (R == 0), 0.0, 1.0 / R), biconic.py:64-65 / toroidal.py:77-79."""
+    r = np.float64(radius)
+    return np.float64(0.0) if (np.isinf(r) or r == 0) else np.float64(1.0) / r
 
 
 class NotEligible(Exception):
@@ -296,6 +306,24 @@ def pack_surface_group(surfaces, wavelengths, record="all", skip: int = 0) -> Pa
             if any(len(r) != J for r in rows):
                 raise NotEligible("ragged polynomial coefficient table")
             ncoef, aux = len(rows) * J, J
+            for r in rows:
+                reals += r
+        elif geom == L.GEOM_BICONIC:      # cx cy (1+kx)cx^2 (1+ky)cy^2 -- the reference's own scalar expressions
+            cx, cy = _curvature(_f(g.Rx)), _curvature(_f(g.Ry))
+            kx, ky = np.float64(_f(g.kx)), np.float64(_f(g.ky))
+            ncoef = 4
+            reals += [float(cx), float(cy), float((1.0 + kx) * cx**2), float((1.0 + ky) * cy**2)]
+        elif geom == L.GEOM_TOROIDAL:     # R_rot c_yz (1+k)c_yz^2 poly...
+            c = _curvature(_f(g.R_yz))
+            kk = np.float64(_f(g.k_yz))
+            poly = [_f(v) for v in g.coeffs_poly_y]
+            ncoef, aux = 3 + len(poly), len(poly)
+            reals += [_f(g.R_rot), float(c), float((1.0 + kk) * c**2)] + poly
+        elif geom == L.GEOM_CHEBYSHEV:    # norm_x norm_y C[i][j]
+            rows = [[_f(c) for c in r] for r in np.atleast_2d(np.asarray(g.coefficients, dtype=object)).tolist()]
+            J = len(rows[0]) if rows else 0
+            ncoef, aux = 2 + len(rows) * J, J
+            reals += [_f(g.norm_x), _f(g.norm_y)]
             for r in rows:
                 reals += r
         elif geom == L.GEOM_ZERNIKE:

@@ -175,6 +175,57 @@ def build_freeform_plate(lens, ap, zernike_type="fringe"):
     return lens
 
 
+def build_anamorphic(lens):
+    """Anamorphic test system for the SURVEY.md 8f N4 geometries: two biconics (one with a flat x profile), a
+    tilted toroid with a conic + polynomial Y-Z profile and a cylinder (toroid with an infinite rotation radius)."""
+    lens.set_aperture(aperture_type="EPD", value=14)
+    lens.set_field_type(field_type="angle")
+    for fx, fy in ((0, 0), (0, 5), (3, 4)):
+        lens.add_field(y=fy, x=fx)
+    lens.add_wavelength(value=0.55, is_primary=True)
+    lens.add_surface(index=0, radius=INF, thickness=INF)
+    lens.add_surface(index=1, surface_type="biconic", radius_x=40.0, radius_y=55.0, conic_x=-0.5, conic_y=0.3,
+                     thickness=5.0, material="N-BK7", is_stop=True)
+    lens.add_surface(index=2, surface_type="biconic", radius_x=INF, radius_y=-80.0, conic_y=-1.2, thickness=3.0)
+    lens.add_surface(index=3, surface_type="toroidal", radius_x=30.0, radius_y=60.0, conic=-0.4,
+                     toroidal_coeffs_poly_y=[1.0e-5, -2.0e-8], thickness=4.0, material="N-SK16", rx=0.02, dy=0.2)
+    lens.add_surface(index=4, surface_type="toroidal", radius_x=INF, radius_y=-50.0, thickness=30.0)
+    lens.add_surface(index=5)
+    return lens
+
+
+CHEBYSHEV_COEFFS = [[0.0, 2.0e-2, -1.0e-2], [1.5e-2, 0.0, 4.0e-3], [-6.0e-3, 3.0e-3, 1.0e-3]]
+
+
+def build_chebyshev_plate(lens, to_array=list):
+    """A Chebyshev freeform front surface (3 x 3 coefficients, two of them zero) on a singlet."""
+    lens.set_aperture(aperture_type="EPD", value=10)
+    lens.set_field_type(field_type="angle")
+    for fy in (0, 5):
+        lens.add_field(y=fy)
+    lens.add_wavelength(value=0.55, is_primary=True)
+    lens.add_surface(index=0, radius=INF, thickness=INF)
+    lens.add_surface(index=1, surface_type="chebyshev", radius=80.0, conic=-0.2, thickness=5.0, material="N-BK7",
+                     is_stop=True, coefficients=to_array(CHEBYSHEV_COEFFS), norm_x=12.0, norm_y=12.0)
+    lens.add_surface(index=2, radius=-70.0, thickness=40.0)
+    lens.add_surface(index=3)
+    return lens
+
+
+class Anamorphic(Optic):
+    def __init__(self):
+        super().__init__("Anamorphic")
+        build_anamorphic(self)
+        self.set_paraxial(EPL=0.0, EPD=14.0)
+
+
+class ChebyshevPlate(Optic):
+    def __init__(self):
+        super().__init__("ChebyshevPlate")
+        build_chebyshev_plate(self)
+        self.set_paraxial(EPL=0.0, EPD=10.0)
+
+
 class ThreeMirrorAnastigmat(Optic):
     def __init__(self):
         super().__init__("TMA")

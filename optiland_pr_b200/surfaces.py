@@ -19,8 +19,8 @@ import torch
 from . import backend as be
 from .apertures import configure_aperture
 from .coordinate_system import CoordinateSystem
-from .geometries import (EvenAsphere, OddAsphere, Plane, PolynomialGeometry, StandardGeometry,
-                         ZernikePolynomialGeometry)
+from .geometries import (BiconicGeometry, ChebyshevPolynomialGeometry, EvenAsphere, OddAsphere, Plane,
+                         PolynomialGeometry, StandardGeometry, ToroidalGeometry, ZernikePolynomialGeometry)
 from .materials import BaseMaterial, IdealMaterial, Material
 from .prescription import PackedSystem, pack_surface_group
 from .rays import RealRays
@@ -174,6 +174,19 @@ class SurfaceGroup:
             geometry = ZernikePolynomialGeometry(cs, radius, conic, tol, max_iter, coefficients,
                                                  kwargs.get("zernike_type", "fringe"),
                                                  kwargs.get("norm_radius", 1.0))
+        elif surface_type == "biconic":      # geometry_factory.py:229-257
+            rx, ry = kwargs.get("radius_x", math.inf), kwargs.get("radius_y", math.inf)
+            kx, ky = kwargs.get("conic_x", 0.0), kwargs.get("conic_y", 0.0)
+            if math.isinf(float(rx)) and math.isinf(float(ry)) and kx == 0.0 and ky == 0.0:
+                geometry = Plane(cs)
+            else:
+                geometry = BiconicGeometry(cs, rx, ry, kx, ky, tol, max_iter)
+        elif surface_type == "toroidal":     # geometry_factory.py:259-279
+            geometry = ToroidalGeometry(cs, kwargs.get("radius_x", math.inf), kwargs.get("radius_y", math.inf), conic,
+                                        kwargs.get("toroidal_coeffs_poly_y"), tol, max_iter)
+        elif surface_type == "chebyshev":    # geometry_factory.py:183-203
+            geometry = ChebyshevPolynomialGeometry(cs, radius, conic, tol, max_iter, coefficients,
+                                                   kwargs.get("norm_x", 1.0), kwargs.get("norm_y", 1.0))
         else:
             raise ValueError(f"surface_type {surface_type!r} is not implemented in optiland_pr_b200")
         if index == 0:
@@ -284,6 +297,9 @@ class SurfaceGroup:
         if res.status & 1:
             raise ValueError("Zernike coordinates must be normalized to [-1, 1]. Consider updating "
                              "the normalization radius to 1.1x the surface aperture.")
+        if res.status & 8:
+            raise ValueError("Chebyshev input coordinates must be normalized to [-1, 1]. Consider updating the "
+                             "normalization factors.")
         if res.status & 2:
             raise ValueError("a ray wavelength is missing from `wavelengths`")
         self._finish(rays, packed, res.out, res.record, res.dir0, res.nr_iters)

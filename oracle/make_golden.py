@@ -138,6 +138,13 @@ def main():
         lens = my_samples.build_freeform_plate(ref_optic.Optic(name="plate"), ref_ap, zt)
         rays = gen_rays(lens, lens.fields.get_field_coords(), [0.55], "random", 700, seed=3)
         run_case("freeform_plate_" + zt, lens, rays, [0.55])
+    # SURVEY.md 8f N4 geometries: biconic / toroidal (anamorphic system) and a Chebyshev freeform
+    lens = my_samples.build_anamorphic(ref_optic.Optic(name="anamorphic"))
+    rays = gen_rays(lens, lens.fields.get_field_coords(), [0.55], "random", 300, seed=4)
+    run_case("anamorphic", lens, rays, [0.55])
+    lens = my_samples.build_chebyshev_plate(ref_optic.Optic(name="chebyshev"), to_array=np.array)
+    rays = gen_rays(lens, lens.fields.get_field_coords(), [0.55], "random", 300, seed=5)
+    run_case("chebyshev_plate", lens, rays, [0.55])
 
 
 if __name__ == "__main__":

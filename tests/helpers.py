@@ -18,6 +18,8 @@ MIRRORS = {
     "freeform_plate_fringe": lambda: samples.FreeformPlate("fringe"),
     "freeform_plate_noll": lambda: samples.FreeformPlate("noll"),
     "freeform_plate_standard": lambda: samples.FreeformPlate("standard"),
+    "anamorphic": samples.Anamorphic,
+    "chebyshev_plate": samples.ChebyshevPlate,
 }
 # lenses inside the backward kernel's differentiable set (gradient fixtures exist for these)
 GRAD_MIRRORS = ("cooke_triplet", "double_gauss", "even_asphere_double_gauss", "aspheric_singlet")

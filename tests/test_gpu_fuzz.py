@@ -101,3 +101,48 @@ def test_tolerance_mode_with_dead_rays(lens_name, n):
     assert (per_ray > 1e-10).mean() <= 1e-4, (per_ray > 1e-10).sum()
     assert per_ray.max() <= 1e-6, per_ray.max()
     assert res.nr_iters == ora["nr_iters"]
+
+
+def test_anamorphic_strict_bit_exact_with_dead_rays():
+    """Biconic / toroidal surfaces (interpreter kernel, + - * / sqrt only) on wild rays: misses of the base conic,
+    the toroid's invalid domain ((R - z_y)^2 < x^2 -> NaN sag, toroidal.py:176-186) and TIR all occur, the reference
+    then runs all max_iter Newton updates, and the strict kernel still gives the oracle's bits."""
+    lens = samples.Anamorphic()
+    for s in lens.surface_group.surfaces[1:]:
+        if hasattr(s.geometry, "max_iter"):
+            s.geometry.max_iter = 12              # keeps the oracle quick; the exit rule never fires (NaN residual)
+    lens.surface_group.surfaces[3].aperture = RadialAperture(r_max=20.0, r_min=0.1)
+    packed = pack_surface_group(lens.surface_group.surfaces, [0.55])
+    rays_in = _wild_rays(40_000, 13, [0.55], half_width=30.0, cone=0.5)
+    ora = trace_np.trace_packed(packed, trace_np.Rays(*rays_in))
+    ref = np.array(ora["records"])
+    dead = np.isnan(ref[-1, 0])
+    assert 0.02 < dead.mean() < 0.98, dead.mean()
+    assert np.isnan(ref[2, 0]).sum() > np.isnan(ref[1, 0]).sum()      # rays really die at the toroid
+    res = fused_trace(packed, [torch.tensor(rays_in[q], device="cuda") for q in range(8)])
+    torch.cuda.synchronize()
+    assert res.nr_iters == ora["nr_iters"] == [12, 12, 12, 12, 0]
+    rec = res.record.cpu().numpy()
+    for q, f in enumerate(FIELDS8):
+        if f == "intensity":
+            assert np.allclose(rec[:, q], ref[:, q], rtol=1e-14, atol=0, equal_nan=True)
+        else:
+            assert np.array_equal(rec[:, q], ref[:, q], equal_nan=True), f
+    fast = fused_trace(packed, [torch.tensor(rays_in[q], device="cuda") for q in range(8)], fast=True)
+    rf = fast.record.cpu().numpy()
+    bad = (np.isnan(rf) != np.isnan(ref)).any(axis=(0, 1)) | ((rf[:, 6] == 0) != (ref[:, 6] == 0)).any(axis=0)
+    assert bad.mean() <= 1e-4, int(bad.sum())
+    m = ~np.isnan(ref[:, :, ~bad])
+    err = np.abs(rf[:, :, ~bad][m] - ref[:, :, ~bad][m]) / np.maximum(np.abs(ref[:, :, ~bad][m]), 1.0)
+    assert (err > 1e-10).mean() <= 1e-4 and err.max() <= 1e-5, ((err > 1e-10).mean(), err.max())
+
+
+def test_chebyshev_range_error():
+    """Rays outside [-norm, norm] at a Chebyshev surface raise the reference's ValueError (chebyshev.py:204-217)."""
+    from optiland_pr_b200 import backend as be
+    be.set_precision("float64")
+    lens = samples.ChebyshevPlate()
+    lens.surface_group.surfaces[1].geometry.norm_x = 3.0
+    fields = lens.get_field_coords()
+    with pytest.raises(ValueError, match="Chebyshev input coordinates must be normalized"):
+        lens.trace(np.array([fields[0][0]]), np.array([fields[0][1]]), 0.55, num_rays=6, distribution="hexapolar")

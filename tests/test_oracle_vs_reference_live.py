@@ -130,3 +130,33 @@ def test_rim_rays_on_the_aperture_edge(ref):
     want, got = _both(ref, lens, rays_in, [0.55])
     assert (want[0, 6] == 0).any() and (want[0, 6] != 0).any()
     assert np.array_equal(got, want, equal_nan=True)
+
+
+def test_anamorphic_geometries_bit_exact_on_wild_rays(ref):
+    """Biconic + toroidal surfaces built in the REFERENCE by the shared builder (samples.build_anamorphic): wild rays
+    that miss the base conic, fall outside the toroid's domain (NaN sag) or totally reflect -- the oracle gives the
+    reference's bits at every surface (only + - * / sqrt on this path; intensity has no absorption here... exp)."""
+    from optiland_pr_b200 import samples as my_samples
+    lens = my_samples.build_anamorphic(ref["Optic"]())
+    for s in lens.surface_group.surfaces[1:]:
+        if hasattr(s.geometry, "max_iter"):
+            s.geometry.max_iter = 10
+    rays_in = _wild(3000, 31, [0.55], half_width=30.0, cone=0.5)
+    want, got = _both(ref, lens, rays_in, [0.55])
+    assert np.isnan(want[2, 0]).sum() > np.isnan(want[1, 0]).sum()      # rays die at the toroid
+    assert 0.02 < np.isnan(want[-1, 0]).mean() < 0.98
+    for q, f in enumerate(FIELDS8):
+        if f == "intensity":
+            assert np.allclose(got[:, q], want[:, q], rtol=1e-14, atol=0, equal_nan=True)
+        else:
+            assert np.array_equal(got[:, q], want[:, q], equal_nan=True), f
+
+
+def test_chebyshev_surface_bit_exact(ref):
+    from optiland_pr_b200 import samples as my_samples
+    lens = my_samples.build_chebyshev_plate(ref["Optic"](), to_array=np.array)
+    rays_in = _wild(2000, 32, [0.55], half_width=5.0, cone=0.05, z0=-3.0)
+    want, got = _both(ref, lens, rays_in, [0.55])
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    m = ~np.isnan(want)
+    assert np.max(np.abs(got[m] - want[m]) / np.maximum(np.abs(want[m]), 1.0)) <= 1e-13
