@@ -79,7 +79,15 @@ enum {
 
 enum {
   OLRT_F_RADIUS_INF = 1,  /* StandardGeometry with infinite radius: clamped plane branch, standard.py:100-103 */
-  OLRT_F_ABSORB = 2       /* material_pre has k>0 for some wavelength: homogeneous.py:45-53 */
+  OLRT_F_ABSORB = 2,      /* material_pre has k>0 for some wavelength: homogeneous.py:45-53 */
+  /* The next three put a surface on the interpreter kernel (never a fast kind, not differentiable). Their reals sit
+   * at the END of the surface's block, just before the aperture parameters: [focal length][coating factor]. */
+  OLRT_F_COATING = 4,     /* SimpleCoating: intensity *= transmittance (reflectance at a mirror) after the
+                             interaction, coatings.py:156-224 + interactions/base.py:111-128 */
+  OLRT_F_THIN_LENS = 8,   /* ThinLensInteractionModel.interact_real_rays (paraxial surface of focal length f),
+                             interactions/thin_lens_interaction_model.py:55-113: leaves (L, M, 1) un-normalised */
+  OLRT_F_RENORM = 16      /* the previous surface was a thin lens: the direction is normalised at the end of this
+                             surface's propagation step, propagation/homogeneous.py:55-57, rays/real_rays.py:503-509 */
 };
 
 /* aperture program tokens (reverse Polish), optiland/physical_apertures/ */

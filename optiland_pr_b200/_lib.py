@@ -29,7 +29,7 @@ GEOM_REALS = 4
 
 GEOM_PLANE, GEOM_STANDARD, GEOM_EVEN_ASPHERE, GEOM_POLYNOMIAL, GEOM_ZERNIKE, GEOM_ODD_ASPHERE = range(6)
 GEOM_BICONIC, GEOM_TOROIDAL, GEOM_CHEBYSHEV = 6, 7, 8
-F_RADIUS_INF, F_ABSORB = 1, 2
+F_RADIUS_INF, F_ABSORB, F_COATING, F_THIN_LENS, F_RENORM = 1, 2, 4, 8, 16
 AP_RADIAL, AP_OFFSET_RADIAL, AP_ELLIPTICAL, AP_RECTANGULAR = 1, 2, 3, 4
 AP_OR, AP_AND, AP_DIFF = 10, 11, 12
 ST_ZERNIKE_RANGE, ST_WAVELENGTH, ST_BAD_HINT, ST_CHEBYSHEV_RANGE = 1, 2, 4, 8

@@ -117,7 +117,8 @@ enum { KIND_GENERIC = 0, KIND_PLANE = 1, KIND_CONIC = 2, KIND_EVEN = 3 };
 
 __device__ __forceinline__ int surface_kind(const int32_t* op) {
   const int geom = op[OLRT_OP_GEOM], flags = op[OLRT_OP_FLAGS];
-  const bool simple = op[OLRT_OP_NFRAMES] == 1 && op[OLRT_OP_FRAMEFLAGS] == 0;
+  const bool simple = op[OLRT_OP_NFRAMES] == 1 && op[OLRT_OP_FRAMEFLAGS] == 0 &&
+                      !(flags & (OLRT_F_COATING | OLRT_F_THIN_LENS | OLRT_F_RENORM));
   if (!simple) return KIND_GENERIC;
   if (geom == OLRT_GEOM_PLANE) return KIND_PLANE;
   if (geom == OLRT_GEOM_STANDARD && !(flags & OLRT_F_RADIUS_INF)) return KIND_CONIC;
@@ -191,6 +192,10 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
     const R alpha = four_pi * kk / wavelength;
     r.i = r.i * r_exp((-alpha) * t * R(1e3));
   }
+  if (KIND == KIND_GENERIC && (flags & OLRT_F_RENORM)) {  // homogeneous.py:55-57 -> real_rays.py:503-509
+    const Recip<R, MM> rm(m_sqrt<MM>(r.L * r.L + r.M * r.M + r.N * r.N));
+    r.L = rm.div(r.L); r.M = rm.div(r.M); r.N = rm.div(r.N);
+  }
   // rays.opd = rays.opd + |t * n_pre|, standard_surface.py:218
   r.opd = r.opd + r_abs(t * sp.n1);
 
@@ -201,6 +206,22 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
     if (!inside) r.i = R(0);
   }
 
+  const bool coated = (KIND == KIND_GENERIC) && (flags & OLRT_F_COATING);
+  if (KIND == KIND_GENERIC && (flags & OLRT_F_THIN_LENS)) {
+    // ThinLensInteractionModel.interact_real_rays, thin_lens_interaction_model.py:55-113
+    const R f = sp.aper[coated ? -2 : -1];
+    r.opd = r.opd - m_div<MM>(r.x * r.x + r.y * r.y, R(2) * f);
+    const R n1 = sp.n1;
+    const R n2 = (op[OLRT_OP_INTERACT] == 1) ? -n1 : sp.media[W + widx];
+    const Recip<R, MM> rN(r.N);
+    const R ux1 = rN.div(r.L), uy1 = rN.div(r.M);
+    const R in2 = m_div<MM>(R(1), n2);
+    const R ux2 = in2 * (n1 * ux1 - m_div<MM>(r.x, f));
+    const R uy2 = in2 * (n1 * uy1 - m_div<MM>(r.y, f));
+    L0 = r.L; M0 = r.M; N0 = r.N;
+    if (coated) r.i = r.i * sp.aper[-1];
+    r.L = ux2; r.M = uy2; r.N = R(1);
+  } else {
   // interaction_model.interact_real_rays, refractive_reflective_model.py:32-55
   R nx, ny, nz;
   if (geom == OLRT_GEOM_PLANE) {
@@ -217,6 +238,8 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
   L0 = r.L; M0 = r.M; N0 = r.N;
   if (op[OLRT_OP_INTERACT] == 1) reflect(r, nx, ny, nz);
   else refract<R, MM>(r, nx, ny, nz, sp.u, sp.u2);
+  if (coated) r.i = r.i * sp.aper[-1];   // BaseCoating.interact -> SimpleCoating.transmit / reflect
+  }
 
   // geometry.globalize, standard_surface.py:228
   if (KIND == KIND_GENERIC) cs_globalize(r, sp.frames, nframes, fflags);

@@ -130,6 +130,8 @@ class PackedSystem:
             geom, flags = int(op[L.OP_GEOM]), int(op[L.OP_FLAGS])
             if op[L.OP_NFRAMES] != 1 or op[L.OP_FRAMEFLAGS] != 0:
                 return False
+            if flags & (L.F_COATING | L.F_THIN_LENS | L.F_RENORM):
+                return False
             if geom == L.GEOM_PLANE:
                 pass
             elif geom in (L.GEOM_STANDARD, L.GEOM_EVEN_ASPHERE) and not flags & L.F_RADIUS_INF:
@@ -217,10 +219,15 @@ def check_surface(surf) -> None:
     if gname not in _GEOM_BY_NAME:
         raise NotEligible(f"geometry {gname} is not implemented in the fused kernel")
     im = surf.interaction_model
-    if type(im).__name__ != "RefractiveReflectiveModel":
+    if type(im).__name__ not in ("RefractiveReflectiveModel", "ThinLensInteractionModel"):
         raise NotEligible(f"interaction model {type(im).__name__} is not implemented")
-    if getattr(im, "coating", None) is not None or getattr(im, "bsdf", None) is not None:
-        raise NotEligible("coatings / BSDFs are not implemented in the fused kernel")
+    if type(im).__name__ == "ThinLensInteractionModel" and gname != "Plane":
+        raise NotEligible("a thin lens on a curved geometry is not implemented")
+    coating = getattr(im, "coating", None)
+    if coating is not None and type(coating).__name__ != "SimpleCoating":
+        raise NotEligible(f"coating {type(coating).__name__} needs polarised rays: not implemented")
+    if getattr(im, "bsdf", None) is not None:
+        raise NotEligible("BSDFs are not implemented in the fused kernel")
     for mat in (surf.material_pre, surf.material_post):
         pm = getattr(mat, "propagation_model", None)
         if pm is not None and type(pm).__name__ != "HomogeneousPropagation":
@@ -337,6 +344,17 @@ def pack_surface_group(surfaces, wavelengths, record="all", skip: int = 0) -> Pa
                 extra_ops += [n, m]
                 zterms.append((n, m, len(reals), norm))
                 reals += [c, c * norm] + zernike_radial_coefficients(n, m)
+        # interpreter-only extras, [focal length][coating factor] just before the aperture parameters (olrt.h)
+        im = surf.interaction_model
+        if type(im).__name__ == "ThinLensInteractionModel":
+            flags |= L.F_THIN_LENS
+            reals.append(_f(im.f))
+        coating = getattr(im, "coating", None)
+        if coating is not None:
+            flags |= L.F_COATING
+            reals.append(_f(coating.reflectance if im.is_reflective else coating.transmittance))
+        if k > 0 and type(real[k - 1][1].interaction_model).__name__ == "ThinLensInteractionModel":
+            flags |= L.F_RENORM
         aoff_reals = len(reals) - doff
         ap_off, ap_len = -1, 0
         if surf.aperture:

@@ -212,11 +212,41 @@ def build_chebyshev_plate(lens, to_array=list):
     return lens
 
 
+def build_coated_relay(lens, coating_cls):
+    """Paraxial thin lenses (one coated), SimpleCoating on refracting surfaces and on a mirror: the interaction
+    models / coatings of SURVEY.md 8f N4. The surface after each thin lens renormalises the direction.
+    The coatings are attached after construction: the reference's add_surface replaces any coating passed to it by
+    a FresnelCoating when the surface is linked to its predecessor (surfaces/standard_surface.py:100-108)."""
+    lens.set_aperture(aperture_type="EPD", value=8)
+    lens.set_field_type(field_type="angle")
+    for fy in (0, 4):
+        lens.add_field(y=fy)
+    lens.add_wavelength(value=0.55, is_primary=True)
+    lens.add_surface(index=0, radius=INF, thickness=INF)
+    lens.add_surface(index=1, surface_type="paraxial", f=50.0, thickness=20.0, is_stop=True)
+    lens.add_surface(index=2, radius=40.0, thickness=4.0, material="N-BK7")
+    lens.add_surface(index=3, radius=-60.0, conic=-0.5, thickness=6.0)
+    lens.add_surface(index=4, surface_type="paraxial", f=-120.0, thickness=8.0)
+    lens.add_surface(index=5, radius=-200.0, thickness=-10.0, material="mirror")
+    lens.add_surface(index=6)
+    for k, (t, r) in {2: (0.96, 0.04), 3: (0.97, 0.03), 4: (0.9, 0.1), 5: (0.05, 0.92)}.items():
+        lens.surface_group.surfaces[k].interaction_model.coating = coating_cls(t, r)
+    return lens
+
+
 class Anamorphic(Optic):
     def __init__(self):
         super().__init__("Anamorphic")
         build_anamorphic(self)
         self.set_paraxial(EPL=0.0, EPD=14.0)
+
+
+class CoatedRelay(Optic):
+    def __init__(self):
+        super().__init__("CoatedRelay")
+        from .surfaces import SimpleCoating
+        build_coated_relay(self, SimpleCoating)
+        self.set_paraxial(EPL=0.0, EPD=8.0)
 
 
 class ChebyshevPlate(Optic):

@@ -41,6 +41,25 @@ class RefractiveReflectiveModel:
         self.bsdf = bsdf
 
 
+class ThinLensInteractionModel(RefractiveReflectiveModel):
+    """interactions/thin_lens_interaction_model.py:23-113: a paraxial thin lens of focal length f on a plane."""
+
+    interaction_type = "thin_lens"
+
+    def __init__(self, parent_surface=None, focal_length=None, is_reflective=False, coating=None, bsdf=None):
+        super().__init__(parent_surface, is_reflective, coating, bsdf)
+        self.f = focal_length
+
+
+class SimpleCoating:
+    """coatings.py:156-224: intensity *= transmittance (refraction) or reflectance (mirror)."""
+
+    def __init__(self, transmittance, reflectance=0):
+        self.transmittance = transmittance
+        self.reflectance = reflectance
+        self.absorptance = 1 - reflectance - transmittance
+
+
 class Surface:
     def __init__(self, previous_surface, material_post, geometry, is_stop=False, aperture=None,
                  surface_type=None, comment="", interaction_model=None):
@@ -174,6 +193,8 @@ class SurfaceGroup:
             geometry = ZernikePolynomialGeometry(cs, radius, conic, tol, max_iter, coefficients,
                                                  kwargs.get("zernike_type", "fringe"),
                                                  kwargs.get("norm_radius", 1.0))
+        elif surface_type == "paraxial":     # geometry_factory.py:352-362: a plane; the thin lens is the interaction
+            geometry = Plane(cs)
         elif surface_type == "biconic":      # geometry_factory.py:229-257
             rx, ry = kwargs.get("radius_x", math.inf), kwargs.get("radius_y", math.inf)
             kx, ky = kwargs.get("conic_x", 0.0), kwargs.get("conic_y", 0.0)
@@ -189,13 +210,17 @@ class SurfaceGroup:
                                                    kwargs.get("norm_x", 1.0), kwargs.get("norm_y", 1.0))
         else:
             raise ValueError(f"surface_type {surface_type!r} is not implemented in optiland_pr_b200")
+        reflective = isinstance(material, str) and material == "mirror"
         if index == 0:
             surf = ObjectSurface(geometry, post, comment)
         else:
             surf = Surface(None, post, geometry, is_stop=is_stop, aperture=kwargs.get("aperture"),
                            surface_type=surface_type, comment=comment,
-                           interaction_model=RefractiveReflectiveModel(
-                               None, is_reflective=(isinstance(material, str) and material == "mirror")))
+                           interaction_model=(
+                               ThinLensInteractionModel(None, kwargs.get("f"), reflective, kwargs.get("coating"))
+                               if surface_type == "paraxial" else
+                               RefractiveReflectiveModel(None, is_reflective=reflective,
+                                                         coating=kwargs.get("coating"))))
         surf.thickness = kwargs.get("thickness", 0.0)
         self._surfaces.append(surf)
         self._link()

@@ -145,6 +145,11 @@ def main():
     lens = my_samples.build_chebyshev_plate(ref_optic.Optic(name="chebyshev"), to_array=np.array)
     rays = gen_rays(lens, lens.fields.get_field_coords(), [0.55], "random", 300, seed=5)
     run_case("chebyshev_plate", lens, rays, [0.55])
+    # thin lenses + SimpleCoating (interaction models / coatings of 8f N4)
+    from optiland.coatings import SimpleCoating
+    lens = my_samples.build_coated_relay(ref_optic.Optic(name="coated_relay"), SimpleCoating)
+    rays = gen_rays(lens, lens.fields.get_field_coords(), [0.55], "random", 300, seed=6)
+    run_case("coated_relay", lens, rays, [0.55])
 
 
 if __name__ == "__main__":

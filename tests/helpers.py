@@ -20,11 +20,12 @@ MIRRORS = {
     "freeform_plate_standard": lambda: samples.FreeformPlate("standard"),
     "anamorphic": samples.Anamorphic,
     "chebyshev_plate": samples.ChebyshevPlate,
+    "coated_relay": samples.CoatedRelay,
 }
 # lenses inside the backward kernel's differentiable set (gradient fixtures exist for these)
 GRAD_MIRRORS = ("cooke_triplet", "double_gauss", "even_asphere_double_gauss", "aspheric_singlet")
 # fixtures whose surfaces are all closed-form (+,-,*,/,sqrt only): oracle must match the reference bit for bit
-CLOSED_FORM = ("cooke_triplet", "double_gauss")
+CLOSED_FORM = ("cooke_triplet", "double_gauss", "coated_relay")
 
 
 def load_golden(name):
