@@ -183,7 +183,11 @@ int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* o
  *  gpresc  [n_presc][presc_stride] accumulated with atomicAdd (caller zero-initialises): filled for
  *          frame x y z, radius, conic and even-asphere coefficients; other entries stay zero
  *  status  NULL or one uint32: OLRT_ST_BAD_HINT when a surface is outside the differentiable set (plane /
- *          conic / even asphere with <= 8 coefficients on one untilted frame): nothing is written then   */
+ *          conic / even asphere with <= 8 coefficients on one untilted frame): nothing is written then
+ *  flags   0: lenses with olrt_sys.kernel_hint & OLRT_HINT_FASTKINDS and <= 3 Newton updates per surface run the
+ *          reduced-algebra adjoint kernel (csrc/trace_bx.cuh), every other differentiable lens the general one
+ *          (csrc/trace_bwd.cuh); OLRT_BWD_GENERIC forces the general kernel                                  */
+#define OLRT_BWD_GENERIC 1
 int olrt_trace_bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, int64_t n_rays,
                        const double* const in[8], const double* record, const double* const gout[8],
                        const double* grecord, double* const gin[8], double* gpresc, uint32_t* status,

@@ -34,6 +34,8 @@ AP_RADIAL, AP_OFFSET_RADIAL, AP_ELLIPTICAL, AP_RECTANGULAR = 1, 2, 3, 4
 AP_OR, AP_AND, AP_DIFF = 10, 11, 12
 ST_ZERNIKE_RANGE, ST_WAVELENGTH, ST_BAD_HINT, ST_CHEBYSHEV_RANGE = 1, 2, 4, 8
 HINT_FASTKINDS = 1
+BWD_GENERIC = 1          # olrt_trace_bwd_* flag: force the general adjoint kernel (csrc/trace_bwd.cuh)
+BX_MAXK = 3              # Newton updates per surface the reduced-algebra adjoint kernel (csrc/trace_bx.cuh) unrolls
 FWD_FAST = 1
 FWD_REPLAY = 2
 SPOT_VALID_ONLY = 1

@@ -60,7 +60,7 @@ class FusedTraceFn(torch.autograd.Function):
     """(presc, x, y, z, L, M, N, i, opd_in, w) -> (out [8, N], record [S, 8, N])."""
 
     @staticmethod
-    def forward(ctx, presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast):
+    def forward(ctx, presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast, generic_adjoint=False):
         if packed.record_surfaces != [lay.index for lay in packed.layouts]:
             raise L.OlrtLibraryError("the differentiable trace needs every surface recorded (record='all')")
         ins = [x, y, z, Lc, M, N, inten, w]
@@ -69,6 +69,7 @@ class FusedTraceFn(torch.autograd.Function):
                           presc=presc.detach().reshape(1, -1), want_dir0=True, fast=fast)
         ctx.set_materialize_grads(False)
         ctx.packed = packed
+        ctx.generic_adjoint = bool(generic_adjoint)
         ctx.nr_iters = list(res.nr_iters)
         ctx.save_for_backward(presc.detach(), *[t.detach() for t in ins if t is not None], res.record)
         ctx.has_w = w is not None
@@ -91,7 +92,9 @@ class FusedTraceFn(torch.autograd.Function):
         lib = L.load()
         packed.set_nr_iters(ctx.nr_iters)
         ops_d, _ = _device_tables(packed, dtype, device)
-        gin = torch.zeros((8, n), dtype=dtype, device=device)
+        # d loss / d rays only where a ray tensor asks for it (the kernel writes every element of a requested array)
+        need = [bool(ctx.needs_input_grad[1 + q]) for q in range(7)] + [bool(ctx.has_opd and ctx.needs_input_grad[8])]
+        gin = torch.empty((8, n), dtype=dtype, device=device) if any(need) else None
         gpresc = torch.zeros_like(presc)
         status = torch.zeros(1, dtype=torch.int32, device=device)
         gout = None if gout is None else gout.contiguous()
@@ -101,10 +104,12 @@ class FusedTraceFn(torch.autograd.Function):
         fn = lib.olrt_trace_bwd_f64 if dtype == torch.float64 else lib.olrt_trace_bwd_f32
         in_arr = L.PtrArray8(*[_ptr(t) for t in ins])
         gout_arr = L.PtrArray8(*[0 if gout is None else gout[q].data_ptr() for q in range(8)])
-        gin_arr = L.PtrArray8(*[gin[q].data_ptr() for q in range(8)])
+        gin_arr = L.PtrArray8(*[gin[q].data_ptr() if need[q] else 0 for q in range(8)])
+        # the reduced-algebra adjoint (csrc/trace_bx.cuh) keeps <= BX_MAXK Newton iterates in registers
+        flags = L.BWD_GENERIC if (ctx.generic_adjoint or max(ctx.nr_iters, default=0) > L.BX_MAXK) else 0
         with torch.cuda.device(device):
             rc = fn(C.byref(sys_), presc.data_ptr(), ops_d.data_ptr(), n, in_arr, record.data_ptr(), gout_arr,
-                    _ptr(grecord), gin_arr, gpresc.data_ptr(), status.data_ptr(), 0,
+                    _ptr(grecord), gin_arr, gpresc.data_ptr(), status.data_ptr(), flags,
                     torch.cuda.current_stream(device).cuda_stream)
         if rc == -4:
             raise NotImplementedError("olrt_trace_bwd: this lens is outside the differentiable set")
@@ -113,15 +118,16 @@ class FusedTraceFn(torch.autograd.Function):
             raise NotImplementedError(
                 "olrt_trace_bwd: gradients are implemented for plane / conic / even-asphere surfaces on an "
                 "untilted frame; this lens has a surface outside that set")
-        g = [gin[q] for q in range(7)]
-        return (gpresc, g[0], g[1], g[2], g[3], g[4], g[5], g[6], gin[7] if ctx.has_opd else None, None, None,
-                None)
+        g = [gin[q] if need[q] else None for q in range(8)]
+        return (gpresc, g[0], g[1], g[2], g[3], g[4], g[5], g[6], g[7], None, None, None, None)
 
 
-def trace_differentiable(packed: PackedSystem, presc: torch.Tensor, rays_in, opd_in=None, fast: bool = False):
-    """rays_in: 8 tensors (w may be None for a single wavelength). Returns (out, record, dir0)."""
+def trace_differentiable(packed: PackedSystem, presc: torch.Tensor, rays_in, opd_in=None, fast: bool = False,
+                         generic_adjoint: bool = False):
+    """rays_in: 8 tensors (w may be None for a single wavelength). Returns (out, record, dir0).
+    generic_adjoint=True forces the general backward kernel (csrc/trace_bwd.cuh) instead of the reduced-algebra one."""
     x, y, z, Lc, M, N, inten, w = (list(rays_in) + [None])[:8]
-    return FusedTraceFn.apply(presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast)
+    return FusedTraceFn.apply(presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast, generic_adjoint)
 
 
 def _rms_merit(lens, fields, wavelength, Px, Py):

@@ -307,22 +307,20 @@ extern "C" int olrt_trace_bwd_f64(const olrt_sys* sys, const double* presc, cons
                                   const double* const gout[8], const double* grecord,
                                   double* const gin[8], double* gpresc, uint32_t* status, int flags,
                                   void* stream) {
-  (void)flags;
   int rc = check_bwd<double>(sys, presc, ops, n_rays, in, record, gpresc);
   if (rc) return rc;
   if (n_rays == 0) return OLRT_OK;
-  return olrt_fast::bwd_f64(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status,
+  return olrt_fast::bwd_f64(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, flags,
                             (cudaStream_t)stream);
 }
 extern "C" int olrt_trace_bwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops,
                                   int64_t n_rays, const float* const in[8], const float* record,
                                   const float* const gout[8], const float* grecord, float* const gin[8],
                                   float* gpresc, uint32_t* status, int flags, void* stream) {
-  (void)flags;
   int rc = check_bwd<float>(sys, presc, ops, n_rays, in, record, gpresc);
   if (rc) return rc;
   if (n_rays == 0) return OLRT_OK;
-  return olrt_fast::bwd_f32(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status,
+  return olrt_fast::bwd_f32(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, flags,
                             (cudaStream_t)stream);
 }
 

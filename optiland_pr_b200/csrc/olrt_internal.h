@@ -33,7 +33,7 @@ int selftest_math(const double* a, const double* b, double* q, double* r, long l
   namespace olrt_fast {                                                                                \
   int bwd_##SUF(const olrt_sys* sys, const R* presc, const int32_t* ops, long long n_rays,             \
                 const R* const in[8], const R* record, const R* const gout[8], const R* grecord,       \
-                R* const gin[8], R* gpresc, uint32_t* status, cudaStream_t stream);                    \
+                R* const gin[8], R* gpresc, uint32_t* status, int flags, cudaStream_t stream);         \
   }
 OLRT_DECL_BWD(f64, double)
 OLRT_DECL_BWD(f32, float)

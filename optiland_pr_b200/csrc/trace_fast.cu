@@ -3,6 +3,7 @@
 #define OLRT_NS olrt_fast
 #define OLRT_FX 1  // this TU also carries the reduced-algebra kernel (trace_fx.cuh)
 #include "trace_launch.cuh"
+#include "trace_bx.cuh"
 #include "olrt_internal.h"
 
 namespace olrt_fast {
@@ -41,12 +42,12 @@ int pupil_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, const
 }
 int bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, long long n_rays,
             const double* const in[8], const double* record, const double* const gout[8], const double* grecord,
-            double* const gin[8], double* gpresc, uint32_t* status, cudaStream_t stream) {
-  return launch_bwd<double>(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, stream);
+            double* const gin[8], double* gpresc, uint32_t* status, int flags, cudaStream_t stream) {
+  return launch_bx<double>(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, flags, stream);
 }
 int bwd_f32(const olrt_sys* sys, const float* presc, const int32_t* ops, long long n_rays,
             const float* const in[8], const float* record, const float* const gout[8], const float* grecord,
-            float* const gin[8], float* gpresc, uint32_t* status, cudaStream_t stream) {
-  return launch_bwd<float>(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, stream);
+            float* const gin[8], float* gpresc, uint32_t* status, int flags, cudaStream_t stream) {
+  return launch_bx<float>(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, flags, stream);
 }
 }  // namespace olrt_fast
