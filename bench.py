@@ -376,15 +376,16 @@ def main():
 
     # ---- e2e: public API with host inputs
     h2d = Px_h.numel() * 8 * 2 + nf * 8 * 2
-    d2h = nf * 8
+    # read back per step: the spot sums [nf][10] doubles, the status word, the Newton residual maxima
+    d2h = nf * _lib.SPOT_SUMS * 8 + 4 + packed.n_surfaces * _lib.RESID_STRIDE * 8
     rms_host = torch.empty(nf, dtype=torch.float64).pin_memory()
 
     def step_e2e():
         rr = lens.trace(Hx, Hy, WAVELENGTH, distribution=(Px_h, Py_h), spot=True)
-        s = rr.spot_sums
         if world > 1:
-            s = parallel.allreduce_spot_sums(s)
-        rms_host.copy_(spot.spot_stats(s)["rms"], non_blocking=False)
+            rms_host.copy_(spot.spot_stats(parallel.allreduce_spot_sums(rr.spot_sums))["rms"], non_blocking=False)
+        else:   # the sums came back with the status word (one pinned read-back inside Optic.trace)
+            rms_host.copy_(spot.spot_stats(rr.spot_sums_host)["rms"])
 
     del out, Px_d, Py_d
     torch.cuda.empty_cache()

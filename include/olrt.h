@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define OLRT_ABI_VERSION 4
+#define OLRT_ABI_VERSION 5
 
 #define OLRT_MAX_SURFACES 64    /* intersected surfaces per system (object surface excluded) */
 #define OLRT_MAX_WAVELENGTHS 8  /* distinct wavelengths per launch */
@@ -116,6 +116,7 @@ enum {
 #define OLRT_ST_ZERNIKE_RANGE 1u /* |x/R_n|>1 or |y/R_n|>1 at a Zernike surface: zernike.py:234-246 */
 #define OLRT_ST_WAVELENGTH 2u    /* a ray wavelength is not in olrt_sys.wavelengths */
 #define OLRT_ST_CHEBYSHEV_RANGE 8u /* |x/norm_x|>1 or |y/norm_y|>1 at a Chebyshev surface: chebyshev.py:204-217 */
+#define OLRT_ST_TIMEOUT 16u      /* streamed pupil grid (olrt_pupil.ready): a chunk never arrived */
 #define OLRT_ST_BAD_HINT 4u      /* olrt_sys.kernel_hint claims something the ops table does not satisfy: nothing traced */
 
 /* kernel_hint bits */
@@ -248,6 +249,14 @@ typedef struct olrt_pupil {
   int32_t n_fields;
   int32_t reserved0;
   double EPD, EPL, z_start, wavelength;
+  /* olrt_trace_pupil_* only, streamed pupil grid: NULL, or [ceil(n_pupil / ready_chunk)] device words that a copy
+   * engine sets to non-zero, in order, as the host->device copy of pupil points [c * ready_chunk, (c+1) *
+   * ready_chunk) of Px and Py lands (a 4-byte cudaMemcpyAsync queued behind each chunk's copies on the copy stream).
+   * ONE launch then covers the whole grid while it is still arriving: the kernel's CTAs walk the pupil in copy
+   * order and wait on the word of the chunk they reach. ready_chunk must be a multiple of 256; needs
+   * olrt_sys.n_presc == 1, p_lo == 0. A word that stays zero for ~2 s sets OLRT_ST_TIMEOUT and ends the launch. */
+  const uint32_t* ready;
+  int64_t ready_chunk;
 } olrt_pupil;
 int olrt_generate_rays_f64(const olrt_pupil* pupil, double* const out[8], void* stream);
 int olrt_generate_rays_f32(const olrt_pupil* pupil, float* const out[8], void* stream);
@@ -278,6 +287,14 @@ int olrt_generate_rays_f32(const olrt_pupil* pupil, float* const out[8], void* s
  *             rays < tol, newton_raphson.py:148) gives each group its own K_s (<= OLRT_GROUP_RESID - 1 here).
  *  group_resid NULL, or [groups][n_surfaces][OLRT_GROUP_RESID] u64 (device, zeroed by the caller): max |f| per
  *             group, surface and iteration (bits of a non-negative double), for the caller to check K_s with.    */
+/* Host -> device upload of a pinned pupil grid for the streamed mode above, in ONE call: for every chunk c of
+ * `ready_chunk` points, cudaMemcpyAsync of Px and Py followed by a 4-byte copy that sets ready[c] (from `one_host`,
+ * a pinned non-zero word), all on `copy_stream` -- the copy engine executes them in order, so ready[c] != 0 implies
+ * the chunk's data is in device memory. The caller zeroes `ready` (ordered before this call's stream) and launches
+ * olrt_trace_pupil_* with the same ready / ready_chunk on its compute stream AFTER this call returns.           */
+int olrt_upload_pupil(double* Px_dev, double* Py_dev, const double* Px_host, const double* Py_host,
+                      int64_t n_pupil, int64_t ready_chunk, uint32_t* ready, const uint32_t* one_host,
+                      void* copy_stream);
 #define OLRT_GROUP_RESID 8
 int olrt_trace_pupil_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, const olrt_pupil* pupil,
                          double* const out[8], double* dir0, unsigned long long* nr_resid, uint32_t* status,

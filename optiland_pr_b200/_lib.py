@@ -12,7 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("OLRT_LIB") or os.path.join(_HERE, "libolrt.so")  # OLRT_LIB: A/B builds only
 
-OLRT_ABI_VERSION = 4
+OLRT_ABI_VERSION = 5
 MAX_SURFACES = 64
 MAX_WAVELENGTHS = 8
 MAX_NR_ITERS = 128
@@ -32,7 +32,7 @@ GEOM_BICONIC, GEOM_TOROIDAL, GEOM_CHEBYSHEV = 6, 7, 8
 F_RADIUS_INF, F_ABSORB, F_COATING, F_THIN_LENS, F_RENORM = 1, 2, 4, 8, 16
 AP_RADIAL, AP_OFFSET_RADIAL, AP_ELLIPTICAL, AP_RECTANGULAR = 1, 2, 3, 4
 AP_OR, AP_AND, AP_DIFF = 10, 11, 12
-ST_ZERNIKE_RANGE, ST_WAVELENGTH, ST_BAD_HINT, ST_CHEBYSHEV_RANGE = 1, 2, 4, 8
+ST_ZERNIKE_RANGE, ST_WAVELENGTH, ST_BAD_HINT, ST_CHEBYSHEV_RANGE, ST_TIMEOUT = 1, 2, 4, 8, 16
 HINT_FASTKINDS = 1
 BWD_GENERIC = 1          # olrt_trace_bwd_* flag: force the general adjoint kernel (csrc/trace_bwd.cuh)
 BX_MAXK = 3              # Newton updates per surface the reduced-algebra adjoint kernel (csrc/trace_bx.cuh) unrolls
@@ -69,6 +69,7 @@ class OlrtPupil(C.Structure):
         ("n_pupil", C.c_int64), ("p_lo", C.c_int64), ("p_len", C.c_int64),
         ("n_fields", C.c_int32), ("reserved0", C.c_int32),
         ("EPD", C.c_double), ("EPL", C.c_double), ("z_start", C.c_double), ("wavelength", C.c_double),
+        ("ready", C.c_void_p), ("ready_chunk", C.c_int64),
     ]
 
 
@@ -93,6 +94,7 @@ EXPORTS = [
     "olrt_generate_rays_f64", "olrt_generate_rays_f32",
     "olrt_trace_pupil_f64", "olrt_trace_pupil_f32",
     "olrt_opd_epilogue_f64", "olrt_opd_epilogue_f32",
+    "olrt_upload_pupil",
 ]
 
 _lib = None
@@ -117,6 +119,9 @@ def load():
         if not hasattr(lib, name):
             raise OlrtLibraryError(f"libolrt.so does not export {name}")
     lib.olrt_version.restype = C.c_int
+    lib.olrt_upload_pupil.restype = C.c_int
+    lib.olrt_upload_pupil.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                      C.c_void_p, C.c_void_p, C.c_void_p]
     lib.olrt_build_info.restype = C.c_char_p
     v = C.c_void_p
     fwd_args = [C.POINTER(OlrtSys), v, v, C.c_int64, PtrArray8, v, PtrArray8, v, v, v, v, v, C.c_int, v]

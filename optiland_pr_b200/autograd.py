@@ -13,6 +13,7 @@ whatever those depend on (e.g. cs.z of later surfaces on an earlier thickness, o
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -56,6 +57,10 @@ def prescription_tensor(packed: PackedSystem, surfaces, dtype, device) -> torch.
     return base.scatter(0, idx, vals)
 
 
+# OLRT_CHECK_BWD_STATUS=1: also read the backward kernel's status word back after every launch (a device sync)
+_CHECK_BWD_STATUS = os.environ.get("OLRT_CHECK_BWD_STATUS", "0") == "1"
+
+
 class FusedTraceFn(torch.autograd.Function):
     """(presc, x, y, z, L, M, N, i, opd_in, w) -> (out [8, N], record [S, 8, N])."""
 
@@ -90,6 +95,10 @@ class FusedTraceFn(torch.autograd.Function):
         dtype, device = record.dtype, record.device
         n = int(record.shape[2])
         lib = L.load()
+        if not packed.differentiable():
+            raise NotImplementedError(
+                "olrt_trace_bwd: gradients are implemented for plane / conic / even-asphere surfaces (<= 8 "
+                "coefficients) on an untilted frame; this lens has a surface outside that set")
         packed.set_nr_iters(ctx.nr_iters)
         ops_d, _ = _device_tables(packed, dtype, device)
         # d loss / d rays only where a ray tensor asks for it (the kernel writes every element of a requested array)
@@ -114,7 +123,8 @@ class FusedTraceFn(torch.autograd.Function):
         if rc == -4:
             raise NotImplementedError("olrt_trace_bwd: this lens is outside the differentiable set")
         L.check(rc, "olrt_trace_bwd")
-        if int(status.item()) & L.ST_BAD_HINT:
+        # the host check above mirrors the kernels' own; reading the device word back would serialise every step
+        if _CHECK_BWD_STATUS and int(status.item()) & L.ST_BAD_HINT:
             raise NotImplementedError(
                 "olrt_trace_bwd: gradients are implemented for plane / conic / even-asphere surfaces on an "
                 "untilted frame; this lens has a surface outside that set")

@@ -324,6 +324,23 @@ extern "C" int olrt_trace_bwd_f32(const olrt_sys* sys, const float* presc, const
                             (cudaStream_t)stream);
 }
 
+extern "C" int olrt_upload_pupil(double* Px_dev, double* Py_dev, const double* Px_host, const double* Py_host,
+                                 int64_t n_pupil, int64_t ready_chunk, uint32_t* ready, const uint32_t* one_host,
+                                 void* copy_stream) {
+  if (!Px_dev || !Py_dev || !Px_host || !Py_host || !ready || !one_host || n_pupil < 0) return OLRT_E_ARG;
+  if (ready_chunk <= 0 || ready_chunk % 256 != 0) return OLRT_E_ARG;
+  cudaStream_t st = (cudaStream_t)copy_stream;
+  int64_t c = 0;
+  for (int64_t lo = 0; lo < n_pupil; lo += ready_chunk, ++c) {
+    const int64_t len = (n_pupil - lo < ready_chunk) ? (n_pupil - lo) : ready_chunk;
+    if (cudaMemcpyAsync(Px_dev + lo, Px_host + lo, (size_t)len * sizeof(double), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+        cudaMemcpyAsync(Py_dev + lo, Py_host + lo, (size_t)len * sizeof(double), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+        cudaMemcpyAsync(ready + c, one_host, sizeof(uint32_t), cudaMemcpyHostToDevice, st) != cudaSuccess)
+      return OLRT_E_LAUNCH;
+  }
+  return OLRT_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // OPD / wavefront epilogue (kernel in trace_strict.cu)
 // ---------------------------------------------------------------------------------------------

@@ -25,6 +25,8 @@ struct GenParams {
   long long len;
   int n_fields;
   double EPD, EPL, z_start, wavelength;
+  const unsigned* ready;  // nullptr, or one word per ready_chunk pupil points, set by the copy engine (olrt.h)
+  long long ready_chunk;
 };
 
 // ray (field f, pupil point p): origin on the launch plane (or the object point), direction towards the pupil point
@@ -32,7 +34,7 @@ struct GenParams {
 // exact), and vx = 1 multiplies exactly, so one product serves both and the unvignetted bits do not change.
 __device__ __forceinline__ void gen_ray(const GenParams& G, int f, long long p, double& x0, double& y0, double& z0,
                                         double& L, double& M, double& N) {
-  const double px = G.px[p], py = G.py[p];
+  const double px = __ldcg(G.px + p), py = __ldcg(G.py + p);  // L2 only: read once per field, maybe just copied in
   const double xf = G.fxy[2 * f], yf = G.fxy[2 * f + 1];
   double x1 = __dmul_rn(px, G.EPD), y1 = __dmul_rn(py, G.EPD);
   if (G.vig != nullptr) {

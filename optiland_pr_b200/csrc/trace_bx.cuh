@@ -354,7 +354,10 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
   }
   const long long N = P.n_rays;
   const int lane = threadIdx.x & 31;
-  const unsigned ck_a = (unsigned)__cvta_generic_to_shared(s_ck + threadIdx.x);  // this thread's column
+  // this thread's column of the checkpoint buffers as a 32-bit shared address; the volatile asm keeps the compiler
+  // from re-deriving it (cvta + 64-bit arithmetic) at every cp.async
+  unsigned ck_a;
+  asm volatile("{ .reg .u64 t; cvta.to.shared.u64 t, %1; cvt.u32.u64 %0, t; }" : "=r"(ck_a) : "l"(s_ck + threadIdx.x));
   const R* ck_t = s_ck + threadIdx.x;
   int cur_p = -1;
   const long long n_tiles = (N + bd - 1) / bd;

@@ -21,6 +21,7 @@ static GenParams to_gen(const olrt_pupil* q) {
   GenParams g;
   g.px = q->Px; g.py = q->Py; g.fxy = q->field_xy; g.vig = q->field_vig; g.fz = q->field_z;
   g.n_pupil = q->n_pupil; g.p_lo = q->p_lo; g.len = q->p_len;
+  g.ready = q->ready; g.ready_chunk = q->ready_chunk;
   g.n_fields = q->n_fields; g.EPD = q->EPD; g.EPL = q->EPL; g.z_start = q->z_start; g.wavelength = q->wavelength;
   return g;
 }

@@ -382,6 +382,7 @@ trace_fx_kernel(const FwdParams<R> P) {
   int32_t* s_ops = reinterpret_cast<int32_t*>(s_info + S);
   unsigned long long* s_resid = reinterpret_cast<unsigned long long*>(s_ops + ((P.ops_len + 3) & ~3));
   __shared__ int s_bad, s_nresid;
+  __shared__ unsigned s_ready;
   __shared__ int s_gk[OLRT_MAX_SURFACES];  // group mode: the current group's Newton trip counts
 
   for (int q = threadIdx.x; q < P.ops_len; q += blockDim.x) s_ops[q] = P.ops[q];
@@ -425,7 +426,17 @@ trace_fx_kernel(const FwdParams<R> P) {
   const long long n_tiles = pupil ? tpf * P.gen.n_fields * P.n_presc : (P.n_rays + blockDim.x - 1) / blockDim.x;
   const long long NT = P.n_total;
   long long tile_lo = blockIdx.x, tile_hi = n_tiles, tile_step = gridDim.x;
-  if (pupil) {
+  // streamed pupil grid (olrt_pupil.ready): the grid is still arriving from the host, chunk by chunk in pupil order.
+  // CTA b keeps ONE field, b % n_fields, and walks that field's pupil tiles b / n_fields, + gridDim / n_fields, ...
+  // so every CTA consumes the pupil in copy order; before a tile it waits for the word of the chunk the tile ends in.
+  const bool streamed = pupil && (P.gen.ready != nullptr);
+  const long long s_off = streamed ? (long long)(blockIdx.x % P.gen.n_fields) * tpf : 0;
+  int ready_c = -1;
+  if (streamed) {
+    tile_lo = blockIdx.x / P.gen.n_fields;
+    tile_hi = tpf;
+    tile_step = gridDim.x / P.gen.n_fields;
+  } else if (pupil) {
     tile_lo = n_tiles * blockIdx.x / gridDim.x;
     tile_hi = n_tiles * (blockIdx.x + 1) / gridDim.x;
     tile_step = 1;
@@ -435,8 +446,31 @@ trace_fx_kernel(const FwdParams<R> P) {
   int sp_g = -1;
   double sp_cnt = 0, sp_x = 0, sp_y = 0, sp_xx = 0, sp_yy = 0, sp_i = 0, sp_max = 0, sp_sx = 0, sp_sy = 0;
   bool sp_nan = false;
-  for (long long tile = tile_lo; tile < tile_hi; tile += tile_step) {
+  for (long long it = tile_lo; it < tile_hi; it += tile_step) {
+    const long long tile = it + s_off;
     const long long base = tile * blockDim.x;
+    if (streamed) {
+      long long last = (it + 1) * blockDim.x - 1;
+      if (last > P.gen.len - 1) last = P.gen.len - 1;
+      const int c = (int)((P.gen.p_lo + last) / P.gen.ready_chunk);
+      if (c > ready_c) {  // the copy engine sets the words in order: waiting for the last one covers the tile
+        if (threadIdx.x == 0) {  // one poller per CTA; the barrier hands its acquire on to the other threads
+          const long long t0 = clock64();
+          unsigned v;
+          for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(P.gen.ready + c) : "memory");
+            if (v != 0u || clock64() - t0 > 4000000000LL) break;  // ~2 s: never hang the GPU
+            __nanosleep(256);
+          }
+          s_ready = v;
+        }
+        __syncthreads();
+        const unsigned v = s_ready;
+        __syncthreads();
+        if (v == 0u) { status |= OLRT_ST_TIMEOUT; break; }  // CTA-uniform
+        ready_c = c;
+      }
+    }
     const int grp = pupil ? (int)(tile / tpf) : 0;
     const int p = (P.n_presc > 1) ? (pupil ? grp / P.gen.n_fields : (int)(base / P.rays_per_presc)) : 0;
     if (p != cur_p) {
@@ -511,18 +545,18 @@ trace_fx_kernel(const FwdParams<R> P) {
       }
       const int slot = info.record;
       if (slot >= 0 && valid && P.record != nullptr) {  // Surface._record, standard_surface.py:266-286
-        R* rec = P.record + (long long)slot * 8 * NT + idx;
-        rec[0] = r.x; rec[NT] = r.y; rec[2 * NT] = r.z;
-        rec[3 * NT] = r.L; rec[4 * NT] = r.M; rec[5 * NT] = r.N;
-        rec[6 * NT] = fk_intensity(r.i, att); rec[7 * NT] = r.opd;
+        R* rec = P.record + (long long)slot * 8 * NT + idx;  // streaming stores: never re-read by this launch
+        __stcs(rec, r.x); __stcs(rec + NT, r.y); __stcs(rec + 2 * NT, r.z);
+        __stcs(rec + 3 * NT, r.L); __stcs(rec + 4 * NT, r.M); __stcs(rec + 5 * NT, r.N);
+        __stcs(rec + 6 * NT, fk_intensity(r.i, att)); __stcs(rec + 7 * NT, r.opd);
       }
     }
     r.i = fk_intensity(r.i, att);
     if (valid) {
       if (P.out[0] != nullptr) {
-        P.out[0][idx] = r.x; P.out[1][idx] = r.y; P.out[2][idx] = r.z;
-        P.out[3][idx] = r.L; P.out[4][idx] = r.M; P.out[5][idx] = r.N;
-        P.out[6][idx] = r.i; P.out[7][idx] = r.opd;
+        __stcs(P.out[0] + idx, r.x); __stcs(P.out[1] + idx, r.y); __stcs(P.out[2] + idx, r.z);
+        __stcs(P.out[3] + idx, r.L); __stcs(P.out[4] + idx, r.M); __stcs(P.out[5] + idx, r.N);
+        __stcs(P.out[6] + idx, r.i); __stcs(P.out[7] + idx, r.opd);
       }
       if (P.dir0 != nullptr) {
         P.dir0[idx] = L0; P.dir0[NT + idx] = M0; P.dir0[2 * NT + idx] = N0;

@@ -103,6 +103,13 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
     if (per_sm < 1) per_sm = 1;
     long long grid = (long long)sm_count() * per_sm;
     if (grid > n_tiles) grid = n_tiles;
+    if (gen != nullptr && gen->ready != nullptr) {  // streamed pupil grid: every CTA keeps one field
+      if (sys->n_presc != 1 || gen->p_lo != 0 || gen->ready_chunk <= 0 || gen->ready_chunk % 256 != 0 ||
+          group_k != nullptr)
+        return OLRT_E_ARG;
+      grid = grid / gen->n_fields * gen->n_fields;
+      if (grid < gen->n_fields) grid = gen->n_fields;
+    }
     trace_fx_kernel<R><<<(unsigned)grid, block, xsmem, stream>>>(P);
 #endif
   } else if (fk) {

@@ -48,6 +48,7 @@ static GenParams to_gen(const olrt_pupil* q) {
   g.px = q->Px; g.py = q->Py; g.fxy = q->field_xy; g.vig = q->field_vig; g.fz = q->field_z;
   g.n_pupil = q->n_pupil; g.p_lo = 0; g.len = q->n_pupil;
   g.n_fields = q->n_fields; g.EPD = q->EPD; g.EPL = q->EPL; g.z_start = q->z_start; g.wavelength = q->wavelength;
+  g.ready = nullptr; g.ready_chunk = 0;
   return g;
 }
 template <typename R>

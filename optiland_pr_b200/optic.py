@@ -51,6 +51,9 @@ def pupil_points(distribution: str, num_rays: int, seed=None):
     raise ValueError(f"distribution {distribution!r} is not implemented")
 
 
+_FIELD_CACHE: dict = {}
+
+
 class FieldTable:
     """The per-field scalars of the ray launch (include/olrt.h, olrt_pupil): `fxy` [F, 2] launch-plane offsets
     (object at infinity) or object points (finite object), `vig` [F, 2] = (vx, vy) or None, `fz` [F] or None,
@@ -68,7 +71,14 @@ class FieldTable:
         F = self.n_fields
         parts = [self.fxy.ravel()] + ([self.vig.ravel()] if self.vig is not None else []) \
             + ([self.fz.ravel()] if self.fz is not None else [])
-        flat = torch.from_numpy(np.ascontiguousarray(np.concatenate(parts), dtype=np.float64)).to(device, non_blocking=True)
+        host = np.ascontiguousarray(np.concatenate(parts), dtype=np.float64)
+        key = (str(device), host.tobytes())
+        flat = _FIELD_CACHE.get(key)     # by content: the same fields again (every analysis pass) upload nothing
+        if flat is None:
+            flat = torch.from_numpy(host).to(device, non_blocking=True)
+            if len(_FIELD_CACHE) >= 32:
+                _FIELD_CACHE.pop(next(iter(_FIELD_CACHE)))
+            _FIELD_CACHE[key] = flat
         self.fxy_d = flat[:2 * F].view(F, 2)
         o = 2 * F
         if self.vig is not None:
@@ -285,7 +295,9 @@ class Optic:
         return rays
 
     pipeline_min_rays = 1 << 21   # host pupil grids at least this long are streamed in chunks
-    pipeline_chunks = 4
+    pipeline_chunks = 12
+    pipeline_streamed = True     # fused kernel: one launch that waits for the chunks as they arrive
+    pipeline_growth = 1.25       # chunk k + 1 is this much longer than chunk k
 
     def _trace_pipelined(self, Hx, Hy, Px_h, Py_h, wavelength, spot=False, packed=None):
         """Same result as launch_rays + SurfaceGroup.trace for a pupil grid that lives in (pinned) HOST
@@ -314,25 +326,87 @@ class Optic:
         resident = Px_h.is_cuda
         Px_d = Px_h if resident else torch.empty(npup, dtype=torch.float64, device=dev)
         Py_d = Py_h if resident else torch.empty(npup, dtype=torch.float64, device=dev)
-        out = torch.empty((8, n), dtype=dt, device=dev)
-        dir0 = torch.empty((3, n), dtype=dt, device=dev)
-        # chunk edges: a short first chunk (the only copy nothing overlaps), then equal ones
-        C_ = 1 if resident else max(1, min(self.pipeline_chunks, npup // 65536))
-        if C_ >= 4:
-            cuts = [0, npup // (2 * C_), npup // C_] + [c * npup // C_ for c in range(2, C_ + 1)]
-        else:
-            cuts = [c * npup // C_ for c in range(C_ + 1)]
-        edges = [(a_, b_) for a_, b_ in zip(cuts[:-1], cuts[1:]) if b_ > a_]
-        ft = self._field_table(Hx, Hy).to(dev)
-        fxy_all = ft.fxy_d
-        packed = sg.pack([float(wavelength)]) if packed is None else packed
-        fused = bool(sg.fast_math and packed.fastkinds() and self._EPL is not None and self._EPD is not None)
-        if fused and packed.record_surfaces:   # record == "last": the final state IS the last surface's record
-            keep, sg.record = sg.record, "none"
+        # pack first: it decides how the grid is streamed
+        if packed is None:   # packed once, without records: the record mask does not decide eligibility, and in
+            keep, sg.record = sg.record, "none"   # the fused path (record == "last") the final state IS the record
             try:
                 packed = sg.pack([float(wavelength)])
             finally:
                 sg.record = keep
+            fused = bool(sg.fast_math and packed.fastkinds() and self._EPL is not None and self._EPD is not None)
+            if not fused and keep != "none":
+                packed = sg.pack([float(wavelength)])
+        else:
+            fused = bool(sg.fast_math and packed.fastkinds() and self._EPL is not None and self._EPD is not None)
+            if fused and packed.record_surfaces:
+                keep, sg.record = sg.record, "none"
+                try:
+                    packed = sg.pack([float(wavelength)])
+                finally:
+                    sg.record = keep
+        # Streamed mode (fused kernel, host grid): ONE launch covers the whole grid while the copy engine is still
+        # delivering it -- equal chunks, each followed on the copy stream by a 4-byte copy that sets the chunk's
+        # "ready" word; the kernel's CTAs walk the pupil in copy order and wait on those words (olrt.h,
+        # olrt_pupil.ready). Otherwise: one launch per chunk behind an event; the compute of chunk k must outlast
+        # the copy of chunk k + 1 (the kernels are ~1.25x slower per pupil point than the PCIe copy), so the chunks
+        # grow geometrically from a short first one -- the only copy nothing overlaps.
+        C_ = 1 if resident else max(1, min(self.pipeline_chunks, npup // 65536))
+        streamed = bool(fused and not resident and C_ > 1 and self.pipeline_streamed
+                        and Px_h.is_pinned() and Py_h.is_pinned() and Px_h.is_contiguous() and Py_h.is_contiguous()
+                        and Py_h.dtype == torch.float64)
+        ready = None
+        ready_chunk = 0
+        if streamed:
+            ready_chunk = (-(-npup // C_) + 255) // 256 * 256
+            cuts = list(range(0, npup, ready_chunk)) + [npup]
+            ready = torch.zeros(len(cuts) - 1, dtype=torch.int32, device=dev)
+            if getattr(self, "_ones_pinned", None) is None or self._ones_pinned.numel() < len(cuts) - 1:
+                self._ones_pinned = torch.ones(max(64, len(cuts) - 1), dtype=torch.int32).pin_memory()
+        elif C_ >= 4:
+            g_ = self.pipeline_growth
+            w_ = np.cumsum([g_ ** k for k in range(C_)])
+            cuts = [0] + [int(npup * v / w_[-1]) // 256 * 256 for v in w_[:-1]] + [npup]
+        else:
+            cuts = [c * npup // C_ for c in range(C_ + 1)]
+        edges = [(a_, b_) for a_, b_ in zip(cuts[:-1], cuts[1:]) if b_ > a_]
+        events = []
+        tl = [] if getattr(self, "debug_timeline", False) else None   # [(label, timing event)]
+
+        def mark(label, stream):
+            if tl is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record(stream)
+                tl.append((label, e))
+        cs.wait_stream(main)        # (also orders the zeroing of `ready` before the copies that set it)
+        mark("start", main)
+
+        def enqueue_copies(upto):   # copies [len(events), upto) on the side stream, one event (and word) each
+            with torch.cuda.stream(cs):
+                for c_ in range(len(events), min(upto, len(edges))):
+                    lo, hi = edges[c_]
+                    if not resident:
+                        Px_d[lo:hi].copy_(Px_h[lo:hi], non_blocking=True)
+                        Py_d[lo:hi].copy_(Py_h[lo:hi], non_blocking=True)
+                    if streamed:
+                        ready[c_:c_ + 1].copy_(self._ones_pinned[c_:c_ + 1], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(cs)
+                    events.append(ev)
+                    mark(f"copy{c_}", cs)
+        # streamed: ALL copies are queued before the kernel that waits for them is launched (it must never wait for
+        # work the host has not submitted); otherwise the later ones are queued once the first kernel is on its way
+        if streamed:
+            L.check(L.load().olrt_upload_pupil(Px_d.data_ptr(), Py_d.data_ptr(), Px_h.data_ptr(), Py_h.data_ptr(), npup,
+                                               ready_chunk, ready.data_ptr(), self._ones_pinned.data_ptr(),
+                                               cs.cuda_stream), "olrt_upload_pupil")
+            if tl is not None:
+                mark("copies", cs)
+        else:
+            enqueue_copies(2)
+        out = torch.empty((8, n), dtype=dt, device=dev)
+        dir0 = torch.empty((3, n), dtype=dt, device=dev)
+        ft = self._field_table(Hx, Hy).to(dev)
+        fxy_all = ft.fxy_d
         gen_kw = dict(EPD=self._EPD, EPL=self._EPL, wavelength=float(wavelength), dtype=dt, **ft.kwargs())
         status_t = torch.zeros(1, dtype=torch.int32, device=dev)
         sums = shift = None
@@ -343,27 +417,9 @@ class Optic:
                 chief = torch.empty((8, nf), dtype=dt, device=dev)
                 fused_trace_pupil(packed, zero, zero, fxy_all, out=chief, status_t=status_t, **gen_kw)
                 shift = chief[:2].t().to(torch.float64).nan_to_num(0.0, 0.0, 0.0).contiguous()
-        cs.wait_stream(main)
-        events = []
-        tl = [] if getattr(self, "debug_timeline", False) else None   # [(label, timing event)]
-
-        def mark(label, stream):
-            if tl is not None:
-                e = torch.cuda.Event(enable_timing=True)
-                e.record(stream)
-                tl.append((label, e))
-        mark("start", main)
-        with torch.cuda.stream(cs):
-            for c_, (lo, hi) in enumerate(edges):
-                if not resident:
-                    Px_d[lo:hi].copy_(Px_h[lo:hi], non_blocking=True)
-                    Py_d[lo:hi].copy_(Py_h[lo:hi], non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record(cs)
-                events.append(ev)
-                mark(f"copy{c_}", cs)
+        launches = [(0, npup)] if streamed else edges
         rays_in = None if fused else torch.empty((8, n), dtype=dt, device=dev)
-        n_slices = len(edges) * (1 if fused else nf)
+        n_slices = len(launches) * (1 if fused else nf)
         has_nr = bool(packed.nr_rows())
         for attempt in range(8):
             k_used = packed.nr_iters()
@@ -372,12 +428,16 @@ class Optic:
             if attempt and sums is not None:
                 sums.zero_()
             q_ = 0
-            for (lo, hi), ev in zip(edges, events):
-                main.wait_event(ev)
+            for c_, (lo, hi) in enumerate(launches):
+                if c_ == 1 and not streamed:
+                    enqueue_copies(len(edges))
+                if not streamed:
+                    main.wait_event(events[c_])
                 if fused:
                     fused_trace_pupil(packed, Px_d, Py_d, fxy_all, p_lo=lo, p_len=hi - lo, out=out, dir0=dir0,
                                       spot=sums, spot_shift=shift, status_t=status_t,
-                                      resid_out=None if resid is None else resid[q_], **gen_kw)
+                                      resid_out=None if resid is None else resid[q_], ready=ready,
+                                      ready_chunk=ready_chunk, **gen_kw)
                     mark(f"chunk{q_}", main)
                     q_ += 1
                     continue
@@ -390,10 +450,19 @@ class Optic:
                                 status_t=status_t, resid_out=None if resid is None else resid[q_])
                     mark(f"slice{q_}", main)
                     q_ += 1
+            # ONE read-back for the whole batch (pinned staging, one wait): the residual maxima (the batch-global
+            # exit rule is the max over the slices), the status word and, in the fused path, the spot sums
+            if spot and fused:
+                sums[:, 8:10] = shift
+            pins = self._pinned_tail(resid, status_t, sums if (spot and fused) else None)
+            done = torch.cuda.Event()
+            done.record(main)
+            done.synchronize()
+            st = int(pins[1][0])
+            sums_host = None if pins[2] is None else pins[2].clone()
             if not has_nr:
                 break
-            # ONE read-back for the whole batch: the batch-global exit rule is the max over the slices
-            rows = resid.cpu().numpy().view(np.float64)
+            rows = pins[0].numpy().view(np.float64)
             per_slice = [slice_true_iters(packed, rows[q], k_used) for q in range(n_slices)]
             if any(v is None for ps in per_slice for v in ps):      # some slice needs more updates
                 packed.set_nr_iters([min(lay.max_iter, max(k * 2, k + 2)) if lay.geom >= 2 else 0
@@ -403,7 +472,10 @@ class Optic:
             if batch == k_used:
                 break
             packed.set_nr_iters(batch)
-        st = int(status_t.item())
+        if streamed:
+            main.wait_stream(cs)    # the copies are done (the kernel consumed them); this tells the allocator so
+        if st & L.ST_TIMEOUT:
+            raise L.OlrtLibraryError("streamed pupil grid: a host->device chunk never arrived (OLRT_ST_TIMEOUT)")
         if tl is not None:
             torch.cuda.synchronize(dev)
             self.last_timeline = [(lb, tl[0][1].elapsed_time(e)) for lb, e in tl]
@@ -420,12 +492,30 @@ class Optic:
             sg.surfaces[-1]._set_record(out)
         if spot:
             if fused:
-                sums[:, 8:10] = shift
+                rays.spot_sums_host = sums_host   # the same sums, already on the host (read back with the status)
             else:
                 from .spot import spot_sums
                 spot_sums(rays.x, rays.y, rays.i, nf, npup, out=sums)
             rays.spot_sums = sums
         return rays
+
+    def _pinned_tail(self, resid, status_t, sums):
+        """Queue the device->host copies of the small per-call results into cached pinned buffers (no sync here).
+        Returns (resid_host or None, status_host, sums_host or None)."""
+        cache = self.__dict__.setdefault("_pin_cache", {})
+        outs = []
+        for name, t in (("resid", resid), ("status", status_t), ("sums", sums)):
+            if t is None:
+                outs.append(None)
+                continue
+            key = (name, t.dtype, tuple(t.shape))
+            h = cache.get(key)
+            if h is None:
+                h = torch.empty(t.shape, dtype=t.dtype).pin_memory()
+                cache[key] = h
+            h.copy_(t, non_blocking=True)
+            outs.append(h)
+        return outs
 
     def _field_offsets(self, Hx, Hy):
         """(fxy [F, 2] NumPy, z_start): -tan(radians(max_field H)) (offset + EPL) per field and the launch plane,

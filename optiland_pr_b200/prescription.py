@@ -48,6 +48,8 @@ class NotEligible(Exception):
 
 def _f(v) -> float:
     """Scalar value of a python number / numpy 0-d or 1-element array / torch tensor."""
+    if type(v) is float or type(v) is int:     # the common case: no NumPy round trip
+        return float(v)
     if hasattr(v, "detach"):
         return float(v.detach().cpu().reshape(-1)[0].item())
     a = np.asarray(v, dtype=np.float64).reshape(-1)
@@ -140,6 +142,28 @@ class PackedSystem:
                 return False
             aoff = int(op[L.OP_APER_OFF])
             if aoff >= 0 and not (op[L.OP_APER_LEN] == 1 and self.ops[aoff] == L.AP_RADIAL):
+                return False
+        return True
+
+    def differentiable(self) -> bool:
+        """True when the backward kernels cover every surface (csrc/trace_bwd.cuh: bwd_supported): plane / finite
+        conic / even asphere with <= 8 coefficients on one untilted frame, any aperture program, no coating or
+        thin-lens flag, every surface recorded. The kernels re-check it (OLRT_ST_BAD_HINT)."""
+        if self.record_surfaces != [lay.index for lay in self.layouts]:
+            return False
+        for k in range(self.n_surfaces):
+            row = k * L.OPS_STRIDE
+            op = self.ops[row:row + L.OPS_STRIDE]
+            geom, flags = int(op[L.OP_GEOM]), int(op[L.OP_FLAGS])
+            if op[L.OP_NFRAMES] != 1 or op[L.OP_FRAMEFLAGS] != 0:
+                return False
+            if flags & (L.F_COATING | L.F_THIN_LENS | L.F_RENORM):
+                return False
+            if geom == L.GEOM_PLANE:
+                continue
+            if geom not in (L.GEOM_STANDARD, L.GEOM_EVEN_ASPHERE) or flags & L.F_RADIUS_INF:
+                return False
+            if geom == L.GEOM_EVEN_ASPHERE and int(op[L.OP_NCOEF]) > 8:
                 return False
         return True
 

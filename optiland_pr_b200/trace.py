@@ -52,15 +52,21 @@ def _fixup_workspace(n: int, device):
     return t
 
 
+_TABLE_CACHE: dict = {}      # (dtype, device, ops bytes, presc bytes) -> (ops, presc) device tensors, a few entries
+
+
 def _device_tables(packed: PackedSystem, dtype, device):
-    """ops / presc on the device, cached on the PackedSystem until it is mutated."""
-    key = (str(dtype), str(device), packed.ops.tobytes(), packed.presc.ctypes.data, packed.presc.shape)
-    cache = getattr(packed, "_dev_cache", None)
-    if cache is not None and cache[0] == key and cache[3] == packed.presc.tobytes():
-        return cache[1], cache[2]
+    """ops / presc on the device. Cached by CONTENT (a few KB of bytes): a lens that is packed again with the same
+    prescription -- every Optic.trace call packs -- does not upload its tables again."""
+    key = (str(dtype), str(device), packed.ops.tobytes(), packed.presc.tobytes(), packed.presc.shape)
+    hit = _TABLE_CACHE.get(key)
+    if hit is not None:
+        return hit
     ops = torch.from_numpy(packed.ops.copy()).to(device)
     presc = torch.from_numpy(np.ascontiguousarray(packed.presc)).to(device=device, dtype=dtype)
-    packed._dev_cache = (key, ops, presc, packed.presc.tobytes())
+    if len(_TABLE_CACHE) >= 16:
+        _TABLE_CACHE.pop(next(iter(_TABLE_CACHE)))
+    _TABLE_CACHE[key] = (ops, presc)
     return ops, presc
 
 
@@ -218,7 +224,8 @@ def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, 
                       resid_out: torch.Tensor | None = None, status_t: torch.Tensor | None = None,
                       presc: torch.Tensor | None = None, group_k: torch.Tensor | None = None,
                       group_resid: torch.Tensor | None = None, field_vig: torch.Tensor | None = None,
-                      field_z: torch.Tensor | None = None) -> None:
+                      field_z: torch.Tensor | None = None, ready: torch.Tensor | None = None,
+                      ready_chunk: int = 0) -> None:
     """Enqueue `olrt_trace_pupil_*` (include/olrt.h): launch the rays of every field for pupil points
     [p_lo, p_lo + p_len) in the kernel, trace them, optionally accumulate the spot sums. Nothing is read back:
     the caller owns `status_t`, `resid_out` (see fused_trace) and checks them after the last chunk.
@@ -230,6 +237,9 @@ def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, 
     receives each group's residual maxima (`group_true_iters` applies the reference's exit rule to them).
     field_vig: optional [F, 2] float64 device tensor of (vx, vy) = 1 - vignetting factors; field_z: optional [F]
     float64 device tensor -- finite object, `field_xy` / `field_z` are then each field's object point (olrt.h).
+    ready / ready_chunk: streamed pupil grid (include/olrt.h, olrt_pupil.ready): int32 device words, one per
+    `ready_chunk` pupil points, that a copy engine sets as the host->device copy of Px / Py lands; the one launch
+    covers the whole grid and waits, chunk by chunk, for the data.
     Raises NotImplementedError where the C ABI answers
     OLRT_E_UNSUPPORTED (the caller then uses launch + fused_trace + spot_sums)."""
     lib = L.load()
@@ -245,7 +255,7 @@ def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, 
         presc_d = presc.to(device=device, dtype=dtype).contiguous()
         n_presc = int(presc_d.shape[0])
     pu = L.OlrtPupil(Px.data_ptr(), Py.data_ptr(), field_xy.data_ptr(), _ptr(field_vig), _ptr(field_z), npup, int(p_lo), int(p_len), nf, 0,
-                     float(EPD), float(EPL), float(z_start), float(wavelength))
+                     float(EPD), float(EPL), float(z_start), float(wavelength), _ptr(ready), int(ready_chunk))
     sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=nf * p_len)
     sys_.presc_stride = int(presc_d.shape[1])
     n_total = n_presc * nf * npup
