@@ -71,7 +71,7 @@ class FusedTraceFn(torch.autograd.Function):
         ins = [x, y, z, Lc, M, N, inten, w]
         res = fused_trace(packed, [t.detach() if t is not None else None for t in ins],
                           opd_in=None if opd_in is None else opd_in.detach(),
-                          presc=presc.detach().reshape(1, -1), want_dir0=True, fast=fast)
+                          presc=presc.detach().reshape(1, -1), want_dir0=True, fast=fast, alias_out=True)
         ctx.set_materialize_grads(False)
         ctx.packed = packed
         ctx.generic_adjoint = bool(generic_adjoint)

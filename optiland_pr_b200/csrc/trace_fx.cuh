@@ -527,6 +527,8 @@ trace_fx_kernel(const FwdParams<R> P) {
     }
 
     R L0 = r.L, M0 = r.M, N0 = r.N, att = R(0);
+    R i_rec = r.i;          // intensity as recorded: r.i exp(att), re-evaluated only when att or r.i changed
+    R att_rec = R(0), i_src = r.i;
     for (int s = 0; s < S; ++s) {
       // direction entering the surface: after the loop, the pre-interaction direction at the last surface
       // (real_rays.py:82-86; the frame of a fast kind has no rotation, so local == global direction)
@@ -548,7 +550,10 @@ trace_fx_kernel(const FwdParams<R> P) {
         R* rec = P.record + (long long)slot * 8 * NT + idx;  // streaming stores: never re-read by this launch
         __stcs(rec, r.x); __stcs(rec + NT, r.y); __stcs(rec + 2 * NT, r.z);
         __stcs(rec + 3 * NT, r.L); __stcs(rec + 4 * NT, r.M); __stcs(rec + 5 * NT, r.N);
-        __stcs(rec + 6 * NT, fk_intensity(r.i, att)); __stcs(rec + 7 * NT, r.opd);
+        if (att != att_rec || r.i != i_src || r.i != r.i) {  // (NaN intensities never compare equal)
+          i_rec = fk_intensity(r.i, att); att_rec = att; i_src = r.i;
+        }
+        __stcs(rec + 6 * NT, i_rec); __stcs(rec + 7 * NT, r.opd);
       }
     }
     r.i = fk_intensity(r.i, att);

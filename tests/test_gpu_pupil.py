@@ -121,3 +121,31 @@ def test_unsupported_lens_is_refused_not_approximated():
     out = torch.empty((8, 4), dtype=torch.float64, device="cuda")
     with pytest.raises(NotImplementedError):
         fused_trace_pupil(packed, z, z, fxy, out=out, EPD=1.0, EPL=0.0, z_start=-1.0, wavelength=0.55)
+
+
+@pytest.mark.parametrize("npup,chunks", [(300_001, 5), (131_072, 12), (70_000, 3)])
+def test_streamed_host_grid_equals_chunked_and_resident(npup, chunks):
+    """Streamed mode (olrt_pupil.ready: ONE launch waits for the chunks the copy engine delivers) against the
+    per-chunk launches and the device-resident grid: same bits, ragged last chunk and tile included."""
+    be.set_precision("float64")
+    px, py = raygen_np.random_pupil(npup, seed=21)
+    Px_h, Py_h = torch.from_numpy(px).pin_memory(), torch.from_numpy(py).pin_memory()
+    Hx, Hy = [f[0] for f in FIELDS], [f[1] for f in FIELDS]
+    got = []
+    for mode in ("streamed", "chunked", "resident"):
+        lens = samples.EvenAsphereDoubleGauss()
+        lens.surface_group.record = "none"
+        lens.pipeline_min_rays = 1 << 12
+        lens.pipeline_chunks = chunks
+        lens.pipeline_streamed = (mode == "streamed")
+        dist = (Px_h.cuda(), Py_h.cuda()) if mode == "resident" else (Px_h, Py_h)
+        rays = lens.trace(Hx, Hy, 0.5876, distribution=dist, spot=True)
+        got.append(rays)
+        if mode != "resident":
+            assert torch.equal(rays.spot_sums.cpu(), rays.spot_sums_host)
+    for name in ("x", "y", "z", "L", "M", "N", "i", "opd", "L0", "M0", "N0"):
+        assert torch.equal(getattr(got[0], name), getattr(got[1], name)), name
+        assert torch.equal(getattr(got[0], name), getattr(got[2], name)), name
+    sa, sb = spot.spot_stats(got[0].spot_sums), spot.spot_stats(got[2].spot_sums)
+    for key in ("count", "cx", "cy", "rms", "intensity"):
+        assert torch.allclose(sa[key], sb[key], rtol=1e-10, atol=1e-10), key
