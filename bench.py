@@ -543,18 +543,21 @@ def bench_monte_carlo(torch, lens, S_eff, trials=4096, rays=262_144):
     Py = torch.from_numpy(np.sqrt(r_) * np.sin(th)).cuda()
     mc = MonteCarloSpot(lens, perts)
     mc.run(64, [0.0], [1.0], WAVELENGTH, Px, Py)           # warm-up (workspace allocation)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    rms = mc.run(trials, [0.0], [1.0], WAVELENGTH, Px, Py)
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
+    dts = []
+    for _ in range(2):           # wall clock of a 0.2 s host + device job: the better of two runs
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        rms = mc.run(trials, [0.0], [1.0], WAVELENGTH, Px, Py)
+        torch.cuda.synchronize()
+        dts.append(time.perf_counter() - t0)
+    dt = min(dts)
     t1 = time.perf_counter()
     MonteCarloSpot(lens, perts).draw(trials)
     t_draw = time.perf_counter() - t1
     rms = rms.cpu().numpy()
     return {"mc_tolerancing_c5": {
         "trials": trials, "rays_per_trial": rays, "perturbations": len(perts), "path": mc.last_path,
-        "seconds": dt, "seconds_host_draws": t_draw, "ray_surfaces_per_s": trials * rays * S_eff / dt,
+        "seconds": dt, "seconds_runs": dts, "seconds_host_draws": t_draw, "ray_surfaces_per_s": trials * rays * S_eff / dt,
         "rms_spot_mm_mean_std": [float(rms.mean()), float(rms.std())],
         "note": "wall clock of MonteCarloSpot.run: reference-order scalar draws on the host, nominal-lens Newton "
                 "counts, chief rays, one fused launch per round, per-trial Newton-count check, merits read back"}}

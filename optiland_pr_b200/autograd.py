@@ -180,8 +180,10 @@ def smoke_backward() -> str:
 
 
 def bench_backward(lens, packed, ins64, timed, args, fp64_peak) -> dict:
-    """fwd (all surfaces recorded = checkpoints) + bwd on the bench batch, one field at a time is not needed:
-    the record buffer for 50M rays x 12 surfaces x 8 doubles is 38.7 GB and fits the 180 GB HBM."""
+    """fwd (all surfaces recorded = checkpoints) + bwd on the bench batch: the record buffer for 50M rays x 12 surfaces
+    x 8 doubles is 38.7 GB and fits the 180 GB HBM. Two legs: gradients w.r.t. the whole prescription AND the six
+    ray components (what a caller differentiating the launch needs), and w.r.t. the prescription alone (BASELINE C4:
+    curvature / thickness / conic / asphere variables; no per-ray gradient arrays are written)."""
     from . import flops
     from .prescription import pack_surface_group
 
@@ -191,21 +193,27 @@ def bench_backward(lens, packed, ins64, timed, args, fp64_peak) -> dict:
     pk.set_nr_iters(packed.nr_iters())
     dev = ins64[0].device
     presc = torch.tensor(pk.presc[0], dtype=torch.float64, device=dev, requires_grad=True)
-    rays = [t.detach().requires_grad_(q < 6) if t is not None else None for q, t in enumerate(ins64)]
     gout_w = torch.zeros((8, n), dtype=torch.float64, device=dev)
     gout_w[0] = 1.0
     gout_w[1] = 0.5
-
-    def step():
-        presc.grad = None
-        out, record, _ = trace_differentiable(pk, presc, rays, fast=True)
-        out.backward(gout_w)
-
-    ms = timed(step, max(2, args.steps // 2), 3)
     fl = 3.0 * flops.flops_per_ray(pk)
-    return {"fp64_fwd_bwd": {"ray_surfaces_per_s": n * S / (ms * 1e-3), "ms": ms,
-                             "frac_fp64_fma_peak": fl * n / (ms * 1e-3) / 1e12 / fp64_peak,
-                             "flops_per_ray_fwd_bwd": fl,
-                             "checkpoint_bytes_per_ray": 64 * S,
-                             "note": "forward records every surface (64 B x S per ray, the checkpoints), "
-                                     "backward reads 56 B per surface per ray"}}
+    out = {}
+    for name, ray_grads in (("fp64_fwd_bwd", True), ("fp64_fwd_bwd_prescription_only", False)):
+        rays = [t.detach().requires_grad_(ray_grads and q < 6) if t is not None else None
+                for q, t in enumerate(ins64)]
+
+        def step():
+            presc.grad = None
+            o, record, _ = trace_differentiable(pk, presc, rays, fast=True)
+            o.backward(gout_w)
+
+        ms = timed(step, max(2, args.steps // 2), 3)
+        out[name] = {"ray_surfaces_per_s": n * S / (ms * 1e-3), "ms": ms,
+                     "frac_fp64_fma_peak": fl * n / (ms * 1e-3) / 1e12 / fp64_peak,
+                     "flops_per_ray_fwd_bwd": fl, "checkpoint_bytes_per_ray": 64 * S,
+                     "gradients": "prescription (frames, radii, conics, asphere coefficients)"
+                                  + (" + x y z L M N of every ray" if ray_grads else ""),
+                     "kernels": "trace_fx_kernel<double> recording every surface (64 B x S per ray, the "
+                                "checkpoints; the final state aliases the last record) + trace_bx_kernel<double> "
+                                "(reduced-algebra adjoint, reads 56 B per surface per ray)"}
+    return out

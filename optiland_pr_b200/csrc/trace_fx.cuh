@@ -430,7 +430,6 @@ trace_fx_kernel(const FwdParams<R> P) {
   // CTA b keeps ONE field, b % n_fields, and walks that field's pupil tiles b / n_fields, + gridDim / n_fields, ...
   // so every CTA consumes the pupil in copy order; before a tile it waits for the word of the chunk the tile ends in.
   const bool streamed = pupil && (P.gen.ready != nullptr);
-  const long long s_off = streamed ? (long long)(blockIdx.x % P.gen.n_fields) * tpf : 0;
   int ready_c = -1;
   if (streamed) {
     tile_lo = blockIdx.x / P.gen.n_fields;
@@ -447,7 +446,7 @@ trace_fx_kernel(const FwdParams<R> P) {
   double sp_cnt = 0, sp_x = 0, sp_y = 0, sp_xx = 0, sp_yy = 0, sp_i = 0, sp_max = 0, sp_sx = 0, sp_sy = 0;
   bool sp_nan = false;
   for (long long it = tile_lo; it < tile_hi; it += tile_step) {
-    const long long tile = it + s_off;
+    const long long tile = streamed ? it + (long long)(blockIdx.x % P.gen.n_fields) * tpf : it;
     const long long base = tile * blockDim.x;
     if (streamed) {
       long long last = (it + 1) * blockDim.x - 1;
@@ -527,8 +526,8 @@ trace_fx_kernel(const FwdParams<R> P) {
     }
 
     R L0 = r.L, M0 = r.M, N0 = r.N, att = R(0);
-    R i_rec = r.i;          // intensity as recorded: r.i exp(att), re-evaluated only when att or r.i changed
-    R att_rec = R(0), i_src = r.i;
+    R i_rec = r.i;          // intensity as recorded, r.i exp(att): exp() only after an absorbing medium
+    bool i_stale = false;
     for (int s = 0; s < S; ++s) {
       // direction entering the surface: after the loop, the pre-interaction direction at the last surface
       // (real_rays.py:82-86; the frame of a fast kind has no rotation, so local == global direction)
@@ -545,14 +544,14 @@ trace_fx_kernel(const FwdParams<R> P) {
                      want_resid ? (s_resid + info.roff) : nullptr, att);
           break;
       }
+      if (md.nalpha != R(0)) i_stale = true;
       const int slot = info.record;
       if (slot >= 0 && valid && P.record != nullptr) {  // Surface._record, standard_surface.py:266-286
         R* rec = P.record + (long long)slot * 8 * NT + idx;  // streaming stores: never re-read by this launch
         __stcs(rec, r.x); __stcs(rec + NT, r.y); __stcs(rec + 2 * NT, r.z);
         __stcs(rec + 3 * NT, r.L); __stcs(rec + 4 * NT, r.M); __stcs(rec + 5 * NT, r.N);
-        if (att != att_rec || r.i != i_src || r.i != r.i) {  // (NaN intensities never compare equal)
-          i_rec = fk_intensity(r.i, att); att_rec = att; i_src = r.i;
-        }
+        if (i_stale) { i_rec = fk_intensity(r.i, att); i_stale = false; }
+        else if (!(r.i != R(0))) i_rec = r.i;  // clipped at this surface (att was reset with it)
         __stcs(rec + 6 * NT, i_rec); __stcs(rec + 7 * NT, r.opd);
       }
     }

@@ -11,5 +11,5 @@ python scratch/prof_fx.py > gpurun_out/prof_fx.log 2>&1 && \
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:trace_fx_kernel -s 3 -c 1 -f -o gpurun_out/prof_fx \
   python scratch/prof_fx.py > gpurun_out/ncu_fx.log 2>&1; echo "ncu fx rc=$?"; cat gpurun_out/prof_fx.log
 python scratch/prof_bwd.py > gpurun_out/prof_bwd.log 2>&1 && \
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:trace_bwd_kernel -s 1 -c 1 -f -o gpurun_out/prof_bwd \
-  python scratch/prof_bwd.py > gpurun_out/ncu_bwd.log 2>&1; echo "ncu bwd rc=$?"; cat gpurun_out/prof_bwd.log
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:trace_bx_kernel -s 1 -c 1 -f -o gpurun_out/prof_bx \
+  python scratch/prof_bwd.py > gpurun_out/ncu_bwd.log 2>&1; echo "ncu bx rc=$?"; cat gpurun_out/prof_bwd.log
