@@ -142,6 +142,17 @@ __device__ __forceinline__ void fx_build_surface(const int32_t* s_ops, const R* 
     sf.rmax2 = R(0); sf.rmin2 = R(0);
   }
   s_info[s].kind = kind;
+  // dense variant id for the kernel's switch: 0-2 = plane / conic / even asphere with run-time flags; 3-7 = the same
+  // with the flags of an ordinary lens surface (centred, refracting, no aperture) fixed at compile time
+  {
+    const int k3 = kind & 15;
+    int v = (k3 == KIND_PLANE) ? 0 : ((k3 == KIND_CONIC) ? 1 : 2);
+    if ((kind & (FX_CENTERED | FX_REFLECT | FX_APER)) == FX_CENTERED) {
+      const bool sph = (kind & FX_SPHERE) != 0;
+      v = (k3 == KIND_PLANE) ? 3 : ((k3 == KIND_CONIC) ? (sph ? 4 : 5) : (sph ? 6 : 7));
+    }
+    s_info[s].pad1 = v;
+  }
   s_info[s].K = op[OLRT_OP_NR_ITERS];
   // coefficients, zero-padded to a multiple of 4: slot = (reals before this surface) + 4 s bounds the padding
   const int m = ((kind & 15) == KIND_EVEN) ? op[OLRT_OP_NCOEF] : 0;
@@ -442,6 +453,7 @@ trace_fx_kernel(const FwdParams<R> P) {
   }
   // fused spot epilogue: per-thread sums for the current group, flushed when the group changes
   const bool want_spot = (P.spot != nullptr);
+  const bool rec_on = (P.record != nullptr);
   int sp_g = -1;
   double sp_cnt = 0, sp_x = 0, sp_y = 0, sp_xx = 0, sp_yy = 0, sp_i = 0, sp_max = 0, sp_sx = 0, sp_sy = 0;
   bool sp_nan = false;
@@ -536,17 +548,29 @@ trace_fx_kernel(const FwdParams<R> P) {
       const FxMedium<R>& md = s_med[s * W + widx];
       const FxInfo& info = s_info[s];
       const int kind = info.kind;
-      switch (kind & 15) {  // warp-uniform
-        case KIND_PLANE: fx_plane<R>(r, sf, md, kind, att); break;
-        case KIND_CONIC: fx_conic<R>(r, sf, md, kind, att); break;
+      switch (info.pad1) {  // warp-uniform, dense (fx_build_surface)
+        case 0: fx_plane<R>(r, sf, md, kind, att); break;
+        case 1: fx_conic<R>(r, sf, md, kind, att); break;
+        case 3: fx_plane<R>(r, sf, md, KIND_PLANE | FX_CENTERED, att); break;
+        case 4: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED | FX_SPHERE, att); break;
+        case 5: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED, att); break;
+        case 6:
+          fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED | FX_SPHERE, info, gmode ? s_gk[s] : info.K,
+                     s_coef + info.coef_off, valid, want_resid ? (s_resid + info.roff) : nullptr, att);
+          break;
+        case 7:
+          fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED, info, gmode ? s_gk[s] : info.K, s_coef + info.coef_off,
+                     valid, want_resid ? (s_resid + info.roff) : nullptr, att);
+          break;
         default:
           fx_even<R>(r, sf, md, kind, info, gmode ? s_gk[s] : info.K, s_coef + info.coef_off, valid,
                      want_resid ? (s_resid + info.roff) : nullptr, att);
           break;
       }
+      if (!rec_on) continue;
       if (md.nalpha != R(0)) i_stale = true;
       const int slot = info.record;
-      if (slot >= 0 && valid && P.record != nullptr) {  // Surface._record, standard_surface.py:266-286
+      if (slot >= 0 && valid) {  // Surface._record, standard_surface.py:266-286
         R* rec = P.record + (long long)slot * 8 * NT + idx;  // streaming stores: never re-read by this launch
         __stcs(rec, r.x); __stcs(rec + NT, r.y); __stcs(rec + 2 * NT, r.z);
         __stcs(rec + 3 * NT, r.L); __stcs(rec + 4 * NT, r.M); __stcs(rec + 5 * NT, r.N);
