@@ -32,6 +32,7 @@ namespace OLRT_NS {
 #endif
 #define OLRT_BX_MAXK 3  // Newton updates whose iterates are kept in registers
 #define OLRT_BX_MAX_MEDIA 256  // surfaces x wavelengths of the static media table
+#define OLRT_BX_COLS 33        // accumulator columns per slot: 32 lanes + one for the idle lanes of a tail tile
 
 // d(opd)/dt of opd += |t n1| (standard_surface.py:218)
 template <typename R>
@@ -306,9 +307,31 @@ __device__ __forceinline__ void bx_even(const FxSurf<R>& sf, const FxMedium<R>& 
 // prescription, padded coefficient table, ops; the per-surface FxSurf / FxInfo / FxMedium tables are static
 template <typename R>
 __host__ __device__ __forceinline__ size_t bx_smem_bytes(int presc_stride, int S, int W, int ops_len, int block) {
-  return (size_t)2 * 7 * block * sizeof(R) + (size_t)S * OLRT_BWD_SLOTS * 32 * sizeof(R) +
+  return (size_t)2 * 7 * block * sizeof(R) + (size_t)((S * OLRT_BWD_SLOTS * OLRT_BX_COLS + 3) & ~3) * sizeof(R) +
          (size_t)((presc_stride + 3) & ~3) * sizeof(R) +
          (size_t)((presc_stride + 4 * S + 3) & ~3) * sizeof(R) + (size_t)((ops_len + 3) & ~3) * sizeof(int32_t);
+}
+
+// sum the 32 lane columns of every (surface, slot) into the prescription gradient and clear all 33 (trace_bwd.cuh:
+// bwd_flush); coefficient slots beyond the surface's real count (padding of the table) are dropped
+template <typename R>
+__device__ __forceinline__ void bx_flush(R* s_acc, const int32_t* s_ops, int S, int W, R* gpresc) {
+  for (int q = threadIdx.x; q < S * OLRT_BWD_SLOTS; q += blockDim.x) {
+    const int s = q / OLRT_BWD_SLOTS, j = q - s * OLRT_BWD_SLOTS;
+    R* a = s_acc + (size_t)q * OLRT_BX_COLS;
+    R v = R(0);
+    for (int l = 0; l < 32; ++l) { v += a[(l + threadIdx.x) & 31]; }
+    for (int l = 0; l < OLRT_BX_COLS; ++l) a[l] = R(0);
+    const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
+    if (v == R(0) || (j >= 5 && j - 5 >= op[OLRT_OP_NCOEF])) continue;
+    const int doff = op[OLRT_OP_DOFF];
+    const int goff = doff + op[OLRT_OP_NFRAMES] * OLRT_FRAME_REALS;
+    int off;
+    if (j < 3) off = doff + j;
+    else if (j < 5) off = goff + (j - 3);
+    else off = goff + OLRT_GEOM_REALS + 3 * W + (j - 5);
+    atomicAdd(gpresc + off, v);
+  }
 }
 
 // 4- or 8-byte cp.async with a 32-bit shared address
@@ -316,6 +339,19 @@ template <typename R>
 __device__ __forceinline__ void bx_cp_async(unsigned dst, const R* src) {
   if (sizeof(R) == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
   else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+
+// shared load from a 32-bit shared address + element offset
+template <typename R> __device__ __forceinline__ R bx_lds(unsigned base, int elem);
+template <> __device__ __forceinline__ double bx_lds<double>(unsigned base, int elem) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(base + (unsigned)elem * 8u) : "memory");
+  return v;
+}
+template <> __device__ __forceinline__ float bx_lds<float>(unsigned base, int elem) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(base + (unsigned)elem * 4u) : "memory");
+  return v;
 }
 
 // BD: block size known at compile time (256), or 0 = blockDim.x (prescription batches with short tiles)
@@ -330,14 +366,15 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
   const int bd = BD ? BD : (int)blockDim.x;
   // entry states (checkpoints) staged one surface ahead by cp.async: s_ck[(buf * 7 + q) * bd + tid]
   R* s_ck = reinterpret_cast<R*>(smem_raw);
-  // d loss / d presc per LANE (trace_bwd.cuh): s_acc[(s * OLRT_BWD_SLOTS + j) * 32 + lane]
+  // d loss / d presc per LANE (trace_bwd.cuh): s_acc[(s * OLRT_BWD_SLOTS + j) * OLRT_BX_COLS + lane]; the lanes a
+  // tail tile leaves idle add (to) column 32, which is never summed: no `valid` branch around the atomics
   R* s_acc = s_ck + 2 * 7 * bd;
-  R* s_presc = s_acc + (size_t)S * OLRT_BWD_SLOTS * 32;
+  R* s_presc = s_acc + ((S * OLRT_BWD_SLOTS * OLRT_BX_COLS + 3) & ~3);  // keep 16 B alignment
   R* s_coef = s_presc + ((P.presc_stride + 3) & ~3);
   int32_t* s_ops = reinterpret_cast<int32_t*>(s_coef + ((P.presc_stride + 4 * S + 3) & ~3));
 
   for (int q = threadIdx.x; q < P.ops_len; q += bd) s_ops[q] = P.ops[q];
-  for (int q = threadIdx.x; q < S * OLRT_BWD_SLOTS * 32; q += bd) s_acc[q] = R(0);
+  for (int q = threadIdx.x; q < S * OLRT_BWD_SLOTS * OLRT_BX_COLS; q += bd) s_acc[q] = R(0);
   if (threadIdx.x == 0) s_bad = 0;
   __syncthreads();
   if (threadIdx.x < S) {
@@ -358,7 +395,6 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
   // from re-deriving it (cvta + 64-bit arithmetic) at every cp.async
   unsigned ck_a;
   asm volatile("{ .reg .u64 t; cvta.to.shared.u64 t, %1; cvt.u32.u64 %0, t; }" : "=r"(ck_a) : "l"(s_ck + threadIdx.x));
-  const R* ck_t = s_ck + threadIdx.x;
   int cur_p = -1;
   const long long n_tiles = (N + bd - 1) / bd;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -367,7 +403,7 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
     if (p != cur_p) {
       __syncthreads();
       if (cur_p >= 0) {
-        bwd_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
+        bx_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
         __syncthreads();
       }
       const R* src = P.presc + (long long)p * P.presc_stride;
@@ -384,6 +420,7 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
     const long long item = base + threadIdx.x;
     const bool valid = item < N;
     const long long idx = valid ? item : (N - 1);
+    const int col = valid ? lane : 32;
     int widx = 0;
     if (W > 1) {
       const R wl = P.in[7][idx];
@@ -419,29 +456,29 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
         gx += g[0]; gy += g[N]; gz += g[2 * N]; gL += g[3 * N]; gM += g[4 * N]; gN += g[5 * N];
         gi += g[6 * N]; gopd += g[7 * N];
       }
-      const R* ck = ck_t + (s & 1) * 7 * bd;
-      const R ex = ck[0], ey = ck[bd], ez = ck[2 * bd], eL = ck[3 * bd], eM = ck[4 * bd], eN = ck[5 * bd],
-              ei = ck[6 * bd];
+      const unsigned cka = ck_a + (unsigned)((s & 1) * 7 * bd * (int)sizeof(R));
+      const R ex = bx_lds<R>(cka, 0), ey = bx_lds<R>(cka, bd), ez = bx_lds<R>(cka, 2 * bd),
+              eL = bx_lds<R>(cka, 3 * bd), eM = bx_lds<R>(cka, 4 * bd), eN = bx_lds<R>(cka, 5 * bd),
+              ei = bx_lds<R>(cka, 6 * bd);
       const FxSurf<R>& sf = s_surf[s];
       const FxMedium<R>& md = s_med[s * W + widx];
       const FxInfo& info = s_info[s];
       const int kind = info.kind;
-      R* acc = s_acc + s * (OLRT_BWD_SLOTS * 32) + lane;
+      R* acc = s_acc + s * (OLRT_BWD_SLOTS * OLRT_BX_COLS) + col;
       switch (kind & 15) {  // warp-uniform
         case KIND_PLANE: {
           R gTz;
           bx_plane<R>(sf, md, kind, z0, ez, eL, eM, eN, ei, irec, ex, ey, gx, gy, gz, gL, gM, gN, gi, gopd, gTz);
-          if (valid) atomicAdd(acc + 2 * 32, gTz);
+          atomicAdd(acc + 2 * OLRT_BX_COLS, gTz);
           break;
         }
         case KIND_CONIC: {
           R gTx, gTy, gTz, gR, gk;
           bx_conic<R>(sf, md, kind, z0, ex, ey, ez, eL, eM, eN, ei, irec, Qgx, Qgy, Qgz, gx, gy, gz, gL, gM, gN, gi,
                       gopd, gTx, gTy, gTz, gR, gk);
-          if (valid) {
-            atomicAdd(acc + 0 * 32, gTx); atomicAdd(acc + 1 * 32, gTy); atomicAdd(acc + 2 * 32, gTz);
-            atomicAdd(acc + 3 * 32, gR); atomicAdd(acc + 4 * 32, gk);
-          }
+          atomicAdd(acc + 0 * OLRT_BX_COLS, gTx); atomicAdd(acc + 1 * OLRT_BX_COLS, gTy);
+          atomicAdd(acc + 2 * OLRT_BX_COLS, gTz); atomicAdd(acc + 3 * OLRT_BX_COLS, gR);
+          atomicAdd(acc + 4 * OLRT_BX_COLS, gk);
           break;
         }
         default: {
@@ -452,13 +489,16 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
           const int m4 = info.ncoef;
           bx_even<R>(sf, md, kind, info.K, m4, s_coef + info.coef_off, z0, ex, ey, ez, eL, eM, eN, ei, irec, gx, gy,
                      gz, gL, gM, gN, gi, gopd, gTx, gTy, gTz, gR, gk, gC);
-          if (valid) {
-            atomicAdd(acc + 0 * 32, gTx); atomicAdd(acc + 1 * 32, gTy); atomicAdd(acc + 2 * 32, gTz);
-            atomicAdd(acc + 3 * 32, gR); atomicAdd(acc + 4 * 32, gk);
-            const int m = info.pad0;
+          atomicAdd(acc + 0 * OLRT_BX_COLS, gTx); atomicAdd(acc + 1 * OLRT_BX_COLS, gTy);
+          atomicAdd(acc + 2 * OLRT_BX_COLS, gTz); atomicAdd(acc + 3 * OLRT_BX_COLS, gR);
+          atomicAdd(acc + 4 * OLRT_BX_COLS, gk);
+          // coefficient partials in blocks of 4 like the padded table (bx_flush drops the padding's)
 #pragma unroll
-            for (int i = 0; i < OLRT_BWD_MAXC; ++i)
-              if (i < m) atomicAdd(acc + (5 + i) * 32, gC[i]);
+          for (int blk = 0; blk < OLRT_BWD_MAXC; blk += 4) {
+            if (blk < m4) {
+#pragma unroll
+              for (int i = blk; i < blk + 4; ++i) atomicAdd(acc + (5 + i) * OLRT_BX_COLS, gC[i]);
+            }
           }
           break;
         }
@@ -477,7 +517,7 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
     }
   }
   __syncthreads();
-  if (cur_p >= 0) bwd_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
+  if (cur_p >= 0) bx_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
 }
 
 template <typename R, int BD>
