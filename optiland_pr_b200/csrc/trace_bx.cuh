@@ -334,6 +334,32 @@ __device__ __forceinline__ void bx_flush(R* s_acc, const int32_t* s_ops, int S, 
   }
 }
 
+// Add NV partials to consecutive accumulator slots of this lane's column. sm_100a has no shared-memory fp64 add: the
+// compiler's atomicAdd is a load / add / compare-and-swap loop per value, whose three latencies then run one after
+// the other for every partial. Here the NV loads are issued together, then the adds, then the NV compare-and-swaps;
+// a value that lost its race (another warp of the CTA updated the same lane's slot in between: rare) falls back to
+// the plain loop. fp32 has a native shared-memory add.
+template <int NV>
+__device__ __forceinline__ void bx_add_n(double* acc, const double* v) {
+  unsigned long long o[NV], r[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+    o[i] = *reinterpret_cast<volatile unsigned long long*>(acc + i * OLRT_BX_COLS);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const unsigned long long n = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)o[i]) + v[i]);
+    r[i] = atomicCAS(reinterpret_cast<unsigned long long*>(acc + i * OLRT_BX_COLS), o[i], n);
+  }
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+    if (r[i] != o[i]) atomicAdd(acc + i * OLRT_BX_COLS, v[i]);
+}
+template <int NV>
+__device__ __forceinline__ void bx_add_n(float* acc, const float* v) {
+#pragma unroll
+  for (int i = 0; i < NV; ++i) atomicAdd(acc + i * OLRT_BX_COLS, v[i]);
+}
+
 // 4- or 8-byte cp.async with a 32-bit shared address
 template <typename R>
 __device__ __forceinline__ void bx_cp_async(unsigned dst, const R* src) {
@@ -476,9 +502,8 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
           R gTx, gTy, gTz, gR, gk;
           bx_conic<R>(sf, md, kind, z0, ex, ey, ez, eL, eM, eN, ei, irec, Qgx, Qgy, Qgz, gx, gy, gz, gL, gM, gN, gi,
                       gopd, gTx, gTy, gTz, gR, gk);
-          atomicAdd(acc + 0 * OLRT_BX_COLS, gTx); atomicAdd(acc + 1 * OLRT_BX_COLS, gTy);
-          atomicAdd(acc + 2 * OLRT_BX_COLS, gTz); atomicAdd(acc + 3 * OLRT_BX_COLS, gR);
-          atomicAdd(acc + 4 * OLRT_BX_COLS, gk);
+          const R pv[5] = {gTx, gTy, gTz, gR, gk};
+          bx_add_n<5>(acc, pv);
           break;
         }
         default: {
@@ -489,17 +514,11 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
           const int m4 = info.ncoef;
           bx_even<R>(sf, md, kind, info.K, m4, s_coef + info.coef_off, z0, ex, ey, ez, eL, eM, eN, ei, irec, gx, gy,
                      gz, gL, gM, gN, gi, gopd, gTx, gTy, gTz, gR, gk, gC);
-          atomicAdd(acc + 0 * OLRT_BX_COLS, gTx); atomicAdd(acc + 1 * OLRT_BX_COLS, gTy);
-          atomicAdd(acc + 2 * OLRT_BX_COLS, gTz); atomicAdd(acc + 3 * OLRT_BX_COLS, gR);
-          atomicAdd(acc + 4 * OLRT_BX_COLS, gk);
+          const R pv[5] = {gTx, gTy, gTz, gR, gk};
+          bx_add_n<5>(acc, pv);
           // coefficient partials in blocks of 4 like the padded table (bx_flush drops the padding's)
-#pragma unroll
-          for (int blk = 0; blk < OLRT_BWD_MAXC; blk += 4) {
-            if (blk < m4) {
-#pragma unroll
-              for (int i = blk; i < blk + 4; ++i) atomicAdd(acc + (5 + i) * OLRT_BX_COLS, gC[i]);
-            }
-          }
+          if (m4 > 0) bx_add_n<4>(acc + 5 * OLRT_BX_COLS, gC);
+          if (m4 > 4) bx_add_n<4>(acc + 9 * OLRT_BX_COLS, gC + 4);
           break;
         }
       }
