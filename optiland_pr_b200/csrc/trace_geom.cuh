@@ -84,6 +84,35 @@ __device__ __forceinline__ void polynomial_eval(const SurfParams<R>& sp, R x, R 
   R denom;
   conic_sag_denom<R, MM>(r2, sp.cc, sag, denom);
   if (WANT_SLOPES) { const Recip<R, MM> rd(denom); zx = rd.div(x); zy = rd.div(y); }
+#ifdef OLRT_FX
+  // tolerance build (-fmad=true TU): the same polynomial and partials by bivariate Horner -- per row i the sum
+  // A_i(y) = sum_j C_ij y^j and its derivative, then P = sum_i x^i A_i(y), dP/dx, dP/dy by Horner in x: 2 FMAs per
+  // coefficient + 3 per row instead of ~11 multiplications per coefficient, no integer division, no int -> double
+  {
+    const int J = sp.aux;
+    R P = R(0), Px = R(0), Py = R(0);
+    if (J > 0) {
+      for (int b = sp.ncoef - J; b >= 0; b -= J) {  // rows i = I-1 .. 0
+        const R* c = sp.coef + b;
+        R A, Ad = R(0);
+        if (J == 4) {
+          A = c[3];
+          Ad = A;               A = fma(A, y, c[2]);
+          Ad = fma(Ad, y, A);   A = fma(A, y, c[1]);
+          Ad = fma(Ad, y, A);   A = fma(A, y, c[0]);
+        } else {
+          A = c[J - 1];
+          for (int j = J - 2; j >= 0; --j) { Ad = fma(Ad, y, A); A = fma(A, y, c[j]); }
+        }
+        if (WANT_SLOPES) { Px = fma(Px, x, P); Py = fma(Py, x, Ad); }
+        P = fma(P, x, A);
+      }
+    }
+    sag = sag + P;
+    if (WANT_SLOPES) { zx = zx + Px; zy = zy + Py; }
+    return;
+  }
+#endif
   const int J = sp.aux, I = (J > 0) ? sp.ncoef / J : 0;
   R xi = R(1), xim1 = R(0);  // x**i, x**(i-1)
   for (int i = 0; i < I; ++i) {
