@@ -58,6 +58,10 @@ def test_constants_match_header():
     assert d["OLRT_FRAME_REALS"] == _lib.FRAME_REALS
     assert d["OLRT_GEOM_REALS"] == _lib.GEOM_REALS
     assert ctypes.sizeof(_lib.OlrtSys) == 8 * 4 + 8 + 8 * _lib.MAX_WAVELENGTHS
+    # struct olrt_pupil (ABI v5): 5 pointers, 3 int64, 2 int32, 4 doubles, the ready pointer and its chunk length
+    assert ctypes.sizeof(_lib.OlrtPupil) == 5 * 8 + 3 * 8 + 2 * 4 + 4 * 8 + 8 + 8
+    assert d["OLRT_BWD_GENERIC"] == _lib.BWD_GENERIC
+    assert d["OLRT_ST_TIMEOUT"] == _lib.ST_TIMEOUT
 
 
 def test_argument_errors_do_not_need_a_gpu():
@@ -69,6 +73,12 @@ def test_argument_errors_do_not_need_a_gpu():
     assert rc == -1
     rc = lib.olrt_spot_sums_f64(None, None, None, 0, 0, 1, None, 0, None, None)
     assert rc == -1
+    # streamed upload: NULL buffers and a chunk length that is not a multiple of 256 are refused before any copy
+    assert lib.olrt_upload_pupil(None, None, None, None, 1024, 256, None, None, None) == -1
+    buf = (ctypes.c_double * 4)()
+    word = (ctypes.c_uint32 * 1)(1)
+    a = ctypes.addressof(buf)
+    assert lib.olrt_upload_pupil(a, a, a, a, 4, 100, ctypes.addressof(word), ctypes.addressof(word), None) == -1
 
 
 def test_missing_library_fails_loudly(monkeypatch):
