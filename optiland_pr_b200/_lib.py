@@ -34,6 +34,9 @@ AP_RADIAL, AP_OFFSET_RADIAL, AP_ELLIPTICAL, AP_RECTANGULAR = 1, 2, 3, 4
 AP_OR, AP_AND, AP_DIFF = 10, 11, 12
 ST_ZERNIKE_RANGE, ST_WAVELENGTH, ST_BAD_HINT, ST_CHEBYSHEV_RANGE, ST_TIMEOUT = 1, 2, 4, 8, 16
 HINT_FASTKINDS = 1
+FWD_CKPT_BLOCKED = 4     # olrt_trace_fwd_* flag: `record` is the tile-blocked checkpoint buffer (include/olrt.h)
+BWD_CKPT_BLOCKED = 2     # olrt_trace_bwd_* flag: `record` is that buffer
+CKPT_TILE = 256
 BWD_GENERIC = 1          # olrt_trace_bwd_* flag: force the general adjoint kernel (csrc/trace_bwd.cuh)
 BX_MAXK = 3              # Newton updates per surface the reduced-algebra adjoint kernel (csrc/trace_bx.cuh) unrolls
 FWD_FAST = 1

@@ -65,22 +65,36 @@ class FusedTraceFn(torch.autograd.Function):
     """(presc, x, y, z, L, M, N, i, opd_in, w) -> (out [8, N], record [S, 8, N])."""
 
     @staticmethod
-    def forward(ctx, presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast, generic_adjoint=False):
-        if packed.record_surfaces != [lay.index for lay in packed.layouts]:
+    def forward(ctx, presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast, generic_adjoint=False,
+                blocked=False):
+        if not blocked and packed.record_surfaces != [lay.index for lay in packed.layouts]:
             raise L.OlrtLibraryError("the differentiable trace needs every surface recorded (record='all')")
+        if blocked and (packed.record_surfaces or not fast or generic_adjoint or not packed.fastkinds()):
+            raise NotImplementedError("blocked checkpoints: record='none', tolerance mode, plane / conic / "
+                                      "even-asphere lens, reduced-algebra adjoint")
         ins = [x, y, z, Lc, M, N, inten, w]
         res = fused_trace(packed, [t.detach() if t is not None else None for t in ins],
                           opd_in=None if opd_in is None else opd_in.detach(),
-                          presc=presc.detach().reshape(1, -1), want_dir0=True, fast=fast, alias_out=True)
+                          presc=presc.detach().reshape(1, -1), want_dir0=True, fast=fast, alias_out=True,
+                          ckpt=blocked)
+        if blocked and max(res.nr_iters, default=0) > L.BX_MAXK:
+            raise NotImplementedError("blocked checkpoints: a surface took more than 3 Newton updates")
+        ctx.blocked = bool(blocked)
+        ctx.ckpt = res.ckpt
         ctx.set_materialize_grads(False)
         ctx.packed = packed
         ctx.generic_adjoint = bool(generic_adjoint)
         ctx.nr_iters = list(res.nr_iters)
-        ctx.save_for_backward(presc.detach(), *[t.detach() for t in ins if t is not None], res.record)
+        ctx.save_for_backward(presc.detach(), *[t.detach() for t in ins if t is not None],
+                              *([] if blocked else [res.record]))
         ctx.has_w = w is not None
         ctx.has_opd = opd_in is not None
         ctx.status = res.status
         ctx.dir0 = res.dir0
+        if blocked:   # no [S, 8, N] records in this mode: the second output is an empty placeholder
+            empty = res.out.new_empty((0, 8, 0))
+            ctx.mark_non_differentiable(res.dir0, empty)
+            return res.out, empty, res.dir0
         ctx.mark_non_differentiable(res.dir0)
         return res.out, res.record, res.dir0
 
@@ -88,14 +102,18 @@ class FusedTraceFn(torch.autograd.Function):
     def backward(ctx, gout, grecord, _gdir0):
         packed = ctx.packed
         saved = ctx.saved_tensors
-        presc, record = saved[0], saved[-1]
-        ins = list(saved[1:-1])
+        if ctx.blocked:
+            presc, record, grecord = saved[0], ctx.ckpt, None
+            ins = list(saved[1:])
+        else:
+            presc, record = saved[0], saved[-1]
+            ins = list(saved[1:-1])
         if not ctx.has_w:
             ins.append(None)
-        dtype, device = record.dtype, record.device
-        n = int(record.shape[2])
+        dtype, device = ins[0].dtype, ins[0].device
+        n = int(ins[0].numel())
         lib = L.load()
-        if not packed.differentiable():
+        if not packed.differentiable(require_records=not ctx.blocked):
             raise NotImplementedError(
                 "olrt_trace_bwd: gradients are implemented for plane / conic / even-asphere surfaces (<= 8 "
                 "coefficients) on an untilted frame; this lens has a surface outside that set")
@@ -116,6 +134,11 @@ class FusedTraceFn(torch.autograd.Function):
         gin_arr = L.PtrArray8(*[gin[q].data_ptr() if need[q] else 0 for q in range(8)])
         # the reduced-algebra adjoint (csrc/trace_bx.cuh) keeps <= BX_MAXK Newton iterates in registers
         flags = L.BWD_GENERIC if (ctx.generic_adjoint or max(ctx.nr_iters, default=0) > L.BX_MAXK) else 0
+        if ctx.blocked:
+            if flags:
+                raise NotImplementedError("blocked checkpoints: a surface took more than 3 Newton updates; trace "
+                                          "with record='all'")
+            flags = L.BWD_CKPT_BLOCKED
         with torch.cuda.device(device):
             rc = fn(C.byref(sys_), presc.data_ptr(), ops_d.data_ptr(), n, in_arr, record.data_ptr(), gout_arr,
                     _ptr(grecord), gin_arr, gpresc.data_ptr(), status.data_ptr(), flags,
@@ -129,15 +152,18 @@ class FusedTraceFn(torch.autograd.Function):
                 "olrt_trace_bwd: gradients are implemented for plane / conic / even-asphere surfaces on an "
                 "untilted frame; this lens has a surface outside that set")
         g = [gin[q] if need[q] else None for q in range(8)]
-        return (gpresc, g[0], g[1], g[2], g[3], g[4], g[5], g[6], g[7], None, None, None, None)
+        return (gpresc, g[0], g[1], g[2], g[3], g[4], g[5], g[6], g[7], None, None, None, None, None)
 
 
 def trace_differentiable(packed: PackedSystem, presc: torch.Tensor, rays_in, opd_in=None, fast: bool = False,
-                         generic_adjoint: bool = False):
+                         generic_adjoint: bool = False, blocked: bool = False):
     """rays_in: 8 tensors (w may be None for a single wavelength). Returns (out, record, dir0).
-    generic_adjoint=True forces the general backward kernel (csrc/trace_bwd.cuh) instead of the reduced-algebra one."""
+    generic_adjoint=True forces the general backward kernel (csrc/trace_bwd.cuh) instead of the reduced-algebra one.
+    blocked=True (packed with record="none", tolerance mode, plane / conic / even-asphere lens): the checkpoints are
+    tile-blocked (include/olrt.h, OLRT_FWD_CKPT_BLOCKED) -- 56 B per ray and surface, fetched by the backward with one
+    bulk copy per tile and surface -- and `record` comes back empty."""
     x, y, z, Lc, M, N, inten, w = (list(rays_in) + [None])[:8]
-    return FusedTraceFn.apply(presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast, generic_adjoint)
+    return FusedTraceFn.apply(presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast, generic_adjoint, blocked)
 
 
 def _rms_merit(lens, fields, wavelength, Px, Py):
@@ -198,19 +224,24 @@ def bench_backward(lens, packed, ins64, timed, args, fp64_peak) -> dict:
     gout_w[1] = 0.5
     fl = 3.0 * flops.flops_per_ray(pk)
     out = {}
-    for name, ray_grads in (("fp64_fwd_bwd", True), ("fp64_fwd_bwd_prescription_only", False)):
+    pkb = pack_surface_group(lens.surface_group.surfaces, packed.wavelengths, record="none")
+    pkb.set_nr_iters(packed.nr_iters())
+    for name, ray_grads, blocked in (("fp64_fwd_bwd", True, False), ("fp64_fwd_bwd_prescription_only", False, False),
+                                     ("fp64_fwd_bwd_blocked_checkpoints", True, True)):
         rays = [t.detach().requires_grad_(ray_grads and q < 6) if t is not None else None
                 for q, t in enumerate(ins64)]
 
         def step():
             presc.grad = None
-            o, record, _ = trace_differentiable(pk, presc, rays, fast=True)
+            o, record, _ = trace_differentiable(pkb if blocked else pk, presc, rays, fast=True, blocked=blocked)
             o.backward(gout_w)
 
         ms = timed(step, max(2, args.steps // 2), 3)
         out[name] = {"ray_surfaces_per_s": n * S / (ms * 1e-3), "ms": ms,
                      "frac_fp64_fma_peak": fl * n / (ms * 1e-3) / 1e12 / fp64_peak,
-                     "flops_per_ray_fwd_bwd": fl, "checkpoint_bytes_per_ray": 64 * S,
+                     "flops_per_ray_fwd_bwd": fl, "checkpoint_bytes_per_ray": (56 if blocked else 64) * S,
+                     "checkpoints": "tile-blocked [tile][surface][7][256] (what Optic.trace uses when no per-surface "
+                                    "records are asked for)" if blocked else "[S][8][N] records",
                      "gradients": "prescription (frames, radii, conics, asphere coefficients)"
                                   + (" + x y z L M N of every ray" if ray_grads else ""),
                      "kernels": "trace_fx_kernel<double> recording every surface (64 B x S per ray, the "

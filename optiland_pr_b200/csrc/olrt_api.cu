@@ -49,6 +49,7 @@ extern "C" int olrt_trace_fwd_f64(const olrt_sys* sys, const double* presc, cons
   if (sys->n_record > 0 && !record) return OLRT_E_ARG;
   if (!fixup || n_rays > 0xffffffffLL) return OLRT_E_ARG;
   cudaStream_t st = (cudaStream_t)stream;
+  if ((flags & OLRT_FWD_CKPT_BLOCKED) && !(flags & OLRT_FWD_FAST)) return OLRT_E_UNSUPPORTED;
   if (flags & OLRT_FWD_FAST)
     return olrt_fast::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags, st);
   return olrt_strict::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, 0, st);
@@ -291,14 +292,15 @@ extern "C" int olrt_selftest_math_f64(const double* a, const double* b, double* 
 // ---------------------------------------------------------------------------------------------
 template <typename R>
 static int check_bwd(const olrt_sys* sys, const R* presc, const int32_t* ops, long long n_rays,
-                     const R* const in[8], const R* record, R* gpresc) {
+                     const R* const in[8], const R* record, R* gpresc, int flags) {
   int rc = check_sys(sys, presc, ops, n_rays);
   if (rc) return rc;
   if (!in || !record || !gpresc) return OLRT_E_ARG;
   for (int q = 0; q < 7; ++q)
     if (!in[q]) return OLRT_E_ARG;
   if (sys->n_wavelengths > 1 && !in[7]) return OLRT_E_ARG;
-  if (sys->n_record != sys->n_surfaces) return OLRT_E_UNSUPPORTED;  // every surface must be recorded
+  if (!(flags & OLRT_BWD_CKPT_BLOCKED) && sys->n_record != sys->n_surfaces)
+    return OLRT_E_UNSUPPORTED;  // every surface must be recorded (or tile-blocked checkpoints passed)
   return OLRT_OK;
 }
 
@@ -307,7 +309,7 @@ extern "C" int olrt_trace_bwd_f64(const olrt_sys* sys, const double* presc, cons
                                   const double* const gout[8], const double* grecord,
                                   double* const gin[8], double* gpresc, uint32_t* status, int flags,
                                   void* stream) {
-  int rc = check_bwd<double>(sys, presc, ops, n_rays, in, record, gpresc);
+  int rc = check_bwd<double>(sys, presc, ops, n_rays, in, record, gpresc, flags);
   if (rc) return rc;
   if (n_rays == 0) return OLRT_OK;
   return olrt_fast::bwd_f64(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, flags,
@@ -317,7 +319,7 @@ extern "C" int olrt_trace_bwd_f32(const olrt_sys* sys, const float* presc, const
                                   int64_t n_rays, const float* const in[8], const float* record,
                                   const float* const gout[8], const float* grecord, float* const gin[8],
                                   float* gpresc, uint32_t* status, int flags, void* stream) {
-  int rc = check_bwd<float>(sys, presc, ops, n_rays, in, record, gpresc);
+  int rc = check_bwd<float>(sys, presc, ops, n_rays, in, record, gpresc, flags);
   if (rc) return rc;
   if (n_rays == 0) return OLRT_OK;
   return olrt_fast::bwd_f32(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, flags,

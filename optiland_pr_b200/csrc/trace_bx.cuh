@@ -306,8 +306,9 @@ __device__ __forceinline__ void bx_even(const FxSurf<R>& sf, const FxMedium<R>& 
 // dynamic shared memory: checkpoints (offset 0: constant addresses), lane-private gradient accumulators,
 // prescription, padded coefficient table, ops; the per-surface FxSurf / FxInfo / FxMedium tables are static
 template <typename R>
-__host__ __device__ __forceinline__ size_t bx_smem_bytes(int presc_stride, int S, int W, int ops_len, int block) {
-  return (size_t)2 * 7 * block * sizeof(R) + (size_t)((S * OLRT_BWD_SLOTS * OLRT_BX_COLS + 3) & ~3) * sizeof(R) +
+__host__ __device__ __forceinline__ size_t bx_smem_bytes(int presc_stride, int S, int W, int ops_len, int block,
+                                                         int nbuf = 2) {
+  return (size_t)nbuf * 7 * block * sizeof(R) + (size_t)((S * OLRT_BWD_SLOTS * OLRT_BX_COLS + 3) & ~3) * sizeof(R) +
          (size_t)((presc_stride + 3) & ~3) * sizeof(R) +
          (size_t)((presc_stride + 4 * S + 3) & ~3) * sizeof(R) + (size_t)((ops_len + 3) & ~3) * sizeof(int32_t);
 }
@@ -380,21 +381,27 @@ template <> __device__ __forceinline__ float bx_lds<float>(unsigned base, int el
   return v;
 }
 
-// BD: block size known at compile time (256), or 0 = blockDim.x (prescription batches with short tiles)
-template <typename R, int BD>
+// BD: block size known at compile time (256), or 0 = blockDim.x (prescription batches with short tiles).
+// CK: checkpoints are tile-blocked, [tile][surface][7][256] (olrt.h, OLRT_BWD_CKPT_BLOCKED): P.record is that buffer;
+// a thread's seven values of a surface sit at compile-time offsets from ONE pointer that steps back a block per
+// surface, so the cp.async copies need no per-copy address arithmetic. (A variant that fetched each 14 KB block with
+// one cp.async.bulk per CTA behind mbarriers was measured slower: +9 % instructions for the barrier hand-off and the
+// warps of a CTA coupled to its slowest one -- per-thread copies keep the warps independent.)
+template <typename R, int BD, bool CK>
 __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const BwdParams<R> P, uint32_t* status) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ FxSurf<R> s_surf[OLRT_MAX_SURFACES];
   __shared__ FxInfo s_info[OLRT_MAX_SURFACES];
   __shared__ FxMedium<R> s_med[OLRT_BX_MAX_MEDIA];
   __shared__ int s_bad;
+  constexpr int NB = 2;  // checkpoint buffers
   const int S = P.n_surfaces, W = P.n_wavelengths;
   const int bd = BD ? BD : (int)blockDim.x;
   // entry states (checkpoints) staged one surface ahead by cp.async: s_ck[(buf * 7 + q) * bd + tid]
   R* s_ck = reinterpret_cast<R*>(smem_raw);
   // d loss / d presc per LANE (trace_bwd.cuh): s_acc[(s * OLRT_BWD_SLOTS + j) * OLRT_BX_COLS + lane]; the lanes a
   // tail tile leaves idle add (to) column 32, which is never summed: no `valid` branch around the atomics
-  R* s_acc = s_ck + 2 * 7 * bd;
+  R* s_acc = s_ck + NB * 7 * bd;
   R* s_presc = s_acc + ((S * OLRT_BWD_SLOTS * OLRT_BX_COLS + 3) & ~3);  // keep 16 B alignment
   R* s_coef = s_presc + ((P.presc_stride + 3) & ~3);
   int32_t* s_ops = reinterpret_cast<int32_t*>(s_coef + ((P.presc_stride + 4 * S + 3) & ~3));
@@ -407,7 +414,7 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
     const int32_t* op = s_ops + threadIdx.x * OLRT_OPS_STRIDE;
     const int k = fk_kind(s_ops, threadIdx.x);
     s_info[threadIdx.x].kind = k;
-    if (k == KIND_GENERIC || op[OLRT_OP_RECORD] != (int)threadIdx.x) s_bad = 1;
+    if (k == KIND_GENERIC || (!CK && op[OLRT_OP_RECORD] != (int)threadIdx.x)) s_bad = 1;
     if (k == KIND_EVEN && (op[OLRT_OP_NCOEF] > OLRT_BWD_MAXC || op[OLRT_OP_NR_ITERS] > OLRT_BX_MAXK)) s_bad = 1;
   }
   __syncthreads();
@@ -453,11 +460,24 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
       for (int q = 0; q < W; ++q) if (wl == P.wavelengths[q]) widx = q;
     }
     // state after the last surface, then the entry state of surface S-1 (= record S-2; the launch state for S == 1)
-    const R* rp = P.record + (long long)(S - 1) * 8 * N + idx;
-    R Qgx = rp[0], Qgy = rp[N], Qgz = rp[2 * N], irec = rp[6 * N];
+    const R* rp = CK ? P.record + (tile * S + (S - 1)) * (long long)(7 * bd) + threadIdx.x  // block of surface S-1
+                     : P.record + (long long)(S - 1) * 8 * N + idx;
+    R Qgx, Qgy, Qgz, irec;
+    if (CK) {
+      Qgx = rp[0]; Qgy = rp[bd]; Qgz = rp[2 * bd]; irec = rp[6 * bd];
+    } else {
+      Qgx = rp[0]; Qgy = rp[N]; Qgz = rp[2 * N]; irec = rp[6 * N];
+    }
     const long long N8 = 8 * N;
     auto stage = [&](int s_) {  // entry state of surface s_ -> buffer s_ & 1; rp walks down the records
       const unsigned dst = ck_a + (unsigned)((s_ & 1) * 7 * bd * (int)sizeof(R));
+      if (CK && s_ > 0) {
+        rp -= 7 * bd;  // block of surface s_ - 1 (rp already includes this thread's column)
+#pragma unroll
+        for (int q = 0; q < 7; ++q) bx_cp_async<R>(dst + (unsigned)(q * bd * (int)sizeof(R)), rp + q * bd);
+        cp_async_commit();
+        return;
+      }
       if (s_ == 0) {
 #pragma unroll
         for (int q = 0; q < 7; ++q) bx_cp_async<R>(dst + (unsigned)(q * bd * (int)sizeof(R)), P.in[q] + idx);
@@ -476,13 +496,14 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
     R gi = ld(P.gout[6]), gopd = ld(P.gout[7]);
     const bool z0 = (P.in[6][idx] == R(0));
     for (int s = S - 1; s >= 0; --s) {
+      const int cb = s & 1;  // buffer of surface s
       if (s > 0) { stage(s - 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
-      if (P.grecord != nullptr && valid) {
+      if (!CK && P.grecord != nullptr && valid) {
         const R* g = P.grecord + (long long)s * 8 * N + idx;
         gx += g[0]; gy += g[N]; gz += g[2 * N]; gL += g[3 * N]; gM += g[4 * N]; gN += g[5 * N];
         gi += g[6 * N]; gopd += g[7 * N];
       }
-      const unsigned cka = ck_a + (unsigned)((s & 1) * 7 * bd * (int)sizeof(R));
+      const unsigned cka = ck_a + (unsigned)(cb * 7 * bd * (int)sizeof(R));
       const R ex = bx_lds<R>(cka, 0), ey = bx_lds<R>(cka, bd), ez = bx_lds<R>(cka, 2 * bd),
               eL = bx_lds<R>(cka, 3 * bd), eM = bx_lds<R>(cka, 4 * bd), eN = bx_lds<R>(cka, 5 * bd),
               ei = bx_lds<R>(cka, 6 * bd);
@@ -539,19 +560,19 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
   if (cur_p >= 0) bx_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
 }
 
-template <typename R, int BD>
+template <typename R, int BD, bool CK>
 int bx_launch_kernel(const BwdParams<R>& P, int block, size_t smem, long long n_tiles, uint32_t* status,
                      cudaStream_t stream) {
   // static tables (16 KB) + dynamic can pass the 48 KB default even when the dynamic part alone does not
-  cudaFuncSetAttribute(trace_bx_kernel<R, BD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaFuncSetAttribute(trace_bx_kernel<R, BD, CK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   int per_sm = 0, dev = 0, sms = 148;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_bx_kernel<R, BD>, block, smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_bx_kernel<R, BD, CK>, block, smem);
   if (per_sm < 1) per_sm = 1;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   long long grid = (long long)sms * per_sm;
   if (grid > n_tiles) grid = n_tiles;
-  trace_bx_kernel<R, BD><<<(unsigned)grid, block, smem, stream>>>(P, status);
+  trace_bx_kernel<R, BD, CK><<<(unsigned)grid, block, smem, stream>>>(P, status);
   return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
 }
 
@@ -560,6 +581,8 @@ template <typename R>
 int launch_bx(const olrt_sys* sys, const R* presc, const int32_t* ops, long long n_rays, const R* const in[8],
               const R* record, const R* const gout[8], const R* grecord, R* const gin[8], R* gpresc,
               uint32_t* status, int flags, cudaStream_t stream) {
+  if ((flags & OLRT_BWD_CKPT_BLOCKED) && (!(sys->kernel_hint & OLRT_HINT_FASTKINDS) || (flags & OLRT_BWD_GENERIC)))
+    return OLRT_E_UNSUPPORTED;
   if (!(sys->kernel_hint & OLRT_HINT_FASTKINDS) || (flags & OLRT_BWD_GENERIC))
     return launch_bwd<R>(sys, presc, ops, n_rays, in, record, gout, grecord, gin, gpresc, status, stream);
   BwdParams<R> P;
@@ -579,8 +602,12 @@ int launch_bx(const olrt_sys* sys, const R* presc, const int32_t* ops, long long
   const size_t smem = bx_smem_bytes<R>(sys->presc_stride, sys->n_surfaces, sys->n_wavelengths, sys->ops_len, block);
   if (smem > 180 * 1024 || sys->n_surfaces * sys->n_wavelengths > OLRT_BX_MAX_MEDIA) return OLRT_E_LIMIT;
   const long long n_tiles = (n_rays + block - 1) / block;
-  if (block == 256) return bx_launch_kernel<R, 256>(P, block, smem, n_tiles, status, stream);
-  return bx_launch_kernel<R, 0>(P, block, smem, n_tiles, status, stream);
+  if (flags & OLRT_BWD_CKPT_BLOCKED) {  // `record` is the tile-blocked checkpoint buffer of the forward
+    if (block != OLRT_CKPT_TILE || sys->n_presc > 1 || grecord != nullptr) return OLRT_E_UNSUPPORTED;
+    return bx_launch_kernel<R, 256, true>(P, block, smem, n_tiles, status, stream);
+  }
+  if (block == 256) return bx_launch_kernel<R, 256, false>(P, block, smem, n_tiles, status, stream);
+  return bx_launch_kernel<R, 0, false>(P, block, smem, n_tiles, status, stream);
 }
 
 }  // namespace OLRT_NS

@@ -15,6 +15,7 @@ struct FwdParams {
   const R* opd_in;
   R* out[8];
   R* record;
+  R* ckpt;  // nullptr, or tile-blocked checkpoints [tile][surface][7][OLRT_CKPT_TILE] (olrt.h, OLRT_FWD_CKPT_BLOCKED)
   R* dir0;
   const R* presc;
   const int32_t* ops;
@@ -302,6 +303,12 @@ __device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r,
       rec[0] = r.x; rec[NT] = r.y; rec[2 * NT] = r.z;
       rec[3 * NT] = r.L; rec[4 * NT] = r.M; rec[5 * NT] = r.N;
       rec[6 * NT] = r.i; rec[7 * NT] = r.opd;
+    }
+    if (P.ckpt != nullptr && valid) {  // blocked checkpoint of this ray (the fix-up pass repairs single rays)
+      R* ck = P.ckpt + (((idx / OLRT_CKPT_TILE) * S + s) * 7) * OLRT_CKPT_TILE + (idx % OLRT_CKPT_TILE);
+      ck[0] = r.x; ck[OLRT_CKPT_TILE] = r.y; ck[2 * OLRT_CKPT_TILE] = r.z;
+      ck[3 * OLRT_CKPT_TILE] = r.L; ck[4 * OLRT_CKPT_TILE] = r.M; ck[5 * OLRT_CKPT_TILE] = r.N;
+      ck[6 * OLRT_CKPT_TILE] = r.i;
     }
   }
 }

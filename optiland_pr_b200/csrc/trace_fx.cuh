@@ -454,6 +454,7 @@ trace_fx_kernel(const FwdParams<R> P) {
   // fused spot epilogue: per-thread sums for the current group, flushed when the group changes
   const bool want_spot = (P.spot != nullptr);
   const bool rec_on = (P.record != nullptr);
+  const bool ck_on = (P.ckpt != nullptr);   // array mode, 256-thread tiles (launch_fwd checks)
   int sp_g = -1;
   double sp_cnt = 0, sp_x = 0, sp_y = 0, sp_xx = 0, sp_yy = 0, sp_i = 0, sp_max = 0, sp_sx = 0, sp_sy = 0;
   bool sp_nan = false;
@@ -567,8 +568,19 @@ trace_fx_kernel(const FwdParams<R> P) {
                      want_resid ? (s_resid + info.roff) : nullptr, att);
           break;
       }
-      if (!rec_on) continue;
+      if (!rec_on && !ck_on) continue;
       if (md.nalpha != R(0)) i_stale = true;
+      if (ck_on) {  // tile-blocked checkpoint: the state after this surface, immediate offsets from one pointer
+        if (i_stale) { i_rec = fk_intensity(r.i, att); i_stale = false; }
+        else if (!(r.i != R(0))) i_rec = r.i;
+        if (valid) {
+          R* ckp = P.ckpt + ((tile * S + s) * 7) * OLRT_CKPT_TILE + threadIdx.x;
+          __stcs(ckp, r.x); __stcs(ckp + OLRT_CKPT_TILE, r.y); __stcs(ckp + 2 * OLRT_CKPT_TILE, r.z);
+          __stcs(ckp + 3 * OLRT_CKPT_TILE, r.L); __stcs(ckp + 4 * OLRT_CKPT_TILE, r.M);
+          __stcs(ckp + 5 * OLRT_CKPT_TILE, r.N); __stcs(ckp + 6 * OLRT_CKPT_TILE, i_rec);
+        }
+        continue;
+      }
       const int slot = info.record;
       if (slot >= 0 && valid) {  // Surface._record, standard_surface.py:266-286
         R* rec = P.record + (long long)slot * 8 * NT + idx;  // streaming stores: never re-read by this launch

@@ -44,7 +44,7 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
                unsigned long long* group_resid = nullptr) {
   FwdParams<R> P;
   for (int q = 0; q < 8; ++q) { P.in[q] = in ? in[q] : nullptr; P.out[q] = out ? out[q] : nullptr; }
-  P.opd_in = opd_in; P.record = record; P.dir0 = dir0; P.presc = presc; P.ops = ops;
+  P.opd_in = opd_in; P.record = record; P.ckpt = nullptr; P.dir0 = dir0; P.presc = presc; P.ops = ops;
   P.nr_resid = nr_resid; P.status = status; P.n_rays = n_rays;
   P.fixup = (sizeof(R) == 8) ? fixup : nullptr;
   P.rays_per_presc = sys->rays_per_presc > 0 ? sys->rays_per_presc : n_rays;
@@ -71,6 +71,11 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
 #endif
   const int block = pick_block(sys, fk, fx, gen != nullptr);
   if (block == 0) return OLRT_E_ARG;
+  if (flags & OLRT_FWD_CKPT_BLOCKED) {  // `record` is the tile-blocked checkpoint buffer
+    if (!fx || gen != nullptr || sys->n_record != 0 || sys->n_presc > 1 || block != OLRT_CKPT_TILE || record == nullptr)
+      return OLRT_E_UNSUPPORTED;
+    P.ckpt = record; P.record = nullptr;
+  }
   int resid_words = nr_resid ? sys->nr_resid_words : 0;
   if (P.group_resid != nullptr && resid_words < sys->n_surfaces * OLRT_GROUP_RESID)
     resid_words = sys->n_surfaces * OLRT_GROUP_RESID;

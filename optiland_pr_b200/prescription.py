@@ -145,11 +145,11 @@ class PackedSystem:
                 return False
         return True
 
-    def differentiable(self) -> bool:
+    def differentiable(self, require_records: bool = True) -> bool:
         """True when the backward kernels cover every surface (csrc/trace_bwd.cuh: bwd_supported): plane / finite
         conic / even asphere with <= 8 coefficients on one untilted frame, any aperture program, no coating or
         thin-lens flag, every surface recorded. The kernels re-check it (OLRT_ST_BAD_HINT)."""
-        if self.record_surfaces != [lay.index for lay in self.layouts]:
+        if require_records and self.record_surfaces != [lay.index for lay in self.layouts]:
             return False
         for k in range(self.n_surfaces):
             row = k * L.OPS_STRIDE

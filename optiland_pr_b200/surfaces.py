@@ -113,6 +113,7 @@ class SurfaceGroup:
         # identical vignetting / TIR masks (reduced-algebra kernel, csrc/trace_fx.cuh). False: strict mode --
         # the reference's operation order without FMA contraction, bit-identical for + - * / sqrt, ~2x slower.
         self.fast_math = True
+        self.blocked_checkpoints = True   # differentiable traces with record 'none' / 'last': tile-blocked checkpoints
         self._packed_cache = None
         self.forced_nr_iters = None  # {surface index: K}: skip the exit-rule check (sharded batches, parallel.py)
         self.last_trace = None
@@ -308,13 +309,30 @@ class SurfaceGroup:
         if self._wants_grad(rays):
             # one autograd node: forward kernel (records = checkpoints) + backward kernel (autograd.py)
             from .autograd import prescription_tensor, trace_differentiable
-            if self.record != "all":
-                packed = pack_surface_group(self._surfaces, wavelengths, record="all", skip=skip)
-                for k in packed.nr_rows():
-                    packed.ops[k * 16 + 6] = min(packed.layouts[k].max_iter,
-                                                 (self._packed_cache or {}).get(packed.layouts[k].index, 2))
-            presc_t = prescription_tensor(packed, self._surfaces, ins[0].dtype, ins[0].device)
-            out, record, dir0 = trace_differentiable(packed, presc_t, ins, opd_in=rays.opd, fast=self.fast_math)
+            def repack(mode):
+                pk = pack_surface_group(self._surfaces, wavelengths, record=mode, skip=skip)
+                for k in pk.nr_rows():
+                    pk.ops[k * 16 + 6] = min(pk.layouts[k].max_iter,
+                                             (self._packed_cache or {}).get(pk.layouts[k].index, 2))
+                return pk
+            out = None
+            if self.record in ("none", "last", None) and self.fast_math and self.blocked_checkpoints:
+                # nobody reads per-surface records: tile-blocked checkpoints (56 B per ray and surface, no second
+                # copy of the final state) instead of [S, 8, N] records -- lenses of planes / conics / even aspheres
+                pk = repack("none")
+                if pk.fastkinds():
+                    presc_t = prescription_tensor(pk, self._surfaces, ins[0].dtype, ins[0].device)
+                    try:
+                        out, record, dir0 = trace_differentiable(pk, presc_t, ins, opd_in=rays.opd, fast=True,
+                                                                 blocked=True)
+                        packed, record = pk, None
+                    except NotImplementedError:     # e.g. a surface that needs more than 3 Newton updates
+                        out = None
+            if out is None:
+                if self.record != "all":
+                    packed = repack("all")
+                presc_t = prescription_tensor(packed, self._surfaces, ins[0].dtype, ins[0].device)
+                out, record, dir0 = trace_differentiable(packed, presc_t, ins, opd_in=rays.opd, fast=self.fast_math)
             res = TraceResult(out=out, record=record, dir0=dir0, nr_iters=packed.nr_iters(), status=0, launches=1)
         else:
             res = fused_trace(packed, ins, opd_in=rays.opd, want_dir0=True, fast=self.fast_math,
@@ -328,5 +346,7 @@ class SurfaceGroup:
         if res.status & 2:
             raise ValueError("a ray wavelength is missing from `wavelengths`")
         self._finish(rays, packed, res.out, res.record, res.dir0, res.nr_iters)
+        if self.record == "last" and not packed.record_surfaces:   # blocked checkpoints: the final state IS the record
+            self._surfaces[-1]._set_record(res.out)
         self.last_trace = res
         return rays

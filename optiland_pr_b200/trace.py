@@ -33,6 +33,7 @@ class TraceResult:
     launches: int
     fixups: int = -1             # rays re-traced by the IEEE fix-up kernel (fp64; -1 = not read back)
     nr_true: list | None = None  # with nr_floor: the counts this slice alone satisfies the exit rule with
+    ckpt: torch.Tensor | None = None  # tile-blocked checkpoints (fused_trace(ckpt=True)), else None
 
 
 def _ptr(t) -> int:
@@ -96,7 +97,7 @@ def slice_true_iters(packed: PackedSystem, resid_rows: np.ndarray, k_used):
 def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tensor | None = None,
                 n_presc: int = 1, rays_per_presc: int = 0, want_dir0: bool = False,
                 fast: bool = False, verify_nr: bool = True, out: torch.Tensor | None = None,
-                alias_out: bool = False, max_relaunch: int = 24, read_fixups: bool = True, check_status: bool = True,
+                alias_out: bool = False, ckpt: bool = False, max_relaunch: int = 24, read_fixups: bool = True, check_status: bool = True,
                 dir0_out: torch.Tensor | None = None, status_t: torch.Tensor | None = None,
                 nr_floor: bool = False, resid_out: torch.Tensor | None = None,
                 replay: bool = False) -> TraceResult:
@@ -141,6 +142,12 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
         n_presc = int(presc_d.shape[0])
     n_rec = len(packed.record_surfaces)
     record = torch.empty((n_rec, 8, n), dtype=dtype, device=device) if n_rec else None
+    ckpt_buf = None
+    if ckpt:  # tile-blocked checkpoints [tile][surface][7][256] instead of records (include/olrt.h)
+        if n_rec or not fast or n_presc != 1:
+            raise L.OlrtLibraryError("blocked checkpoints need record='none', tolerance mode and one prescription")
+        tiles = -(-n // L.CKPT_TILE)
+        ckpt_buf = torch.empty(tiles * packed.n_surfaces * 7 * L.CKPT_TILE, dtype=dtype, device=device)
     if out is None:
         if alias_out and n_rec and packed.record_surfaces[-1] == packed.layouts[-1].index:
             # the final state IS the last surface's record: both stores land on the same lines (merged in L2),
@@ -178,8 +185,11 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
             sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=rays_per_presc)
             sys_.presc_stride = int(presc_d.shape[1])
             rc = fn(C.byref(sys_), presc_d.data_ptr(), ops_d.data_ptr(), n, in_arr, _ptr(opd_in),
-                    out_arr, _ptr(record), dir0_ptr, _ptr(resid), status_t.data_ptr(), _ptr(fixup),
-                    (L.FWD_FAST if fast else 0) | (L.FWD_REPLAY if replay else 0), stream)
+                    out_arr, _ptr(ckpt_buf if ckpt else record), dir0_ptr, _ptr(resid), status_t.data_ptr(),
+                    _ptr(fixup), (L.FWD_FAST if fast else 0) | (L.FWD_REPLAY if replay else 0)
+                    | (L.FWD_CKPT_BLOCKED if ckpt else 0), stream)
+            if rc == -4 and ckpt:
+                raise NotImplementedError("olrt_trace_fwd: blocked checkpoints need a lens of planes / conics / even aspheres")
             L.check(rc, "olrt_trace_fwd")
             launches += 1
             if resid is None or n == 0 or resid_out is not None:
@@ -217,7 +227,7 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
         raise L.OlrtLibraryError("kernel_hint does not match the ops table (packer bug)")
     fixups = int(fixup[0].item()) if (fixup is not None and read_fixups and check_status) else -1
     return TraceResult(out=out, record=record, dir0=dir0, nr_iters=packed.nr_iters(), status=status,
-                       launches=launches, fixups=fixups,
+                       launches=launches, fixups=fixups, ckpt=ckpt_buf,
                        nr_true=nr_true if nr_true is not None else packed.nr_iters())
 
 

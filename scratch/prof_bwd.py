@@ -37,3 +37,14 @@ def fwd_bwd():
     out.backward(g)
 a, b = tm(fwd_only), tm(fwd_bwd)
 print(f"n={n}: fwd(record all) {a:.3f} ms, fwd+bwd {b:.3f} ms, bwd {b-a:.3f} ms  ({n*12/b/1e6:.1f} G rs/s fwd+bwd)")
+pkb = pack_surface_group(lens.surface_group.surfaces, [0.5876], record="none"); pkb.set_nr_iters(pk.nr_iters())
+def fwd_only_b():
+    with torch.no_grad():
+        trace_differentiable(pkb, presc, leaf, fast=True, blocked=True)
+def fwd_bwd_b():
+    presc.grad = None
+    out, rec, _ = trace_differentiable(pkb, presc, leaf, fast=True, blocked=True)
+    out.backward(g)
+if len(sys.argv) > 2:
+    a, b = tm(fwd_only_b), tm(fwd_bwd_b)
+    print(f"n={n}: BLOCKED fwd {a:.3f} ms, fwd+bwd {b:.3f} ms, bwd {b-a:.3f} ms  ({n*12/b/1e6:.1f} G rs/s fwd+bwd)")

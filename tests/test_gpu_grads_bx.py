@@ -149,3 +149,68 @@ def test_reduced_adjoint_valid_rays_only_prescription_gradient():
     nz = p0 != 0
     rel = np.abs(p1[nz] - p0[nz]) / np.maximum(np.abs(p0[nz]), 1e-6 * np.abs(p0).max())
     assert rel.max() <= 1e-8, rel.max()
+
+
+@pytest.mark.parametrize("name,n", [("EvenAsphereDoubleGauss", 70_001), ("CookeTriplet", 4_096), ("_Mixed", 33_000)])
+def test_blocked_checkpoints_give_the_same_gradients(name, n):
+    """Tile-blocked checkpoints (OLRT_FWD_CKPT_BLOCKED / OLRT_BWD_CKPT_BLOCKED: 7 components per surface, one bulk copy
+    per tile and surface in the backward) against the [S, 8, N] records: same forward state, same adjoint arithmetic,
+    so the gradients agree to rounding of the accumulation order; ragged last tile included."""
+    lens = _Mixed() if name == "_Mixed" else getattr(samples, name)()
+    wls = list(lens.wavelengths)
+    rng = np.random.default_rng(17)
+    r_, th = np.sqrt(rng.uniform(size=n)), rng.uniform(0, 2 * np.pi, n)
+    wl = np.asarray(wls)[rng.integers(0, len(wls), n)]
+    Hy = rng.choice([0.0, 0.7, 1.0], n)
+    rays = lens.generate_rays(torch.zeros(n, dtype=torch.float64, device="cuda"), torch.from_numpy(Hy).cuda(),
+                              torch.from_numpy(r_ * np.cos(th)).cuda(), torch.from_numpy(r_ * np.sin(th)).cuda(),
+                              torch.from_numpy(wl).cuda())
+    ins = rays.components()
+    ins[6] = ins[6].clone()
+    ins[6][::19] = 0.0
+    gout = torch.from_numpy(rng.normal(size=(8, n))).cuda()
+    got = []
+    for blocked in (False, True):
+        pk = pack_surface_group(lens.surface_group.surfaces, wls, record="none" if blocked else "all")
+        presc = torch.tensor(pk.presc[0], dtype=torch.float64, device="cuda", requires_grad=True)
+        leaf = [t.detach().clone().requires_grad_(q < 7) for q, t in enumerate(ins)]
+        opd_in = torch.zeros(n, dtype=torch.float64, device="cuda", requires_grad=True)
+        out, record, dir0 = trace_differentiable(pk, presc, leaf, opd_in=opd_in, fast=True, blocked=blocked)
+        assert (record.numel() == 0) == blocked
+        (out * gout).nan_to_num(0.0).sum().backward()
+        gin = torch.stack([leaf[q].grad for q in range(7)] + [opd_in.grad]).cpu().numpy()
+        got.append((out.detach().cpu().numpy(), dir0.cpu().numpy(), gin, presc.grad.cpu().numpy()))
+    (o0, d0, g0, p0), (o1, d1, g1, p1) = got
+    assert np.array_equal(o0, o1, equal_nan=True) and np.array_equal(d0, d1, equal_nan=True)
+    assert np.array_equal(g0, g1, equal_nan=True)            # per-ray gradients: the same arithmetic, bit for bit
+    if np.isfinite(p0).all():
+        assert np.array_equal(p0 != 0, p1 != 0)
+        assert np.abs(p1 - p0).max() <= 1e-11 * np.abs(p0).max()
+    else:
+        assert np.array_equal(np.isnan(p0), np.isnan(p1))
+
+
+def test_public_api_gradients_do_not_depend_on_the_checkpoint_layout():
+    """Optic.trace with record 'none' (tile-blocked checkpoints) and record 'all' ([S, 8, N] records): the same
+    d(merit) / d(radius, thickness-driven frame z) through the public autograd path."""
+    from optiland_pr_b200.autograd import _rms_merit
+    rng = np.random.default_rng(4)
+    rr, th = np.sqrt(rng.uniform(size=3000)), rng.uniform(0, 2 * np.pi, 3000)
+    Px, Py = rr * np.cos(th), rr * np.sin(th)
+    fields = [(0.0, 0.0), (0.0, 0.7), (0.0, 1.0)]
+    grads = []
+    for mode in ("all", "none"):
+        lens = samples.CookeTriplet()
+        lens.surface_group.record = mode
+        r1 = torch.tensor(22.01359, dtype=torch.float64, device="cuda", requires_grad=True)
+        r4 = torch.tensor(20.29192, dtype=torch.float64, device="cuda", requires_grad=True)
+        lens.set_radius(r1, 1)
+        lens.set_radius(r4, 4)
+        loss = _rms_merit(lens, fields, 0.55, Px, Py)
+        loss.backward()
+        grads.append((float(loss), float(r1.grad), float(r4.grad)))
+        used_blocked = lens.surface_group.last_trace.record is None
+        assert used_blocked == (mode == "none")
+    (l0, a0, b0), (l1, a1, b1) = grads
+    assert l0 == l1
+    assert abs(a1 - a0) <= 1e-11 * abs(a0) and abs(b1 - b0) <= 1e-11 * abs(b0)
