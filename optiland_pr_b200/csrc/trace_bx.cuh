@@ -512,36 +512,43 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
       const FxInfo& info = s_info[s];
       const int kind = info.kind;
       R* acc = s_acc + s * (OLRT_BWD_SLOTS * OLRT_BX_COLS) + col;
-      switch (kind & 15) {  // warp-uniform
-        case KIND_PLANE: {
-          R gTz;
-          bx_plane<R>(sf, md, kind, z0, ez, eL, eM, eN, ei, irec, ex, ey, gx, gy, gz, gL, gM, gN, gi, gopd, gTz);
-          atomicAdd(acc + 2 * OLRT_BX_COLS, gTz);
-          break;
-        }
-        case KIND_CONIC: {
-          R gTx, gTy, gTz, gR, gk;
-          bx_conic<R>(sf, md, kind, z0, ex, ey, ez, eL, eM, eN, ei, irec, Qgx, Qgy, Qgz, gx, gy, gz, gL, gM, gN, gi,
-                      gopd, gTx, gTy, gTz, gR, gk);
-          const R pv[5] = {gTx, gTy, gTz, gR, gk};
-          bx_add_n<5>(acc, pv);
-          break;
-        }
-        default: {
-          R gTx, gTy, gTz, gR, gk;
-          R gC[OLRT_BWD_MAXC];
+      // the per-kind bodies take the flag word as a parameter: the dense variant id of fx_build_surface lets an
+      // ordinary lens surface (centred, refracting, no aperture) pass its flags as a compile-time constant
+      auto do_plane = [&](const int kk) {
+        R gTz;
+        bx_plane<R>(sf, md, kk, z0, ez, eL, eM, eN, ei, irec, ex, ey, gx, gy, gz, gL, gM, gN, gi, gopd, gTz);
+        atomicAdd(acc + 2 * OLRT_BX_COLS, gTz);
+      };
+      auto do_conic = [&](const int kk) {
+        R gTx, gTy, gTz, gR, gk;
+        bx_conic<R>(sf, md, kk, z0, ex, ey, ez, eL, eM, eN, ei, irec, Qgx, Qgy, Qgz, gx, gy, gz, gL, gM, gN, gi,
+                    gopd, gTx, gTy, gTz, gR, gk);
+        const R pv[5] = {gTx, gTy, gTz, gR, gk};
+        bx_add_n<5>(acc, pv);
+      };
+      auto do_even = [&](const int kk) {
+        R gTx, gTy, gTz, gR, gk;
+        R gC[OLRT_BWD_MAXC];
 #pragma unroll
-          for (int i = 0; i < OLRT_BWD_MAXC; ++i) gC[i] = R(0);
-          const int m4 = info.ncoef;
-          bx_even<R>(sf, md, kind, info.K, m4, s_coef + info.coef_off, z0, ex, ey, ez, eL, eM, eN, ei, irec, gx, gy,
-                     gz, gL, gM, gN, gi, gopd, gTx, gTy, gTz, gR, gk, gC);
-          const R pv[5] = {gTx, gTy, gTz, gR, gk};
-          bx_add_n<5>(acc, pv);
-          // coefficient partials in blocks of 4 like the padded table (bx_flush drops the padding's)
-          if (m4 > 0) bx_add_n<4>(acc + 5 * OLRT_BX_COLS, gC);
-          if (m4 > 4) bx_add_n<4>(acc + 9 * OLRT_BX_COLS, gC + 4);
-          break;
-        }
+        for (int i = 0; i < OLRT_BWD_MAXC; ++i) gC[i] = R(0);
+        const int m4 = info.ncoef;
+        bx_even<R>(sf, md, kk, info.K, m4, s_coef + info.coef_off, z0, ex, ey, ez, eL, eM, eN, ei, irec, gx, gy,
+                   gz, gL, gM, gN, gi, gopd, gTx, gTy, gTz, gR, gk, gC);
+        const R pv[5] = {gTx, gTy, gTz, gR, gk};
+        bx_add_n<5>(acc, pv);
+        // coefficient partials in blocks of 4 like the padded table (bx_flush drops the padding's)
+        if (m4 > 0) bx_add_n<4>(acc + 5 * OLRT_BX_COLS, gC);
+        if (m4 > 4) bx_add_n<4>(acc + 9 * OLRT_BX_COLS, gC + 4);
+      };
+      switch (info.pad1) {  // warp-uniform, dense
+        case 0: do_plane(kind); break;
+        case 1: do_conic(kind); break;
+        case 3: do_plane(KIND_PLANE | FX_CENTERED); break;
+        case 4:
+        case 5: do_conic(KIND_CONIC | FX_CENTERED); break;
+        case 6: do_even(KIND_EVEN | FX_CENTERED | FX_SPHERE); break;
+        case 7: do_even(KIND_EVEN | FX_CENTERED); break;
+        default: do_even(kind); break;
       }
       Qgx = ex; Qgy = ey; Qgz = ez; irec = ei;
     }
