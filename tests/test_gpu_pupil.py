@@ -149,3 +149,23 @@ def test_streamed_host_grid_equals_chunked_and_resident(npup, chunks):
     sa, sb = spot.spot_stats(got[0].spot_sums), spot.spot_stats(got[2].spot_sums)
     for key in ("count", "cx", "cy", "rms", "intensity"):
         assert torch.allclose(sa[key], sb[key], rtol=1e-10, atol=1e-10), key
+
+
+def test_streamed_launch_times_out_instead_of_hanging():
+    """A "ready" word that is never set (a copy that was never queued) ends the launch with OLRT_ST_TIMEOUT after
+    ~2 s; words that are set let the same launch through. The GPU is never left spinning."""
+    import time
+    _, packed, Px, Py, _, _, fxy, _, kw = _setup(samples.EvenAsphereDoubleGauss, 4096, torch.float64)
+    out = torch.empty((8, 3 * 4096), dtype=torch.float64, device="cuda")
+    for words, want in ((torch.ones(4, dtype=torch.int32, device="cuda"), 0),
+                        (torch.tensor([1, 1, 0, 0], dtype=torch.int32, device="cuda"), L.ST_TIMEOUT)):
+        status = torch.zeros(1, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        fused_trace_pupil(packed, Px, Py, fxy, out=out, status_t=status, ready=words, ready_chunk=1024, **kw)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        assert int(status.item()) & L.ST_TIMEOUT == want
+        assert dt < 10.0
+        if want:
+            assert dt > 0.5
