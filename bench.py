@@ -157,6 +157,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_cpus = parallel.bind_to_gpu_numa(local) if world > 1 else None   # before any pinned allocation
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -409,7 +410,9 @@ def main():
                    "rays_per_gpu": n, "surfaces": S_eff, "precision": "float64, tolerance mode (<= 1e-10 relative to the reference, identical masks; "
                                                                   "the bit-identical strict mode is timed in roofline.strict_mode)",
                    "l2": "inputs (268 MB pupil grid) and outputs (3.2 GB) per step exceed the 126 MB L2; no flush needed",
-                   "parallelism": f"rays sharded over {world} GPU(s), spot sums all-reduced"},
+                   "parallelism": f"rays sharded over {world} GPU(s), spot sums all-reduced",
+                   "host_affinity": (f"each rank pinned to its GPU's NUMA CPUs ({len(numa_cpus)} on rank 0)"
+                                     if numa_cpus else "default")},
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h,
                 "api": "Optic.trace(Hx, Hy, wl, distribution=(Px, Py) pinned host, spot=True) + spot.spot_stats -> host; "

@@ -24,6 +24,27 @@ def world():
     return 0, 1
 
 
+def bind_to_gpu_numa(local_rank: int) -> list | None:
+    """Pin this process to the CPUs closest to GPU `local_rank` (NVML's ideal affinity: the GPU's NUMA node) BEFORE it
+    allocates pinned host buffers, so that the host -> device stream of a rank does not cross the socket
+    interconnect. One process per GPU makes this the rank's whole affinity. Returns the CPU list, or None when NVML
+    or the affinity call is unavailable (nothing is changed then)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1]
+        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None
+
+
 def shard_range(n: int, rank: int | None = None, world_size: int | None = None):
     """Contiguous [lo, hi) of n items for this rank; the first n % world ranks get one extra."""
     r, w = world()
