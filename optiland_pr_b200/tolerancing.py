@@ -108,14 +108,20 @@ class MonteCarloSpot:
         self.values = None      # [n_trials, n_perturbations], the draws (trial-major, the reference's order)
         self.last_path = None
 
-    def draw(self, num_iterations):
-        vals = np.empty((num_iterations, len(self.perturbations)))
-        for t in range(num_iterations):          # monte_carlo.py:86-92: per trial, every perturbation in order
+    def _draw_rows(self, vals):
+        """Fill `vals` [rows, n_perturbations] with the next draws of every sampler, trial by trial."""
+        for t in range(vals.shape[0]):           # monte_carlo.py:86-92: per trial, every perturbation in order
             for j, p in enumerate(self.perturbations):
                 p.value = p.sampler.sample()
                 vals[t, j] = p.value
+
+    def draw(self, num_iterations):
+        vals = np.empty((num_iterations, len(self.perturbations)))
+        self._draw_rows(vals)
         self.values = vals
         return vals
+
+    draw_chunks = 4      # fused path, >= 1024 trials: the draws of chunk c + 1 run on the host while chunk c traces
 
     def prescriptions(self, packed, values):
         """[n_trials, stride] float64: the nominal row with every trial's perturbed entries."""
@@ -133,14 +139,26 @@ class MonteCarloSpot:
         lens, sg = self.optic, self.optic.surface_group
         dev = torch.device(be.get_device())
         dt = be.get_precision()
-        values = self.draw(num_iterations)
         keep = sg.record
         sg.record = "none"
         try:
             packed = sg.pack([float(wavelength)])
         finally:
             sg.record = keep
-        batch = self.prescriptions(packed, values)
+        fused = bool(packed.fastkinds())
+        # Fused path: the reference-order scalar draws (one Python call per trial and perturbation) are made chunk by
+        # chunk, each chunk while the previous one is on the GPU; every sampler keeps its own generator, so the values
+        # are the ones one pass over all trials would draw. Every rank draws every chunk (same generator state).
+        chunked_draws = fused and num_iterations >= 1024 and self.draw_chunks > 1 and trials_per_launch is None
+        if chunked_draws:
+            values = np.empty((num_iterations, len(self.perturbations)))
+            self.values = values
+            draw_edges = [int(v) for v in np.linspace(0, num_iterations, self.draw_chunks + 1)]
+            self._draw_rows(values[draw_edges[0]:draw_edges[1]])
+            batch = None
+        else:
+            values = self.draw(num_iterations)
+            batch = self.prescriptions(packed, values)
         lo, hi = parallel.shard_range(num_iterations)
         Hx = np.atleast_1d(np.asarray(Hx, dtype=np.float64))
         Hy = np.atleast_1d(np.asarray(Hy, dtype=np.float64))
@@ -154,7 +172,6 @@ class MonteCarloSpot:
         fxy = ft.fxy_d
         gen_kw = dict(EPD=lens._EPD, EPL=lens._EPL, wavelength=float(wavelength), dtype=dt, **ft.kwargs())
         rms_local = torch.empty((hi - lo, nf), dtype=torch.float64, device=dev)
-        fused = bool(packed.fastkinds())
         self.last_path = "fused" if fused else "chunked"
         step = trials_per_launch or (hi - lo if fused else max(1, (1 << 26) // max(1, nf * npup)))
         zero1 = torch.zeros(1, dtype=torch.float64, device=dev)
@@ -164,10 +181,10 @@ class MonteCarloSpot:
         S = packed.n_surfaces
         nr_rows = packed.nr_rows()
 
-        def fused_groups(presc_t, k0):
+        def fused_groups(presc_t, k0, between=None):
             """(rms [T, nf], counts [T * nf, S]) from trace.fused_spot_groups: one fused launch per round over
             `presc_t` [T, stride], Newton trip counts per (trial, field) group."""
-            sums, kg = fused_spot_groups(packed, presc_t, Px, Py, fxy, gen_kw, k0)
+            sums, kg = fused_spot_groups(packed, presc_t, Px, Py, fxy, gen_kw, k0, between=between)
             return spot_stats(sums)["rms"].reshape(int(presc_t.shape[0]), nf), kg
 
         k_nominal = np.zeros((nf, S), dtype=np.int32)
@@ -179,7 +196,23 @@ class MonteCarloSpot:
             _, kg0 = fused_groups(nominal, k_nominal)
             k_nominal = kg0.reshape(nf, S)
         self.group_iters = None
-        for a in range(lo, hi, max(1, step)):
+        if chunked_draws:
+            for c in range(self.draw_chunks):
+                a, b = max(draw_edges[c], lo), min(draw_edges[c + 1], hi)
+                nxt = None
+                if c + 1 < self.draw_chunks:
+                    nxt = (lambda c_=c: self._draw_rows(values[draw_edges[c_ + 1]:draw_edges[c_ + 2]]))
+                if b > a:
+                    presc = torch.from_numpy(self.prescriptions(packed, values[a:b])).to(dev)
+                    rms_ab, kg = fused_groups(presc, k_nominal, between=nxt)
+                    rms_local[a - lo:b - lo] = rms_ab
+                    self.group_iters = kg if self.group_iters is None else np.concatenate([self.group_iters, kg])
+                elif nxt is not None:
+                    nxt()
+            lo_loop = hi       # nothing left for the generic loop below
+        else:
+            lo_loop = lo
+        for a in range(lo_loop, hi, max(1, step)):
             b = min(hi, a + step)
             presc = torch.from_numpy(batch[a:b]).to(dev)
             T = b - a

@@ -313,7 +313,7 @@ def group_true_iters(packed: PackedSystem, resid: np.ndarray, k_used: np.ndarray
 
 def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Tensor, Py: torch.Tensor,
                       field_xy: torch.Tensor, gen_kw: dict, k0: np.ndarray, *, shift: torch.Tensor | None = None,
-                      valid_only: bool = False, settle: bool = True):
+                      valid_only: bool = False, settle: bool = True, between=None):
     """Spot sums of every (prescription, field) group from fused launch + trace + spot kernels that write nothing
     per ray. `presc_t` [T, stride] holds one prescription per row (Monte-Carlo trials, or one row per WAVELENGTH:
     the media live in the prescription row); the groups are g = row * n_fields + field. The Newton trip counts are
@@ -321,7 +321,8 @@ def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Ten
     `k0` [n_fields, S] is the first guess, groups whose counts fail the exit rule are traced again with corrected
     counts (settle=False: `k0` is [G, S] and trusted). shift: [G, 2] point the sums are taken about (default: each
     group's chief-ray image point, from one more tiny launch). Returns (sums [G, SPOT_SUMS] with columns 8:10 =
-    shift, counts [G, S] int32)."""
+    shift, counts [G, S] int32). `between`: optional host callback run ONCE right after the first launch is queued and
+    before its results are waited for (the caller's host work then overlaps the kernel)."""
     dev = Px.device
     dt = gen_kw.get("dtype", torch.float64)
     nf, S = int(field_xy.shape[0]), packed.n_surfaces
@@ -351,6 +352,9 @@ def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Ten
                           presc=presc_t[sel].contiguous(), group_k=k_t, group_resid=gres, **gen_kw)
         sums[:, 8:10] = sh
         out_sums[gsel_t] = sums
+        if between is not None:
+            between()
+            between = None
         if not check:
             break
         kt = group_true_iters(packed, gres.cpu().numpy().view(np.float64), kg[gsel])
