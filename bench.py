@@ -384,7 +384,8 @@ def main():
     def step_e2e():
         rr = lens.trace(Hx, Hy, WAVELENGTH, distribution=(Px_h, Py_h), spot=True)
         if world > 1:
-            rms_host.copy_(spot.spot_stats(parallel.allreduce_spot_sums(rr.spot_sums))["rms"], non_blocking=False)
+            # merit exchange (one < 1 KB all-reduce), then ONE read-back of the merged sums; the statistics on the host
+            rms_host.copy_(spot.spot_stats(parallel.allreduce_spot_sums(rr.spot_sums).cpu())["rms"])
         else:   # the sums came back with the status word (one pinned read-back inside Optic.trace)
             rms_host.copy_(spot.spot_stats(rr.spot_sums_host)["rms"])
 
