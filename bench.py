@@ -525,6 +525,29 @@ def bench_other_configs(torch, timed, args):
                                                        "nr_iters": res.nr_iters,
                                                        "kernel": "trace_fwd_kernel (interpreter: 4x4 polynomial "
                                                                  "freeforms, Newton-Raphson, tilts, decenters)"}
+    # ---- C3, second half: refractive Zernike (fringe, 36 terms) + odd-asphere plate, tilts about three axes,
+    # elliptical / rectangular / boolean apertures, TIR at the rim -- the interpreter kernel again
+    lens = samples.FreeformPlate()
+    wl = lens.primary_wavelength
+    nz = 1 << 22
+    r_, th = rng.uniform(size=nz), rng.uniform(0, 2 * np.pi, size=nz)
+    Px = torch.from_numpy(np.sqrt(r_) * np.cos(th)).to(dev)
+    Py = torch.from_numpy(np.sqrt(r_) * np.sin(th)).to(dev)
+    f0 = lens.get_field_coords()[0]
+    rays = lens.launch_rays(np.array([f0[0]]), np.array([f0[1]]), Px, Py, wl)
+    ins = rays.components()
+    ins[7] = None
+    lens.surface_group.record = "none"
+    packed = lens.surface_group.pack([float(wl)])
+    o = torch.empty((8, nz), dtype=torch.float64, device=dev)
+    res = fused_trace(packed, ins, out=o, fast=True)
+    Sz = lens.surface_group.num_surfaces - 1
+    ms = timed(lambda: fused_trace(packed, ins, out=o, fast=True, verify_nr=False, check_status=False),
+               max(2, args.steps // 2), 2)
+    out["c3_zernike_freeform_plate_4M_tolerance"] = {"ms": ms, "ray_surfaces_per_s": nz * Sz / (ms * 1e-3),
+                                                     "nr_iters": res.nr_iters,
+                                                     "kernel": "trace_fwd_kernel (interpreter: Zernike fringe freeform, "
+                                                               "odd asphere, aperture programs, tilted frames)"}
     return out
 
 
