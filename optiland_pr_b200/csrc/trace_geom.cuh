@@ -175,6 +175,11 @@ __device__ __forceinline__ void zernike_eval(const SurfParams<R>& sp, R x, R y, 
   const int32_t* nm = sp.ops + sp.aux;
   const R* tc = sp.coef;
   const int nterms = sp.ncoef;
+  // cos(|m| phi), sin(|m| phi), rho^|m| and rho^(|m|-1) are carried from term to term: the angle-addition steps and the
+  // power chain from |m'| to |m| > |m'| are exactly the tail of the steps from 0 to |m|, so continuing gives the same
+  // bits as starting over (the index schemes visit (n, m), (n, -m) back to back); a smaller |m| starts over.
+  int cur = 0;
+  R cm = R(1), sm = R(0), rm = R(1), rm1 = R(1);
   for (int j = 0; j < nterms; ++j) {
     const int n = nm[2 * j], m = nm[2 * j + 1];
     const int ma = (m < 0) ? -m : m;
@@ -182,28 +187,30 @@ __device__ __forceinline__ void zernike_eval(const SurfParams<R>& sp, R x, R y, 
     const R c = tc[0], cN = tc[1];
     const R* rc = tc + 2;
     tc += 2 + smax;
-    // cos(ma*phi), sin(ma*phi)
-    R cm = R(1), sm = R(0);
-    for (int q = 0; q < ma; ++q) {
+    if (ma < cur) { cur = 0; cm = R(1); sm = R(0); rm = R(1); rm1 = R(1); }
+    for (; cur < ma; ++cur) {
       const R cn = cm * cph - sm * sph;
       sm = sm * cph + cm * sph;
       cm = cn;
+      rm1 = rm;
+      rm = rm * rho;
     }
-    // radial polynomial and derivative (Horner in rho^2)
+    // radial polynomial and derivative (Horner in rho^2); the constant term (m == 0, last k) has no derivative
     R H = R(0), Hd = R(0);
-    for (int k = 0; k < smax; ++k) {
-      H = H * rho2 + rc[k];
-      if (WANT_SLOPES) {
-        const int e = n - 2 * k;  // power of this term
-        if (ma > 0 || k < smax - 1) Hd = Hd * rho2 + rc[k] * R(e);
+    {
+      int e = n;  // power of the k-th radial term
+      for (int k = 0; k < smax - 1; ++k, e -= 2) {
+        H = H * rho2 + rc[k];
+        if (WANT_SLOPES) Hd = Hd * rho2 + rc[k] * R(e);
       }
+      H = H * rho2 + rc[smax - 1];
+      if (WANT_SLOPES && ma > 0) Hd = Hd * rho2 + rc[smax - 1] * R(e);
     }
-    const R rm = ipow(rho, ma);
     const R Rad = H * rm;
     const R az = (m >= 0) ? cm : sm;
     zsum = zsum + (cN * Rad) * az;
     if (WANT_SLOPES && c != R(0)) {
-      const R dRad = (ma > 0) ? Hd * ipow(rho, ma - 1) : Hd * rho;
+      const R dRad = (ma > 0) ? Hd * rm1 : Hd * rho;
       R dZdr, dZdp;
       if (m == 0) { dZdr = dRad; dZdp = R(0); }
       else if (m > 0) { dZdr = dRad * cm; dZdp = R(-m) * Rad * sm; }
