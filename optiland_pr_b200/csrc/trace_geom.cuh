@@ -183,7 +183,7 @@ __device__ __forceinline__ void zernike_eval(const SurfParams<R>& sp, R x, R y, 
   for (int j = 0; j < nterms; ++j) {
     const int n = nm[2 * j], m = nm[2 * j + 1];
     const int ma = (m < 0) ? -m : m;
-    const int smax = (n - ma) / 2 + 1;
+    const int smax = ((n - ma) >> 1) + 1;  // n - |m| is even and >= 0
     const R c = tc[0], cN = tc[1];
     const R* rc = tc + 2;
     tc += 2 + smax;
