@@ -28,3 +28,13 @@ for _ in range(5): fused_trace(packed, ins, out=o, fast=fast, verify_nr=False, c
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 5
 print(f"n={n3} fast={fast}: {ms:.3f} ms, {n3*4/ms/1e6:.1f} G ray-surfaces/s")
+from optiland_pr_b200 import _lib as L
+resid = torch.zeros((packed.n_surfaces, L.RESID_STRIDE), dtype=torch.int64, device="cuda")
+st = torch.zeros(1, dtype=torch.int32, device="cuda")
+for _ in range(3): fused_trace(packed, ins, out=o, fast=fast, verify_nr=False, check_status=False, resid_out=resid, status_t=st)
+torch.cuda.synchronize()
+e0.record()
+for _ in range(5): fused_trace(packed, ins, out=o, fast=fast, verify_nr=False, check_status=False, resid_out=resid, status_t=st)
+e1.record(); torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / 5
+print(f"n={n3} fast={fast} WITH residual report: {ms:.3f} ms, {n3*4/ms/1e6:.1f} G ray-surfaces/s")
