@@ -320,7 +320,9 @@ class SurfaceGroup:
                 # nobody reads per-surface records: tile-blocked checkpoints (56 B per ray and surface, no second
                 # copy of the final state) instead of [S, 8, N] records -- lenses of planes / conics / even aspheres
                 pk = repack("none")
-                if pk.fastkinds():
+                # (a lens whose last trace needed more Newton updates than the reduced-algebra adjoint unrolls goes
+                # straight to the record path instead of tracing twice)
+                if pk.fastkinds() and max(pk.nr_iters(), default=0) <= 3:
                     presc_t = prescription_tensor(pk, self._surfaces, ins[0].dtype, ins[0].device)
                     try:
                         out, record, dir0 = trace_differentiable(pk, presc_t, ins, opd_in=rays.opd, fast=True,
