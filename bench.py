@@ -525,6 +525,42 @@ def bench_other_configs(torch, timed, args):
                                                        "nr_iters": res.nr_iters,
                                                        "kernel": "trace_fwd_kernel (interpreter: 4x4 polynomial "
                                                                  "freeforms, Newton-Raphson, tilts, decenters)"}
+    # ---- C4: one optimisation step through the public API (Optic.trace under autograd -> FusedTraceFn: forward with
+    # tile-blocked checkpoints + reduced-algebra adjoint kernel), merit = sum over 3 wavelengths x 3 fields of the squared
+    # RMS spot radius, variables = the six radii and six conic constants of the Cooke triplet (live torch Parameters), Adam update included
+    from optiland_pr_b200.autograd import _rms_merit
+    lens4 = samples.CookeTriplet()
+    lens4.surface_group.record = "none"
+    sfs = lens4.surface_group.surfaces
+    pars = []
+    for k in range(1, 7):
+        p_ = torch.nn.Parameter(torch.tensor(float(sfs[k].geometry.radius), dtype=torch.float64, device=dev))
+        lens4.set_radius(p_, k)
+        pars.append(p_)
+    for k in range(1, 7):
+        p_ = torch.nn.Parameter(torch.tensor(0.0, dtype=torch.float64, device=dev))
+        lens4.set_conic(p_, k)
+        pars.append(p_)
+    opt = torch.optim.Adam(pars, lr=1e-6)
+    n4 = 1_000_000
+    r_, th = rng.uniform(size=n4), rng.uniform(0, 2 * np.pi, size=n4)
+    Px4 = torch.from_numpy(np.sqrt(r_) * np.cos(th)).to(dev)
+    Py4 = torch.from_numpy(np.sqrt(r_) * np.sin(th)).to(dev)
+    fields4 = lens4.get_field_coords()
+    wls4 = list(lens4.wavelengths)
+
+    def c4():
+        opt.zero_grad()
+        loss = sum(_rms_merit(lens4, fields4, w_, Px4, Py4) for w_ in wls4)
+        loss.backward()
+        opt.step()
+        return loss
+
+    ms = timed(c4, max(2, args.steps // 2), 3)
+    out["c4_cooke_merit_adam_step_9_pairs_x_1M"] = {
+        "ms": ms, "ray_surfaces_per_s": 9 * n4 * S1 / (ms * 1e-3), "variables": len(pars),
+        "api": "Optic.trace under autograd (one FusedTraceFn node per wavelength: 3 fields x 1M rays), torch RMS-spot "
+               "merit, loss.backward(), Adam step"}
     # ---- C3, second half: refractive Zernike (fringe, 36 terms) + odd-asphere plate, tilts about three axes,
     # elliptical / rectangular / boolean apertures, TIR at the rim -- the interpreter kernel again
     lens = samples.FreeformPlate()

@@ -46,11 +46,46 @@ class NotEligible(Exception):
     """The surface group contains something the fused kernel does not implement."""
 
 
+# values of the scalar torch parameters of the lens being packed, read back in ONE device->host copy
+# (prefetch_tensor_scalars): id(tensor) -> (tensor, float). Without it every tensor-valued radius / conic / thickness is
+# its own synchronising read-back, and an optimisation step packs the lens several times.
+_TENSOR_VALUES: dict = {}
+
+
+def prefetch_tensor_scalars(surfaces) -> None:
+    """Collect every scalar CUDA tensor among the packer's geometry inputs and fetch their values with one copy."""
+    import torch
+    found = []
+    for s in surfaces:
+        g = getattr(s, "geometry", None)
+        if g is None:
+            continue
+        cs = getattr(g, "cs", None)
+        vals = [getattr(g, "radius", None), getattr(g, "k", None), getattr(s, "thickness", None)]
+        if cs is not None:
+            vals += [getattr(cs, nm, None) for nm in ("x", "y", "z", "rx", "ry", "rz")]
+        co = getattr(g, "coefficients", None)
+        if isinstance(co, (list, tuple)):
+            vals += list(co)
+        for v in vals:
+            if isinstance(v, torch.Tensor) and v.is_cuda and v.numel() == 1:
+                found.append(v)
+    _TENSOR_VALUES.clear()
+    if not found:
+        return
+    flat = torch.stack([v.detach().reshape(()).to(torch.float64) for v in found]).cpu().tolist()
+    for v, x in zip(found, flat):
+        _TENSOR_VALUES[id(v)] = (v, x)
+
+
 def _f(v) -> float:
     """Scalar value of a python number / numpy 0-d or 1-element array / torch tensor."""
     if type(v) is float or type(v) is int:     # the common case: no NumPy round trip
         return float(v)
     if hasattr(v, "detach"):
+        hit = _TENSOR_VALUES.get(id(v))
+        if hit is not None and hit[0] is v:
+            return hit[1]
         return float(v.detach().cpu().reshape(-1)[0].item())
     a = np.asarray(v, dtype=np.float64).reshape(-1)
     return float(a[0])
@@ -261,6 +296,14 @@ def check_surface(surf) -> None:
 def pack_surface_group(surfaces, wavelengths, record="all", skip: int = 0) -> PackedSystem:
     """Pack `surfaces[skip:]` for the distinct `wavelengths` (micrometres)."""
     wavelengths = [float(w) for w in wavelengths]
+    prefetch_tensor_scalars(surfaces)
+    try:
+        return _pack_surface_group(surfaces, wavelengths, record, skip)
+    finally:
+        _TENSOR_VALUES.clear()    # values are only valid for this pack: parameters change between optimiser steps
+
+
+def _pack_surface_group(surfaces, wavelengths, record, skip) -> PackedSystem:
     W = len(wavelengths)
     if not 1 <= W <= L.MAX_WAVELENGTHS:
         raise NotEligible(f"{W} distinct wavelengths (limit {L.MAX_WAVELENGTHS})")

@@ -304,16 +304,17 @@ class SurfaceGroup:
         self.reset()
         if wavelengths is None:
             wavelengths = torch.unique(rays.w).cpu().tolist()
-        packed = self.pack(wavelengths, skip)
         ins = rays.components()
-        if self._wants_grad(rays):
+        wants_grad = self._wants_grad(rays)
+        packed = None if wants_grad else self.pack(wavelengths, skip)   # the autograd path packs what it needs
+        if wants_grad:
             # one autograd node: forward kernel (records = checkpoints) + backward kernel (autograd.py)
             from .autograd import prescription_tensor, trace_differentiable
             def repack(mode):
                 pk = pack_surface_group(self._surfaces, wavelengths, record=mode, skip=skip)
+                guess = self.forced_nr_iters or self._packed_cache or {}
                 for k in pk.nr_rows():
-                    pk.ops[k * 16 + 6] = min(pk.layouts[k].max_iter,
-                                             (self._packed_cache or {}).get(pk.layouts[k].index, 2))
+                    pk.ops[k * 16 + 6] = min(pk.layouts[k].max_iter, guess.get(pk.layouts[k].index, 2))
                 return pk
             out = None
             if self.record in ("none", "last", None) and self.fast_math and self.blocked_checkpoints:
@@ -331,8 +332,7 @@ class SurfaceGroup:
                     except NotImplementedError:     # e.g. a surface that needs more than 3 Newton updates
                         out = None
             if out is None:
-                if self.record != "all":
-                    packed = repack("all")
+                packed = repack("all")
                 presc_t = prescription_tensor(packed, self._surfaces, ins[0].dtype, ins[0].device)
                 out, record, dir0 = trace_differentiable(packed, presc_t, ins, opd_in=rays.opd, fast=self.fast_math)
             res = TraceResult(out=out, record=record, dir0=dir0, nr_iters=packed.nr_iters(), status=0, launches=1)
