@@ -561,6 +561,19 @@ def bench_other_configs(torch, timed, args):
         "ms": ms, "ray_surfaces_per_s": 9 * n4 * S1 / (ms * 1e-3), "variables": len(pars),
         "api": "Optic.trace under autograd (one FusedTraceFn node per wavelength: 3 fields x 1M rays), torch RMS-spot "
                "merit, loss.backward(), Adam step"}
+    from optiland_pr_b200.autograd import _rms_merit_fused
+
+    def c4f():
+        opt.zero_grad()
+        loss = sum(_rms_merit_fused(lens4, fields4, w_, Px4, Py4) for w_ in wls4)
+        loss.backward()
+        opt.step()
+        return loss
+
+    ms = timed(c4f, max(2, args.steps // 2), 3)
+    out["c4_cooke_merit_adam_step_fused_spot_merit"] = {
+        "ms": ms, "ray_surfaces_per_s": 9 * n4 * S1 / (ms * 1e-3), "variables": len(pars),
+        "api": "the same step with spot.rms_spot_sq (spot-sum kernel forward, one dense gradient backward) as the merit"}
     # ---- C3, second half: refractive Zernike (fringe, 36 terms) + odd-asphere plate, tilts about three axes,
     # elliptical / rectangular / boolean apertures, TIR at the rim -- the interpreter kernel again
     lens = samples.FreeformPlate()

@@ -160,8 +160,8 @@ def trace_differentiable(packed: PackedSystem, presc: torch.Tensor, rays_in, opd
     """rays_in: 8 tensors (w may be None for a single wavelength). Returns (out, record, dir0).
     generic_adjoint=True forces the general backward kernel (csrc/trace_bwd.cuh) instead of the reduced-algebra one.
     blocked=True (packed with record="none", tolerance mode, plane / conic / even-asphere lens): the checkpoints are
-    tile-blocked (include/olrt.h, OLRT_FWD_CKPT_BLOCKED) -- 56 B per ray and surface, fetched by the backward with one
-    bulk copy per tile and surface -- and `record` comes back empty."""
+    tile-blocked (include/olrt.h, OLRT_FWD_CKPT_BLOCKED) -- 56 B per ray and surface, read by the backward at fixed
+    offsets from one pointer -- and `record` comes back empty."""
     x, y, z, Lc, M, N, inten, w = (list(rays_in) + [None])[:8]
     return FusedTraceFn.apply(presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast, generic_adjoint, blocked)
 
@@ -175,6 +175,20 @@ def _rms_merit(lens, fields, wavelength, Px, Py):
     y = rays.y.reshape(nf, -1)
     r2 = (x - x.mean(dim=1, keepdim=True)) ** 2 + (y - y.mean(dim=1, keepdim=True)) ** 2
     return r2.mean(dim=1).sum()
+
+
+def _rms_merit_fused(lens, fields, wavelength, Px, Py):
+    """The same merit with the spot reduction and its gradient in the library's own epilogue (spot.rms_spot_sq: two
+    passes of the spot-sum kernel forward, one dense gradient backward) instead of recorded torch elementwise ops."""
+    from .spot import rms_spot_sq
+    nf = len(fields)
+    rays = lens.trace([f[0] for f in fields], [f[1] for f in fields], wavelength, distribution=(Px, Py))
+    lt = getattr(lens.surface_group, "last_trace", None)
+    if lt is not None and lt.out is not None and lt.out[0].data_ptr() == rays.x.data_ptr():
+        out = lt.out          # the [8, N] output of this very trace (rays.x ... are its rows)
+    else:
+        out = torch.stack([rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd])
+    return rms_spot_sq(out, nf).sum()
 
 
 def smoke_backward() -> str:

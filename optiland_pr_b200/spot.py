@@ -52,6 +52,46 @@ def spot_stats(sums: torch.Tensor) -> dict:
                 rms=torch.sqrt(torch.clamp(var, min=0.0)), intensity=sums[:, 6])
 
 
+class _RmsSpotSq(torch.autograd.Function):
+    """mean((x - mean x)^2 + (y - mean y)^2) per group of a traced batch `out` [8, N] (field-major, equal groups), all
+    rays counted as RayOperand.rms_spot_size does (operand/ray.py:336-340). Forward: two passes of the spot-sum kernel
+    (centroid, then sums about it). Backward: d / d x_i = 2 (x_i - mean x) / n exactly (the centroid's own dependence
+    cancels) -- ONE dense [8, N] gradient with two filled rows instead of the ~30 elementwise kernels autograd records
+    for the same expression."""
+
+    @staticmethod
+    def forward(ctx, out, n_groups):
+        x, y, inten = out[0], out[1], out[6]
+        n = int(x.numel())
+        per = n // n_groups
+        if per * n_groups != n:
+            raise ValueError("rms_spot_sq needs equal groups")
+        st = spot_stats(spot_sums(x, y, inten, n_groups, per))   # sums about each group's first ray + that shift
+        cen = torch.stack([st["cx"], st["cy"]], dim=1).contiguous()
+        s2 = spot_sums(x, y, inten, n_groups, per, shift=cen)
+        cnt = s2[:, 0]
+        val = (s2[:, 3] + s2[:, 4]) / cnt - (s2[:, 1] / cnt) ** 2 - (s2[:, 2] / cnt) ** 2
+        ctx.save_for_backward(out, cen)
+        ctx.shape = (n_groups, per)
+        return val
+
+    @staticmethod
+    def backward(ctx, g):
+        out, cen = ctx.saved_tensors
+        ng, per = ctx.shape
+        G = torch.zeros_like(out)
+        scale = (g * (2.0 / per)).to(out.dtype).unsqueeze(1)
+        c = cen.to(out.dtype)
+        torch.mul(out[0].view(ng, per) - c[:, 0:1], scale, out=G[0].view(ng, per))
+        torch.mul(out[1].view(ng, per) - c[:, 1:2], scale, out=G[1].view(ng, per))
+        return G, None
+
+
+def rms_spot_sq(out: torch.Tensor, n_groups: int) -> torch.Tensor:
+    """Squared RMS spot radius per group, differentiable w.r.t. the traced batch `out` [8, N] (see _RmsSpotSq)."""
+    return _RmsSpotSq.apply(out, n_groups)
+
+
 def rms_spot_size(x, y, intensity, n_groups=1, rays_per_group=None, valid_only=False):
     """sqrt(mean((x - mean x)^2 + (y - mean y)^2)) per group (ray.py:336-340 when valid_only is
     False: vignetted and NaN rays are included, exactly as the reference's operand does)."""

@@ -112,3 +112,28 @@ def test_adam_reduces_rms_spot_merit_through_the_fused_kernels():
         opt.step()
         history.append(float(loss))
     assert history[-1] < 0.5 * history[0], history
+
+
+def test_fused_spot_merit_matches_the_torch_expression():
+    """spot.rms_spot_sq (spot-sum kernel forward, analytic dense gradient backward) against the recorded torch
+    expression of the same merit: value and d / d(radius, conic) through the public autograd path."""
+    from optiland_pr_b200.autograd import _rms_merit, _rms_merit_fused
+    be.set_precision("float64")
+    rng = np.random.default_rng(2)
+    rr, th = np.sqrt(rng.uniform(size=5000)), rng.uniform(0, 2 * np.pi, 5000)
+    Px, Py = rr * np.cos(th), rr * np.sin(th)
+    fields = [(0.0, 0.0), (0.0, 0.7), (0.0, 1.0)]
+    got = []
+    for merit in (_rms_merit, _rms_merit_fused):
+        lens = samples.CookeTriplet()
+        lens.surface_group.record = "none"
+        r1 = torch.tensor(22.01359, dtype=torch.float64, device="cuda", requires_grad=True)
+        k3 = torch.tensor(0.05, dtype=torch.float64, device="cuda", requires_grad=True)
+        lens.set_radius(r1, 1)
+        lens.set_conic(k3, 3)
+        loss = merit(lens, fields, 0.55, Px, Py)
+        loss.backward()
+        got.append((float(loss.detach()), float(r1.grad), float(k3.grad)))
+    (l0, a0, b0), (l1, a1, b1) = got
+    assert abs(l1 - l0) <= 1e-10 * abs(l0), (l0, l1)
+    assert abs(a1 - a0) <= 1e-8 * abs(a0) and abs(b1 - b0) <= 1e-8 * abs(b0), (got,)
