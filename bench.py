@@ -574,6 +574,23 @@ def bench_other_configs(torch, timed, args):
     out["c4_cooke_merit_adam_step_fused_spot_merit"] = {
         "ms": ms, "ray_surfaces_per_s": 9 * n4 * S1 / (ms * 1e-3), "variables": len(pars),
         "api": "the same step with spot.rms_spot_sq (spot-sum kernel forward, one dense gradient backward) as the merit"}
+    try:   # all 9 (wavelength, field) pairs as ONE autograd node (per-ray wavelengths)
+        from optiland_pr_b200.autograd import _rms_merit_all
+
+        def c4a():
+            opt.zero_grad()
+            loss = _rms_merit_all(lens4, fields4, wls4, Px4, Py4)
+            loss.backward()
+            opt.step()
+            return loss
+
+        ms = timed(c4a, max(2, args.steps // 2), 3)
+        out["c4_cooke_merit_adam_step_one_node"] = {
+            "ms": ms, "ray_surfaces_per_s": 9 * n4 * S1 / (ms * 1e-3), "variables": len(pars),
+            "api": "generate_rays for all 9 pairs with per-ray wavelengths + SurfaceGroup.trace (one FusedTraceFn node) "
+                   "+ spot.rms_spot_sq + loss.backward() + Adam step"}
+    except Exception as e:   # an extra leg must never take the bench line down
+        out["c4_cooke_merit_adam_step_one_node"] = {"error": repr(e)[:200]}
     # ---- C3, second half: refractive Zernike (fringe, 36 terms) + odd-asphere plate, tilts about three axes,
     # elliptical / rectangular / boolean apertures, TIR at the rim -- the interpreter kernel again
     lens = samples.FreeformPlate()

@@ -191,6 +191,28 @@ def _rms_merit_fused(lens, fields, wavelength, Px, Py):
     return rms_spot_sq(out, nf).sum()
 
 
+def _rms_merit_all(lens, fields, wavelengths, Px, Py):
+    """sum over wavelengths x fields of rms_spot_size^2 from ONE traced batch: the rays of every (wavelength, field)
+    pair carry their wavelength (the kernels index the media per ray), so an optimisation step is one FusedTraceFn
+    node -- one pack, one launch pair, one backward -- instead of one per wavelength. Px, Py: device tensors [P]."""
+    from . import backend as be
+    from .spot import rms_spot_sq
+    nf, nw, npup = len(fields), len(wavelengths), int(Px.numel())
+    dev = Px.device
+    Hx = torch.tensor([f[0] for f in fields], dtype=torch.float64, device=dev).repeat_interleave(npup).repeat(nw)
+    Hy = torch.tensor([f[1] for f in fields], dtype=torch.float64, device=dev).repeat_interleave(npup).repeat(nw)
+    wl = torch.tensor([float(w) for w in wavelengths], dtype=torch.float64, device=dev).repeat_interleave(nf * npup)
+    rays = lens.generate_rays(Hx, Hy, Px.repeat(nf * nw), Py.repeat(nf * nw), wl)
+    sg = lens.surface_group
+    sg.trace(rays, wavelengths=[float(w) for w in wavelengths])
+    lt = sg.last_trace
+    if lt is not None and lt.out is not None and lt.out[0].data_ptr() == rays.x.data_ptr():
+        out = lt.out
+    else:
+        out = torch.stack([rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd])
+    return rms_spot_sq(out, nw * nf).sum()
+
+
 def smoke_backward() -> str:
     """forward + backward through the public API on the Cooke triplet: finite, non-zero gradients that agree
     with a central finite difference of the merit."""

@@ -137,3 +137,30 @@ def test_fused_spot_merit_matches_the_torch_expression():
     (l0, a0, b0), (l1, a1, b1) = got
     assert abs(l1 - l0) <= 1e-10 * abs(l0), (l0, l1)
     assert abs(a1 - a0) <= 1e-8 * abs(a0) and abs(b1 - b0) <= 1e-8 * abs(b0), (got,)
+
+
+def test_one_node_merit_over_all_wavelengths_matches_the_per_wavelength_sum():
+    """_rms_merit_all (9 (wavelength, field) pairs, per-ray wavelengths, ONE FusedTraceFn node) against the sum of the
+    per-wavelength merits: value and gradients."""
+    from optiland_pr_b200.autograd import _rms_merit_all, _rms_merit_fused
+    be.set_precision("float64")
+    rng = np.random.default_rng(6)
+    rr, th = np.sqrt(rng.uniform(size=2000)), rng.uniform(0, 2 * np.pi, 2000)
+    Px = torch.from_numpy(rr * np.cos(th)).cuda()
+    Py = torch.from_numpy(rr * np.sin(th)).cuda()
+    got = []
+    for one_node in (False, True):
+        lens = samples.CookeTriplet()
+        lens.surface_group.record = "none"
+        fields, wls = lens.get_field_coords(), list(lens.wavelengths)
+        r1 = torch.tensor(22.01359, dtype=torch.float64, device="cuda", requires_grad=True)
+        r6 = torch.tensor(-18.39533, dtype=torch.float64, device="cuda", requires_grad=True)
+        lens.set_radius(r1, 1)
+        lens.set_radius(r6, 6)
+        loss = (_rms_merit_all(lens, fields, wls, Px, Py) if one_node
+                else sum(_rms_merit_fused(lens, fields, w, Px, Py) for w in wls))
+        loss.backward()
+        got.append((float(loss.detach()), float(r1.grad), float(r6.grad)))
+    (l0, a0, b0), (l1, a1, b1) = got
+    assert abs(l1 - l0) <= 1e-10 * abs(l0), got
+    assert abs(a1 - a0) <= 1e-8 * abs(a0) and abs(b1 - b0) <= 1e-8 * abs(b0), got
