@@ -173,6 +173,21 @@ int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const int32_t* o
                        unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags,
                        void* stream);
 
+/* Forward trace that ALLOCATES NOTHING. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it). Same arguments, kernels and results as olrt_trace_fwd_f64, minus `fixup`: the re-trace list lives in a
+ * file-scope `static __device__ __align__(256)` array of 1 + OLRT_NOALLOC_MAX_RAYS uint32 inside the library (4 MiB
+ * per GPU that loads libolrt.so, held until the process exits; its device address is taken once per device with
+ * cudaGetSymbolAddress). n_rays > OLRT_NOALLOC_MAX_RAYS returns OLRT_E_LIMIT. The call issues no cudaMalloc / cudaFree
+ * or allocating library routine: a cudaMemsetAsync of the list's counter and the kernel launches, all on `stream`.
+ * EVERY call on a GPU shares the one array (its counter is cleared per call, older entries are never read): calls
+ * that overlap on the same GPU (different streams, different host threads) race -- serialise them.              */
+#define OLRT_NOALLOC_MAX_RAYS 1048576
+int olrt_trace_fwd_noalloc_f64(const olrt_sys* sys /*host*/, const double* presc, const int32_t* ops,
+                               int64_t n_rays, const double* const in[8], const double* opd_in,
+                               double* const out[8], double* record, double* dir0,
+                               unsigned long long* nr_resid, uint32_t* status, int flags, void* stream);
+
 /* Backward (adjoint) of the forward trace: what torch autograd computes through Surface.trace on the
  * reference torch backend (optimization/optimizer/torch/base.py:95-154 -> loss.backward()).
  * Checkpoints = the forward's records: the forward must have recorded EVERY surface (n_record ==

@@ -20,6 +20,7 @@ OPS_STRIDE = 16
 RESID_STRIDE = MAX_NR_ITERS + 1
 SPOT_SUMS = 10
 GROUP_RESID = 8
+NOALLOC_MAX_RAYS = 1 << 20   # olrt_trace_fwd_noalloc_f64: rays per call (its re-trace list is a static device array)
 FRAME_REALS = 9
 GEOM_REALS = 4
 
@@ -89,7 +90,7 @@ PtrArray8 = C.c_void_p * 8
 # every symbol include/olrt.h declares (tests/test_abi.py checks the header against this list)
 EXPORTS = [
     "olrt_version", "olrt_build_info",
-    "olrt_trace_fwd_f64", "olrt_trace_fwd_f32",
+    "olrt_trace_fwd_f64", "olrt_trace_fwd_f32", "olrt_trace_fwd_noalloc_f64",
     "olrt_trace_bwd_f64", "olrt_trace_bwd_f32",
     "olrt_spot_sums_f64", "olrt_spot_sums_f32",
     "olrt_fma_peak_f64", "olrt_fma_peak_f32",
@@ -139,6 +140,8 @@ def load():
         f.argtypes = [v, v, v, C.c_int64, C.c_int64, C.c_int32, v, C.c_int, v, v]
         f = getattr(lib, f"olrt_fma_peak_{suf}")
         f.restype, f.argtypes = C.c_int, [v, C.c_int64, C.c_int, C.c_int, v]
+    lib.olrt_trace_fwd_noalloc_f64.restype = C.c_int   # olrt_trace_fwd_f64 without the `fixup` argument
+    lib.olrt_trace_fwd_noalloc_f64.argtypes = fwd_args[:11] + fwd_args[12:]
     for suf in ("f64", "f32"):
         f = getattr(lib, f"olrt_generate_rays_{suf}")
         f.restype = C.c_int

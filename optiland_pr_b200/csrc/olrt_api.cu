@@ -1,6 +1,7 @@
 // olrt_api.cu -- the extern "C" boundary (include/olrt.h), the spot epilogue and the FMA-peak probe.
 #include <cuda_runtime.h>
 #include <math.h>
+#include <mutex>
 #include "olrt_internal.h"
 
 // ---------------------------------------------------------------------------------------------
@@ -68,6 +69,59 @@ extern "C" int olrt_trace_fwd_f32(const olrt_sys* sys, const float* presc, const
   if (sys->n_record > 0 && !record) return OLRT_E_ARG;
   return olrt_fast::fwd_f32(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags,
                             (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Forward trace that allocates nothing (include/olrt.h: olrt_trace_fwd_noalloc_f64). The re-trace list the caller of
+// olrt_trace_fwd_f64 passes as `fixup` lives here, in the library's own device image: one copy per GPU that loads
+// libolrt.so, held until the process exits, shared by every call (calls that overlap on one GPU race on it).
+// In HOST code `g_noalloc_fixup` is only a stand-in for the symbol -- the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) uint32_t g_noalloc_fixup[1 + OLRT_NOALLOC_MAX_RAYS];
+
+#define OLRT_NOALLOC_MAX_DEVICES 64
+static uint32_t* g_noalloc_addr[OLRT_NOALLOC_MAX_DEVICES];  // per-device address of g_noalloc_fixup, 0 = not asked yet
+static std::mutex g_noalloc_mutex;
+
+static int noalloc_fixup_address(uint32_t** ptr) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return OLRT_E_LAUNCH;
+  if (dev < 0 || dev >= OLRT_NOALLOC_MAX_DEVICES) return OLRT_E_LIMIT;
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_addr[dev] == nullptr) {
+    uint32_t* p = nullptr;
+    if (cudaGetSymbolAddress((void**)&p, g_noalloc_fixup) != cudaSuccess || p == nullptr) {
+      (void)cudaGetLastError();
+      return OLRT_E_LAUNCH;
+    }
+    g_noalloc_addr[dev] = p;
+  }
+  *ptr = g_noalloc_addr[dev];
+  return OLRT_OK;
+}
+
+extern "C" int olrt_trace_fwd_noalloc_f64(const olrt_sys* sys, const double* presc, const int32_t* ops,
+                                          int64_t n_rays, const double* const in[8], const double* opd_in,
+                                          double* const out[8], double* record, double* dir0,
+                                          unsigned long long* nr_resid, uint32_t* status, int flags, void* stream) {
+  if (n_rays > OLRT_NOALLOC_MAX_RAYS) return OLRT_E_LIMIT;  // the list holds one entry per ray
+  int rc = check_sys(sys, presc, ops, n_rays);
+  if (rc) return rc;
+  if (n_rays == 0) return OLRT_OK;
+  rc = check_rays<double>(sys, in, out);
+  if (rc) return rc;
+  if (sys->n_record > 0 && !record) return OLRT_E_ARG;
+  if ((flags & OLRT_FWD_CKPT_BLOCKED) && !(flags & OLRT_FWD_FAST)) return OLRT_E_UNSUPPORTED;
+  uint32_t* fixup = nullptr;
+  rc = noalloc_fixup_address(&fixup);
+  if (rc) return rc;
+  // the launcher clears the list's counter (word 0) on `stream` before the main kernel; entries past the counter
+  // are never read, so the previous call's contents need no other clearing
+  cudaStream_t st = (cudaStream_t)stream;
+  if (flags & OLRT_FWD_FAST)
+    return olrt_fast::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags, st);
+  return olrt_strict::fwd_f64(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, 0, st);
 }
 
 template <typename R>
