@@ -6,9 +6,12 @@ are imported at module scope on the hot path's import chain
 (optiland/backend/numpy_backend.py:12, optiland/optic/optic.py:37-42) but never
 called on it, so permissive stub modules are enough.
 
-Used only by oracle/make_golden.py and by CPU tests that pin the oracle against
-the live reference. /root/reference does not exist on the GPU box: nothing in
-the product package, the gpu tests, smoke() or bench.py imports this file.
+Used by oracle/make_golden*.py, by the CPU tests that pin the oracle against the live
+reference, by the drop-in tests (tests/test_*dropin*.py: the fused trace under the
+reference's own classes) and by bench.py's reference baselines. /root/reference does not
+exist on the GPU box: there the verbatim copy under oracle/_ref/ (oracle/fetch_ref.py, made
+by __graft_entry__.build(), git-ignored, shipped with the working tree) is imported
+instead. The product package never imports this file.
 """
 from __future__ import annotations
 
@@ -17,7 +20,19 @@ import os
 import sys
 import types
 
-REFERENCE_PATH = os.environ.get("OLRT_REFERENCE_PATH", "/root/reference")
+_COPY = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def _pick_reference_path() -> str:
+    env = os.environ.get("OLRT_REFERENCE_PATH")
+    if env:
+        return env
+    if os.path.isdir("/root/reference/optiland"):
+        return "/root/reference"
+    return _COPY
+
+
+REFERENCE_PATH = _pick_reference_path()
 
 _STUBS = [
     "matplotlib", "matplotlib.pyplot", "matplotlib.path", "matplotlib.axes",
