@@ -14,8 +14,10 @@ call `Optic.trace(Hx, Hy, wl, distribution=(Px, Py))` with the pupil grid in pin
 all inside the timed region). Multi-GPU: rays are independent, every rank traces its own batch
 (weak scaling); the only collective is an NCCL all-reduce of the [3][10] spot sums.
 
-Only the `cpu_baseline` leg and `--impl reference` execute oracle/ (the NumPy restatement of the
-reference; the Python reference itself cannot travel to the GPU box).
+Only the `cpu_baseline` / `extras.reference_torch_eager_cuda` legs and `--impl reference` execute oracle/: they run
+the UNMODIFIED reference (oracle/ref_bench.py; on the GPU box the verbatim copy under oracle/_ref that
+__graft_entry__.build() makes) -- NumPy backend on the host cores, and its torch-eager path on the same GPU -- and the
+NumPy port (oracle/cpu_bench.py) as a second, faster CPU figure.
 """
 from __future__ import annotations
 
@@ -39,6 +41,9 @@ FIELDS = [(0.0, 0.0), (0.0, 10.0 / 14.0), (0.0, 1.0)]
 WAVELENGTH = 0.5876
 METRIC = "ray-surfaces/sec fwd (fp64, even-asphere double Gauss, 3 fields x 16M rays) on B200"
 UNIT = "ray-surfaces/s"
+# the SAME string in both arms (the reference arm states its bounded sub-sample under config.sample only)
+WORKLOAD = ("even-asphere double Gauss (12 intersected surfaces, 4 Newton-Raphson even aspheres), 3 fields x 16777216 "
+            "random pupil rays per GPU, primary wavelength, ray launch + fwd trace + final ray state + RMS spot")
 
 
 def parse():
@@ -114,21 +119,39 @@ def cpu_arm(steps: int, warmup: int, budget_s: float = 20.0):
                                     steps=steps, warmup=warmup, budget_s=budget_s)
 
 
+def reference_cpu(steps: int, warmup: int, budget_all: float, budget_single: float):
+    """The UNMODIFIED reference on the host cores (oracle/ref_bench.py): every core (one worker process per core, each
+    tracing its own chunk through the reference's Optic.trace) and one process as shipped."""
+    from oracle import ref_bench
+    if not ref_bench.available():
+        return None
+    r_all = ref_bench.run_subprocess(["numpy", "--mode", "all", "--steps", steps, "--warmup", warmup,
+                                      "--budget", budget_all])
+    r_one = ref_bench.run_subprocess(["numpy", "--mode", "single", "--steps", 1, "--budget", budget_single])
+    return {"value": r_all["value"], "unit": UNIT, "cores": r_all["cores"], "kind": "reference",
+            "sample": r_all["sample"], "ms_per_step": r_all["ms_per_step"], "rms_spot_mm": r_all["rms"],
+            "single_process": {"value": r_one["value"], "unit": UNIT, "cores": 1, "sample": r_one["sample"],
+                               "rms_spot_mm": r_one["rms"]}}
+
+
 def reference_main(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = max(1, min(args.steps, 5))
-    r = cpu_arm(steps, min(args.warmup, 1), budget_s=30.0)
+    steps = max(1, min(args.steps, 3))
+    warm = min(args.warmup, 1)
+    r = reference_cpu(steps, warm, budget_all=40.0, budget_single=15.0)
+    if r is None:   # no reference on this box (oracle/_ref not built): the NumPy port of it
+        p = cpu_arm(steps, warm, budget_s=30.0)
+        r = {"value": p["value"], "unit": UNIT, "cores": p["cores"], "kind": "port", "sample": p["sample"],
+             "ms_per_step": p["ms_per_step"]}
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
-        "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": r["ms_per_step"],
+        "steps": steps, "warmup": warm, "ms_per_step": r["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": "even-asphere double Gauss, 3 fields x 16M random pupil rays, fwd trace + RMS spot",
-                   "sample": r["sample"]},
-        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-                         "sample": r["sample"]},
+        "config": {"workload": WORKLOAD, "sample": r["sample"]},
+        "cpu_baseline": {k: v for k, v in r.items() if k != "ms_per_step"},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -406,8 +429,7 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "even-asphere double Gauss (12 intersected surfaces, 4 Newton-Raphson even aspheres), "
-                               f"{nf} fields x {npf} random pupil rays per GPU, primary wavelength, ray launch + fwd trace + final ray state + RMS spot",
+        "config": {"workload": WORKLOAD if npf == RAYS_PER_FIELD else WORKLOAD.replace(str(RAYS_PER_FIELD), str(npf)),
                    "rays_per_gpu": n, "surfaces": S_eff, "precision": "float64, tolerance mode (<= 1e-10 relative to the reference, identical masks; "
                                                                   "the bit-identical strict mode is timed in roofline.strict_mode)",
                    "l2": "inputs (268 MB pupil grid) and outputs (3.2 GB) per step exceed the 126 MB L2; no flush needed",
@@ -425,12 +447,44 @@ def main():
         "extras": extras,
     }
     if not args.no_cpu_baseline and world == 1:
-        r = cpu_arm(1, 0, budget_s=15.0)
-        line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-                                "sample": r["sample"], "rms_spot_mm": r.get("rms")}
+        r = cpu_arm(1, 0, budget_s=12.0)
+        port = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"],
+                "rms_spot_mm": r.get("rms")}
+        ref = None
+        try:
+            ref = reference_cpu(1, 0, budget_all=15.0, budget_single=12.0)
+        except Exception as e:   # a baseline leg must never take the bench line down
+            port["reference_error"] = repr(e)[:300]
+        if ref is not None:
+            line["cpu_baseline"] = ref
+            line["cpu_baseline"]["port_all_cores"] = port     # the NumPy restatement (oracle/trace_np.py), ~6x faster
+        else:
+            line["cpu_baseline"] = port
+        if args.extras:
+            line["extras"]["reference_torch_eager_cuda"] = reference_torch_eager()
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def reference_torch_eager():
+    """The reference's own torch backend on this GPU (README.md:120 of the reference): C1 and C2,
+    fp64 and fp32, 1 M rays per Optic.trace. Runs after this process has released its device memory."""
+    from oracle import ref_bench
+    out = {}
+    if not ref_bench.available():
+        return {"unavailable": "no reference on this box (oracle/_ref not built)"}
+    for lens_name in ("c2", "c1"):
+        for prec in ("float64", "float32"):
+            key = f"{lens_name}_{prec}"
+            try:
+                r = ref_bench.run_subprocess(["torch", "--lens", lens_name, "--precision", prec, "--rays", 1_000_000,
+                                              "--steps", 1, "--warmup", 1], timeout=600)
+                out[key] = {"ray_surfaces_per_s": r["value"], "ms_per_step": r["ms_per_step"], "sample": r["sample"],
+                            "rms_spot_mm": r["rms"]}
+            except Exception as e:
+                out[key] = {"error": repr(e)[:300]}
+    return out
 
 
 def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64_peak):
