@@ -207,12 +207,18 @@ int olrt_trace_fwd_noalloc_f64(const olrt_sys* sys /*host*/, const double* presc
 /* Tile-blocked checkpoints (differentiable trace without user-visible records): with OLRT_FWD_CKPT_BLOCKED the
  * forward's `record` argument is a buffer of ceil(n_rays / 256) * n_surfaces * 7 * 256 reals laid out
  * [tile][surface][x y z L M N intensity][256]: the state after every surface, 56 B per ray and surface, one
- * contiguous 14 KB block per (256-ray tile, surface). olrt_sys.n_record must be 0 (no [S][8][N] records in the same
+ * contiguous 14 KB block per (256-ray tile, surface). (Leaving the planes out and recomputing their exit states in
+ * the backward was measured: -224 B per ray of traffic but +160 instructions per ray in kernels that are
+ * issue-bound, not bandwidth-bound: slower. DESIGN.md section 5.)
+ * olrt_sys.n_record must be 0 (no [S][8][N] records in the same
  * launch); lenses of planes / conics / even aspheres in tolerance mode only (OLRT_E_UNSUPPORTED otherwise).
  * With OLRT_BWD_CKPT_BLOCKED the backward's `record` argument is that buffer (grecord must be NULL): a thread's
- * seven values of a surface sit at fixed offsets from one pointer (cp.async copies without address arithmetic). */
+ * seven values of a surface sit at fixed offsets from one pointer (cp.async copies without address arithmetic).
+ * OLRT_BWD_NO_FRAME_XY: the caller does not want d loss / d (frame x, frame y) (no decenter is a variable): those two
+ * columns of gpresc stay zero and the reduced-algebra kernel skips their accumulation (ignored by the general one). */
 #define OLRT_FWD_CKPT_BLOCKED 4
 #define OLRT_BWD_CKPT_BLOCKED 2
+#define OLRT_BWD_NO_FRAME_XY 4
 #define OLRT_CKPT_TILE 256
 int olrt_trace_bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, int64_t n_rays,
                        const double* const in[8], const double* record, const double* const gout[8],

@@ -50,6 +50,8 @@ def prescription_tensor(packed: PackedSystem, surfaces, dtype, device) -> torch.
     """Flat prescription [stride] on `device`, differentiable w.r.t. the live parameter tensors."""
     base = torch.from_numpy(np.ascontiguousarray(packed.presc[0])).to(device=device, dtype=dtype)
     live = _live_entries(packed, surfaces)
+    # offsets that can receive a gradient: the backward skips the frame x / y columns when none of them is live
+    packed.live_offsets = frozenset(o for o, t in live if t.requires_grad)
     if not live:
         return base
     idx = torch.tensor([o for o, _ in live], dtype=torch.int64, device=device)
@@ -81,6 +83,9 @@ class FusedTraceFn(torch.autograd.Function):
             raise NotImplementedError("blocked checkpoints: a surface took more than 3 Newton updates")
         ctx.blocked = bool(blocked)
         ctx.ckpt = res.ckpt
+        live = getattr(packed, "live_offsets", None)     # set by prescription_tensor; None: a caller's own leaf row
+        ctx.no_frame_xy = live is not None and not any(o in live for lay in packed.layouts
+                                                       for o in (lay.frames, lay.frames + 1))
         ctx.set_materialize_grads(False)
         ctx.packed = packed
         ctx.generic_adjoint = bool(generic_adjoint)
@@ -139,6 +144,8 @@ class FusedTraceFn(torch.autograd.Function):
                 raise NotImplementedError("blocked checkpoints: a surface took more than 3 Newton updates; trace "
                                           "with record='all'")
             flags = L.BWD_CKPT_BLOCKED
+        if ctx.no_frame_xy:
+            flags |= L.BWD_NO_FRAME_XY
         with torch.cuda.device(device):
             rc = fn(C.byref(sys_), presc.data_ptr(), ops_d.data_ptr(), n, in_arr, record.data_ptr(), gout_arr,
                     _ptr(grecord), gin_arr, gpresc.data_ptr(), status.data_ptr(), flags,
@@ -242,12 +249,19 @@ def smoke_backward() -> str:
 
 
 def bench_backward(lens, packed, ins64, timed, args, fp64_peak) -> dict:
-    """fwd (all surfaces recorded = checkpoints) + bwd on the bench batch: the record buffer for 50M rays x 12 surfaces
-    x 8 doubles is 38.7 GB and fits the 180 GB HBM. Two legs: gradients w.r.t. the whole prescription AND the six
-    ray components (what a caller differentiating the launch needs), and w.r.t. the prescription alone (BASELINE C4:
-    curvature / thickness / conic / asphere variables; no per-ray gradient arrays are written)."""
-    from . import flops
+    """fwd + bwd on the bench batch (C2 lens, 50 M rays) and on the Cooke triplet (C1 / C4 lens, 9 x 1 M rays), kernel
+    level: `trace_differentiable` = olrt_trace_fwd_f64 writing checkpoints + olrt_trace_bwd_f64, driven by a fixed
+    d loss / d out. Legs: gradients w.r.t. the whole prescription AND the six ray components with [S][8][N] records
+    (what a caller that also reads per-surface arrays gets); the same with tile-blocked checkpoints; and the BASELINE
+    C4 configuration -- curvature / thickness / conic / asphere variables only: blocked checkpoints, no per-ray
+    gradient arrays, no frame x / y partials (OLRT_BWD_NO_FRAME_XY). Forward + backward counts as 3x the forward's
+    algorithmic flops."""
+    from . import flops, samples
     from .prescription import pack_surface_group
+
+    def no_decenter(pk_):   # what prescription_tensor records when no cs.x / cs.y is a variable
+        pk_.live_offsets = frozenset(o for lay in pk_.layouts for o in range(lay.frames + 2, lay.aper))
+        return pk_
 
     n = int(ins64[0].numel())
     S = packed.n_surfaces
@@ -262,25 +276,76 @@ def bench_backward(lens, packed, ins64, timed, args, fp64_peak) -> dict:
     out = {}
     pkb = pack_surface_group(lens.surface_group.surfaces, packed.wavelengths, record="none")
     pkb.set_nr_iters(packed.nr_iters())
-    for name, ray_grads, blocked in (("fp64_fwd_bwd", True, False), ("fp64_fwd_bwd_prescription_only", False, False),
-                                     ("fp64_fwd_bwd_blocked_checkpoints", True, True)):
+    pkc = no_decenter(pack_surface_group(lens.surface_group.surfaces, packed.wavelengths, record="none"))
+    pkc.set_nr_iters(packed.nr_iters())
+    n_ck = S
+    legs = (("fp64_fwd_bwd", pk, True, False), ("fp64_fwd_bwd_blocked_checkpoints", pkb, True, True),
+            ("fp64_fwd_bwd_prescription_only", pkc, False, True))
+    for name, pk_, ray_grads, blocked in legs:
         rays = [t.detach().requires_grad_(ray_grads and q < 6) if t is not None else None
                 for q, t in enumerate(ins64)]
 
         def step():
             presc.grad = None
-            o, record, _ = trace_differentiable(pkb if blocked else pk, presc, rays, fast=True, blocked=blocked)
+            o, record, _ = trace_differentiable(pk_, presc, rays, fast=True, blocked=blocked)
             o.backward(gout_w)
 
         ms = timed(step, max(2, args.steps // 2), 3)
         out[name] = {"ray_surfaces_per_s": n * S / (ms * 1e-3), "ms": ms,
                      "frac_fp64_fma_peak": fl * n / (ms * 1e-3) / 1e12 / fp64_peak,
-                     "flops_per_ray_fwd_bwd": fl, "checkpoint_bytes_per_ray": (56 if blocked else 64) * S,
-                     "checkpoints": "tile-blocked [tile][surface][7][256] (what Optic.trace uses when no per-surface "
-                                    "records are asked for)" if blocked else "[S][8][N] records",
-                     "gradients": "prescription (frames, radii, conics, asphere coefficients)"
-                                  + (" + x y z L M N of every ray" if ray_grads else ""),
-                     "kernels": "trace_fx_kernel<double> recording every surface (64 B x S per ray, the "
-                                "checkpoints; the final state aliases the last record) + trace_bx_kernel<double> "
-                                "(reduced-algebra adjoint, reads 56 B per surface per ray)"}
+                     "flops_per_ray_fwd_bwd": fl, "checkpoint_bytes_per_ray": 56 * n_ck if blocked else 64 * S,
+                     "checkpoints": "tile-blocked [tile][surface][7][256]" if blocked else "[S][8][N] records",
+                     "gradients": "prescription (frame z, radii, conics, asphere coefficients)" if not ray_grads else
+                                  "prescription (frames, radii, conics, asphere coefficients) + x y z L M N of every ray",
+                     "kernels": "trace_fx_kernel<double> writing the checkpoints + trace_bx_kernel<double> "
+                                "(reduced-algebra adjoint)"}
+    del gout_w, rays
+    torch.cuda.empty_cache()
+    # ---- Cooke triplet (north star: "the fused fp64 forward+backward trace on the Cooke triplet and ..."): 3 fields x
+    # 3 wavelengths x 1 M rays in one batch with per-ray wavelengths, prescription gradients only
+    cooke = samples.CookeTriplet()
+    wls = [float(w) for w in cooke.wavelengths]
+    fields = cooke.get_field_coords()
+    n1 = 1_000_000
+    rng = np.random.default_rng(0)
+    r_, th = rng.uniform(size=n1), rng.uniform(0, 2 * np.pi, size=n1)
+    Px = torch.from_numpy(np.sqrt(r_) * np.cos(th)).to(dev)
+    Py = torch.from_numpy(np.sqrt(r_) * np.sin(th)).to(dev)
+    nf, nw = len(fields), len(wls)
+    Hx = torch.tensor([f[0] for f in fields], dtype=torch.float64, device=dev).repeat_interleave(n1).repeat(nw)
+    Hy = torch.tensor([f[1] for f in fields], dtype=torch.float64, device=dev).repeat_interleave(n1).repeat(nw)
+    wl = torch.tensor(wls, dtype=torch.float64, device=dev).repeat_interleave(nf * n1)
+    crays = cooke.generate_rays(Hx, Hy, Px.repeat(nf * nw), Py.repeat(nf * nw), wl)
+    cins = [t.detach() for t in crays.components()]
+    nC = int(cins[0].numel())
+    pkk = no_decenter(pack_surface_group(cooke.surface_group.surfaces, wls, record="none"))
+    Sc = pkk.n_surfaces
+    cpresc = torch.tensor(pkk.presc[0], dtype=torch.float64, device=dev, requires_grad=True)
+    gw = torch.zeros((8, nC), dtype=torch.float64, device=dev)
+    gw[0] = 1.0
+    gw[1] = 0.5
+    flc = 3.0 * flops.flops_per_ray(pkk)
+
+    def cstep():
+        cpresc.grad = None
+        o, _, _ = trace_differentiable(pkk, cpresc, cins, fast=True, blocked=True)
+        o.backward(gw)
+
+    ms = timed(cstep, max(3, args.steps), 3)
+    n_ckc = Sc
+    out["fp64_fwd_bwd_cooke"] = {
+        "ray_surfaces_per_s": nC * Sc / (ms * 1e-3), "ms": ms, "rays": nC,
+        "frac_fp64_fma_peak": flc * nC / (ms * 1e-3) / 1e12 / fp64_peak, "flops_per_ray_fwd_bwd": flc,
+        "checkpoint_bytes_per_ray": 56 * n_ckc,
+        "workload": "Cooke triplet, 3 fields x 3 wavelengths x 1 M random pupil rays (per-ray wavelengths), "
+                    "prescription gradients (frame z, radii, conics), blocked checkpoints"}
+
+    def cfwd():
+        fused_trace(pkk, cins, fast=True, verify_nr=False, check_status=False, out=gw)
+
+    ms = timed(cfwd, max(3, args.steps), 3)
+    out["fp64_fwd_cooke"] = {"ray_surfaces_per_s": nC * Sc / (ms * 1e-3), "ms": ms, "rays": nC,
+                             "frac_fp64_fma_peak": flc / 3.0 * nC / (ms * 1e-3) / 1e12 / fp64_peak,
+                             "flops_per_ray": flc / 3.0,
+                             "workload": "the same 9 M rays, forward only (ray arrays in, final state out)"}
     return out

@@ -49,7 +49,7 @@ __device__ __forceinline__ R bx_intensity(R& gi, R ei, R irec, R t, R r2, const 
     const bool inside = !(kind & FX_APER) || ((r2 <= sf.rmax2) & (r2 >= sf.rmin2));
     if (!inside) gi = R(0);
     else if (md.nalpha != R(0)) {
-      const R E = r_exp(md.nalpha * t);
+      const R E = fx_exp(md.nalpha * t);
       gt = gi * ei * E * md.nalpha;
       gi = gi * E;
     }
@@ -368,6 +368,34 @@ __device__ __forceinline__ void bx_cp_async(unsigned dst, const R* src) {
   else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
 }
 
+// the seven components of one checkpoint, STRIDE bytes apart on both sides (tile-blocked checkpoints: 256 reals):
+// one asm block with immediate offsets -- no per-copy address arithmetic
+template <typename R, int STRIDE>
+__device__ __forceinline__ void bx_cp_async7(unsigned dst, const R* src) {
+  if (sizeof(R) == 8)
+    asm volatile(
+        "cp.async.ca.shared.global [%0], [%1], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%2], [%1+%2], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%3], [%1+%3], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%4], [%1+%4], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%5], [%1+%5], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%6], [%1+%6], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%7], [%1+%7], 8;" ::"r"(dst), "l"(src), "n"(STRIDE), "n"(2 * STRIDE),
+        "n"(3 * STRIDE), "n"(4 * STRIDE), "n"(5 * STRIDE), "n"(6 * STRIDE)
+        : "memory");
+  else
+    asm volatile(
+        "cp.async.ca.shared.global [%0], [%1], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%2], [%1+%2], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%3], [%1+%3], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%4], [%1+%4], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%5], [%1+%5], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%6], [%1+%6], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%7], [%1+%7], 4;" ::"r"(dst), "l"(src), "n"(STRIDE), "n"(2 * STRIDE),
+        "n"(3 * STRIDE), "n"(4 * STRIDE), "n"(5 * STRIDE), "n"(6 * STRIDE)
+        : "memory");
+}
+
 // shared load from a 32-bit shared address + element offset
 template <typename R> __device__ __forceinline__ R bx_lds(unsigned base, int elem);
 template <> __device__ __forceinline__ double bx_lds<double>(unsigned base, int elem) {
@@ -387,7 +415,9 @@ template <> __device__ __forceinline__ float bx_lds<float>(unsigned base, int el
 // surface, so the cp.async copies need no per-copy address arithmetic. (A variant that fetched each 14 KB block with
 // one cp.async.bulk per CTA behind mbarriers was measured slower: +9 % instructions for the barrier hand-off and the
 // warps of a CTA coupled to its slowest one -- per-thread copies keep the warps independent.)
-template <typename R, int BD, bool CK>
+// NOXY: the caller does not want d loss / d (frame x, frame y) (OLRT_BWD_NO_FRAME_XY: no decenter is a variable):
+// two of a curved surface's five shared-memory accumulations less.
+template <typename R, int BD, bool CK, bool NOXY>
 __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const BwdParams<R> P, uint32_t* status) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ FxSurf<R> s_surf[OLRT_MAX_SURFACES];
@@ -473,8 +503,7 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
       const unsigned dst = ck_a + (unsigned)((s_ & 1) * 7 * bd * (int)sizeof(R));
       if (CK && s_ > 0) {
         rp -= 7 * bd;  // block of surface s_ - 1 (rp already includes this thread's column)
-#pragma unroll
-        for (int q = 0; q < 7; ++q) bx_cp_async<R>(dst + (unsigned)(q * bd * (int)sizeof(R)), rp + q * bd);
+        bx_cp_async7<R, (BD ? BD : 256) * (int)sizeof(R)>(dst, rp);   // CK implies 256-ray tiles
         cp_async_commit();
         return;
       }
@@ -490,7 +519,8 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
       cp_async_commit();
     };
     stage(S - 1);
-    auto ld = [&](const R* ptr) { return (ptr != nullptr && valid) ? ptr[idx] : R(0); };
+    // idx is clamped for the idle lanes of a tail tile: they read the last ray's values and add to the spare column
+    auto ld = [&](const R* ptr) { return (ptr != nullptr) ? ptr[idx] : R(0); };
     R gx = ld(P.gout[0]), gy = ld(P.gout[1]), gz = ld(P.gout[2]);
     R gL = ld(P.gout[3]), gM = ld(P.gout[4]), gN = ld(P.gout[5]);
     R gi = ld(P.gout[6]), gopd = ld(P.gout[7]);
@@ -523,8 +553,8 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
         R gTx, gTy, gTz, gR, gk;
         bx_conic<R>(sf, md, kk, z0, ex, ey, ez, eL, eM, eN, ei, irec, Qgx, Qgy, Qgz, gx, gy, gz, gL, gM, gN, gi,
                     gopd, gTx, gTy, gTz, gR, gk);
-        const R pv[5] = {gTx, gTy, gTz, gR, gk};
-        bx_add_n<5>(acc, pv);
+        if (NOXY) { const R pv[3] = {gTz, gR, gk}; bx_add_n<3>(acc + 2 * OLRT_BX_COLS, pv); }
+        else { const R pv[5] = {gTx, gTy, gTz, gR, gk}; bx_add_n<5>(acc, pv); }
       };
       auto do_even = [&](const int kk) {
         R gTx, gTy, gTz, gR, gk;
@@ -534,8 +564,8 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
         const int m4 = info.ncoef;
         bx_even<R>(sf, md, kk, info.K, m4, s_coef + info.coef_off, z0, ex, ey, ez, eL, eM, eN, ei, irec, gx, gy,
                    gz, gL, gM, gN, gi, gopd, gTx, gTy, gTz, gR, gk, gC);
-        const R pv[5] = {gTx, gTy, gTz, gR, gk};
-        bx_add_n<5>(acc, pv);
+        if (NOXY) { const R pv[3] = {gTz, gR, gk}; bx_add_n<3>(acc + 2 * OLRT_BX_COLS, pv); }
+        else { const R pv[5] = {gTx, gTy, gTz, gR, gk}; bx_add_n<5>(acc, pv); }
         // coefficient partials in blocks of 4 like the padded table (bx_flush drops the padding's)
         if (m4 > 0) bx_add_n<4>(acc + 5 * OLRT_BX_COLS, gC);
         if (m4 > 4) bx_add_n<4>(acc + 9 * OLRT_BX_COLS, gC + 4);
@@ -567,19 +597,19 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
   if (cur_p >= 0) bx_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
 }
 
-template <typename R, int BD, bool CK>
+template <typename R, int BD, bool CK, bool NOXY>
 int bx_launch_kernel(const BwdParams<R>& P, int block, size_t smem, long long n_tiles, uint32_t* status,
                      cudaStream_t stream) {
   // static tables (16 KB) + dynamic can pass the 48 KB default even when the dynamic part alone does not
-  cudaFuncSetAttribute(trace_bx_kernel<R, BD, CK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaFuncSetAttribute(trace_bx_kernel<R, BD, CK, NOXY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   int per_sm = 0, dev = 0, sms = 148;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_bx_kernel<R, BD, CK>, block, smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_bx_kernel<R, BD, CK, NOXY>, block, smem);
   if (per_sm < 1) per_sm = 1;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   long long grid = (long long)sms * per_sm;
   if (grid > n_tiles) grid = n_tiles;
-  trace_bx_kernel<R, BD, CK><<<(unsigned)grid, block, smem, stream>>>(P, status);
+  trace_bx_kernel<R, BD, CK, NOXY><<<(unsigned)grid, block, smem, stream>>>(P, status);
   return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
 }
 
@@ -611,10 +641,14 @@ int launch_bx(const olrt_sys* sys, const R* presc, const int32_t* ops, long long
   const long long n_tiles = (n_rays + block - 1) / block;
   if (flags & OLRT_BWD_CKPT_BLOCKED) {  // `record` is the tile-blocked checkpoint buffer of the forward
     if (block != OLRT_CKPT_TILE || sys->n_presc > 1 || grecord != nullptr) return OLRT_E_UNSUPPORTED;
-    return bx_launch_kernel<R, 256, true>(P, block, smem, n_tiles, status, stream);
+    if (flags & OLRT_BWD_NO_FRAME_XY) return bx_launch_kernel<R, 256, true, true>(P, block, smem, n_tiles, status, stream);
+    return bx_launch_kernel<R, 256, true, false>(P, block, smem, n_tiles, status, stream);
   }
-  if (block == 256) return bx_launch_kernel<R, 256, false>(P, block, smem, n_tiles, status, stream);
-  return bx_launch_kernel<R, 0, false>(P, block, smem, n_tiles, status, stream);
+  if (block == 256) {
+    if (flags & OLRT_BWD_NO_FRAME_XY) return bx_launch_kernel<R, 256, false, true>(P, block, smem, n_tiles, status, stream);
+    return bx_launch_kernel<R, 256, false, false>(P, block, smem, n_tiles, status, stream);
+  }
+  return bx_launch_kernel<R, 0, false, false>(P, block, smem, n_tiles, status, stream);
 }
 
 }  // namespace OLRT_NS

@@ -169,7 +169,11 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
         if (resid != nullptr) {
           // MM_FAST: a NaN here puts the ray on the fix-up list, whose IEEE re-trace reports it instead
           const unsigned long long key = (valid && !(MM == MM_FAST && f != f)) ? resid_bits((double)r_abs(f)) : 0ull;
-          report_resid(resid + j, key);
+          // the IEEE fix-up pass (MM_IEEE) re-traces a handful of listed rays, one per lane: in group mode every lane
+          // has its OWN slot pointer and trip count (its ray's group), so no warp-wide aggregation there -- each
+          // valid lane raises its own slot
+          if (MM == MM_IEEE) { if (key != 0ull) atomicMax(resid + j, key); }
+          else report_resid(resid + j, key);
         }
         if (j == K) break;
         R nx, ny, nz;

@@ -81,6 +81,23 @@ template <> struct FxMath<float> {
   }
 };
 
+// exp() of a Beer-Lambert exponent (homogeneous.py:49: -(4 pi k / lambda) t 1e3). Through optical glass it is a small
+// negative number (k ~ 1e-8: |x| ~ 1e-3 per cm), where ten Horner steps of the Taylor series are exact to 3e-18
+// (|x| < 1/8) against ~50 instructions and a slow-path call for the library routine, which larger arguments still get.
+template <typename R>
+__device__ __forceinline__ R fx_exp(R x) {
+  if (sizeof(R) == 8 && r_abs(x) < R(0.125)) {
+    R p = R(1.0 / 3628800.0);
+    p = fma(p, x, R(1.0 / 362880.0)); p = fma(p, x, R(1.0 / 40320.0)); p = fma(p, x, R(1.0 / 5040.0));
+    p = fma(p, x, R(1.0 / 720.0)); p = fma(p, x, R(1.0 / 120.0)); p = fma(p, x, R(1.0 / 24.0));
+    p = fma(p, x, R(1.0 / 6.0)); p = fma(p, x, R(0.5)); p = fma(p, x, R(1.0));
+    return fma(p, x, R(1.0));
+  }
+  return r_exp(x);
+}
+template <typename R>
+__device__ __forceinline__ R fx_intensity(R i, R att) { return (att != R(0)) ? i * fx_exp(att) : i; }
+
 // per-surface table in shared memory, built once per CTA (per prescription of a Monte-Carlo batch)
 template <typename R> struct __align__(16) FxSurf {
   R xc, yc;
@@ -539,6 +556,8 @@ trace_fx_kernel(const FwdParams<R> P) {
     }
 
     R L0 = r.L, M0 = r.M, N0 = r.N, att = R(0);
+    // this thread's column of the tile's first checkpoint block; surface s sits s blocks further on
+    R* const ck_ptr = ck_on ? P.ckpt + (tile * S * 7) * OLRT_CKPT_TILE + threadIdx.x : nullptr;
     R i_rec = r.i;          // intensity as recorded, r.i exp(att): exp() only after an absorbing medium
     bool i_stale = false;
     for (int s = 0; s < S; ++s) {
@@ -571,10 +590,10 @@ trace_fx_kernel(const FwdParams<R> P) {
       if (!rec_on && !ck_on) continue;
       if (md.nalpha != R(0)) i_stale = true;
       if (ck_on) {  // tile-blocked checkpoint: the state after this surface, immediate offsets from one pointer
-        if (i_stale) { i_rec = fk_intensity(r.i, att); i_stale = false; }
+        if (i_stale) { i_rec = fx_intensity(r.i, att); i_stale = false; }
         else if (!(r.i != R(0))) i_rec = r.i;
         if (valid) {
-          R* ckp = P.ckpt + ((tile * S + s) * 7) * OLRT_CKPT_TILE + threadIdx.x;
+          R* ckp = ck_ptr + (long long)s * (7 * OLRT_CKPT_TILE);
           __stcs(ckp, r.x); __stcs(ckp + OLRT_CKPT_TILE, r.y); __stcs(ckp + 2 * OLRT_CKPT_TILE, r.z);
           __stcs(ckp + 3 * OLRT_CKPT_TILE, r.L); __stcs(ckp + 4 * OLRT_CKPT_TILE, r.M);
           __stcs(ckp + 5 * OLRT_CKPT_TILE, r.N); __stcs(ckp + 6 * OLRT_CKPT_TILE, i_rec);
@@ -586,12 +605,12 @@ trace_fx_kernel(const FwdParams<R> P) {
         R* rec = P.record + (long long)slot * 8 * NT + idx;  // streaming stores: never re-read by this launch
         __stcs(rec, r.x); __stcs(rec + NT, r.y); __stcs(rec + 2 * NT, r.z);
         __stcs(rec + 3 * NT, r.L); __stcs(rec + 4 * NT, r.M); __stcs(rec + 5 * NT, r.N);
-        if (i_stale) { i_rec = fk_intensity(r.i, att); i_stale = false; }
+        if (i_stale) { i_rec = fx_intensity(r.i, att); i_stale = false; }
         else if (!(r.i != R(0))) i_rec = r.i;  // clipped at this surface (att was reset with it)
         __stcs(rec + 6 * NT, i_rec); __stcs(rec + 7 * NT, r.opd);
       }
     }
-    r.i = fk_intensity(r.i, att);
+    r.i = fx_intensity(r.i, att);
     if (valid) {
       if (P.out[0] != nullptr) {
         __stcs(P.out[0] + idx, r.x); __stcs(P.out[1] + idx, r.y); __stcs(P.out[2] + idx, r.z);

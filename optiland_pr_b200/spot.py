@@ -127,7 +127,6 @@ class SpotDiagram:
 
         from . import backend as be
         from .optic import pupil_points
-        from .trace import fused_spot_groups
         self.optic = optic
         self.fields = optic.get_field_coords() if fields == "all" else list(fields)
         self.wavelengths = list(optic.wavelengths) if wavelengths == "all" else [float(w) for w in wavelengths]
@@ -154,22 +153,17 @@ class SpotDiagram:
         p0 = packs[0]
         fused = bool(sg.fast_math and p0.fastkinds() and optic._EPL is not None and optic._EPD is not None
                      and all(np.array_equal(p.ops, p0.ops) for p in packs))
-        self.path = "fused" if fused else "per_pair"
+        s2 = None
         if fused:
-            ft = optic._field_table(Hx, Hy).to(dev)
-            gen_kw = dict(EPD=optic._EPD, EPL=optic._EPL, wavelength=float(self.wavelengths[0]), dtype=dt, **ft.kwargs())
-            presc = torch.from_numpy(np.concatenate([p.presc for p in packs], axis=0)).to(dev)
-            k0 = np.zeros((nf, p0.n_surfaces), dtype=np.int32)
-            for k in p0.nr_rows():
-                k0[:, k] = 2
-            s1, kg = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, k0, valid_only=True)
-            st = spot_stats(s1)
-            cen = torch.stack([st["cx"], st["cy"]], dim=1).reshape(nw, nf, 2)[self.ref_index]     # [nf, 2]
-            shift2 = cen.unsqueeze(0).expand(nw, nf, 2).reshape(-1, 2).contiguous()
-            s2, _ = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, kg, shift=shift2, valid_only=True,
-                                      settle=False)
-            self.group_iters = kg
-        else:
+            try:
+                s2, cen = self._fused_sums(optic, p0, packs, Px, Py, Hx, Hy, dev, dt, nf, nw)
+            except NotImplementedError:
+                # a (field, wavelength) group needs more Newton updates than the fused launch holds -- e.g. a ray
+                # that misses an asphere makes the reference run max_iter of them (newton_raphson.py:137-149):
+                # trace pair by pair, every trace with its own counts
+                fused = False
+        self.path = "fused" if fused else "per_pair"
+        if not fused:
             npup = int(Px.numel())
             xs, ys, is_ = [], [], []
             for w in self.wavelengths:      # one trace per pair: the Newton exit rule is per trace
@@ -186,6 +180,33 @@ class SpotDiagram:
         self._rms = torch.sqrt((s2[:, 3] + s2[:, 4]) / s2[:, 0]).reshape(nw, nf)
         self._geo = torch.sqrt(s2[:, 5]).reshape(nw, nf)
         self.count = s2[:, 0].reshape(nw, nf)
+
+    def _fused_sums(self, optic, p0, packs, Px, Py, Hx, Hy, dev, dt, nf, nw):
+        """Both passes through trace.fused_spot_groups; returns (second-pass sums [nw * nf, 10], centroids [nf, 2])."""
+        import numpy as np
+
+        from .trace import fused_spot_groups
+        ft = optic._field_table(Hx, Hy).to(dev)
+        gen_kw = dict(EPD=optic._EPD, EPL=optic._EPL, wavelength=float(self.wavelengths[0]), dtype=dt, **ft.kwargs())
+        rows = np.concatenate([p.presc for p in packs], axis=0)
+        # the kernels form the Beer-Lambert exponent 4 pi k / lambda (homogeneous.py:49) with the launch's ONE
+        # wavelength (the first row's): rows of other wavelengths carry k lambda_0 / lambda_row instead of k
+        for r, w in enumerate(self.wavelengths):
+            if r:
+                for lay in p0.layouts:
+                    rows[r, lay.media + 2] *= float(self.wavelengths[0]) / float(w)
+        presc = torch.from_numpy(rows).to(dev)
+        k0 = np.zeros((nf, p0.n_surfaces), dtype=np.int32)
+        for k in p0.nr_rows():
+            k0[:, k] = 2
+        s1, kg = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, k0, valid_only=True)
+        st = spot_stats(s1)
+        cen = torch.stack([st["cx"], st["cy"]], dim=1).reshape(nw, nf, 2)[self.ref_index]     # [nf, 2]
+        shift2 = cen.unsqueeze(0).expand(nw, nf, 2).reshape(-1, 2).contiguous()
+        s2, _ = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, kg, shift=shift2, valid_only=True,
+                                  settle=False)
+        self.group_iters = kg
+        return s2, cen
 
     def centroid(self):
         """[(cx, cy)] per field, reference wavelength (spot_diagram.py:317-327)."""

@@ -10,7 +10,9 @@ are made in the same order (so the perturbation values are the reference's, bit 
 row of a `[n_trials, stride]` prescription batch, and ONE kernel launch traces all trials: each trial launches the
 same pupil grid for every field, traces it through its own prescription and reduces its spot sums in the kernel
 (`olrt_trace_pupil_*` with olrt_sys.n_presc > 1) -- no per-ray data exists in HBM at any point. Lenses or
-perturbations outside that kernel (tilts) go through launch + trace + spot kernels on chunks of trials.
+perturbations outside that kernel (tilts, freeform surfaces), and trials whose Newton counts the fused launch cannot
+hold (a missing ray makes the reference run max_iter updates), go trial by trial through launch + trace + spot
+kernels -- one launch per trial, each with its own Newton counts, exactly like the reference's loop.
 
 Sharding: trials are independent; rank r takes a contiguous range of them and the per-trial merits are gathered
 (`parallel.py`), nothing else crosses NVLink.
@@ -23,7 +25,7 @@ import torch
 from . import _lib as L
 from . import backend as be
 from . import parallel
-from .trace import fused_trace, fused_trace_pupil, slice_true_iters
+from .trace import fused_trace
 
 
 class RangeSampler:
@@ -123,15 +125,42 @@ class MonteCarloSpot:
 
     draw_chunks = 4      # fused path, >= 1024 trials: the draws of chunk c + 1 run on the host while chunk c traces
 
-    def prescriptions(self, packed, values):
-        """[n_trials, stride] float64: the nominal row with every trial's perturbed entries."""
+    def has_tilt(self) -> bool:
+        return any(p.variable_type == "tilt" for p in self.perturbations)
+
+    def prescriptions(self, packed, values, ops_out=None):
+        """[n_trials, stride] float64: the nominal row with every trial's perturbed entries. Tilt perturbations
+        (cs.rx / ry / rz := value, radians) also decide a frame flag of the ops table -- the reference applies a
+        rotation only when the angle is truthy (coordinate_system.py:73-107) -- so they need `ops_out`, a list that
+        receives one int32 ops table per trial."""
         base = np.ascontiguousarray(packed.presc[0], dtype=np.float64)
         batch = np.repeat(base[None, :], values.shape[0], axis=0)
+        tilts = []
         for j, p in enumerate(self.perturbations):
             if p.variable_type == "tilt":
-                raise NotImplementedError("tilt perturbations change the ops table: use run(), not prescriptions()")
+                if ops_out is None:
+                    raise NotImplementedError("tilt perturbations change the ops table: pass ops_out (run() does)")
+                tilts.append((j, p))
+                continue
             for off, scale, nominal in _offsets(packed, self.optic, p):
                 batch[:, off] += scale * (values[:, j] - nominal)
+        if ops_out is not None:
+            rows = {lay.index: k for k, lay in enumerate(packed.layouts)}
+            for t in range(values.shape[0]):
+                ops = packed.ops.copy()
+                for j, p in tilts:
+                    k = rows[p.surface_number]
+                    lay = packed.layouts[k]
+                    q = lay.nframes - 1                      # the surface's own frame is the last of its chain
+                    c_off, s_off, bit = {"z": (3, 4, 1), "y": (5, 6, 2), "x": (7, 8, 4)}[p.axis]
+                    v = np.float64(values[t, j])
+                    batch[t, lay.frames + q * L.FRAME_REALS + c_off] = np.cos(v)
+                    batch[t, lay.frames + q * L.FRAME_REALS + s_off] = np.sin(v)
+                    word = int(ops[k * L.OPS_STRIDE + L.OP_FRAMEFLAGS]) & ~(bit << (3 * q))
+                    if bool(v):
+                        word |= bit << (3 * q)
+                    ops[k * L.OPS_STRIDE + L.OP_FRAMEFLAGS] = word
+                ops_out.append(ops)
         return batch
 
     def run(self, num_iterations, Hx, Hy, wavelength, Px, Py, trials_per_launch=None):
@@ -145,7 +174,7 @@ class MonteCarloSpot:
             packed = sg.pack([float(wavelength)])
         finally:
             sg.record = keep
-        fused = bool(packed.fastkinds())
+        fused = bool(packed.fastkinds()) and not self.has_tilt()
         # Fused path: the reference-order scalar draws (one Python call per trial and perturbation) are made chunk by
         # chunk, each chunk while the previous one is on the GPU; every sampler keeps its own generator, so the values
         # are the ones one pass over all trials would draw. Every rank draws every chunk (same generator state).
@@ -158,7 +187,8 @@ class MonteCarloSpot:
             batch = None
         else:
             values = self.draw(num_iterations)
-            batch = self.prescriptions(packed, values)
+            ops_rows = [] if self.has_tilt() else None
+            batch = self.prescriptions(packed, values, ops_out=ops_rows)
         lo, hi = parallel.shard_range(num_iterations)
         Hx = np.atleast_1d(np.asarray(Hx, dtype=np.float64))
         Hy = np.atleast_1d(np.asarray(Hy, dtype=np.float64))
@@ -172,19 +202,47 @@ class MonteCarloSpot:
         fxy = ft.fxy_d
         gen_kw = dict(EPD=lens._EPD, EPL=lens._EPL, wavelength=float(wavelength), dtype=dt, **ft.kwargs())
         rms_local = torch.empty((hi - lo, nf), dtype=torch.float64, device=dev)
-        self.last_path = "fused" if fused else "chunked"
-        step = trials_per_launch or (hi - lo if fused else max(1, (1 << 26) // max(1, nf * npup)))
-        zero1 = torch.zeros(1, dtype=torch.float64, device=dev)
-        has_nr = bool(packed.nr_rows())
+        self.last_path = "fused" if fused else "per_trial"
+        self.fallback_trials = 0
+        step = trials_per_launch or (hi - lo)
         from .spot import spot_stats, spot_sums
         from .trace import fused_spot_groups
         S = packed.n_surfaces
         nr_rows = packed.nr_rows()
 
-        def fused_groups(presc_t, k0, between=None):
+        launched = []      # the launched rays of the nominal fields, made once for the per-trial path
+
+        def per_trial(rows, ops_list=None):
+            """rms [T, nf] trial by trial, the reference's own loop shape (monte_carlo.py:86-109): one launch per
+            trial through `fused_trace`, which settles that trial's Newton counts with the reference's exit rule
+            (a NaN ray -> max_iter). Any lens the kernels trace, any ray count, tilts included."""
+            import dataclasses
+            if not launched:
+                rays = lens.launch_rays(Hx, Hy, Px, Py, wavelength)
+                launched.append(rays.components()[:7] + [None])
+            out_rms = torch.empty((rows.shape[0], nf), dtype=torch.float64, device=dev)
+            for t in range(rows.shape[0]):
+                pk = dataclasses.replace(packed, presc=np.ascontiguousarray(rows[t:t + 1]),
+                                         ops=(ops_list[t] if ops_list is not None else packed.ops).copy())
+                res = fused_trace(pk, launched[0], fast=sg.fast_math)
+                packed.set_nr_iters(res.nr_iters)             # the next trial's first guess
+                if res.status & L.ST_ZERNIKE_RANGE:
+                    raise ValueError("Zernike coordinates must be normalized to [-1, 1]. Consider updating the "
+                                     "normalization radius to 1.1x the surface aperture.")
+                out_rms[t] = spot_stats(spot_sums(res.out[0], res.out[1], res.out[6], nf, npup))["rms"]
+            return out_rms
+
+        def fused_groups(presc_t, k0, between=None, rows=None):
             """(rms [T, nf], counts [T * nf, S]) from trace.fused_spot_groups: one fused launch per round over
-            `presc_t` [T, stride], Newton trip counts per (trial, field) group."""
-            sums, kg = fused_spot_groups(packed, presc_t, Px, Py, fxy, gen_kw, k0, between=between)
+            `presc_t` [T, stride], Newton trip counts per (trial, field) group. Where a group needs more Newton
+            updates than the fused launch holds (OLRT_GROUP_RESID - 1; a ray that misses an asphere makes the
+            reference run max_iter of them) the batch goes trial by trial instead."""
+            try:
+                sums, kg = fused_spot_groups(packed, presc_t, Px, Py, fxy, gen_kw, k0, between=between)
+            except NotImplementedError:
+                self.fallback_trials += int(presc_t.shape[0])
+                rows_np = rows if rows is not None else presc_t.cpu().numpy()
+                return per_trial(rows_np), None
             return spot_stats(sums)["rms"].reshape(int(presc_t.shape[0]), nf), kg
 
         k_nominal = np.zeros((nf, S), dtype=np.int32)
@@ -194,7 +252,8 @@ class MonteCarloSpot:
             # the nominal lens first: its per-field counts are the guess for every trial
             nominal = torch.from_numpy(np.ascontiguousarray(packed.presc[:1], dtype=np.float64)).to(dev)
             _, kg0 = fused_groups(nominal, k_nominal)
-            k_nominal = kg0.reshape(nf, S)
+            if kg0 is not None:
+                k_nominal = kg0.reshape(nf, S)
         self.group_iters = None
         if chunked_draws:
             for c in range(self.draw_chunks):
@@ -206,7 +265,8 @@ class MonteCarloSpot:
                     presc = torch.from_numpy(self.prescriptions(packed, values[a:b])).to(dev)
                     rms_ab, kg = fused_groups(presc, k_nominal, between=nxt)
                     rms_local[a - lo:b - lo] = rms_ab
-                    self.group_iters = kg if self.group_iters is None else np.concatenate([self.group_iters, kg])
+                    if kg is not None:
+                        self.group_iters = kg if self.group_iters is None else np.concatenate([self.group_iters, kg])
                 elif nxt is not None:
                     nxt()
             lo_loop = hi       # nothing left for the generic loop below
@@ -214,31 +274,14 @@ class MonteCarloSpot:
             lo_loop = lo
         for a in range(lo_loop, hi, max(1, step)):
             b = min(hi, a + step)
-            presc = torch.from_numpy(batch[a:b]).to(dev)
-            T = b - a
             if fused:
-                rms_ab, kg = fused_groups(presc, k_nominal)
+                presc = torch.from_numpy(batch[a:b]).to(dev)
+                rms_ab, kg = fused_groups(presc, k_nominal, rows=batch[a:b])
                 rms_local[a - lo:b - lo] = rms_ab
-                self.group_iters = kg if self.group_iters is None else np.concatenate([self.group_iters, kg])
+                if kg is not None:
+                    self.group_iters = kg if self.group_iters is None else np.concatenate([self.group_iters, kg])
                 continue
-            for attempt in range(8):
-                status = torch.zeros(1, dtype=torch.int32, device=dev)
-                resid = (torch.zeros((S, L.RESID_STRIDE), dtype=torch.int64, device=dev) if has_nr else None)
-                sums = torch.zeros((T * nf, L.SPOT_SUMS), dtype=torch.float64, device=dev)
-                rays = lens.launch_rays(Hx, Hy, Px, Py, wavelength)           # one copy of the launched rays
-                ins = [t.repeat(T) for t in rays.components()[:7]] + [None]   # trial-major batch
-                res = fused_trace(packed, ins, presc=presc, rays_per_presc=nf * npup, fast=sg.fast_math,
-                                  verify_nr=False, check_status=False, status_t=status, resid_out=resid)
-                spot_sums(res.out[0], res.out[1], res.out[6], T * nf, npup, out=sums)
-                if not has_nr:
-                    break
-                k_used = packed.nr_iters()
-                k_true = slice_true_iters(packed, resid.cpu().numpy().view(np.float64), k_used)
-                if k_true == k_used:
-                    break
-                packed.set_nr_iters([min(lay.max_iter, max(k * 2, k + 2)) if kt is None else kt
-                                     for k, kt, lay in zip(k_used, k_true, packed.layouts)])
-            rms_local[a - lo:b - lo] = spot_stats(sums)["rms"].reshape(T, nf)
+            rms_local[a - lo:b - lo] = per_trial(batch[a:b], ops_rows[a:b] if ops_rows is not None else None)
         r, w = parallel.world()
         if w == 1:
             return rms_local

@@ -70,3 +70,32 @@ def test_samplers_match_the_reference_bit_for_bit():
         assert [a.sample() for _ in range(50)] == [float(b.sample()) for _ in range(50)]
     a, b = RangeSampler(0.0, 1.0, 7), RefRange(0.0, 1.0, 7)
     assert [a.sample() for _ in range(16)] == [float(b.sample()) for _ in range(16)]
+
+
+def test_tilt_perturbation_rows_equal_packing_the_tilted_lens():
+    """Tilt perturbations (cs.rx / ry := value) set the frame's cos / sin entries AND the frame flag of the ops table
+    (the reference rotates only when the angle is truthy, coordinate_system.py:73-107)."""
+    lens = samples.FreeformPlate()
+    s = lens.surface_group.surfaces
+    perts = [Perturbation(lens, "tilt", DistributionSampler("normal", seed=3, loc=float(s[3].geometry.cs.ry),
+                                                            scale=0.003), 3, axis="y"),
+             Perturbation(lens, "tilt", RangeSampler(0.0, 0.002, 3), 4, axis="x"),     # first value 0.0: flag stays off
+             Perturbation(lens, "radius", DistributionSampler("normal", seed=4, loc=35.0, scale=0.02), 3)]
+    mc = MonteCarloSpot(lens, perts)
+    vals = mc.draw(3)
+    packed = pack_surface_group(s, [0.55], record="none")
+    with pytest.raises(NotImplementedError):
+        mc.prescriptions(packed, vals)
+    ops_rows = []
+    batch = mc.prescriptions(packed, vals, ops_out=ops_rows)
+    assert len(ops_rows) == 3
+    for t in range(3):
+        pl = samples.FreeformPlate()
+        ps = pl.surface_group.surfaces
+        ps[3].geometry.cs.ry = float(vals[t, 0])
+        ps[4].geometry.cs.rx = float(vals[t, 1])
+        ps[3].geometry.radius = float(vals[t, 2])
+        want = pack_surface_group(ps, [0.55], record="none")
+        assert np.array_equal(batch[t], want.presc[0]), t
+        assert np.array_equal(ops_rows[t], want.ops), t
+    assert vals[0, 1] == 0.0 and not np.array_equal(ops_rows[0], ops_rows[1])
