@@ -339,6 +339,29 @@ def main():
               "vignetting_mask_identical": bool(((out[6] == 0) == (strict_out[6] == 0)).all()),
               "bar": "1e-10 relative, masks identical (BASELINE.json north_star)"}
     del den
+    # ---- the same check where the masks are not trivial ("C2 with aperture= radial stops"): the lens with
+    # radial stops on its first, stop and last glass surfaces vignettes part of every off-axis bundle; tolerance-mode
+    # kernel vs the strict kernel on the same 50 M rays: every clip decision must be the same one
+    from optiland_pr_b200.apertures import RadialAperture
+    lens_s = samples.EvenAsphereDoubleGauss()
+    lens_s.surface_group.record = "none"
+    sfs_s = lens_s.surface_group.surfaces
+    sfs_s[1].aperture = RadialAperture(r_max=20.5)
+    sfs_s[6].aperture = RadialAperture(r_max=6.2, r_min=0.05)
+    sfs_s[11].aperture = RadialAperture(r_max=16.5)
+    packed_s = lens_s.surface_group.pack([WAVELENGTH])
+    packed_s.set_nr_iters(packed.nr_iters())
+    out_s = fused_trace(packed_s, ins, fast=True).out
+    fused_trace(packed_s, ins, out=strict_out, fast=False)
+    clipped = (strict_out[6] == 0)
+    den = torch.clamp(strict_out.abs(), min=1.0)
+    parity["stopped_lens"] = {
+        "radial_stops": "r_max 20.5 (surface 1), 0.05 <= r <= 6.2 (stop), r_max 16.5 (surface 11)",
+        "rays": int(n), "clipped_rays": int(clipped.sum()), "clipped_fraction": float(clipped.double().mean()),
+        "vignetting_mask_identical": bool(((out_s[6] == 0) == clipped).all()),
+        "nan_pattern_identical": bool((out_s.isnan() == strict_out.isnan()).all()),
+        "max_rel_err_vs_strict_kernel": float(((out_s - strict_out).abs() / den).nan_to_num(0.0).max())}
+    del den, out_s, clipped
     ms_strict = timed(lambda: fused_trace(packed, ins, out=strict_out, fast=False, verify_nr=False, check_status=False),
                       max(2, args.steps // 2), 3)
     ms_fx_arrays = timed(lambda: fused_trace(packed, ins, out=strict_out, fast=True, verify_nr=False, check_status=False),

@@ -26,6 +26,8 @@ OLRT_DECL_PUPIL(f64, double)
 OLRT_DECL_PUPIL(f32, float)
 
 namespace olrt_strict {
+// launch the strict build's IEEE fix-up kernel on a FwdParams<double> passed by bytes (trace_launch.cuh)
+int fixup_raw_f64(const void* params, size_t bytes, unsigned grid, int block, size_t smem, cudaStream_t stream);
 int selftest_math(const double* a, const double* b, double* q, double* r, long long n, cudaStream_t stream);
 }
 

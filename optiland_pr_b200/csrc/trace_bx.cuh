@@ -236,7 +236,8 @@ __device__ __forceinline__ void bx_even(const FxSurf<R>& sf, const FxMedium<R>& 
   typedef FxMath<R> Mx;
   const bool cen = (kind & FX_CENTERED) != 0;
   const R x = cen ? ex : ex - sf.xc, y = cen ? ey : ey - sf.yc, z = ez - sf.zc;
-  const R t0 = fx_conic_t(x, y, z, eL, eM, eN, sf, (kind & FX_SPHERE) != 0);
+  int unused_guard = 0;
+  const R t0 = fx_conic_t(x, y, z, eL, eM, eN, sf, (kind & FX_SPHERE) != 0, unused_guard);
   R t = t0, t1 = t0, t2 = t0;
   BxEval<R> e;
   for (int j = 0; j < K; ++j) {  // forward recompute of the iterates

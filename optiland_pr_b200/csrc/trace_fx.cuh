@@ -17,6 +17,14 @@
 // Zero radicands, zero divisors and NaN rays leave this kernel as non-finite outputs and are re-traced by
 // the IEEE fix-up pass (trace_fwd.cuh, FIX = true) exactly like in the strict build; fp32 uses the
 // hardware's IEEE-safe sqrtf / reciprocal instead (there is no fp32 fix-up pass).
+// DECISIONS (fp64). The values above differ from the reference's by rounding (~1e-15 relative), so a yes / no
+// decision taken on them -- inside the aperture? does the ray hit the conic (discriminant >= 0)? total internal
+// reflection (Snell radicand < 0)? which root? which side of the normal? -- could come out differently from the
+// reference's when the deciding quantity sits within that rounding of its threshold. Every such quantity is
+// therefore also tested against a GUARD BAND of 2^-36 (1.5e-11 relative, four orders of magnitude wider than the
+// rounding differences): a ray inside a band is put on the fix-up list and re-traced by the STRICT build's IEEE
+// kernel (-fmad=false, the reference's operation order), so the decision that is stored is always the one the
+// reference takes. Masks, NaN patterns and root choices are identical to the reference's for every ray.
 #pragma once
 #include "trace_fk.cuh"
 
@@ -32,6 +40,7 @@ namespace OLRT_NS {
 #define OLRT_FX_MIN_BLOCKS_F32 3
 #endif
 
+#define OLRT_FX_GHI 0x3DB00000   /* high word of 2^-36: the guard band of every decision (see DECISIONS) */
 template <typename R> struct FxMath;
 template <> struct FxMath<double> {
   static __device__ __forceinline__ double rcp(double b) {
@@ -54,6 +63,20 @@ template <> struct FxMath<double> {
   // m * sign(s) for s != 0: flip m's sign bit when s is negative
   static __device__ __forceinline__ double flipsign(double m, double s) {
     return __hiloint2double(__double2hiint(m) ^ (__double2hiint(s) & (int)0x80000000), __double2loint(m));
+  }
+  // Guard-band tests (see "DECISIONS" above) on the high words -- exponent and top 20 mantissa bits, a monotone proxy
+  // of log2 -- in the INTEGER pipe: every test folds one margin into a running minimum `g` (one or two integer
+  // instructions, no FP64 issue slot), and the kernel compares that minimum ONCE per ray with OLRT_FX_GHI = the high
+  // word of 2^-36. A margin below it (or negative: the quantity itself was negative) lists the ray for the strict pass.
+  static __device__ __forceinline__ void g_pos(int& g, double v) { g = min(g, __double2hiint(v)); }   // v > 2^-36 ?
+  static __device__ __forceinline__ void g_abs(int& g, double v) { g = min(g, __double2hiint(v) & 0x7fffffff); }
+  // a > 2^-18 |b| ?  (the margin is rescaled so that the common threshold applies; flags below 2^-18, not above 2^-16)
+  static __device__ __forceinline__ void g_ratio18(int& g, double a, double b) {
+    g = min(g, __double2hiint(a) - (__double2hiint(b) & 0x7fffffff) + ((17 << 20) + OLRT_FX_GHI));
+  }
+  // |v| > 1e-12 ?  (rescaled: hi(1e-12) = 0x3D719799)
+  static __device__ __forceinline__ void g_abs12(int& g, double v) {
+    g = min(g, (__double2hiint(v) & 0x7fffffff) + (OLRT_FX_GHI - 0x3D719799));
   }
 };
 // fp32: the hardware's approximate reciprocal / rsqrt / sqrt (1-2 ulp, one MUFU each; 0 -> inf / 0, negative -> NaN
@@ -79,6 +102,11 @@ template <> struct FxMath<float> {
   static __device__ __forceinline__ float flipsign(float m, float s) {
     return __int_as_float(__float_as_int(m) ^ (__float_as_int(s) & (int)0x80000000));
   }
+  // fp32 has no fix-up pass and no guard bands (its bar is 1e-5 with the masks of its own arithmetic)
+  static __device__ __forceinline__ void g_pos(int&, float) {}
+  static __device__ __forceinline__ void g_abs(int&, float) {}
+  static __device__ __forceinline__ void g_ratio18(int&, float, float) {}
+  static __device__ __forceinline__ void g_abs12(int&, float) {}
 };
 
 // exp() of a Beer-Lambert exponent (homogeneous.py:49: -(4 pi k / lambda) t 1e3). Through optical glass it is a small
@@ -106,7 +134,10 @@ template <typename R> struct __align__(16) FxSurf {
   R k, c1iR2;       // k, (1+k)/R^2
   R rmax2, rmin2;   // radial aperture (r_max^2, r_min^2)
   R twoR, pad;
+  R gmax, gmin;     // guard bands of the aperture test: 2^-36 r_max^2, 2^-36 r_min^2
 };
+#define OLRT_FX_GB 1.4551915228366852e-11      /* 2^-36 */
+#define OLRT_FX_GB_SQRT 3.814697265625e-06     /* 2^-18 */
 template <typename R> struct __align__(16) FxMedium {
   R n1, u, u2, nalpha;  // n_pre, n_pre/n_post, its square, -(4 pi k / lambda) * 1e3
 };
@@ -158,6 +189,7 @@ __device__ __forceinline__ void fx_build_surface(const int32_t* s_ops, const R* 
   } else {
     sf.rmax2 = R(0); sf.rmin2 = R(0);
   }
+  sf.gmax = R(OLRT_FX_GB) * sf.rmax2; sf.gmin = R(OLRT_FX_GB) * sf.rmin2;
   s_info[s].kind = kind;
   // dense variant id for the kernel's switch: 0-2 = plane / conic / even asphere with run-time flags; 3-7 = the same
   // with the flags of an ordinary lens surface (centred, refracting, no aperture) fixed at compile time
@@ -191,7 +223,7 @@ __device__ __forceinline__ void fx_build_surface(const int32_t* s_ops, const R* 
 
 // StandardGeometry.distance, standard.py:89-140, for a ray already in the surface frame
 template <typename R>
-__device__ __forceinline__ R fx_conic_t(R x, R y, R z, R L, R M, R N, const FxSurf<R>& sf, bool sphere) {
+__device__ __forceinline__ R fx_conic_t(R x, R y, R z, R L, R M, R N, const FxSurf<R>& sf, bool sphere, int& guard) {
   typedef FxMath<R> Mx;
   if (sizeof(R) == 4) {
     // fp32: b^2 - 4ac cancels catastrophically for a ray launched far from the vertex, so the
@@ -227,31 +259,41 @@ __device__ __forceinline__ R fx_conic_t(R x, R y, R z, R L, R M, R N, const FxSu
   const R ra = Mx::rcp(a);
   const R t1 = (sd - hb) * ra, t2 = (-hb - sd) * ra;
   const R z1 = fma(t1, N, z), z2 = fma(t2, N, z);
-  return (r_abs(z1) <= r_abs(z2)) ? t1 : t2;  // a == 0 (paraboloid, ray along the axis): non-finite -> fix-up
+  const R az1 = r_abs(z1), az2 = r_abs(z2);
+  // guard bands. Hit / miss: sqrt(discriminant) against |b| / 2. Root choice: the two intersections of a sphere (or
+  // any conic with k > -1, whose sag has the sign of R) lie on one side of the vertex plane, so |z1| == |z2| needs
+  // the discriminant to vanish -- the same band; only a hyperboloid's two sheets need the explicit test.
+  Mx::g_ratio18(guard, sd, hb);
+  if (!sphere && sf.c1 < R(0) && r_abs(az1 - az2) <= R(OLRT_FX_GB) * (az1 + az2)) guard = -1;
+  return (az1 <= az2) ? t1 : t2;  // a == 0 (paraboloid, ray along the axis): non-finite -> fix-up
 }
 
 // propagate + Beer-Lambert exponent + OPD + radial clip, with the ray in the surface frame
 template <typename R>
 __device__ __forceinline__ void fx_arrive(RayState<R>& r, R t, const FxSurf<R>& sf, const FxMedium<R>& md,
-                                          int kind, R r2, R& att) {
+                                          int kind, R r2, R& att, int& guard) {
   att = fma(md.nalpha, t, att);
   r.opd = fma(r_abs(t), r_abs(md.n1), r.opd);  // opd + |t n|, standard_surface.py:218
   if (kind & FX_APER) {
     const bool inside = (r2 <= sf.rmax2) & (r2 >= sf.rmin2);
+    if (sizeof(R) == 8 && ((r_abs(r2 - sf.rmax2) <= sf.gmax) | (r_abs(r2 - sf.rmin2) < sf.gmin))) guard = -1;
     if (!inside) { r.i = R(0); att = R(0); }
   }
 }
 
 // RealRays.refract / reflect, real_rays.py:141-181, with dot = D . n already known
 template <typename R>
-__device__ __forceinline__ void fx_interact(RayState<R>& r, R nx, R ny, R nz, R dot, const FxMedium<R>& md, int kind) {
+__device__ __forceinline__ void fx_interact(RayState<R>& r, R nx, R ny, R nz, R dot, const FxMedium<R>& md, int kind,
+                                            int& guard) {
   typedef FxMath<R> Mx;
+  Mx::g_abs(guard, dot);           // which side of the normal: sign(dot), real_rays.py:529
   if (kind & FX_REFLECT) {
     const R d2 = dot + dot;
     r.L = fma(-d2, nx, r.L); r.M = fma(-d2, ny, r.M); r.N = fma(-d2, nz, r.N);
     return;
   }
   const R v = fma(md.u2, fma(dot, dot, R(-1)), R(1));  // 1 - u^2 (1 - dot^2); < 0: TIR -> NaN
+  Mx::g_pos(guard, v);             // refracted or totally reflected
   const R root = Mx::sqrt_(v);
   R g = Mx::flipsign(fma(-md.u, r_abs(dot), root), dot);
   if (dot == R(0)) g = R(0);  // n * sign(0)
@@ -273,17 +315,19 @@ __device__ __forceinline__ void fx_globalize(RayState<R>& r, const FxSurf<R>& sf
 
 template <typename R>
 __device__ __forceinline__ void fx_plane(RayState<R>& r, const FxSurf<R>& sf, const FxMedium<R>& md, int kind,
-                                         R& att) {
+                                         R& att, int& guard) {
   typedef FxMath<R> Mx;
   fx_localize(r, sf, kind);
   const R t = -r.z * Mx::rcp(r.N);  // plane.py:61-77
   r.x = fma(t, r.L, r.x); r.y = fma(t, r.M, r.y); r.z = fma(t, r.N, r.z);
-  fx_arrive(r, t, sf, md, kind, fma(r.x, r.x, r.y * r.y), att);
+  fx_arrive(r, t, sf, md, kind, fma(r.x, r.x, r.y * r.y), att, guard);
   if (kind & FX_REFLECT) {
     r.N = -r.N;
   } else {  // n = (0, 0, 1): T = (u L, u M, sgn(N) root)
     const R N = r.N;
-    const R root = Mx::sqrt_(fma(md.u2, fma(N, N, R(-1)), R(1)));
+    const R v = fma(md.u2, fma(N, N, R(-1)), R(1));
+    Mx::g_pos(guard, v); Mx::g_abs(guard, N);
+    const R root = Mx::sqrt_(v);
     r.L = md.u * r.L; r.M = md.u * r.M;
     r.N = (N == R(0)) ? R(0) * root : Mx::copysign_(root, N);
   }
@@ -292,14 +336,14 @@ __device__ __forceinline__ void fx_plane(RayState<R>& r, const FxSurf<R>& sf, co
 
 template <typename R>
 __device__ __forceinline__ void fx_conic(RayState<R>& r, const FxSurf<R>& sf, const FxMedium<R>& md, int kind,
-                                         R& att) {
+                                         R& att, int& guard) {
   typedef FxMath<R> Mx;
   fx_localize(r, sf, kind);
   const bool sphere = (kind & FX_SPHERE) != 0;
-  const R t = fx_conic_t(r.x, r.y, r.z, r.L, r.M, r.N, sf, sphere);
+  const R t = fx_conic_t(r.x, r.y, r.z, r.L, r.M, r.N, sf, sphere, guard);
   r.x = fma(t, r.L, r.x); r.y = fma(t, r.M, r.y); r.z = fma(t, r.N, r.z);
   const R r2 = fma(r.x, r.x, r.y * r.y);
-  fx_arrive(r, t, sf, md, kind, r2, att);
+  fx_arrive(r, t, sf, md, kind, r2, att, guard);
   R nx, ny, nz;
   if (sphere) {
     nx = r.x * sf.iR; ny = r.y * sf.iR; nz = fma(r.z, sf.iR, R(-1));
@@ -309,7 +353,7 @@ __device__ __forceinline__ void fx_conic(RayState<R>& r, const FxSurf<R>& sf, co
     nx = r.x * g; ny = r.y * g; nz = -w * g;
   }
   const R dot = fma(r.L, nx, fma(r.M, ny, r.N * nz));
-  fx_interact(r, nx, ny, nz, dot, md, kind);
+  fx_interact(r, nx, ny, nz, dot, md, kind, guard);
   fx_globalize(r, sf, kind);
 }
 
@@ -319,10 +363,10 @@ __device__ __forceinline__ void fx_conic(RayState<R>& r, const FxSurf<R>& sf, co
 template <typename R>
 __device__ __forceinline__ void fx_even(RayState<R>& r, const FxSurf<R>& sf, const FxMedium<R>& md, int kind,
                                         const FxInfo& info, int K, const R* coef, bool valid,
-                                        unsigned long long* resid, R& att) {
+                                        unsigned long long* resid, R& att, int& guard) {
   typedef FxMath<R> Mx;
   fx_localize(r, sf, kind);
-  R t = fx_conic_t(r.x, r.y, r.z, r.L, r.M, r.N, sf, (kind & FX_SPHERE) != 0);
+  R t = fx_conic_t(r.x, r.y, r.z, r.L, r.M, r.N, sf, (kind & FX_SPHERE) != 0, guard);
   const int m = info.ncoef;
   R xi, yi, zi, zx, zy, fp, r2;
   for (int j = 0;; ++j) {
@@ -358,12 +402,13 @@ __device__ __forceinline__ void fx_even(RayState<R>& r, const FxSurf<R>& sf, con
     }
     if (lastj) break;
     const R dfs = (r_abs(fp) > R(1e-14)) ? fp : R(1e-14);
+    Mx::g_abs12(guard, fp);   // near the reference's |f'| > 1e-14 switch, newton_raphson.py:162
     t = fma(-f, Mx::rcp(dfs), t);
   }
   r.x = xi; r.y = yi; r.z = zi;
-  fx_arrive(r, t, sf, md, kind, r2, att);
+  fx_arrive(r, t, sf, md, kind, r2, att, guard);
   const R w = Mx::rsqrt(fma(zx, zx, fma(zy, zy, R(1))));
-  fx_interact(r, zx * w, zy * w, -w, fp * w, md, kind);
+  fx_interact(r, zx * w, zy * w, -w, fp * w, md, kind, guard);
   fx_globalize(r, sf, kind);
 }
 
@@ -556,6 +601,7 @@ trace_fx_kernel(const FwdParams<R> P) {
     }
 
     R L0 = r.L, M0 = r.M, N0 = r.N, att = R(0);
+    int guard = 0x7fffffff;  // smallest decision margin seen (FxMath::g_*): below OLRT_FX_GHI the strict pass takes the ray
     // this thread's column of the tile's first checkpoint block; surface s sits s blocks further on
     R* const ck_ptr = ck_on ? P.ckpt + (tile * S * 7) * OLRT_CKPT_TILE + threadIdx.x : nullptr;
     R i_rec = r.i;          // intensity as recorded, r.i exp(att): exp() only after an absorbing medium
@@ -569,22 +615,22 @@ trace_fx_kernel(const FwdParams<R> P) {
       const FxInfo& info = s_info[s];
       const int kind = info.kind;
       switch (info.pad1) {  // warp-uniform, dense (fx_build_surface)
-        case 0: fx_plane<R>(r, sf, md, kind, att); break;
-        case 1: fx_conic<R>(r, sf, md, kind, att); break;
-        case 3: fx_plane<R>(r, sf, md, KIND_PLANE | FX_CENTERED, att); break;
-        case 4: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED | FX_SPHERE, att); break;
-        case 5: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED, att); break;
+        case 0: fx_plane<R>(r, sf, md, kind, att, guard); break;
+        case 1: fx_conic<R>(r, sf, md, kind, att, guard); break;
+        case 3: fx_plane<R>(r, sf, md, KIND_PLANE | FX_CENTERED, att, guard); break;
+        case 4: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED | FX_SPHERE, att, guard); break;
+        case 5: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED, att, guard); break;
         case 6:
           fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED | FX_SPHERE, info, gmode ? s_gk[s] : info.K,
-                     s_coef + info.coef_off, valid, want_resid ? (s_resid + info.roff) : nullptr, att);
+                     s_coef + info.coef_off, valid, want_resid ? (s_resid + info.roff) : nullptr, att, guard);
           break;
         case 7:
           fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED, info, gmode ? s_gk[s] : info.K, s_coef + info.coef_off,
-                     valid, want_resid ? (s_resid + info.roff) : nullptr, att);
+                     valid, want_resid ? (s_resid + info.roff) : nullptr, att, guard);
           break;
         default:
           fx_even<R>(r, sf, md, kind, info, gmode ? s_gk[s] : info.K, s_coef + info.coef_off, valid,
-                     want_resid ? (s_resid + info.roff) : nullptr, att);
+                     want_resid ? (s_resid + info.roff) : nullptr, att, guard);
           break;
       }
       if (!rec_on && !ck_on) continue;
@@ -623,7 +669,7 @@ trace_fx_kernel(const FwdParams<R> P) {
     }
     bool bad = false;
     if (sizeof(R) == 8 && P.fixup != nullptr) {
-      bad = valid && (nonfinite(r.x) | nonfinite(r.y) | nonfinite(r.z) | nonfinite(r.L) |
+      bad = valid && ((guard < OLRT_FX_GHI) | nonfinite(r.x) | nonfinite(r.y) | nonfinite(r.z) | nonfinite(r.L) |
                       nonfinite(r.M) | nonfinite(r.N) | nonfinite(r.opd) | nonfinite(r.i));
       const unsigned m = __ballot_sync(0xffffffffu, bad);
       if (m != 0u) {

@@ -1,6 +1,7 @@
 // trace_launch.cuh -- host-side launchers, instantiated once per translation unit
 // (strict / fast). Grid = one wave of persistent CTAs: SM count x resident CTAs per SM.
 #pragma once
+#include "olrt_internal.h"
 #include "trace_fwd.cuh"
 #include "trace_fk.cuh"
 #ifdef OLRT_FX
@@ -30,8 +31,17 @@ inline int pick_block(const olrt_sys* sys, bool fk, bool fx, bool pupil) {
   return 0;
 }
 
+// The IEEE re-trace of the listed rays always runs the STRICT build's kernel (trace_strict.cu: -fmad=false, the
+// reference's operation order), also when the main pass was a tolerance-mode kernel of the fast build: a ray that
+// is listed because one of its decisions fell inside a guard band (trace_fx.cuh) gets the reference's decision.
 inline void launch_fixup(const FwdParams<double>& P, unsigned grid, int block, size_t smem, cudaStream_t stream) {
+#ifdef OLRT_FX
+  olrt_strict::fixup_raw_f64(&P, sizeof(P), grid, block, smem, stream);   // same struct layout in both namespaces
+#else
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(trace_fwd_kernel<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   trace_fwd_kernel<double, true><<<grid, block, smem, stream>>>(P);
+#endif
 }
 inline void launch_fixup(const FwdParams<float>&, unsigned, int, size_t, cudaStream_t) {}
 

@@ -1,5 +1,6 @@
 // Strict build: compiled with -fmad=false so that every + - * / sqrt rounds exactly where the
 // reference's NumPy float64 expression rounds (bit-identical vignetting masks).
+#include <cstring>
 #define OLRT_NS olrt_strict
 #include "trace_launch.cuh"
 #include "olrt_internal.h"
@@ -9,6 +10,14 @@ int fwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, long l
             const double* const in[8], const double* opd_in, double* const out[8], double* record,
             double* dir0, unsigned long long* nr_resid, uint32_t* status, uint32_t* fixup, int flags, cudaStream_t stream) {
   return launch_fwd<double>(sys, presc, ops, n_rays, in, opd_in, out, record, dir0, nr_resid, status, fixup, flags, stream);
+}
+
+int fixup_raw_f64(const void* params, size_t bytes, unsigned grid, int block, size_t smem, cudaStream_t stream) {
+  FwdParams<double> P;
+  if (bytes != sizeof(P)) return OLRT_E_ARG;
+  memcpy(&P, params, sizeof(P));
+  launch_fixup(P, grid, block, smem, stream);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
 }
 
 __global__ void selftest_math_kernel(const double* a, const double* b, double* q, double* r, long long n) {

@@ -74,11 +74,16 @@ def test_strict_bit_exact_with_dead_rays(lens_name, n):
 @pytest.mark.parametrize("lens_name,n", [("CookeTriplet", 200_000), ("DoubleGauss", 100_000),
                                          ("EvenAsphereDoubleGauss", 100_000), ("AsphericSinglet", 50_000)])
 def test_tolerance_mode_with_dead_rays(lens_name, n):
-    """OLRT_FWD_FAST (reduced-algebra kernel) on the same wild batches. The bar is a tolerance, and these rays
-    are far outside any clear aperture: a ray within rounding of a miss / TIR boundary is ill-conditioned for ANY
-    evaluation order (sqrt of a difference that cancels to ~0), so the test states what it measures:
-      * NaN pattern and vignetting mask identical except for at most 5e-5 of the rays (boundary rays),
-      * every other ray within 1e-10 except at most 1e-4 of them (conditioning), none beyond 1e-6."""
+    """OLRT_FWD_FAST (reduced-algebra kernel) on the same wild batches: 2 - 98 % of the rays miss a surface, are
+    totally reflected or are vignetted. What is asserted:
+      * NaN pattern and vignetting mask IDENTICAL to the reference's for every ray and every surface on the
+        closed-form lenses: a ray whose hit / miss, TIR, clip or root decision falls inside a guard band is re-traced
+        by the strict IEEE kernel (trace_fx.cuh, "DECISIONS"), so the stored decision is the reference's. On the
+        even-asphere lenses the reference itself evaluates r2**3 with libm pow() (not reproducible bit for bit, see
+        test_strict_bit_exact_with_dead_rays) and, with dead rays in the batch, runs all 100 Newton updates: the
+        same <= 5e-5 of wild boundary rays as in strict mode may differ there;
+      * values: within 1e-10 except at most 1e-4 of the rays (wild rays that are ill-conditioned for any evaluation
+        order: sqrt of a difference that cancels to ~0), none beyond 1e-6."""
     lens = getattr(samples, lens_name)()
     lens.surface_group.surfaces[2].aperture = RadialAperture(r_max=7.5, r_min=0.25)
     wl = lens.wavelengths
@@ -90,7 +95,12 @@ def test_tolerance_mode_with_dead_rays(lens_name, n):
     torch.cuda.synchronize()
     rec = res.record.cpu().numpy()
     bad = (np.isnan(rec) != np.isnan(ref)).any(axis=(0, 1)) | ((rec[:, 6] == 0) != (ref[:, 6] == 0)).any(axis=0)
-    assert bad.mean() <= 5e-5, int(bad.sum())
+    if lens_name in ("CookeTriplet", "DoubleGauss"):
+        assert int(bad.sum()) == 0, int(bad.sum())
+    else:
+        assert bad.mean() <= 5e-5, int(bad.sum())
+    dead = np.isnan(ref[-1, 0])
+    assert 0.02 < dead.mean() < 0.98 and (ref[:, 6] == 0).any()
     rec, ref = rec[:, :, ~bad], ref[:, :, ~bad]
     m = ~np.isnan(ref)
     err = np.zeros_like(ref)
