@@ -150,7 +150,10 @@ const char* olrt_build_info(void);
  *  record     NULL or [n_record][8][n_rays]: x y z L M N intensity opd after each recorded surface
  *  dir0       NULL or [3][n_rays]: L0 M0 N0, local pre-interaction direction at the last surface
  *  nr_resid   NULL or [n_surfaces][OLRT_RESID_STRIDE] u64-ordered doubles, zero-initialised by the
- *             caller: max over rays of |f| seen at Newton iteration j (NaN recorded as +inf)
+ *             caller: a value v_j per Newton iteration j with  v_j < tol  <=>  every ray had |f_j| < tol  (the
+ *             reference's exit test, newton_raphson.py:148), and v_j = +inf when a ray's f_j was NaN. The strict
+ *             kernels and the fix-up pass store the maximum of |f_j|; the tolerance-mode kernel stores 1e300 where
+ *             some ray failed the test and leaves 0 otherwise (one compare per ray instead of a running maximum)
  *  status     NULL or one uint32, OR-accumulated
  *  fixup      [1 + n_rays] uint32 workspace, required by _f64 (ignored by _f32): the main kernel uses
  *             unguarded division / square-root sequences and lists the rays whose result came out

@@ -40,6 +40,7 @@ namespace OLRT_NS {
 #define OLRT_FX_MIN_BLOCKS_F32 3
 #endif
 
+#define OLRT_RESID_FAILED 0x7E37E43C8800759CULL   /* bits of 1e300: "some ray failed |f| < tol" (nr_resid, bits mode) */
 #define OLRT_FX_GHI 0x3DB00000   /* high word of 2^-36: the guard band of every decision (see DECISIONS) */
 template <typename R> struct FxMath;
 template <> struct FxMath<double> {
@@ -133,7 +134,7 @@ template <typename R> struct __align__(16) FxSurf {
   R iR, c1;         // 1/R, 1+k
   R k, c1iR2;       // k, (1+k)/R^2
   R rmax2, rmin2;   // radial aperture (r_max^2, r_min^2)
-  R twoR, pad;
+  R twoR, tol;      // 2 R; Newton exit tolerance (newton_raphson.py:148)
   R gmax, gmin;     // guard bands of the aperture test: 2^-36 r_max^2, 2^-36 r_min^2
 };
 #define OLRT_FX_GB 1.4551915228366852e-11      /* 2^-36 */
@@ -177,7 +178,7 @@ __device__ __forceinline__ void fx_build_surface(const int32_t* s_ops, const R* 
   sf.iR = R(1) / radius;
   sf.c1iR2 = (R(1) + k) / (radius * radius);
   sf.twoR = R(2) * radius;
-  sf.pad = R(0);
+  sf.tol = g[2];
   int kind = s_info[s].kind & 15;
   if (is_pos_zero(f[0]) && is_pos_zero(f[1])) kind |= FX_CENTERED;
   if (op[OLRT_OP_INTERACT] == 1) kind |= FX_REFLECT;
@@ -363,7 +364,7 @@ __device__ __forceinline__ void fx_conic(RayState<R>& r, const FxSurf<R>& sf, co
 template <typename R>
 __device__ __forceinline__ void fx_even(RayState<R>& r, const FxSurf<R>& sf, const FxMedium<R>& md, int kind,
                                         const FxInfo& info, int K, const R* coef, bool valid,
-                                        unsigned long long* resid, R& att, int& guard) {
+                                        unsigned long long* resid, unsigned* rbits, R& att, int& guard) {
   typedef FxMath<R> Mx;
   fx_localize(r, sf, kind);
   R t = fx_conic_t(r.x, r.y, r.z, r.L, r.M, r.N, sf, (kind & FX_SPHERE) != 0, guard);
@@ -394,9 +395,14 @@ __device__ __forceinline__ void fx_even(RayState<R>& r, const FxSurf<R>& sf, con
     zx = xi * g; zy = yi * g;
     fp = fma(zx, r.L, fma(zy, r.M, -r.N));
     const bool lastj = (j >= K);
-    if (lastj && resid == nullptr) break;
+    if (lastj && resid == nullptr && rbits == nullptr) break;
     const R f = fma(r2, Q, (r2 * sf.iR) * Mx::rcp(R(1) + q)) - zi;
-    if (resid != nullptr) {  // NaN: the fix-up pass (IEEE) reports it
+    if (rbits != nullptr) {
+      // the reference's exit test is max_rays |f_j| < tol (newton_raphson.py:148): what the host needs per iteration
+      // is whether SOME ray fails it -- one bit per (surface, iteration) kept in a register for the whole launch.
+      // NaN compares false here: the fix-up pass (IEEE) reports that ray.
+      if (valid && r_abs(f) >= sf.tol) *rbits |= 1u << (info.roff + j);
+    } else if (resid != nullptr) {  // NaN: the fix-up pass (IEEE) reports it
       const unsigned long long key = (valid && f == f) ? resid_bits((double)r_abs(f)) : 0ull;
       report_resid(resid + j, key);
     }
@@ -442,9 +448,15 @@ __device__ __forceinline__ void fx_spot_flush(double* spot, int g, double cnt, d
   }
 }
 
-template <typename R>
+// MODE (compile time, so that a launch carries only the code and registers of what it was asked for):
+//   bit 0  Newton verification: the residual reports (nr_resid / group_resid)
+//   bit 1  per-surface stores: [S][8][N] records or tile-blocked checkpoints
+//   bit 2  (with bit 0) the reports are running maxima in shared memory (per-group counts, or more than 32
+//          residual slots); without it they are one bit per (surface, iteration) in a register
+template <typename R, int MODE>
 __global__ void __launch_bounds__(OLRT_FX_BLOCK, (sizeof(R) == 4 ? OLRT_FX_MIN_BLOCKS_F32 : OLRT_FX_MIN_BLOCKS))
 trace_fx_kernel(const FwdParams<R> P) {
+  constexpr bool M_VERIFY = (MODE & 1) != 0, M_STORES = (MODE & 2) != 0, M_MAXIMA = (MODE & 4) != 0;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int S = P.n_surfaces, W = P.n_wavelengths;
   R* s_presc = reinterpret_cast<R*>(smem_raw);
@@ -462,8 +474,8 @@ trace_fx_kernel(const FwdParams<R> P) {
   if (threadIdx.x == 0) s_bad = 0;
   __syncthreads();
   // group mode: per-(trial, field) Newton trip counts and residual maxima (FwdParams::group_k)
-  const bool gmode = (P.gen.px != nullptr) && (P.group_k != nullptr);
-  const bool want_resid = gmode ? (P.group_resid != nullptr) : (P.nr_resid != nullptr);
+  const bool gmode = M_MAXIMA && (P.gen.px != nullptr) && (P.group_k != nullptr);   // launch_fwd picks the variant
+  const bool want_resid = M_VERIFY && (gmode ? (P.group_resid != nullptr) : (P.nr_resid != nullptr));
   if (threadIdx.x < S) {
     const int k = fk_kind(s_ops, threadIdx.x);
     s_info[threadIdx.x].kind = k;
@@ -487,6 +499,12 @@ trace_fx_kernel(const FwdParams<R> P) {
   const int n_resid = s_nresid;
   for (int q = threadIdx.x; q < n_resid; q += blockDim.x) s_resid[q] = 0ull;
   __syncthreads();
+  // Newton verification by bits (batch-global counts, <= 32 residual slots): a thread ORs "some ray of mine failed
+  // |f_j| < tol" into one register; the warps merge at the end of the launch and store OLRT_RESID_FAILED (a huge
+  // finite value) in the failing slots of nr_resid -- the host's rule "first j with nr_resid[j] < tol" reads the
+  // same counts from it as from the true maxima, which the strict kernels and the fix-up pass store
+  const bool bits_mode = M_VERIFY && !M_MAXIMA && want_resid;   // launch_fwd: not group mode, n_resid <= 32
+  unsigned rbits = 0u;
 
   uint32_t status = 0;
   int cur_p = -1, cur_g = -1;
@@ -515,8 +533,8 @@ trace_fx_kernel(const FwdParams<R> P) {
   }
   // fused spot epilogue: per-thread sums for the current group, flushed when the group changes
   const bool want_spot = (P.spot != nullptr);
-  const bool rec_on = (P.record != nullptr);
-  const bool ck_on = (P.ckpt != nullptr);   // array mode, 256-thread tiles (launch_fwd checks)
+  const bool rec_on = M_STORES && (P.record != nullptr);
+  const bool ck_on = M_STORES && (P.ckpt != nullptr);   // array mode, 256-thread tiles (launch_fwd checks)
   int sp_g = -1;
   double sp_cnt = 0, sp_x = 0, sp_y = 0, sp_xx = 0, sp_yy = 0, sp_i = 0, sp_max = 0, sp_sx = 0, sp_sy = 0;
   bool sp_nan = false;
@@ -622,15 +640,18 @@ trace_fx_kernel(const FwdParams<R> P) {
         case 5: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED, att, guard); break;
         case 6:
           fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED | FX_SPHERE, info, gmode ? s_gk[s] : info.K,
-                     s_coef + info.coef_off, valid, want_resid ? (s_resid + info.roff) : nullptr, att, guard);
+                     s_coef + info.coef_off, valid, (M_MAXIMA && want_resid) ? (s_resid + info.roff) : nullptr,
+                     bits_mode ? &rbits : nullptr, att, guard);
           break;
         case 7:
           fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED, info, gmode ? s_gk[s] : info.K, s_coef + info.coef_off,
-                     valid, want_resid ? (s_resid + info.roff) : nullptr, att, guard);
+                     valid, (M_MAXIMA && want_resid) ? (s_resid + info.roff) : nullptr, bits_mode ? &rbits : nullptr,
+                     att, guard);
           break;
         default:
           fx_even<R>(r, sf, md, kind, info, gmode ? s_gk[s] : info.K, s_coef + info.coef_off, valid,
-                     want_resid ? (s_resid + info.roff) : nullptr, att, guard);
+                     (M_MAXIMA && want_resid) ? (s_resid + info.roff) : nullptr, bits_mode ? &rbits : nullptr, att,
+                     guard);
           break;
       }
       if (!rec_on && !ck_on) continue;
@@ -702,7 +723,16 @@ trace_fx_kernel(const FwdParams<R> P) {
   if (want_spot && sp_g >= 0) fx_spot_flush(P.spot, sp_g, sp_cnt, sp_x, sp_y, sp_xx, sp_yy, sp_i, sp_max, sp_nan);
 
   __syncthreads();
-  if (gmode) {
+  if (bits_mode) {
+    rbits = __reduce_or_sync(0xffffffffu, rbits);
+    if ((threadIdx.x & 31) == 0 && rbits != 0u) {
+      for (int s = 0; s < S; ++s) {
+        const int lo = s_info[s].roff, hi = (s + 1 < S) ? s_info[s + 1].roff : n_resid;
+        for (int q = lo; q < hi; ++q)
+          if (rbits & (1u << q)) atomicMax(P.nr_resid + (long long)s * OLRT_RESID_STRIDE + (q - lo), OLRT_RESID_FAILED);
+      }
+    }
+  } else if (gmode) {
     if (want_resid && cur_g >= 0) fx_group_flush(P.group_resid, cur_g, S, s_resid);
   } else if (want_resid) {
     for (int s = 0; s < S; ++s) {

@@ -112,9 +112,19 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
     const size_t xsmem = fx_smem_bytes<R>(sys->presc_stride, sys->n_surfaces, sys->n_wavelengths, sys->ops_len,
                                           resid_words);
     if (xsmem > 200 * 1024) return OLRT_E_LIMIT;
-    if (xsmem > 48 * 1024)
-      cudaFuncSetAttribute(trace_fx_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xsmem);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fx_kernel<R>, block, xsmem);
+    // group mode without residual reports still needs the per-group trip counts: the maxima variant carries them
+    const bool verify = nr_resid != nullptr || P.group_resid != nullptr;
+    const bool maxima = P.group_k != nullptr || resid_words > 32;
+    const int mode = ((verify || P.group_k != nullptr) ? 1 : 0) | ((P.record != nullptr || P.ckpt != nullptr) ? 2 : 0) |
+                     (((verify || P.group_k != nullptr) && maxima) ? 4 : 0);
+    void (*kern)(const FwdParams<R>) = (mode == 0)   ? trace_fx_kernel<R, 0>
+                                       : (mode == 1) ? trace_fx_kernel<R, 1>
+                                       : (mode == 2) ? trace_fx_kernel<R, 2>
+                                       : (mode == 3) ? trace_fx_kernel<R, 3>
+                                       : (mode == 5) ? trace_fx_kernel<R, 5>
+                                                     : trace_fx_kernel<R, 7>;
+    if (xsmem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xsmem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, xsmem);
     if (per_sm < 1) per_sm = 1;
     long long grid = (long long)sm_count() * per_sm;
     if (grid > n_tiles) grid = n_tiles;
@@ -125,7 +135,7 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
       grid = grid / gen->n_fields * gen->n_fields;
       if (grid < gen->n_fields) grid = gen->n_fields;
     }
-    trace_fx_kernel<R><<<(unsigned)grid, block, xsmem, stream>>>(P);
+    kern<<<(unsigned)grid, block, xsmem, stream>>>(P);
 #endif
   } else if (fk) {
     if (smem > 48 * 1024)

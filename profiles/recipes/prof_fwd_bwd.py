@@ -44,6 +44,10 @@ iters = pk_plain.nr_iters()
 out_buf = torch.empty((8, n), dtype=torch.float64, device=dev)
 t_plain = tm(lambda: fused_trace(pk_plain, ins, fast=True, verify_nr=False, check_status=False, out=out_buf))
 print(f"{which} n={n} S={S} K={iters}: fwd (no checkpoints) {t_plain:.3f} ms")
+from optiland_pr_b200 import _lib as L
+resid = torch.zeros((pk_plain.n_surfaces, L.RESID_STRIDE), dtype=torch.int64, device=dev)
+t_ver = tm(lambda: (resid.zero_(), fused_trace(pk_plain, ins, fast=True, check_status=False, out=out_buf, resid_out=resid)))
+print(f"  fwd with Newton verification (residual bits): {t_ver:.3f} ms")
 for label, record, blocked, ray_grads, noxy in (("records, all grads", "all", False, True, False),
                                                 ("blocked, all grads", "none", True, True, False),
                                                 ("blocked, presc only", "none", True, False, False),
