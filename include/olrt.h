@@ -122,6 +122,10 @@ enum {
 /* kernel_hint bits */
 #define OLRT_HINT_FASTKINDS 1 /* every surface is a plane / conic / even asphere on one untilted frame,
                                 aperture none or a single RadialAperture: the straight-line kernel (trace_fk.cuh) runs */
+#define OLRT_HINT_ORDINARY 2  /* with FASTKINDS: every surface of EVERY prescription of the batch is also centred
+                                (frame x = y = +0.0), refracting and has no aperture -- an ordinary lens. The kernels
+                                then run variants that carry only those surface bodies (smaller code, fewer registers).
+                                Verified on the device: a wrong hint sets OLRT_ST_BAD_HINT and traces nothing */
 
 typedef struct olrt_sys {
   int32_t n_surfaces;     /* intersected surfaces */
@@ -210,7 +214,8 @@ int olrt_trace_fwd_noalloc_f64(const olrt_sys* sys /*host*/, const double* presc
 /* Tile-blocked checkpoints (differentiable trace without user-visible records): with OLRT_FWD_CKPT_BLOCKED the
  * forward's `record` argument is a buffer of ceil(n_rays / 256) * n_surfaces * 7 * 256 reals laid out
  * [tile][surface][x y z L M N intensity][256]: the state after every surface, 56 B per ray and surface, one
- * contiguous 14 KB block per (256-ray tile, surface). (Leaving the planes out and recomputing their exit states in
+ * contiguous 14 KB block per (256-ray tile, surface). A plane as the LAST surface (the image plane) is the one
+ * exception: its block is never written nor read (nothing needs its exit state). (Leaving ALL the planes out and recomputing their exit states in
  * the backward was measured: -224 B per ray of traffic but +160 instructions per ray in kernels that are
  * issue-bound, not bandwidth-bound: slower. DESIGN.md section 5.)
  * olrt_sys.n_record must be 0 (no [S][8][N] records in the same

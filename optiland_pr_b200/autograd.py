@@ -78,7 +78,7 @@ class FusedTraceFn(torch.autograd.Function):
         res = fused_trace(packed, [t.detach() if t is not None else None for t in ins],
                           opd_in=None if opd_in is None else opd_in.detach(),
                           presc=presc.detach().reshape(1, -1), want_dir0=True, fast=fast, alias_out=True,
-                          ckpt=blocked)
+                          ckpt=blocked, own_rows=True)   # the row was assembled from this very pack
         if blocked and max(res.nr_iters, default=0) > L.BX_MAXK:
             raise NotImplementedError("blocked checkpoints: a surface took more than 3 Newton updates")
         ctx.blocked = bool(blocked)

@@ -418,7 +418,9 @@ template <> __device__ __forceinline__ float bx_lds<float>(unsigned base, int el
 // warps of a CTA coupled to its slowest one -- per-thread copies keep the warps independent.)
 // NOXY: the caller does not want d loss / d (frame x, frame y) (OLRT_BWD_NO_FRAME_XY: no decenter is a variable):
 // two of a curved surface's five shared-memory accumulations less.
-template <typename R, int BD, bool CK, bool NOXY>
+// ORD: every surface is centred, refracting and aperture-free (OLRT_HINT_ORDINARY, verified below): only those
+// surface bodies are compiled into the variant.
+template <typename R, int BD, bool CK, bool NOXY, bool ORD>
 __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const BwdParams<R> P, uint32_t* status) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ FxSurf<R> s_surf[OLRT_MAX_SURFACES];
@@ -478,8 +480,13 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
         fx_build_surface<R>(s_ops, s_presc, s_surf, s_med, s_info, s_coef, threadIdx.x, S, W, P.wavelengths,
                             P.four_pi);
         s_info[threadIdx.x].pad0 = s_ops[threadIdx.x * OLRT_OPS_STRIDE + OLRT_OP_NCOEF];  // unpadded count
+        if (ORD && s_info[threadIdx.x].pad1 < 3) s_bad = 1;   // the hint claimed an ordinary lens
       }
       __syncthreads();
+      if (ORD && s_bad) {   // CTA-uniform: nothing is written for a wrong hint
+        if (threadIdx.x == 0 && status != nullptr) atomicOr(status, OLRT_ST_BAD_HINT);
+        return;
+      }
     }
     const long long item = base + threadIdx.x;
     const bool valid = item < N;
@@ -493,9 +500,12 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
     // state after the last surface, then the entry state of surface S-1 (= record S-2; the launch state for S == 1)
     const R* rp = CK ? P.record + (tile * S + (S - 1)) * (long long)(7 * bd) + threadIdx.x  // block of surface S-1
                      : P.record + (long long)(S - 1) * 8 * N + idx;
-    R Qgx, Qgy, Qgz, irec;
+    // CK: a plane as the last surface has no checkpoint (olrt.h): bx_plane needs no exit point, and its intensity
+    // factor is computed directly (z0p below) instead of from the exit intensity
+    const bool last_plane = CK && (s_info[S - 1].kind & 15) == KIND_PLANE;
+    R Qgx = R(0), Qgy = R(0), Qgz = R(0), irec = R(0);
     if (CK) {
-      Qgx = rp[0]; Qgy = rp[bd]; Qgz = rp[2 * bd]; irec = rp[6 * bd];
+      if (!last_plane) { Qgx = rp[0]; Qgy = rp[bd]; Qgz = rp[2 * bd]; irec = rp[6 * bd]; }
     } else {
       Qgx = rp[0]; Qgy = rp[N]; Qgz = rp[2 * N]; irec = rp[6 * N];
     }
@@ -545,9 +555,10 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
       R* acc = s_acc + s * (OLRT_BWD_SLOTS * OLRT_BX_COLS) + col;
       // the per-kind bodies take the flag word as a parameter: the dense variant id of fx_build_surface lets an
       // ordinary lens surface (centred, refracting, no aperture) pass its flags as a compile-time constant
+      const bool z0p = z0 || (last_plane && s == S - 1);
       auto do_plane = [&](const int kk) {
         R gTz;
-        bx_plane<R>(sf, md, kk, z0, ez, eL, eM, eN, ei, irec, ex, ey, gx, gy, gz, gL, gM, gN, gi, gopd, gTz);
+        bx_plane<R>(sf, md, kk, z0p, ez, eL, eM, eN, ei, irec, ex, ey, gx, gy, gz, gL, gM, gN, gi, gopd, gTz);
         atomicAdd(acc + 2 * OLRT_BX_COLS, gTz);
       };
       auto do_conic = [&](const int kk) {
@@ -571,15 +582,25 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
         if (m4 > 0) bx_add_n<4>(acc + 5 * OLRT_BX_COLS, gC);
         if (m4 > 4) bx_add_n<4>(acc + 9 * OLRT_BX_COLS, gC + 4);
       };
-      switch (info.pad1) {  // warp-uniform, dense
-        case 0: do_plane(kind); break;
-        case 1: do_conic(kind); break;
-        case 3: do_plane(KIND_PLANE | FX_CENTERED); break;
-        case 4:
-        case 5: do_conic(KIND_CONIC | FX_CENTERED); break;
-        case 6: do_even(KIND_EVEN | FX_CENTERED | FX_SPHERE); break;
-        case 7: do_even(KIND_EVEN | FX_CENTERED); break;
-        default: do_even(kind); break;
+      if (ORD) {
+        switch (info.pad1) {  // warp-uniform
+          case 3: do_plane(KIND_PLANE | FX_CENTERED); break;
+          case 4:
+          case 5: do_conic(KIND_CONIC | FX_CENTERED); break;
+          case 6: do_even(KIND_EVEN | FX_CENTERED | FX_SPHERE); break;
+          default: do_even(KIND_EVEN | FX_CENTERED); break;
+        }
+      } else {
+        switch (info.pad1) {  // warp-uniform, dense
+          case 0: do_plane(kind); break;
+          case 1: do_conic(kind); break;
+          case 3: do_plane(KIND_PLANE | FX_CENTERED); break;
+          case 4:
+          case 5: do_conic(KIND_CONIC | FX_CENTERED); break;
+          case 6: do_even(KIND_EVEN | FX_CENTERED | FX_SPHERE); break;
+          case 7: do_even(KIND_EVEN | FX_CENTERED); break;
+          default: do_even(kind); break;
+        }
       }
       Qgx = ex; Qgy = ey; Qgz = ez; irec = ei;
     }
@@ -598,19 +619,19 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
   if (cur_p >= 0) bx_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
 }
 
-template <typename R, int BD, bool CK, bool NOXY>
+template <typename R, int BD, bool CK, bool NOXY, bool ORD>
 int bx_launch_kernel(const BwdParams<R>& P, int block, size_t smem, long long n_tiles, uint32_t* status,
                      cudaStream_t stream) {
   // static tables (16 KB) + dynamic can pass the 48 KB default even when the dynamic part alone does not
-  cudaFuncSetAttribute(trace_bx_kernel<R, BD, CK, NOXY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaFuncSetAttribute(trace_bx_kernel<R, BD, CK, NOXY, ORD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   int per_sm = 0, dev = 0, sms = 148;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_bx_kernel<R, BD, CK, NOXY>, block, smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_bx_kernel<R, BD, CK, NOXY, ORD>, block, smem);
   if (per_sm < 1) per_sm = 1;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   long long grid = (long long)sms * per_sm;
   if (grid > n_tiles) grid = n_tiles;
-  trace_bx_kernel<R, BD, CK, NOXY><<<(unsigned)grid, block, smem, stream>>>(P, status);
+  trace_bx_kernel<R, BD, CK, NOXY, ORD><<<(unsigned)grid, block, smem, stream>>>(P, status);
   return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
 }
 
@@ -642,14 +663,20 @@ int launch_bx(const olrt_sys* sys, const R* presc, const int32_t* ops, long long
   const long long n_tiles = (n_rays + block - 1) / block;
   if (flags & OLRT_BWD_CKPT_BLOCKED) {  // `record` is the tile-blocked checkpoint buffer of the forward
     if (block != OLRT_CKPT_TILE || sys->n_presc > 1 || grecord != nullptr) return OLRT_E_UNSUPPORTED;
-    if (flags & OLRT_BWD_NO_FRAME_XY) return bx_launch_kernel<R, 256, true, true>(P, block, smem, n_tiles, status, stream);
-    return bx_launch_kernel<R, 256, true, false>(P, block, smem, n_tiles, status, stream);
+    const bool noxy = (flags & OLRT_BWD_NO_FRAME_XY) != 0, ord = (sys->kernel_hint & OLRT_HINT_ORDINARY) != 0;
+    if (noxy && ord) return bx_launch_kernel<R, 256, true, true, true>(P, block, smem, n_tiles, status, stream);
+    if (noxy) return bx_launch_kernel<R, 256, true, true, false>(P, block, smem, n_tiles, status, stream);
+    if (ord) return bx_launch_kernel<R, 256, true, false, true>(P, block, smem, n_tiles, status, stream);
+    return bx_launch_kernel<R, 256, true, false, false>(P, block, smem, n_tiles, status, stream);
   }
   if (block == 256) {
-    if (flags & OLRT_BWD_NO_FRAME_XY) return bx_launch_kernel<R, 256, false, true>(P, block, smem, n_tiles, status, stream);
-    return bx_launch_kernel<R, 256, false, false>(P, block, smem, n_tiles, status, stream);
+    const bool noxy = (flags & OLRT_BWD_NO_FRAME_XY) != 0, ord = (sys->kernel_hint & OLRT_HINT_ORDINARY) != 0;
+    if (noxy && ord) return bx_launch_kernel<R, 256, false, true, true>(P, block, smem, n_tiles, status, stream);
+    if (noxy) return bx_launch_kernel<R, 256, false, true, false>(P, block, smem, n_tiles, status, stream);
+    if (ord) return bx_launch_kernel<R, 256, false, false, true>(P, block, smem, n_tiles, status, stream);
+    return bx_launch_kernel<R, 256, false, false, false>(P, block, smem, n_tiles, status, stream);
   }
-  return bx_launch_kernel<R, 0, false, false>(P, block, smem, n_tiles, status, stream);
+  return bx_launch_kernel<R, 0, false, false, false>(P, block, smem, n_tiles, status, stream);
 }
 
 }  // namespace OLRT_NS

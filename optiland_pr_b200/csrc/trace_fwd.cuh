@@ -308,7 +308,8 @@ __device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r,
       rec[3 * NT] = r.L; rec[4 * NT] = r.M; rec[5 * NT] = r.N;
       rec[6 * NT] = r.i; rec[7 * NT] = r.opd;
     }
-    if (P.ckpt != nullptr && valid) {  // blocked checkpoint of this ray (the fix-up pass repairs single rays)
+    if (P.ckpt != nullptr && valid && !(s == S - 1 && s_kind[s] == KIND_PLANE)) {
+      // blocked checkpoint of this ray (the fix-up pass repairs single rays; a last plane has none, olrt.h)
       R* ck = P.ckpt + (((idx / OLRT_CKPT_TILE) * S + s) * 7) * OLRT_CKPT_TILE + (idx % OLRT_CKPT_TILE);
       ck[0] = r.x; ck[OLRT_CKPT_TILE] = r.y; ck[2 * OLRT_CKPT_TILE] = r.z;
       ck[3 * OLRT_CKPT_TILE] = r.L; ck[4 * OLRT_CKPT_TILE] = r.M; ck[5 * OLRT_CKPT_TILE] = r.N;

@@ -451,12 +451,15 @@ __device__ __forceinline__ void fx_spot_flush(double* spot, int g, double cnt, d
 // MODE (compile time, so that a launch carries only the code and registers of what it was asked for):
 //   bit 0  Newton verification: the residual reports (nr_resid / group_resid)
 //   bit 1  per-surface stores: [S][8][N] records or tile-blocked checkpoints
+//   bit 3  every surface is centred, refracting and aperture-free (OLRT_HINT_ORDINARY, verified on the device):
+//          only those surface bodies are compiled in
 //   bit 2  (with bit 0) the reports are running maxima in shared memory (per-group counts, or more than 32
 //          residual slots); without it they are one bit per (surface, iteration) in a register
 template <typename R, int MODE>
 __global__ void __launch_bounds__(OLRT_FX_BLOCK, (sizeof(R) == 4 ? OLRT_FX_MIN_BLOCKS_F32 : OLRT_FX_MIN_BLOCKS))
 trace_fx_kernel(const FwdParams<R> P) {
   constexpr bool M_VERIFY = (MODE & 1) != 0, M_STORES = (MODE & 2) != 0, M_MAXIMA = (MODE & 4) != 0;
+  constexpr bool M_ORD = (MODE & 8) != 0;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int S = P.n_surfaces, W = P.n_wavelengths;
   R* s_presc = reinterpret_cast<R*>(smem_raw);
@@ -632,34 +635,39 @@ trace_fx_kernel(const FwdParams<R> P) {
       const FxMedium<R>& md = s_med[s * W + widx];
       const FxInfo& info = s_info[s];
       const int kind = info.kind;
-      switch (info.pad1) {  // warp-uniform, dense (fx_build_surface)
-        case 0: fx_plane<R>(r, sf, md, kind, att, guard); break;
-        case 1: fx_conic<R>(r, sf, md, kind, att, guard); break;
-        case 3: fx_plane<R>(r, sf, md, KIND_PLANE | FX_CENTERED, att, guard); break;
-        case 4: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED | FX_SPHERE, att, guard); break;
-        case 5: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED, att, guard); break;
-        case 6:
-          fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED | FX_SPHERE, info, gmode ? s_gk[s] : info.K,
-                     s_coef + info.coef_off, valid, (M_MAXIMA && want_resid) ? (s_resid + info.roff) : nullptr,
-                     bits_mode ? &rbits : nullptr, att, guard);
-          break;
-        case 7:
-          fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED, info, gmode ? s_gk[s] : info.K, s_coef + info.coef_off,
-                     valid, (M_MAXIMA && want_resid) ? (s_resid + info.roff) : nullptr, bits_mode ? &rbits : nullptr,
-                     att, guard);
-          break;
-        default:
-          fx_even<R>(r, sf, md, kind, info, gmode ? s_gk[s] : info.K, s_coef + info.coef_off, valid,
-                     (M_MAXIMA && want_resid) ? (s_resid + info.roff) : nullptr, bits_mode ? &rbits : nullptr, att,
-                     guard);
-          break;
+      const int Ks = gmode ? s_gk[s] : info.K;
+      unsigned long long* const rs = (M_MAXIMA && want_resid) ? (s_resid + info.roff) : nullptr;
+      unsigned* const rb = bits_mode ? &rbits : nullptr;
+      const R* const cf = s_coef + info.coef_off;
+      if (M_ORD) {  // ordinary lens: centred, refracting, aperture-free surfaces only (warp-uniform switch)
+        switch (info.pad1) {
+          case 3: fx_plane<R>(r, sf, md, KIND_PLANE | FX_CENTERED, att, guard); break;
+          case 4: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED | FX_SPHERE, att, guard); break;
+          case 5: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED, att, guard); break;
+          case 6: fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED | FX_SPHERE, info, Ks, cf, valid, rs, rb, att, guard); break;
+          case 7: fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED, info, Ks, cf, valid, rs, rb, att, guard); break;
+          default: status |= OLRT_ST_BAD_HINT; r.x = R(0) / R(0); break;   // the hint was wrong: nothing usable comes out
+        }
+      } else {
+        switch (info.pad1) {  // warp-uniform, dense (fx_build_surface)
+          case 0: fx_plane<R>(r, sf, md, kind, att, guard); break;
+          case 1: fx_conic<R>(r, sf, md, kind, att, guard); break;
+          case 3: fx_plane<R>(r, sf, md, KIND_PLANE | FX_CENTERED, att, guard); break;
+          case 4: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED | FX_SPHERE, att, guard); break;
+          case 5: fx_conic<R>(r, sf, md, KIND_CONIC | FX_CENTERED, att, guard); break;
+          case 6: fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED | FX_SPHERE, info, Ks, cf, valid, rs, rb, att, guard); break;
+          case 7: fx_even<R>(r, sf, md, KIND_EVEN | FX_CENTERED, info, Ks, cf, valid, rs, rb, att, guard); break;
+          default: fx_even<R>(r, sf, md, kind, info, Ks, cf, valid, rs, rb, att, guard); break;
+        }
       }
       if (!rec_on && !ck_on) continue;
       if (md.nalpha != R(0)) i_stale = true;
       if (ck_on) {  // tile-blocked checkpoint: the state after this surface, immediate offsets from one pointer
         if (i_stale) { i_rec = fx_intensity(r.i, att); i_stale = false; }
         else if (!(r.i != R(0))) i_rec = r.i;
-        if (valid) {
+        // a plane as the LAST surface (the image plane) is not checkpointed: nothing downstream needs its exit state
+        // and the backward computes the plane's own intensity factor directly (trace_bx.cuh, z0p)
+        if (valid && !(s == S - 1 && (kind & 15) == KIND_PLANE)) {
           R* ckp = ck_ptr + (long long)s * (7 * OLRT_CKPT_TILE);
           __stcs(ckp, r.x); __stcs(ckp + OLRT_CKPT_TILE, r.y); __stcs(ckp + 2 * OLRT_CKPT_TILE, r.z);
           __stcs(ckp + 3 * OLRT_CKPT_TILE, r.L); __stcs(ckp + 4 * OLRT_CKPT_TILE, r.M);

@@ -117,12 +117,20 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
     const bool maxima = P.group_k != nullptr || resid_words > 32;
     const int mode = ((verify || P.group_k != nullptr) ? 1 : 0) | ((P.record != nullptr || P.ckpt != nullptr) ? 2 : 0) |
                      (((verify || P.group_k != nullptr) && maxima) ? 4 : 0);
-    void (*kern)(const FwdParams<R>) = (mode == 0)   ? trace_fx_kernel<R, 0>
-                                       : (mode == 1) ? trace_fx_kernel<R, 1>
-                                       : (mode == 2) ? trace_fx_kernel<R, 2>
-                                       : (mode == 3) ? trace_fx_kernel<R, 3>
-                                       : (mode == 5) ? trace_fx_kernel<R, 5>
-                                                     : trace_fx_kernel<R, 7>;
+    const bool ord = (sys->kernel_hint & OLRT_HINT_ORDINARY) != 0 && (mode & 4) == 0;
+    void (*kern)(const FwdParams<R>) = nullptr;
+    switch (mode | (ord ? 8 : 0)) {
+      case 0: kern = trace_fx_kernel<R, 0>; break;
+      case 1: kern = trace_fx_kernel<R, 1>; break;
+      case 2: kern = trace_fx_kernel<R, 2>; break;
+      case 3: kern = trace_fx_kernel<R, 3>; break;
+      case 5: kern = trace_fx_kernel<R, 5>; break;
+      case 7: kern = trace_fx_kernel<R, 7>; break;
+      case 8: kern = trace_fx_kernel<R, 8>; break;
+      case 9: kern = trace_fx_kernel<R, 9>; break;
+      case 10: kern = trace_fx_kernel<R, 10>; break;
+      default: kern = trace_fx_kernel<R, 11>; break;
+    }
     if (xsmem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xsmem);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, xsmem);
     if (per_sm < 1) per_sm = 1;

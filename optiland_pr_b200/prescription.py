@@ -202,9 +202,28 @@ class PackedSystem:
                 return False
         return True
 
-    def make_sys(self, n_presc: int = 1, rays_per_presc: int = 0) -> "L.OlrtSys":
+    def ordinary(self) -> bool:
+        """fastkinds() and every surface centred (frame x = y = +0.0), refracting, without an aperture
+        (include/olrt.h, OLRT_HINT_ORDINARY). Judged on this object's own prescription rows."""
+        if not self.fastkinds():
+            return False
+        pz = np.float64(0.0).tobytes()
+        for k, lay in enumerate(self.layouts):
+            row = k * L.OPS_STRIDE
+            if self.ops[row + L.OP_INTERACT] != 0 or self.ops[row + L.OP_APER_OFF] >= 0:
+                return False
+            for r in range(self.presc.shape[0]):
+                if self.presc[r, lay.frames].tobytes() != pz or self.presc[r, lay.frames + 1].tobytes() != pz:
+                    return False
+        return True
+
+    def make_sys(self, n_presc: int = 1, rays_per_presc: int = 0, own_rows: bool = True) -> "L.OlrtSys":
+        """own_rows: the launch traces this object's own prescription row(s) (or a device copy with the same frame
+        x / y entries) -- only then may OLRT_HINT_ORDINARY be claimed."""
         s = L.OlrtSys()
         s.kernel_hint = L.HINT_FASTKINDS if self.fastkinds() else 0
+        if own_rows and n_presc == self.presc.shape[0] and self.ordinary():
+            s.kernel_hint |= L.HINT_ORDINARY
         s.n_surfaces = self.n_surfaces
         s.n_wavelengths = len(self.wavelengths)
         s.n_presc = n_presc

@@ -100,7 +100,7 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
                 alias_out: bool = False, ckpt: bool = False, max_relaunch: int = 24, read_fixups: bool = True, check_status: bool = True,
                 dir0_out: torch.Tensor | None = None, status_t: torch.Tensor | None = None,
                 nr_floor: bool = False, resid_out: torch.Tensor | None = None,
-                replay: bool = False) -> TraceResult:
+                replay: bool = False, own_rows: bool | None = None) -> TraceResult:
     """Trace rays through a packed system on the current CUDA device and stream.
 
     rays_in: sequence of 8 tensors x y z L M N intensity wavelength (1-D, same length, CUDA,
@@ -111,6 +111,8 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
              the caller checks them later with `slice_true_iters` (slices of one batch, optic.py).
     fast:    tolerance mode (<= 1e-10 relative to the reference, identical masks) instead of bit-faithful;
              `replay` keeps the reference's operation order even then (A/B measurements; fp32 too).
+    own_rows: `presc` holds `packed`'s own row (same frame x / y entries), so the OLRT_HINT_ORDINARY judged on
+             `packed` applies (default: only when `presc` is None).
     nr_floor: this call traces one SLICE of a larger batch: never lower the Newton trip counts below the
              ones in `packed` (another slice may need them), only raise them; the counts this slice alone
              would have needed come back in `TraceResult.nr_true`.
@@ -182,7 +184,8 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
             elif nr_rows and verify_nr:
                 resid = torch.zeros((packed.n_surfaces, L.RESID_STRIDE), dtype=torch.int64, device=device)
                 ops_d, _ = _device_tables(packed, dtype, device)
-            sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=rays_per_presc)
+            sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=rays_per_presc,
+                                   own_rows=(presc is None) if own_rows is None else own_rows)
             sys_.presc_stride = int(presc_d.shape[1])
             rc = fn(C.byref(sys_), presc_d.data_ptr(), ops_d.data_ptr(), n, in_arr, _ptr(opd_in),
                     out_arr, _ptr(ckpt_buf if ckpt else record), dir0_ptr, _ptr(resid), status_t.data_ptr(),
@@ -271,7 +274,7 @@ def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, 
         n_presc = int(presc_d.shape[0])
     pu = L.OlrtPupil(Px.data_ptr(), Py.data_ptr(), field_xy.data_ptr(), _ptr(field_vig), _ptr(field_z), npup, int(p_lo), int(p_len), nf, 0,
                      float(EPD), float(EPL), float(z_start), float(wavelength), _ptr(ready), int(ready_chunk))
-    sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=nf * p_len)
+    sys_ = packed.make_sys(n_presc=n_presc, rays_per_presc=nf * p_len, own_rows=presc is None)
     sys_.presc_stride = int(presc_d.shape[1])
     n_total = n_presc * nf * npup
     fixup = _fixup_workspace(n_total, device) if dtype == torch.float64 else None
