@@ -8,10 +8,12 @@
 Workload (BASELINE.json configs[1]): the even-asphere double Gauss (S_eff = 12 intersected
 surfaces, 4 of them Newton-Raphson even aspheres), 3 fields x 16 777 216 random pupil rays at the
 primary wavelength, fp64, forward trace + RMS-spot epilogue. One step = one pass over that batch.
-`value` = rays x S_eff / time with the rays resident in HBM; `e2e` = the same through the public
-call `Optic.trace(Hx, Hy, wl, distribution=(Px, Py))` with the pupil grid in pinned HOST memory
-(host->device copy, ray generation, trace, epilogue and the device->host read of the RMS values
-all inside the timed region). Multi-GPU: rays are independent, every rank traces its own batch
+`value` = rays x S_eff / time with the pupil grid resident in HBM; `e2e` = the same through the public
+call in the reference's own shape, `Optic.trace(Hx, Hy, wl, num_rays, "random", seed)`: the named distribution
+is drawn on the device from its seed every step (NumPy's PCG64 stream), traced, reduced and the RMS values read back
+to the host -- all inside the timed region; `e2e.host_grid` is the same with the caller's own pupil grid in pinned
+HOST memory (`distribution=(Px, Py)`: 16 bytes per pupil point cross PCIe every step, streamed under the kernel).
+Multi-GPU: rays are independent, every rank traces its own batch
 (weak scaling); the only collective is an NCCL all-reduce of the [3][10] spot sums.
 
 Only the `cpu_baseline` / `extras.reference_torch_eager_cuda` legs and `--impl reference` execute oracle/: they run
@@ -433,22 +435,36 @@ def main():
     d2h = nf * _lib.SPOT_SUMS * 8 + 4 + packed.n_surfaces * _lib.RESID_STRIDE * 8
     rms_host = torch.empty(nf, dtype=torch.float64).pin_memory()
 
-    def step_e2e():
-        rr = lens.trace(Hx, Hy, WAVELENGTH, distribution=(Px_h, Py_h), spot=True)
+    def finish_e2e(rr):
         if world > 1:
             # merit exchange (one < 1 KB all-reduce), then ONE read-back of the merged sums; the statistics on the host
             rms_host.copy_(spot.spot_stats(parallel.allreduce_spot_sums(rr.spot_sums).cpu())["rms"])
         else:   # the sums came back with the status word (one pinned read-back inside Optic.trace)
             rms_host.copy_(spot.spot_stats(rr.spot_sums_host)["rms"])
 
+    def step_e2e():
+        # the reference's own call shape, Optic.trace(Hx, Hy, wavelength, num_rays, "random") (optic/optic.py:584-609 ->
+        # distribution.py:132-158): the pupil is a NAMED distribution, so what travels to the GPU is its seed -- the
+        # generator's 128-bit state -- and the points are drawn on the device (olrt_pupil_random_f64), every step
+        finish_e2e(lens.trace(Hx, Hy, WAVELENGTH, npf, "random", seed=1 + rank, spot=True))
+
+    def step_e2e_grid():
+        # the caller owns the pupil grid in (pinned) host memory: 16 bytes per pupil point cross PCIe every step
+        finish_e2e(lens.trace(Hx, Hy, WAVELENGTH, distribution=(Px_h, Py_h), spot=True))
+
     del out, Px_d, Py_d
     torch.cuda.empty_cache()
     ms_e2e = timed(step_e2e, max(2, args.steps // 2), 3)
     e2e_value = n * S_eff * world / (ms_e2e * 1e-3)
+    rms_e2e_named = rms_host.tolist()
+    ms_e2e_grid = timed(step_e2e_grid, max(2, args.steps // 2), 3)
+    h2d_named = 32 + nf * 8 * 2     # generator state + increment, the field table
 
     extras = {}
+    if args.extras:
+        extras["scaling_legs"] = scaling_legs(torch, dist, lens, packed, npf, nf, S_eff, timed, args, rank, world, dev)
     if args.extras and world == 1:
-        extras = run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64_peak)
+        extras.update(run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64_peak))
 
     if rank != 0:
         if world > 1:
@@ -465,14 +481,19 @@ def main():
                    "parallelism": f"rays sharded over {world} GPU(s), spot sums all-reduced",
                    "host_affinity": (f"each rank pinned to its GPU's NUMA CPUs ({len(numa_cpus)} on rank 0)"
                                      if numa_cpus else "default")},
-        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
+        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d_named,
                 "d2h_bytes_per_step": d2h,
-                "api": "Optic.trace(Hx, Hy, wl, distribution=(Px, Py) pinned host, spot=True) + spot.spot_stats -> host; "
-                       "the pupil copy is streamed in chunks on a side stream and overlaps the fused launch + trace + "
-                       "spot kernel of the chunks already on the device"},
+                "api": "Optic.trace(Hx, Hy, wl, num_rays, 'random', seed, spot=True) + spot.spot_stats -> host: the "
+                       "reference's call shape; the named distribution is drawn on the device from the seed (NumPy's "
+                       "PCG64 stream, bit for bit) every step, traced, reduced, and the per-field RMS read back",
+                "host_grid": {"value": n * S_eff * world / (ms_e2e_grid * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e_grid,
+                              "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                              "api": "Optic.trace(Hx, Hy, wl, distribution=(Px, Py) pinned host, spot=True): the caller's "
+                                     "own pupil grid; the copy is streamed in chunks on a side stream and overlaps the "
+                                     "fused launch + trace + spot kernel of the chunks already on the device"}},
         "gpu_launches": launches_per_step * args.steps,
         "roofline": roofline, "parity_check": parity, "clocks": clocks,
-        "rms_spot_mm": rms_resident, "rms_spot_mm_e2e": rms_host.tolist(),
+        "rms_spot_mm": rms_resident, "rms_spot_mm_e2e": rms_e2e_named, "rms_spot_mm_e2e_host_grid": rms_host.tolist(),
         "extras": extras,
     }
     if not args.no_cpu_baseline and world == 1:
@@ -494,6 +515,89 @@ def main():
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def scaling_legs(torch, dist, lens, packed, npf, nf, S_eff, timed, args, rank, world, dev):
+    """The configurations BASELINE.json names for several GPUs, run at EVERY N (N = 1 is their baseline), so that the
+    driver's per-N runs give their scaling curves:
+      strong_c2  the C2 batch at FIXED total size (3 fields x 16.7 M rays) split over the ranks by pupil range, spot
+                 sums all-reduced (the headline `value` is weak scaling: every rank its own 50 M rays);
+      c5         Monte-Carlo tolerancing, 4096 trials x 262 144 rays, trials dealt to the ranks, merits gathered
+                 (tolerancing/monte_carlo.py:60-123);
+      c4         one Adam step of the RMS-spot merit on the Cooke triplet, 3 fields x 3 wavelengths x 1 M rays, the
+                 (field, wavelength) pairs dealt round-robin to the ranks, parameter gradients all-reduced, the same
+                 optimiser step on every rank (optimization/optimizer/torch/base.py:95-154)."""
+    from optiland_pr_b200 import _lib, parallel, samples, spot
+    from optiland_pr_b200.autograd import rms_merit_sharded
+    from optiland_pr_b200.optic import random_pupil_device
+    from optiland_pr_b200.trace import fused_trace_pupil
+    out = {}
+    # ---- strong scaling of C2
+    Px, Py = random_pupil_device(npf, 1, dev)             # the same grid on every rank (same seed)
+    lo, hi = parallel.shard_range(npf)
+    Hx = np.asarray([f[0] for f in FIELDS]); Hy = np.asarray([f[1] for f in FIELDS])
+    fxy_np, z_start = lens._field_offsets(Hx, Hy)
+    fxy_d = torch.from_numpy(fxy_np).to(dev)
+    gen_kw = dict(EPD=lens._EPD, EPL=lens._EPL, z_start=z_start, wavelength=WAVELENGTH, dtype=torch.float64)
+    o = torch.empty((8, nf * npf), dtype=torch.float64, device=dev)
+    sums = torch.zeros((nf, _lib.SPOT_SUMS), dtype=torch.float64, device=dev)
+    zero1 = torch.zeros(1, dtype=torch.float64, device=dev)
+    chief = torch.empty((8, nf), dtype=torch.float64, device=dev)
+    fused_trace_pupil(packed, zero1, zero1, fxy_d, out=chief, **gen_kw)
+    shift = chief[:2].t().nan_to_num(0.0, 0.0, 0.0).contiguous()
+    resid = torch.zeros((packed.n_surfaces, _lib.RESID_STRIDE), dtype=torch.int64, device=dev)
+    merged = [None]
+
+    def strong():
+        sums.zero_()
+        resid.zero_()
+        fused_trace_pupil(packed, Px, Py, fxy_d, p_lo=lo, p_len=hi - lo, out=o, spot=sums, spot_shift=shift,
+                          resid_out=resid, **gen_kw)
+        merged[0] = parallel.allreduce_spot_sums(sums)
+
+    ms = timed(strong, args.steps, 3)
+    out["strong_c2"] = {"ms_per_step": ms, "ray_surfaces_per_s": nf * npf * S_eff / (ms * 1e-3),
+                        "rays_total": nf * npf, "rays_per_rank": nf * (hi - lo),
+                        "rms_spot_mm": spot.spot_stats(merged[0])["rms"].cpu().tolist()}
+    del o, Px, Py
+    torch.cuda.empty_cache()
+    # ---- C5
+    out.update(bench_monte_carlo(torch, lens, S_eff))
+    # ---- C4
+    lens4 = samples.CookeTriplet()
+    lens4.surface_group.record = "none"
+    sfs = lens4.surface_group.surfaces
+    pars = []
+    for k in range(1, 7):
+        p_ = torch.nn.Parameter(torch.tensor(float(sfs[k].geometry.radius), dtype=torch.float64, device=dev))
+        lens4.set_radius(p_, k)
+        pars.append(p_)
+    for k in range(1, 7):
+        p_ = torch.nn.Parameter(torch.tensor(0.0, dtype=torch.float64, device=dev))
+        lens4.set_conic(p_, k)
+        pars.append(p_)
+    opt = torch.optim.Adam(pars, lr=1e-6)
+    n4 = 1_000_000
+    Px4, Py4 = random_pupil_device(n4, 0, dev)
+    fields4 = lens4.get_field_coords()
+    wls4 = list(lens4.wavelengths)
+    S4 = lens4.surface_group.num_surfaces - 1
+    last = [None]
+
+    def c4():
+        opt.zero_grad()
+        last[0] = rms_merit_sharded(lens4, fields4, wls4, Px4, Py4, params=pars)
+        opt.step()
+
+    ms = timed(c4, max(3, args.steps // 2), 3)
+    out["c4_cooke_adam_step_sharded_pairs"] = {
+        "ms": ms, "ray_surfaces_per_s": 9 * n4 * S4 / (ms * 1e-3), "variables": len(pars),
+        "pairs_per_rank": [len(parallel.shard_items(range(9), r, world)) for r in range(world)],
+        "merit": float(last[0]),
+        "api": "autograd.rms_merit_sharded: 9 (field, wavelength) pairs round-robin over the ranks, one FusedTraceFn "
+               "node per rank (forward with blocked checkpoints + reduced-algebra adjoint), ONE all-reduce of the flat "
+               "parameter gradient, Adam step on every rank"}
+    return out
 
 
 def reference_torch_eager():
@@ -547,7 +651,6 @@ def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64
                        "hbm_gbs": 60 * n / (ms * 1e-3) / 1e9}
     out["fp64_fma_peak_tflops"] = fp64_peak
     out["fp32_fma_peak_tflops"] = fp32_peak
-    out.update(bench_monte_carlo(torch, lens, S_eff))
     out.update(bench_other_configs(torch, timed, args))
     try:
         from optiland_pr_b200.autograd import bench_backward

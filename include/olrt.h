@@ -344,6 +344,17 @@ int olrt_trace_pupil_f32(const olrt_sys* sys, const float* presc, const int32_t*
                          uint32_t* fixup, double* spot_sums, const double* spot_shift, int spot_flags,
                          const int32_t* group_k, unsigned long long* group_resid, int flags, void* stream);
 
+/* Random pupil distribution generated on the device: RandomDistribution.generate_points
+ * (optiland/distribution.py:132-158) with the NumPy backend's generator, numpy.random.default_rng(seed) = PCG64:
+ * r = uniform(size = n), theta = uniform(0, 2 pi, size = n), Px = sqrt(r) cos(theta), Py = sqrt(r) sin(theta).
+ * `Optic.trace(Hx, Hy, wavelength, num_rays, "random")` then moves a seed, not 16 bytes per pupil point, to the GPU.
+ *  state, inc [host] the generator's 128-bit state and increment BEFORE its first draw, high word first
+ *             (numpy: default_rng(seed).bit_generator.state["state"]["state" | "inc"]; the seed hashing stays in NumPy)
+ *  Px, Py     [n] doubles (device)
+ *  raw        NULL, or [2][n] doubles (device): the draws r and theta themselves (NumPy's, bit for bit)      */
+int olrt_pupil_random_f64(const uint64_t state[2] /*host*/, const uint64_t inc[2] /*host*/, int64_t n, double* Px,
+                          double* Py, double* raw, void* stream);
+
 /* OPD / wavefront epilogue: per ray, the optical path from the image surface back to the
  * reference sphere, the launch-plane tilt correction and the OPD in waves relative to the chief ray --
  * ReferenceStrategy._opd_image_to_xp (optiland/wavefront/strategy.py:68-116), _correct_tilt (:118-166) and steps

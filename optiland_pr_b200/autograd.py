@@ -220,6 +220,53 @@ def _rms_merit_all(lens, fields, wavelengths, Px, Py):
     return rms_spot_sq(out, nw * nf).sum()
 
 
+def _rms_merit_pairs(lens, pairs, Px, Py):
+    """sum of rms_spot_size^2 over the given ((Hx, Hy), wavelength) pairs from ONE traced batch (per-ray wavelengths:
+    one FusedTraceFn node). `pairs` may be any subset of fields x wavelengths -- a rank's share of them."""
+    from .spot import rms_spot_sq
+    npair, npup = len(pairs), int(Px.numel())
+    dev = Px.device
+    Hx = torch.tensor([p[0][0] for p in pairs], dtype=torch.float64, device=dev).repeat_interleave(npup)
+    Hy = torch.tensor([p[0][1] for p in pairs], dtype=torch.float64, device=dev).repeat_interleave(npup)
+    wl = torch.tensor([float(p[1]) for p in pairs], dtype=torch.float64, device=dev).repeat_interleave(npup)
+    rays = lens.generate_rays(Hx, Hy, Px.repeat(npair), Py.repeat(npair), wl)
+    sg = lens.surface_group
+    sg.trace(rays, wavelengths=sorted({float(p[1]) for p in pairs}))
+    lt = sg.last_trace
+    if lt is not None and lt.out is not None and lt.out[0].data_ptr() == rays.x.data_ptr():
+        out = lt.out
+    else:
+        out = torch.stack([rays.x, rays.y, rays.z, rays.L, rays.M, rays.N, rays.i, rays.opd])
+    return rms_spot_sq(out, npair).sum()
+
+
+def rms_merit_sharded(lens, fields, wavelengths, Px, Py, params=None):
+    """BASELINE C4 across GPUs (SURVEY.md 8e level 1): the (field, wavelength) pairs of the merit are dealt round-robin
+    to the ranks (`parallel.shard_items`), every rank traces ITS pairs forward + backward, and what crosses NVLink is
+    one all-reduce of the loss scalar and -- with `params` -- ONE all-reduce (SUM) of the flat parameter-gradient
+    vector after the local backward (the ranks hold different numbers of pairs, so per-trace collectives would not
+    pair up; DDP's shape). Returns the GLOBAL loss (a detached scalar tensor); `params[i].grad` holds the global
+    gradient on every rank, ready for the same optimiser step everywhere."""
+    from . import parallel
+    pairs = [(tuple(f), float(w)) for w in wavelengths for f in fields]
+    mine = parallel.shard_items(pairs)
+    dev = Px.device
+    if mine:
+        loss = _rms_merit_pairs(lens, mine, Px, Py)
+        if params is not None:
+            loss.backward()
+        total = loss.detach().clone()
+    else:
+        total = torch.zeros((), dtype=torch.float64, device=dev)
+    _, w = parallel.world()
+    if w > 1:
+        import torch.distributed as dist
+        dist.all_reduce(total, op=dist.ReduceOp.SUM)
+    if params is not None:
+        parallel.allreduce_param_grads(params)
+    return total
+
+
 def smoke_backward() -> str:
     """forward + backward through the public API on the Cooke triplet: finite, non-zero gradients that agree
     with a central finite difference of the merit."""

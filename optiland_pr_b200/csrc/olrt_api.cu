@@ -398,6 +398,80 @@ extern "C" int olrt_upload_pupil(double* Px_dev, double* Py_dev, const double* P
 }
 
 // ---------------------------------------------------------------------------------------------
+// Random pupil on the device: RandomDistribution.generate_points (optiland/distribution.py:132-158) draws
+//   r = rng.uniform(size=n); theta = rng.uniform(0, 2 pi, size=n); x = sqrt(r) cos(theta); y = sqrt(r) sin(theta)
+// from numpy.random.default_rng(seed) = PCG64: a 128-bit LCG (state = state * MULT + inc) with the XSL-RR output
+// rotr64(hi ^ lo, hi >> 58) taken AFTER the step, a double = (u64 >> 11) * 2^-53, uniform(a, b) = a + (b - a) d.
+// The stream is random-access: thread t jumps to draw t in O(log t) 128-bit steps (LCG advance), then walks on with
+// the one multiplier / increment pair of its fixed stride. r uses draws [0, n), theta draws [n, 2n): the host passes
+// the generator's state before its first draw (SeedSequence hashing stays in NumPy, microseconds) and the same state
+// advanced by n. The draws are NumPy's bit for bit; x and y differ from NumPy's by the last bit or two of cos / sin
+// (libm vs CUDA), tests/test_gpu_pupil_random.py.
+// ---------------------------------------------------------------------------------------------
+typedef unsigned __int128 u128;
+__host__ __device__ static inline u128 mk128(unsigned long long hi, unsigned long long lo) { return ((u128)hi << 64) | lo; }
+#define OLRT_PCG_MULT mk128(0x2360ED051FC65DA4ULL, 0x4385DF649FCCF645ULL)
+
+// (acc_mult, acc_plus) of `delta` LCG steps: state' = acc_mult * state + acc_plus
+__host__ __device__ static inline void pcg_advance(u128 mult, u128 plus, unsigned long long delta, u128& am, u128& ap) {
+  am = 1; ap = 0;
+  while (delta > 0) {
+    if (delta & 1) { am *= mult; ap = ap * mult + plus; }
+    plus = (mult + 1) * plus;
+    mult *= mult;
+    delta >>= 1;
+  }
+}
+__device__ __forceinline__ double pcg_double(u128 state) {
+  const unsigned long long hi = (unsigned long long)(state >> 64), lo = (unsigned long long)state;
+  const unsigned long long x = hi ^ lo;
+  const unsigned rot = (unsigned)(hi >> 58);
+  const unsigned long long o = (x >> rot) | (x << ((64u - rot) & 63u));
+  return (double)(o >> 11) * (1.0 / 9007199254740992.0);
+}
+
+__global__ void __launch_bounds__(256) pupil_random_kernel(u128 s_r, u128 s_t, u128 inc, u128 a_stride, u128 c_stride,
+                                                           long long n, double two_pi, double* Px, double* Py,
+                                                           double* raw) {
+  const long long T = (long long)gridDim.x * blockDim.x;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  u128 am, ap;
+  pcg_advance(OLRT_PCG_MULT, inc, (unsigned long long)i + 1ull, am, ap);   // the output follows the step: draw i = state i + 1
+  u128 sr = am * s_r + ap, st = am * s_t + ap;
+  for (; i < n; i += T) {
+    const double r = pcg_double(sr);
+    const double th = 0.0 + two_pi * pcg_double(st);   // Generator.uniform: low + (high - low) * d
+    double sn, cs;
+    sincos(th, &sn, &cs);
+    const double q = sqrt(r);
+    Px[i] = q * cs; Py[i] = q * sn;
+    if (raw != nullptr) { raw[i] = r; raw[n + i] = th; }
+    sr = a_stride * sr + c_stride; st = a_stride * st + c_stride;
+  }
+}
+
+extern "C" int olrt_pupil_random_f64(const uint64_t state[2], const uint64_t inc[2], int64_t n, double* Px, double* Py,
+                                     double* raw, void* stream) {
+  if (!state || !inc || !Px || !Py || n < 0) return OLRT_E_ARG;
+  if (n == 0) return OLRT_OK;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  long long grid = (long long)sms * 8;
+  const long long need = (n + 255) / 256;
+  if (grid > need) grid = need;
+  const u128 s0 = mk128(state[0], state[1]), ic = mk128(inc[0], inc[1]);
+  u128 am, ap, as, cs;
+  pcg_advance(OLRT_PCG_MULT, ic, (unsigned long long)n, am, ap);            // theta's draws start n steps on
+  const u128 s_t = am * s0 + ap;
+  pcg_advance(OLRT_PCG_MULT, ic, (unsigned long long)(grid * 256), as, cs);  // one stride of the grid
+  pupil_random_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(s0, s_t, ic, as, cs, n, 2.0 * 3.141592653589793,
+                                                                        Px, Py, raw);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+
+// ---------------------------------------------------------------------------------------------
 // OPD / wavefront epilogue (kernel in trace_strict.cu)
 // ---------------------------------------------------------------------------------------------
 template <typename R>

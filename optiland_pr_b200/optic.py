@@ -51,6 +51,31 @@ def pupil_points(distribution: str, num_rays: int, seed=None):
     raise ValueError(f"distribution {distribution!r} is not implemented")
 
 
+def random_pupil_device(num_rays: int, seed=None, device=None, want_raw: bool = False):
+    """RandomDistribution(seed).generate_points(num_rays) (optiland/distribution.py:132-158, NumPy backend generator
+    = PCG64) generated ON THE DEVICE by `olrt_pupil_random_f64`: the seed's 128-bit generator state goes to the GPU,
+    not 16 bytes per pupil point. The uniform draws are NumPy's bit for bit; Px, Py differ from NumPy's by the last
+    bit or two of cos / sin. Returns (Px, Py) device tensors (+ raw [2, n] draws when asked)."""
+    import ctypes as C
+
+    from . import _lib as L
+    lib = L.load()
+    dev = torch.device(device if device is not None else be.get_device())
+    st = np.random.default_rng(seed).bit_generator.state["state"]
+    mask = (1 << 64) - 1
+    state = (C.c_uint64 * 2)(st["state"] >> 64, st["state"] & mask)
+    inc = (C.c_uint64 * 2)(st["inc"] >> 64, st["inc"] & mask)
+    n = int(num_rays)
+    Px = torch.empty(n, dtype=torch.float64, device=dev)
+    Py = torch.empty(n, dtype=torch.float64, device=dev)
+    raw = torch.empty((2, n), dtype=torch.float64, device=dev) if want_raw else None
+    with torch.cuda.device(dev):
+        rc = lib.olrt_pupil_random_f64(C.byref(state), C.byref(inc), n, Px.data_ptr(), Py.data_ptr(),
+                                       0 if raw is None else raw.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
+    L.check(rc, "olrt_pupil_random_f64")
+    return (Px, Py, raw) if want_raw else (Px, Py)
+
+
 _FIELD_CACHE: dict = {}
 
 
@@ -263,11 +288,14 @@ class Optic:
         spot=True also leaves the per-field spot sums (layout: include/olrt.h, olrt_spot_sums_*) in
         `rays.spot_sums` -- taken inside the trace kernel when the lens allows it (spot.spot_stats turns them
         into centroid / RMS radius)."""
+        dev = be.get_device()
         if isinstance(distribution, str):
-            Px, Py = pupil_points(distribution, num_rays, seed)
+            if distribution == "random" and str(dev).startswith("cuda") and num_rays >= self.device_pupil_min_rays:
+                Px, Py = random_pupil_device(num_rays, seed, dev)   # the seed travels, not the grid
+            else:
+                Px, Py = pupil_points(distribution, num_rays, seed)
         else:
             Px, Py = distribution
-        dev = be.get_device()
         Hx = np.atleast_1d(np.asarray(Hx, dtype=np.float64))
         Hy = np.atleast_1d(np.asarray(Hy, dtype=np.float64))
         sg = self.surface_group
@@ -294,6 +322,7 @@ class Optic:
             rays.spot_sums = spot_sums(rays.x, rays.y, rays.i, int(Hx.size), int(Px.numel()))
         return rays
 
+    device_pupil_min_rays = 4096  # "random" distributions at least this long are generated on the device
     pipeline_min_rays = 1 << 21   # host pupil grids at least this long are streamed in chunks
     pipeline_chunks = 12
     pipeline_streamed = True     # fused kernel: one launch that waits for the chunks as they arrive

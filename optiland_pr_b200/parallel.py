@@ -101,6 +101,27 @@ def allreduce_gradients(*grads: torch.Tensor):
     return grads
 
 
+def allreduce_param_grads(params):
+    """Data-parallel gradient exchange for an optimiser step: ONE all-reduce (SUM) of the flat vector of every
+    parameter's gradient (a missing .grad counts as zero), written back in place. A few hundred bytes."""
+    _, w = world()
+    params = [p for p in params]
+    if w == 1 or not params:
+        return
+    dev, dt = params[0].device, params[0].dtype
+    flat = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1).to(dt) for p in params])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+    off = 0
+    for p in params:
+        k = p.numel()
+        g = flat[off:off + k].reshape(p.shape).to(p.dtype)
+        if p.grad is None:
+            p.grad = g.clone()
+        else:
+            p.grad.copy_(g)
+        off += k
+
+
 def sharded_trace(surface_group, rays, wavelengths=None):
     """`SurfaceGroup.trace` on this rank's shard with BATCH-global Newton trip counts: trace the shard
     (its own exit rule), all-reduce K_s with MAX -- the reference's test is a maximum over all rays of the

@@ -43,6 +43,12 @@ class RangeSampler:
         self.index += 1
         return float(v)
 
+    def sample_n(self, n):
+        """The next n values of `sample()` at once."""
+        idx = (self.index % len(self.values) + np.arange(n)) % len(self.values)
+        self.index = int(idx[-1]) + 1 if n else self.index
+        return self.values[idx].astype(np.float64)
+
 
 class DistributionSampler:
     """perturbation.py:91-134: one scalar draw per call from numpy's default_rng(seed)."""
@@ -60,6 +66,15 @@ class DistributionSampler:
             return float(self.generator.normal(**self.params))
         if self.distribution == "uniform":
             return float(self.generator.uniform(**self.params))
+        raise ValueError(f"Unknown distribution: {self.distribution}")
+
+    def sample_n(self, n):
+        """The next n values of `sample()` in one call: numpy's Generator fills an array with the same routine it
+        uses for a scalar, so the values (and the generator's state afterwards) are those of n scalar draws."""
+        if self.distribution == "normal":
+            return self.generator.normal(size=n, **self.params)
+        if self.distribution == "uniform":
+            return self.generator.uniform(size=n, **self.params)
         raise ValueError(f"Unknown distribution: {self.distribution}")
 
 
@@ -111,11 +126,20 @@ class MonteCarloSpot:
         self.last_path = None
 
     def _draw_rows(self, vals):
-        """Fill `vals` [rows, n_perturbations] with the next draws of every sampler, trial by trial."""
-        for t in range(vals.shape[0]):           # monte_carlo.py:86-92: per trial, every perturbation in order
-            for j, p in enumerate(self.perturbations):
-                p.value = p.sampler.sample()
-                vals[t, j] = p.value
+        """Fill `vals` [rows, n_perturbations] with the next draws of every sampler. The reference draws trial by
+        trial, every perturbation in order (monte_carlo.py:86-92) -- but every sampler owns its generator
+        (perturbation.py:91-134), so the t-th value of a perturbation is its sampler's t-th draw whatever the
+        interleaving: one vectorised draw per perturbation gives the same values. Samplers without `sample_n`
+        (a caller's own) are drawn one by one."""
+        T = vals.shape[0]
+        for j, p in enumerate(self.perturbations):
+            if hasattr(p.sampler, "sample_n"):
+                vals[:, j] = p.sampler.sample_n(T)
+            else:
+                for t in range(T):
+                    vals[t, j] = p.sampler.sample()
+            if T:
+                p.value = float(vals[-1, j])
 
     def draw(self, num_iterations):
         vals = np.empty((num_iterations, len(self.perturbations)))

@@ -39,7 +39,14 @@ def _worker(rank, world, port, q):
     g = torch.full((4,), float(rank + 1), dtype=torch.float64)
     parallel.allreduce_gradients(g)
     items = parallel.shard_items(range(9))
-    q.put((rank, (lo, hi), ok_sums, iters, g.tolist(), items))
+    # data-parallel parameter gradients: one all-reduce of the flat vector; a missing .grad counts as zero
+    pa = torch.nn.Parameter(torch.zeros(3, dtype=torch.float64))
+    pb = torch.nn.Parameter(torch.zeros((), dtype=torch.float64))
+    pa.grad = torch.tensor([1.0, 2.0, 3.0], dtype=torch.float64) * (rank + 1)
+    if rank == 1:
+        pb.grad = torch.tensor(5.0, dtype=torch.float64)
+    parallel.allreduce_param_grads([pa, pb])
+    q.put((rank, (lo, hi), ok_sums, iters, g.tolist() + pa.grad.tolist() + [float(pb.grad)], items))
     dist.destroy_process_group()
 
 
@@ -58,7 +65,7 @@ def test_two_rank_reductions_on_gloo():
     assert rng0 == (0, 5001) and rng1 == (5001, 10001)          # contiguous, covering, first rank gets the extra
     assert ok0 and ok1
     assert it0 == it1 == [2, 0, 2]                                # element-wise max
-    assert g0 == g1 == [3.0] * 4                                  # sum
+    assert g0 == g1 == [3.0] * 4 + [3.0, 6.0, 9.0, 5.0]           # sums (plain vectors, then parameter gradients)
     assert items0 == [0, 2, 4, 6, 8] and items1 == [1, 3, 5, 7]
 
 

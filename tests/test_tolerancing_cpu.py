@@ -99,3 +99,16 @@ def test_tilt_perturbation_rows_equal_packing_the_tilted_lens():
         assert np.array_equal(batch[t], want.presc[0]), t
         assert np.array_equal(ops_rows[t], want.ops), t
     assert vals[0, 1] == 0.0 and not np.array_equal(ops_rows[0], ops_rows[1])
+
+
+def test_vectorised_draws_equal_scalar_draws():
+    """MonteCarloSpot draws every perturbation's values in one call per sampler: same values, same generator state."""
+    for kind, kw in (("normal", dict(loc=3.0, scale=0.1)), ("uniform", dict(low=-1.0, high=2.0))):
+        a, b = DistributionSampler(kind, seed=5, **kw), DistributionSampler(kind, seed=5, **kw)
+        x = np.array([a.sample() for _ in range(500)])
+        y = np.concatenate([b.sample_n(123), b.sample_n(377)])
+        assert np.array_equal(x, y) and a.sample() == b.sample()
+    a, b = RangeSampler(-1, 1, 7), RangeSampler(-1, 1, 7)
+    x = np.array([a.sample() for _ in range(20)])
+    y = np.concatenate([b.sample_n(5), b.sample_n(15)])
+    assert np.array_equal(x, y) and a.sample() == b.sample()
