@@ -78,7 +78,11 @@ class FusedTraceFn(torch.autograd.Function):
         res = fused_trace(packed, [t.detach() if t is not None else None for t in ins],
                           opd_in=None if opd_in is None else opd_in.detach(),
                           presc=presc.detach().reshape(1, -1), want_dir0=True, fast=fast, alias_out=True,
-                          ckpt=blocked, own_rows=True)   # the row was assembled from this very pack
+                          ckpt=blocked, own_rows=True,   # the row was assembled from this very pack
+                          # a lens of planes / conics / even aspheres can only raise the packer-bug bits of the status
+                          # word (no Zernike / Chebyshev range errors): do not stall the optimiser step on reading it
+                          # or the fix-up count back (OLRT_CHECK_BWD_STATUS=1 reads both)
+                          check_status=_CHECK_BWD_STATUS or not packed.fastkinds(), read_fixups=_CHECK_BWD_STATUS)
         if blocked and max(res.nr_iters, default=0) > L.BX_MAXK:
             raise NotImplementedError("blocked checkpoints: a surface took more than 3 Newton updates")
         ctx.blocked = bool(blocked)
@@ -223,15 +227,26 @@ def _rms_merit_all(lens, fields, wavelengths, Px, Py):
 def _rms_merit_pairs(lens, pairs, Px, Py):
     """sum of rms_spot_size^2 over the given ((Hx, Hy), wavelength) pairs from ONE traced batch (per-ray wavelengths:
     one FusedTraceFn node). `pairs` may be any subset of fields x wavelengths -- a rank's share of them."""
+    from . import backend as be
+    from .rays import RealRays
     from .spot import rms_spot_sq
     npair, npup = len(pairs), int(Px.numel())
     dev = Px.device
-    Hx = torch.tensor([p[0][0] for p in pairs], dtype=torch.float64, device=dev).repeat_interleave(npup)
-    Hy = torch.tensor([p[0][1] for p in pairs], dtype=torch.float64, device=dev).repeat_interleave(npup)
-    wl = torch.tensor([float(p[1]) for p in pairs], dtype=torch.float64, device=dev).repeat_interleave(npup)
-    rays = lens.generate_rays(Hx, Hy, Px.repeat(npair), Py.repeat(npair), wl)
+    # the rays of every pair from the ray-launch kernel (one launch per wavelength: its fields share the pupil grid),
+    # pair after pair in one [8, npair * npup] batch -- no elementwise torch ops, nothing recorded by autograd (the
+    # launch depends on EPL / EPD only, which this package takes as inputs)
+    wls = sorted({float(p[1]) for p in pairs})
+    buf = torch.empty((8, npair * npup), dtype=be.get_precision(), device=dev)
+    a = 0
+    for w in wls:
+        fw = [p[0] for p in pairs if float(p[1]) == w]
+        b = a + len(fw) * npup
+        lens.launch_rays(np.array([f[0] for f in fw], dtype=np.float64), np.array([f[1] for f in fw], dtype=np.float64),
+                         Px, Py, w, out=buf[:, a:b])
+        a = b
+    rays = RealRays(*[buf[q] for q in range(8)])
     sg = lens.surface_group
-    sg.trace(rays, wavelengths=sorted({float(p[1]) for p in pairs}))
+    sg.trace(rays, wavelengths=wls)
     lt = sg.last_trace
     if lt is not None and lt.out is not None and lt.out[0].data_ptr() == rays.x.data_ptr():
         out = lt.out
