@@ -381,7 +381,10 @@ def main():
 
     def only_trace():
         fused_trace_pupil(packed, Px_d, Py_d, fxy_d, out=out, spot=sums, spot_shift=shift0, **gen_kw)
-    ms_kernel = timed(only_trace, args.steps, 3)
+    leg_clock = ClockSampler(local)      # the SM clock DURING this leg: the arithmetic peak below is quoted at it
+    leg_clock.start()
+    ms_kernel = timed(only_trace, max(args.steps, 40), 3)
+    leg_clocks = leg_clock.stop()
     fl_ray = flops.flops_per_ray(packed, nr_iters)
     by_ray = 64.0 + 16.0 / nf   # 8 output doubles per ray + the pupil point (Px, Py) shared by the nf fields
     # measured FP64 FMA peak on this GPU (dependent-free DFMA chains, all SMs)
@@ -397,7 +400,12 @@ def main():
         return blocks * threads * iters * 8 * 2 / (ms * 1e-3) / 1e12
 
     sink32 = torch.zeros(1, dtype=torch.float32, device=dev)
+    peak_clock = ClockSampler(local)
+    peak_clock.start()
     fp64_peak = peak(lib.olrt_fma_peak_f64, 1 << 16, sms * 8, 256)
+    for _ in range(6):                   # long enough for a few clock samples
+        peak(lib.olrt_fma_peak_f64, 1 << 16, sms * 8, 256)
+    peak_clocks = peak_clock.stop()
     fp32_peak = peak(lib.olrt_fma_peak_f32, 1 << 17, sms * 8, 256)
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     hbm_peak, hbm_src = 6650.0, "fallback"
@@ -411,6 +419,14 @@ def main():
                   "<= 1e-10 relative, masks identical) + its IEEE fix-up pass",
         "bound": "fp64_fma", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s",
         "frac": ach_tf / fp64_peak, "peak_source": "olrt_fma_peak_f64 measured in this run",
+        # 64 FP64 FMA lanes per SM and clock (B200_PROFILING.md): the arithmetic ceiling at the clock each leg ran at
+        "peak_arithmetic": {"formula": "SMs x 64 DFMA/clk x 2 flop x SM clock",
+                            "sms": sms, "sm_mhz_this_leg": leg_clocks.get("sm_mhz"),
+                            "sm_mhz_peak_leg": peak_clocks.get("sm_mhz"),
+                            "tflops_at_leg_clock": (sms * 64 * 2 * leg_clocks["sm_mhz"] * 1e6 / 1e12
+                                                    if leg_clocks.get("sm_mhz") else None),
+                            "tflops_at_peak_leg_clock": (sms * 64 * 2 * peak_clocks["sm_mhz"] * 1e6 / 1e12
+                                                         if peak_clocks.get("sm_mhz") else None)},
         "flops_per_ray": fl_ray, "flops_note": "the trace's algorithmic count (SURVEY.md 8d); ray launch and spot "
                                                "sums are executed but not counted",
         "bytes_per_ray": by_ray, "nr_iters": nr_iters, "ms_per_launch": ms_kernel,
@@ -651,7 +667,7 @@ def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64
                        "hbm_gbs": 60 * n / (ms * 1e-3) / 1e9}
     out["fp64_fma_peak_tflops"] = fp64_peak
     out["fp32_fma_peak_tflops"] = fp32_peak
-    out.update(bench_other_configs(torch, timed, args))
+    out.update(bench_other_configs(torch, timed, args, fp64_peak))
     try:
         from optiland_pr_b200.autograd import bench_backward
     except ImportError:
@@ -661,7 +677,7 @@ def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64
     return out
 
 
-def bench_other_configs(torch, timed, args):
+def bench_other_configs(torch, timed, args, fp64_peak):
     """BASELINE configs C1 (Cooke triplet, 3 fields x 3 wavelengths x 1M rays, RMS spot per pair) and C3 (off-axis
     three-mirror polynomial freeform system: Newton-Raphson on every mirror, tilts, decenters -- the interpreter
     kernel) as throughput figures next to the headline; their VALUES are pinned by the parity tests."""
@@ -688,33 +704,38 @@ def bench_other_configs(torch, timed, args):
                                     "passes": 2,
                                     "api": "spot.SpotDiagram(lens): centroid pass + radius pass over 3 fields x 3 "
                                            "wavelengths, one fused launch + trace + spot kernel each, RMS -> host"}
-    # ---- C3
+    # ---- C3 (BASELINE configs[2]: 64 M rays, seed 2): off-axis three-mirror system, 4 x 4 polynomial freeforms, rx tilts,
+    # dy decenters -- the interpreter kernel. The pupil is drawn on the device (NumPy's stream for seed 2).
+    from optiland_pr_b200 import flops
+    from optiland_pr_b200.optic import random_pupil_device
     lens = samples.ThreeMirrorAnastigmat()
     wl = lens.primary_wavelength
-    n3 = 1 << 24
-    r_, th = rng.uniform(size=n3), rng.uniform(0, 2 * np.pi, size=n3)
-    Px = torch.from_numpy(np.sqrt(r_) * np.cos(th)).to(dev)
-    Py = torch.from_numpy(np.sqrt(r_) * np.sin(th)).to(dev)
+    n3 = 1 << 26
+    Px, Py = random_pupil_device(n3, 2, dev)
     f0 = lens.get_field_coords()[0]
     rays = lens.launch_rays(np.array([f0[0]]), np.array([f0[1]]), Px, Py, wl)
     ins = rays.components()
     ins[7] = None
+    del Px, Py
     lens.surface_group.record = "none"
     packed = lens.surface_group.pack([float(wl)])
     o = torch.empty((8, n3), dtype=torch.float64, device=dev)
     res = fused_trace(packed, ins, out=o, fast=True)           # settles the Newton counts
     S3 = lens.surface_group.num_surfaces - 1
+    fl3 = flops.flops_per_ray(packed, res.nr_iters)
     for name, fast in (("tolerance", True), ("strict", False)):
         ms = timed(lambda: fused_trace(packed, ins, out=o, fast=fast, verify_nr=False, check_status=False),
                    max(2, args.steps // 2), 2)
-        out["c3_three_mirror_freeform_16M_" + name] = {"ms": ms, "ray_surfaces_per_s": n3 * S3 / (ms * 1e-3),
-                                                       "nr_iters": res.nr_iters,
-                                                       "kernel": "trace_fwd_kernel (interpreter: 4x4 polynomial "
-                                                                 "freeforms, Newton-Raphson, tilts, decenters)"}
+        out["c3_three_mirror_freeform_64M_" + name] = {
+            "ms": ms, "rays": n3, "ray_surfaces_per_s": n3 * S3 / (ms * 1e-3), "nr_iters": res.nr_iters,
+            "frac_fp64_fma_peak": fl3 * n3 / (ms * 1e-3) / 1e12 / fp64_peak, "flops_per_ray": fl3,
+            "flop_model": flops.flop_model(packed, res.nr_iters),
+            "kernel": "trace_fwd_kernel (interpreter: 4x4 polynomial freeforms, Newton-Raphson, tilts, decenters)"}
+    del o, ins, rays
+    torch.cuda.empty_cache()
     # ---- C4: one optimisation step through the public API (Optic.trace under autograd -> FusedTraceFn: forward with
     # tile-blocked checkpoints + reduced-algebra adjoint kernel), merit = sum over 3 wavelengths x 3 fields of the squared
     # RMS spot radius, variables = the six radii and six conic constants of the Cooke triplet (live torch Parameters), Adam update included
-    from optiland_pr_b200.autograd import _rms_merit
     lens4 = samples.CookeTriplet()
     lens4.surface_group.record = "none"
     sfs = lens4.surface_group.surfaces
@@ -735,31 +756,6 @@ def bench_other_configs(torch, timed, args):
     fields4 = lens4.get_field_coords()
     wls4 = list(lens4.wavelengths)
 
-    def c4():
-        opt.zero_grad()
-        loss = sum(_rms_merit(lens4, fields4, w_, Px4, Py4) for w_ in wls4)
-        loss.backward()
-        opt.step()
-        return loss
-
-    ms = timed(c4, max(2, args.steps // 2), 3)
-    out["c4_cooke_merit_adam_step_9_pairs_x_1M"] = {
-        "ms": ms, "ray_surfaces_per_s": 9 * n4 * S1 / (ms * 1e-3), "variables": len(pars),
-        "api": "Optic.trace under autograd (one FusedTraceFn node per wavelength: 3 fields x 1M rays), torch RMS-spot "
-               "merit, loss.backward(), Adam step"}
-    from optiland_pr_b200.autograd import _rms_merit_fused
-
-    def c4f():
-        opt.zero_grad()
-        loss = sum(_rms_merit_fused(lens4, fields4, w_, Px4, Py4) for w_ in wls4)
-        loss.backward()
-        opt.step()
-        return loss
-
-    ms = timed(c4f, max(2, args.steps // 2), 3)
-    out["c4_cooke_merit_adam_step_fused_spot_merit"] = {
-        "ms": ms, "ray_surfaces_per_s": 9 * n4 * S1 / (ms * 1e-3), "variables": len(pars),
-        "api": "the same step with spot.rms_spot_sq (spot-sum kernel forward, one dense gradient backward) as the merit"}
     try:   # all 9 (wavelength, field) pairs as ONE autograd node (per-ray wavelengths)
         from optiland_pr_b200.autograd import _rms_merit_all
 
@@ -778,28 +774,33 @@ def bench_other_configs(torch, timed, args):
     except Exception as e:   # an extra leg must never take the bench line down
         out["c4_cooke_merit_adam_step_one_node"] = {"error": repr(e)[:200]}
     # ---- C3, second half: refractive Zernike (fringe, 36 terms) + odd-asphere plate, tilts about three axes,
-    # elliptical / rectangular / boolean apertures, TIR at the rim -- the interpreter kernel again
+    # elliptical / rectangular / boolean apertures, TIR at the rim -- the interpreter kernel again, 64 M rays
     lens = samples.FreeformPlate()
     wl = lens.primary_wavelength
-    nz = 1 << 22
-    r_, th = rng.uniform(size=nz), rng.uniform(0, 2 * np.pi, size=nz)
-    Px = torch.from_numpy(np.sqrt(r_) * np.cos(th)).to(dev)
-    Py = torch.from_numpy(np.sqrt(r_) * np.sin(th)).to(dev)
-    f0 = lens.get_field_coords()[0]
+    nz = 1 << 26
+    Px, Py = random_pupil_device(nz, 2, dev)
+    f0 = lens.get_field_coords()[-1]     # the off-axis field: part of the pupil is past the critical angle
     rays = lens.launch_rays(np.array([f0[0]]), np.array([f0[1]]), Px, Py, wl)
     ins = rays.components()
     ins[7] = None
+    del Px, Py
     lens.surface_group.record = "none"
     packed = lens.surface_group.pack([float(wl)])
     o = torch.empty((8, nz), dtype=torch.float64, device=dev)
     res = fused_trace(packed, ins, out=o, fast=True)
     Sz = lens.surface_group.num_surfaces - 1
+    flz = flops.flops_per_ray(packed, res.nr_iters)
     ms = timed(lambda: fused_trace(packed, ins, out=o, fast=True, verify_nr=False, check_status=False),
                max(2, args.steps // 2), 2)
-    out["c3_zernike_freeform_plate_4M_tolerance"] = {"ms": ms, "ray_surfaces_per_s": nz * Sz / (ms * 1e-3),
-                                                     "nr_iters": res.nr_iters,
-                                                     "kernel": "trace_fwd_kernel (interpreter: Zernike fringe freeform, "
-                                                               "odd asphere, aperture programs, tilted frames)"}
+    out["c3_zernike_freeform_plate_64M_tolerance"] = {
+        "ms": ms, "rays": nz, "ray_surfaces_per_s": nz * Sz / (ms * 1e-3), "nr_iters": res.nr_iters,
+        "dead_rays": int(torch.isnan(o[0]).sum()), "clipped_rays": int((o[6] == 0).sum()),
+        "frac_fp64_fma_peak": flz * nz / (ms * 1e-3) / 1e12 / fp64_peak, "flops_per_ray": flz,
+        "flop_model": flops.flop_model(packed, res.nr_iters),
+        "kernel": "trace_fwd_kernel (interpreter: Zernike fringe freeform, odd asphere, aperture programs, tilted "
+                  "frames, TIR at the rim)"}
+    del o, ins, rays
+    torch.cuda.empty_cache()
     return out
 
 

@@ -15,11 +15,24 @@ from __future__ import annotations
 from . import _lib as L
 
 
+_GEOM_NAMES = {L.GEOM_PLANE: "plane", L.GEOM_STANDARD: "conic", L.GEOM_EVEN_ASPHERE: "even asphere",
+               L.GEOM_ODD_ASPHERE: "odd asphere", L.GEOM_POLYNOMIAL: "polynomial", L.GEOM_ZERNIKE: "zernike",
+               L.GEOM_BICONIC: "biconic", L.GEOM_TOROIDAL: "toroidal", L.GEOM_CHEBYSHEV: "chebyshev"}
+
+
 def flops_per_ray(packed, nr_iters=None) -> float:
     """Algorithmic forward flops for one ray through every intersected surface."""
+    return sum(row["flops"] for row in flop_model(packed, nr_iters))
+
+
+def flop_model(packed, nr_iters=None) -> list:
+    """The enumerated model, one row per intersected surface ("the builder's enumerated model must be
+    printed with the result"): geometry, coefficient terms m, Newton updates K, active rotations, aperture leaves,
+    absorbing medium, and the flops they add up to."""
     iters = nr_iters if nr_iters is not None else packed.nr_iters()
-    total = 0.0
+    rows = []
     for k, lay in enumerate(packed.layouts):
+        m = 0
         row = k * L.OPS_STRIDE
         geom = int(packed.ops[row + L.OP_GEOM])
         mirror = int(packed.ops[row + L.OP_INTERACT]) == 1
@@ -40,8 +53,12 @@ def flops_per_ray(packed, nr_iters=None) -> float:
                        if int(packed.ops[int(packed.ops[row + L.OP_APER_OFF]) + q]) < 10)
         if flags & L.F_ABSORB:
             f += 8.0
-        total += f
-    return total
+        rows.append({"surface": int(lay.index), "geometry": _GEOM_NAMES.get(geom, str(geom)), "mirror": bool(mirror),
+                     "terms_m": int(m), "newton_K": int(iters[k]), "rotations": bin(fflags).count("1"),
+                     "aperture_leaves": sum(1 for q in range(int(packed.ops[row + L.OP_APER_LEN]))
+                                            if int(packed.ops[int(packed.ops[row + L.OP_APER_OFF]) + q]) < 10),
+                     "absorbing": bool(flags & L.F_ABSORB), "flops": f})
+    return rows
 
 
 def bytes_per_ray(itemsize: int, n_wavelengths: int, n_record: int = 0, opd_in: bool = False,

@@ -169,3 +169,24 @@ def test_streamed_launch_times_out_instead_of_hanging():
         assert dt < 10.0
         if want:
             assert dt > 0.5
+
+
+def test_optic_trace_raises_when_a_chunk_never_arrives():
+    """The host side of the same failure: `Optic.trace` streams a pinned pupil grid; the words its copies write are
+    made zero here (as if the copies had never landed), the kernel gives up after ~2 s with OLRT_ST_TIMEOUT and the
+    call RAISES instead of returning rays computed from an unfilled buffer. The same lens then traces normally."""
+    be.set_device("cuda:0")
+    be.set_precision("float64")
+    px, py = raygen_np.random_pupil(1 << 14, seed=5)
+    Px_h, Py_h = torch.from_numpy(px).pin_memory(), torch.from_numpy(py).pin_memory()
+    lens = samples.EvenAsphereDoubleGauss()
+    lens.surface_group.record = "none"
+    lens.pipeline_min_rays = 1 << 12
+    lens.pipeline_chunks = 4
+    lens._ones_pinned = torch.zeros(64, dtype=torch.int32).pin_memory()
+    with pytest.raises(L.OlrtLibraryError, match="OLRT_ST_TIMEOUT"):
+        lens.trace([0.0], [1.0], 0.5876, distribution=(Px_h, Py_h))
+    lens._ones_pinned = None
+    rays = lens.trace([0.0], [1.0], 0.5876, distribution=(Px_h, Py_h))
+    want = lens.trace([0.0], [1.0], 0.5876, distribution=(Px_h.cuda(), Py_h.cuda()))
+    assert torch.equal(rays.x, want.x) and torch.equal(rays.opd, want.opd)
