@@ -67,7 +67,9 @@ done.append("forward + backward")
 # 5. wavefront epilogue
 from optiland_pr_b200.wavefront import Wavefront
 ck = samples.CookeTriplet()
-Wavefront(ck, fields=[(0.0, 1.0)], wavelengths=[0.55], num_rays=8)
+g = load_golden("wavefront_cooke")
+ck.set_paraxial(EPL=float(g["EPL"]), EPD=float(g["EPD"]), XPL=float(g["XPL"]))
+Wavefront(ck, fields=[(0.0, 1.0)], wavelengths=[0.55], num_rays=8).get_data((0.0, 1.0), 0.55)
 done.append("OPD epilogue")
 torch.cuda.synchronize()
 print("sanitize_case ok:", "; ".join(done))

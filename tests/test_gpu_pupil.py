@@ -177,7 +177,7 @@ def test_optic_trace_raises_when_a_chunk_never_arrives():
     call RAISES instead of returning rays computed from an unfilled buffer. The same lens then traces normally."""
     be.set_device("cuda:0")
     be.set_precision("float64")
-    px, py = raygen_np.random_pupil(1 << 14, seed=5)
+    px, py = raygen_np.random_pupil(1 << 18, seed=5)      # >= 2 chunks of 65 536 points: the grid is streamed
     Px_h, Py_h = torch.from_numpy(px).pin_memory(), torch.from_numpy(py).pin_memory()
     lens = samples.EvenAsphereDoubleGauss()
     lens.surface_group.record = "none"
