@@ -1,6 +1,6 @@
 """BASELINE C3 (three-mirror polynomial freeform, interpreter kernel) for timing / ncu. usage: prof_c3.py [n] [strict]"""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 import optiland_pr_b200 as ol
 from optiland_pr_b200 import samples

@@ -1,7 +1,7 @@
 """The bench's dominant launch (olrt_trace_pupil_f64: ray launch + trace + final state + spot sums) on the bench lens,
-for ncu.  usage: python scratch/prof_fx.py [rays_per_field]"""
+for ncu.  usage: python profiles/recipes/prof_fx.py [rays_per_field]"""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 import optiland_pr_b200 as ol
 from optiland_pr_b200 import _lib, samples
