@@ -212,22 +212,25 @@ int olrt_trace_fwd_noalloc_f64(const olrt_sys* sys /*host*/, const double* presc
  *          (csrc/trace_bwd.cuh); OLRT_BWD_GENERIC forces the general kernel                                  */
 #define OLRT_BWD_GENERIC 1
 /* Tile-blocked checkpoints (differentiable trace without user-visible records): with OLRT_FWD_CKPT_BLOCKED the
- * forward's `record` argument is a buffer of ceil(n_rays / 256) * n_surfaces * 7 * 256 reals laid out
- * [tile][surface][x y z L M N intensity][256]: the state after every surface, 56 B per ray and surface, one
- * contiguous 14 KB block per (256-ray tile, surface). A plane as the LAST surface (the image plane) is the one
+ * forward's `record` argument is a buffer of ceil(n_rays / 256) * n_surfaces * OLRT_CKPT_VALS * 256 reals laid out
+ * [tile][surface][x y z L M copysign(intensity, N)][256]: the state after every surface, 48 B per ray and surface, one
+ * contiguous 12 KB block per (256-ray tile, surface). N is not stored: the backward rebuilds it as
+ * copysign(sqrt(1 - L^2 - M^2), sixth value) -- the direction is a unit vector to a few ulps, the sign rides on the
+ * intensity (>= 0, so its sign bit is free) -- a square root per surface for 1/7 of the checkpoint traffic. A plane as the LAST surface (the image plane) is the one
  * exception: its block is never written nor read (nothing needs its exit state). (Leaving ALL the planes out and recomputing their exit states in
  * the backward was measured: -224 B per ray of traffic but +160 instructions per ray in kernels that are
  * issue-bound, not bandwidth-bound: slower. DESIGN.md section 5.)
  * olrt_sys.n_record must be 0 (no [S][8][N] records in the same
  * launch); lenses of planes / conics / even aspheres in tolerance mode only (OLRT_E_UNSUPPORTED otherwise).
  * With OLRT_BWD_CKPT_BLOCKED the backward's `record` argument is that buffer (grecord must be NULL): a thread's
- * seven values of a surface sit at fixed offsets from one pointer (cp.async copies without address arithmetic).
+ * six values of a surface sit at fixed offsets from one pointer (cp.async copies without address arithmetic).
  * OLRT_BWD_NO_FRAME_XY: the caller does not want d loss / d (frame x, frame y) (no decenter is a variable): those two
  * columns of gpresc stay zero and the reduced-algebra kernel skips their accumulation (ignored by the general one). */
 #define OLRT_FWD_CKPT_BLOCKED 4
 #define OLRT_BWD_CKPT_BLOCKED 2
 #define OLRT_BWD_NO_FRAME_XY 4
 #define OLRT_CKPT_TILE 256
+#define OLRT_CKPT_VALS 6
 int olrt_trace_bwd_f64(const olrt_sys* sys, const double* presc, const int32_t* ops, int64_t n_rays,
                        const double* const in[8], const double* record, const double* const gout[8],
                        const double* grecord, double* const gin[8], double* gpresc, uint32_t* status,

@@ -40,6 +40,7 @@ FWD_CKPT_BLOCKED = 4     # olrt_trace_fwd_* flag: `record` is the tile-blocked c
 BWD_CKPT_BLOCKED = 2     # olrt_trace_bwd_* flag: `record` is that buffer
 BWD_NO_FRAME_XY = 4      # olrt_trace_bwd_* flag: d loss / d (frame x, frame y) is not wanted (no decenter variable)
 CKPT_TILE = 256
+CKPT_VALS = 6            # x y z L M copysign(intensity, N) per ray and surface (include/olrt.h)
 BWD_GENERIC = 1          # olrt_trace_bwd_* flag: force the general adjoint kernel (csrc/trace_bwd.cuh)
 BX_MAXK = 3              # Newton updates per surface the reduced-algebra adjoint kernel (csrc/trace_bx.cuh) unrolls
 FWD_FAST = 1

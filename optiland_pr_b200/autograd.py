@@ -171,7 +171,7 @@ def trace_differentiable(packed: PackedSystem, presc: torch.Tensor, rays_in, opd
     """rays_in: 8 tensors (w may be None for a single wavelength). Returns (out, record, dir0).
     generic_adjoint=True forces the general backward kernel (csrc/trace_bwd.cuh) instead of the reduced-algebra one.
     blocked=True (packed with record="none", tolerance mode, plane / conic / even-asphere lens): the checkpoints are
-    tile-blocked (include/olrt.h, OLRT_FWD_CKPT_BLOCKED) -- 56 B per ray and surface, read by the backward at fixed
+    tile-blocked (include/olrt.h, OLRT_FWD_CKPT_BLOCKED) -- 48 B per ray and surface, read by the backward at fixed
     offsets from one pointer -- and `record` comes back empty."""
     x, y, z, Lc, M, N, inten, w = (list(rays_in) + [None])[:8]
     return FusedTraceFn.apply(presc, x, y, z, Lc, M, N, inten, opd_in, w, packed, fast, generic_adjoint, blocked)

@@ -124,13 +124,14 @@ template <typename R>
 __device__ __forceinline__ void bx_conic(const FxSurf<R>& sf, const FxMedium<R>& md, int kind, bool z0, R ex, R ey,
                                          R ez, R eL, R eM, R eN, R ei, R irec, R Qgx, R Qgy, R Qgz, R& gx, R& gy,
                                          R& gz, R& gL, R& gM, R& gN, R& gi, R gopd, R& gTx, R& gTy, R& gTz, R& gR,
-                                         R& gk) {
+                                         R& gk, bool unit_dir = false) {
   typedef FxMath<R> Mx;
   const bool cen = (kind & FX_CENTERED) != 0;
   const R x = cen ? ex : ex - sf.xc, y = cen ? ey : ey - sf.yc, z = ez - sf.zc;
   const R Qx = cen ? Qgx : Qgx - sf.xc, Qy = cen ? Qgy : Qgy - sf.yc, Qz = Qgz - sf.zc;
-  const R dd = fma(eL, eL, fma(eM, eM, eN * eN));
-  const R t = fma(Qx - x, eL, fma(Qy - y, eM, (Qz - z) * eN)) * Mx::rcp(dd);
+  // unit_dir: N was rebuilt as sqrt(1 - L^2 - M^2) (blocked checkpoints), so |d|^2 = 1 by construction
+  R t = fma(Qx - x, eL, fma(Qy - y, eM, (Qz - z) * eN));
+  if (!unit_dir) t *= Mx::rcp(fma(eL, eL, fma(eM, eM, eN * eN)));
   const R r2 = fma(Qx, Qx, Qy * Qy);
   const R w = fma(-sf.c1, Qz, sf.radius);
   const R G = Mx::rcp(w);
@@ -397,6 +398,31 @@ __device__ __forceinline__ void bx_cp_async7(unsigned dst, const R* src) {
         : "memory");
 }
 
+// the six components of one tile-blocked checkpoint (x y z L M copysign(i, N), olrt.h)
+template <typename R, int STRIDE>
+__device__ __forceinline__ void bx_cp_async6(unsigned dst, const R* src) {
+  if (sizeof(R) == 8)
+    asm volatile(
+        "cp.async.ca.shared.global [%0], [%1], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%2], [%1+%2], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%3], [%1+%3], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%4], [%1+%4], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%5], [%1+%5], 8;\n\t"
+        "cp.async.ca.shared.global [%0+%6], [%1+%6], 8;" ::"r"(dst), "l"(src), "n"(STRIDE), "n"(2 * STRIDE),
+        "n"(3 * STRIDE), "n"(4 * STRIDE), "n"(5 * STRIDE)
+        : "memory");
+  else
+    asm volatile(
+        "cp.async.ca.shared.global [%0], [%1], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%2], [%1+%2], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%3], [%1+%3], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%4], [%1+%4], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%5], [%1+%5], 4;\n\t"
+        "cp.async.ca.shared.global [%0+%6], [%1+%6], 4;" ::"r"(dst), "l"(src), "n"(STRIDE), "n"(2 * STRIDE),
+        "n"(3 * STRIDE), "n"(4 * STRIDE), "n"(5 * STRIDE)
+        : "memory");
+}
+
 // shared load from a 32-bit shared address + element offset
 template <typename R> __device__ __forceinline__ R bx_lds(unsigned base, int elem);
 template <> __device__ __forceinline__ double bx_lds<double>(unsigned base, int elem) {
@@ -498,14 +524,14 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
       for (int q = 0; q < W; ++q) if (wl == P.wavelengths[q]) widx = q;
     }
     // state after the last surface, then the entry state of surface S-1 (= record S-2; the launch state for S == 1)
-    const R* rp = CK ? P.record + (tile * S + (S - 1)) * (long long)(7 * bd) + threadIdx.x  // block of surface S-1
+    const R* rp = CK ? P.record + (tile * S + (S - 1)) * (long long)(OLRT_CKPT_VALS * bd) + threadIdx.x  // block of surface S-1
                      : P.record + (long long)(S - 1) * 8 * N + idx;
     // CK: a plane as the last surface has no checkpoint (olrt.h): bx_plane needs no exit point, and its intensity
     // factor is computed directly (z0p below) instead of from the exit intensity
     const bool last_plane = CK && (s_info[S - 1].kind & 15) == KIND_PLANE;
     R Qgx = R(0), Qgy = R(0), Qgz = R(0), irec = R(0);
     if (CK) {
-      if (!last_plane) { Qgx = rp[0]; Qgy = rp[bd]; Qgz = rp[2 * bd]; irec = rp[6 * bd]; }
+      if (!last_plane) { Qgx = rp[0]; Qgy = rp[bd]; Qgz = rp[2 * bd]; irec = fabs(rp[5 * bd]); }
     } else {
       Qgx = rp[0]; Qgy = rp[N]; Qgz = rp[2 * N]; irec = rp[6 * N];
     }
@@ -513,8 +539,8 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
     auto stage = [&](int s_) {  // entry state of surface s_ -> buffer s_ & 1; rp walks down the records
       const unsigned dst = ck_a + (unsigned)((s_ & 1) * 7 * bd * (int)sizeof(R));
       if (CK && s_ > 0) {
-        rp -= 7 * bd;  // block of surface s_ - 1 (rp already includes this thread's column)
-        bx_cp_async7<R, (BD ? BD : 256) * (int)sizeof(R)>(dst, rp);   // CK implies 256-ray tiles
+        rp -= OLRT_CKPT_VALS * bd;  // block of surface s_ - 1 (rp already includes this thread's column)
+        bx_cp_async6<R, (BD ? BD : 256) * (int)sizeof(R)>(dst, rp);   // CK implies 256-ray tiles
         cp_async_commit();
         return;
       }
@@ -546,8 +572,16 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
       }
       const unsigned cka = ck_a + (unsigned)(cb * 7 * bd * (int)sizeof(R));
       const R ex = bx_lds<R>(cka, 0), ey = bx_lds<R>(cka, bd), ez = bx_lds<R>(cka, 2 * bd),
-              eL = bx_lds<R>(cka, 3 * bd), eM = bx_lds<R>(cka, 4 * bd), eN = bx_lds<R>(cka, 5 * bd),
-              ei = bx_lds<R>(cka, 6 * bd);
+              eL = bx_lds<R>(cka, 3 * bd), eM = bx_lds<R>(cka, 4 * bd);
+      R eN = bx_lds<R>(cka, 5 * bd), ei;
+      if (CK && s > 0) {   // blocked checkpoints keep copysign(intensity, N) in the sixth slot (olrt.h): rebuild N
+        typedef FxMath<R> Mq;
+        ei = fabs(eN);
+        const R n2 = fma(-eM, eM, fma(-eL, eL, R(1)));
+        eN = Mq::copysign_(n2 > R(0) ? n2 * Mq::rsqrt(n2) : n2 * R(0), eN);
+      } else {
+        ei = bx_lds<R>(cka, 6 * bd);
+      }
       const FxSurf<R>& sf = s_surf[s];
       const FxMedium<R>& md = s_med[s * W + widx];
       const FxInfo& info = s_info[s];
@@ -564,7 +598,7 @@ __global__ void __launch_bounds__(256, OLRT_BX_MIN_BLOCKS) trace_bx_kernel(const
       auto do_conic = [&](const int kk) {
         R gTx, gTy, gTz, gR, gk;
         bx_conic<R>(sf, md, kk, z0, ex, ey, ez, eL, eM, eN, ei, irec, Qgx, Qgy, Qgz, gx, gy, gz, gL, gM, gN, gi,
-                    gopd, gTx, gTy, gTz, gR, gk);
+                    gopd, gTx, gTy, gTz, gR, gk, CK && s > 0);
         if (NOXY) { const R pv[3] = {gTz, gR, gk}; bx_add_n<3>(acc + 2 * OLRT_BX_COLS, pv); }
         else { const R pv[5] = {gTx, gTy, gTz, gR, gk}; bx_add_n<5>(acc, pv); }
       };

@@ -15,7 +15,7 @@ struct FwdParams {
   const R* opd_in;
   R* out[8];
   R* record;
-  R* ckpt;  // nullptr, or tile-blocked checkpoints [tile][surface][7][OLRT_CKPT_TILE] (olrt.h, OLRT_FWD_CKPT_BLOCKED)
+  R* ckpt;  // nullptr, or tile-blocked checkpoints [tile][surface][OLRT_CKPT_VALS][OLRT_CKPT_TILE] (olrt.h, OLRT_FWD_CKPT_BLOCKED)
   R* dir0;
   const R* presc;
   const int32_t* ops;
@@ -310,10 +310,9 @@ __device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r,
     }
     if (P.ckpt != nullptr && valid && !(s == S - 1 && s_kind[s] == KIND_PLANE)) {
       // blocked checkpoint of this ray (the fix-up pass repairs single rays; a last plane has none, olrt.h)
-      R* ck = P.ckpt + (((idx / OLRT_CKPT_TILE) * S + s) * 7) * OLRT_CKPT_TILE + (idx % OLRT_CKPT_TILE);
+      R* ck = P.ckpt + (((idx / OLRT_CKPT_TILE) * S + s) * OLRT_CKPT_VALS) * OLRT_CKPT_TILE + (idx % OLRT_CKPT_TILE);
       ck[0] = r.x; ck[OLRT_CKPT_TILE] = r.y; ck[2 * OLRT_CKPT_TILE] = r.z;
-      ck[3 * OLRT_CKPT_TILE] = r.L; ck[4 * OLRT_CKPT_TILE] = r.M; ck[5 * OLRT_CKPT_TILE] = r.N;
-      ck[6 * OLRT_CKPT_TILE] = r.i;
+      ck[3 * OLRT_CKPT_TILE] = r.L; ck[4 * OLRT_CKPT_TILE] = r.M; ck[5 * OLRT_CKPT_TILE] = copysign(r.i, r.N);
     }
   }
 }

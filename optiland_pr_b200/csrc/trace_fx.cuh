@@ -7,7 +7,7 @@
 // far fewer fp64 instructions, and is held to the stated tolerance (1e-10 relative, identical masks)
 // instead of to the bit:
 //   * 1/b and 1/sqrt(a) come from the MUFU seed (2^-20, measured) and ONE third-order refinement
-//     (measured 2^-53 on 2^22 operands, scratch/seed_probe.cu); a/b = a * (1/b), sqrt(a) = a * rsqrt(a)
+//     (measured 2^-53 on 2^22 operands, profiles/recipes/seed_probe.cu); a/b = a * (1/b), sqrt(a) = a * rsqrt(a)
 //   * sphere normal = (P - C)/R (no square root); conic normal = sgn(R) (x, y, -(R - (1+k) z)) / |.|
 //     (standard.py:142-167 evaluates the same vector as (x/(R q), y/(R q), -1)/|.|, q = sqrt(1-(1+k)r^2/R^2),
 //     and R q = R - (1+k) z on the sheet the root selection picks)
@@ -624,7 +624,7 @@ trace_fx_kernel(const FwdParams<R> P) {
     R L0 = r.L, M0 = r.M, N0 = r.N, att = R(0);
     int guard = 0x7fffffff;  // smallest decision margin seen (FxMath::g_*): below OLRT_FX_GHI the strict pass takes the ray
     // this thread's column of the tile's first checkpoint block; surface s sits s blocks further on
-    R* const ck_ptr = ck_on ? P.ckpt + (tile * S * 7) * OLRT_CKPT_TILE + threadIdx.x : nullptr;
+    R* const ck_ptr = ck_on ? P.ckpt + (tile * S * OLRT_CKPT_VALS) * OLRT_CKPT_TILE + threadIdx.x : nullptr;
     R i_rec = r.i;          // intensity as recorded, r.i exp(att): exp() only after an absorbing medium
     bool i_stale = false;
     for (int s = 0; s < S; ++s) {
@@ -668,10 +668,10 @@ trace_fx_kernel(const FwdParams<R> P) {
         // a plane as the LAST surface (the image plane) is not checkpointed: nothing downstream needs its exit state
         // and the backward computes the plane's own intensity factor directly (trace_bx.cuh, z0p)
         if (valid && !(s == S - 1 && (kind & 15) == KIND_PLANE)) {
-          R* ckp = ck_ptr + (long long)s * (7 * OLRT_CKPT_TILE);
+          R* ckp = ck_ptr + (long long)s * (OLRT_CKPT_VALS * OLRT_CKPT_TILE);
           __stcs(ckp, r.x); __stcs(ckp + OLRT_CKPT_TILE, r.y); __stcs(ckp + 2 * OLRT_CKPT_TILE, r.z);
           __stcs(ckp + 3 * OLRT_CKPT_TILE, r.L); __stcs(ckp + 4 * OLRT_CKPT_TILE, r.M);
-          __stcs(ckp + 5 * OLRT_CKPT_TILE, r.N); __stcs(ckp + 6 * OLRT_CKPT_TILE, i_rec);
+          __stcs(ckp + 5 * OLRT_CKPT_TILE, FxMath<R>::copysign_(i_rec, r.N));   // N itself is rebuilt by the backward (olrt.h)
         }
         continue;
       }

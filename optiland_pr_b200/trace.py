@@ -145,11 +145,11 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
     n_rec = len(packed.record_surfaces)
     record = torch.empty((n_rec, 8, n), dtype=dtype, device=device) if n_rec else None
     ckpt_buf = None
-    if ckpt:  # tile-blocked checkpoints [tile][surface][7][256] instead of records (include/olrt.h)
+    if ckpt:  # tile-blocked checkpoints [tile][surface][6][256] instead of records (include/olrt.h)
         if n_rec or not fast or n_presc != 1:
             raise L.OlrtLibraryError("blocked checkpoints need record='none', tolerance mode and one prescription")
         tiles = -(-n // L.CKPT_TILE)
-        ckpt_buf = torch.empty(tiles * packed.n_surfaces * 7 * L.CKPT_TILE, dtype=dtype, device=device)
+        ckpt_buf = torch.empty(tiles * packed.n_surfaces * L.CKPT_VALS * L.CKPT_TILE, dtype=dtype, device=device)
     if out is None:
         if alias_out and n_rec and packed.record_surfaces[-1] == packed.layouts[-1].index:
             # the final state IS the last surface's record: both stores land on the same lines (merged in L2),

@@ -153,7 +153,7 @@ def test_reduced_adjoint_valid_rays_only_prescription_gradient():
 
 @pytest.mark.parametrize("name,n", [("EvenAsphereDoubleGauss", 70_001), ("CookeTriplet", 4_096), ("_Mixed", 33_000)])
 def test_blocked_checkpoints_give_the_same_gradients(name, n):
-    """Tile-blocked checkpoints (OLRT_FWD_CKPT_BLOCKED / OLRT_BWD_CKPT_BLOCKED: 7 components per surface, one bulk copy
+    """Tile-blocked checkpoints (OLRT_FWD_CKPT_BLOCKED / OLRT_BWD_CKPT_BLOCKED: 6 components per surface, one bulk copy
     per tile and surface in the backward) against the [S, 8, N] records: same forward state, same adjoint arithmetic,
     so the gradients agree to rounding of the accumulation order; ragged last tile included."""
     lens = _Mixed() if name == "_Mixed" else getattr(samples, name)()
@@ -182,7 +182,12 @@ def test_blocked_checkpoints_give_the_same_gradients(name, n):
         got.append((out.detach().cpu().numpy(), dir0.cpu().numpy(), gin, presc.grad.cpu().numpy()))
     (o0, d0, g0, p0), (o1, d1, g1, p1) = got
     assert np.array_equal(o0, o1, equal_nan=True) and np.array_equal(d0, d1, equal_nan=True)
-    assert np.array_equal(g0, g1, equal_nan=True)            # per-ray gradients: the same arithmetic, bit for bit
+    # per-ray gradients: the same arithmetic on the same states, except that the blocked layout keeps no N -- the
+    # backward rebuilds it as sqrt(1 - L^2 - M^2) (include/olrt.h), a few ulps from the stored one
+    assert np.array_equal(np.isnan(g0), np.isnan(g1))
+    for q in range(8):
+        fin = np.isfinite(g0[q])
+        assert np.abs(g1[q][fin] - g0[q][fin]).max() <= 1e-12 * max(np.abs(g0[q][fin]).max(), 1e-300), q
     if np.isfinite(p0).all():
         assert np.array_equal(p0 != 0, p1 != 0)
         assert np.abs(p1 - p0).max() <= 1e-11 * np.abs(p0).max()
