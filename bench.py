@@ -480,7 +480,7 @@ def main():
     if args.extras:
         extras["scaling_legs"] = scaling_legs(torch, dist, lens, packed, npf, nf, S_eff, timed, args, rank, world, dev)
     if args.extras and world == 1:
-        extras.update(run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64_peak))
+        extras.update(run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64_peak, hbm_peak=hbm_peak))
 
     if rank != 0:
         if world > 1:
@@ -636,7 +636,7 @@ def reference_torch_eager():
     return out
 
 
-def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64_peak):
+def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64_peak, hbm_peak=None):
     """Other precisions / modes on the same workload, one field at a time to bound memory."""
     from optiland_pr_b200 import flops
     from optiland_pr_b200.trace import fused_trace
@@ -673,7 +673,7 @@ def run_extras(torch, lens, packed, npf, nf, S_eff, timed, args, fp32_peak, fp64
     except ImportError:
         bench_backward = None
     if bench_backward is not None:
-        out.update(bench_backward(lens, packed, ins64, timed, args, fp64_peak))
+        out.update(bench_backward(lens, packed, ins64, timed, args, fp64_peak, hbm_peak=hbm_peak))
     return out
 
 

@@ -310,7 +310,7 @@ def smoke_backward() -> str:
     return f"fwd+bwd ok: d(merit)/d(R1) = {g:.9e} (finite difference {fd:.9e})"
 
 
-def bench_backward(lens, packed, ins64, timed, args, fp64_peak) -> dict:
+def bench_backward(lens, packed, ins64, timed, args, fp64_peak, hbm_peak=None) -> dict:
     """fwd + bwd on the bench batch (C2 lens, 50 M rays) and on the Cooke triplet (C1 / C4 lens, 9 x 1 M rays), kernel
     level: `trace_differentiable` = olrt_trace_fwd_f64 writing checkpoints + olrt_trace_bwd_f64, driven by a fixed
     d loss / d out. Legs: gradients w.r.t. the whole prescription AND the six ray components with [S][8][N] records
@@ -353,10 +353,15 @@ def bench_backward(lens, packed, ins64, timed, args, fp64_peak) -> dict:
             o.backward(gout_w)
 
         ms = timed(step, max(2, args.steps // 2), 3)
+        # algorithmic HBM bytes per ray: fwd reads 7 inputs, writes 8 outputs + the checkpoints; bwd reads the
+        # checkpoints, 7 inputs and 8 output gradients, writes 6 ray gradients when they are wanted
+        by = 56 + 64 + 56 + 64 + (48 if ray_grads else 0) + 2 * (48 * (n_ck - 1) if blocked else 64 * S)
         out[name] = {"ray_surfaces_per_s": n * S / (ms * 1e-3), "ms": ms,
                      "frac_fp64_fma_peak": fl * n / (ms * 1e-3) / 1e12 / fp64_peak,
-                     "flops_per_ray_fwd_bwd": fl, "checkpoint_bytes_per_ray": 56 * n_ck if blocked else 64 * S,
-                     "checkpoints": "tile-blocked [tile][surface][7][256]" if blocked else "[S][8][N] records",
+                     "hbm_bytes_per_ray": by, "hbm_gbs": by * n / (ms * 1e-3) / 1e9,
+                     "frac_hbm_peak": (by * n / (ms * 1e-3) / 1e9 / hbm_peak) if hbm_peak else None,
+                     "flops_per_ray_fwd_bwd": fl, "checkpoint_bytes_per_ray": 48 * n_ck if blocked else 64 * S,
+                     "checkpoints": "tile-blocked [tile][surface][6][256] (x y z L M copysign(i, N))" if blocked else "[S][8][N] records",
                      "gradients": "prescription (frame z, radii, conics, asphere coefficients)" if not ray_grads else
                                   "prescription (frames, radii, conics, asphere coefficients) + x y z L M N of every ray",
                      "kernels": "trace_fx_kernel<double> writing the checkpoints + trace_bx_kernel<double> "
@@ -398,7 +403,14 @@ def bench_backward(lens, packed, ins64, timed, args, fp64_peak) -> dict:
     out["fp64_fwd_bwd_cooke"] = {
         "ray_surfaces_per_s": nC * Sc / (ms * 1e-3), "ms": ms, "rays": nC,
         "frac_fp64_fma_peak": flc * nC / (ms * 1e-3) / 1e12 / fp64_peak, "flops_per_ray_fwd_bwd": flc,
-        "checkpoint_bytes_per_ray": 56 * n_ckc,
+        "checkpoint_bytes_per_ray": 48 * (n_ckc - 1),
+        # 8 inputs (per-ray wavelengths) + 8 outputs + 6 of 7 checkpoint blocks written (the image plane has none),
+        # then the checkpoints, 8 inputs and 8 output gradients read: the sphere-only triplet is HBM-bound
+        "hbm_bytes_per_ray": 256 + 96 * (n_ckc - 1),
+        "hbm_gbs": (256 + 96 * (n_ckc - 1)) * nC / (ms * 1e-3) / 1e9,
+        "frac_hbm_peak": ((256 + 96 * (n_ckc - 1)) * nC / (ms * 1e-3) / 1e9 / hbm_peak) if hbm_peak else None,
+        "bound": "hbm: 2586 flop over 832 B per ray = 3.1 flop/B, below the machine's 5.5 flop/B (35.8 TFLOP/s over "
+                 "6.5 TB/s): the FP64 fraction is what the bandwidth leaves",
         "workload": "Cooke triplet, 3 fields x 3 wavelengths x 1 M random pupil rays (per-ray wavelengths), "
                     "prescription gradients (frame z, radii, conics), blocked checkpoints"}
 
