@@ -206,7 +206,7 @@ def main():
     Hy = [f[1] for f in FIELDS]
 
     # ---- device-resident inputs for `value`: the pupil grid (what Optic.trace is given), already in HBM
-    from optiland_pr_b200.trace import fused_trace_pupil, slice_true_iters
+    from optiland_pr_b200.trace import fused_trace_pupil, group_true_iters
     Px_d, Py_d = Px_h.to(dev), Py_h.to(dev)
     n = nf * npf
     packed = lens.surface_group.pack([WAVELENGTH])
@@ -216,7 +216,12 @@ def main():
     out = torch.empty((8, n), dtype=torch.float64, device=dev)
     sums = torch.zeros((nf, _lib.SPOT_SUMS), dtype=torch.float64, device=dev)
     status_t = torch.zeros(1, dtype=torch.int32, device=dev)
-    resid = torch.zeros((packed.n_surfaces, _lib.RESID_STRIDE), dtype=torch.int64, device=dev)
+    # Newton trip counts PER FIELD (the reference's Optic.trace takes one field per call, so each field's rays decide
+    # their own exit test, newton_raphson.py:148): kf [nf][S] goes to the kernel as `group_k`, the per-field reports
+    # come back in `resid` [nf][S][GROUP_RESID]
+    kf = np.tile(np.asarray(packed.nr_iters(), dtype=np.int32), (nf, 1))
+    group_k = [torch.from_numpy(kf.copy()).to(dev)]
+    resid = torch.zeros((nf, packed.n_surfaces, _lib.GROUP_RESID), dtype=torch.int64, device=dev)
     zero1 = torch.zeros(1, dtype=torch.float64, device=dev)
     chief = torch.empty((8, nf), dtype=torch.float64, device=dev)
 
@@ -242,8 +247,7 @@ def main():
     def check_newton(slot):
         """The reference's exit rule (newton_raphson.py:148) on the residual maxima one step reported."""
         resid_ev[slot].synchronize()
-        k_used = packed.nr_iters()
-        return slice_true_iters(packed, resid_h[slot].numpy().view(np.float64), k_used) == k_used
+        return bool((group_true_iters(packed, resid_h[slot].numpy().view(np.float64), kf) == kf).all())
 
     shift_box = [None]
 
@@ -262,8 +266,8 @@ def main():
             fused_trace_pupil(packed, zero1, zero1, fxy_d, out=chief, **gen_kw)
             shift_box[0] = chief[:2].t().nan_to_num(0.0, 0.0, 0.0).contiguous()
         shift = shift_box[0]
-        fused_trace_pupil(packed, Px_d, Py_d, fxy_d, out=out, spot=cur, spot_shift=shift, resid_out=resid,
-                          status_t=status_t, **gen_kw)
+        fused_trace_pupil(packed, Px_d, Py_d, fxy_d, out=out, spot=cur, spot_shift=shift, group_k=group_k[0],
+                          group_resid=resid, status_t=status_t, **gen_kw)
         cur[:, 8:10] = shift
         if world > 1:
             works[slot] = dist.all_gather(parts2[slot], cur, async_op=True)
@@ -280,12 +284,12 @@ def main():
         tick[0] += 1
         if settle:   # first calls: find the counts the exit rule asks for
             resid_ev[slot].synchronize()
-            k_used = packed.nr_iters()
-            k_true = slice_true_iters(packed, resid_h[slot].numpy().view(np.float64), k_used)
+            kt = group_true_iters(packed, resid_h[slot].numpy().view(np.float64), kf)
             resid_ev[slot] = None
-            if k_true != k_used:
-                packed.set_nr_iters([min(lay.max_iter, max(k * 2, k + 2)) if kt is None else kt
-                                     for k, kt, lay in zip(k_used, k_true, packed.layouts)])
+            if not (kt == kf).all():
+                kf[:] = np.where(kt < 0, np.minimum(kf * 2 + 1, _lib.GROUP_RESID - 1), kt)
+                packed.set_nr_iters(kf.max(axis=0).tolist())   # the kernel's slot layout covers every field's counts
+                group_k[0] = torch.from_numpy(kf.copy()).to(dev)
                 return False
         return True
 
@@ -316,6 +320,7 @@ def main():
         if step_resident(settle=True):
             break
     nr_iters = packed.nr_iters()
+    nr_iters_per_field = kf.tolist()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -340,13 +345,27 @@ def main():
     rays = lens.launch_rays(np.asarray(Hx), np.asarray(Hy), Px_d, Py_d, WAVELENGTH)
     ins = rays.components()
     ins[7] = None
-    strict_out = fused_trace(packed, ins, fast=False).out
+    # field by field, as the reference's Optic.trace is called: each field's rays settle their own Newton trip counts
+    # (newton_raphson.py:148); the one-launch step must have used exactly those (`nr_iters_coincide`)
+    strict_out = torch.empty_like(out)
+    pk_f = lens.surface_group.pack([WAVELENGTH])
+    per_field = []
+    for f_ in range(nf):
+        sl = slice(f_ * npf, (f_ + 1) * npf)
+        res_f = fused_trace(pk_f, [c[sl] if c is not None else None for c in ins], out=strict_out[:, sl], fast=False)
+        per_field.append([int(k) for k in res_f.nr_iters])
     den = torch.clamp(strict_out.abs(), min=1.0)
     parity = {"max_rel_err_vs_strict_kernel": float(((out - strict_out).abs() / den).nan_to_num(0.0).max()),
               "nan_pattern_identical": bool((out.isnan() == strict_out.isnan()).all()),
               "vignetting_mask_identical": bool(((out[6] == 0) == (strict_out[6] == 0)).all()),
               "bar": "1e-10 relative, masks identical (BASELINE.json north_star)"}
     del den
+    parity["nr_iters_per_field"] = nr_iters_per_field
+    parity["nr_iters_field_by_field_calls"] = per_field
+    parity["nr_iters_coincide"] = per_field == nr_iters_per_field
+    if not parity["nr_iters_coincide"]:
+        raise SystemExit(f"Newton trip counts of the one-launch step {nr_iters_per_field} differ from those of "
+                         f"field-by-field calls {per_field}")
     # ---- the same check where the masks are not trivial ("C2 with aperture= radial stops"): the lens with
     # radial stops on its first, stop and last glass surfaces vignettes part of every off-axis bundle; tolerance-mode
     # kernel vs the strict kernel on the same 50 M rays: every clip decision must be the same one
@@ -380,12 +399,13 @@ def main():
     shift0 = sums[:, 8:10].contiguous()
 
     def only_trace():
-        fused_trace_pupil(packed, Px_d, Py_d, fxy_d, out=out, spot=sums, spot_shift=shift0, **gen_kw)
+        fused_trace_pupil(packed, Px_d, Py_d, fxy_d, out=out, spot=sums, spot_shift=shift0, group_k=group_k[0],
+                          group_resid=resid, **gen_kw)
     leg_clock = ClockSampler(local)      # the SM clock DURING this leg: the arithmetic peak below is quoted at it
     leg_clock.start()
     ms_kernel = timed(only_trace, max(args.steps, 40), 3)
     leg_clocks = leg_clock.stop()
-    fl_ray = flops.flops_per_ray(packed, nr_iters)
+    fl_ray = float(np.mean([flops.flops_per_ray(packed, k) for k in nr_iters_per_field]))   # equal ray counts per field
     by_ray = 64.0 + 16.0 / nf   # 8 output doubles per ray + the pupil point (Px, Py) shared by the nf fields
     # measured FP64 FMA peak on this GPU (dependent-free DFMA chains, all SMs)
     sink = torch.zeros(1, dtype=torch.float64, device=dev)
@@ -429,7 +449,7 @@ def main():
                                                          if peak_clocks.get("sm_mhz") else None)},
         "flops_per_ray": fl_ray, "flops_note": "the trace's algorithmic count (SURVEY.md 8d); ray launch and spot "
                                                "sums are executed but not counted",
-        "bytes_per_ray": by_ray, "nr_iters": nr_iters, "ms_per_launch": ms_kernel,
+        "bytes_per_ray": by_ray, "nr_iters": nr_iters, "nr_iters_per_field": nr_iters_per_field, "ms_per_launch": ms_kernel,
         "hbm": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs / hbm_peak,
                 "peak_source": hbm_src + " (MEASURED_PEAKS.json hbm_gbs)"},
         "traffic": None,

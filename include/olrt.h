@@ -327,8 +327,12 @@ int olrt_generate_rays_f32(const olrt_pupil* pupil, float* const out[8], void* s
  *  group_k    NULL, or [groups][n_surfaces] int32 (device): Newton trip counts PER GROUP instead of ops word 6.
  *             The reference traces every (trial, field) on its own, so its exit rule (max |f| over that trace's
  *             rays < tol, newton_raphson.py:148) gives each group its own K_s (<= OLRT_GROUP_RESID - 1 here).
- *  group_resid NULL, or [groups][n_surfaces][OLRT_GROUP_RESID] u64 (device, zeroed by the caller): max |f| per
- *             group, surface and iteration (bits of a non-negative double), for the caller to check K_s with.    */
+ *             Ops word 6 must hold the MAXIMUM of the groups' counts for every Newton surface (a group never takes
+ *             more than that many updates). Allowed together with a streamed grid when olrt_sys.nr_resid_words <= 32.
+ *  group_resid NULL, or [groups][n_surfaces][OLRT_GROUP_RESID] u64 (device, zeroed by the caller): v_j per group,
+ *             surface and iteration with "v_j < tol <=> every ray of the group converged at iteration j" (bits of a
+ *             non-negative double: the true maximum of |f|, or OLRT_RESID_FAILED for a failing slot when the counts
+ *             fit one register -- nr_resid_words <= 32 -- exactly as for nr_resid), for the caller to check K_s with. */
 /* Host -> device upload of a pinned pupil grid for the streamed mode above, in ONE call: for every chunk c of
  * `ready_chunk` points, cudaMemcpyAsync of Px and Py followed by a 4-byte copy that sets ready[c] (from `one_host`,
  * a pinned non-zero word), all on `copy_stream` -- the copy engine executes them in order, so ready[c] != 0 implies

@@ -453,13 +453,15 @@ __device__ __forceinline__ void fx_spot_flush(double* spot, int g, double cnt, d
 //   bit 1  per-surface stores: [S][8][N] records or tile-blocked checkpoints
 //   bit 3  every surface is centred, refracting and aperture-free (OLRT_HINT_ORDINARY, verified on the device):
 //          only those surface bodies are compiled in
-//   bit 2  (with bit 0) the reports are running maxima in shared memory (per-group counts, or more than 32
-//          residual slots); without it they are one bit per (surface, iteration) in a register
+//   bit 2  (with bit 0) the reports are running maxima in shared memory (more than 32 residual slots); without it
+//          they are one bit per (surface, iteration) in a register
+//   bit 4  (with bit 0, without bit 2) per-group Newton trip counts (FwdParams::group_k) with the bit reports: the
+//          register is handed to the group's rows of group_resid whenever a CTA moves on to another group
 template <typename R, int MODE>
 __global__ void __launch_bounds__(OLRT_FX_BLOCK, (sizeof(R) == 4 ? OLRT_FX_MIN_BLOCKS_F32 : OLRT_FX_MIN_BLOCKS))
 trace_fx_kernel(const FwdParams<R> P) {
   constexpr bool M_VERIFY = (MODE & 1) != 0, M_STORES = (MODE & 2) != 0, M_MAXIMA = (MODE & 4) != 0;
-  constexpr bool M_ORD = (MODE & 8) != 0;
+  constexpr bool M_ORD = (MODE & 8) != 0, M_GBITS = (MODE & 16) != 0;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int S = P.n_surfaces, W = P.n_wavelengths;
   R* s_presc = reinterpret_cast<R*>(smem_raw);
@@ -478,7 +480,10 @@ trace_fx_kernel(const FwdParams<R> P) {
   __syncthreads();
   // group mode: per-(trial, field) Newton trip counts and residual maxima (FwdParams::group_k)
   const bool gmode = M_MAXIMA && (P.gen.px != nullptr) && (P.group_k != nullptr);   // launch_fwd picks the variant
-  const bool want_resid = M_VERIFY && (gmode ? (P.group_resid != nullptr) : (P.nr_resid != nullptr));
+  // the same counts with bit reports: slots are laid out by the ops table's counts (the caller stores the maximum
+  // over the groups there), a group uses the first K_g + 1 of each surface's
+  const bool gbits = M_GBITS && (P.gen.px != nullptr) && (P.group_k != nullptr);
+  const bool want_resid = M_VERIFY && ((gmode || gbits) ? (P.group_resid != nullptr) : (P.nr_resid != nullptr));
   if (threadIdx.x < S) {
     const int k = fk_kind(s_ops, threadIdx.x);
     s_info[threadIdx.x].kind = k;
@@ -579,6 +584,27 @@ trace_fx_kernel(const FwdParams<R> P) {
                             P.four_pi);
       __syncthreads();
     }
+    if (M_GBITS && gbits && grp != cur_g) {  // next (trial, field): hand the bits over, fetch its trip counts
+      __syncthreads();
+      if (bits_mode && cur_g >= 0) {
+        rbits = __reduce_or_sync(0xffffffffu, rbits);
+        if ((threadIdx.x & 31) == 0 && rbits != 0u) {
+          for (int s = 0; s < S; ++s) {
+            const int lo = s_info[s].roff, hi = (s + 1 < S) ? s_info[s + 1].roff : n_resid;
+            for (int q = lo; q < hi; ++q)
+              if (rbits & (1u << q))
+                atomicMax(P.group_resid + ((long long)cur_g * S + s) * OLRT_GROUP_RESID + (q - lo), OLRT_RESID_FAILED);
+          }
+        }
+        rbits = 0u;
+      }
+      if (threadIdx.x < S) {
+        const int k = P.group_k[(long long)grp * S + threadIdx.x], kmax = s_info[threadIdx.x].K;
+        s_gk[threadIdx.x] = k < kmax ? k : kmax;   // never past the slots the ops table's counts laid out
+      }
+      cur_g = grp;
+      __syncthreads();
+    }
     if (gmode && grp != cur_g) {  // next (trial, field): hand its residual maxima over, fetch its trip counts
       __syncthreads();
       if (want_resid && cur_g >= 0) fx_group_flush(P.group_resid, cur_g, S, s_resid);
@@ -635,7 +661,7 @@ trace_fx_kernel(const FwdParams<R> P) {
       const FxMedium<R>& md = s_med[s * W + widx];
       const FxInfo& info = s_info[s];
       const int kind = info.kind;
-      const int Ks = gmode ? s_gk[s] : info.K;
+      const int Ks = (gmode || (M_GBITS && gbits)) ? s_gk[s] : info.K;
       unsigned long long* const rs = (M_MAXIMA && want_resid) ? (s_resid + info.roff) : nullptr;
       unsigned* const rb = bits_mode ? &rbits : nullptr;
       const R* const cf = s_coef + info.coef_off;
@@ -733,11 +759,14 @@ trace_fx_kernel(const FwdParams<R> P) {
   __syncthreads();
   if (bits_mode) {
     rbits = __reduce_or_sync(0xffffffffu, rbits);
-    if ((threadIdx.x & 31) == 0 && rbits != 0u) {
+    if ((threadIdx.x & 31) == 0 && rbits != 0u && !(M_GBITS && gbits && cur_g < 0)) {
+      unsigned long long* const dst = (M_GBITS && gbits) ? P.group_resid + (long long)cur_g * S * OLRT_GROUP_RESID
+                                                         : P.nr_resid;
+      const int stride = (M_GBITS && gbits) ? OLRT_GROUP_RESID : OLRT_RESID_STRIDE;
       for (int s = 0; s < S; ++s) {
         const int lo = s_info[s].roff, hi = (s + 1 < S) ? s_info[s + 1].roff : n_resid;
         for (int q = lo; q < hi; ++q)
-          if (rbits & (1u << q)) atomicMax(P.nr_resid + (long long)s * OLRT_RESID_STRIDE + (q - lo), OLRT_RESID_FAILED);
+          if (rbits & (1u << q)) atomicMax(dst + (long long)s * stride + (q - lo), OLRT_RESID_FAILED);
       }
     }
   } else if (gmode) {

@@ -114,9 +114,12 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
     if (xsmem > 200 * 1024) return OLRT_E_LIMIT;
     // group mode without residual reports still needs the per-group trip counts: the maxima variant carries them
     const bool verify = nr_resid != nullptr || P.group_resid != nullptr;
-    const bool maxima = P.group_k != nullptr || resid_words > 32;
-    const int mode = ((verify || P.group_k != nullptr) ? 1 : 0) | ((P.record != nullptr || P.ckpt != nullptr) ? 2 : 0) |
-                     (((verify || P.group_k != nullptr) && maxima) ? 4 : 0);
+    // per-group counts: bit reports when the ops table's counts fit one register (nr_resid_words <= 32), else maxima
+    const bool grp = P.group_k != nullptr;
+    const bool gbits = grp && sys->nr_resid_words <= 32 && P.record == nullptr && P.ckpt == nullptr;
+    const bool maxima = grp ? !gbits : resid_words > 32;
+    const int mode = ((verify || grp) ? 1 : 0) | ((P.record != nullptr || P.ckpt != nullptr) ? 2 : 0) |
+                     (((verify || grp) && maxima) ? 4 : 0) | (gbits ? 16 : 0);
     const bool ord = (sys->kernel_hint & OLRT_HINT_ORDINARY) != 0 && (mode & 4) == 0;
     void (*kern)(const FwdParams<R>) = nullptr;
     switch (mode | (ord ? 8 : 0)) {
@@ -129,7 +132,9 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
       case 8: kern = trace_fx_kernel<R, 8>; break;
       case 9: kern = trace_fx_kernel<R, 9>; break;
       case 10: kern = trace_fx_kernel<R, 10>; break;
-      default: kern = trace_fx_kernel<R, 11>; break;
+      case 11: kern = trace_fx_kernel<R, 11>; break;
+      case 17: kern = trace_fx_kernel<R, 17>; break;
+      default: kern = trace_fx_kernel<R, 25>; break;
     }
     if (xsmem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xsmem);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, xsmem);
@@ -138,7 +143,7 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
     if (grid > n_tiles) grid = n_tiles;
     if (gen != nullptr && gen->ready != nullptr) {  // streamed pupil grid: every CTA keeps one field
       if (sys->n_presc != 1 || gen->p_lo != 0 || gen->ready_chunk <= 0 || gen->ready_chunk % 256 != 0 ||
-          group_k != nullptr)
+          (group_k != nullptr && !gbits))   // per-field counts ride on the bit reports only
         return OLRT_E_ARG;
       grid = grid / gen->n_fields * gen->n_fields;
       if (grid < gen->n_fields) grid = gen->n_fields;

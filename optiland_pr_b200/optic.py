@@ -283,7 +283,10 @@ class Optic:
 
     # ---- RealRayTracer.trace / trace_generic, real_ray_tracer.py:37-133 -------------------------
     def trace(self, Hx, Hy, wavelength, num_rays=100, distribution="hexapolar", seed=None, spot=False):
-        """N rays = fields x pupil points, field-major (real_ray_tracer.py:61-77). `distribution`
+        """N rays = fields x pupil points, field-major (real_ray_tracer.py:61-77). A call with several fields is ONE
+        batch, like the reference's `trace_generic` with array-valued Hx, Hy: the Newton-Raphson exit test
+        (newton_raphson.py:148) is a maximum over all its rays. Trace field by field (scalars, as SpotDiagram does) for
+        per-field trip counts. `distribution`
         may be a name or a (Px, Py) pair of NumPy arrays / torch tensors (pinned host or device).
         spot=True also leaves the per-field spot sums (layout: include/olrt.h, olrt_spot_sums_*) in
         `rays.spot_sums` -- taken inside the trace kernel when the lens allows it (spot.spot_stats turns them
@@ -342,7 +345,7 @@ class Optic:
         them against the reference's exit rule (newton_raphson.py:148) and, if the counts were wrong for some
         chunk, the whole batch is traced again with the corrected counts."""
         from . import _lib as L
-        from .trace import fused_trace, fused_trace_pupil, slice_true_iters
+        from .trace import fused_trace, fused_trace_pupil, group_true_iters, slice_true_iters
         sg = self.surface_group
         dev = torch.device(be.get_device())
         dt = be.get_precision()
@@ -450,10 +453,21 @@ class Optic:
         rays_in = None if fused else torch.empty((8, n), dtype=dt, device=dev)
         n_slices = len(launches) * (1 if fused else nf)
         has_nr = bool(packed.nr_rows())
+        # Newton trip counts PER FIELD in the fused path: the reference's Optic.trace takes one field per call, so each
+        # field's rays decide their own exit test (newton_raphson.py:148); the kernel reads the counts of a tile's
+        # field from `group_k` and reports per field (include/olrt.h, olrt_trace_pupil_*)
+        per_field = bool(fused and has_nr and nf > 1)
+        kf = np.tile(np.asarray(packed.nr_iters(), dtype=np.int32), (nf, 1)) if per_field else None
         for attempt in range(8):
+            if per_field:
+                packed.set_nr_iters(kf.max(axis=0).tolist())   # the slot layout covers every field's counts
+                group_k = torch.from_numpy(kf).to(dev)
+                resid = torch.zeros((nf, packed.n_surfaces, L.GROUP_RESID), dtype=torch.int64, device=dev)
+            else:
+                group_k = None
+                resid = (torch.zeros((n_slices, packed.n_surfaces, L.RESID_STRIDE), dtype=torch.int64, device=dev)
+                         if has_nr else None)
             k_used = packed.nr_iters()
-            resid = (torch.zeros((n_slices, packed.n_surfaces, L.RESID_STRIDE), dtype=torch.int64, device=dev)
-                     if has_nr else None)
             if attempt and sums is not None:
                 sums.zero_()
             q_ = 0
@@ -465,7 +479,8 @@ class Optic:
                 if fused:
                     fused_trace_pupil(packed, Px_d, Py_d, fxy_all, p_lo=lo, p_len=hi - lo, out=out, dir0=dir0,
                                       spot=sums, spot_shift=shift, status_t=status_t,
-                                      resid_out=None if resid is None else resid[q_], ready=ready,
+                                      resid_out=None if (resid is None or per_field) else resid[q_],
+                                      group_k=group_k, group_resid=resid if per_field else None, ready=ready,
                                       ready_chunk=ready_chunk, **gen_kw)
                     mark(f"chunk{q_}", main)
                     q_ += 1
@@ -491,6 +506,15 @@ class Optic:
             sums_host = None if pins[2] is None else pins[2].clone()
             if not has_nr:
                 break
+            if per_field:
+                kt = group_true_iters(packed, pins[0].numpy().view(np.float64), kf)
+                if (kt == kf).all():
+                    break
+                if ((kt < 0) & (kf >= L.GROUP_RESID - 1)).any():
+                    raise L.OlrtLibraryError("a field needs more than %d Newton updates per surface"
+                                             % (L.GROUP_RESID - 1))
+                kf = np.where(kt < 0, np.minimum(kf * 2 + 1, L.GROUP_RESID - 1), kt).astype(np.int32)
+                continue
             rows = pins[0].numpy().view(np.float64)
             per_slice = [slice_true_iters(packed, rows[q], k_used) for q in range(n_slices)]
             if any(v is None for ps in per_slice for v in ps):      # some slice needs more updates
@@ -517,6 +541,7 @@ class Optic:
             rays = RealRays(*[rays_in[q] for q in range(8)])
         sg.reset()
         sg._finish(rays, packed, out, None, dir0, packed.nr_iters())
+        rays.nr_iters_per_field = kf.tolist() if per_field else [packed.nr_iters()] * nf
         if fused and sg.record == "last":
             sg.surfaces[-1]._set_record(out)
         if spot:

@@ -334,6 +334,7 @@ def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Ten
     nr_rows = packed.nr_rows()
     kg = (np.repeat(k0[None, :, :], T, axis=0).reshape(G, S) if k0.shape[0] == nf and k0.ndim == 2 and G != nf
           else np.asarray(k0).reshape(G, S)).astype(np.int32)
+    packed.set_nr_iters(np.maximum(kg.max(axis=0), 0).tolist())   # (see the launch below)
     if shift is None:
         zero1 = torch.zeros(1, dtype=torch.float64, device=dev)
         chief = torch.empty((8, G), dtype=dt, device=dev)
@@ -351,6 +352,8 @@ def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Ten
         check = bool(nr_rows) and settle
         gres = torch.zeros((gsel.size, S, L.GROUP_RESID), dtype=torch.int64, device=dev) if check else None
         sh = shift[gsel_t].contiguous()
+        # the kernel lays its residual slots out by the ops table's counts and never gives a group more than those
+        packed.set_nr_iters(np.maximum(kg[gsel].max(axis=0), 0).tolist())
         fused_trace_pupil(packed, Px, Py, field_xy, out=None, spot=sums, spot_shift=sh, spot_valid_only=valid_only,
                           presc=presc_t[sel].contiguous(), group_k=k_t, group_resid=gres, **gen_kw)
         sums[:, 8:10] = sh

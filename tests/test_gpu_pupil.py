@@ -8,6 +8,7 @@ import torch
 from oracle import raygen_np
 from optiland_pr_b200 import _lib as L
 from optiland_pr_b200 import backend as be
+from optiland_pr_b200 import optic as optic_mod
 from optiland_pr_b200 import samples, spot
 from optiland_pr_b200.apertures import RadialAperture
 from optiland_pr_b200.trace import fused_trace, fused_trace_pupil
@@ -190,3 +191,35 @@ def test_optic_trace_raises_when_a_chunk_never_arrives():
     rays = lens.trace([0.0], [1.0], 0.5876, distribution=(Px_h, Py_h))
     want = lens.trace([0.0], [1.0], 0.5876, distribution=(Px_h.cuda(), Py_h.cuda()))
     assert torch.equal(rays.x, want.x) and torch.equal(rays.opd, want.opd)
+
+
+def test_multi_field_trace_uses_each_fields_own_newton_counts():
+    """One Optic.trace over three fields == three single-field calls, bit for bit: the reference's Optic.trace takes one
+    field per call, so every field's rays decide their own Newton exit test (newton_raphson.py:148). At this size the
+    outer field needs one more update on one asphere than the inner two -- the one launch must not hand it to them."""
+    be.set_device("cuda:0")
+    be.set_precision("float64")
+    px, py = optic_mod.random_pupil_device(1 << 22, 1, "cuda:0")
+    Hx, Hy = [0.0, 0.0, 0.0], [0.0, 10.0 / 14.0, 1.0]
+    lens = samples.EvenAsphereDoubleGauss()
+    lens.surface_group.record = "none"
+    got = lens.trace(Hx, Hy, 0.5876, distribution=(px, py), spot=True)
+    n = px.numel()
+    counts = []
+    for f in range(3):
+        one = samples.EvenAsphereDoubleGauss()
+        one.surface_group.record = "none"
+        want = one.trace([Hx[f]], [Hy[f]], 0.5876, distribution=(px, py), spot=True)
+        counts.append(want.nr_iters_per_field[0])
+        for name in ("x", "y", "z", "L", "M", "N", "i", "opd"):
+            assert torch.equal(getattr(got, name)[f * n:(f + 1) * n], getattr(want, name)), (f, name)
+        assert torch.allclose(got.spot_sums[f], want.spot_sums[0], rtol=1e-11, atol=1e-9)   # atomics: order of addition
+    assert got.nr_iters_per_field == counts
+    assert len({tuple(c) for c in counts}) > 1, "pick a size where the fields' counts differ"
+    # the streamed host grid takes the same per-field counts
+    lens2 = samples.EvenAsphereDoubleGauss()
+    lens2.surface_group.record = "none"
+    lens2.pipeline_chunks = 4
+    s2 = lens2.trace(Hx, Hy, 0.5876, distribution=(px.cpu().pin_memory(), py.cpu().pin_memory()), spot=True)
+    assert s2.nr_iters_per_field == counts
+    assert torch.equal(s2.x, got.x) and torch.equal(s2.opd, got.opd)

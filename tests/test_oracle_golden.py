@@ -59,3 +59,18 @@ def test_wavefront_oracle_bit_exact():
         assert np.array_equal(got["opd"], g[f"f{k}_opd"], equal_nan=True)
         assert np.array_equal(np.stack([got["pupil_x"], got["pupil_y"], got["pupil_z"]]), g[f"f{k}_pupil"], equal_nan=True)
         assert np.array_equal(got["intensity"], g[f"f{k}_intensity"])
+
+
+@pytest.mark.parametrize("name", ["even_asphere_double_gauss", "three_mirror"])
+def test_oracle_pool_reproduces_one_big_call(name):
+    """oracle/pool.py (chunks on a process pool, batch-global Newton counts) == one call of the oracle on the batch."""
+    from oracle import pool
+    from helpers import mirror_packed
+    g = load_golden(name)
+    _, packed = mirror_packed(name, g["wavelengths"], record="none")
+    whole = trace_np.Rays(*[a.copy() for a in g["rays_in"]])
+    res = trace_np.trace_packed(packed, whole)
+    got, k = pool.trace_batch(packed, g["rays_in"], chunk=97, procs=3)
+    assert list(k) == list(res["nr_iters"])
+    want = np.stack([whole.x, whole.y, whole.z, whole.L, whole.M, whole.N, whole.i, whole.opd])
+    assert np.array_equal(got, want, equal_nan=True)
