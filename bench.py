@@ -405,6 +405,10 @@ def main():
     leg_clock.start()
     ms_kernel = timed(only_trace, max(args.steps, 40), 3)
     leg_clocks = leg_clock.stop()
+
+    def only_trace_unverified():   # the same launch without the Newton residual reports (counts trusted, not checked)
+        fused_trace_pupil(packed, Px_d, Py_d, fxy_d, out=out, spot=sums, spot_shift=shift0, **gen_kw)
+    ms_unverified = timed(only_trace_unverified, args.steps, 3)
     fl_ray = float(np.mean([flops.flops_per_ray(packed, k) for k in nr_iters_per_field]))   # equal ray counts per field
     by_ray = 64.0 + 16.0 / nf   # 8 output doubles per ray + the pupil point (Px, Py) shared by the nf fields
     # measured FP64 FMA peak on this GPU (dependent-free DFMA chains, all SMs)
@@ -435,8 +439,15 @@ def main():
     ach_tf = fl_ray * n / (ms_kernel * 1e-3) / 1e12
     ach_gbs = by_ray * n / (ms_kernel * 1e-3) / 1e9
     roofline = {
-        "kernel": "trace_fx_kernel<double>, pupil mode (in-kernel ray launch + trace + spot sums; tolerance mode: "
-                  "<= 1e-10 relative, masks identical) + its IEEE fix-up pass",
+        "kernel": "trace_fx_kernel<double, ordinary-lens variant with per-field Newton counts and residual reports>, "
+                  "pupil mode (in-kernel ray launch + trace + spot sums; tolerance mode: <= 1e-10 relative, masks "
+                  "identical) + its IEEE fix-up pass: the launch of the timed step",
+        "without_newton_reports": {
+            "ms_per_launch": ms_unverified,
+            "frac": flops.flops_per_ray(packed, nr_iters) * n / (ms_unverified * 1e-3) / 1e12 / fp64_peak,
+            "flops_per_ray": flops.flops_per_ray(packed, nr_iters),
+            "note": "the variant round 1's roofline was quoted on: batch-global trip counts taken on trust, no "
+                    "evaluation of the exit test (the reference evaluates it every iteration)"},
         "bound": "fp64_fma", "achieved": ach_tf, "peak": fp64_peak, "unit": "TFLOP/s",
         "frac": ach_tf / fp64_peak, "peak_source": "olrt_fma_peak_f64 measured in this run",
         # 64 FP64 FMA lanes per SM and clock (B200_PROFILING.md): the arithmetic ceiling at the clock each leg ran at

@@ -534,6 +534,9 @@ trace_fx_kernel(const FwdParams<R> P) {
     tile_lo = blockIdx.x / P.gen.n_fields;
     tile_hi = tpf;
     tile_step = gridDim.x / P.gen.n_fields;
+  } else if (M_GBITS && pupil && P.n_presc == 1) {
+    // per-field counts on one prescription: the fields differ in cost, so every CTA takes the same share of each
+    // (tiles b, b + grid, ...: still one run of tiles per field)
   } else if (pupil) {
     tile_lo = n_tiles * blockIdx.x / gridDim.x;
     tile_hi = n_tiles * (blockIdx.x + 1) / gridDim.x;
@@ -598,9 +601,10 @@ trace_fx_kernel(const FwdParams<R> P) {
         }
         rbits = 0u;
       }
-      if (threadIdx.x < S) {
-        const int k = P.group_k[(long long)grp * S + threadIdx.x], kmax = s_info[threadIdx.x].K;
-        s_gk[threadIdx.x] = k < kmax ? k : kmax;   // never past the slots the ops table's counts laid out
+      if (threadIdx.x < S) {  // the group's counts replace the table's in s_info: the surface loop is the batch one
+        const int k = P.group_k[(long long)grp * S + threadIdx.x];
+        const int kmax = s_ops[threadIdx.x * OLRT_OPS_STRIDE + OLRT_OP_NR_ITERS];
+        s_info[threadIdx.x].K = k < kmax ? k : kmax;   // never past the slots the ops table's counts laid out
       }
       cur_g = grp;
       __syncthreads();
@@ -661,7 +665,7 @@ trace_fx_kernel(const FwdParams<R> P) {
       const FxMedium<R>& md = s_med[s * W + widx];
       const FxInfo& info = s_info[s];
       const int kind = info.kind;
-      const int Ks = (gmode || (M_GBITS && gbits)) ? s_gk[s] : info.K;
+      const int Ks = gmode ? s_gk[s] : info.K;
       unsigned long long* const rs = (M_MAXIMA && want_resid) ? (s_resid + info.roff) : nullptr;
       unsigned* const rb = bits_mode ? &rbits : nullptr;
       const R* const cf = s_coef + info.coef_off;

@@ -457,7 +457,15 @@ class Optic:
         # field's rays decide their own exit test (newton_raphson.py:148); the kernel reads the counts of a tile's
         # field from `group_k` and reports per field (include/olrt.h, olrt_trace_pupil_*)
         per_field = bool(fused and has_nr and nf > 1)
-        kf = np.tile(np.asarray(packed.nr_iters(), dtype=np.int32), (nf, 1)) if per_field else None
+        kf = None
+        if per_field:   # first guess: what the same fields settled on last time (the exit rule is checked either way)
+            kf_key = (tuple(np.asarray(Hx, dtype=np.float64).reshape(-1).tolist()),
+                      tuple(np.asarray(Hy, dtype=np.float64).reshape(-1).tolist()), float(wavelength))
+            kf_cache = sg.__dict__.setdefault("_field_counts_cache", {})
+            kf = kf_cache.get(kf_key)
+            if kf is None or kf.shape != (nf, packed.n_surfaces):
+                kf = np.tile(np.asarray(packed.nr_iters(), dtype=np.int32), (nf, 1))
+            kf = kf.copy()
         for attempt in range(8):
             if per_field:
                 packed.set_nr_iters(kf.max(axis=0).tolist())   # the slot layout covers every field's counts
@@ -542,6 +550,10 @@ class Optic:
         sg.reset()
         sg._finish(rays, packed, out, None, dir0, packed.nr_iters())
         rays.nr_iters_per_field = kf.tolist() if per_field else [packed.nr_iters()] * nf
+        if per_field:
+            if len(kf_cache) > 16:
+                kf_cache.clear()
+            kf_cache[kf_key] = kf.copy()
         if fused and sg.record == "last":
             sg.surfaces[-1]._set_record(out)
         if spot:
