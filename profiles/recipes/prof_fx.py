@@ -13,7 +13,7 @@ lens = samples.EvenAsphereDoubleGauss(); lens.surface_group.record = "none"
 rng = np.random.default_rng(1)
 r = torch.from_numpy(rng.uniform(size=npf)).to(dev); th = torch.from_numpy(rng.uniform(0, 2*np.pi, npf)).to(dev)
 Px, Py = torch.sqrt(r)*torch.cos(th), torch.sqrt(r)*torch.sin(th)
-Hx, Hy = np.array([0.0, 0.0, 0.0]), np.array([0.0, 0.7, 1.0])
+Hx, Hy = np.array([0.0, 0.0, 0.0]), np.array([0.0, 10.0 / 14.0, 1.0])
 packed = lens.surface_group.pack([0.5876])
 packed.set_nr_iters([1, 0, 0, 0, 2, 0, 1, 0, 0, 0, 1, 0])   # the counts bench.py settles on
 fxy_np, z_start = lens._field_offsets(Hx, Hy)
@@ -23,6 +23,10 @@ n = 3 * npf
 out = torch.empty((8, n), dtype=torch.float64, device=dev)
 sums = torch.zeros((3, _lib.SPOT_SUMS), dtype=torch.float64, device=dev)
 shift = torch.zeros((3, 2), dtype=torch.float64, device=dev)
+# per-field Newton counts and residual reports, as in the timed step of bench.py (trace_fx_kernel<double, 25>)
+kf = torch.tensor([[1, 0, 0, 0, 1, 0, 1, 0, 0, 0, 1, 0]] * 2 + [[1, 0, 0, 0, 2, 0, 1, 0, 0, 0, 1, 0]], dtype=torch.int32, device=dev)
+gres = torch.zeros((3, packed.n_surfaces, _lib.GROUP_RESID), dtype=torch.int64, device=dev)
+kw.update(group_k=kf, group_resid=gres)
 for _ in range(3):
     fused_trace_pupil(packed, Px, Py, fxy, out=out, spot=sums, spot_shift=shift, **kw)
 torch.cuda.synchronize()
