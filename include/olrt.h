@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define OLRT_ABI_VERSION 5
+#define OLRT_ABI_VERSION 6   /* 6: 6-value blocked checkpoints, OLRT_HINT_ORDINARY, OLRT_BWD_NO_FRAME_XY, group counts with bit reports, olrt_pupil_random_f64, olrt_trace_fwd_noalloc_f64 */
 
 #define OLRT_MAX_SURFACES 64    /* intersected surfaces per system (object surface excluded) */
 #define OLRT_MAX_WAVELENGTHS 8  /* distinct wavelengths per launch */

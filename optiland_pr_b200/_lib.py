@@ -12,7 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("OLRT_LIB") or os.path.join(_HERE, "libolrt.so")  # OLRT_LIB: A/B builds only
 
-OLRT_ABI_VERSION = 5
+OLRT_ABI_VERSION = 6
 MAX_SURFACES = 64
 MAX_WAVELENGTHS = 8
 MAX_NR_ITERS = 128
