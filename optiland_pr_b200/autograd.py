@@ -43,6 +43,20 @@ def _live_entries(packed: PackedSystem, surfaces):
             for i, c in enumerate(g.coefficients):
                 if isinstance(c, torch.Tensor):
                     out.append((lay.coef + i, c))
+        if lay.geom == L.GEOM_POLYNOMIAL:      # C[i][j] row-major (geometries/polynomial.py:93-111)
+            co = g.coefficients
+            for i in range(len(co)):
+                for j in range(len(co[i])):
+                    c = co[i][j]
+                    if isinstance(c, torch.Tensor):
+                        out.append((lay.coef + i * len(co[i]) + j, c))
+        # tilts (optimization/variable/tilt.py:59): the row holds cos / sin of rz, ry, rx of the surface's one frame
+        if getattr(cs, "reference_cs", None) is None:
+            for q, nm in enumerate(("rz", "ry", "rx")):
+                v = getattr(cs, nm, None)
+                if isinstance(v, torch.Tensor):
+                    out.append((lay.frames + 3 + 2 * q, torch.cos(v)))
+                    out.append((lay.frames + 4 + 2 * q, torch.sin(v)))
     return out
 
 
@@ -71,7 +85,7 @@ class FusedTraceFn(torch.autograd.Function):
                 blocked=False):
         if not blocked and packed.record_surfaces != [lay.index for lay in packed.layouts]:
             raise L.OlrtLibraryError("the differentiable trace needs every surface recorded (record='all')")
-        if blocked and (packed.record_surfaces or not fast or generic_adjoint or not packed.fastkinds()):
+        if blocked and (packed.record_surfaces or not fast or generic_adjoint or not packed.reduced_adjoint()):
             raise NotImplementedError("blocked checkpoints: record='none', tolerance mode, plane / conic / "
                                       "even-asphere lens, reduced-algebra adjoint")
         ins = [x, y, z, Lc, M, N, inten, w]
@@ -124,8 +138,9 @@ class FusedTraceFn(torch.autograd.Function):
         lib = L.load()
         if not packed.differentiable(require_records=not ctx.blocked):
             raise NotImplementedError(
-                "olrt_trace_bwd: gradients are implemented for plane / conic / even-asphere surfaces (<= 8 "
-                "coefficients) on an untilted frame; this lens has a surface outside that set")
+                "olrt_trace_bwd: gradients are implemented for plane / conic / even-asphere / x^i y^j polynomial "
+                "surfaces (<= 16 coefficients) on one (decentred, tilted) frame; this lens has a surface outside "
+                "that set")
         packed.set_nr_iters(ctx.nr_iters)
         ops_d, _ = _device_tables(packed, dtype, device)
         # d loss / d rays only where a ray tensor asks for it (the kernel writes every element of a requested array)
@@ -142,7 +157,8 @@ class FusedTraceFn(torch.autograd.Function):
         gout_arr = L.PtrArray8(*[0 if gout is None else gout[q].data_ptr() for q in range(8)])
         gin_arr = L.PtrArray8(*[gin[q].data_ptr() if need[q] else 0 for q in range(8)])
         # the reduced-algebra adjoint (csrc/trace_bx.cuh) keeps <= BX_MAXK Newton iterates in registers
-        flags = L.BWD_GENERIC if (ctx.generic_adjoint or max(ctx.nr_iters, default=0) > L.BX_MAXK) else 0
+        flags = L.BWD_GENERIC if (ctx.generic_adjoint or max(ctx.nr_iters, default=0) > L.BX_MAXK
+                                  or not packed.reduced_adjoint()) else 0
         if ctx.blocked:
             if flags:
                 raise NotImplementedError("blocked checkpoints: a surface took more than 3 Newton updates; trace "

@@ -15,17 +15,21 @@
 // second derivatives of the sag), NOT replaced by the implicit-function gradient of the converged
 // root -- the two differ by O(residual), more than the 1e-8 gradient bar when tol = 1e-6.
 //
-// Differentiable here: plane, sphere / conic, even asphere on a single untilted frame (the fast kinds
-// of trace_fk.cuh) with any aperture program, absorption, refraction and reflection; gradients w.r.t.
-// frame x y z, radius, conic, even-asphere coefficients and the input rays x y z L M N intensity opd.
+// Differentiable here: plane, sphere / conic, even asphere and POLYNOMIAL (x^i y^j freeform, polynomial.py:93-142)
+// surfaces on ONE frame that may be decentred AND tilted (coordinate_system.py:73-107: rz, ry, rx), with any
+// aperture program, absorption, refraction and reflection; gradients w.r.t. the frame's x y z and the cosines /
+// sines of its three angles (the caller chains d cos / d angle: optimization/variable/tilt.py:59), radius, conic,
+// even-asphere / polynomial coefficients (polynomial_coeff.py:72) and the input rays x y z L M N intensity opd.
 // Anything else returns OLRT_E_UNSUPPORTED on the host side (no silent approximation).
 #pragma once
 #include "trace_fwd.cuh"
 
 namespace OLRT_NS {
 
-#define OLRT_BWD_MAXC 8  // even-asphere coefficients with a gradient slot in registers
-#define OLRT_BWD_SLOTS (5 + OLRT_BWD_MAXC)  // frame x y z, radius, conic, coefficients
+#define OLRT_BWD_MAXC 8  // even-asphere coefficients with a gradient slot in registers (reduced kernel, trace_bx.cuh)
+#define OLRT_BWD_SLOTS (5 + OLRT_BWD_MAXC)  // frame x y z, radius, conic, coefficients (reduced kernel)
+#define OLRT_BWG_MAXC 16                    // this kernel: even-asphere / polynomial coefficients with a gradient slot
+#define OLRT_BWG_SLOTS (OLRT_FRAME_REALS + 2 + OLRT_BWG_MAXC)  // frame x y z cz sz cy sy cx sx, radius, conic, coefficients
 
 template <typename R>
 struct BwdParams {
@@ -66,13 +70,15 @@ struct BwdConst {
 // sag S, slope factor G (zx = x G, zy = y G) and dG/dr2 of conic + even-asphere terms at (x, y)
 template <typename R>
 struct SagEval {
-  R r2, s, is, i1s, S, G, Gp;  // is = 1/s, i1s = 1/(1+s)
+  R r2, s, is, i1s, S, G, Gp;  // radial part: zx = x G, zy = y G; is = 1/s, i1s = 1/(1+s)
+  R Px, Py, Pxx, Pxy, Pyy;     // non-radial part (polynomial x^i y^j terms): zx = x G + Px, zxx = G + 2 x^2 Gp + Pxx ...
 };
 
 template <typename R>
 __device__ __forceinline__ void sag_eval(const SurfParams<R>& sp, const BwdConst<R>& bc, bool plane, R x, R y,
                                          SagEval<R>& e) {
   e.r2 = x * x + y * y;
+  e.Px = R(0); e.Py = R(0); e.Pxx = R(0); e.Pxy = R(0); e.Pyy = R(0);
   if (plane) { e.s = R(1); e.is = R(1); e.i1s = R(0.5); e.S = R(0); e.G = R(0); e.Gp = R(0); return; }
   const R c1 = sp.cc.c1;
   const R B = R(1) - c1 * e.r2 * bc.iR2;
@@ -93,8 +99,29 @@ __device__ __forceinline__ void sag_eval(const SurfParams<R>& sp, const BwdConst
       pw = pw * e.r2;
       e.S += Ci * pw;
     }
+  } else if (sp.geom == OLRT_GEOM_POLYNOMIAL) {  // sum C[i][j] x^i y^j, polynomial.py:108-111, :129-136
+    const int J = sp.aux, I = (J > 0) ? sp.ncoef / J : 0;
+    R xi = R(1), xim1 = R(0), xim2 = R(0);  // x^i, x^(i-1), x^(i-2)
+    for (int i = 0; i < I; ++i) {
+      R yj = R(1), yjm1 = R(0), yjm2 = R(0);
+      for (int j = 0; j < J; ++j) {
+        const R C = sp.coef[i * J + j];
+        e.S += C * xi * yj;
+        e.Px += R(i) * C * xim1 * yj;
+        e.Py += R(j) * C * xi * yjm1;
+        e.Pxx += R(i * (i - 1)) * C * xim2 * yj;
+        e.Pxy += R(i * j) * C * xim1 * yjm1;
+        e.Pyy += R(j * (j - 1)) * C * xi * yjm2;
+        yjm2 = yjm1; yjm1 = yj; yj = yj * y;
+      }
+      xim2 = xim1; xim1 = xi; xi = xi * x;
+    }
   }
 }
+
+// slopes of the sag at the evaluation point
+template <typename R> __device__ __forceinline__ R sag_zx(const SagEval<R>& e, R x) { return x * e.G + e.Px; }
+template <typename R> __device__ __forceinline__ R sag_zy(const SagEval<R>& e, R y) { return y * e.G + e.Py; }
 
 // adjoint of (S, zx, zy)(x, y; R, k, C) given (gS, gzx, gzy); accumulates gx, gy and the parameter partials
 template <typename R>
@@ -103,9 +130,9 @@ __device__ __forceinline__ void sag_adjoint(const SurfParams<R>& sp, const BwdCo
                                             R* gC) {
   if (plane) return;
   const R q = gzx * x + gzy * y;  // gradient w.r.t. G
-  const R zx = x * e.G, zy = y * e.G;
-  gx += gS * zx + gzx * e.G + q * e.Gp * (R(2) * x);
-  gy += gS * zy + gzy * e.G + q * e.Gp * (R(2) * y);
+  const R zx = x * e.G + e.Px, zy = y * e.G + e.Py;
+  gx += gS * zx + gzx * (e.G + e.Pxx) + gzy * e.Pxy + q * e.Gp * (R(2) * x);
+  gy += gS * zy + gzy * (e.G + e.Pyy) + gzx * e.Pxy + q * e.Gp * (R(2) * y);
   const R c1 = sp.cc.c1, r2 = e.r2;
   const R ds_dR = c1 * r2 * bc.iR3 * e.is;
   const R ds_dk = R(-0.5) * r2 * bc.iR2 * e.is;
@@ -117,8 +144,7 @@ __device__ __forceinline__ void sag_adjoint(const SurfParams<R>& sp, const BwdCo
   gk += (gS * dSc_ds + q * dg0_ds) * ds_dk;
   if (sp.geom == OLRT_GEOM_EVEN_ASPHERE) {
     R pw = R(1);
-#pragma unroll
-    for (int i = 0; i < OLRT_BWD_MAXC; ++i) {
+    for (int i = 0; i < OLRT_BWG_MAXC; ++i) {
       if (i < sp.ncoef) {
         const R k2 = R(2 * (i + 1));
         const R pw1 = pw * r2;
@@ -126,7 +152,80 @@ __device__ __forceinline__ void sag_adjoint(const SurfParams<R>& sp, const BwdCo
         pw = pw1;
       }
     }
+  } else if (sp.geom == OLRT_GEOM_POLYNOMIAL) {
+    const int J = sp.aux, I = (J > 0) ? sp.ncoef / J : 0;
+    R xi = R(1), xim1 = R(0);
+    for (int i = 0; i < I; ++i) {
+      R yj = R(1), yjm1 = R(0);
+      for (int j = 0; j < J; ++j) {
+        gC[i * J + j] += gS * xi * yj + gzx * (R(i) * xim1 * yj) + gzy * (R(j) * xi * yjm1);
+        yjm1 = yj; yj = yj * y;
+      }
+      xim1 = xi; xi = xi * x;
+    }
   }
+}
+
+// Adjoint of one plane rotation (a', b') = (a c - b s, a s + b c) -- RealRays.rotate_x / y / z, real_rays.py:90-130 --
+// walked BACKWARDS: on entry (a, b) is the rotated pair and (ga, gb) the gradient w.r.t. it; on exit they are the pair
+// before the rotation (the inverse of an orthogonal map is its transpose: no intermediate state is stored) and the
+// gradient w.r.t. that; gc / gs collect d loss / d cos, d sin.
+template <typename R>
+__device__ __forceinline__ void rot_adjoint(R c, R s, R& a, R& b, R& ga, R& gb, R& gc, R& gs) {
+  const R a0 = a * c + b * s, b0 = b * c - a * s;
+  gc += a0 * ga + b0 * gb;
+  gs += a0 * gb - b0 * ga;
+  const R ga0 = c * ga + s * gb, gb0 = c * gb - s * ga;
+  a = a0; b = b0; ga = ga0; gb = gb0;
+}
+
+// Adjoint of frame_globalize (trace_common.cuh): (P, D) is the GLOBAL state after the frame, g* the gradient w.r.t.
+// it; on exit both refer to the local state before it. gF[9]: d loss / d (x y z cz sz cy sy cx sx) of the frame.
+template <typename R>
+__device__ __forceinline__ void frame_globalize_adjoint(const R* f, int fl, R& x, R& y, R& z, R& L, R& M, R& N,
+                                                        R& gx, R& gy, R& gz, R& gL, R& gM, R& gN, R* gF) {
+  gF[0] += gx; gF[1] += gy; gF[2] += gz;
+  x -= f[0]; y -= f[1]; z -= f[2];
+  if (fl & 1) {  // rotate_z(rz): pairs (x, y), (L, M)
+    rot_adjoint(f[3], f[4], x, y, gx, gy, gF[3], gF[4]);
+    rot_adjoint(f[3], f[4], L, M, gL, gM, gF[3], gF[4]);
+  }
+  if (fl & 2) {  // rotate_y(ry): z' = z c - x s, x' = z s + x c: pairs (z, x), (N, L)
+    rot_adjoint(f[5], f[6], z, x, gz, gx, gF[5], gF[6]);
+    rot_adjoint(f[5], f[6], N, L, gN, gL, gF[5], gF[6]);
+  }
+  if (fl & 4) {  // rotate_x(rx): pairs (y, z), (M, N)
+    rot_adjoint(f[7], f[8], y, z, gy, gz, gF[7], gF[8]);
+    rot_adjoint(f[7], f[8], M, N, gM, gN, gF[7], gF[8]);
+  }
+}
+
+// Adjoint of frame_localize: (P, D) is the LOCAL state after the frame (translate by -T, rotate_z(-rz), rotate_y(-ry),
+// rotate_x(-rx)); on exit the global state before it. The rotations use sin(-a) = -sin a: the sine gradients flip sign.
+template <typename R>
+__device__ __forceinline__ void frame_localize_adjoint(const R* f, int fl, R& x, R& y, R& z, R& L, R& M, R& N,
+                                                       R& gx, R& gy, R& gz, R& gL, R& gM, R& gN, R* gF) {
+  R gs;
+  if (fl & 4) {
+    gs = R(0);
+    rot_adjoint(f[7], -f[8], y, z, gy, gz, gF[7], gs);
+    rot_adjoint(f[7], -f[8], M, N, gM, gN, gF[7], gs);
+    gF[8] -= gs;
+  }
+  if (fl & 2) {
+    gs = R(0);
+    rot_adjoint(f[5], -f[6], z, x, gz, gx, gF[5], gs);
+    rot_adjoint(f[5], -f[6], N, L, gN, gL, gF[5], gs);
+    gF[6] -= gs;
+  }
+  if (fl & 1) {
+    gs = R(0);
+    rot_adjoint(f[3], -f[4], x, y, gx, gy, gF[3], gs);
+    rot_adjoint(f[3], -f[4], L, M, gL, gM, gF[3], gs);
+    gF[4] -= gs;
+  }
+  gF[0] -= gx; gF[1] -= gy; gF[2] -= gz;
+  x += f[0]; y += f[1]; z += f[2];
 }
 
 // closed-form conic intersection in the half-b form (trace_common.cuh); also returns a, hb for the adjoint
@@ -164,17 +263,22 @@ __device__ __forceinline__ R warp_sum(R v) {
 
 // one surface, reverse mode. Entry state e* (global), incoming grads g* (w.r.t. the state after the surface,
 // global) are replaced by the grads w.r.t. the entry state. gi: intensity, gopd: opd (passes through).
+// gF[9]: d loss / d (frame x y z cz sz cy sy cx sx); gC[OLRT_BWG_MAXC]: coefficients.
 template <typename R>
 __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int widx, R ex, R ey, R ez, R eL, R eM,
                                             R eN, R ei, R& gx, R& gy, R& gz, R& gL, R& gM, R& gN, R& gi, R gopd,
-                                            R& gTx, R& gTy, R& gTz, R& gR, R& gk, R* gC) {
+                                            R* gF, R& gR, R& gk, R* gC) {
   const int32_t* op = sp.op;
   const bool plane = (sp.geom == OLRT_GEOM_PLANE);
   const int flags = op[OLRT_OP_FLAGS];
   const R* f = sp.frames;
-  // ---- forward recompute (local frame)
-  const R x = ex - f[0], y = ey - f[1], z = ez - f[2];
-  const R L = eL, M = eM, N = eN;
+  const int fl = op[OLRT_OP_FRAMEFLAGS] & 7;
+  // ---- forward recompute (local frame): CoordinateSystem.localize, coordinate_system.py:73-88
+  RayState<R> loc;
+  loc.x = ex; loc.y = ey; loc.z = ez; loc.L = eL; loc.M = eM; loc.N = eN; loc.i = ei; loc.opd = R(0);
+  frame_localize(loc, f, fl);
+  const R x = loc.x, y = loc.y, z = loc.z;
+  const R L = loc.L, M = loc.M, N = loc.N;
   BwdConst<R> bc;
   bc.iR = plane ? R(0) : brcp(sp.cc.radius);
   bc.iR2 = bc.iR * bc.iR;
@@ -183,37 +287,49 @@ __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int 
   R a = R(0), hb = R(0), t0;
   if (plane) t0 = -z * iN;
   else t0 = conic_t(sp, x, y, z, L, M, N, a, hb);
-  const int K = (sp.geom == OLRT_GEOM_EVEN_ASPHERE) ? op[OLRT_OP_NR_ITERS] : 0;
+  const int K = (sp.geom >= OLRT_GEOM_EVEN_ASPHERE) ? op[OLRT_OP_NR_ITERS] : 0;
   R t = t0;
   for (int j = 0; j < K; ++j) {
     SagEval<R> e;
     const R qx = x + t * L, qy = y + t * M, qz = z + t * N;
     sag_eval(sp, bc, false, qx, qy, e);
-    const R h = qx * e.G * L + qy * e.G * M - N;
+    const R h = sag_zx(e, qx) * L + sag_zy(e, qy) * M - N;
     t = t - (e.S - qz) * brcp(h);
   }
-  const R Qx = x + t * L, Qy = y + t * M;
+  const R Qx = x + t * L, Qy = y + t * M, Qz = z + t * N;
   SagEval<R> eq;
   sag_eval(sp, bc, plane, Qx, Qy, eq);
   R nx, ny, nz, imag = R(1);
-  const R zx = Qx * eq.G, zy = Qy * eq.G;
+  const R zx = sag_zx(eq, Qx), zy = sag_zy(eq, Qy);
   if (plane) { nx = R(0); ny = R(0); nz = R(1); }
   else { imag = brcp(bsqrt(zx * zx + zy * zy + R(1))); nx = zx * imag; ny = zy * imag; nz = -imag; }
   const R dot = L * nx + M * ny + N * nz;
   const R sg = r_sign(dot), c = r_abs(dot);
   const R ax = nx * sg, ay = ny * sg, az = nz * sg;  // aligned normal
-  // ---- adjoint of globalize: out = local + T
-  gTx += gx; gTy += gy; gTz += gz;
+  const bool mirror = (op[OLRT_OP_INTERACT] == 1);
+  const R u = sp.u, u2 = sp.u2;
+  const R root = mirror ? R(0) : bsqrt(R(1) - u2 * (R(1) - c * c));
+  const R w = root - u * c;
+  // ---- adjoint of globalize (coordinate_system.py:90-107): needs the state it was applied to. Rebuild the local
+  // exit state (position Q, new direction), push it through the frame, and walk back
+  if (fl != 0) {
+    RayState<R> o;
+    o.x = Qx; o.y = Qy; o.z = Qz;
+    if (mirror) { o.L = L - R(2) * c * ax; o.M = M - R(2) * c * ay; o.N = N - R(2) * c * az; }
+    else { o.L = u * L + ax * w; o.M = u * M + ay * w; o.N = u * N + az * w; }
+    o.i = R(0); o.opd = R(0);
+    frame_globalize(o, f, fl);
+    frame_globalize_adjoint(f, fl, o.x, o.y, o.z, o.L, o.M, o.N, gx, gy, gz, gL, gM, gN, gF);
+  } else {  // out = local + T
+    gF[0] += gx; gF[1] += gy; gF[2] += gz;
+  }
   // ---- interaction
   R gDx, gDy, gDz, gax, gay, gaz, gc;
-  if (op[OLRT_OP_INTERACT] == 1) {  // D' = D - 2 c a
+  if (mirror) {  // D' = D - 2 c a
     gDx = gL; gDy = gM; gDz = gN;
     gc = R(-2) * (ax * gL + ay * gM + az * gN);
     gax = R(-2) * c * gL; gay = R(-2) * c * gM; gaz = R(-2) * c * gN;
   } else {  // D' = u D + a (root - u c)
-    const R u = sp.u, u2 = sp.u2;
-    const R root = bsqrt(R(1) - u2 * (R(1) - c * c));
-    const R w = root - u * c;
     gDx = u * gL; gDy = u * gM; gDz = u * gN;
     gax = w * gL; gay = w * gM; gaz = w * gN;
     const R gw = ax * gL + ay * gM + az * gN;
@@ -254,12 +370,12 @@ __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int 
       SagEval<R> e;
       const R qx = x + tj * L, qy = y + tj * M, qz = z + tj * N;
       sag_eval(sp, bc, false, qx, qy, e);
-      tj = tj - (e.S - qz) * brcp(qx * e.G * L + qy * e.G * M - N);
+      tj = tj - (e.S - qz) * brcp(sag_zx(e, qx) * L + sag_zy(e, qy) * M - N);
     }
     SagEval<R> e;
     const R qx = x + tj * L, qy = y + tj * M, qz = z + tj * N;
     sag_eval(sp, bc, false, qx, qy, e);
-    const R sx = qx * e.G, sy = qy * e.G;
+    const R sx = sag_zx(e, qx), sy = sag_zy(e, qy);
     const R fj = e.S - qz, ih = brcp(sx * L + sy * M - N);
     const R gf = -gtj * ih, gh = gtj * fj * ih * ih;
     gDx += gh * sx; gDy += gh * sy; gDz -= gh;
@@ -287,10 +403,15 @@ __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int 
     gPy += ghb * M + R(2) * gcc * y;
     gPz += ghb * (k * N + N) + gcc * (R(2) * k * z - R(2) * Rr + R(2) * z);
   }
-  // ---- localize: P = entry - T
-  gTx -= gPx; gTy -= gPy; gTz -= gPz;
+  // ---- localize: the entry state went through translate(-T) and the three rotations
   gx = gPx; gy = gPy; gz = gPz;
   gL = gDx; gM = gDy; gN = gDz;
+  if (fl != 0) {
+    R lx = x, ly = y, lz = z, lL = L, lM = M, lN = N;
+    frame_localize_adjoint(f, fl, lx, ly, lz, lL, lM, lN, gx, gy, gz, gL, gM, gN, gF);
+  } else {  // P = entry - T
+    gF[0] -= gPx; gF[1] -= gPy; gF[2] -= gPz;
+  }
 }
 
 
@@ -298,8 +419,8 @@ __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int 
 // the accumulators. Called by the whole CTA after a __syncthreads().
 template <typename R>
 __device__ __forceinline__ void bwd_flush(R* s_acc, const int32_t* s_ops, int S, int W, R* gpresc) {
-  for (int q = threadIdx.x; q < S * OLRT_BWD_SLOTS; q += blockDim.x) {
-    const int s = q / OLRT_BWD_SLOTS, j = q - s * OLRT_BWD_SLOTS;
+  for (int q = threadIdx.x; q < S * OLRT_BWG_SLOTS; q += blockDim.x) {
+    const int s = q / OLRT_BWG_SLOTS, j = q - s * OLRT_BWG_SLOTS;
     R* a = s_acc + (size_t)q * 32;
     R v = R(0);
     for (int l = 0; l < 32; ++l) { v += a[(l + threadIdx.x) & 31]; }   // rotated start: no bank conflicts
@@ -309,9 +430,9 @@ __device__ __forceinline__ void bwd_flush(R* s_acc, const int32_t* s_ops, int S,
     const int doff = op[OLRT_OP_DOFF];
     const int goff = doff + op[OLRT_OP_NFRAMES] * OLRT_FRAME_REALS;
     int off;
-    if (j < 3) off = doff + j;
-    else if (j < 5) off = goff + (j - 3);
-    else off = goff + OLRT_GEOM_REALS + 3 * W + (j - 5);
+    if (j < OLRT_FRAME_REALS) off = doff + j;                                  // x y z cz sz cy sy cx sx
+    else if (j < OLRT_FRAME_REALS + 2) off = goff + (j - OLRT_FRAME_REALS);    // radius, conic
+    else off = goff + OLRT_GEOM_REALS + 3 * W + (j - OLRT_FRAME_REALS - 2);    // coefficients
     atomicAdd(gpresc + off, v);
   }
 }
@@ -319,9 +440,14 @@ __device__ __forceinline__ void bwd_flush(R* s_acc, const int32_t* s_ops, int S,
 template <typename R>
 __device__ __forceinline__ bool bwd_supported(const int32_t* s_ops, int s) {
   const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
-  const int k = surface_kind(op);
-  if (k == KIND_GENERIC) return false;
-  if (op[OLRT_OP_GEOM] == OLRT_GEOM_EVEN_ASPHERE && op[OLRT_OP_NCOEF] > OLRT_BWD_MAXC) return false;
+  const int geom = op[OLRT_OP_GEOM], flags = op[OLRT_OP_FLAGS];
+  if (op[OLRT_OP_NFRAMES] != 1) return false;                                 // one frame, tilted or not
+  if (flags & (OLRT_F_COATING | OLRT_F_THIN_LENS | OLRT_F_RENORM)) return false;
+  if (geom != OLRT_GEOM_PLANE) {
+    if (geom != OLRT_GEOM_STANDARD && geom != OLRT_GEOM_EVEN_ASPHERE && geom != OLRT_GEOM_POLYNOMIAL) return false;
+    if (flags & OLRT_F_RADIUS_INF) return false;
+    if (geom != OLRT_GEOM_STANDARD && op[OLRT_OP_NCOEF] > OLRT_BWG_MAXC) return false;
+  }
   return op[OLRT_OP_RECORD] == s;
 }
 
@@ -339,12 +465,12 @@ __global__ void __launch_bounds__(256, 2) trace_bwd_kernel(const BwdParams<R> P,
   R* s_acc = s_der + der_pad;
   // entry states (checkpoints) of the next surface, staged by cp.async while the current one is differentiated:
   // s_ck[(buf * 7 + q) * blockDim + tid]
-  R* s_ck = s_acc + (size_t)S * OLRT_BWD_SLOTS * 32;
+  R* s_ck = s_acc + (size_t)S * OLRT_BWG_SLOTS * 32;
   int32_t* s_ops = reinterpret_cast<int32_t*>(s_ck + 2 * 7 * blockDim.x);
   __shared__ int s_bad;
 
   for (int q = threadIdx.x; q < P.ops_len; q += blockDim.x) s_ops[q] = P.ops[q];
-  for (int q = threadIdx.x; q < S * OLRT_BWD_SLOTS * 32; q += blockDim.x) s_acc[q] = R(0);
+  for (int q = threadIdx.x; q < S * OLRT_BWG_SLOTS * 32; q += blockDim.x) s_acc[q] = R(0);
   if (threadIdx.x == 0) s_bad = 0;
   __syncthreads();
   if (threadIdx.x < S && !bwd_supported<R>(s_ops, threadIdx.x)) s_bad = 1;
@@ -411,21 +537,26 @@ __global__ void __launch_bounds__(256, 2) trace_bwd_kernel(const BwdParams<R> P,
               eM = ck[4 * blockDim.x], eN = ck[5 * blockDim.x], ei = ck[6 * blockDim.x];
       SurfParams<R> sp;
       load_surface<R, false>(sp, s_ops, s_presc, s_der, s, W, widx);
-      R gTx = R(0), gTy = R(0), gTz = R(0), gR = R(0), gk = R(0);
-      R gC[OLRT_BWD_MAXC];
+      R gR = R(0), gk = R(0);
+      R gF[OLRT_FRAME_REALS];
+      R gC[OLRT_BWG_MAXC];
 #pragma unroll
-      for (int i = 0; i < OLRT_BWD_MAXC; ++i) gC[i] = R(0);
-      bwd_surface<R>(sp, W, widx, ex, ey, ez, eL, eM, eN, ei, gx, gy, gz, gL, gM, gN, gi, gopd, gTx, gTy, gTz,
-                     gR, gk, gC);
+      for (int i = 0; i < OLRT_FRAME_REALS; ++i) gF[i] = R(0);
+#pragma unroll
+      for (int i = 0; i < OLRT_BWG_MAXC; ++i) gC[i] = R(0);
+      bwd_surface<R>(sp, W, widx, ex, ey, ez, eL, eM, eN, ei, gx, gy, gz, gL, gM, gN, gi, gopd, gF, gR, gk, gC);
       if (valid) {  // parameter partials: one lane-private shared atomic each
-        R* acc = s_acc + (size_t)s * OLRT_BWD_SLOTS * 32 + lane;
-        atomicAdd(acc + 0 * 32, gTx); atomicAdd(acc + 1 * 32, gTy); atomicAdd(acc + 2 * 32, gTz);
-        if (sp.geom != OLRT_GEOM_PLANE) {
-          atomicAdd(acc + 3 * 32, gR); atomicAdd(acc + 4 * 32, gk);
-          if (sp.geom == OLRT_GEOM_EVEN_ASPHERE) {
+        R* acc = s_acc + (size_t)s * OLRT_BWG_SLOTS * 32 + lane;
+        atomicAdd(acc + 0 * 32, gF[0]); atomicAdd(acc + 1 * 32, gF[1]); atomicAdd(acc + 2 * 32, gF[2]);
+        if (sp.op[OLRT_OP_FRAMEFLAGS] & 7) {
 #pragma unroll
-            for (int i = 0; i < OLRT_BWD_MAXC; ++i)
-              if (i < sp.ncoef) atomicAdd(acc + (5 + i) * 32, gC[i]);
+          for (int i = 3; i < OLRT_FRAME_REALS; ++i) atomicAdd(acc + i * 32, gF[i]);
+        }
+        if (sp.geom != OLRT_GEOM_PLANE) {
+          atomicAdd(acc + OLRT_FRAME_REALS * 32, gR); atomicAdd(acc + (OLRT_FRAME_REALS + 1) * 32, gk);
+          if (sp.geom != OLRT_GEOM_STANDARD) {
+            for (int i = 0; i < OLRT_BWG_MAXC; ++i)
+              if (i < sp.ncoef) atomicAdd(acc + (OLRT_FRAME_REALS + 2 + i) * 32, gC[i]);
           }
         }
       }
@@ -466,7 +597,7 @@ int launch_bwd(const olrt_sys* sys, const R* presc, const int32_t* ops, long lon
   const size_t pp = (size_t)((sys->presc_stride + 1) & ~1);
   const size_t smem = pp * sizeof(R) +
                       (size_t)((sys->n_surfaces * der_stride(sys->n_wavelengths) + 1) & ~1) * sizeof(R) +
-                      (size_t)sys->n_surfaces * OLRT_BWD_SLOTS * 32 * sizeof(R) + (size_t)2 * 7 * block * sizeof(R) +
+                      (size_t)sys->n_surfaces * OLRT_BWG_SLOTS * 32 * sizeof(R) + (size_t)2 * 7 * block * sizeof(R) +
                       (size_t)((sys->ops_len + 1) & ~1) * sizeof(int32_t);
   if (smem > 200 * 1024) return OLRT_E_LIMIT;
   if (smem > 48 * 1024)

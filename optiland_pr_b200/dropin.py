@@ -70,17 +70,17 @@ def _undifferentiated_variable(surfaces):
         g = getattr(s, "geometry", None)
         if g is None:
             continue
-        cs = g.cs
+        cs = getattr(g.cs, "reference_cs", None)     # tilts of the surface's own frame are differentiated (trace_bwd.cuh)
         while cs is not None:
-            for nm in ("rx", "ry", "rz"):
+            for nm in ("rx", "ry", "rz", "x", "y", "z"):
                 if _depends_on_variable(getattr(cs, nm, None)):
-                    return f"surface {k}: tilt {nm}"
+                    return f"surface {k}: {nm} of a parent frame"
             cs = getattr(cs, "reference_cs", None)
         for nm in ("norm_radius", "norm_x", "norm_y", "Rx", "Ry", "kx", "ky", "R_rot", "R_yz", "k_yz"):
             if _depends_on_variable(getattr(g, nm, None)):
                 return f"surface {k}: {nm}"
         gname = type(g).__name__
-        if gname not in ("EvenAsphere", "Plane", "StandardGeometry"):
+        if gname not in ("EvenAsphere", "Plane", "StandardGeometry", "PolynomialGeometry"):
             co = getattr(g, "coefficients", None)
             if co is None and getattr(g, "zernike", None) is not None:
                 co = g.zernike.coeffs
@@ -115,7 +115,7 @@ def _wants_grad(be, rays, surfaces) -> bool:
         g = getattr(s, "geometry", None)
         if g is None:
             continue
-        vals = [g.cs.x, g.cs.y, g.cs.z, getattr(g, "radius", None), getattr(g, "k", None)]
+        vals = [g.cs.x, g.cs.y, g.cs.z, g.cs.rx, g.cs.ry, g.cs.rz, getattr(g, "radius", None), getattr(g, "k", None)]
         co = getattr(g, "coefficients", None)
         if isinstance(co, torch.Tensor):
             vals.append(co)

@@ -182,25 +182,35 @@ class PackedSystem:
 
     def differentiable(self, require_records: bool = True) -> bool:
         """True when the backward kernels cover every surface (csrc/trace_bwd.cuh: bwd_supported): plane / finite
-        conic / even asphere with <= 8 coefficients on one untilted frame, any aperture program, no coating or
-        thin-lens flag, every surface recorded. The kernels re-check it (OLRT_ST_BAD_HINT)."""
+        conic / even asphere / x^i y^j polynomial (<= 16 coefficients) on ONE frame (decentred, tilted or both), any
+        aperture program, no coating or thin-lens flag, every surface recorded. The kernels re-check it
+        (OLRT_ST_BAD_HINT)."""
         if require_records and self.record_surfaces != [lay.index for lay in self.layouts]:
             return False
         for k in range(self.n_surfaces):
             row = k * L.OPS_STRIDE
             op = self.ops[row:row + L.OPS_STRIDE]
             geom, flags = int(op[L.OP_GEOM]), int(op[L.OP_FLAGS])
-            if op[L.OP_NFRAMES] != 1 or op[L.OP_FRAMEFLAGS] != 0:
+            if op[L.OP_NFRAMES] != 1:
                 return False
             if flags & (L.F_COATING | L.F_THIN_LENS | L.F_RENORM):
                 return False
             if geom == L.GEOM_PLANE:
                 continue
-            if geom not in (L.GEOM_STANDARD, L.GEOM_EVEN_ASPHERE) or flags & L.F_RADIUS_INF:
+            if geom not in (L.GEOM_STANDARD, L.GEOM_EVEN_ASPHERE, L.GEOM_POLYNOMIAL) or flags & L.F_RADIUS_INF:
                 return False
-            if geom == L.GEOM_EVEN_ASPHERE and int(op[L.OP_NCOEF]) > 8:
+            if geom != L.GEOM_STANDARD and int(op[L.OP_NCOEF]) > L.BWG_MAXC:
                 return False
         return True
+
+    def reduced_adjoint(self) -> bool:
+        """True when the reduced-algebra adjoint (csrc/trace_bx.cuh) covers the lens: the fast kinds with <= 8
+        even-asphere coefficients per surface. Other differentiable lenses take the general kernel."""
+        if not self.fastkinds():
+            return False
+        return all(int(self.ops[k * L.OPS_STRIDE + L.OP_NCOEF]) <= L.BX_MAXC
+                   for k in range(self.n_surfaces)
+                   if int(self.ops[k * L.OPS_STRIDE + L.OP_GEOM]) == L.GEOM_EVEN_ASPHERE)
 
     def ordinary(self) -> bool:
         """fastkinds() and every surface centred (frame x = y = +0.0), refracting, without an aperture

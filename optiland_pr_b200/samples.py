@@ -107,6 +107,20 @@ class AsphericSinglet(Optic):
         self.set_paraxial(EPL=0.0, EPD=20.0)
 
 
+class TiltedSinglet(AsphericSinglet):
+    """The aspheric singlet with both surfaces decentred and tilted (oracle/make_golden_grads.py: ref_tilted_singlet):
+    refraction through tilted frames, the tilt variables of optimization/variable/tilt.py."""
+
+    def __init__(self):
+        super().__init__()
+        s1, s2 = self.surface_group.surfaces[1], self.surface_group.surfaces[2]
+        s1.geometry.cs.rx, s1.geometry.cs.ry, s1.geometry.cs.rz = 0.03, -0.02, 0.4
+        s1.geometry.cs.x, s1.geometry.cs.y = 0.15, -0.1
+        s2.geometry.cs.rx, s2.geometry.cs.ry = -0.025, 0.015
+        s2.geometry.cs.y = 0.2
+        self.surface_group.invalidate()
+
+
 # ---- builders shared with oracle/make_golden.py: the SAME calls build the lens on the reference's Optic and
 # ---- on this package's Optic (`lens` is either; `ap` is the module holding the aperture classes)
 TMA_COEFFS = (

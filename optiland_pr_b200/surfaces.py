@@ -267,9 +267,13 @@ class SurfaceGroup:
             return True
         for s in self._surfaces:
             g = s.geometry
-            vals = [g.cs.x, g.cs.y, g.cs.z, getattr(g, "radius", None), getattr(g, "k", None)]
-            for c in (getattr(g, "coefficients", None) or []):
-                vals += list(c) if isinstance(c, (list, tuple)) else [c]
+            vals = [g.cs.x, g.cs.y, g.cs.z, g.cs.rx, g.cs.ry, g.cs.rz, getattr(g, "radius", None), getattr(g, "k", None)]
+            co = getattr(g, "coefficients", None)
+            if isinstance(co, torch.Tensor):
+                vals.append(co)
+            else:
+                for c in (co if co is not None else []):
+                    vals += list(c) if isinstance(c, (list, tuple)) else [c]
             if any(isinstance(v, torch.Tensor) and v.requires_grad for v in vals):
                 return True
         return False
@@ -323,7 +327,7 @@ class SurfaceGroup:
                 pk = repack("none")
                 # (a lens whose last trace needed more Newton updates than the reduced-algebra adjoint unrolls goes
                 # straight to the record path instead of tracing twice)
-                if pk.fastkinds() and max(pk.nr_iters(), default=0) <= 3:
+                if pk.reduced_adjoint() and max(pk.nr_iters(), default=0) <= 3:
                     presc_t = prescription_tensor(pk, self._surfaces, ins[0].dtype, ins[0].device)
                     try:
                         out, record, dir0 = trace_differentiable(pk, presc_t, ins, opd_in=rays.opd, fast=True,

@@ -3,14 +3,16 @@
     python oracle/make_golden_grads.py        # needs /root/reference (build container only)
 
 For each lens: the reference is switched to its torch backend (cpu, float64, grad enabled), every
-differentiable prescription entry of the hot path (geometry.radius, geometry.k, even-asphere
-coefficients, cs.x / cs.y / cs.z of every surface) and every input-ray component is made a leaf
+differentiable prescription entry of the hot path (geometry.radius, geometry.k, even-asphere and
+polynomial coefficients, cs.x / cs.y / cs.z and the non-zero tilt angles cs.rx / ry / rz of every
+surface) and every input-ray component is made a leaf
 tensor, `surface_group.trace(rays)` runs, and the scalar
         loss = sum_s sum_q sum_rays  w[s, q, ray] * record[s, q, ray]       (w: fixed random weights)
 is back-propagated. Stored: rays_in, w, the loss, d loss / d rays_in ([7, N]: x y z L M N i) and
 d loss / d presc in the packed layout of optiland_pr_b200/prescription.py (zeros where the reference
-has no differentiable leaf: media, tol, trigonometric frame entries). The -m gpu tests feed the same
-rays and w to the CUDA backward kernel and compare at 1e-8 (BASELINE.json north_star).
+has no differentiable leaf: media, tol) and `gangle` [S, 3] = d loss / d (rz, ry, rx) of every surface's
+frame -- the kernel returns d loss / d cos and d sin of each angle, the test chains them. The -m gpu
+tests feed the same rays and w to the CUDA backward kernel and compare at 1e-8 (BASELINE.json north_star).
 """
 from __future__ import annotations
 
@@ -53,6 +55,11 @@ def leafify(lens):
             t = mk(getattr(cs, nm))
             setattr(cs, nm, t)
             leaves.append((k, "frame_" + nm, 0, t))
+        for q, nm in enumerate(("rz", "ry", "rx")):      # tilts (optimization/variable/tilt.py:59): truthy angles only,
+            if float(getattr(cs, nm)) != 0.0:            # the reference skips a rotation whose angle is falsy
+                t = mk(getattr(cs, nm))
+                setattr(cs, nm, t)
+                leaves.append((k, "angle", q, t))
         if type(g).__name__ == "Plane":
             continue
         if np.isfinite(float(g.radius)):
@@ -65,6 +72,10 @@ def leafify(lens):
             g.coefficients = cs_
             for i, c in enumerate(cs_):
                 leaves.append((k, "coef", i, c))
+        if type(g).__name__ == "PolynomialGeometry":     # C[i][j], optimization/variable/polynomial_coeff.py:72
+            c2 = torch.tensor(np.asarray(be.to_numpy(g.coefficients), dtype=np.float64), requires_grad=True)
+            g.coefficients = c2
+            leaves.append((k, "coef2d", 0, c2))
     return leaves
 
 
@@ -105,8 +116,19 @@ def run_case(name, make_lens, wavelengths, n_pupil, seed):
     gin = np.stack([comps[q].grad.numpy() if comps[q].grad is not None else np.zeros(n) for q in range(7)])
     gpresc = np.zeros(packed.stride)
     have = np.zeros(packed.stride, dtype=bool)
+    gangle = np.zeros((S, 3))
+    have_angle = np.zeros((S, 3), dtype=bool)
     for (k, nm, i, t) in leaves:
         lay = packed.layouts[k]
+        if nm == "angle":
+            gangle[k, i] = 0.0 if t.grad is None else float(t.grad)
+            have_angle[k, i] = True
+            continue
+        if nm == "coef2d":
+            g2 = np.zeros(tuple(t.shape)) if t.grad is None else t.grad.numpy()
+            gpresc[lay.coef:lay.coef + g2.size] = g2.reshape(-1)
+            have[lay.coef:lay.coef + g2.size] = True
+            continue
         off = {"frame_x": lay.frames, "frame_y": lay.frames + 1, "frame_z": lay.frames + 2,
                "radius": lay.radius, "conic": lay.conic, "coef": lay.coef + i}[nm]
         gpresc[off] = 0.0 if t.grad is None else float(t.grad)
@@ -114,6 +136,7 @@ def run_case(name, make_lens, wavelengths, n_pupil, seed):
     be.grad_mode.disable()
     be.set_backend("numpy")
     out = dict(rays_in=rays_in, weights=w8, loss=float(loss.detach()), gin=gin, gpresc=gpresc, have=have,
+               gangle=gangle, have_angle=have_angle,
                wavelengths=np.asarray(wavelengths, dtype=np.float64), ops=packed.ops, presc=packed.presc)
     path = os.path.join(GOLDEN, name + "_grads.npz")
     np.savez_compressed(path, **out)
@@ -121,7 +144,36 @@ def run_case(name, make_lens, wavelengths, n_pupil, seed):
           f"nan_gin={int(np.isnan(gin).sum())} -> {os.path.getsize(path) / 1024:.0f} KiB")
 
 
+def ref_three_mirror():
+    """BASELINE config C3: off-axis three-mirror anastigmat, 4 x 4 polynomial freeform mirrors, rx tilts, dy decenters."""
+    from optiland import optic as ref_optic
+    from optiland_pr_b200 import samples as my_samples
+    to_arr = (lambda a: np.array(a)) if be.get_backend() == "numpy" else (lambda a: [list(r) for r in a])
+    return my_samples.build_three_mirror(ref_optic.Optic(name="TMA"), to_array=to_arr)
+
+
+def ref_tilted_singlet():
+    """An aspheric singlet whose two surfaces are decentred and tilted about all three axes (refraction through
+    tilted frames; the tilt variables of optimization/variable/tilt.py)."""
+    lens = AsphericSinglet()
+    s1, s2 = lens.surface_group.surfaces[1], lens.surface_group.surfaces[2]
+    s1.geometry.cs.rx, s1.geometry.cs.ry, s1.geometry.cs.rz = 0.03, -0.02, 0.4
+    s1.geometry.cs.x, s1.geometry.cs.y = 0.15, -0.1
+    s2.geometry.cs.rx, s2.geometry.cs.ry = -0.025, 0.015
+    s2.geometry.cs.y = 0.2
+    return lens
+
+
 def main():
+    only = sys.argv[1:]
+    if only:
+        cases = {"three_mirror": lambda: run_case("three_mirror", ref_three_mirror, [0.587], 48, 7),
+                 "tilted_singlet": lambda: run_case("tilted_singlet", ref_tilted_singlet, [0.587], 96, 8)}
+        for nm in only:
+            cases[nm]()
+        return
+    run_case("three_mirror", ref_three_mirror, [0.587], 48, 7)
+    run_case("tilted_singlet", ref_tilted_singlet, [0.587], 96, 8)
     run_case("cooke_triplet", CookeTriplet, [0.48, 0.55, 0.65], 24, 3)
     run_case("double_gauss", DoubleGauss, [0.5876], 64, 4)
     run_case("even_asphere_double_gauss", ref_even_asphere_double_gauss, [0.5876], 64, 5)
