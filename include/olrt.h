@@ -204,12 +204,16 @@ int olrt_trace_fwd_noalloc_f64(const olrt_sys* sys /*host*/, const double* presc
  *  grecord NULL or [n_surfaces][8][n_rays]: d loss / d recorded state (added to gout at the last surface)
  *  gin     [8] device ptrs: d loss / d in x y z L M N intensity opd_in (NULL entry = not wanted)
  *  gpresc  [n_presc][presc_stride] accumulated with atomicAdd (caller zero-initialises): filled for
- *          frame x y z, radius, conic and even-asphere coefficients; other entries stay zero
- *  status  NULL or one uint32: OLRT_ST_BAD_HINT when a surface is outside the differentiable set (plane /
- *          conic / even asphere with <= 8 coefficients on one untilted frame): nothing is written then
- *  flags   0: lenses with olrt_sys.kernel_hint & OLRT_HINT_FASTKINDS and <= 3 Newton updates per surface run the
- *          reduced-algebra adjoint kernel (csrc/trace_bx.cuh), every other differentiable lens the general one
- *          (csrc/trace_bwd.cuh); OLRT_BWD_GENERIC forces the general kernel                                  */
+ *          frame x y z, radius, conic, even-asphere / polynomial coefficients and -- general kernel, tilted frames --
+ *          the frame's cos rz, sin rz, cos ry, sin ry, cos rx, sin rx entries (the caller chains them to the angles:
+ *          d / d angle = -sin * g_cos + cos * g_sin, optimization/variable/tilt.py:59); other entries stay zero
+ *  status  NULL or one uint32: OLRT_ST_BAD_HINT when a surface is outside the differentiable set (plane / conic /
+ *          even asphere / x^i y^j polynomial with <= 16 coefficients on ONE frame, decentred and / or tilted; no
+ *          coating or thin-lens flag): nothing is written then
+ *  flags   0: lenses with olrt_sys.kernel_hint & OLRT_HINT_FASTKINDS, <= 3 Newton updates and <= 8 even-asphere
+ *          coefficients per surface run the reduced-algebra adjoint kernel (csrc/trace_bx.cuh), every other
+ *          differentiable lens (tilted frames, polynomial freeforms, more updates or coefficients: the caller passes
+ *          OLRT_BWD_GENERIC for the last two) the general one (csrc/trace_bwd.cuh); OLRT_BWD_GENERIC forces it   */
 #define OLRT_BWD_GENERIC 1
 /* Tile-blocked checkpoints (differentiable trace without user-visible records): with OLRT_FWD_CKPT_BLOCKED the
  * forward's `record` argument is a buffer of ceil(n_rays / 256) * n_surfaces * OLRT_CKPT_VALS * 256 reals laid out

@@ -78,6 +78,11 @@ def prefetch_tensor_scalars(surfaces) -> None:
         _TENSOR_VALUES[id(v)] = (v, x)
 
 
+def torch_float64():
+    import torch
+    return torch.float64
+
+
 def _f(v) -> float:
     """Scalar value of a python number / numpy 0-d or 1-element array / torch tensor."""
     if type(v) is float or type(v) is int:     # the common case: no NumPy round trip
@@ -404,7 +409,11 @@ def _pack_surface_group(surfaces, wavelengths, record, skip) -> PackedSystem:
             ncoef = len(cs_)
             reals += cs_
         elif geom == L.GEOM_POLYNOMIAL:
-            rows = [[_f(c) for c in r] for r in g.coefficients]
+            co2 = g.coefficients
+            if hasattr(co2, "detach"):          # a 2-D tensor (a live optimisation variable): one copy, not one per entry
+                rows = co2.detach().to("cpu", torch_float64()).tolist()
+            else:
+                rows = [[_f(c) for c in r] for r in co2]
             J = len(rows[0]) if rows else 0
             if any(len(r) != J for r in rows):
                 raise NotEligible("ragged polynomial coefficient table")

@@ -21,8 +21,9 @@ MIRRORS = {
     "anamorphic": samples.Anamorphic,
     "chebyshev_plate": samples.ChebyshevPlate,
     "coated_relay": samples.CoatedRelay,
-    "tilted_singlet": samples.TiltedSinglet,
 }
+# lenses with a gradient fixture only (tests/golden/<name>_grads.npz)
+GRAD_ONLY_MIRRORS = {"tilted_singlet": samples.TiltedSinglet}
 # lenses inside the backward kernel's differentiable set (gradient fixtures exist for these)
 GRAD_MIRRORS = ("cooke_triplet", "double_gauss", "even_asphere_double_gauss", "aspheric_singlet")
 # lenses of the general adjoint kernel only: tilted frames, x^i y^j polynomial freeforms (tilt and polynomial-coefficient
@@ -38,7 +39,7 @@ def load_golden(name):
 
 
 def mirror_packed(name, wavelengths, record="all"):
-    lens = MIRRORS[name]()
+    lens = (MIRRORS.get(name) or GRAD_ONLY_MIRRORS[name])()
     return lens, pack_surface_group(lens.surface_group.surfaces, list(wavelengths), record=record)
 
 

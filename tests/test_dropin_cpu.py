@@ -98,8 +98,12 @@ def test_variables_the_adjoint_does_not_differentiate_are_detected():
     assert dropin._undifferentiated_variable(surfaces) is None      # grad-mode leaves are not variables
     p = torch.nn.Parameter(torch.tensor(0.01, dtype=torch.float64))
     surfaces[2].geometry.cs.rx = p * 1.0
-    assert "tilt rx" in dropin._undifferentiated_variable(surfaces)
+    assert dropin._undifferentiated_variable(surfaces) is None      # tilts of a surface's own frame are differentiated
     surfaces[2].geometry.cs.rx = 0.0
+    from optiland.coordinate_system import CoordinateSystem
+    surfaces[2].geometry.cs.reference_cs = CoordinateSystem(rx=p * 1.0)
+    assert "rx of a parent frame" in dropin._undifferentiated_variable(surfaces)
+    surfaces[2].geometry.cs.reference_cs = None
     from optiland.materials import IdealMaterial
     mat = IdealMaterial(n=1.5)
     mat.index = (p * 0 + 1.5).reshape(1)

@@ -290,16 +290,93 @@ def test_torch_adam_on_the_fused_trace_matches_the_reference_autograd(name):
     assert abs(got["final"] - want["final"]) <= 1e-8 * abs(want["final"])
 
 
-def test_gradient_wanted_for_an_undifferentiated_quantity_uses_the_stock_graph():
-    """A tilt that depends on an optimisation variable: the adjoint kernels do not differentiate tilts, so the patched
-    method must hand the trace to the stock loop (autograd through the reference's own ops), not drop the gradient."""
-    _fused(grad=True)
+def _tilt_case(device):
     lens = rc.make_lens("cooke")
-    p = torch.nn.Parameter(torch.tensor(0.01, dtype=torch.float64, device="cuda"))
+    p = torch.nn.Parameter(torch.tensor(0.01, dtype=torch.float64, device=device))
     lens.surface_group.surfaces[3].geometry.cs.rx = p * 1.0
     rays = lens.trace(0.0, 1.0, 0.55, 6, "hexapolar")
     loss = (rays.y[torch.isfinite(rays.y)] ** 2).mean()
     loss.backward()
+    return float(loss), float(p.grad)
+
+
+def test_tilt_variable_goes_through_the_adjoint_kernel():
+    """A tilt that depends on an optimisation variable (optimization/variable/tilt.py:59): the general adjoint kernel
+    returns d loss / d cos, d sin of the frame's angles and autograd chains them to the angle. Against the reference's
+    own op-by-op graph on the same device (stock method), <= 1e-8."""
+    rc.use_torch("cuda", "float64", grad=True)
+    want = _tilt_case("cuda")
+    _fused(grad=True)
+    got = _tilt_case("cuda")
     st = dropin.stats()
-    assert st.get("stock:grad of tilt rx", 0) == 1 and "fused_grad" not in st, st
+    assert st.get("fused_grad", 0) == 1 and not any(k.startswith("stock:grad") for k in st), st
+    assert abs(got[0] - want[0]) <= 1e-10 * abs(want[0])
+    assert want[1] != 0.0 and abs(got[1] - want[1]) <= 1e-8 * abs(want[1]), (got, want)
+
+
+def _three_mirror_case(device):
+    """BASELINE C3's three-mirror system built on the reference's Optic; leaves: the rx tilt of every mirror, the dy
+    decenter of the second, the 4 x 4 polynomial coefficients, radius and conic of the first."""
+    from optiland import optic as ref_optic
+    from optiland_pr_b200 import samples as my_samples
+    lens = my_samples.build_three_mirror(ref_optic.Optic(name="TMA"), to_array=lambda a: [list(r) for r in a])
+    sf = lens.surface_group.surfaces
+    mk = lambda v: torch.tensor(float(v), dtype=torch.float64, device=device, requires_grad=True)
+    leaves = []
+    for k in (1, 2, 3):
+        t = mk(sf[k].geometry.cs.rx)
+        sf[k].geometry.cs.rx = t
+        leaves.append(t)
+    t = mk(sf[2].geometry.cs.y)
+    sf[2].geometry.cs.y = t
+    leaves.append(t)
+    c2 = torch.tensor(rc.to_np(sf[1].geometry.coefficients), dtype=torch.float64, device=device, requires_grad=True)
+    sf[1].geometry.coefficients = c2
+    leaves.append(c2)
+    for nm in ("radius", "k"):
+        t = mk(getattr(sf[1].geometry, nm))
+        setattr(sf[1].geometry, nm, t)
+        leaves.append(t)
+    loss = 0.0
+    for Hy in (0.0, 1.0, -1.0):
+        rays = lens.trace(0.0, Hy, 0.587, 8, "hexapolar")
+        loss = loss + ((rays.x - rays.x.mean()) ** 2 + (rays.y - rays.y.mean()) ** 2).mean()
+    loss.backward()
+    return float(loss), np.concatenate([t.grad.detach().cpu().numpy().reshape(-1) for t in leaves])
+
+
+def test_three_mirror_tilts_decenters_and_polynomial_coefficients_through_the_adjoint_kernel():
+    """tilt, decenter, radius, conic and polynomial-coefficient gradients of the off-axis three-mirror
+    freeform system (optimization/variable/tilt.py:59, decenter.py, polynomial_coeff.py:72) from the fused forward +
+    general adjoint kernel, against the reference's own torch graph on the same device: <= 1e-8 of the largest entry per
+    parameter kind."""
+    rc.use_torch("cuda", "float64", grad=True)
+    want = _three_mirror_case("cuda")
+    _fused(grad=True)
+    got = _three_mirror_case("cuda")
+    st = dropin.stats()
+    assert st.get("fused_grad", 0) == 3 and not any(k.startswith("stock:grad") for k in st), st
+    assert abs(got[0] - want[0]) <= 1e-10 * abs(want[0])
+    g, w = got[1], want[1]
+    assert np.isfinite(w).all() and (w != 0).sum() >= 20
+    for sl in (slice(0, 3), slice(3, 4), slice(4, 20), slice(20, 22)):      # tilts, decenter, coefficients, R and k
+        assert np.max(np.abs(g[sl] - w[sl])) <= 1e-8 * np.abs(w[sl]).max(), (sl, g[sl], w[sl])
+
+
+def test_gradient_wanted_for_an_undifferentiated_quantity_uses_the_stock_graph():
+    """Odd-asphere coefficients that depend on an optimisation variable: the adjoint kernels do not differentiate that
+    geometry, so the patched method must hand the trace to the stock loop (autograd through the reference's own ops),
+    not drop the gradient."""
+    from optiland.geometries import OddAsphere
+    _fused(grad=True)
+    lens = rc.make_lens("aspheric_singlet")
+    p = torch.nn.Parameter(torch.tensor(1.0e-4, dtype=torch.float64, device="cuda"))
+    s1 = lens.surface_group.surfaces[1]
+    g0 = s1.geometry
+    s1.geometry = OddAsphere(g0.cs, g0.radius, g0.k, coefficients=[0.0, p * 1.0, -2.0e-5])
+    rays = lens.trace(0.0, 0.0, 0.587, 32, "random")      # (no ray through r = 0: the reference's own d r / d x is NaN there)
+    loss = (rays.y[torch.isfinite(rays.y)] ** 2).mean()
+    loss.backward()
+    st = dropin.stats()
+    assert st.get("stock:grad of OddAsphere coefficients", 0) == 1 and "fused_grad" not in st, st
     assert p.grad is not None and np.isfinite(float(p.grad)) and float(p.grad) != 0.0

@@ -9,15 +9,18 @@ from optiland_pr_b200 import samples
 from optiland_pr_b200.prescription import _f, pack_surface_group
 
 
-@pytest.mark.parametrize("name,want", [("CookeTriplet", True), ("DoubleGauss", True), ("EvenAsphereDoubleGauss", True),
-                                       ("AsphericSinglet", True), ("ThreeMirrorAnastigmat", False),
-                                       ("CoatedRelay", False), ("Anamorphic", False)])
-def test_differentiable_set(name, want):
+@pytest.mark.parametrize("name,want,reduced", [
+    ("CookeTriplet", True, True), ("DoubleGauss", True, True), ("EvenAsphereDoubleGauss", True, True),
+    ("AsphericSinglet", True, True),
+    ("ThreeMirrorAnastigmat", True, False), ("TiltedSinglet", True, False),   # general adjoint kernel only
+    ("FreeformPlate", False, False), ("CoatedRelay", False, False), ("Anamorphic", False, False)])
+def test_differentiable_set(name, want, reduced):
     lens = getattr(samples, name)()
     wl = [float(lens.wavelengths[lens.primary_index])]
     pk = pack_surface_group(lens.surface_group.surfaces, wl, record="all")
     assert pk.differentiable() is want
-    if want:
+    assert pk.reduced_adjoint() is reduced
+    if reduced:
         assert pk.fastkinds() and pk.make_sys().kernel_hint & L.HINT_FASTKINDS
         # every surface must be recorded: the records are the checkpoints
         assert not pack_surface_group(lens.surface_group.surfaces, wl, record="last").differentiable()
