@@ -208,8 +208,9 @@ int olrt_trace_fwd_noalloc_f64(const olrt_sys* sys /*host*/, const double* presc
  *          the frame's cos rz, sin rz, cos ry, sin ry, cos rx, sin rx entries (the caller chains them to the angles:
  *          d / d angle = -sin * g_cos + cos * g_sin, optimization/variable/tilt.py:59); other entries stay zero
  *  status  NULL or one uint32: OLRT_ST_BAD_HINT when a surface is outside the differentiable set (plane / conic /
- *          even asphere / x^i y^j polynomial with <= 16 coefficients on ONE frame, decentred and / or tilted; no
- *          coating or thin-lens flag): nothing is written then
+ *          even or odd asphere / x^i y^j polynomial / Zernike surface on ONE frame, decentred and / or tilted; at most
+ *          32 coefficient gradient slots per surface -- a Zernike term takes two, for its c and c N entries -- announced
+ *          in bits 8-15 of olrt_sys.kernel_hint when more than 16; no coating or thin-lens flag): nothing is written then
  *  flags   0: lenses with olrt_sys.kernel_hint & OLRT_HINT_FASTKINDS, <= 3 Newton updates and <= 8 even-asphere
  *          coefficients per surface run the reduced-algebra adjoint kernel (csrc/trace_bx.cuh), every other
  *          differentiable lens (tilted frames, polynomial freeforms, more updates or coefficients: the caller passes

@@ -44,7 +44,8 @@ CKPT_VALS = 6            # x y z L M copysign(intensity, N) per ray and surface 
 BWD_GENERIC = 1          # olrt_trace_bwd_* flag: force the general adjoint kernel (csrc/trace_bwd.cuh)
 BX_MAXK = 3              # Newton updates per surface the reduced-algebra adjoint kernel (csrc/trace_bx.cuh) unrolls
 BX_MAXC = 8              # even-asphere coefficients per surface in the reduced adjoint (OLRT_BWD_MAXC)
-BWG_MAXC = 16            # even-asphere / polynomial coefficients per surface in the general adjoint (OLRT_BWG_MAXC)
+BWG_MAXC = 32            # coefficient gradient slots per surface in the general adjoint (OLRT_BWG_MAXC)
+BWG_MAXM = 12            # largest |m| of a Zernike term there (OLRT_BWG_MAXM)
 FWD_FAST = 1
 FWD_REPLAY = 2
 SPOT_VALID_ONLY = 1

@@ -50,6 +50,13 @@ def _live_entries(packed: PackedSystem, surfaces):
                     c = co[i][j]
                     if isinstance(c, torch.Tensor):
                         out.append((lay.coef + i * len(co[i]) + j, c))
+        if lay.geom == L.GEOM_ZERNIKE:         # per term the row holds c and c N (optimization/variable/zernike_coeff.py:71)
+            co = g.zernike.coeffs
+            for j, (_, _, off, norm) in enumerate(lay.zernike_terms):
+                c = co[j]
+                if isinstance(c, torch.Tensor):
+                    out.append((off, c))
+                    out.append((off + 1, c * norm))
         # tilts (optimization/variable/tilt.py:59): the row holds cos / sin of rz, ry, rx of the surface's one frame
         if getattr(cs, "reference_cs", None) is None:
             for q, nm in enumerate(("rz", "ry", "rx")):
@@ -138,8 +145,8 @@ class FusedTraceFn(torch.autograd.Function):
         lib = L.load()
         if not packed.differentiable(require_records=not ctx.blocked):
             raise NotImplementedError(
-                "olrt_trace_bwd: gradients are implemented for plane / conic / even-asphere / x^i y^j polynomial "
-                "surfaces (<= 16 coefficients) on one (decentred, tilted) frame; this lens has a surface outside "
+                "olrt_trace_bwd: gradients are implemented for plane / conic / even- or odd-asphere / x^i y^j "
+                "polynomial / Zernike surfaces on one (decentred, tilted) frame; this lens has a surface outside "
                 "that set")
         packed.set_nr_iters(ctx.nr_iters)
         ops_d, _ = _device_tables(packed, dtype, device)

@@ -15,7 +15,7 @@
 // second derivatives of the sag), NOT replaced by the implicit-function gradient of the converged
 // root -- the two differ by O(residual), more than the 1e-8 gradient bar when tol = 1e-6.
 //
-// Differentiable here: plane, sphere / conic, even asphere and POLYNOMIAL (x^i y^j freeform, polynomial.py:93-142)
+// Differentiable here: plane, sphere / conic, even asphere, odd asphere, POLYNOMIAL (x^i y^j, polynomial.py:93-142) and ZERNIKE
 // surfaces on ONE frame that may be decentred AND tilted (coordinate_system.py:73-107: rz, ry, rx), with any
 // aperture program, absorption, refraction and reflection; gradients w.r.t. the frame's x y z and the cosines /
 // sines of its three angles (the caller chains d cos / d angle: optimization/variable/tilt.py:59), radius, conic,
@@ -28,8 +28,9 @@ namespace OLRT_NS {
 
 #define OLRT_BWD_MAXC 8  // even-asphere coefficients with a gradient slot in registers (reduced kernel, trace_bx.cuh)
 #define OLRT_BWD_SLOTS (5 + OLRT_BWD_MAXC)  // frame x y z, radius, conic, coefficients (reduced kernel)
-#define OLRT_BWG_MAXC 16                    // this kernel: even-asphere / polynomial coefficients with a gradient slot
-#define OLRT_BWG_SLOTS (OLRT_FRAME_REALS + 2 + OLRT_BWG_MAXC)  // frame x y z cz sz cy sy cx sx, radius, conic, coefficients
+#define OLRT_BWG_MAXC 32   // this kernel: coefficient gradient slots per surface (a Zernike term takes two: c and c N)
+#define OLRT_BWG_DEFC 16   // ... of them in shared memory unless olrt_sys.kernel_hint asks for more (bits 8-15)
+#define OLRT_BWG_MAXM 12   // largest |m| of a Zernike term
 
 template <typename R>
 struct BwdParams {
@@ -44,6 +45,7 @@ struct BwdParams {
   long long n_rays;
   long long rays_per_presc;
   int n_surfaces, n_wavelengths, n_presc, presc_stride, ops_len;
+  int cslots;  // general kernel: coefficient gradient slots per surface in shared memory (<= OLRT_BWG_MAXC)
   R wavelengths[OLRT_MAX_WAVELENGTHS];
   R four_pi;
 };
@@ -71,14 +73,55 @@ struct BwdConst {
 template <typename R>
 struct SagEval {
   R r2, s, is, i1s, S, G, Gp;  // radial part: zx = x G, zy = y G; is = 1/s, i1s = 1/(1+s)
-  R Px, Py, Pxx, Pxy, Pyy;     // non-radial part (polynomial x^i y^j terms): zx = x G + Px, zxx = G + 2 x^2 Gp + Pxx ...
+  R Px, Py, Pxx, Pxy, Pyy;     // non-radial part of the SLOPES the reference codes: zx = x G + Px, zxx = G + 2 x^2 Gp + Pxx
+  R dSx, dSy;                  // non-radial part of the true d S / d x, d y (= Px, Py except for Zernike terms, whose
+                               // coded slopes leave the normalisation constant out, zernike.py:222-224 vs base.py:63-68)
 };
+
+// One Zernike term in Cartesian form: rho^|m| cos / sin(|m| phi) = Re / Im (xn + i yn)^|m| and R_n^m(rho) =
+// rho^|m| Q(rho^2) (n - |m| is even), so Z = Q(u) H(xn, yn) with u = xn^2 + yn^2 is a polynomial in the normalised
+// coordinates: value, first and second partials w.r.t. (xn, yn). rc: radial coefficients, highest power first;
+// re / im: the powers (xn + i yn)^k.
+template <typename R>
+struct ZTerm { R T, Tx, Ty, Txx, Txy, Tyy; };
+
+template <typename R>
+__device__ __forceinline__ void zernike_term(int n, int m, const R* rc, R xn, R yn, R u, const R* re, const R* im,
+                                             ZTerm<R>& z) {
+  const int ma = (m < 0) ? -m : m;
+  const int smax = ((n - ma) >> 1) + 1;
+  R Q = R(0), Q1 = R(0), Q2 = R(0);  // Q, Q', Q'' by Horner in u
+  for (int k = 0; k < smax; ++k) { Q2 = Q2 * u + R(2) * Q1; Q1 = Q1 * u + Q; Q = Q * u + rc[k]; }
+  R H = R(1), Hx = R(0), Hy = R(0), Hxx = R(0), Hxy = R(0), Hyy = R(0);
+  if (ma > 0) {
+    const R fm = R(ma), fmm = R(ma * (ma - 1));
+    const R r1 = re[ma - 1], i1 = im[ma - 1];
+    const R r2 = (ma >= 2) ? re[ma - 2] : R(0), i2 = (ma >= 2) ? im[ma - 2] : R(0);
+    if (m > 0) { H = re[ma]; Hx = fm * r1; Hy = -fm * i1; Hxx = fmm * r2; Hxy = -fmm * i2; Hyy = -fmm * r2; }
+    else { H = im[ma]; Hx = fm * i1; Hy = fm * r1; Hxx = fmm * i2; Hxy = fmm * r2; Hyy = -fmm * i2; }
+  }
+  z.T = Q * H;
+  z.Tx = R(2) * xn * Q1 * H + Q * Hx;
+  z.Ty = R(2) * yn * Q1 * H + Q * Hy;
+  z.Txx = R(4) * xn * xn * Q2 * H + R(2) * Q1 * H + R(4) * xn * Q1 * Hx + Q * Hxx;
+  z.Txy = R(4) * xn * yn * Q2 * H + R(2) * xn * Q1 * Hy + R(2) * yn * Q1 * Hx + Q * Hxy;
+  z.Tyy = R(4) * yn * yn * Q2 * H + R(2) * Q1 * H + R(4) * yn * Q1 * Hy + Q * Hyy;
+}
+
+template <typename R>
+__device__ __forceinline__ void zernike_powers(R xn, R yn, R* re, R* im) {
+  re[0] = R(1); im[0] = R(0);
+  for (int k = 1; k <= OLRT_BWG_MAXM; ++k) {
+    re[k] = re[k - 1] * xn - im[k - 1] * yn;
+    im[k] = re[k - 1] * yn + im[k - 1] * xn;
+  }
+}
 
 template <typename R>
 __device__ __forceinline__ void sag_eval(const SurfParams<R>& sp, const BwdConst<R>& bc, bool plane, R x, R y,
                                          SagEval<R>& e) {
   e.r2 = x * x + y * y;
-  e.Px = R(0); e.Py = R(0); e.Pxx = R(0); e.Pxy = R(0); e.Pyy = R(0);
+  e.Px = R(0); e.Py = R(0); e.Pxx = R(0); e.Pxy = R(0); e.Pyy = R(0); e.dSx = R(0); e.dSy = R(0);
   if (plane) { e.s = R(1); e.is = R(1); e.i1s = R(0.5); e.S = R(0); e.G = R(0); e.Gp = R(0); return; }
   const R c1 = sp.cc.c1;
   const R B = R(1) - c1 * e.r2 * bc.iR2;
@@ -116,6 +159,39 @@ __device__ __forceinline__ void sag_eval(const SurfParams<R>& sp, const BwdConst
       }
       xim2 = xim1; xim1 = xi; xi = xi * x;
     }
+    e.dSx = e.Px; e.dSy = e.Py;
+  } else if (sp.geom == OLRT_GEOM_ODD_ASPHERE) {  // sum C_i r^(i+1), odd_asphere.py:85-88, :112-121: radial in r
+    const R r = bsqrt(e.r2);
+    const R ir = (r > R(0)) ? brcp(r) : R(0);     // the reference zeroes the non-finite slope terms at r = 0
+    R pm3 = ir * ir * ir, pm1 = ir, pp1 = r;      // r^(i-3), r^(i-1), r^(i+1)
+    for (int i = 0; i < sp.ncoef; ++i) {
+      const R Ci = sp.coef[i];
+      e.S += Ci * pp1;
+      e.G += R(i + 1) * Ci * pm1;
+      e.Gp += R(0.5) * R((i + 1) * (i - 1)) * Ci * pm3;
+      pm3 = pm3 * r; pm1 = pm1 * r; pp1 = pp1 * r;
+    }
+  } else if (sp.geom == OLRT_GEOM_ZERNIKE) {      // zernike.py:133-224
+    const R inr = brcp(sp.norm_radius);
+    const R xn = x * inr, yn = y * inr, u = xn * xn + yn * yn;
+    R re[OLRT_BWG_MAXM + 1], im[OLRT_BWG_MAXM + 1];
+    zernike_powers(xn, yn, re, im);
+    const int32_t* nm = sp.ops + sp.aux;
+    const R* tc = sp.coef;
+    for (int j = 0; j < sp.ncoef; ++j) {
+      const int n = nm[2 * j], m = nm[2 * j + 1];
+      const int ma = (m < 0) ? -m : m;
+      const R c = tc[0], cN = tc[1];
+      ZTerm<R> zt;
+      zernike_term(n, m, tc + 2, xn, yn, u, re, im, zt);
+      tc += 2 + ((n - ma) >> 1) + 1;
+      e.S += cN * zt.T;
+      e.dSx += cN * zt.Tx * inr; e.dSy += cN * zt.Ty * inr;
+      if (c != R(0)) {                            // `if c == 0: continue`, zernike.py:218-219
+        e.Px += c * zt.Tx * inr; e.Py += c * zt.Ty * inr;
+        e.Pxx += c * zt.Txx * inr * inr; e.Pxy += c * zt.Txy * inr * inr; e.Pyy += c * zt.Tyy * inr * inr;
+      }
+    }
   }
 }
 
@@ -130,9 +206,9 @@ __device__ __forceinline__ void sag_adjoint(const SurfParams<R>& sp, const BwdCo
                                             R* gC) {
   if (plane) return;
   const R q = gzx * x + gzy * y;  // gradient w.r.t. G
-  const R zx = x * e.G + e.Px, zy = y * e.G + e.Py;
-  gx += gS * zx + gzx * (e.G + e.Pxx) + gzy * e.Pxy + q * e.Gp * (R(2) * x);
-  gy += gS * zy + gzy * (e.G + e.Pyy) + gzx * e.Pxy + q * e.Gp * (R(2) * y);
+  const R Sx = x * e.G + e.dSx, Sy = y * e.G + e.dSy;   // d S / d x, d y
+  gx += gS * Sx + gzx * (e.G + e.Pxx) + gzy * e.Pxy + q * e.Gp * (R(2) * x);
+  gy += gS * Sy + gzy * (e.G + e.Pyy) + gzx * e.Pxy + q * e.Gp * (R(2) * y);
   const R c1 = sp.cc.c1, r2 = e.r2;
   const R ds_dR = c1 * r2 * bc.iR3 * e.is;
   const R ds_dk = R(-0.5) * r2 * bc.iR2 * e.is;
@@ -162,6 +238,32 @@ __device__ __forceinline__ void sag_adjoint(const SurfParams<R>& sp, const BwdCo
         yjm1 = yj; yj = yj * y;
       }
       xim1 = xi; xi = xi * x;
+    }
+  } else if (sp.geom == OLRT_GEOM_ODD_ASPHERE) {
+    const R r = bsqrt(r2);
+    const R ir = (r > R(0)) ? brcp(r) : R(0);
+    R pm1 = ir, pp1 = r;
+    for (int i = 0; i < OLRT_BWG_MAXC; ++i) {
+      if (i < sp.ncoef) {
+        gC[i] += gS * pp1 + q * R(i + 1) * pm1;
+        pm1 = pm1 * r; pp1 = pp1 * r;
+      }
+    }
+  } else if (sp.geom == OLRT_GEOM_ZERNIKE) {  // slot 2 j: d / d c_j (through the coded slopes), 2 j + 1: d / d (c_j N_j) (sag)
+    const R inr = brcp(sp.norm_radius);
+    const R xn = x * inr, yn = y * inr, u = xn * xn + yn * yn;
+    R re[OLRT_BWG_MAXM + 1], im[OLRT_BWG_MAXM + 1];
+    zernike_powers(xn, yn, re, im);
+    const int32_t* nm = sp.ops + sp.aux;
+    const R* tc = sp.coef;
+    for (int j = 0; j < sp.ncoef && 2 * j + 1 < OLRT_BWG_MAXC; ++j) {
+      const int n = nm[2 * j], m = nm[2 * j + 1];
+      const int ma = (m < 0) ? -m : m;
+      ZTerm<R> zt;
+      zernike_term(n, m, tc + 2, xn, yn, u, re, im, zt);
+      if (tc[0] != R(0)) gC[2 * j] += (gzx * zt.Tx + gzy * zt.Ty) * inr;
+      gC[2 * j + 1] += gS * zt.T;
+      tc += 2 + ((n - ma) >> 1) + 1;
     }
   }
 }
@@ -418,9 +520,9 @@ __device__ __forceinline__ void bwd_surface(const SurfParams<R>& sp, int W, int 
 // sum the 32 lane-private partials of every (surface, slot) and add them to the prescription gradient; clears
 // the accumulators. Called by the whole CTA after a __syncthreads().
 template <typename R>
-__device__ __forceinline__ void bwd_flush(R* s_acc, const int32_t* s_ops, int S, int W, R* gpresc) {
-  for (int q = threadIdx.x; q < S * OLRT_BWG_SLOTS; q += blockDim.x) {
-    const int s = q / OLRT_BWG_SLOTS, j = q - s * OLRT_BWG_SLOTS;
+__device__ __forceinline__ void bwd_flush(R* s_acc, const int32_t* s_ops, int S, int W, int slots, R* gpresc) {
+  for (int q = threadIdx.x; q < S * slots; q += blockDim.x) {
+    const int s = q / slots, j = q - s * slots;
     R* a = s_acc + (size_t)q * 32;
     R v = R(0);
     for (int l = 0; l < 32; ++l) { v += a[(l + threadIdx.x) & 31]; }   // rotated start: no bank conflicts
@@ -432,21 +534,44 @@ __device__ __forceinline__ void bwd_flush(R* s_acc, const int32_t* s_ops, int S,
     int off;
     if (j < OLRT_FRAME_REALS) off = doff + j;                                  // x y z cz sz cy sy cx sx
     else if (j < OLRT_FRAME_REALS + 2) off = goff + (j - OLRT_FRAME_REALS);    // radius, conic
-    else off = goff + OLRT_GEOM_REALS + 3 * W + (j - OLRT_FRAME_REALS - 2);    // coefficients
+    else {                                                                     // coefficients
+      const int ci = j - OLRT_FRAME_REALS - 2;
+      off = goff + OLRT_GEOM_REALS + 3 * W;
+      if (op[OLRT_OP_GEOM] == OLRT_GEOM_ZERNIKE) {  // per term: c, c N, radial coefficients; slot 2 t -> c, 2 t + 1 -> c N
+        const int32_t* nm = s_ops + op[OLRT_OP_AUX];
+        for (int t = 0; t < (ci >> 1); ++t) {
+          const int n = nm[2 * t], m = nm[2 * t + 1];
+          off += 2 + ((n - (m < 0 ? -m : m)) >> 1) + 1;
+        }
+        off += ci & 1;
+      } else {
+        off += ci;
+      }
+    }
     atomicAdd(gpresc + off, v);
   }
 }
 
 template <typename R>
-__device__ __forceinline__ bool bwd_supported(const int32_t* s_ops, int s) {
+__device__ __forceinline__ bool bwd_supported(const int32_t* s_ops, int s, int cslots) {
   const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
   const int geom = op[OLRT_OP_GEOM], flags = op[OLRT_OP_FLAGS];
   if (op[OLRT_OP_NFRAMES] != 1) return false;                                 // one frame, tilted or not
   if (flags & (OLRT_F_COATING | OLRT_F_THIN_LENS | OLRT_F_RENORM)) return false;
   if (geom != OLRT_GEOM_PLANE) {
-    if (geom != OLRT_GEOM_STANDARD && geom != OLRT_GEOM_EVEN_ASPHERE && geom != OLRT_GEOM_POLYNOMIAL) return false;
+    if (geom != OLRT_GEOM_STANDARD && geom != OLRT_GEOM_EVEN_ASPHERE && geom != OLRT_GEOM_POLYNOMIAL &&
+        geom != OLRT_GEOM_ODD_ASPHERE && geom != OLRT_GEOM_ZERNIKE)
+      return false;
     if (flags & OLRT_F_RADIUS_INF) return false;
-    if (geom != OLRT_GEOM_STANDARD && op[OLRT_OP_NCOEF] > OLRT_BWG_MAXC) return false;
+    const int need = (geom == OLRT_GEOM_STANDARD) ? 0 : (geom == OLRT_GEOM_ZERNIKE ? 2 : 1) * op[OLRT_OP_NCOEF];
+    if (need > cslots) return false;
+    if (geom == OLRT_GEOM_ZERNIKE) {
+      const int32_t* nm = s_ops + op[OLRT_OP_AUX];
+      for (int t = 0; t < op[OLRT_OP_NCOEF]; ++t) {
+        const int m = nm[2 * t + 1];
+        if ((m < 0 ? -m : m) > OLRT_BWG_MAXM) return false;
+      }
+    }
   }
   return op[OLRT_OP_RECORD] == s;
 }
@@ -465,15 +590,16 @@ __global__ void __launch_bounds__(256, 2) trace_bwd_kernel(const BwdParams<R> P,
   R* s_acc = s_der + der_pad;
   // entry states (checkpoints) of the next surface, staged by cp.async while the current one is differentiated:
   // s_ck[(buf * 7 + q) * blockDim + tid]
-  R* s_ck = s_acc + (size_t)S * OLRT_BWG_SLOTS * 32;
+  const int slots = OLRT_FRAME_REALS + 2 + P.cslots;
+  R* s_ck = s_acc + (size_t)S * slots * 32;
   int32_t* s_ops = reinterpret_cast<int32_t*>(s_ck + 2 * 7 * blockDim.x);
   __shared__ int s_bad;
 
   for (int q = threadIdx.x; q < P.ops_len; q += blockDim.x) s_ops[q] = P.ops[q];
-  for (int q = threadIdx.x; q < S * OLRT_BWG_SLOTS * 32; q += blockDim.x) s_acc[q] = R(0);
+  for (int q = threadIdx.x; q < S * slots * 32; q += blockDim.x) s_acc[q] = R(0);
   if (threadIdx.x == 0) s_bad = 0;
   __syncthreads();
-  if (threadIdx.x < S && !bwd_supported<R>(s_ops, threadIdx.x)) s_bad = 1;
+  if (threadIdx.x < S && !bwd_supported<R>(s_ops, threadIdx.x, P.cslots)) s_bad = 1;
   __syncthreads();
   if (s_bad) {
     if (threadIdx.x == 0 && status != nullptr) atomicOr(status, OLRT_ST_BAD_HINT);
@@ -489,7 +615,7 @@ __global__ void __launch_bounds__(256, 2) trace_bwd_kernel(const BwdParams<R> P,
     if (p != cur_p) {
       __syncthreads();
       if (cur_p >= 0) {  // flush the previous prescription's gradients
-        bwd_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
+        bwd_flush<R>(s_acc, s_ops, S, W, slots, P.gpresc + (long long)cur_p * P.presc_stride);
         __syncthreads();
       }
       const R* src = P.presc + (long long)p * P.presc_stride;
@@ -546,7 +672,7 @@ __global__ void __launch_bounds__(256, 2) trace_bwd_kernel(const BwdParams<R> P,
       for (int i = 0; i < OLRT_BWG_MAXC; ++i) gC[i] = R(0);
       bwd_surface<R>(sp, W, widx, ex, ey, ez, eL, eM, eN, ei, gx, gy, gz, gL, gM, gN, gi, gopd, gF, gR, gk, gC);
       if (valid) {  // parameter partials: one lane-private shared atomic each
-        R* acc = s_acc + (size_t)s * OLRT_BWG_SLOTS * 32 + lane;
+        R* acc = s_acc + (size_t)s * slots * 32 + lane;
         atomicAdd(acc + 0 * 32, gF[0]); atomicAdd(acc + 1 * 32, gF[1]); atomicAdd(acc + 2 * 32, gF[2]);
         if (sp.op[OLRT_OP_FRAMEFLAGS] & 7) {
 #pragma unroll
@@ -555,8 +681,9 @@ __global__ void __launch_bounds__(256, 2) trace_bwd_kernel(const BwdParams<R> P,
         if (sp.geom != OLRT_GEOM_PLANE) {
           atomicAdd(acc + OLRT_FRAME_REALS * 32, gR); atomicAdd(acc + (OLRT_FRAME_REALS + 1) * 32, gk);
           if (sp.geom != OLRT_GEOM_STANDARD) {
+            const int nc = (sp.geom == OLRT_GEOM_ZERNIKE) ? 2 * sp.ncoef : sp.ncoef;
             for (int i = 0; i < OLRT_BWG_MAXC; ++i)
-              if (i < sp.ncoef) atomicAdd(acc + (OLRT_FRAME_REALS + 2 + i) * 32, gC[i]);
+              if (i < nc && gC[i] != R(0)) atomicAdd(acc + (OLRT_FRAME_REALS + 2 + i) * 32, gC[i]);
           }
         }
       }
@@ -573,7 +700,7 @@ __global__ void __launch_bounds__(256, 2) trace_bwd_kernel(const BwdParams<R> P,
     }
   }
   __syncthreads();
-  if (cur_p >= 0) bwd_flush<R>(s_acc, s_ops, S, W, P.gpresc + (long long)cur_p * P.presc_stride);
+  if (cur_p >= 0) bwd_flush<R>(s_acc, s_ops, S, W, slots, P.gpresc + (long long)cur_p * P.presc_stride);
 }
 
 template <typename R>
@@ -588,6 +715,10 @@ int launch_bwd(const olrt_sys* sys, const R* presc, const int32_t* ops, long lon
   P.presc_stride = sys->presc_stride; P.ops_len = sys->ops_len;
   for (int q = 0; q < OLRT_MAX_WAVELENGTHS; ++q) P.wavelengths[q] = (R)sys->wavelengths[q];
   P.four_pi = (R)(4.0 * 3.141592653589793);
+  // coefficient gradient slots per surface: bits 8-15 of the hint (the caller's maximum over the surfaces), else 16
+  P.cslots = (sys->kernel_hint >> 8) & 0xFF;
+  if (P.cslots == 0) P.cslots = OLRT_BWG_DEFC;
+  if (P.cslots > OLRT_BWG_MAXC) return OLRT_E_UNSUPPORTED;
   int block = 256;
   if (sys->n_presc > 1) {
     block = 0;
@@ -597,7 +728,8 @@ int launch_bwd(const olrt_sys* sys, const R* presc, const int32_t* ops, long lon
   const size_t pp = (size_t)((sys->presc_stride + 1) & ~1);
   const size_t smem = pp * sizeof(R) +
                       (size_t)((sys->n_surfaces * der_stride(sys->n_wavelengths) + 1) & ~1) * sizeof(R) +
-                      (size_t)sys->n_surfaces * OLRT_BWG_SLOTS * 32 * sizeof(R) + (size_t)2 * 7 * block * sizeof(R) +
+                      (size_t)sys->n_surfaces * (OLRT_FRAME_REALS + 2 + P.cslots) * 32 * sizeof(R) +
+                      (size_t)2 * 7 * block * sizeof(R) +
                       (size_t)((sys->ops_len + 1) & ~1) * sizeof(int32_t);
   if (smem > 200 * 1024) return OLRT_E_LIMIT;
   if (smem > 48 * 1024)

@@ -80,7 +80,8 @@ def _undifferentiated_variable(surfaces):
             if _depends_on_variable(getattr(g, nm, None)):
                 return f"surface {k}: {nm}"
         gname = type(g).__name__
-        if gname not in ("EvenAsphere", "Plane", "StandardGeometry", "PolynomialGeometry"):
+        if gname not in ("EvenAsphere", "OddAsphere", "Plane", "StandardGeometry", "PolynomialGeometry",
+                         "ZernikePolynomialGeometry"):
             co = getattr(g, "coefficients", None)
             if co is None and getattr(g, "zernike", None) is not None:
                 co = g.zernike.coeffs
@@ -124,7 +125,9 @@ def _wants_grad(be, rays, surfaces) -> bool:
                 vals += list(c) if isinstance(c, (list, tuple)) else [c]
         if any(isinstance(v, torch.Tensor) and v.requires_grad for v in vals):
             return True
-    return False
+    # a variable on a quantity the kernels do not differentiate (norm radius, index, aperture size, parent frame ...)
+    # must still reach the reference's own graph
+    return _undifferentiated_variable(surfaces) is not None
 
 
 def _make_fused(stock, RealRays, be, opts):

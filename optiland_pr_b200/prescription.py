@@ -187,9 +187,9 @@ class PackedSystem:
 
     def differentiable(self, require_records: bool = True) -> bool:
         """True when the backward kernels cover every surface (csrc/trace_bwd.cuh: bwd_supported): plane / finite
-        conic / even asphere / x^i y^j polynomial (<= 16 coefficients) on ONE frame (decentred, tilted or both), any
-        aperture program, no coating or thin-lens flag, every surface recorded. The kernels re-check it
-        (OLRT_ST_BAD_HINT)."""
+        conic / even or odd asphere / x^i y^j polynomial (<= 32 coefficients) / Zernike freeform (<= 16 terms,
+        |m| <= 12) on ONE frame (decentred, tilted or both), any aperture program, no coating or thin-lens flag, every
+        surface recorded. The kernels re-check it (OLRT_ST_BAD_HINT)."""
         if require_records and self.record_surfaces != [lay.index for lay in self.layouts]:
             return False
         for k in range(self.n_surfaces):
@@ -202,11 +202,24 @@ class PackedSystem:
                 return False
             if geom == L.GEOM_PLANE:
                 continue
-            if geom not in (L.GEOM_STANDARD, L.GEOM_EVEN_ASPHERE, L.GEOM_POLYNOMIAL) or flags & L.F_RADIUS_INF:
+            if geom not in (L.GEOM_STANDARD, L.GEOM_EVEN_ASPHERE, L.GEOM_ODD_ASPHERE, L.GEOM_POLYNOMIAL,
+                            L.GEOM_ZERNIKE) or flags & L.F_RADIUS_INF:
                 return False
-            if geom != L.GEOM_STANDARD and int(op[L.OP_NCOEF]) > L.BWG_MAXC:
+            if geom == L.GEOM_ZERNIKE and any(abs(m) > L.BWG_MAXM for (_, m, _, _) in self.layouts[k].zernike_terms):
                 return False
-        return True
+        return self.coef_slots() <= L.BWG_MAXC
+
+    def coef_slots(self) -> int:
+        """Coefficient gradient slots per surface the general adjoint kernel needs (a Zernike term takes two: its c
+        and its c N entry); travels in bits 8-15 of olrt_sys.kernel_hint."""
+        need = 0
+        for k in range(self.n_surfaces):
+            row = k * L.OPS_STRIDE
+            geom, nc = int(self.ops[row + L.OP_GEOM]), int(self.ops[row + L.OP_NCOEF])
+            if geom in (L.GEOM_PLANE, L.GEOM_STANDARD):
+                continue
+            need = max(need, 2 * nc if geom == L.GEOM_ZERNIKE else nc)
+        return need
 
     def reduced_adjoint(self) -> bool:
         """True when the reduced-algebra adjoint (csrc/trace_bx.cuh) covers the lens: the fast kinds with <= 8
@@ -237,6 +250,9 @@ class PackedSystem:
         x / y entries) -- only then may OLRT_HINT_ORDINARY be claimed."""
         s = L.OlrtSys()
         s.kernel_hint = L.HINT_FASTKINDS if self.fastkinds() else 0
+        cs_ = self.coef_slots()
+        if 16 < cs_ <= L.BWG_MAXC:      # more coefficient gradient slots than the general adjoint's default
+            s.kernel_hint |= cs_ << 8
         if own_rows and n_presc == self.presc.shape[0] and self.ordinary():
             s.kernel_hint |= L.HINT_ORDINARY
         s.n_surfaces = self.n_surfaces

@@ -67,7 +67,7 @@ def leafify(lens):
             leaves.append((k, "radius", 0, g.radius))
         g.k = mk(g.k)
         leaves.append((k, "conic", 0, g.k))
-        if hasattr(g, "coefficients") and type(g).__name__ == "EvenAsphere":
+        if hasattr(g, "coefficients") and type(g).__name__ in ("EvenAsphere", "OddAsphere"):
             cs_ = [mk(c) for c in g.coefficients]
             g.coefficients = cs_
             for i, c in enumerate(cs_):
@@ -76,10 +76,14 @@ def leafify(lens):
             c2 = torch.tensor(np.asarray(be.to_numpy(g.coefficients), dtype=np.float64), requires_grad=True)
             g.coefficients = c2
             leaves.append((k, "coef2d", 0, c2))
+        if type(g).__name__ == "ZernikePolynomialGeometry":   # optimization/variable/zernike_coeff.py:71
+            cz = torch.tensor(np.asarray(be.to_numpy(g.zernike.coeffs), dtype=np.float64), requires_grad=True)
+            g.zernike.coeffs = cz
+            leaves.append((k, "zernike", 0, cz))
     return leaves
 
 
-def run_case(name, make_lens, wavelengths, n_pupil, seed):
+def run_case(name, make_lens, wavelengths, n_pupil, seed, pupil_scale=0.9, grad_mode=True):
     # rays and packed layout from the NumPy backend (identical inputs for both backends)
     be.set_backend("numpy")
     lens = make_lens()
@@ -89,7 +93,7 @@ def run_case(name, make_lens, wavelengths, n_pupil, seed):
     for (hx, hy) in fields:
         for w in wavelengths:
             px, py = raygen_np.random_pupil(n_pupil, int(rng.integers(1 << 30)))
-            r = lens.ray_tracer.ray_generator.generate_rays(np.full(n_pupil, hx), np.full(n_pupil, hy), px * 0.9, py * 0.9, w)
+            r = lens.ray_tracer.ray_generator.generate_rays(np.full(n_pupil, hx), np.full(n_pupil, hy), px * pupil_scale, py * pupil_scale, w)
             parts.append(np.stack([np.asarray(getattr(r, q), dtype=np.float64) for q in ("x", "y", "z", "L", "M", "N", "i", "w")]))
     rays_in = np.concatenate(parts, axis=1)
     packed = pack_surface_group(lens.surface_group.surfaces, wavelengths)
@@ -100,7 +104,13 @@ def run_case(name, make_lens, wavelengths, n_pupil, seed):
     be.set_backend("torch")
     be.set_device("cpu")
     be.set_precision("float64")
-    be.grad_mode.enable()
+    # (grad mode makes every be.array a requires-grad leaf; the reference's Zernike radial term then floor-divides such
+    # tensors -- (n + m) // 2, zernike/base.py -- which torch cannot differentiate: those lenses run with grad mode off
+    # and only the explicit leaves below asking for gradients)
+    if grad_mode:
+        be.grad_mode.enable()
+    else:
+        be.grad_mode.disable()
     lens_t = make_lens()
     leaves = leafify(lens_t)
     comps = [torch.tensor(rays_in[q], dtype=torch.float64, requires_grad=(q < 7)) for q in range(8)]
@@ -123,6 +133,12 @@ def run_case(name, make_lens, wavelengths, n_pupil, seed):
         if nm == "angle":
             gangle[k, i] = 0.0 if t.grad is None else float(t.grad)
             have_angle[k, i] = True
+            continue
+        if nm == "zernike":     # d loss / d c_j stored at the term's `c` entry (the kernel splits it over c and c N)
+            gz = np.zeros(tuple(t.shape)) if t.grad is None else t.grad.numpy()
+            for j, (_, _, off, _) in enumerate(lay.zernike_terms):
+                gpresc[off] = gz[j]
+                have[off] = True
             continue
         if nm == "coef2d":
             g2 = np.zeros(tuple(t.shape)) if t.grad is None else t.grad.numpy()
@@ -152,6 +168,17 @@ def ref_three_mirror():
     return my_samples.build_three_mirror(ref_optic.Optic(name="TMA"), to_array=to_arr)
 
 
+def ref_freeform_plate(zt):
+    """Zernike freeform + odd asphere + tilts about three axes + aperture programs + absorbing glass (the second half
+    of BASELINE config C3); the pupil is kept inside the TIR rim so the summed loss is finite."""
+    def make():
+        from optiland import optic as ref_optic
+        import optiland.physical_apertures as ref_ap
+        from optiland_pr_b200 import samples as my_samples
+        return my_samples.build_freeform_plate(ref_optic.Optic(name="plate"), ref_ap, zt)
+    return make
+
+
 def ref_tilted_singlet():
     """An aspheric singlet whose two surfaces are decentred and tilted about all three axes (refraction through
     tilted frames; the tilt variables of optimization/variable/tilt.py)."""
@@ -167,11 +194,15 @@ def ref_tilted_singlet():
 def main():
     only = sys.argv[1:]
     if only:
-        cases = {"three_mirror": lambda: run_case("three_mirror", ref_three_mirror, [0.587], 48, 7),
+        cases = {"freeform_plate_fringe": lambda: run_case("freeform_plate_fringe", ref_freeform_plate("fringe"), [0.55], 64, 9, 0.55, False),
+                 "freeform_plate_noll": lambda: run_case("freeform_plate_noll", ref_freeform_plate("noll"), [0.55], 64, 10, 0.55, False),
+                 "three_mirror": lambda: run_case("three_mirror", ref_three_mirror, [0.587], 48, 7),
                  "tilted_singlet": lambda: run_case("tilted_singlet", ref_tilted_singlet, [0.587], 96, 8)}
         for nm in only:
             cases[nm]()
         return
+    run_case("freeform_plate_fringe", ref_freeform_plate("fringe"), [0.55], 64, 9, 0.55, False)
+    run_case("freeform_plate_noll", ref_freeform_plate("noll"), [0.55], 64, 10, 0.55, False)
     run_case("three_mirror", ref_three_mirror, [0.587], 48, 7)
     run_case("tilted_singlet", ref_tilted_singlet, [0.587], 96, 8)
     run_case("cooke_triplet", CookeTriplet, [0.48, 0.55, 0.65], 24, 3)

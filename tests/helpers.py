@@ -28,7 +28,7 @@ GRAD_ONLY_MIRRORS = {"tilted_singlet": samples.TiltedSinglet}
 GRAD_MIRRORS = ("cooke_triplet", "double_gauss", "even_asphere_double_gauss", "aspheric_singlet")
 # lenses of the general adjoint kernel only: tilted frames, x^i y^j polynomial freeforms (tilt and polynomial-coefficient
 # variables of the reference: optimization/variable/tilt.py:59, polynomial_coeff.py:72)
-GRAD_MIRRORS_GENERAL = ("three_mirror", "tilted_singlet")
+GRAD_MIRRORS_GENERAL = ("three_mirror", "tilted_singlet", "freeform_plate_fringe", "freeform_plate_noll")
 # fixtures whose surfaces are all closed-form (+,-,*,/,sqrt only): oracle must match the reference bit for bit
 CLOSED_FORM = ("cooke_triplet", "double_gauss", "coated_relay")
 

@@ -13,7 +13,8 @@ from optiland_pr_b200.prescription import _f, pack_surface_group
     ("CookeTriplet", True, True), ("DoubleGauss", True, True), ("EvenAsphereDoubleGauss", True, True),
     ("AsphericSinglet", True, True),
     ("ThreeMirrorAnastigmat", True, False), ("TiltedSinglet", True, False),   # general adjoint kernel only
-    ("FreeformPlate", False, False), ("CoatedRelay", False, False), ("Anamorphic", False, False)])
+    ("FreeformPlate", True, False),                                           # Zernike + odd asphere, tilted frames
+    ("CoatedRelay", False, False), ("Anamorphic", False, False)])
 def test_differentiable_set(name, want, reduced):
     lens = getattr(samples, name)()
     wl = [float(lens.wavelengths[lens.primary_index])]
