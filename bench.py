@@ -726,15 +726,19 @@ def bench_other_configs(torch, timed, args, fp64_peak):
     Py = torch.from_numpy(np.sqrt(r_) * np.sin(th)).to(dev)
     S1 = lens.surface_group.num_surfaces - 1
 
-    def c1():       # SpotDiagram: all 9 (field, wavelength) pairs in one fused launch per pass, two passes
+    passes = [0]
+
+    def c1():       # SpotDiagram: all 9 (field, wavelength) pairs in ONE fused launch; the radius pass re-reads kept states
         sd = spot.SpotDiagram(lens, distribution=(Px, Py))
+        passes[0] = sd.passes
         return sd._rms.cpu()
 
     ms = timed(c1, max(2, args.steps // 2), 3)
-    out["c1_cooke_9_pairs_x_1M"] = {"ms": ms, "ray_surfaces_per_s": 2 * 9 * n1 * S1 / (ms * 1e-3),
-                                    "passes": 2,
-                                    "api": "spot.SpotDiagram(lens): centroid pass + radius pass over 3 fields x 3 "
-                                           "wavelengths, one fused launch + trace + spot kernel each, RMS -> host"}
+    out["c1_cooke_9_pairs_x_1M"] = {"ms": ms, "ray_surfaces_per_s": 9 * n1 * S1 / (ms * 1e-3),
+                                    "trace_passes": passes[0],
+                                    "api": "spot.SpotDiagram(lens): 3 fields x 3 wavelengths in one fused launch + trace "
+                                           "+ spot kernel (centroids), the RMS / geometric radii about the centroids from "
+                                           "a streaming reduction of the kept final states, radii -> host"}
     # ---- C3 (BASELINE configs[2]: 64 M rays, seed 2): off-axis three-mirror system, 4 x 4 polynomial freeforms, rx tilts,
     # dy decenters -- the interpreter kernel. The pupil is drawn on the device (NumPy's stream for seed 2).
     from optiland_pr_b200 import flops

@@ -199,14 +199,28 @@ class SpotDiagram:
         k0 = np.zeros((nf, p0.n_surfaces), dtype=np.int32)
         for k in p0.nr_rows():
             k0[:, k] = 2
-        s1, kg = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, k0, valid_only=True)
+        # ONE trace: the first pass also keeps the final ray states (64 B per ray) when they fit comfortably; the second
+        # pass -- sums about the reference wavelength's centroids -- is then a streaming reduction of the kept x, y, i
+        # (olrt_spot_sums_*), not a second trace
+        npup = int(Px.numel())
+        keep = None
+        if nw * nf * npup * 64 <= self.keep_bytes_limit:
+            keep = torch.empty((8, nw * nf * npup), dtype=dt, device=dev)
+        s1, kg = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, k0, valid_only=True, keep=keep)
         st = spot_stats(s1)
         cen = torch.stack([st["cx"], st["cy"]], dim=1).reshape(nw, nf, 2)[self.ref_index]     # [nf, 2]
         shift2 = cen.unsqueeze(0).expand(nw, nf, 2).reshape(-1, 2).contiguous()
-        s2, _ = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, kg, shift=shift2, valid_only=True,
-                                  settle=False)
+        if keep is not None and getattr(keep, "valid", False):
+            s2 = spot_sums(keep[0], keep[1], keep[6], nw * nf, npup, shift2, True)
+            self.passes = 1
+        else:
+            s2, _ = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, kg, shift=shift2, valid_only=True,
+                                      settle=False)
+            self.passes = 2
         self.group_iters = kg
         return s2, cen
+
+    keep_bytes_limit = 8 << 30     # final states kept for the second pass up to this many bytes, else two traces
 
     def centroid(self):
         """[(cx, cy)] per field, reference wavelength (spot_diagram.py:317-327)."""

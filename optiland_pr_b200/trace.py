@@ -316,7 +316,7 @@ def group_true_iters(packed: PackedSystem, resid: np.ndarray, k_used: np.ndarray
 
 def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Tensor, Py: torch.Tensor,
                       field_xy: torch.Tensor, gen_kw: dict, k0: np.ndarray, *, shift: torch.Tensor | None = None,
-                      valid_only: bool = False, settle: bool = True, between=None):
+                      valid_only: bool = False, settle: bool = True, between=None, keep: torch.Tensor | None = None):
     """Spot sums of every (prescription, field) group from fused launch + trace + spot kernels that write nothing
     per ray. `presc_t` [T, stride] holds one prescription per row (Monte-Carlo trials, or one row per WAVELENGTH:
     the media live in the prescription row); the groups are g = row * n_fields + field. The Newton trip counts are
@@ -325,7 +325,9 @@ def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Ten
     counts (settle=False: `k0` is [G, S] and trusted). shift: [G, 2] point the sums are taken about (default: each
     group's chief-ray image point, from one more tiny launch). Returns (sums [G, SPOT_SUMS] with columns 8:10 =
     shift, counts [G, S] int32). `between`: optional host callback run ONCE right after the first launch is queued and
-    before its results are waited for (the caller's host work then overlaps the kernel)."""
+    before its results are waited for (the caller's host work then overlaps the kernel). `keep`: optional [8, G * P]
+    buffer that receives the final ray states of the FIRST launch (all groups); `keep.valid` is set True when that
+    launch's counts passed the exit rule for every group (so the buffer holds the result), else False."""
     dev = Px.device
     dt = gen_kw.get("dtype", torch.float64)
     nf, S = int(field_xy.shape[0]), packed.n_surfaces
@@ -343,7 +345,8 @@ def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Ten
         shift = chief[:2].t().to(torch.float64).nan_to_num(0.0, 0.0, 0.0).contiguous()
     out_sums = torch.empty((G, L.SPOT_SUMS), dtype=torch.float64, device=dev)
     todo = np.arange(T)
-    for _ in range(8):
+    keep_ok = keep is not None
+    for round_ in range(8):
         sel = torch.from_numpy(todo).to(dev)
         gsel = (todo[:, None] * nf + np.arange(nf)[None, :]).reshape(-1)
         gsel_t = torch.from_numpy(gsel).to(dev)
@@ -354,8 +357,11 @@ def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Ten
         sh = shift[gsel_t].contiguous()
         # the kernel lays its residual slots out by the ops table's counts and never gives a group more than those
         packed.set_nr_iters(np.maximum(kg[gsel].max(axis=0), 0).tolist())
-        fused_trace_pupil(packed, Px, Py, field_xy, out=None, spot=sums, spot_shift=sh, spot_valid_only=valid_only,
+        fused_trace_pupil(packed, Px, Py, field_xy, out=keep if (keep is not None and round_ == 0) else None, spot=sums,
+                          spot_shift=sh, spot_valid_only=valid_only,
                           presc=presc_t[sel].contiguous(), group_k=k_t, group_resid=gres, **gen_kw)
+        if round_ > 0:
+            keep_ok = False       # some group was traced again with other counts: the kept states are stale
         sums[:, 8:10] = sh
         out_sums[gsel_t] = sums
         if between is not None:
@@ -374,4 +380,6 @@ def fused_spot_groups(packed: PackedSystem, presc_t: torch.Tensor, Px: torch.Ten
         todo = np.unique(gsel[wrong] // nf)
     else:
         raise L.OlrtLibraryError("Newton trip counts did not settle")
+    if keep is not None:
+        keep.valid = bool(keep_ok)
     return out_sums, kg
