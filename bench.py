@@ -623,7 +623,7 @@ def scaling_legs(torch, dist, lens, packed, npf, nf, S_eff, timed, args, rank, w
         p_ = torch.nn.Parameter(torch.tensor(0.0, dtype=torch.float64, device=dev))
         lens4.set_conic(p_, k)
         pars.append(p_)
-    opt = torch.optim.Adam(pars, lr=1e-6)
+    opt = torch.optim.Adam(pars, lr=1e-6, fused=True)     # one kernel for the 12 scalar parameters
     n4 = 1_000_000
     Px4, Py4 = random_pupil_device(n4, 0, dev)
     fields4 = lens4.get_field_coords()
@@ -783,7 +783,7 @@ def bench_other_configs(torch, timed, args, fp64_peak):
         p_ = torch.nn.Parameter(torch.tensor(0.0, dtype=torch.float64, device=dev))
         lens4.set_conic(p_, k)
         pars.append(p_)
-    opt = torch.optim.Adam(pars, lr=1e-6)
+    opt = torch.optim.Adam(pars, lr=1e-6, fused=True)     # one kernel for the 12 scalar parameters
     n4 = 1_000_000
     r_, th = rng.uniform(size=n4), rng.uniform(0, 2 * np.pi, size=n4)
     Px4 = torch.from_numpy(np.sqrt(r_) * np.cos(th)).to(dev)

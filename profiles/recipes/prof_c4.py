@@ -15,7 +15,7 @@ for k in range(1, 7):
     p_ = torch.nn.Parameter(torch.tensor(float(sfs[k].geometry.radius), dtype=torch.float64, device=dev)); lens.set_radius(p_, k); pars.append(p_)
 for k in range(1, 7):
     p_ = torch.nn.Parameter(torch.tensor(0.0, dtype=torch.float64, device=dev)); lens.set_conic(p_, k); pars.append(p_)
-opt = torch.optim.Adam(pars, lr=1e-6)
+opt = torch.optim.Adam(pars, lr=1e-6, fused=("fused" in sys.argv))
 Px, Py = random_pupil_device(1_000_000, 0, dev)
 fields, wls = lens.get_field_coords(), list(lens.wavelengths)
 def step():
