@@ -370,6 +370,9 @@ __device__ __forceinline__ void fx_even(RayState<R>& r, const FxSurf<R>& sf, con
   R t = fx_conic_t(r.x, r.y, r.z, r.L, r.M, r.N, sf, (kind & FX_SPHERE) != 0, guard);
   const int m = info.ncoef;
   R xi, yi, zi, zx, zy, fp, r2;
+  // residual reports by bits: the tolerance and this surface's first bit, read once (not per iteration)
+  const R tol_ = (rbits != nullptr) ? sf.tol : R(0);
+  unsigned bit_ = (rbits != nullptr) ? (1u << info.roff) : 0u;
   for (int j = 0;; ++j) {
     xi = fma(t, r.L, r.x); yi = fma(t, r.M, r.y); zi = fma(t, r.N, r.z);
     r2 = fma(xi, xi, yi * yi);
@@ -401,7 +404,8 @@ __device__ __forceinline__ void fx_even(RayState<R>& r, const FxSurf<R>& sf, con
       // the reference's exit test is max_rays |f_j| < tol (newton_raphson.py:148): what the host needs per iteration
       // is whether SOME ray fails it -- one bit per (surface, iteration) kept in a register for the whole launch.
       // NaN compares false here: the fix-up pass (IEEE) reports that ray.
-      if (valid && r_abs(f) >= sf.tol) *rbits |= 1u << (info.roff + j);
+      if (valid && r_abs(f) >= tol_) *rbits |= bit_;
+      bit_ <<= 1;
     } else if (resid != nullptr) {  // NaN: the fix-up pass (IEEE) reports it
       const unsigned long long key = (valid && f == f) ? resid_bits((double)r_abs(f)) : 0ull;
       report_resid(resid + j, key);
