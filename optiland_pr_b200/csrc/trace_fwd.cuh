@@ -114,7 +114,18 @@ __device__ __forceinline__ void load_surface(SurfParams<R>& sp, const int32_t* s
 }
 
 // surface kinds: straight-line instantiations for the common cases, the interpreter for the rest
-enum { KIND_GENERIC = 0, KIND_PLANE = 1, KIND_CONIC = 2, KIND_EVEN = 3 };
+enum { KIND_GENERIC = 0, KIND_PLANE = 1, KIND_CONIC = 2, KIND_EVEN = 3,
+       // interpreter only: an x^i y^j polynomial surface on ANY frame chain (tilts, decenters), refracting or reflecting,
+       // any aperture program: the geometry is fixed at compile time and its divisions / square roots run unguarded
+       // (MM_FAST: the same refinement arithmetic, no slow-path test) -- nothing in that path can hide a NaN behind a
+       // select, so a ray outside the fast path's domain comes out non-finite and is re-traced by the IEEE fix-up pass
+       KIND_POLY = 4,
+       // interpreter only: the generic body (any frame chain, geometry read from the ops table) with the same unguarded
+       // arithmetic, for plane / conic / even- and odd-asphere / Zernike surfaces without coating, thin-lens or
+       // renormalisation flags. The two square roots whose argument can be exactly zero ON the axis (rho of a Zernike
+       // term, r of an odd asphere) keep their guard: their NaN could otherwise disappear behind the reference's own
+       // `where(|f'| > 1e-14, ...)` select
+       KIND_GFAST = 5 };
 
 __device__ __forceinline__ int surface_kind(const int32_t* op) {
   const int geom = op[OLRT_OP_GEOM], flags = op[OLRT_OP_FLAGS];
@@ -135,15 +146,19 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
                                              unsigned long long* resid, uint32_t& status,
                                              R& L0, R& M0, R& N0) {
   const int32_t* op = sp.op;
+  constexpr bool FRAMES = (KIND == KIND_GENERIC || KIND == KIND_POLY || KIND == KIND_GFAST);   // frame chain with rotations
   const int geom = (KIND == KIND_PLANE) ? OLRT_GEOM_PLANE
                    : (KIND == KIND_CONIC) ? OLRT_GEOM_STANDARD
-                   : (KIND == KIND_EVEN) ? OLRT_GEOM_EVEN_ASPHERE : sp.geom;
-  const int flags = (KIND == KIND_GENERIC) ? op[OLRT_OP_FLAGS] : (op[OLRT_OP_FLAGS] & OLRT_F_ABSORB);
-  const int nframes = (KIND == KIND_GENERIC) ? op[OLRT_OP_NFRAMES] : 1;
-  const int fflags = (KIND == KIND_GENERIC) ? op[OLRT_OP_FRAMEFLAGS] : 0;
+                   : (KIND == KIND_EVEN) ? OLRT_GEOM_EVEN_ASPHERE
+                   : (KIND == KIND_POLY) ? OLRT_GEOM_POLYNOMIAL : sp.geom;
+  const int flags = (KIND == KIND_GENERIC) ? op[OLRT_OP_FLAGS]
+                    : (KIND == KIND_GFAST) ? (op[OLRT_OP_FLAGS] & (OLRT_F_ABSORB | OLRT_F_RADIUS_INF))
+                                           : (op[OLRT_OP_FLAGS] & OLRT_F_ABSORB);
+  const int nframes = FRAMES ? op[OLRT_OP_NFRAMES] : 1;
+  const int fflags = FRAMES ? op[OLRT_OP_FRAMEFLAGS] : 0;
 
   // geometry.localize, standard_surface.py:199
-  if (KIND == KIND_GENERIC) cs_localize(r, sp.frames, nframes, fflags);
+  if (FRAMES) cs_localize(r, sp.frames, nframes, fflags);
   else frame_localize(r, sp.frames, 0);
 
   // t = geometry.distance(rays), standard_surface.py:211
@@ -160,9 +175,11 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
         R sag, zx = R(0), zy = R(0);
         if (j < K) {
           if (KIND == KIND_EVEN) even_asphere_eval<R, true, MM>(sp, xi, yi, sag, zx, zy);
+          else if (KIND == KIND_POLY) polynomial_eval<R, true, MM>(sp, xi, yi, sag, zx, zy);
           else nr_eval<R, true, MM>(sp, xi, yi, sag, zx, zy, status);
         } else {
           if (KIND == KIND_EVEN) even_asphere_eval<R, false, MM>(sp, xi, yi, sag, zx, zy);
+          else if (KIND == KIND_POLY) polynomial_eval<R, false, MM>(sp, xi, yi, sag, zx, zy);
           else nr_eval<R, false, MM>(sp, xi, yi, sag, zx, zy, status);
         }
         const R f = sag - zi;
@@ -237,6 +254,7 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
     R sag, zx, zy;
     uint32_t st2 = 0;
     if (KIND == KIND_EVEN) even_asphere_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy);
+    else if (KIND == KIND_POLY) polynomial_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy);
     else nr_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy, st2);
     slopes_to_normal<R, MM>(zx, zy, nx, ny, nz);
   }
@@ -247,7 +265,7 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
   }
 
   // geometry.globalize, standard_surface.py:228
-  if (KIND == KIND_GENERIC) cs_globalize(r, sp.frames, nframes, fflags);
+  if (FRAMES) cs_globalize(r, sp.frames, nframes, fflags);
   else frame_globalize(r, sp.frames, 0);
 }
 
@@ -297,6 +315,8 @@ __device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r,
         case KIND_PLANE: surface_step<R, KIND_PLANE, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
         case KIND_CONIC: surface_step<R, KIND_CONIC, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
         case KIND_EVEN: surface_step<R, KIND_EVEN, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
+        case KIND_POLY: surface_step<R, KIND_POLY, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
+        case KIND_GFAST: surface_step<R, KIND_GFAST, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
         default: surface_step<R, KIND_GENERIC, MM_GUARD>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
       }
     }
@@ -351,7 +371,20 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
   for (int q = threadIdx.x; q < P.ops_len; q += blockDim.x) s_ops[q] = P.ops[q];
   __syncthreads();
   const bool want_resid = (P.nr_resid != nullptr);
-  if (threadIdx.x < S) s_kind[threadIdx.x] = surface_kind(s_ops + threadIdx.x * OLRT_OPS_STRIDE);
+  if (threadIdx.x < S) {
+    const int32_t* op_ = s_ops + threadIdx.x * OLRT_OPS_STRIDE;
+    int k_ = surface_kind(op_);
+    if (k_ == KIND_GENERIC && op_[OLRT_OP_GEOM] == OLRT_GEOM_POLYNOMIAL &&
+        !(op_[OLRT_OP_FLAGS] & (OLRT_F_RADIUS_INF | OLRT_F_COATING | OLRT_F_THIN_LENS | OLRT_F_RENORM)))
+      k_ = KIND_POLY;
+    if (k_ == KIND_GENERIC && !(op_[OLRT_OP_FLAGS] & (OLRT_F_COATING | OLRT_F_THIN_LENS | OLRT_F_RENORM))) {
+      const int g_ = op_[OLRT_OP_GEOM];
+      if (g_ == OLRT_GEOM_PLANE || g_ == OLRT_GEOM_STANDARD || g_ == OLRT_GEOM_EVEN_ASPHERE ||
+          g_ == OLRT_GEOM_ODD_ASPHERE || g_ == OLRT_GEOM_ZERNIKE)
+        k_ = KIND_GFAST;
+    }
+    s_kind[threadIdx.x] = k_;
+  }
   if (threadIdx.x == 0) {
     int off = 0;
     for (int s = 0; s < S; ++s) {

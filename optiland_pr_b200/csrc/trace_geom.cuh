@@ -54,7 +54,9 @@ __device__ __forceinline__ void even_asphere_eval(const SurfParams<R>& sp, R x, 
 template <typename R, bool WANT_SLOPES, int MM>
 __device__ __forceinline__ void odd_asphere_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy) {
   const R r2 = x * x + y * y;
-  const R r = m_sqrt<MM>(r2);
+  // (r can be exactly 0 on the axis: the unguarded square root would turn it into a NaN that the non-finite filter
+  // below and the Newton loop's selects could hide -- this one keeps its guard in every mode)
+  const R r = m_sqrt<(MM == MM_FAST ? MM_GUARD : MM)>(r2);
   R denom;
   conic_sag_denom<R, MM>(r2, sp.cc, sag, denom);
   if (WANT_SLOPES) { const Recip<R, MM> rd(denom); zx = rd.div(x); zy = rd.div(y); }
@@ -150,26 +152,32 @@ __device__ __forceinline__ void polynomial_eval(const SurfParams<R>& sp, R x, R 
 template <typename R, bool WANT_SLOPES, int MM>
 __device__ __forceinline__ void zernike_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy,
                                              uint32_t& status) {
+  // every quotient below goes through m_div / Recip (bit-identical to IEEE division inside the fast path's domain; the
+  // divisors are a positive norm radius, rho under a `rho > 0` test, and sums with eps > 0). rho itself can be exactly
+  // 0 on the axis: its square root keeps the guard in the unguarded mode (a NaN there could hide behind the select)
   const R Rn = sp.norm_radius;
-  const R xn = x / Rn, yn = y / Rn;
+  const Recip<R, MM> rRn(Rn);
+  const R xn = rRn.div(x), yn = rRn.div(y);
   if (r_abs(xn) > R(1) || r_abs(yn) > R(1)) status |= OLRT_ST_ZERNIKE_RANGE;  // zernike.py:234-246
   const R rho2 = xn * xn + yn * yn;
-  const R rho = r_sqrt(rho2);
+  const R rho = m_sqrt<(MM == MM_FAST ? MM_GUARD : MM)>(rho2);
   // phi = arctan2(yn, xn); arctan2(0,0)=0
   R cph = R(1), sph = R(0);
-  if (rho > R(0)) { cph = xn / rho; sph = yn / rho; }
+  if (rho > R(0)) { const Recip<R, MM> rrho(rho); cph = rrho.div(xn); sph = rrho.div(yn); }
   const R r2 = x * x + y * y;
   R denom;
   conic_sag_denom<R, MM>(r2, sp.cc, sag, denom);
   R drho_dx = R(0), drho_dy = R(0), dphi_dx = R(0), dphi_dy = R(0);
   if (WANT_SLOPES) {
-    zx = x / denom; zy = y / denom;
+    { const Recip<R, MM> rd(denom); zx = rd.div(x); zy = rd.div(y); }
     const R eps = R(1e-14);
     const R Rn2 = Rn * Rn;
-    drho_dx = (x / Rn2) / (rho + eps);
-    drho_dy = (y / Rn2) / (rho + eps);
-    dphi_dx = (-yn) / (rho2 + eps) * (R(1) / Rn);
-    dphi_dy = (xn) / (rho2 + eps) * (R(1) / Rn);
+    const Recip<R, MM> rRn2(Rn2), rre(rho + eps), rr2e(rho2 + eps);
+    const R iRn = rRn.div(R(1));
+    drho_dx = rre.div(rRn2.div(x));
+    drho_dy = rre.div(rRn2.div(y));
+    dphi_dx = rr2e.div(-yn) * iRn;
+    dphi_dy = rr2e.div(xn) * iRn;
   }
   R zsum = R(0);
   const int32_t* nm = sp.ops + sp.aux;
