@@ -101,3 +101,43 @@ def test_empty_and_ragged_batches(n, fast):
     assert tuple(res.out.shape) == (8, n)
     if n:
         _check(lens, rays_in, fast)
+
+
+@pytest.mark.parametrize("fast", [True, False])
+@pytest.mark.parametrize("kind", ["zernike_m0", "zernike_tilt", "odd_asphere"])
+def test_rays_on_the_axis_of_zernike_and_odd_asphere_surfaces(kind, fast):
+    """The interpreter's unguarded arithmetic (KIND_GFAST) on surfaces whose evaluation takes a square root of EXACTLY
+    zero on the axis (rho of a Zernike term, r of an odd asphere): an unguarded sqrt(0) is a NaN that the reference's
+    own `where(|f'| > 1e-14, ...)` select could swallow -- a rotationally symmetric Zernike surface (m = 0 terms only)
+    has a finite sag there, so the ray would go on with a wrong finite intersection. Those two roots keep their guard;
+    here rays through the vertex, 1e-300 and 1e-9 off it, and ordinary ones, tilted frame included.
+    Zernike terms go through cos / sin(m phi) (libm in the oracle, angle addition in the kernel): <= 1e-12 even in strict
+    mode, as for every trigonometric surface."""
+    if kind == "odd_asphere":
+        # (no C_1 r term: with one the vertex is a cone tip, the slope C_1 x / r is discontinuous there and the last
+        # ulp of x decides the reference's own answer -- nothing a tolerance can be stated for)
+        kw = dict(radius=40.0, conic=-0.2, surface_type="odd_asphere", coefficients=[0.0, 2.0e-4, -3.0e-5], ry=0.01)
+    elif kind == "zernike_m0":      # fringe 1, 4, 9: piston, defocus, spherical -- no azimuthal dependence
+        kw = dict(radius=50.0, conic=0.1, surface_type="zernike", zernike_type="fringe", norm_radius=8.0,
+                  coefficients=[1.0e-3, 0.0, 0.0, 2.0e-2, 0.0, 0.0, 0.0, 0.0, -5.0e-3])
+    else:                           # tilt + coma terms as well, on a tilted frame
+        kw = dict(radius=50.0, conic=0.1, surface_type="zernike", zernike_type="noll", norm_radius=8.0, rx=0.02,
+                  coefficients=[0.0, 1.0e-2, -2.0e-2, 1.0e-2, 0.0, 3.0e-3, 4.0e-3, -2.0e-3])
+    lens = _singlet(**kw)
+    # (the last ray sits 1e-100 off the axis: r^2 = 2e-200 is still a normal number. A ray 1e-160 off it -- r^2 a
+    # denormal -- is outside the stated domain of the tolerance mode, 2^+-400, and differs there by 4e-6 in the OPD)
+    xs = np.array([0.0, 0.0, 1e-300, 1e-9, -1e-9, 0.5, -2.0, 3.0, 0.0, 1e-100])
+    ys = np.array([0.0, 1e-300, 0.0, 1e-9, 2e-9, -1.5, 0.25, 1.0, 2.5, -1e-100])
+    n = xs.size
+    L_ = np.array([0.0, 0.0, 0.0, 0.0, 1e-3, 0.01, -0.02, 0.0, 0.0, 0.0])
+    M_ = np.zeros(n)
+    rays_in = [xs, ys, np.full(n, -5.0), L_, M_, np.sqrt(1 - L_ * L_ - M_ * M_), np.ones(n), np.full(n, 0.55)]
+    if kind.startswith("zernike") and not fast:
+        packed = pack_surface_group(lens.surface_group.surfaces, [0.55])
+        with np.errstate(all="ignore"):
+            want = np.array(trace_np.trace_packed(packed, trace_np.Rays(*rays_in))["records"])
+        got = fused_trace(packed, [torch.tensor(rays_in[q], device="cuda") for q in range(8)], fast=False).record.cpu().numpy()
+        assert np.array_equal(np.isnan(got), np.isnan(want)) and np.isfinite(want).all()
+        assert np.max(np.abs(got - want) / np.maximum(np.abs(want), 1.0)) <= 1e-12
+    else:
+        _check(lens, rays_in, fast)
