@@ -183,8 +183,8 @@ class FusedTraceFn(torch.autograd.Function):
         # the host check above mirrors the kernels' own; reading the device word back would serialise every step
         if _CHECK_BWD_STATUS and int(status.item()) & L.ST_BAD_HINT:
             raise NotImplementedError(
-                "olrt_trace_bwd: gradients are implemented for plane / conic / even-asphere surfaces on an "
-                "untilted frame; this lens has a surface outside that set")
+                "olrt_trace_bwd: the kernel found a surface outside the differentiable set (plane / conic / asphere / "
+                "polynomial / Zernike on one frame, include/olrt.h)")
         g = [gin[q] if need[q] else None for q in range(8)]
         return (gpresc, g[0], g[1], g[2], g[3], g[4], g[5], g[6], g[7], None, None, None, None, None)
 
