@@ -61,10 +61,18 @@ def random_pupil_device(num_rays: int, seed=None, device=None, want_raw: bool = 
     from . import _lib as L
     lib = L.load()
     dev = torch.device(device if device is not None else be.get_device())
-    st = np.random.default_rng(seed).bit_generator.state["state"]
+    # NumPy hashes the seed into the generator's 128-bit state and increment (SeedSequence): ~0.1 ms, remembered per seed
+    hit = _PCG_STATE.get(seed) if isinstance(seed, int) else None
+    if hit is None:
+        st = np.random.default_rng(seed).bit_generator.state["state"]
+        hit = (st["state"], st["inc"])
+        if isinstance(seed, int):
+            if len(_PCG_STATE) > 256:
+                _PCG_STATE.clear()
+            _PCG_STATE[seed] = hit
     mask = (1 << 64) - 1
-    state = (C.c_uint64 * 2)(st["state"] >> 64, st["state"] & mask)
-    inc = (C.c_uint64 * 2)(st["inc"] >> 64, st["inc"] & mask)
+    state = (C.c_uint64 * 2)(hit[0] >> 64, hit[0] & mask)
+    inc = (C.c_uint64 * 2)(hit[1] >> 64, hit[1] & mask)
     n = int(num_rays)
     Px = torch.empty(n, dtype=torch.float64, device=dev)
     Py = torch.empty(n, dtype=torch.float64, device=dev)
@@ -77,6 +85,7 @@ def random_pupil_device(num_rays: int, seed=None, device=None, want_raw: bool = 
 
 
 _FIELD_CACHE: dict = {}
+_PCG_STATE: dict = {}       # seed -> (state, inc) of numpy.random.default_rng(seed) before its first draw
 
 
 class FieldTable:
@@ -445,10 +454,20 @@ class Optic:
         if spot:  # sums are taken about each field's chief-ray image point (one tiny launch, no read-back)
             sums = torch.zeros((nf, L.SPOT_SUMS), dtype=torch.float64, device=dev)
             if fused:
-                zero = torch.zeros(1, dtype=torch.float64, device=dev)
-                chief = torch.empty((8, nf), dtype=dt, device=dev)
-                fused_trace_pupil(packed, zero, zero, fxy_all, out=chief, status_t=status_t, **gen_kw)
-                shift = chief[:2].t().to(torch.float64).nan_to_num(0.0, 0.0, 0.0).contiguous()
+                # the chief rays only CONDITION the second moments (the statistics do not depend on the point the sums
+                # are taken about): traced once per lens state, fields and wavelength, then remembered on the lens
+                ck_key = (packed.presc.tobytes(), packed.ops.tobytes(), ft.fxy.tobytes(), float(wavelength), str(dt),
+                          str(dev))
+                cache = self.__dict__.setdefault("_chief_shift_cache", {})
+                shift = cache.get(ck_key)
+                if shift is None:
+                    zero = torch.zeros(1, dtype=torch.float64, device=dev)
+                    chief = torch.empty((8, nf), dtype=dt, device=dev)
+                    fused_trace_pupil(packed, zero, zero, fxy_all, out=chief, status_t=status_t, **gen_kw)
+                    shift = chief[:2].t().to(torch.float64).nan_to_num(0.0, 0.0, 0.0).contiguous()
+                    if len(cache) > 8:
+                        cache.clear()
+                    cache[ck_key] = shift
         launches = [(0, npup)] if streamed else edges
         rays_in = None if fused else torch.empty((8, n), dtype=dt, device=dev)
         n_slices = len(launches) * (1 if fused else nf)
