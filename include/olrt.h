@@ -366,6 +366,11 @@ int olrt_trace_pupil_f32(const olrt_sys* sys, const float* presc, const int32_t*
  *  raw        NULL, or [2][n] doubles (device): the draws r and theta themselves (NumPy's, bit for bit)      */
 int olrt_pupil_random_f64(const uint64_t state[2] /*host*/, const uint64_t inc[2] /*host*/, int64_t n, double* Px,
                           double* Py, double* raw, void* stream);
+/* Hexapolar pupil distribution generated on the device: HexagonalDistribution.generate_points
+ * (optiland/distribution.py:189-220) -- the centre, then ring i = 1 .. num_rings with 6 i points at radius
+ * linspace(0, 1, num_rings + 1)[i] and angles linspace(0, 2 pi, 6 i + 1)[:-1]; radii and angles are NumPy's bit for bit,
+ * Px, Py within an ulp or two (cos / sin).  Px, Py: [1 + 3 num_rings (num_rings + 1)] doubles (device).        */
+int olrt_pupil_hexapolar_f64(int32_t num_rings, double* Px, double* Py, void* stream);
 
 /* OPD / wavefront epilogue: per ray, the optical path from the image surface back to the
  * reference sphere, the launch-plane tilt correction and the OPD in waves relative to the chief ray --

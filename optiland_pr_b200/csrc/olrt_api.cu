@@ -471,6 +471,43 @@ extern "C" int olrt_pupil_random_f64(const uint64_t state[2], const uint64_t inc
   return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
 }
 
+// HexagonalDistribution.generate_points (optiland/distribution.py:189-220): the centre, then ring i = 1 .. R with 6 i
+// points at radius linspace(0, 1, R + 1)[i] and angles linspace(0, 2 pi, 6 i + 1)[:-1] -- index arithmetic per point.
+// NumPy's linspace is arange * (delta / div) with the last element set to the stop value.
+__global__ void __launch_bounds__(256) pupil_hexapolar_kernel(int rings, long long n, double two_pi, double* Px,
+                                                              double* Py) {
+  const long long T = (long long)gridDim.x * blockDim.x;
+  const double rstep = 1.0 / (double)rings;
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += T) {
+    if (p == 0) { Px[0] = 0.0; Py[0] = 0.0; continue; }
+    // ring i holds points 1 + 3 (i - 1) i .. 3 i (i + 1): i from the root of 3 i^2 + 3 i = p, corrected exactly
+    long long i = (long long)ceil((sqrt(12.0 * (double)p - 3.0) - 3.0) / 6.0);
+    if (i < 1) i = 1;
+    while (3 * i * (i + 1) < p) ++i;
+    while (i > 1 && 3 * (i - 1) * i >= p) --i;
+    const long long k = p - 1 - 3 * (i - 1) * i;
+    const double r = (i == rings) ? 1.0 : __dmul_rn((double)i, rstep);
+    const double tstep = two_pi / (double)(6 * i);
+    const double th = __dmul_rn((double)k, tstep);
+    double sn, cs;
+    sincos(th, &sn, &cs);
+    Px[p] = __dmul_rn(r, cs); Py[p] = __dmul_rn(r, sn);
+  }
+}
+
+extern "C" int olrt_pupil_hexapolar_f64(int32_t num_rings, double* Px, double* Py, void* stream) {
+  if (!Px || !Py || num_rings < 0) return OLRT_E_ARG;
+  const long long n = 1 + 3LL * num_rings * (num_rings + 1LL);
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  long long grid = (long long)sms * 8;
+  const long long need = (n + 255) / 256;
+  if (grid > need) grid = need;
+  pupil_hexapolar_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(num_rings, n, 2.0 * 3.141592653589793, Px, Py);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+
 // ---------------------------------------------------------------------------------------------
 // OPD / wavefront epilogue (kernel in trace_strict.cu)
 // ---------------------------------------------------------------------------------------------

@@ -84,6 +84,23 @@ def random_pupil_device(num_rays: int, seed=None, device=None, want_raw: bool = 
     return (Px, Py, raw) if want_raw else (Px, Py)
 
 
+def hexapolar_pupil_device(num_rings: int, device=None):
+    """HexagonalDistribution.generate_points(num_rings) (optiland/distribution.py:189-220) generated ON THE DEVICE by
+    `olrt_pupil_hexapolar_f64`: radii and angles are NumPy's linspace values bit for bit, Px, Py within an ulp or two
+    (cos / sin). Returns (Px, Py) device tensors of 1 + 3 R (R + 1) points."""
+    from . import _lib as L
+    lib = L.load()
+    dev = torch.device(device if device is not None else be.get_device())
+    R_ = int(num_rings)
+    n = 1 + 3 * R_ * (R_ + 1)
+    Px = torch.empty(n, dtype=torch.float64, device=dev)
+    Py = torch.empty(n, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.olrt_pupil_hexapolar_f64(R_, Px.data_ptr(), Py.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
+    L.check(rc, "olrt_pupil_hexapolar_f64")
+    return Px, Py
+
+
 _FIELD_CACHE: dict = {}
 _PCG_STATE: dict = {}       # seed -> (state, inc) of numpy.random.default_rng(seed) before its first draw
 
@@ -304,6 +321,9 @@ class Optic:
         if isinstance(distribution, str):
             if distribution == "random" and str(dev).startswith("cuda") and num_rays >= self.device_pupil_min_rays:
                 Px, Py = random_pupil_device(num_rays, seed, dev)   # the seed travels, not the grid
+            elif (distribution == "hexapolar" and str(dev).startswith("cuda")
+                  and 1 + 3 * int(num_rays) * (int(num_rays) + 1) >= self.device_pupil_min_rays):
+                Px, Py = hexapolar_pupil_device(num_rays, dev)      # index arithmetic on the device
             else:
                 Px, Py = pupil_points(distribution, num_rays, seed)
         else:

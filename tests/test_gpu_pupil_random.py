@@ -42,3 +42,43 @@ def test_optic_trace_random_distribution_uses_the_device_generator():
     want = spot.spot_stats(ref.spot_sums)["rms"].cpu().numpy()
     assert np.allclose(got, want, rtol=1e-12, atol=0)
     assert np.max(np.abs(rays.x.cpu().numpy() - ref.x.cpu().numpy())) <= 1e-12
+
+
+@pytest.mark.parametrize("rings", [0, 1, 6, 37, 600])
+def test_hexapolar_pupil_on_the_device_matches_numpy(rings):
+    """olrt_pupil_hexapolar_f64 against HexagonalDistribution.generate_points as the reference writes it with the NumPy
+    backend (optiland/distribution.py:200-220): same point count and order; radii and angles are linspace values (bit
+    for bit, checked through r = hypot and the ring structure), Px / Py within 2 ulp of r cos / r sin from libm."""
+    from optiland_pr_b200.optic import hexapolar_pupil_device
+    x = np.zeros([1])
+    y = np.zeros([1])
+    r = np.linspace(0, 1, rings + 1)
+    for i in range(rings):
+        num_theta = 6 * (i + 1)
+        theta = np.linspace(0, 2 * np.pi, num_theta + 1)[:-1]
+        x = np.concatenate([x, r[i + 1] * np.cos(theta)])
+        y = np.concatenate([y, r[i + 1] * np.sin(theta)])
+    Px, Py = hexapolar_pupil_device(rings, "cuda:0")
+    gx, gy = Px.cpu().numpy(), Py.cpu().numpy()
+    assert gx.shape == x.shape == (1 + 3 * rings * (rings + 1),)
+    # 2 ulp of the radius (cos / sin are within an ulp or two of libm's; near their zeros that is absolute, not relative)
+    tol = 2.0 * np.spacing(np.maximum(np.hypot(x, y), 1e-300))
+    assert np.all(np.abs(gx - x) <= tol) and np.all(np.abs(gy - y) <= tol)
+    if rings:
+        assert gx[0] == 0.0 and gy[0] == 0.0 and gx[1] == r[1] and gy[1] == 0.0      # theta = 0: exactly (r, 0)
+        assert gx[-6 * rings] == 1.0                                                  # the last ring has radius exactly 1
+
+
+def test_optic_trace_with_a_large_hexapolar_grid_uses_the_device_generator():
+    """Optic.trace(..., num_rays=rings, "hexapolar") with >= 4096 points: same rays as with the host-built grid."""
+    from optiland_pr_b200 import backend as be, samples
+    from optiland_pr_b200.optic import pupil_points
+    be.set_device("cuda:0")
+    be.set_precision("float64")
+    lens = samples.CookeTriplet()
+    lens.surface_group.record = "none"
+    a = lens.trace([0.0], [0.7], 0.55, 40, "hexapolar")                  # 4921 points: device generator
+    px, py = pupil_points("hexapolar", 40)
+    b = lens.trace([0.0], [0.7], 0.55, distribution=(px, py))            # the host's NumPy grid
+    assert a.x.numel() == b.x.numel() == 4921
+    assert float((a.x - b.x).abs().max()) <= 1e-12 and float((a.opd - b.opd).abs().max()) <= 1e-11
