@@ -371,6 +371,14 @@ int olrt_pupil_random_f64(const uint64_t state[2] /*host*/, const uint64_t inc[2
  * linspace(0, 1, num_rings + 1)[i] and angles linspace(0, 2 pi, 6 i + 1)[:-1]; radii and angles are NumPy's bit for bit,
  * Px, Py within an ulp or two (cos / sin).  Px, Py: [1 + 3 num_rings (num_rings + 1)] doubles (device).        */
 int olrt_pupil_hexapolar_f64(int32_t num_rings, double* Px, double* Py, void* stream);
+/* Uniform pupil distribution generated on the device: UniformDistribution.generate_points (optiland/distribution.py:
+ * 174-185) -- x = linspace(-1, 1, num_points), the num_points x num_points grid masked to x^2 + y^2 <= 1, rows (y)
+ * first; NumPy's values and mask bit for bit. Two passes, because the number of kept points is data:
+ *   row_count != NULL (row_offset NULL): writes the number of kept points of every row, [num_points] int64 (device);
+ *   row_offset != NULL (row_count NULL): [num_points] int64 (device), the exclusive prefix sum of those counts, which
+ *     the caller forms (it also needs their total to size Px, Py): writes the points.                           */
+int olrt_pupil_uniform_f64(int64_t num_points, const int64_t* row_offset, int64_t* row_count, double* Px, double* Py,
+                           void* stream);
 
 /* OPD / wavefront epilogue: per ray, the optical path from the image surface back to the
  * reference sphere, the launch-plane tilt correction and the OPD in waves relative to the chief ray --

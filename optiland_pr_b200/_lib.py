@@ -104,7 +104,7 @@ EXPORTS = [
     "olrt_generate_rays_f64", "olrt_generate_rays_f32",
     "olrt_trace_pupil_f64", "olrt_trace_pupil_f32",
     "olrt_opd_epilogue_f64", "olrt_opd_epilogue_f32",
-    "olrt_upload_pupil", "olrt_pupil_random_f64", "olrt_pupil_hexapolar_f64",
+    "olrt_upload_pupil", "olrt_pupil_random_f64", "olrt_pupil_hexapolar_f64", "olrt_pupil_uniform_f64",
 ]
 
 _lib = None
@@ -165,6 +165,8 @@ def load():
     lib.olrt_pupil_random_f64.argtypes = [C.POINTER(C.c_uint64 * 2), C.POINTER(C.c_uint64 * 2), C.c_int64, v, v, v, v]
     lib.olrt_pupil_hexapolar_f64.restype = C.c_int
     lib.olrt_pupil_hexapolar_f64.argtypes = [C.c_int32, v, v, v]
+    lib.olrt_pupil_uniform_f64.restype = C.c_int
+    lib.olrt_pupil_uniform_f64.argtypes = [C.c_int64, v, v, v, v, v]
     lib.olrt_selftest_math_f64.restype = C.c_int
     lib.olrt_selftest_math_f64.argtypes = [v, v, v, v, C.c_int64, v]
     if lib.olrt_version() != OLRT_ABI_VERSION:

@@ -508,6 +508,59 @@ extern "C" int olrt_pupil_hexapolar_f64(int32_t num_rings, double* Px, double* P
   return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
 }
 
+// UniformDistribution.generate_points (optiland/distribution.py:174-185): x = linspace(-1, 1, n), the n x n grid
+// (row j holds y = x[j]), masked to x^2 + y^2 <= 1, rows first. Pass 1 counts the kept points of every row, the caller
+// turns the counts into row offsets (an exclusive prefix sum), pass 2 writes the points. NumPy's linspace is
+// arange * (delta / div) + start with the last element set to the stop value; x ** 2 is x * x.
+__device__ __forceinline__ double uniform_coord(long long i, long long n, double step) {
+  return (i == n - 1 && n > 1) ? 1.0 : __dadd_rn(__dmul_rn((double)i, step), -1.0);
+}
+__global__ void __launch_bounds__(256) pupil_uniform_kernel(long long n, double step, const long long* row_offset,
+                                                            long long* row_count, double* Px, double* Py) {
+  // one warp per row: count (row_count != null) or write at row_offset[j] in column order
+  const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  for (long long j = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; j < n; j += warps) {
+    const double y = uniform_coord(j, n, step);
+    const double yy = __dmul_rn(y, y);
+    long long kept = 0;
+    for (long long i0 = 0; i0 < n; i0 += 32) {
+      const long long i = i0 + lane;
+      bool in = false;
+      double x = 0.0;
+      if (i < n) {
+        x = uniform_coord(i, n, step);
+        in = __dadd_rn(__dmul_rn(x, x), yy) <= 1.0;
+      }
+      const unsigned m = __ballot_sync(0xffffffffu, in);
+      if (row_count == nullptr && in) {
+        const long long pos = row_offset[j] + kept + __popc(m & ((1u << lane) - 1u));
+        Px[pos] = x; Py[pos] = y;
+      }
+      kept += __popc(m);
+    }
+    if (row_count != nullptr && lane == 0) row_count[j] = kept;
+  }
+}
+
+extern "C" int olrt_pupil_uniform_f64(int64_t num_points, const int64_t* row_offset, int64_t* row_count, double* Px,
+                                      double* Py, void* stream) {
+  if (num_points < 0) return OLRT_E_ARG;
+  if ((row_count == nullptr) == (row_offset == nullptr)) return OLRT_E_ARG;   // exactly one of the two passes
+  if (row_count == nullptr && (!Px || !Py)) return OLRT_E_ARG;
+  if (num_points == 0) return OLRT_OK;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  long long grid = (long long)sms * 8;
+  const long long need = (num_points + 7) / 8;     // 8 warps (rows) per CTA
+  if (grid > need) grid = need;
+  const double step = (num_points > 1) ? 2.0 / (double)(num_points - 1) : 0.0;
+  pupil_uniform_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(
+      (long long)num_points, step, (const long long*)row_offset, (long long*)row_count, Px, Py);
+  return cudaGetLastError() == cudaSuccess ? OLRT_OK : OLRT_E_LAUNCH;
+}
+
 // ---------------------------------------------------------------------------------------------
 // OPD / wavefront epilogue (kernel in trace_strict.cu)
 // ---------------------------------------------------------------------------------------------

@@ -101,6 +101,32 @@ def hexapolar_pupil_device(num_rings: int, device=None):
     return Px, Py
 
 
+def uniform_pupil_device(num_points: int, device=None):
+    """UniformDistribution.generate_points(num_points) (optiland/distribution.py:174-185) generated ON THE DEVICE by
+    `olrt_pupil_uniform_f64`: a counting pass, a prefix sum of the row counts (the one 8-byte read-back: the number of
+    kept points sizes the arrays), a writing pass. NumPy's values and mask bit for bit."""
+    from . import _lib as L
+    lib = L.load()
+    dev = torch.device(device if device is not None else be.get_device())
+    n = int(num_points)
+    if n == 0:
+        e = torch.empty(0, dtype=torch.float64, device=dev)
+        return e, e.clone()
+    counts = torch.empty(n, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream(dev).cuda_stream
+        L.check(lib.olrt_pupil_uniform_f64(n, 0, counts.data_ptr(), 0, 0, st), "olrt_pupil_uniform_f64")
+        ends = torch.cumsum(counts, 0)
+        total = int(ends[-1].item())
+        offsets = (ends - counts).contiguous()
+        Px = torch.empty(total, dtype=torch.float64, device=dev)
+        Py = torch.empty(total, dtype=torch.float64, device=dev)
+        if total > 0:
+            L.check(lib.olrt_pupil_uniform_f64(n, offsets.data_ptr(), 0, Px.data_ptr(), Py.data_ptr(), st),
+                    "olrt_pupil_uniform_f64")
+    return Px, Py
+
+
 _FIELD_CACHE: dict = {}
 _PCG_STATE: dict = {}       # seed -> (state, inc) of numpy.random.default_rng(seed) before its first draw
 
@@ -324,6 +350,9 @@ class Optic:
             elif (distribution == "hexapolar" and str(dev).startswith("cuda")
                   and 1 + 3 * int(num_rays) * (int(num_rays) + 1) >= self.device_pupil_min_rays):
                 Px, Py = hexapolar_pupil_device(num_rays, dev)      # index arithmetic on the device
+            elif (distribution == "uniform" and str(dev).startswith("cuda")
+                  and int(num_rays) * int(num_rays) >= self.device_pupil_min_rays):
+                Px, Py = uniform_pupil_device(num_rays, dev)
             else:
                 Px, Py = pupil_points(distribution, num_rays, seed)
         else:

@@ -82,3 +82,32 @@ def test_optic_trace_with_a_large_hexapolar_grid_uses_the_device_generator():
     b = lens.trace([0.0], [0.7], 0.55, distribution=(px, py))            # the host's NumPy grid
     assert a.x.numel() == b.x.numel() == 4921
     assert float((a.x - b.x).abs().max()) <= 1e-12 and float((a.opd - b.opd).abs().max()) <= 1e-11
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 7, 64, 1001])
+def test_uniform_pupil_on_the_device_matches_numpy_bit_for_bit(n):
+    """olrt_pupil_uniform_f64 against UniformDistribution.generate_points as the reference writes it with the NumPy
+    backend (optiland/distribution.py:174-185): the same points, in the same order, bit for bit (mask included)."""
+    from optiland_pr_b200.optic import uniform_pupil_device
+    x = np.linspace(-1, 1, n)
+    x, y = np.meshgrid(x, x)
+    r2 = x**2 + y**2
+    wx, wy = x[r2 <= 1], y[r2 <= 1]
+    Px, Py = uniform_pupil_device(n, "cuda:0")
+    assert np.array_equal(Px.cpu().numpy(), wx) and np.array_equal(Py.cpu().numpy(), wy)
+
+
+def test_optic_trace_with_a_large_uniform_grid_uses_the_device_generator():
+    """Optic.trace(..., num_rays=n, "uniform") with n*n >= 4096: the same rays as with the host-built grid, bit for
+    bit (the pupil points are identical, so the launch is the same launch)."""
+    from optiland_pr_b200 import backend as be, samples
+    from optiland_pr_b200.optic import pupil_points
+    be.set_device("cuda:0")
+    be.set_precision("float64")
+    lens = samples.CookeTriplet()
+    lens.surface_group.record = "none"
+    a = lens.trace([0.0], [0.7], 0.55, 80, "uniform")                    # 80 x 80 grid: device generator
+    px, py = pupil_points("uniform", 80)
+    b = lens.trace([0.0], [0.7], 0.55, distribution=(px, py))            # the host's NumPy grid
+    assert a.x.numel() == b.x.numel() == px.size
+    assert bool((a.x == b.x).all()) and bool((a.opd == b.opd).all())
