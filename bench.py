@@ -808,7 +808,7 @@ def bench_other_configs(torch, timed, args, fp64_peak):
                    "+ spot.rms_spot_sq + loss.backward() + Adam step"}
     except Exception as e:   # an extra leg must never take the bench line down
         out["c4_cooke_merit_adam_step_one_node"] = {"error": repr(e)[:200]}
-    # ---- C3, second half: refractive Zernike (fringe, 36 terms) + odd-asphere plate, tilts about three axes,
+    # ---- C3, second half: refractive Zernike (fringe, 12 terms) + odd-asphere plate, tilts about three axes,
     # elliptical / rectangular / boolean apertures, TIR at the rim -- the interpreter kernel again, 64 M rays
     lens = samples.FreeformPlate()
     wl = lens.primary_wavelength
@@ -832,8 +832,9 @@ def bench_other_configs(torch, timed, args, fp64_peak):
         "dead_rays": int(torch.isnan(o[0]).sum()), "clipped_rays": int((o[6] == 0).sum()),
         "frac_fp64_fma_peak": flz * nz / (ms * 1e-3) / 1e12 / fp64_peak, "flops_per_ray": flz,
         "flop_model": flops.flop_model(packed, res.nr_iters),
-        "kernel": "trace_fwd_kernel (interpreter: Zernike fringe freeform, odd asphere, aperture programs, tilted "
-                  "frames, TIR at the rim)"}
+        "kernel": "trace_fwd_kernel (interpreter: Zernike fringe freeform through the merged tables, odd asphere, "
+                  "aperture programs, tilted frames, TIR at the rim); flops_per_ray counts the reference's "
+                  "term-by-term algorithm"}
     del o, ins, rays
     torch.cuda.empty_cache()
     return out

@@ -126,6 +126,11 @@ enum {
                                 (frame x = y = +0.0), refracting and has no aperture -- an ordinary lens. The kernels
                                 then run variants that carry only those surface bodies (smaller code, fewer registers).
                                 Verified on the device: a wrong hint sets OLRT_ST_BAD_HINT and traces nothing */
+#define OLRT_HINT_ZERNIKE 4   /* the ops table holds a Zernike surface: tolerance-mode launches (OLRT_FWD_FAST) run the
+                                interpreter variant that merges each such surface's terms into one polynomial in rho^2
+                                per (|m|, cos / sin) pair, per CTA in shared memory. A hint in the plain
+                                sense: without it the same surfaces run the term loop (slower, same tolerance); with
+                                it and no Zernike surface nothing changes */
 
 typedef struct olrt_sys {
   int32_t n_surfaces;     /* intersected surfaces */

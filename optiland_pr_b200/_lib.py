@@ -36,6 +36,7 @@ AP_OR, AP_AND, AP_DIFF = 10, 11, 12
 ST_ZERNIKE_RANGE, ST_WAVELENGTH, ST_BAD_HINT, ST_CHEBYSHEV_RANGE, ST_TIMEOUT = 1, 2, 4, 8, 16
 HINT_FASTKINDS = 1
 HINT_ORDINARY = 2          # centred, refracting, aperture-free surfaces only (include/olrt.h)
+HINT_ZERNIKE = 4           # a Zernike surface: the tolerance-mode interpreter variant with merged term tables
 FWD_CKPT_BLOCKED = 4     # olrt_trace_fwd_* flag: `record` is the tile-blocked checkpoint buffer (include/olrt.h)
 BWD_CKPT_BLOCKED = 2     # olrt_trace_bwd_* flag: `record` is that buffer
 BWD_NO_FRAME_XY = 4      # olrt_trace_bwd_* flag: d loss / d (frame x, frame y) is not wanted (no decenter variable)

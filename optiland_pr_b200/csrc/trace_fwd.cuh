@@ -111,7 +111,18 @@ __device__ __forceinline__ void load_surface(SurfParams<R>& sp, const int32_t* s
   sp.ncoef = op[OLRT_OP_NCOEF];
   sp.aux = op[OLRT_OP_AUX];
   sp.nr_iters = op[OLRT_OP_NR_ITERS];
+  sp.ztab = nullptr;
+  sp.zlen = nullptr;
 }
+
+#ifdef OLRT_FX
+// the CTA's merged Zernike tables (tolerance build, main pass). Function-scope shared arrays: their addresses are
+// constants of the kernel, so nothing about them is carried in registers through the surface loop
+template <typename R>
+__device__ __forceinline__ R* zt_tab() { __shared__ R t[OLRT_ZT_SURF * OLRT_ZT_REALS]; return t; }
+__device__ __forceinline__ int* zt_len() { __shared__ int t[OLRT_ZT_SURF * OLRT_ZT_INTS]; return t; }
+__device__ __forceinline__ int* zt_slot() { __shared__ int t[OLRT_MAX_SURFACES]; return t; }   // table of a surface, or -1
+#endif
 
 // surface kinds: straight-line instantiations for the common cases, the interpreter for the rest
 enum { KIND_GENERIC = 0, KIND_PLANE = 1, KIND_CONIC = 2, KIND_EVEN = 3,
@@ -125,7 +136,11 @@ enum { KIND_GENERIC = 0, KIND_PLANE = 1, KIND_CONIC = 2, KIND_EVEN = 3,
        // renormalisation flags. The two square roots whose argument can be exactly zero ON the axis (rho of a Zernike
        // term, r of an odd asphere) keep their guard: their NaN could otherwise disappear behind the reference's own
        // `where(|f'| > 1e-14, ...)` select
-       KIND_GFAST = 5 };
+       KIND_GFAST = 5,
+       // tolerance build only: a KIND_GFAST Zernike surface whose terms are merged into the CTA's shared tables
+       // (trace_geom.cuh: zernike_merge / zernike_eval_merged) -- its own instantiation, so the other kinds' code and
+       // register allocation stay what they are without it
+       KIND_ZMERGED = 6 };
 
 __device__ __forceinline__ int surface_kind(const int32_t* op) {
   const int geom = op[OLRT_OP_GEOM], flags = op[OLRT_OP_FLAGS];
@@ -146,13 +161,15 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
                                              unsigned long long* resid, uint32_t& status,
                                              R& L0, R& M0, R& N0) {
   const int32_t* op = sp.op;
-  constexpr bool FRAMES = (KIND == KIND_GENERIC || KIND == KIND_POLY || KIND == KIND_GFAST);   // frame chain with rotations
+  constexpr bool FRAMES = (KIND == KIND_GENERIC || KIND == KIND_POLY || KIND == KIND_GFAST ||
+                           KIND == KIND_ZMERGED);   // frame chain with rotations
   const int geom = (KIND == KIND_PLANE) ? OLRT_GEOM_PLANE
                    : (KIND == KIND_CONIC) ? OLRT_GEOM_STANDARD
                    : (KIND == KIND_EVEN) ? OLRT_GEOM_EVEN_ASPHERE
-                   : (KIND == KIND_POLY) ? OLRT_GEOM_POLYNOMIAL : sp.geom;
+                   : (KIND == KIND_POLY) ? OLRT_GEOM_POLYNOMIAL
+                   : (KIND == KIND_ZMERGED) ? OLRT_GEOM_ZERNIKE : sp.geom;
   const int flags = (KIND == KIND_GENERIC) ? op[OLRT_OP_FLAGS]
-                    : (KIND == KIND_GFAST) ? (op[OLRT_OP_FLAGS] & (OLRT_F_ABSORB | OLRT_F_RADIUS_INF))
+                    : (KIND == KIND_GFAST || KIND == KIND_ZMERGED) ? (op[OLRT_OP_FLAGS] & (OLRT_F_ABSORB | OLRT_F_RADIUS_INF))
                                            : (op[OLRT_OP_FLAGS] & OLRT_F_ABSORB);
   const int nframes = FRAMES ? op[OLRT_OP_NFRAMES] : 1;
   const int fflags = FRAMES ? op[OLRT_OP_FRAMEFLAGS] : 0;
@@ -176,10 +193,12 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
         if (j < K) {
           if (KIND == KIND_EVEN) even_asphere_eval<R, true, MM>(sp, xi, yi, sag, zx, zy);
           else if (KIND == KIND_POLY) polynomial_eval<R, true, MM>(sp, xi, yi, sag, zx, zy);
+          else if (KIND == KIND_ZMERGED) zernike_eval_merged<R, true>(sp, xi, yi, sag, zx, zy, status);
           else nr_eval<R, true, MM>(sp, xi, yi, sag, zx, zy, status);
         } else {
           if (KIND == KIND_EVEN) even_asphere_eval<R, false, MM>(sp, xi, yi, sag, zx, zy);
           else if (KIND == KIND_POLY) polynomial_eval<R, false, MM>(sp, xi, yi, sag, zx, zy);
+          else if (KIND == KIND_ZMERGED) zernike_eval_merged<R, false>(sp, xi, yi, sag, zx, zy, status);
           else nr_eval<R, false, MM>(sp, xi, yi, sag, zx, zy, status);
         }
         const R f = sag - zi;
@@ -255,6 +274,7 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
     uint32_t st2 = 0;
     if (KIND == KIND_EVEN) even_asphere_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy);
     else if (KIND == KIND_POLY) polynomial_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy);
+    else if (KIND == KIND_ZMERGED) zernike_eval_merged<R, true>(sp, r.x, r.y, sag, zx, zy, st2);
     else nr_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy, st2);
     slopes_to_normal<R, MM>(zx, zy, nx, ny, nz);
   }
@@ -290,7 +310,7 @@ template <> __device__ __forceinline__ bool nonfinite<float>(float v) {
 }
 
 // all surfaces for one ray; stores the recorded surfaces on the way
-template <typename R, bool FIX>
+template <typename R, bool FIX, bool ZM = false>
 __device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r, const int32_t* s_ops,
                                           const R* presc, const R* s_der, const int* s_kind,
                                           const int* s_roff, unsigned long long* s_resid, int widx, R wl,
@@ -317,6 +337,15 @@ __device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r,
         case KIND_EVEN: surface_step<R, KIND_EVEN, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
         case KIND_POLY: surface_step<R, KIND_POLY, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
         case KIND_GFAST: surface_step<R, KIND_GFAST, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
+#ifdef OLRT_FX
+        case KIND_ZMERGED:
+          if (ZM) {
+            sp.ztab = zt_tab<R>() + zt_slot()[s] * OLRT_ZT_REALS;
+            sp.zlen = zt_len() + zt_slot()[s] * OLRT_ZT_INTS;
+            surface_step<R, KIND_ZMERGED, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0);
+          }
+          break;
+#endif
         default: surface_step<R, KIND_GENERIC, MM_GUARD>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
       }
     }
@@ -354,7 +383,10 @@ __device__ __forceinline__ void spot_add_one(const FwdParams<R>& P, int g, const
 // FIX = false: the main pass over every ray (tiles of blockDim rays, grid-stride).
 // FIX = true : the fix-up pass over the rays the main pass listed in P.fixup (fp64 only): IEEE
 //              division / square root everywhere, prescription read in place.
-template <typename R, bool FIX>
+// ZM (tolerance build, main pass): the variant that also carries the merged-table Zernike kind (OLRT_HINT_ZERNIKE) --
+//              a kernel of its own, so lenses without such a surface run exactly the code they ran before it existed
+//              (this kernel waits on instruction fetch: 3 % on the three-mirror system from the extra code alone).
+template <typename R, bool FIX, bool ZM = false>
 __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(const FwdParams<R> P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int S = P.n_surfaces, W = P.n_wavelengths;
@@ -395,6 +427,23 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
     s_roff[S] = off;
   }
   __syncthreads();
+#ifdef OLRT_FX
+  if (ZM) {   // merged tables for the first OLRT_ZT_SURF Zernike surfaces of the unguarded kind that fit them
+    if (threadIdx.x == 0) {
+      int used = 0;
+      for (int s = 0; s < S; ++s) {
+        const int32_t* op = s_ops + s * OLRT_OPS_STRIDE;
+        zt_slot()[s] = -1;
+        if (s_kind[s] == KIND_GFAST && op[OLRT_OP_GEOM] == OLRT_GEOM_ZERNIKE && used < OLRT_ZT_SURF &&
+            zernike_mergeable(s_ops + op[OLRT_OP_AUX], op[OLRT_OP_NCOEF])) {
+          zt_slot()[s] = used++;
+          s_kind[s] = KIND_ZMERGED;
+        }
+      }
+    }
+    __syncthreads();
+  }
+#endif
   const int n_resid = s_roff[S];
   for (int q = threadIdx.x; q < n_resid; q += blockDim.x) s_resid[q] = 0ull;
   __syncthreads();
@@ -415,6 +464,15 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
         cur_p = p;
         __syncthreads();
         if (threadIdx.x < S) derive_surface<R>(s_ops, s_presc, s_der, threadIdx.x, W, P.wavelengths, P.four_pi);
+#ifdef OLRT_FX
+        if (ZM && threadIdx.x < S && zt_slot()[threadIdx.x] >= 0) {
+          const int32_t* op = s_ops + threadIdx.x * OLRT_OPS_STRIDE;
+          const R* coef = s_presc + op[OLRT_OP_DOFF] + op[OLRT_OP_NFRAMES] * OLRT_FRAME_REALS + OLRT_GEOM_REALS + 3 * W;
+          const int zs = zt_slot()[threadIdx.x];
+          zernike_merge<R>(s_ops + op[OLRT_OP_AUX], coef, op[OLRT_OP_NCOEF], zt_tab<R>() + zs * OLRT_ZT_REALS,
+                           zt_len() + zs * OLRT_ZT_INTS);
+        }
+#endif
         __syncthreads();
       }
     }
@@ -453,7 +511,7 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
     }
 
     R L0 = r.L, M0 = r.M, N0 = r.N;
-    trace_ray<R, FIX>(P, r, s_ops, presc, s_der, s_kind, s_roff, s_resid, widx, wl, valid, idx, status,
+    trace_ray<R, FIX, ZM>(P, r, s_ops, presc, s_der, s_kind, s_roff, s_resid, widx, wl, valid, idx, status,
                       L0, M0, N0);
     if (valid) {
       if (P.out[0] != nullptr) {

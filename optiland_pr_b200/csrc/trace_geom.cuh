@@ -19,7 +19,57 @@ struct SurfParams {      // one surface's view of the prescription staged in sha
   const R* aper;         // aperture leaf parameters
   int geom, ncoef, aux;
   int nr_iters;          // K_s: Newton updates at this surface (ops word 6, or the ray's group in group mode)
+  const R* ztab;         // tolerance build: this Zernike surface's merged tables in shared memory (zernike_merge), or null
+  const int* zlen;
 };
+
+// Merged Zernike tables (tolerance build only). Every term is rho^|m| Q(u) {cos, sin}(|m| phi) with u = rho^2 and
+// Q a polynomial in u, so the terms of one (|m|, cos / sin) pair add up to ONE polynomial in u:
+//   Z = sum_m A_m(u) Re(w^m) + B_m(u) Im(w^m),   w = xn + i yn.
+// One table per Zernike surface, built once per CTA and prescription: [set][m][cos / sin][power of u], set 0 weighted
+// with c (the reference's slopes, zernike.py:176-232, leave the norm constant out), set 1 with c N (the sag).
+#define OLRT_ZT_SURF 2   /* Zernike surfaces with a table (the rest keep the term loop) */
+#define OLRT_ZT_M 9      /* |m| = 0 .. 8 */
+#define OLRT_ZT_L 8      /* (n - |m|) / 2 <= 7 */
+#define OLRT_ZT_REALS (2 * OLRT_ZT_M * 2 * OLRT_ZT_L)
+#define OLRT_ZT_INTS (OLRT_ZT_M + 2)   /* table length per m, largest m, 1 when both sets coincide */
+
+// can this surface's term list be merged? (ops words only: the same answer for every prescription of a batch)
+__device__ __forceinline__ bool zernike_mergeable(const int32_t* nm, int nterms) {
+  for (int j = 0; j < nterms; ++j) {
+    const int n = nm[2 * j], m = nm[2 * j + 1];
+    const int ma = (m < 0) ? -m : m;
+    if (ma >= OLRT_ZT_M || ((n - ma) >> 1) >= OLRT_ZT_L) return false;
+  }
+  return nterms > 0;
+}
+
+// one thread builds one surface's tables (terms in list order: the same bits in every CTA of every launch)
+template <typename R>
+__device__ __forceinline__ void zernike_merge(const int32_t* nm, const R* tc, int nterms, R* tab, int* len) {
+  for (int q = 0; q < OLRT_ZT_REALS; ++q) tab[q] = R(0);
+  for (int q = 0; q < OLRT_ZT_INTS; ++q) len[q] = 0;
+  int same = 1, mmax = 0;
+  for (int j = 0; j < nterms; ++j) {
+    const int n = nm[2 * j], m = nm[2 * j + 1];
+    const int ma = (m < 0) ? -m : m;
+    const int d = (n - ma) >> 1;
+    const R c = tc[0], cN = tc[1];
+    const R* rc = tc + 2;          // radial coefficients of rho^n, rho^(n-2), ..., rho^|m|
+    tc += 2 + d + 1;
+    if (c != cN) same = 0;
+    R* t0 = tab + ((0 * OLRT_ZT_M + ma) * 2 + (m < 0 ? 1 : 0)) * OLRT_ZT_L;
+    R* t1 = tab + ((1 * OLRT_ZT_M + ma) * 2 + (m < 0 ? 1 : 0)) * OLRT_ZT_L;
+    for (int k = 0; k <= d; ++k) {
+      t0[d - k] = t0[d - k] + c * rc[k];
+      t1[d - k] = t1[d - k] + cN * rc[k];
+    }
+    if (d + 1 > len[ma]) len[ma] = d + 1;
+    if (ma > mmax) mmax = ma;
+  }
+  len[OLRT_ZT_M] = mmax;
+  len[OLRT_ZT_M + 1] = same;
+}
 
 template <typename R>
 __device__ __forceinline__ R ipow(R b, int e) {  // b**e by repeated multiplication, e >= 0
@@ -149,6 +199,69 @@ __device__ __forceinline__ void polynomial_eval(const SurfParams<R>& sp, R x, R 
 //                                                   zernike/base.py:42-299
 // Per term in coef: c, c*N, rc_0 .. rc_{smax-1}  (radial coefficients, highest power first),
 // (n, m) pairs in ops at sp.aux. cos/sin(m phi) by angle-addition from cos phi = x/rho.
+// The merged form (tolerance build). With rho Z_rho = sum_m (m A_m + 2u A_m') Re(w^m) + (m B_m + 2u B_m') Im(w^m) and
+// Z_phi = sum_m m (B_m Re(w^m) - A_m Im(w^m)) the reference's slopes -- INCLUDING its two regularised quotients
+// 1 / (rho + 1e-14) and 1 / (rho^2 + 1e-14), zernike.py:196-205 -- are
+//   zx += (xn rho Z_rho / (rho (rho + eps)) - yn Z_phi / (u + eps)) / Rn,   zy += (yn ... + xn ...) / Rn:
+// no angle, no per-term control flow, one Horner step per table entry.
+template <typename R, bool WANT_SLOPES>
+__device__ __forceinline__ void zernike_eval_merged(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy,
+                                                    uint32_t& status) {
+  const R Rn = sp.norm_radius;
+  const Recip<R, MM_FAST> rRn(Rn);
+  const R xn = rRn.div(x), yn = rRn.div(y);
+  if (r_abs(xn) > R(1) || r_abs(yn) > R(1)) status |= OLRT_ST_ZERNIKE_RANGE;  // zernike.py:234-246
+  const R u = xn * xn + yn * yn;
+  const R r2 = x * x + y * y;
+  R denom;
+  conic_sag_denom<R, MM_FAST>(r2, sp.cc, sag, denom);
+  if (WANT_SLOPES) { const Recip<R, MM_FAST> rd(denom); zx = rd.div(x); zy = rd.div(y); }
+  const int* zl = sp.zlen;
+  const int mmax = zl[OLRT_ZT_M];
+  const bool same = zl[OLRT_ZT_M + 1] != 0;
+  const R two_u = u + u;
+  R C = R(1), S = R(0), Z = R(0), RZ = R(0), ZP = R(0);
+  const R* ta = sp.ztab;
+  for (int m = 0; m <= mmax; ++m, ta += 2 * OLRT_ZT_L) {
+    const int L = zl[m];
+    const R* tb = ta + OLRT_ZT_L;
+    R A = R(0), Ad = R(0), B = R(0), Bd = R(0);
+    for (int j = L - 1; j >= 0; --j) {
+      if (WANT_SLOPES) { Ad = fma(Ad, u, A); Bd = fma(Bd, u, B); }
+      A = fma(A, u, ta[j]);
+      B = fma(B, u, tb[j]);
+    }
+    R An = A, Bn = B;
+    if (!same) {
+      const R* na = ta + OLRT_ZT_M * 2 * OLRT_ZT_L;
+      const R* nb = na + OLRT_ZT_L;
+      An = R(0); Bn = R(0);
+      for (int j = L - 1; j >= 0; --j) { An = fma(An, u, na[j]); Bn = fma(Bn, u, nb[j]); }
+    }
+    Z = fma(An, C, fma(Bn, S, Z));
+    if (WANT_SLOPES) {
+      const R fm = R(m);
+      RZ = fma(fma(fm, A, two_u * Ad), C, fma(fma(fm, B, two_u * Bd), S, RZ));
+      ZP = fma(fm, fma(B, C, -(A * S)), ZP);
+    }
+    const R Cn = fma(C, xn, -(S * yn));
+    S = fma(S, xn, C * yn);
+    C = Cn;
+  }
+  sag = sag + Z;
+  if (WANT_SLOPES) {
+    const R eps = R(1e-14);
+    const R rho = m_sqrt<MM_GUARD>(u);   // exactly 0 on the axis: guarded like the term loop's
+    R q1 = R(0);
+    if (rho > R(0)) q1 = m_div<MM_FAST>(R(1), rho * (rho + eps));
+    const R q2 = m_div<MM_FAST>(R(1), u + eps);
+    const R iRn = rRn.div(R(1));
+    const R a = (RZ * q1) * iRn, b = (ZP * q2) * iRn;
+    zx = zx + fma(xn, a, -(yn * b));
+    zy = zy + fma(yn, a, xn * b);
+  }
+}
+
 template <typename R, bool WANT_SLOPES, int MM>
 __device__ __forceinline__ void zernike_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy,
                                              uint32_t& status) {

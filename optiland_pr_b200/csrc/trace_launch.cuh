@@ -159,11 +159,18 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
     if (grid > n_tiles) grid = n_tiles;
     trace_fk_kernel<R><<<(unsigned)grid, block, smem, stream>>>(P);
   } else {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_fwd_kernel<R, false>, block, smem);
+    void (*kern)(const FwdParams<R>) = trace_fwd_kernel<R, false>;
+#ifdef OLRT_FX
+    if (sys->kernel_hint & OLRT_HINT_ZERNIKE) {   // the variant with the merged Zernike tables (a kernel of its own)
+      kern = trace_fwd_kernel<R, false, true>;
+      if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    }
+#endif
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);
     if (per_sm < 1) per_sm = 1;
     long long grid = (long long)sm_count() * per_sm;
     if (grid > n_tiles) grid = n_tiles;
-    trace_fwd_kernel<R, false><<<(unsigned)grid, block, smem, stream>>>(P);
+    kern<<<(unsigned)grid, block, smem, stream>>>(P);
   }
   if (cudaGetLastError() != cudaSuccess) return OLRT_E_LAUNCH;
   if (sizeof(R) == 8 && P.fixup != nullptr) {

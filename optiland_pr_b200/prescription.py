@@ -255,6 +255,8 @@ class PackedSystem:
             s.kernel_hint |= cs_ << 8
         if own_rows and n_presc == self.presc.shape[0] and self.ordinary():
             s.kernel_hint |= L.HINT_ORDINARY
+        if any(lay.geom == L.GEOM_ZERNIKE for lay in self.layouts):
+            s.kernel_hint |= L.HINT_ZERNIKE
         s.n_surfaces = self.n_surfaces
         s.n_wavelengths = len(self.wavelengths)
         s.n_presc = n_presc

@@ -75,3 +75,12 @@ def test_prescription_tensor_chains_tilts_polynomial_and_zernike_leaves():
     n_, m_, off, norm = pk2.layouts[0].zernike_terms[4]
     (row2[off] * 7.0 + row2[off + 1] * 11.0).backward()
     assert abs(float(cz[4].grad) - (7.0 + 11.0 * norm)) < 1e-12 and norm != 1.0
+
+
+@pytest.mark.parametrize("name, want", [("FreeformPlate", True), ("CookeTriplet", False), ("ThreeMirrorAnastigmat", False)])
+def test_zernike_hint_is_announced_for_zernike_lenses_only(name, want):
+    """olrt_sys.kernel_hint & OLRT_HINT_ZERNIKE (include/olrt.h): the ops table lives on the device, so the host says
+    whether the launch should run the interpreter variant with the merged Zernike tables."""
+    lens = getattr(samples, name)()
+    packed = pack_surface_group(lens.surface_group.surfaces, [0.55])
+    assert bool(packed.make_sys().kernel_hint & L.HINT_ZERNIKE) is want
