@@ -39,6 +39,10 @@ struct FwdParams {
   double* spot;              // fused spot epilogue: [n_groups][OLRT_SPOT_SUMS] sums, group = field (pupil mode)
   const double* spot_shift;  // [n_groups][2] shift the sums are taken about (required with spot)
   int spot_flags;            // OLRT_SPOT_*
+  // trace_fwd_kernel's dynamic shared memory: byte offsets of the derived constants, the ops table and the residual
+  // words behind the prescription row (set by the launcher: the kernel is short of registers and would otherwise
+  // recompute them from presc_stride / n_surfaces / ops_len wherever it needs one of the pointers)
+  int off_der, off_ops, off_resid;
 };
 
 // derived per-surface constants in shared memory: c1, R2, twoR, rR2, then u[W], u2[W], alpha[W]
@@ -391,12 +395,9 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int S = P.n_surfaces, W = P.n_wavelengths;
   R* s_presc = reinterpret_cast<R*>(smem_raw);
-  const int presc_pad = (P.presc_stride + 1) & ~1;
-  R* s_der = s_presc + presc_pad;
-  const int der_pad = (S * der_stride(W) + 1) & ~1;
-  int32_t* s_ops = reinterpret_cast<int32_t*>(s_der + der_pad);
-  const int ops_pad = (P.ops_len + 1) & ~1;
-  unsigned long long* s_resid = reinterpret_cast<unsigned long long*>(s_ops + ops_pad);
+  R* s_der = reinterpret_cast<R*>(smem_raw + P.off_der);
+  int32_t* s_ops = reinterpret_cast<int32_t*>(smem_raw + P.off_ops);
+  unsigned long long* s_resid = reinterpret_cast<unsigned long long*>(smem_raw + P.off_resid);
   __shared__ int s_roff[OLRT_MAX_SURFACES + 1];
   __shared__ int s_kind[OLRT_MAX_SURFACES];
 

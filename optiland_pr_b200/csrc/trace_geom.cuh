@@ -67,6 +67,7 @@ __device__ __forceinline__ void zernike_merge(const int32_t* nm, const R* tc, in
     if (d + 1 > len[ma]) len[ma] = d + 1;
     if (ma > mmax) mmax = ma;
   }
+  for (int q = 0; q <= mmax; ++q) if (len[q] < 1) len[q] = 1;   // the evaluator seeds its Horner pass with entry L - 1
   len[OLRT_ZT_M] = mmax;
   len[OLRT_ZT_M + 1] = same;
 }
@@ -110,6 +111,34 @@ __device__ __forceinline__ void odd_asphere_eval(const SurfParams<R>& sp, R x, R
   R denom;
   conic_sag_denom<R, MM>(r2, sp.cc, sag, denom);
   if (WANT_SLOPES) { const Recip<R, MM> rd(denom); zx = rd.div(x); zy = rd.div(y); }
+#ifdef OLRT_FX
+  // tolerance build: sum_i C_i r^(i+1) = r H(r) and the slope factor G(r) = sum_{i>=1} (i+1) C_i r^(i-1) by Horner;
+  // the C_0 term of the slopes, x C_0 / r, keeps the reference's non-finite filter (the only term that needs it)
+  if (MM == MM_FAST) {
+    const int nc = sp.ncoef;
+    if (nc > 0) {
+      R H = R(0), G = R(0), k = R(nc);
+#pragma unroll 1
+      for (int i = nc - 1; i >= 1; --i) {
+        const R Ci = sp.coef[i];
+        H = fma(H, r, Ci);
+        if (WANT_SLOPES) { G = fma(G, r, k * Ci); k = k - R(1); }
+      }
+      const R C0 = sp.coef[0];
+      H = fma(H, r, C0);
+      sag = fma(H, r, sag);
+      if (WANT_SLOPES) {
+        const R rp = m_div<MM>(R(1), r);
+        R xt = (x * C0) * rp, yt = (y * C0) * rp;
+        if (!isfinite(xt)) xt = R(0);
+        if (!isfinite(yt)) yt = R(0);
+        zx = fma(x, G, zx + xt);
+        zy = fma(y, G, zy + yt);
+      }
+    }
+    return;
+  }
+#endif
   R pw = R(1);  // r**i
   for (int i = 0; i < sp.ncoef; ++i) {
     const R Ci = sp.coef[i];
@@ -223,10 +252,11 @@ __device__ __forceinline__ void zernike_eval_merged(const SurfParams<R>& sp, R x
   R C = R(1), S = R(0), Z = R(0), RZ = R(0), ZP = R(0);
   const R* ta = sp.ztab;
   for (int m = 0; m <= mmax; ++m, ta += 2 * OLRT_ZT_L) {
-    const int L = zl[m];
+    const int L = zl[m];      // >= 1 (an |m| without terms holds one zero)
     const R* tb = ta + OLRT_ZT_L;
-    R A = R(0), Ad = R(0), B = R(0), Bd = R(0);
-    for (int j = L - 1; j >= 0; --j) {
+    R A = ta[L - 1], B = tb[L - 1], Ad = R(0), Bd = R(0);
+#pragma unroll 1            // 0 .. 3 trips as a rule: an unrolled body with its remainder code costs more than it saves
+    for (int j = L - 2; j >= 0; --j) {
       if (WANT_SLOPES) { Ad = fma(Ad, u, A); Bd = fma(Bd, u, B); }
       A = fma(A, u, ta[j]);
       B = fma(B, u, tb[j]);
@@ -235,8 +265,9 @@ __device__ __forceinline__ void zernike_eval_merged(const SurfParams<R>& sp, R x
     if (!same) {
       const R* na = ta + OLRT_ZT_M * 2 * OLRT_ZT_L;
       const R* nb = na + OLRT_ZT_L;
-      An = R(0); Bn = R(0);
-      for (int j = L - 1; j >= 0; --j) { An = fma(An, u, na[j]); Bn = fma(Bn, u, nb[j]); }
+      An = na[L - 1]; Bn = nb[L - 1];
+#pragma unroll 1
+      for (int j = L - 2; j >= 0; --j) { An = fma(An, u, na[j]); Bn = fma(Bn, u, nb[j]); }
     }
     Z = fma(An, C, fma(Bn, S, Z));
     if (WANT_SLOPES) {

@@ -93,6 +93,9 @@ int launch_fwd(const olrt_sys* sys, const R* presc, const int32_t* ops,
                       (size_t)((sys->n_surfaces * der_stride(sys->n_wavelengths) + 1) & ~1) * sizeof(R) +
                       (size_t)((sys->ops_len + 1) & ~1) * sizeof(int32_t) +
                       (size_t)resid_words * sizeof(unsigned long long);
+  P.off_der = ((sys->presc_stride + 1) & ~1) * (int)sizeof(R);
+  P.off_ops = P.off_der + ((sys->n_surfaces * der_stride(sys->n_wavelengths) + 1) & ~1) * (int)sizeof(R);
+  P.off_resid = P.off_ops + ((sys->ops_len + 1) & ~1) * (int)sizeof(int32_t);
   if (smem > 200 * 1024) return OLRT_E_LIMIT;
   if (smem > 48 * 1024) {
     cudaFuncSetAttribute(trace_fwd_kernel<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
