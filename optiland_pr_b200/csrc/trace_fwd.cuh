@@ -196,12 +196,12 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
         R sag, zx = R(0), zy = R(0);
         if (j < K) {
           if (KIND == KIND_EVEN) even_asphere_eval<R, true, MM>(sp, xi, yi, sag, zx, zy);
-          else if (KIND == KIND_POLY) polynomial_eval<R, true, MM>(sp, xi, yi, sag, zx, zy);
+          else if (KIND == KIND_POLY) polynomial_eval<R, true, MM, true>(sp, xi, yi, sag, zx, zy);
           else if (KIND == KIND_ZMERGED) zernike_eval_merged<R, true>(sp, xi, yi, sag, zx, zy, status);
           else nr_eval<R, true, MM>(sp, xi, yi, sag, zx, zy, status);
         } else {
           if (KIND == KIND_EVEN) even_asphere_eval<R, false, MM>(sp, xi, yi, sag, zx, zy);
-          else if (KIND == KIND_POLY) polynomial_eval<R, false, MM>(sp, xi, yi, sag, zx, zy);
+          else if (KIND == KIND_POLY) polynomial_eval<R, false, MM, true>(sp, xi, yi, sag, zx, zy);
           else if (KIND == KIND_ZMERGED) zernike_eval_merged<R, false>(sp, xi, yi, sag, zx, zy, status);
           else nr_eval<R, false, MM>(sp, xi, yi, sag, zx, zy, status);
         }
@@ -277,7 +277,7 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
     R sag, zx, zy;
     uint32_t st2 = 0;
     if (KIND == KIND_EVEN) even_asphere_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy);
-    else if (KIND == KIND_POLY) polynomial_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy);
+    else if (KIND == KIND_POLY) polynomial_eval<R, true, MM, true>(sp, r.x, r.y, sag, zx, zy);
     else if (KIND == KIND_ZMERGED) zernike_eval_merged<R, true>(sp, r.x, r.y, sag, zx, zy, st2);
     else nr_eval<R, true, MM>(sp, r.x, r.y, sag, zx, zy, st2);
     slopes_to_normal<R, MM>(zx, zy, nx, ny, nz);

@@ -159,7 +159,9 @@ __device__ __forceinline__ void odd_asphere_eval(const SurfParams<R>& sp, R x, R
 
 // PolynomialGeometry.sag / _surface_normal  geometries/polynomial.py:93-142
 // coef = C[i][j] row-major, I = ncoef/J rows, J = aux columns
-template <typename R, bool WANT_SLOPES, int MM>
+// STRAIGHT44 (the polynomial surface kind's own call sites only: the interpreter waits on instruction fetch, and the
+// same lines inlined into every generic body cost the Zernike plate 2.5 %): the 4 x 4 table without loop control
+template <typename R, bool WANT_SLOPES, int MM, bool STRAIGHT44 = false>
 __device__ __forceinline__ void polynomial_eval(const SurfParams<R>& sp, R x, R y, R& sag, R& zx, R& zy) {
   const R r2 = x * x + y * y;
   R denom;
@@ -172,7 +174,21 @@ __device__ __forceinline__ void polynomial_eval(const SurfParams<R>& sp, R x, R 
   {
     const int J = sp.aux;
     R P = R(0), Px = R(0), Py = R(0);
-    if (J > 0) {
+    if (STRAIGHT44 && J == 4 && sp.ncoef == 16) {   // the 4 x 4 table (x^3 y^3 freeforms): no loop control at all
+      const R* c = sp.coef;
+#pragma unroll
+      for (int i = 3; i >= 0; --i) {
+        R A = c[4 * i + 3], Ad;
+        Ad = A;               A = fma(A, y, c[4 * i + 2]);
+        Ad = fma(Ad, y, A);   A = fma(A, y, c[4 * i + 1]);
+        Ad = fma(Ad, y, A);   A = fma(A, y, c[4 * i]);
+        if (i == 3) { P = A; Py = Ad; }
+        else {
+          if (WANT_SLOPES) { Px = fma(Px, x, P); Py = fma(Py, x, Ad); }
+          P = fma(P, x, A);
+        }
+      }
+    } else if (J > 0) {
       for (int b = sp.ncoef - J; b >= 0; b -= J) {  // rows i = I-1 .. 0
         const R* c = sp.coef + b;
         R A, Ad = R(0);
