@@ -169,10 +169,14 @@ const char* olrt_build_info(void);
  *             non-finite; a second kernel re-traces exactly those with IEEE div.rn / sqrt.rn, so the
  *             stored result is the IEEE one for every ray. fixup[0] = how many rays were re-traced.
  *  flags      OLRT_FWD_*                                                                  */
-#define OLRT_FWD_FAST 1 /* tolerance mode (<= 1e-10 relative, identical masks; not bit-faithful): FMA contraction, and for
-                           lenses of planes / conics / even aspheres the reduced-algebra kernel (csrc/trace_fx.cuh) */
-#define OLRT_FWD_REPLAY 2 /* with OLRT_FWD_FAST (fp32: always): keep replaying the reference's operation order, only with
-                             FMA contraction -- the round-1 "fast" path, kept for A/B measurements */
+#define OLRT_FWD_FAST 1 /* tolerance mode (<= 1e-10 relative, identical masks; not bit-faithful): FMA contraction, for
+                           lenses of planes / conics / even aspheres the reduced-algebra kernel (csrc/trace_fx.cuh), in
+                           the interpreter kernel Horner forms of the polynomial, odd-asphere and (OLRT_HINT_ZERNIKE)
+                           Zernike sums */
+#define OLRT_FWD_REPLAY 2 /* with OLRT_FWD_FAST (fp32: always): not the reduced-algebra kernel but the straight-line /
+                             interpreter kernels of the tolerance build, which replay the reference's operation order
+                             for planes, conics and even aspheres with FMA contraction -- the round-1 "fast" path, kept
+                             for A/B measurements */
 
 int olrt_trace_fwd_f64(const olrt_sys* sys /*host*/, const double* presc, const int32_t* ops,
                        int64_t n_rays, const double* const in[8] /*host array of device ptrs*/,

@@ -110,7 +110,9 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
              per-iteration residual maxima there and this call does NOT read them back (no host sync);
              the caller checks them later with `slice_true_iters` (slices of one batch, optic.py).
     fast:    tolerance mode (<= 1e-10 relative to the reference, identical masks) instead of bit-faithful;
-             `replay` keeps the reference's operation order even then (A/B measurements; fp32 too).
+             `replay` runs the tolerance build's straight-line / interpreter kernels instead of the reduced-algebra
+             kernel even then (the reference's operation order for planes / conics / even aspheres, with FMA
+             contraction; A/B measurements, fp32 too).
     own_rows: `presc` holds `packed`'s own row (same frame x / y entries), so the OLRT_HINT_ORDINARY judged on
              `packed` applies (default: only when `presc` is None).
     nr_floor: this call traces one SLICE of a larger batch: never lower the Newton trip counts below the
