@@ -345,6 +345,28 @@ def check_surface(surf) -> None:
             raise NotEligible(f"propagation model {type(pm).__name__} is not implemented")
 
 
+def media_row(packed: PackedSystem, surfaces, wavelength: float, skip: int = 0):
+    """The prescription row of the same surfaces at ANOTHER wavelength, for a single-wavelength pack: only the media
+    block (n_pre, n_post, k_pre per surface, optiland/materials/base.py:73-119) depends on it, so the row is a copy
+    with those three entries re-evaluated -- a fraction of a full pack. Returns None when the ops table would differ
+    (a medium that absorbs at one wavelength and not at the other): pack again then."""
+    if len(packed.wavelengths) != 1:
+        return None
+    real = [s for s in list(surfaces)[skip:] if type(s).__name__ != "ObjectSurface"]
+    if len(real) != len(packed.layouts):
+        return None
+    w = float(wavelength)
+    row = packed.presc[0].copy()
+    for k, (lay, surf) in enumerate(zip(packed.layouts, real)):
+        n_pre = _material_value(surf.material_pre, "n", w)
+        n_post = _material_value(surf.material_post, "n", w)
+        k_pre = _material_value(surf.material_pre, "k", w)
+        if (k_pre > 0) != bool(int(packed.ops[k * L.OPS_STRIDE + L.OP_FLAGS]) & L.F_ABSORB):
+            return None
+        row[lay.media], row[lay.media + 1], row[lay.media + 2] = n_pre, n_post, k_pre
+    return row
+
+
 def pack_surface_group(surfaces, wavelengths, record="all", skip: int = 0) -> PackedSystem:
     """Pack `surfaces[skip:]` for the distinct `wavelengths` (micrometres)."""
     wavelengths = [float(w) for w in wavelengths]

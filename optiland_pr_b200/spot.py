@@ -147,16 +147,21 @@ class SpotDiagram:
         keep = sg.record
         sg.record = "none"
         try:
-            packs = [sg.pack([w]) for w in self.wavelengths]
+            # ONE pack; the rows of the other wavelengths differ from it in the media entries only
+            from .prescription import media_row
+            p0 = sg.pack([self.wavelengths[0]])
+            rows = [p0.presc[0]] + [media_row(p0, sg.surfaces, w) for w in self.wavelengths[1:]]
+            if any(r is None for r in rows):       # a medium absorbs at some wavelengths only: full packs
+                packs = [p0] + [sg.pack([w]) for w in self.wavelengths[1:]]
+                rows = [p.presc[0] for p in packs] if all(np.array_equal(p.ops, p0.ops) for p in packs) else None
         finally:
             sg.record = keep
-        p0 = packs[0]
         fused = bool(sg.fast_math and p0.fastkinds() and optic._EPL is not None and optic._EPD is not None
-                     and all(np.array_equal(p.ops, p0.ops) for p in packs))
+                     and rows is not None)
         s2 = None
         if fused:
             try:
-                s2, cen = self._fused_sums(optic, p0, packs, Px, Py, Hx, Hy, dev, dt, nf, nw)
+                s2, cen = self._fused_sums(optic, p0, np.stack(rows), Px, Py, Hx, Hy, dev, dt, nf, nw)
             except NotImplementedError:
                 # a (field, wavelength) group needs more Newton updates than the fused launch holds -- e.g. a ray
                 # that misses an asphere makes the reference run max_iter of them (newton_raphson.py:137-149):
@@ -176,19 +181,22 @@ class SpotDiagram:
             cen = torch.stack([st["cx"], st["cy"]], dim=1).reshape(nw, nf, 2)[self.ref_index]
             shift2 = cen.unsqueeze(0).expand(nw, nf, 2).reshape(-1, 2).contiguous()
             s2 = spot_sums(x, y, i, nw * nf, npup, shift2, True)
-        self._centroid = cen
+        # a handful of numbers per (field, wavelength) pair: ONE read-back, the arithmetic on the host (each tiny
+        # device op would cost more in launch overhead than the whole lot)
+        s2 = s2.cpu()
+        self._centroid = cen.cpu()
         self._rms = torch.sqrt((s2[:, 3] + s2[:, 4]) / s2[:, 0]).reshape(nw, nf)
         self._geo = torch.sqrt(s2[:, 5]).reshape(nw, nf)
         self.count = s2[:, 0].reshape(nw, nf)
 
-    def _fused_sums(self, optic, p0, packs, Px, Py, Hx, Hy, dev, dt, nf, nw):
+    def _fused_sums(self, optic, p0, rows, Px, Py, Hx, Hy, dev, dt, nf, nw):
         """Both passes through trace.fused_spot_groups; returns (second-pass sums [nw * nf, 10], centroids [nf, 2])."""
         import numpy as np
 
         from .trace import fused_spot_groups
         ft = optic._field_table(Hx, Hy).to(dev)
         gen_kw = dict(EPD=optic._EPD, EPL=optic._EPL, wavelength=float(self.wavelengths[0]), dtype=dt, **ft.kwargs())
-        rows = np.concatenate([p.presc for p in packs], axis=0)
+        rows = np.array(rows, dtype=np.float64)      # (a copy: the scaling below must not reach p0's own row)
         # the kernels form the Beer-Lambert exponent 4 pi k / lambda (homogeneous.py:49) with the launch's ONE
         # wavelength (the first row's): rows of other wavelengths carry k lambda_0 / lambda_row instead of k
         for r, w in enumerate(self.wavelengths):
@@ -207,9 +215,9 @@ class SpotDiagram:
         if nw * nf * npup * 64 <= self.keep_bytes_limit:
             keep = torch.empty((8, nw * nf * npup), dtype=dt, device=dev)
         s1, kg = fused_spot_groups(p0, presc, Px, Py, ft.fxy_d, gen_kw, k0, valid_only=True, keep=keep)
-        st = spot_stats(s1)
-        cen = torch.stack([st["cx"], st["cy"]], dim=1).reshape(nw, nf, 2)[self.ref_index]     # [nf, 2]
-        shift2 = cen.unsqueeze(0).expand(nw, nf, 2).reshape(-1, 2).contiguous()
+        st = spot_stats(s1.cpu())     # (the launch above has been waited for: its Newton reports were read)
+        cen = torch.stack([st["cx"], st["cy"]], dim=1).reshape(nw, nf, 2)[self.ref_index]     # [nf, 2], host
+        shift2 = cen.unsqueeze(0).expand(nw, nf, 2).reshape(-1, 2).contiguous().to(dev)
         if keep is not None and getattr(keep, "valid", False):
             s2 = spot_sums(keep[0], keep[1], keep[6], nw * nf, npup, shift2, True)
             self.passes = 1

@@ -84,3 +84,21 @@ def test_zernike_hint_is_announced_for_zernike_lenses_only(name, want):
     lens = getattr(samples, name)()
     packed = pack_surface_group(lens.surface_group.surfaces, [0.55])
     assert bool(packed.make_sys().kernel_hint & L.HINT_ZERNIKE) is want
+
+
+@pytest.mark.parametrize("name", ["CookeTriplet", "EvenAsphereDoubleGauss", "FreeformPlate"])
+def test_media_row_equals_a_full_pack_at_the_other_wavelength(name):
+    """prescription.media_row: the row of the same surfaces at another wavelength is the packed row with the media
+    entries (n_pre, n_post, k_pre, materials/base.py:73-119) re-evaluated -- bit for bit what a full pack gives."""
+    from optiland_pr_b200.prescription import media_row
+    lens = getattr(samples, name)()
+    sf = lens.surface_group.surfaces
+    p0 = pack_surface_group(sf, [0.55], record="none")
+    for w in (0.4861, 0.6563):
+        full = pack_surface_group(sf, [w], record="none")
+        row = media_row(p0, sf, w)
+        if not np.array_equal(full.ops, p0.ops):      # a medium absorbing at one wavelength only
+            assert row is None
+        else:
+            assert row is not None and np.array_equal(row, full.presc[0])
+    assert media_row(pack_surface_group(sf, [0.5, 0.6], record="none"), sf, 0.55) is None   # single-wavelength packs only
