@@ -84,7 +84,7 @@ def test_optic_trace_with_a_large_hexapolar_grid_uses_the_device_generator():
     assert float((a.x - b.x).abs().max()) <= 1e-12 and float((a.opd - b.opd).abs().max()) <= 1e-11
 
 
-@pytest.mark.parametrize("n", [0, 1, 2, 7, 64, 1001])
+@pytest.mark.parametrize("n", [0, 1, 2, 7, 64, 1001, 2049])
 def test_uniform_pupil_on_the_device_matches_numpy_bit_for_bit(n):
     """olrt_pupil_uniform_f64 against UniformDistribution.generate_points as the reference writes it with the NumPy
     backend (optiland/distribution.py:174-185): the same points, in the same order, bit for bit (mask included)."""
