@@ -537,7 +537,13 @@ class Optic:
         for attempt in range(8):
             if per_field:
                 packed.set_nr_iters(kf.max(axis=0).tolist())   # the slot layout covers every field's counts
-                group_k = torch.from_numpy(kf).to(dev)
+                gk_cache = sg.__dict__.setdefault("_group_k_device", {})    # the counts rarely change between calls
+                gk_key = (kf.tobytes(), kf.shape, str(dev))
+                group_k = gk_cache.get(gk_key)
+                if group_k is None:
+                    if len(gk_cache) > 16:
+                        gk_cache.clear()
+                    group_k = gk_cache[gk_key] = torch.from_numpy(kf.copy()).to(dev)
                 resid = torch.zeros((nf, packed.n_surfaces, L.GROUP_RESID), dtype=torch.int64, device=dev)
             else:
                 group_k = None

@@ -36,6 +36,13 @@ class TraceResult:
     ckpt: torch.Tensor | None = None  # tile-blocked checkpoints (fused_trace(ckpt=True)), else None
 
 
+def _row_ptrs(t: torch.Tensor):
+    """Device addresses of the 8 rows of a contiguous [8, n] tensor (plain integer arithmetic: indexing the tensor
+    eight times costs ~25 us of host time per launch)."""
+    base, step = t.data_ptr(), t.stride(0) * t.element_size()
+    return [base + q * step for q in range(8)]
+
+
 def _ptr(t) -> int:
     return 0 if t is None else t.data_ptr()
 
@@ -169,7 +176,7 @@ def fused_trace(packed: PackedSystem, rays_in, opd_in=None, *, presc: torch.Tens
     fixup = _fixup_workspace(n, device) if dtype == torch.float64 else None
     fn = lib.olrt_trace_fwd_f64 if dtype == torch.float64 else lib.olrt_trace_fwd_f32
     in_arr = L.PtrArray8(*[_ptr(t) for t in ins])
-    out_arr = L.PtrArray8(*[out[q].data_ptr() for q in range(8)])
+    out_arr = L.PtrArray8(*_row_ptrs(out))
     # dir0 rows may be slices of a larger buffer: the kernel writes [3][n] with stride n, so a sliced
     # destination needs its own contiguous scratch (copied back below)
     dir0_tmp = None
@@ -284,7 +291,7 @@ def fused_trace_pupil(packed: PackedSystem, Px: torch.Tensor, Py: torch.Tensor, 
     if out is not None:
         if out.dtype != dtype or tuple(out.shape) != (8, n_total) or not out.is_contiguous():
             raise ValueError("out must be a contiguous [8, n_presc * n_fields * n_pupil] tensor of the trace dtype")
-        out_arr = C.byref(L.PtrArray8(*[out[q].data_ptr() for q in range(8)]))
+        out_arr = C.byref(L.PtrArray8(*_row_ptrs(out)))
     fn = lib.olrt_trace_pupil_f64 if dtype == torch.float64 else lib.olrt_trace_pupil_f32
     with torch.cuda.device(device):
         rc = fn(C.byref(sys_), presc_d.data_ptr(), ops_d.data_ptr(), C.byref(pu), out_arr, _ptr(dir0),
