@@ -146,10 +146,51 @@ template <int MM> __device__ __forceinline__ float div_R2(float a, const ConicCo
 // form: scaling by 2 and 4 is exact in binary floating point, so b' = b/2, d' = d/4,
 // sqrt(d') = sqrt(d)/2 and (-b' +- sqrt d')/a are the SAME bits with fewer multiplications.
 // ---------------------------------------------------------------------------
-template <typename R, int MM>
-__device__ __forceinline__ R conic_distance(const RayState<R>& r, const ConicConst<R>& cc, bool radius_inf) {
+// ---------------------------------------------------------------------------
+// Decision margins of the interpreter's tolerance build (G = true; everything below is a no-op otherwise and for
+// fp32). Its arithmetic differs from the strict build's by rounding (FMA contraction, Horner sums), so a DECISION --
+// the sign of a radicand, an aperture comparison, a root choice, one of the reference's 1e-14 switches -- could fall
+// the other way for a ray that sits on the threshold. Each decision folds the high word of its relative distance to
+// the threshold into a running minimum in the INTEGER pipe (exponent and top 20 mantissa bits: a monotone proxy of
+// log2); a ray whose minimum ends below OLRT_GM_HI (2^-36) is listed for the strict build's re-trace like a
+// non-finite one. Same scheme as the reduced-algebra kernel's (trace_fx.cuh, FxMath::g_*).
+// ---------------------------------------------------------------------------
+#define OLRT_GM_HI 0x3DB00000   /* high word of 2^-36 */
+template <bool G> struct Margin {
+  // |d| > 2^-36 |b| ?   (d = lhs - rhs of a comparison, b = its scale)
+  static __device__ __forceinline__ void rel(int& g, double d, double b) {
+    // (the difference is clamped before the bias is added: a scale of exactly 0 -- r_min = 0 -- must not wrap around)
+    if (G) g = min(g, min((__double2hiint(d) & 0x7fffffff) - (__double2hiint(b) & 0x7fffffff), 0x3fffffff) +
+                          ((36 << 20) + OLRT_GM_HI));
+  }
+  // |v| > 2^-36 ?   (v is O(1) by construction: a radicand of unit vectors, a cosine)
+  static __device__ __forceinline__ void unit(int& g, double v) {
+    if (G) g = min(g, __double2hiint(v) & 0x7fffffff);
+  }
+  // v > 2^-36 ?   (negative: listed as well -- the strict build decides what a negative radicand means)
+  static __device__ __forceinline__ void pos(int& g, double v) {
+    if (G) g = min(g, __double2hiint(v));
+  }
+  // | |v| - 1e-14 | > 2^-36 * 1e-14 ?  near one of the reference's `abs(v) > 1e-14` switches (hi(1e-14) = 0x3D06849B)
+  static __device__ __forceinline__ void sw14(int& g, double v) {
+    if (G) {
+      const double d = fabs(v) - 1e-14;
+      g = min(g, (__double2hiint(d) & 0x7fffffff) - 0x3D06849B + ((36 << 20) + OLRT_GM_HI));
+    }
+  }
+  static __device__ __forceinline__ void rel(int&, float, float) {}
+  static __device__ __forceinline__ void unit(int&, float) {}
+  static __device__ __forceinline__ void pos(int&, float) {}
+  static __device__ __forceinline__ void sw14(int&, float) {}
+};
+
+template <typename R, int MM, bool G = false>
+__device__ __forceinline__ R conic_distance(const RayState<R>& r, const ConicConst<R>& cc, bool radius_inf, int* guard = nullptr) {
+  int g_ = 0x7fffffff;
   if (radius_inf) {  // standard.py:100-103
     const R Ns = (r_abs(r.N) > R(1e-14)) ? r.N : R(1e-14);
+    Margin<G>::sw14(g_, r.N);
+    if (G) *guard = min(*guard, g_);
     return m_div<MM>(-r.z, Ns);
   }
   const R radius = cc.radius, k = cc.k;
@@ -192,6 +233,12 @@ __device__ __forceinline__ R conic_distance(const RayState<R>& r, const ConicCon
   const R zz2 = r.z + t2 * r.N;
   R t = (r_abs(z1) <= r_abs(zz2)) ? t1 : t2;
   if (a == R(0)) t = m_div<MM>(-c, R(2) * hb);
+  if (G) {   // hit or miss (d against the b^2 it is the small difference of), which root, the a == 0 branch
+    Margin<G>::rel(g_, d, hb * hb);
+    Margin<G>::rel(g_, r_abs(z1) - r_abs(zz2), z1);
+    if (a != R(0)) Margin<G>::unit(g_, a);   // (exactly 0 -- an axis-parallel ray on a paraboloid -- is 0 in both builds)
+    *guard = min(*guard, g_);
+  }
   return t;
 }
 
@@ -237,20 +284,28 @@ __device__ __forceinline__ void align_normal(R& nx, R& ny, R& nz, R& dot) {
   dot = r_abs(dot);
 }
 
-template <typename R, int MM>
-__device__ __forceinline__ void refract(RayState<R>& r, R nx, R ny, R nz, R u, R u2) {
+template <typename R, int MM, bool G = false>
+__device__ __forceinline__ void refract(RayState<R>& r, R nx, R ny, R nz, R u, R u2, int* guard = nullptr) {
   const R L0 = r.L, M0 = r.M, N0 = r.N;
   R dot = L0 * nx + M0 * ny + N0 * nz;
   align_normal(nx, ny, nz, dot);
-  const R root = m_sqrt<MM>(R(1) - u2 * (R(1) - dot * dot));  // NaN => TIR
+  const R rad = R(1) - u2 * (R(1) - dot * dot);
+  if (G) {   // which side of the normal (real_rays.py:529), refracted or totally reflected
+    int g_ = *guard;
+    Margin<G>::unit(g_, dot);
+    Margin<G>::pos(g_, rad);
+    *guard = g_;
+  }
+  const R root = m_sqrt<MM>(rad);  // NaN => TIR
   r.L = u * L0 + nx * root - (u * nx) * dot;
   r.M = u * M0 + ny * root - (u * ny) * dot;
   r.N = u * N0 + nz * root - (u * nz) * dot;
 }
 
-template <typename R>
-__device__ __forceinline__ void reflect(RayState<R>& r, R nx, R ny, R nz) {
+template <typename R, bool G = false>
+__device__ __forceinline__ void reflect(RayState<R>& r, R nx, R ny, R nz, int* guard = nullptr) {
   R dot = r.L * nx + r.M * ny + r.N * nz;
+  if (G) { int g_ = *guard; Margin<G>::unit(g_, dot); *guard = g_; }
   align_normal(nx, ny, nz, dot);
   const R d2 = R(2) * dot;
   r.L = r.L - d2 * nx;
@@ -261,9 +316,11 @@ __device__ __forceinline__ void reflect(RayState<R>& r, R nx, R ny, R nz) {
 // ---------------------------------------------------------------------------
 // Aperture program (reverse Polish) on local x, y     physical_apertures/*.py
 // ---------------------------------------------------------------------------
-template <typename R>
-__device__ __forceinline__ bool aperture_contains(const int32_t* prog, int len, const R* p, R x, R y) {
+// G: every leaf comparison also reports its margin (any leaf on its edge lists the ray, whatever the tree does with it)
+template <typename R, bool G = false>
+__device__ __forceinline__ bool aperture_contains(const int32_t* prog, int len, const R* p, R x, R y, int* guard = nullptr) {
   uint32_t stack = 0;  // bit stack, top = bit 0
+  int g_ = 0x7fffffff;
   for (int q = 0; q < len; ++q) {
     const int tok = prog[q];
     bool v;
@@ -271,6 +328,7 @@ __device__ __forceinline__ bool aperture_contains(const int32_t* prog, int len, 
       case OLRT_AP_RADIAL: {  // radial.py:56-70
         const R r2 = x * x + y * y;
         v = (r2 <= p[0]) & (r2 >= p[1]);
+        Margin<G>::rel(g_, r2 - p[0], p[0]); Margin<G>::rel(g_, r2 - p[1], p[1]);
         p += 2;
         stack = (stack << 1) | (v ? 1u : 0u);
         break;
@@ -279,19 +337,27 @@ __device__ __forceinline__ bool aperture_contains(const int32_t* prog, int len, 
         const R dx = x - p[2], dy = y - p[3];
         const R r2 = dx * dx + dy * dy;
         v = (r2 <= p[0]) & (r2 >= p[1]);
+        Margin<G>::rel(g_, r2 - p[0], p[0]); Margin<G>::rel(g_, r2 - p[1], p[1]);
         p += 4;
         stack = (stack << 1) | (v ? 1u : 0u);
         break;
       }
       case OLRT_AP_ELLIPTICAL: {  // elliptical.py:42
         const R dx = x - p[2], dy = y - p[3];
-        v = ((dx * dx) / p[0] + (dy * dy) / p[1]) <= R(1);
+        const R e = (dx * dx) / p[0] + (dy * dy) / p[1];
+        v = e <= R(1);
+        Margin<G>::unit(g_, e - R(1));
         p += 4;
         stack = (stack << 1) | (v ? 1u : 0u);
         break;
       }
       case OLRT_AP_RECTANGULAR: {  // rectangular.py:42
         v = (p[0] <= x) & (x <= p[1]) & (p[2] <= y) & (y <= p[3]);
+        if (G) {   // the scale of an edge at 0 is the opening's width
+          const R wx = p[1] - p[0], wy = p[3] - p[2];
+          Margin<G>::rel(g_, x - p[0], wx); Margin<G>::rel(g_, x - p[1], wx);
+          Margin<G>::rel(g_, y - p[2], wy); Margin<G>::rel(g_, y - p[3], wy);
+        }
         p += 4;
         stack = (stack << 1) | (v ? 1u : 0u);
         break;
@@ -307,6 +373,7 @@ __device__ __forceinline__ bool aperture_contains(const int32_t* prog, int len, 
       }
     }
   }
+  if (G) *guard = min(*guard, g_);
   return (stack & 1u) != 0;
 }
 

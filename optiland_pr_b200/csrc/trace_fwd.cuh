@@ -163,8 +163,13 @@ template <typename R, int KIND, int MM>
 __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>& sp, int widx, int W,
                                              R wavelength, R four_pi, bool valid,
                                              unsigned long long* resid, uint32_t& status,
-                                             R& L0, R& M0, R& N0) {
+                                             R& L0, R& M0, R& N0, int& guard) {
   const int32_t* op = sp.op;
+#ifdef OLRT_FX   // tolerance build, main pass, fp64: decision margins (trace_common.cuh, Margin)
+  constexpr bool GD = (MM != MM_IEEE) && (sizeof(R) == 8);
+#else
+  constexpr bool GD = false;
+#endif
   constexpr bool FRAMES = (KIND == KIND_GENERIC || KIND == KIND_POLY || KIND == KIND_GFAST ||
                            KIND == KIND_ZMERGED);   // frame chain with rotations
   const int geom = (KIND == KIND_PLANE) ? OLRT_GEOM_PLANE
@@ -187,7 +192,7 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
   if (geom == OLRT_GEOM_PLANE) {
     t = m_div<MM>(-r.z, r.N);  // plane.py:61-77
   } else {
-    t = conic_distance<R, MM>(r, sp.cc, (flags & OLRT_F_RADIUS_INF) != 0);
+    t = conic_distance<R, MM, GD>(r, sp.cc, (flags & OLRT_F_RADIUS_INF) != 0, &guard);
     if (geom >= OLRT_GEOM_EVEN_ASPHERE) {  // newton_raphson.py:119-168
       const int K = sp.nr_iters;
       for (int j = 0; j <= K; ++j) {
@@ -223,6 +228,7 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
         const R fx = rn.div(-nx), fy = rn.div(-ny);
         const R df = fx * r.L + fy * r.M - r.N;
         const R dfs = (r_abs(df) > R(1e-14)) ? df : R(1e-14);
+        Margin<GD>::sw14(guard, nz); Margin<GD>::sw14(guard, df);   // newton_raphson.py:157, :162
         t = t - m_div<MM>(f, dfs);
       }
     }
@@ -247,7 +253,7 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
   // aperture.clip, physical_apertures/base.py:71-82 -> real_rays.py:132-139
   const int aoff = op[OLRT_OP_APER_OFF];
   if (aoff >= 0) {
-    const bool inside = aperture_contains(sp.ops + aoff, op[OLRT_OP_APER_LEN], sp.aper, r.x, r.y);
+    const bool inside = aperture_contains<R, GD>(sp.ops + aoff, op[OLRT_OP_APER_LEN], sp.aper, r.x, r.y, &guard);
     if (!inside) r.i = R(0);
   }
 
@@ -283,8 +289,8 @@ __device__ __forceinline__ void surface_step(RayState<R>& r, const SurfParams<R>
     slopes_to_normal<R, MM>(zx, zy, nx, ny, nz);
   }
   L0 = r.L; M0 = r.M; N0 = r.N;
-  if (op[OLRT_OP_INTERACT] == 1) reflect(r, nx, ny, nz);
-  else refract<R, MM>(r, nx, ny, nz, sp.u, sp.u2);
+  if (op[OLRT_OP_INTERACT] == 1) reflect<R, GD>(r, nx, ny, nz, &guard);
+  else refract<R, MM, GD>(r, nx, ny, nz, sp.u, sp.u2, &guard);
   if (coated) r.i = r.i * sp.aper[-1];   // BaseCoating.interact -> SimpleCoating.transmit / reflect
   }
 
@@ -318,7 +324,8 @@ template <typename R, bool FIX, bool ZM = false>
 __device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r, const int32_t* s_ops,
                                           const R* presc, const R* s_der, const int* s_kind,
                                           const int* s_roff, unsigned long long* s_resid, int widx, R wl,
-                                          bool valid, long long idx, uint32_t& status, R& L0, R& M0, R& N0) {
+                                          bool valid, long long idx, uint32_t& status, R& L0, R& M0, R& N0,
+                                          int& guard) {
   const int S = P.n_surfaces, W = P.n_wavelengths;
   const bool want_resid = (P.nr_resid != nullptr);
   for (int s = 0; s < S; ++s) {
@@ -333,24 +340,24 @@ __device__ __forceinline__ void trace_ray(const FwdParams<R>& P, RayState<R>& r,
                   ? P.group_resid + (g_ * S + s) * OLRT_GROUP_RESID : nullptr;
     }
     if (FIX) {
-      surface_step<R, KIND_GENERIC, MM_IEEE>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0);
+      surface_step<R, KIND_GENERIC, MM_IEEE>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0, guard);
     } else {
       switch (s_kind[s]) {  // warp-uniform
-        case KIND_PLANE: surface_step<R, KIND_PLANE, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
-        case KIND_CONIC: surface_step<R, KIND_CONIC, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
-        case KIND_EVEN: surface_step<R, KIND_EVEN, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
-        case KIND_POLY: surface_step<R, KIND_POLY, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
-        case KIND_GFAST: surface_step<R, KIND_GFAST, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
+        case KIND_PLANE: surface_step<R, KIND_PLANE, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0, guard); break;
+        case KIND_CONIC: surface_step<R, KIND_CONIC, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0, guard); break;
+        case KIND_EVEN: surface_step<R, KIND_EVEN, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0, guard); break;
+        case KIND_POLY: surface_step<R, KIND_POLY, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0, guard); break;
+        case KIND_GFAST: surface_step<R, KIND_GFAST, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0, guard); break;
 #ifdef OLRT_FX
         case KIND_ZMERGED:
           if (ZM) {
             sp.ztab = zt_tab<R>() + zt_slot()[s] * OLRT_ZT_REALS;
             sp.zlen = zt_len() + zt_slot()[s] * OLRT_ZT_INTS;
-            surface_step<R, KIND_ZMERGED, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0);
+            surface_step<R, KIND_ZMERGED, MM_FAST>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0, guard);
           }
           break;
 #endif
-        default: surface_step<R, KIND_GENERIC, MM_GUARD>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0); break;
+        default: surface_step<R, KIND_GENERIC, MM_GUARD>(r, sp, widx, W, wl, P.four_pi, valid, resid, status, L0, M0, N0, guard); break;
       }
     }
     const int slot = sp.op[OLRT_OP_RECORD];
@@ -512,8 +519,9 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
     }
 
     R L0 = r.L, M0 = r.M, N0 = r.N;
+    int guard = 0x7fffffff;   // smallest decision margin of this ray (tolerance build; untouched elsewhere)
     trace_ray<R, FIX, ZM>(P, r, s_ops, presc, s_der, s_kind, s_roff, s_resid, widx, wl, valid, idx, status,
-                      L0, M0, N0);
+                      L0, M0, N0, guard);
     if (valid) {
       if (P.out[0] != nullptr) {
         P.out[0][idx] = r.x; P.out[1][idx] = r.y; P.out[2][idx] = r.z;
@@ -529,7 +537,8 @@ __global__ void __launch_bounds__(256, OLRT_FWD_MIN_BLOCKS) trace_fwd_kernel(con
     if (!FIX && sizeof(R) == 8 && P.fixup != nullptr) {
       // anything non-finite (a real miss / TIR, or a value outside the fast path's domain): list the
       // ray for the IEEE re-trace. Warp-aggregated append.
-      const bool bad = valid && (nonfinite(r.x) | nonfinite(r.y) | nonfinite(r.z) | nonfinite(r.L) |
+      // ... or a decision taken within 2^-36 of its threshold (tolerance build): the strict build decides
+      const bool bad = valid && ((guard < OLRT_GM_HI) | nonfinite(r.x) | nonfinite(r.y) | nonfinite(r.z) | nonfinite(r.L) |
                                  nonfinite(r.M) | nonfinite(r.N) | nonfinite(r.opd) | nonfinite(r.i));
       const unsigned m = __ballot_sync(0xffffffffu, bad);
       if (m != 0u) {

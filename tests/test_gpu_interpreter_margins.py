@@ -1,0 +1,104 @@
+"""Decision margins of the interpreter kernel's tolerance build (csrc/trace_common.cuh: Margin): a ray
+whose aperture comparison, Snell radicand, discriminant, root choice or 1e-14 switch lies within 2^-36 (relative) of
+its threshold is listed for the strict build's re-trace, so its clip / TIR / miss DECISION is the reference's.
+Rays are put ON the thresholds here (aperture edges to the ulp, a sweep of adjacent doubles across the critical
+angle) on lenses that the reduced-algebra kernel does not take (odd asphere, tilted faces): masks and NaN patterns
+must equal the strict build's -- which is bit-identical to the reference on these closed-form lenses -- ray for ray."""
+import numpy as np
+import pytest
+import torch
+
+from optiland_pr_b200 import backend as be
+from optiland_pr_b200.apertures import (DifferenceAperture, EllipticalAperture, RadialAperture, RectangularAperture)
+from optiland_pr_b200.optic import Optic
+from optiland_pr_b200.prescription import pack_surface_group
+from optiland_pr_b200.trace import fused_trace
+
+pytestmark = pytest.mark.gpu
+INF = float("inf")
+
+
+def _singlet(first, second=None):
+    be.set_precision("float64")
+    lens = Optic("margins")
+    lens.add_surface(index=0, radius=INF, thickness=INF)
+    lens.add_surface(index=1, thickness=6.0, material="N-SF11", is_stop=True, **first)
+    lens.add_surface(index=2, thickness=20.0, **(second or dict(radius=INF)))
+    lens.add_surface(index=3)
+    lens.add_wavelength(0.55, is_primary=True)
+    return lens
+
+
+def _both(lens, rays_in):
+    packed = pack_surface_group(lens.surface_group.surfaces, [0.55])
+    assert not packed.fastkinds()                       # the interpreter kernel, not the reduced-algebra one
+    dev = [torch.tensor(np.ascontiguousarray(v), device="cuda") for v in rays_in]
+    fast = fused_trace(packed, dev, fast=True)
+    strict = fused_trace(packed, dev, fast=False)
+    return fast, strict
+
+
+def _edge_values(v):
+    """v itself, its neighbours to the ulp, v (1 +- 1e-13) (inside the band), v (1 +- 1e-9) (outside)."""
+    return [v, np.nextafter(v, 0), np.nextafter(v, 2 * v), v * (1 + 1e-13), v * (1 - 1e-13), v * (1 + 1e-9), v * (1 - 1e-9)]
+
+
+@pytest.mark.parametrize("kind", ["radial", "rectangular", "elliptical_minus_rectangle"])
+def test_rays_on_aperture_edges_take_the_strict_decision(kind):
+    if kind == "radial":
+        ap = RadialAperture(r_max=3.0, r_min=0.5)
+        xs = _edge_values(3.0) + _edge_values(0.5) + [1.0, 2.0, 4.0]
+        ys = [0.0] * len(xs)
+        on_edge = 5 + 5
+    elif kind == "rectangular":
+        ap = RectangularAperture(-2.0, 1.5, -1.0, 0.75)
+        xs = _edge_values(1.5) + [0.3] * 7 + [-v for v in _edge_values(2.0)] + [0.0, 5.0]
+        ys = [0.1] * 7 + _edge_values(0.75) + [0.2] * 7 + [0.0, 0.0]
+        on_edge = 5 + 5 + 5
+    else:
+        ap = DifferenceAperture(EllipticalAperture(4.0, 2.0), RectangularAperture(-1.0, 1.0, -0.5, 0.5))
+        xs = _edge_values(4.0) + [0.0] * 7 + _edge_values(1.0) + [2.0, 0.2]
+        ys = [0.0] * 7 + _edge_values(2.0) + [0.1] * 7 + [0.5, 0.1]
+        on_edge = 5 + 5 + 5
+    # an odd asphere keeps the lens off the reduced-algebra kernel; axis-parallel rays: the local x, y at the surface
+    # are the launch values exactly, in both builds
+    lens = _singlet(dict(radius=60.0, conic=0.0, surface_type="odd_asphere", coefficients=[0.0, 1.0e-4], aperture=ap))
+    n = len(xs)
+    rays_in = [np.array(xs), np.array(ys), np.full(n, -5.0), np.zeros(n), np.zeros(n), np.ones(n), np.ones(n), np.full(n, 0.55)]
+    fast, strict = _both(lens, rays_in)
+    a, b = fast.out.cpu().numpy(), strict.out.cpu().numpy()
+    assert np.array_equal(a[6] == 0, b[6] == 0) and (b[6] == 0).any() and (b[6] != 0).any()
+    assert np.array_equal(np.isnan(a), np.isnan(b))
+    assert np.max(np.abs(a - b) / np.maximum(np.abs(b), 1.0)) <= 1e-10
+    assert int(fast.fixups) >= on_edge          # the rays within 2^-36 of an edge went to the strict build
+    assert int(fast.fixups) < n                 # ... the others did not
+
+
+def test_adjacent_doubles_across_the_critical_angle():
+    """Glass-to-air exit face tilted by 0.3 rad: the ray direction is swept, one double at a time, across the angle
+    where the exit radicand 1 - u^2 (1 - dot^2) changes sign. 2001 adjacent values of M around the transition: the
+    tolerance build's TIR pattern is the strict build's, ray for ray."""
+    lens = _singlet(dict(radius=80.0), dict(radius=INF, rx=0.3))
+
+    def dead(M):
+        M = np.atleast_1d(np.asarray(M, dtype=np.float64))
+        n = M.size
+        rays_in = [np.zeros(n), np.zeros(n), np.full(n, -5.0), np.zeros(n), M, np.sqrt(1 - M * M), np.ones(n), np.full(n, 0.55)]
+        fast, strict = _both(lens, rays_in)
+        return np.isnan(fast.out[3].cpu().numpy()), np.isnan(strict.out[3].cpu().numpy()), fast
+
+    lo, hi = 0.0, 0.9                         # refracted at lo, totally reflected at hi
+    _, d, _ = dead([lo, hi])
+    assert not d[0] and d[1]
+    for _ in range(80):                        # bisection with the strict build down to adjacent doubles
+        mid = 0.5 * (lo + hi)
+        if mid == lo or mid == hi:
+            break
+        _, d, _ = dead([mid])
+        lo, hi = (lo, mid) if d[0] else (mid, hi)
+    bits = np.array([lo], dtype=np.float64).view(np.int64)[0]
+    M = (bits + np.arange(-1000, 1001, dtype=np.int64)).view(np.float64)
+    df, ds, fast = dead(M)
+    assert ds.any() and not ds.all()
+    assert np.array_equal(df, ds)
+    assert int(fast.fixups) == M.size         # every one of them is inside the band

@@ -128,9 +128,9 @@ def test_prescription_batch_rebuilds_the_tables():
 
 @pytest.mark.parametrize("ztype", ["fringe", "noll", "standard"])
 def test_plate_masks_equal_the_strict_build_on_two_million_rays(ztype):
-    """The interpreter's tolerance build has no guard bands (they exist in the reduced-algebra kernel of
-    the plane / conic / even-asphere lenses): its clip / TIR / miss decisions are taken by arithmetic that differs from
-    the strict build's by rounding. What that means in practice, on the C3 plate (annular, elliptical, rectangular and
+    """Bulk check next to tests/test_gpu_interpreter_margins.py (the interpreter's tolerance build
+    takes its clip / TIR / miss decisions with arithmetic that differs from the strict build's by rounding, and hands
+    a ray within 2^-36 of a threshold to the strict build). On the C3 plate (annular, elliptical, rectangular and
     boolean apertures, TIR on part of the pupil), both fields, 2 M random rays each: not one ray decides differently,
     and the values agree to 1e-10."""
     from optiland_pr_b200 import samples
