@@ -156,3 +156,49 @@ def test_chebyshev_range_error():
     fields = lens.get_field_coords()
     with pytest.raises(ValueError, match="Chebyshev input coordinates must be normalized"):
         lens.trace(np.array([fields[0][0]]), np.array([fields[0][1]]), 0.55, num_rays=6, distribution="hexapolar")
+
+
+def test_tolerance_mode_of_the_interpreter_with_dead_rays():
+    """The Cooke triplet with three tilted / decentred surfaces and an elliptical-minus-rectangular, a rectangular and
+    an annular aperture: closed-form surfaces (the oracle's bits in strict mode), but the interpreter kernel
+    (`trace_fwd_kernel`), whose tolerance build takes its decisions with contracted arithmetic and hands a ray within
+    2^-36 of a threshold to the strict build (trace_common.cuh: Margin). 200 k wild rays (misses, TIR, clipped rays):
+    NaN pattern and vignetting mask identical to the reference's for every ray at every surface, values to 1e-10
+    except ill-conditioned wild rays (as for the reduced-algebra kernel above)."""
+    from optiland_pr_b200.apertures import DifferenceAperture, EllipticalAperture, RectangularAperture
+    lens = samples.CookeTriplet()
+    s = lens.surface_group.surfaces
+    s[1].geometry.cs.rx, s[1].geometry.cs.x = 0.03, 0.2
+    s[3].geometry.cs.ry, s[3].geometry.cs.rz, s[3].geometry.cs.y = -0.02, 0.3, -0.15
+    s[5].geometry.cs.rx, s[5].geometry.cs.ry = -0.04, 0.025
+    s[2].aperture = DifferenceAperture(EllipticalAperture(8.0, 7.0, 0.1, -0.2), RectangularAperture(-0.5, 0.4, -0.3, 0.6))
+    s[4].aperture = RectangularAperture(-5.0, 5.5, -4.5, 5.0)
+    s[6].aperture = RadialAperture(r_max=7.5, r_min=0.25)
+    lens.surface_group.invalidate()
+    wl = lens.wavelengths
+    packed = pack_surface_group(lens.surface_group.surfaces, wl)
+    assert not packed.fastkinds()
+    n = 200_000
+    rays_in = _wild_rays(n, 13, wl)
+    ora = trace_np.trace_packed(packed, trace_np.Rays(*rays_in))
+    ref = np.array(ora["records"])
+    dead = np.isnan(ref[-1, 0])
+    assert 0.02 < dead.mean() < 0.98 and (ref[:, 6] == 0).any()
+    dev = [torch.tensor(rays_in[q], device="cuda") for q in range(8)]
+    strict = fused_trace(packed, dev).record.cpu().numpy()
+    for q, f in enumerate(FIELDS8):            # strict build: the oracle's bits (intensity through exp)
+        if f != "intensity":
+            assert np.array_equal(strict[:, q], ref[:, q], equal_nan=True), f
+    res = fused_trace(packed, dev, fast=True)
+    rec = res.record.cpu().numpy()
+    bad = (np.isnan(rec) != np.isnan(ref)).any(axis=(0, 1)) | ((rec[:, 6] == 0) != (ref[:, 6] == 0)).any(axis=0)
+    assert int(bad.sum()) == 0, int(bad.sum())
+    m = ~np.isnan(ref)
+    err = np.zeros_like(ref)
+    err[m] = np.abs(rec[m] - ref[m]) / np.maximum(np.abs(ref[m]), 1.0)
+    per_ray = err.max(axis=(0, 1))
+    print("interpreter, tolerance build: worst", per_ray.max(), "frac > 1e-10", (per_ray > 1e-10).mean(),
+          "re-traced", int(res.fixups), "dead", int(dead.sum()))
+    assert (per_ray > 1e-10).mean() <= 1e-4, (per_ray > 1e-10).sum()
+    assert per_ray.max() <= 1e-6, per_ray.max()
+    assert int(res.fixups) >= int(dead.sum())
