@@ -102,3 +102,27 @@ def test_adjacent_doubles_across_the_critical_angle():
     assert ds.any() and not ds.all()
     assert np.array_equal(df, ds)
     assert int(fast.fixups) == M.size         # every one of them is inside the band
+
+
+def test_paraxial_rays_on_a_paraboloid_take_the_strict_answer():
+    """k = -1: a = L^2 + M^2 of the quadratic is ~1e-11 for rays a few microradians off the axis and the reference's
+    (-b + sqrt d) / 2a cancels: its t depends on the evaluation order far beyond 1e-10 (nothing a tolerance could be
+    stated for). Rays with |a| < 2^-20 are re-traced by the strict build, so the tolerance mode returns the reference's
+    own values; rays exactly along the axis (a == 0 in both builds: the -c / 2b branch, standard.py:136-138) stay on
+    the fast path."""
+    lens = _singlet(dict(radius=40.0, conic=-1.0, dy=0.3), dict(radius=INF, rx=0.1))
+    n = 4096
+    rng = np.random.default_rng(1)
+    x, y = rng.uniform(-3, 3, n), rng.uniform(-3, 3, n)
+    L_ = rng.uniform(-4e-6, 4e-6, n)
+    M_ = rng.uniform(-4e-6, 4e-6, n)
+    L_[:64], M_[:64] = 0.0, 0.0
+    rays_in = [x, y, np.full(n, -5.0), L_, M_, np.sqrt(1 - L_ * L_ - M_ * M_), np.ones(n), np.full(n, 0.55)]
+    fast, strict = _both(lens, rays_in)
+    a, b = fast.out.cpu().numpy(), strict.out.cpu().numpy()
+    assert np.isfinite(b).all()
+    # (a ray so close to the axis that L^2 + M^2 is absorbed by N^2 - N^2 has a == 0 exactly like the axial ones)
+    assert n - 72 <= int(fast.fixups) <= n - 64
+    same = (a == b).all(axis=0)
+    assert int(same[64:].sum()) >= n - 72                              # re-traced: the strict build's bits
+    assert np.max(np.abs(a - b) / np.maximum(np.abs(b), 1.0)) <= 1e-12
