@@ -126,3 +126,33 @@ def test_paraxial_rays_on_a_paraboloid_take_the_strict_answer():
     same = (a == b).all(axis=0)
     assert int(same[64:].sum()) >= n - 72                              # re-traced: the strict build's bits
     assert np.max(np.abs(a - b) / np.maximum(np.abs(b), 1.0)) <= 1e-12
+
+
+@pytest.mark.parametrize("tilted", [False, True], ids=["reduced_algebra_kernel", "interpreter_kernel"])
+def test_tolerance_mode_near_the_axis_of_a_paraboloid(tilted):
+    """Both tolerance-mode kernels on a paraboloid (k = -1), ray bundles within 1e-7 ... 0.1 rad of its axis: the
+    leading coefficient a = L^2 + M^2 of the reference's quadratic goes to 0, its root cancels, and the reference's t
+    carries rounding noise of ~4e-16 / a relative -- which only its own operation order reproduces. Rays with
+    |a| < 2^-17 are re-traced by the strict build (band in trace_fx.cuh: fx_conic_t and trace_common.cuh:
+    conic_distance), so tolerance mode stays within 1e-10 of the reference there too. Without the band the
+    reduced-algebra kernel differs by 3.5 (relative) at 1e-7 rad and by 1e-9 at 1e-2 rad."""
+    first = dict(radius=40.0, conic=-1.0, dy=0.3) if tilted else dict(radius=40.0, conic=-1.0)
+    lens = _singlet(first, dict(radius=INF, rx=0.05) if tilted else None)
+    packed = pack_surface_group(lens.surface_group.surfaces, [0.55])
+    assert packed.fastkinds() != tilted
+    n = 8192
+    for amp in (1e-7, 1e-5, 1e-3, 1e-2, 0.1):
+        rng = np.random.default_rng(1)
+        x, y = rng.uniform(-3, 3, n), rng.uniform(-3, 3, n)
+        L_, M_ = rng.uniform(-amp, amp, n), rng.uniform(-amp, amp, n)
+        rays_in = [x, y, np.full(n, -5.0), L_, M_, np.sqrt(1 - L_ * L_ - M_ * M_), np.ones(n), np.full(n, 0.55)]
+        dev = [torch.tensor(v, device="cuda") for v in rays_in]
+        fast = fused_trace(packed, dev, fast=True)
+        a, b = fast.out.cpu().numpy(), fused_trace(packed, dev, fast=False).out.cpu().numpy()
+        assert np.isfinite(b).all()
+        assert np.max(np.abs(a - b) / np.maximum(np.abs(b), 1.0)) <= 1e-10, amp
+        if amp <= 1e-3:
+            # a <= 2e-6: every ray -- but for those whose L^2 + M^2 is absorbed to an exact 0 (the -c / 2b branch)
+            assert int(fast.fixups) >= n * 9 // 10, (amp, int(fast.fixups))
+        elif amp >= 0.1:
+            assert int(fast.fixups) < n // 100, (amp, int(fast.fixups))    # a handful that happen to be near the axis
