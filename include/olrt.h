@@ -170,9 +170,10 @@ const char* olrt_build_info(void);
  *             stored result is the IEEE one for every ray. fixup[0] = how many rays were re-traced.
  *             With OLRT_FWD_FAST the list also takes every ray one of whose DECISIONS (hit / miss, root choice,
  *             aperture comparison, side of the normal, total reflection, the reference's 1e-14 switches) was
- *             taken within 2^-36 (relative) of its threshold, and every ray whose conic quadratic has a leading
- *             coefficient |a| < 2^-17 (the reference's root cancels there): the re-trace is always the strict
- *             build's (the reference's operation order), so those rays carry the reference's decision / value.
+ *             taken within 2^-36 (relative) of its threshold, and every ray whose conic quadratic a t^2 + 2 b t + c
+ *             has |a| < 2^-20 |b| (the reference's root cancels there: a paraboloid near its axis, a "flat" surface
+ *             entered with a huge radius): the re-trace is always the strict build's (the reference's operation
+ *             order), so those rays carry the reference's decision / value.
  *  flags      OLRT_FWD_*                                                                  */
 #define OLRT_FWD_FAST 1 /* tolerance mode (<= 1e-10 relative, identical masks; not bit-faithful): FMA contraction, for
                            lenses of planes / conics / even aspheres the reduced-algebra kernel (csrc/trace_fx.cuh), in

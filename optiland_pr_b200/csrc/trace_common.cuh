@@ -236,11 +236,12 @@ __device__ __forceinline__ R conic_distance(const RayState<R>& r, const ConicCon
   if (G) {   // hit or miss (d against the b^2 it is the small difference of), which root, the a == 0 branch
     Margin<G>::rel(g_, d, hb * hb);
     Margin<G>::rel(g_, r_abs(z1) - r_abs(zz2), z1);
-    // a -> 0 (k = -1 and a ray nearly along the axis; an asymptotic direction of a hyperboloid): the reference's
-    // (-b + sqrt d) / 2a cancels, its t carries an error of ~ulp * b / a that depends on the evaluation order -- beyond
-    // 1e-10 once a < ~1e-5. Those rays take the strict build's (= the reference's) answer: band 2^-17 on a. Exactly
-    // 0 -- L = M = 0 on a paraboloid -- is 0 in both builds and takes the well-conditioned -c / 2b branch
-    if (a != R(0)) Margin<G>::rel(g_, a, R(524288.0));
+    // conditioning, not a decision: the reference's (-b + sqrt d) / 2a cancels when |b / a| is large -- a -> 0 (k = -1 and
+    // a ray nearly along the axis, an asymptotic direction of a hyperboloid) or a huge radius (b ~ N R) -- and its t
+    // then carries ~5 ulp(1) |b / a| of absolute noise that depends on the evaluation order. Rays with
+    // |a| < 2^-20 |b| take the strict build's (= the reference's) answer. a exactly 0 -- L = M = 0 on a paraboloid -- is
+    // 0 in both builds and takes the well-conditioned -c / 2b branch
+    if (a != R(0)) Margin<G>::rel(g_, a, hb * R(65536.0));
     *guard = min(*guard, g_);
   }
   return t;

@@ -79,9 +79,9 @@ template <> struct FxMath<double> {
   static __device__ __forceinline__ void g_abs12(int& g, double v) {
     g = min(g, (__double2hiint(v) & 0x7fffffff) + (OLRT_FX_GHI - 0x3D719799));
   }
-  // |v| > 2^-17 ?  (rescaled: hi(2^-17) = 0x3EE00000) -- the leading coefficient of a conic's quadratic, see fx_conic_t
-  static __device__ __forceinline__ void g_abs17(int& g, double v) {
-    g = min(g, (__double2hiint(v) & 0x7fffffff) + (OLRT_FX_GHI - 0x3EE00000));
+  // |a| > 2^-20 |b| ?  -- conditioning of the conic's quadratic, see fx_conic_t
+  static __device__ __forceinline__ void g_ratio20(int& g, double a, double b) {
+    g = min(g, (__double2hiint(a) & 0x7fffffff) - (__double2hiint(b) & 0x7fffffff) + ((20 << 20) + OLRT_FX_GHI));
   }
 };
 // fp32: the hardware's approximate reciprocal / rsqrt / sqrt (1-2 ulp, one MUFU each; 0 -> inf / 0, negative -> NaN
@@ -112,7 +112,7 @@ template <> struct FxMath<float> {
   static __device__ __forceinline__ void g_abs(int&, float) {}
   static __device__ __forceinline__ void g_ratio18(int&, float, float) {}
   static __device__ __forceinline__ void g_abs12(int&, float) {}
-  static __device__ __forceinline__ void g_abs17(int&, float) {}
+  static __device__ __forceinline__ void g_ratio20(int&, float, float) {}
 };
 
 // exp() of a Beer-Lambert exponent (homogeneous.py:49: -(4 pi k / lambda) t 1e3). Through optical glass it is a small
@@ -260,12 +260,14 @@ __device__ __forceinline__ R fx_conic_t(R x, R y, R z, R L, R M, R N, const FxSu
     a = fma(k, NN, a);
     hb = fma(k * N, z, hb);
     c = fma(k * z, z, c);
-    // a -> 0 (k = -1 and a ray nearly along the axis, an asymptotic direction of a hyperboloid): the REFERENCE's
-    // (-b + sqrt d) / 2a cancels, and its t carries rounding noise of ~4e-16 / a relative that no other evaluation
-    // order reproduces (measured: 3.5 relative at 1e-7 rad from a paraboloid's axis, 1e-9 at 1e-2 rad). Those rays
-    // take the strict build's value, i.e. the reference's own: band 2^-17 on |a|
-    Mx::g_abs17(guard, a);
   }
+  // Conditioning, not a decision: the REFERENCE's root (-b + sqrt d) / 2a cancels when |b / a| is large -- a -> 0 (k = -1
+  // and a ray nearly along the axis, an asymptotic direction of a hyperboloid) or a huge radius (b ~ N R: a "flat"
+  // surface entered as R = 1e10) -- and its t then carries rounding noise of ~5 ulp(1) |b / a| ABSOLUTE that no other
+  // evaluation order reproduces (measured against the strict build: 3.5 relative at 1e-7 rad from a paraboloid's
+  // axis; 1.6e-17 R relative on weak spheres, i.e. 1.7e-7 at R = 1e10). Rays with |a| < 2^-20 |b| take the strict
+  // build's value, which is the reference's own
+  Mx::g_ratio20(guard, a, hb);
   const R sd = Mx::sqrt_(fma(hb, hb, -(a * c)));  // miss: NaN
   const R ra = Mx::rcp(a);
   const R t1 = (sd - hb) * ra, t2 = (-hb - sd) * ra;
